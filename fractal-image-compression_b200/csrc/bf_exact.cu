@@ -1,0 +1,480 @@
+// Brute-force encoder, exact scan path (CUDA cores).
+//
+// Replaces the scan of bruteforce/jit_bfencoder.py:32-95 (mode 1) and bruteforce/bf_encoder.py:29-71
+// (mode 0): every range block against every lattice position under the 8 isometries, the reference's
+// scalar arithmetic replayed bit for bit (scorer.cuh), first strict minimum in scan order.
+//
+// This path is (a) the parity baseline for the tensor-core screen in bf_screen.cu, (b) the producer of
+// the per-range upper bounds the screen needs, (c) the fallback for ranges the screen cannot decide and
+// (d) the only path for NumPy semantics, strides != 1 and range sizes != 8.
+//
+// Data layout in HBM (8x8 ranges):
+//   boxsum  uint16 [(H-1),(W-1)]   P[y][x] = sum of the 2x2 pixel cell at (y,x); the pooled domain at
+//                                  (di,dj) is D4[a][b] = P[di+2a][dj+2b] = 4*d  (integers <= 1020)
+//   stats   per stride-1 position p = di*(W-16)+dj, structure of arrays:
+//             sd4  uint32 [NP]     sum of D4  (4 * float32 domain_sum, exact)
+//             sq4  uint32 [NP]     sum of D4^2 (16 * exact sum of d^2, NumPy mode)
+//             sdd  float  [8][NP]  float32 SEQUENTIAL sum of d*d in the row-major order of each
+//                                  isometry -- the one order-dependent quantity (jit_bfencoder.py:54)
+//   partial BestRec [ranges][chunks]  per-CTA winners, reduced by bf_finalize_kernel
+//
+// For 8x8 blocks everything else is exact: sum d*r < 2^24 quarter-units, so float32 sequential == integer.
+#include "fic_common.cuh"
+#include "scorer.cuh"
+
+#define BF_THREADS 256
+#define BF_G 8  // ranges per CTA
+#define BF_SCAN_DYN_SMEM (BF_G * BF_THREADS * (sizeof(double) + sizeof(uint32_t)))
+
+struct BfGeom {
+    int H, W;        // image
+    int npi, npj;    // lattice size
+    int si, sj;      // lattice strides
+    int PW;          // W-16 : positions per row at stride 1
+    int BW;          // W-1  : boxsum row pitch
+};
+
+// ---- prep: box sums -------------------------------------------------------------------------
+__global__ void bf_boxsum_kernel(const uint8_t* __restrict__ img, int H, int W, uint16_t* __restrict__ P)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (x >= W - 1 || y >= H - 1) return;
+    const uint8_t* p = img + (size_t)y * W + x;
+    P[(size_t)y * (W - 1) + x] = (uint16_t)((int)p[0] + p[1] + p[W] + p[W + 1]);
+}
+
+// ---- prep: per-position statistics (stride-1 positions) ---------------------------------------
+__global__ void bf_stats_kernel(const uint16_t* __restrict__ P, int H, int W, uint32_t* __restrict__ sd4,
+                                uint32_t* __restrict__ sq4, float* __restrict__ sdd)
+{
+    const int PW = W - 16, PH = H - 16, BW = W - 1;
+    const int NP = PW * PH;
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= NP) return;
+    int di = p / PW, dj = p - di * PW;
+    float sq[64];
+    uint32_t s = 0, s2 = 0;
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            uint32_t v = P[(size_t)(di + 2 * a) * BW + dj + 2 * b];
+            s += v;
+            s2 += v * v;
+            float d = __fmul_rn((float)v, 0.25f);
+            sq[a * 8 + b] = __fmul_rn(d, d);  // exact: v^2/16 < 2^24 significant bits
+        }
+    sd4[p] = s;
+    sq4[p] = s2;
+    for (int t = 0; t < 8; ++t) {
+        float acc = 0.f;
+        for (int i = 0; i < 8; ++i)
+            for (int j = 0; j < 8; ++j) {
+                int sa, sb;
+                fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
+                acc = __fadd_rn(acc, sq[sa * 8 + sb]);
+            }
+        sdd[(size_t)t * NP + p] = acc;
+    }
+}
+
+// ---- the scan ---------------------------------------------------------------------------------
+// grid = (range groups, chunks).  Each thread walks lattice positions q = chunk*chunk_len + tid + k*256,
+// keeps the 64 D4 values of its position in registers and scores the CTA's BF_G ranges x 8 isometries.
+template <int MODE>
+__global__ void __launch_bounds__(BF_THREADS)
+bf_scan8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
+                const uint32_t* __restrict__ sq4, const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
+                const int32_t* __restrict__ range_list, int chunk_len, int n_chunks, BestRec* __restrict__ partial)
+{
+    __shared__ __align__(16) float rv[BF_G][8][64];  // inverse-transformed range blocks
+    __shared__ double r_sum[BF_G], r_sq[BF_G];
+    __shared__ BestRec red[BF_G][BF_THREADS / 32];
+
+    const int tid = threadIdx.x;
+    const int grp = blockIdx.x, chunk = blockIdx.y;
+    const int rw = g.W / 8;
+    const int NP = g.PW * (g.H - 16);
+
+    // stage the ranges: rv[gi][t][sa*8+sb] = r[i][j] where (sa,sb) = iso_t(i,j)
+    for (int e = tid; e < BF_G * 8 * 64; e += BF_THREADS) {
+        int gi = e / 512, t = (e >> 6) & 7, k = e & 63;
+        int slot = grp * BF_G + gi;
+        float v = 0.f;
+        int sa = 0, sb = 0;
+        fic_iso_bf(t >> 2, t & 3, 8, k >> 3, k & 7, sa, sb);
+        if (slot < n_ranges) {
+            int ridx = range_list ? range_list[slot] : range_begin + slot;
+            int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+            v = (float)img[(size_t)(ri + (k >> 3)) * g.W + rj + (k & 7)];
+        }
+        rv[gi][t][sa * 8 + sb] = v;
+    }
+    if (tid < BF_G) {
+        int slot = grp * BF_G + tid;
+        unsigned long long s = 0, q = 0;
+        if (slot < n_ranges) {
+            int ridx = range_list ? range_list[slot] : range_begin + slot;
+            int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+            for (int k = 0; k < 64; ++k) {
+                unsigned v = img[(size_t)(ri + (k >> 3)) * g.W + rj + (k & 7)];
+                s += v;
+                q += MODE == FIC_BF_MODE_JIT ? v * v : ((v * v) & 255u);  // bf_encoder.py:33 wraps in uint8
+            }
+        }
+        r_sum[tid] = (double)s;
+        r_sq[tid] = (double)q;
+    }
+    __syncthreads();
+
+    // per-thread running winners live in shared memory ([range][thread], conflict-free) so the range loop can
+    // stay rolled; they are pulled into registers once per (position, range) and written back on change only
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    double* sBestR = reinterpret_cast<double*>(dyn_smem);                           // [BF_G][BF_THREADS]
+    uint32_t* sBestSeq = reinterpret_cast<uint32_t*>(sBestR + BF_G * BF_THREADS);   // [BF_G][BF_THREADS]
+#pragma unroll
+    for (int gi = 0; gi < BF_G; ++gi) {
+        sBestR[gi * BF_THREADS + tid] = __longlong_as_double(0x7ff0000000000000ll);
+        sBestSeq[gi * BF_THREADS + tid] = 0xffffffffu;
+    }
+
+    const long long nq = (long long)g.npi * g.npj;
+    const long long q0 = (long long)chunk * chunk_len;
+    long long q1 = q0 + chunk_len;
+    if (q1 > nq) q1 = nq;
+
+    for (long long q = q0 + tid; q < q1; q += BF_THREADS) {
+        int pi = (int)(q / g.npj), pj = (int)(q - (long long)pi * g.npj);
+        int di = pi * g.si, dj = pj * g.sj;
+        size_t p = (size_t)di * g.PW + dj;
+        float D[64];
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+            for (int b = 0; b < 8; ++b) D[a * 8 + b] = (float)P[(size_t)(di + 2 * a) * g.BW + dj + 2 * b];
+        const float dsf = __fmul_rn((float)sd4[p], 0.25f);
+        const double ds = (double)dsf;
+        float sds_t[8];
+        double dsds = 0.0, sds_np = 0.0;
+        if (MODE == FIC_BF_MODE_JIT) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) sds_t[t] = sdd[(size_t)t * NP + p];
+            dsds = (double)__fmul_rn(dsf, dsf);
+        } else {
+            sds_np = DM((double)sq4[p], 0.0625);
+        }
+#pragma unroll 1
+        for (int gi = 0; gi < BF_G; ++gi) {
+            const double rs = r_sum[gi], sqr = r_sq[gi];
+            double bR = sBestR[gi * BF_THREADS + tid];
+            uint32_t bSeq = sBestSeq[gi * BF_THREADS + tid];
+            bool changed = false;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const float4* rp = reinterpret_cast<const float4*>(&rv[gi][t][0]);
+                float x0 = 0.f, x1 = 0.f, x2 = 0.f, x3 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    float4 r4 = rp[k];
+                    x0 = fmaf(r4.x, D[4 * k + 0], x0);  // integers < 2^24: every partial sum is exact
+                    x1 = fmaf(r4.y, D[4 * k + 1], x1);
+                    x2 = fmaf(r4.z, D[4 * k + 2], x2);
+                    x3 = fmaf(r4.w, D[4 * k + 3], x3);
+                }
+                const double ab = DM((double)((x0 + x1) + (x2 + x3)), 0.25);
+                BfScore sc;
+                if (MODE == FIC_BF_MODE_JIT) sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, ds, (double)sds_t[t], dsds, ab);
+                else sc = fic_bfnp_score(64.0, 0.015625, rs, sqr, ds, sds_np, ab);
+                uint32_t seq = (uint32_t)q * 8u + t;
+                if (fic_better(sc.R, seq, bR, bSeq)) {
+                    bR = sc.R;
+                    bSeq = seq;
+                    changed = true;
+                }
+            }
+            if (changed) {
+                sBestR[gi * BF_THREADS + tid] = bR;
+                sBestSeq[gi * BF_THREADS + tid] = bSeq;
+            }
+        }
+    }
+
+    // CTA reduction per range
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll 1
+    for (int gi = 0; gi < BF_G; ++gi) {
+        double R = sBestR[gi * BF_THREADS + tid];
+        uint32_t sq_ = sBestSeq[gi * BF_THREADS + tid];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            double oR = __shfl_xor_sync(0xffffffffu, R, off);
+            uint32_t oS = __shfl_xor_sync(0xffffffffu, sq_, off);
+            if (fic_better(oR, oS, R, sq_)) { R = oR; sq_ = oS; }
+        }
+        if (lane == 0) { red[gi][warp].R = R; red[gi][warp].seq = sq_ == 0xffffffffu ? ~0ull : (unsigned long long)sq_; }
+    }
+    __syncthreads();
+    if (tid < BF_G) {
+        int slot = grp * BF_G + tid;
+        if (slot < n_ranges) {
+            BestRec b = red[tid][0];
+            for (int w = 1; w < BF_THREADS / 32; ++w)
+                if (fic_better(red[tid][w].R, red[tid][w].seq, b.R, b.seq)) b = red[tid][w];
+            partial[(size_t)slot * n_chunks + chunk] = b;
+        }
+    }
+}
+
+// One thread per range: reduce the chunk winners, decode the scan index, re-score the winner for (s, o).
+template <int MODE>
+__global__ void bf_finalize8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
+                                    const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4,
+                                    const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
+                                    const int32_t* __restrict__ range_list, int n_chunks, const BestRec* __restrict__ partial,
+                                    int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+{
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_ranges) return;
+    BestRec b = partial[(size_t)slot * n_chunks];
+    for (int c = 1; c < n_chunks; ++c) {
+        BestRec o = partial[(size_t)slot * n_chunks + c];
+        if (fic_better(o.R, o.seq, b.R, b.seq)) b = o;
+    }
+    int ridx = range_list ? range_list[slot] : range_begin + slot;
+    // with a range list the outputs are indexed by absolute range number minus range_begin
+    size_t oslot = range_list ? (size_t)(ridx - range_begin) : (size_t)slot;
+    if (b.seq == ~0ull) {  // nothing scanned / nothing finite: jit_bfencoder.py:35 keeps the zero tuple
+        for (int k = 0; k < 4; ++k) out_idx[4 * oslot + k] = 0;
+        out_so[2 * oslot] = 0.0;
+        out_so[2 * oslot + 1] = 0.0;
+        if (out_R) out_R[oslot] = 0.0;
+        return;
+    }
+    int t = (int)(b.seq & 7ull);
+    long long q = (long long)(b.seq >> 3);
+    int pi = (int)(q / g.npj), pj = (int)(q - (long long)pi * g.npj);
+    int di = pi * g.si, dj = pj * g.sj;
+    size_t p = (size_t)di * g.PW + dj;
+    const int NP = g.PW * (g.H - 16);
+    const int rw = g.W / 8;
+    int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+    unsigned long long rs = 0, sq = 0;
+    long long x = 0;
+    for (int i = 0; i < 8; ++i)
+        for (int j = 0; j < 8; ++j) {
+            unsigned v = img[(size_t)(ri + i) * g.W + rj + j];
+            rs += v;
+            sq += MODE == FIC_BF_MODE_JIT ? v * v : ((v * v) & 255u);
+            int sa, sb;
+            fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
+            x += (long long)v * P[(size_t)(di + 2 * sa) * g.BW + dj + 2 * sb];
+        }
+    const double ds = (double)__fmul_rn((float)sd4[p], 0.25f);
+    const double ab = DM((double)x, 0.25);
+    BfScore sc;
+    if (MODE == FIC_BF_MODE_JIT) {
+        float dsf = __fmul_rn((float)sd4[p], 0.25f);
+        sc = fic_bfjit_score(64.0, 0.015625, (double)rs, (double)sq, ds, (double)sdd[(size_t)t * NP + p],
+                             (double)__fmul_rn(dsf, dsf), ab);
+    } else {
+        sc = fic_bfnp_score(64.0, 0.015625, (double)rs, (double)sq, ds, DM((double)sq4[p], 0.0625), ab);
+    }
+    out_idx[4 * oslot + 0] = di;
+    out_idx[4 * oslot + 1] = dj;
+    out_idx[4 * oslot + 2] = t >> 2;
+    out_idx[4 * oslot + 3] = t & 3;
+    out_so[2 * oslot] = sc.s;
+    out_so[2 * oslot + 1] = sc.o;
+    if (out_R) out_R[oslot] = sc.R;
+}
+
+// ---- generic range size: sequential replay straight from the image ----------------------------
+// One CTA per range, threads over lattice positions, the 8 isometries inside.  float32 sequential sums in
+// the row-major order of the oriented pooled block (jit) or exact integer sums (numpy).
+template <int MODE>
+__global__ void __launch_bounds__(BF_THREADS)
+bf_scan_generic_kernel(const uint8_t* __restrict__ img, int H, int W, int R, int si, int sj, int npi, int npj,
+                       int range_begin, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                       double* __restrict__ out_R)
+{
+    __shared__ BestRec red[BF_THREADS / 32];
+    __shared__ double red_s[BF_THREADS / 32], red_o[BF_THREADS / 32];
+    const int tid = threadIdx.x;
+    const int slot = blockIdx.x;
+    const int ridx = range_begin + slot;
+    const int rw = W / R;
+    const int ri = (ridx / rw) * R, rj = (ridx % rw) * R;
+    const int nn = R * R;
+    const double n = (double)nn, inv_n = DD(1.0, n);
+    unsigned long long rs = 0, sq = 0;
+    for (int k = 0; k < nn; ++k) {
+        unsigned v = img[(size_t)(ri + k / R) * W + rj + k % R];
+        rs += v;
+        sq += MODE == FIC_BF_MODE_JIT ? v * v : ((v * v) & 255u);
+    }
+    double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
+    unsigned long long bseq = ~0ull;
+    const long long nq = (long long)npi * npj;
+    for (long long q = tid; q < nq; q += BF_THREADS) {
+        int pi = (int)(q / npj), pj = (int)(q - (long long)pi * npj);
+        int di = pi * si, dj = pj * sj;
+        for (int t = 0; t < 8; ++t) {
+            float dsf = 0.f, sdsf = 0.f, abf = 0.f;
+            long long isd = 0, isq = 0, iab = 0;
+            for (int i = 0; i < R; ++i)
+                for (int j = 0; j < R; ++j) {
+                    int sa, sb;
+                    fic_iso_bf(t >> 2, t & 3, R, i, j, sa, sb);
+                    const uint8_t* pp = img + (size_t)(di + 2 * sa) * W + dj + 2 * sb;
+                    int d4 = (int)pp[0] + pp[1] + pp[W] + pp[W + 1];
+                    unsigned rvv = img[(size_t)(ri + i) * W + rj + j];
+                    if (MODE == FIC_BF_MODE_JIT) {
+                        float d = __fmul_rn((float)d4, 0.25f);
+                        dsf = __fadd_rn(dsf, d);
+                        sdsf = __fadd_rn(sdsf, __fmul_rn(d, d));
+                        abf = __fadd_rn(abf, __fmul_rn(d, (float)rvv));
+                    } else {
+                        isd += d4;
+                        isq += (long long)d4 * d4;
+                        iab += (long long)d4 * rvv;
+                    }
+                }
+            BfScore sc;
+            if (MODE == FIC_BF_MODE_JIT)
+                sc = fic_bfjit_score(n, inv_n, (double)rs, (double)sq, (double)dsf, (double)sdsf,
+                                     (double)__fmul_rn(dsf, dsf), (double)abf);
+            else
+                sc = fic_bfnp_score(n, inv_n, (double)rs, (double)sq, DM((double)isd, 0.25), DM((double)isq, 0.0625),
+                                    DM((double)iab, 0.25));
+            unsigned long long seq = (unsigned long long)q * 8ull + t;
+            if (fic_better(sc.R, seq, bR, bseq)) { bR = sc.R; bseq = seq; bs = sc.s; bo = sc.o; }
+        }
+    }
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        double oR = __shfl_xor_sync(0xffffffffu, bR, off);
+        unsigned long long oS = __shfl_xor_sync(0xffffffffu, bseq, off);
+        double os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
+        if (fic_better(oR, oS, bR, bseq)) { bR = oR; bseq = oS; bs = os; bo = oo; }
+    }
+    if (lane == 0) { red[warp].R = bR; red[warp].seq = bseq; red_s[warp] = bs; red_o[warp] = bo; }
+    __syncthreads();
+    if (tid == 0) {
+        BestRec b = red[0];
+        double s = red_s[0], o = red_o[0];
+        for (int w = 1; w < BF_THREADS / 32; ++w)
+            if (fic_better(red[w].R, red[w].seq, b.R, b.seq)) { b = red[w]; s = red_s[w]; o = red_o[w]; }
+        if (b.seq == ~0ull) {
+            for (int k = 0; k < 4; ++k) out_idx[4 * (size_t)slot + k] = 0;
+            out_so[2 * (size_t)slot] = 0.0; out_so[2 * (size_t)slot + 1] = 0.0;
+            if (out_R) out_R[slot] = 0.0;
+        } else {
+            int t = (int)(b.seq & 7ull);
+            long long q = (long long)(b.seq >> 3);
+            int pi = (int)(q / npj), pj = (int)(q - (long long)pi * npj);
+            out_idx[4 * (size_t)slot + 0] = pi * si;
+            out_idx[4 * (size_t)slot + 1] = pj * sj;
+            out_idx[4 * (size_t)slot + 2] = t >> 2;
+            out_idx[4 * (size_t)slot + 3] = t & 3;
+            out_so[2 * (size_t)slot] = s;
+            out_so[2 * (size_t)slot + 1] = o;
+            if (out_R) out_R[slot] = b.R;
+        }
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// Builds boxsum + stats for an 8x8 encode (shared with the screen path).
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st)
+{
+    const int PW = W - 16, PH = H - 16;
+    FIC_TRY(h->bf_boxsum.reserve((size_t)(H - 1) * (W - 1) * sizeof(uint16_t)));
+    dim3 gb(ceil_div(W - 1, 256), H - 1);
+    bf_boxsum_kernel<<<gb, 256, 0, st>>>(d_img, H, W, h->bf_boxsum.as<uint16_t>());
+    FIC_CHECK_LAUNCH(h, "bf_boxsum_kernel");
+    if (PW > 0 && PH > 0) {
+        size_t NP = (size_t)PW * PH;
+        FIC_TRY(h->bf_stats.reserve(NP * (2 * sizeof(uint32_t) + 8 * sizeof(float))));
+        uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+        uint32_t* sq4 = sd4 + NP;
+        float* sdd = reinterpret_cast<float*>(sq4 + NP);
+        bf_stats_kernel<<<ceil_div(NP, 128), 128, 0, st>>>(h->bf_boxsum.as<uint16_t>(), H, W, sd4, sq4, sdd);
+        FIC_CHECK_LAUNCH(h, "bf_stats_kernel");
+    }
+    return FIC_OK;
+}
+
+// Exact scan of `n_ranges` ranges (contiguous from range_begin, or the explicit device list) over the lattice
+// with strides (si,sj).  Outputs are written at index (range - range_begin).  Requires bf_prepare8.
+int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int mode, int range_begin,
+                   int n_ranges, const int32_t* d_range_list, int32_t* d_idx, double* d_so, double* d_R,
+                   cudaStream_t st)
+{
+    if (n_ranges <= 0) return FIC_OK;
+    BfGeom g;
+    g.H = H; g.W = W; g.si = si; g.sj = sj; g.PW = W - 16; g.BW = W - 1;
+    g.npi = H - 16 > 0 ? ceil_div(H - 16, si) : 0;
+    g.npj = W - 16 > 0 ? ceil_div(W - 16, sj) : 0;
+    const long long nq = (long long)g.npi * g.npj;
+    const int groups = ceil_div(n_ranges, BF_G);
+    // enough CTAs for ~8 waves of 148 SMs x 2, but never less than 4 positions per thread
+    int n_chunks = 1;
+    if (nq > 0) {
+        long long want = (long long)h->num_sms * 16;
+        n_chunks = (int)((want + groups - 1) / groups);
+        int max_chunks = ceil_div(nq, BF_THREADS * 4);
+        if (n_chunks > max_chunks) n_chunks = max_chunks;
+        if (n_chunks < 1) n_chunks = 1;
+        if (n_chunks > 65535) n_chunks = 65535;
+    }
+    int chunk_len = nq > 0 ? ceil_div(nq, n_chunks) : 1;
+    chunk_len = ceil_div(chunk_len, BF_THREADS) * BF_THREADS;
+    n_chunks = nq > 0 ? ceil_div(nq, chunk_len) : 1;
+    FIC_TRY(h->bf_partial.reserve((size_t)n_ranges * n_chunks * sizeof(BestRec)));
+    const size_t NP = (size_t)(W - 16 > 0 ? W - 16 : 0) * (size_t)(H - 16 > 0 ? H - 16 : 0);
+    const uint16_t* P = h->bf_boxsum.as<uint16_t>();
+    const uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    const uint32_t* sq4 = sd4 + NP;
+    const float* sdd = reinterpret_cast<const float*>(sq4 + NP);
+    BestRec* partial = h->bf_partial.as<BestRec>();
+    dim3 grid(groups, n_chunks);
+    if (mode == FIC_BF_MODE_JIT) {
+        {
+            ProfScope prof(h, st);
+            bf_scan8_kernel<FIC_BF_MODE_JIT><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                      d_range_list, chunk_len, n_chunks, partial);
+        }
+        FIC_CHECK_LAUNCH(h, "bf_scan8_kernel<jit>");
+        bf_finalize8_kernel<FIC_BF_MODE_JIT><<<ceil_div(n_ranges, 128), 128, 0, st>>>(
+            d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges, d_range_list, n_chunks, partial, d_idx, d_so, d_R);
+        FIC_CHECK_LAUNCH(h, "bf_finalize8_kernel<jit>");
+    } else {
+        bf_scan8_kernel<FIC_BF_MODE_NUMPY><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                        d_range_list, chunk_len, n_chunks, partial);
+        FIC_CHECK_LAUNCH(h, "bf_scan8_kernel<numpy>");
+        bf_finalize8_kernel<FIC_BF_MODE_NUMPY><<<ceil_div(n_ranges, 128), 128, 0, st>>>(
+            d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges, d_range_list, n_chunks, partial, d_idx, d_so, d_R);
+        FIC_CHECK_LAUNCH(h, "bf_finalize8_kernel<numpy>");
+    }
+    return FIC_OK;
+}
+
+int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
+                     int range_begin, int n_ranges, int32_t* d_idx, double* d_so, double* d_R, cudaStream_t st)
+{
+    if (n_ranges <= 0) return FIC_OK;
+    const int D = 2 * range;
+    int npi = H - D > 0 ? ceil_div(H - D, si) : 0, npj = W - D > 0 ? ceil_div(W - D, sj) : 0;
+    if (mode == FIC_BF_MODE_JIT)
+        bf_scan_generic_kernel<FIC_BF_MODE_JIT><<<n_ranges, BF_THREADS, 0, st>>>(d_img, H, W, range, si, sj, npi, npj,
+                                                                                 range_begin, d_idx, d_so, d_R);
+    else
+        bf_scan_generic_kernel<FIC_BF_MODE_NUMPY><<<n_ranges, BF_THREADS, 0, st>>>(d_img, H, W, range, si, sj, npi, npj,
+                                                                                   range_begin, d_idx, d_so, d_R);
+    FIC_CHECK_LAUNCH(h, "bf_scan_generic_kernel");
+    return FIC_OK;
+}

@@ -1,0 +1,326 @@
+// Decoders and the 2x2 pooling primitive.
+//
+//  * bf_decode_*   bruteforce/decoder.py:12-32 -- float32 image, sweep 1 from zeros, then IN PLACE in range
+//                  order (the reference aliases img and next_img at decoder.py:30), int-truncating pool
+//                  (utils.py:22), unclipped uint8 cast.  The in-place order is reproduced exactly with a level
+//                  schedule: range k may run once every earlier range it reads from (RAW), every earlier range
+//                  that reads its target block (WAR) and every earlier writer of the same block (WAW) is done.
+//  * tree_decode_* quadtree/decoder.py:34-116 and hvv2/decoder.py:29-89 -- true Jacobi sweeps in float64, one
+//                  thread per output pixel through a pixel->leaf map, coalesced row-major writes.
+//  * subsample     utils.py:13-34.
+//
+// HBM traffic per Jacobi sweep: H*W*(4 gathered reads + 1 write)*8 B + 4 B leaf id + 48 B per leaf record.
+#include <algorithm>
+
+#include "fic_common.cuh"
+#include "scorer.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// brute-force decoder
+// ------------------------------------------------------------------------------------------------
+#define BFD_THREADS 1024
+#define BFD_RANGES_PER_STEP (BFD_THREADS / 64)
+
+__global__ void __launch_bounds__(BFD_THREADS)
+bf_decode_kernel(const int32_t* __restrict__ idx, const double* __restrict__ so, const int32_t* __restrict__ order,
+                 const int32_t* __restrict__ level_start, int n_levels, int width, int height, int iterations,
+                 float* __restrict__ buf, uint8_t* __restrict__ out)
+{
+    const int tid = threadIdx.x;
+    const int sub = tid >> 6, px = tid & 63;
+    const int a = px >> 3, b = px & 7;
+    for (int it = 0; it < iterations; ++it) {
+        for (int lv = 0; lv < n_levels; ++lv) {
+            const int l0 = level_start[lv], l1 = level_start[lv + 1];
+            for (int base = l0; base < l1; base += BFD_RANGES_PER_STEP) {
+                const int e = base + sub;
+                float val = 0.f;
+                int dst = -1;
+                if (e < l1) {
+                    const int k = order[e];
+                    const int range_i = (k / (width / 8)) * 8;   // decoder.py:19
+                    const int range_j = (k % (height / 8)) * 8;  // decoder.py:20 (sic)
+                    const int di = idx[4 * k], dj = idx[4 * k + 1], orient = idx[4 * k + 2], rot = idx[4 * k + 3];
+                    int acc = 0;
+                    if (it > 0) {  // sweep 1 reads the all-zero image
+#pragma unroll
+                        for (int u = 0; u < 2; ++u)
+#pragma unroll
+                            for (int v = 0; v < 2; ++v) {
+                                int sa, sb;
+                                fic_iso_bf(orient, rot, 16, 2 * a + u, 2 * b + v, sa, sb);
+                                acc += __float2int_rz(buf[(size_t)(di + sa) * width + dj + sb]);  // astype(int32), utils.py:22
+                            }
+                    }
+                    double v64 = DA(DM(DM((double)acc, 0.25), so[2 * k]), so[2 * k + 1]);
+                    val = __double2float_rn(v64);
+                    dst = (range_i + a) * width + range_j + b;
+                }
+                __syncthreads();  // every read of this step happens before any write of it
+                if (dst >= 0) buf[dst] = val;
+                __syncthreads();
+            }
+        }
+    }
+    for (int p = tid; p < width * height; p += BFD_THREADS) out[p] = (uint8_t)__float2int_rz(buf[p]);
+}
+
+int bf_decode_impl(fic_handle* h, const int32_t* h_idx, const int32_t* d_idx, const double* d_so, int n, int width,
+                   int height, int iterations, uint8_t* d_out, cudaStream_t st)
+{
+    const int bw = width / 8, bh = height / 8;
+    // level schedule over 8x8 blocks
+    std::vector<int> last_write((size_t)bw * bh, -1), last_read((size_t)bw * bh, -1), level(n, 0);
+    int n_levels = 0;
+    for (int k = 0; k < n; ++k) {
+        const int wi = k / bw, wj = k % bh;  // block coordinates of the target
+        const int di = h_idx[4 * k], dj = h_idx[4 * k + 1];
+        const int b0i = di / 8, b1i = (di + 15) / 8, b0j = dj / 8, b1j = (dj + 15) / 8;
+        int lv = 0;
+        for (int bi = b0i; bi <= b1i; ++bi)
+            for (int bj = b0j; bj <= b1j; ++bj) lv = std::max(lv, last_write[(size_t)bi * bw + bj] + 1);  // RAW
+        const size_t wb = (size_t)wi * bw + wj;
+        lv = std::max(lv, last_read[wb] + 1);   // WAR (reads of this very range do not count: registered below)
+        lv = std::max(lv, last_write[wb] + 1);  // WAW
+        level[k] = lv;
+        for (int bi = b0i; bi <= b1i; ++bi)
+            for (int bj = b0j; bj <= b1j; ++bj) last_read[(size_t)bi * bw + bj] = std::max(last_read[(size_t)bi * bw + bj], lv);
+        last_write[wb] = lv;
+        n_levels = std::max(n_levels, lv + 1);
+    }
+    // a range that reads its own target block: its reads precede its write inside one step, which the kernel
+    // guarantees; but a LATER range in the same level must not read that block -- excluded by RAW above.
+    std::vector<int32_t> sched((size_t)n + n_levels + 1);
+    int32_t* level_start = sched.data();
+    int32_t* order = sched.data() + n_levels + 1;
+    std::fill(level_start, level_start + n_levels + 1, 0);
+    for (int k = 0; k < n; ++k) level_start[level[k] + 1]++;
+    for (int l = 0; l < n_levels; ++l) level_start[l + 1] += level_start[l];
+    {
+        std::vector<int32_t> cur(level_start, level_start + n_levels);
+        for (int k = 0; k < n; ++k) order[cur[level[k]]++] = k;
+    }
+    FIC_TRY(h->dec_sched.reserve(sched.size() * sizeof(int32_t) + 16));
+    FIC_TRY(h->pin_b.reserve(sched.size() * sizeof(int32_t) + 16));
+    memcpy(h->pin_b.p, sched.data(), sched.size() * sizeof(int32_t));
+    FIC_TRY(fic_copy_in(h, h->dec_sched.p, h->pin_b.p, sched.size() * sizeof(int32_t), false, st));
+    FIC_TRY(h->dec_img.reserve((size_t)width * height * sizeof(float)));
+    FIC_CUDA(cudaMemsetAsync(h->dec_img.p, 0, (size_t)width * height * sizeof(float), st));
+    const int32_t* d_sched = h->dec_sched.as<int32_t>();
+    bf_decode_kernel<<<1, BFD_THREADS, 0, st>>>(d_idx, d_so, d_sched + n_levels + 1, d_sched, n_levels, width, height,
+                                                iterations, h->dec_img.as<float>(), d_out);
+    FIC_CHECK_LAUNCH(h, "bf_decode_kernel");
+    // pin_b is reused by the next call: make sure the upload has been consumed
+    FIC_CUDA(cudaStreamSynchronize(st));
+    return FIC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// quadtree / HV Jacobi decoder
+// ------------------------------------------------------------------------------------------------
+__global__ void tree_paint_kernel(const int32_t* __restrict__ leaves, int n, int W, int32_t* __restrict__ leaf_map)
+{
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int32_t* L = leaves + 8 * (size_t)k;
+    const int ri = L[0], rj = L[1], hh = L[2], ww = L[3];
+    for (int e = threadIdx.x; e < hh * ww; e += blockDim.x) {
+        int a = e / ww, b = e - a * ww;
+        leaf_map[(size_t)(ri + a) * W + rj + b] = k;
+    }
+}
+
+#define TD_THREADS 256
+
+template <int KIND, bool REDUCE>
+__global__ void __launch_bounds__(TD_THREADS)
+tree_sweep_kernel(const int32_t* __restrict__ leaves, const double* __restrict__ so, const int32_t* __restrict__ leaf_map,
+                  int H, int W, int f32_affine, const double* __restrict__ img, double* __restrict__ next,
+                  double* __restrict__ red)
+{
+    const size_t p = (size_t)blockIdx.x * TD_THREADS + threadIdx.x;
+    double e2 = 0.0, s2 = 0.0;
+    if (p < (size_t)H * W) {
+        const int k = leaf_map[p];
+        if (k >= 0) {
+            const int y = (int)(p / W), x = (int)(p - (size_t)y * W);
+            const int4 L0 = *reinterpret_cast<const int4*>(leaves + 8 * (size_t)k);
+            const int4 L1 = *reinterpret_cast<const int4*>(leaves + 8 * (size_t)k + 4);
+            const int a = y - L0.x, b = x - L0.y, hh = L0.z, ww = L0.w, di = L1.x, dj = L1.y, orient = L1.z, rot = L1.w;
+            const double scale = so[2 * (size_t)k], offset = so[2 * (size_t)k + 1];
+            double val;
+            if (KIND == FIC_TREE_QUADTREE) {
+                int acc = 0;
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int v = 0; v < 2; ++v) {
+                        int sa, sb;
+                        fic_iso_bf(orient, rot, 2 * hh, 2 * a + u, 2 * b + v, sa, sb);  // .T then rot90, decoder.py:102-104
+                        acc += __double2int_rz(img[(size_t)(di + sa) * W + dj + sb]);   // utils.py:22
+                    }
+                val = DA(DM(DM((double)acc, 0.25), scale), offset);
+            } else {
+                float q[4];
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int v = 0; v < 2; ++v) {
+                        int sa, sb;
+                        fic_iso_hv(orient, rot, 2 * hh, 2 * ww, 2 * a + u, 2 * b + v, sa, sb);
+                        q[u * 2 + v] = __double2float_rn(img[(size_t)(di + sa) * W + dj + sb]);
+                    }
+                float pooled = __fmul_rn(__fadd_rn(__fadd_rn(__fadd_rn(q[0], q[1]), q[2]), q[3]), 0.25f);  // utils.py:32-33
+                if (f32_affine)
+                    val = (double)__fadd_rn(__fmul_rn(pooled, __double2float_rn(scale)), __double2float_rn(offset));
+                else
+                    val = DA(DM((double)pooled, scale), offset);
+            }
+            next[p] = val;
+            if (REDUCE) {
+                double dlt = DS(val, img[p]);
+                e2 = DM(dlt, dlt);
+                s2 = DM(val, val);
+            }
+        } else if (REDUCE) {
+            // uncovered pixel: next stays what it was (zero here)
+            double v = next[p], dlt = DS(v, img[p]);
+            e2 = DM(dlt, dlt);
+            s2 = DM(v, v);
+        }
+    }
+    if (REDUCE) {
+        __shared__ double se[TD_THREADS / 32], ss[TD_THREADS / 32];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            e2 = DA(e2, __shfl_xor_sync(0xffffffffu, e2, off));
+            s2 = DA(s2, __shfl_xor_sync(0xffffffffu, s2, off));
+        }
+        if ((threadIdx.x & 31) == 0) { se[threadIdx.x >> 5] = e2; ss[threadIdx.x >> 5] = s2; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0, b = 0.0;
+            for (int w = 0; w < TD_THREADS / 32; ++w) { a = DA(a, se[w]); b = DA(b, ss[w]); }
+            red[2 * (size_t)blockIdx.x] = a;
+            red[2 * (size_t)blockIdx.x + 1] = b;
+        }
+    }
+}
+
+// fixed-order final sum of the per-CTA partials (deterministic run to run)
+__global__ void tree_reduce_kernel(const double* __restrict__ red, int nblocks, double* __restrict__ out2)
+{
+    __shared__ double se[256], ss[256];
+    double a = 0.0, b = 0.0;
+    for (int k = threadIdx.x; k < nblocks; k += 256) { a = DA(a, red[2 * (size_t)k]); b = DA(b, red[2 * (size_t)k + 1]); }
+    se[threadIdx.x] = a;
+    ss[threadIdx.x] = b;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) { se[threadIdx.x] = DA(se[threadIdx.x], se[threadIdx.x + off]); ss[threadIdx.x] = DA(ss[threadIdx.x], ss[threadIdx.x + off]); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out2[0] = se[0]; out2[1] = ss[0]; }
+}
+
+__global__ void tree_finish_kernel(const double* __restrict__ img, size_t npx, uint8_t* __restrict__ out)
+{
+    size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npx) return;
+    double v = img[p];
+    v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);  // clip(0., 255.), decoder.py:61
+    out[p] = (uint8_t)__double2int_rz(v);
+}
+
+template <int KIND>
+static int launch_sweep(fic_handle* h, bool reduce, const int32_t* leaves, const double* so, const int32_t* map, int H,
+                        int W, int f32_affine, const double* img, double* next, double* red, int nblocks, cudaStream_t st)
+{
+    if (reduce)
+        tree_sweep_kernel<KIND, true><<<nblocks, TD_THREADS, 0, st>>>(leaves, so, map, H, W, f32_affine, img, next, red);
+    else
+        tree_sweep_kernel<KIND, false><<<nblocks, TD_THREADS, 0, st>>>(leaves, so, map, H, W, f32_affine, img, next, red);
+    FIC_CHECK_LAUNCH(h, "tree_sweep_kernel");
+    return FIC_OK;
+}
+
+int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const double* d_so, int n, int H, int W,
+                     int iterations, double stop, int min_it, int max_it, int f32_affine, uint8_t* d_out,
+                     int32_t* iters_done, cudaStream_t st)
+{
+    const size_t npx = (size_t)H * W;
+    const int nblocks = (int)((npx + TD_THREADS - 1) / TD_THREADS);
+    FIC_TRY(h->dec_img.reserve(npx * sizeof(double)));
+    FIC_TRY(h->dec_next.reserve(npx * sizeof(double)));
+    FIC_TRY(h->dec_map.reserve(npx * sizeof(int32_t)));
+    FIC_TRY(h->dec_red.reserve(((size_t)nblocks * 2 + 2) * sizeof(double)));
+    FIC_TRY(h->pin_b.reserve(64));
+    FIC_CUDA(cudaMemsetAsync(h->dec_img.p, 0, npx * sizeof(double), st));
+    FIC_CUDA(cudaMemsetAsync(h->dec_next.p, 0, npx * sizeof(double), st));
+    FIC_CUDA(cudaMemsetAsync(h->dec_map.p, 0xff, npx * sizeof(int32_t), st));
+    if (n > 0) {
+        tree_paint_kernel<<<n, 64, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
+        FIC_CHECK_LAUNCH(h, "tree_paint_kernel");
+    }
+    double* img = h->dec_img.as<double>();
+    double* next = h->dec_next.as<double>();
+    double* red = h->dec_red.as<double>();
+    double* red_out = red + (size_t)nblocks * 2;
+    const int32_t* map = h->dec_map.as<int32_t>();
+    int done = 0;
+    auto sweep = [&](bool reduce) -> int {
+        int rc = kind == FIC_TREE_QUADTREE
+                     ? launch_sweep<FIC_TREE_QUADTREE>(h, reduce, d_leaves, d_so, map, H, W, f32_affine, img, next, red, nblocks, st)
+                     : launch_sweep<FIC_TREE_HV>(h, reduce, d_leaves, d_so, map, H, W, f32_affine, img, next, red, nblocks, st);
+        if (rc < 0) return rc;
+        std::swap(img, next);  // img[:] = next_img[:]; every covered pixel is rewritten each sweep
+        ++done;
+        return FIC_OK;
+    };
+    if (iterations == FIC_ITER_AUTO) {
+        for (int it = 0; it < min_it; ++it) FIC_TRY(sweep(false));
+        for (int it = min_it; it < max_it; ++it) {
+            FIC_TRY(sweep(true));
+            tree_reduce_kernel<<<1, 256, 0, st>>>(red, nblocks, red_out);
+            FIC_CHECK_LAUNCH(h, "tree_reduce_kernel");
+            double* hp = h->pin_b.as<double>();
+            FIC_TRY(fic_copy_out(h, hp, red_out, 2 * sizeof(double), false, st));
+            FIC_CUDA(cudaStreamSynchronize(st));
+            if (sqrt(hp[0]) / sqrt(hp[1]) < stop) break;  // decoder.py:45-49
+        }
+    } else {
+        for (int it = 0; it < iterations; ++it) FIC_TRY(sweep(false));
+    }
+    tree_finish_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(img, npx, d_out);
+    FIC_CHECK_LAUNCH(h, "tree_finish_kernel");
+    if (iters_done) *iters_done = done;
+    return FIC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// utils.average_subsample / average_subsample_jit
+// ------------------------------------------------------------------------------------------------
+__global__ void subsample_kernel(const double* __restrict__ arr, int h2, int w2, int jit, double* __restrict__ out)
+{
+    const int ow = w2 / 2, oh = h2 / 2;
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= ow * oh) return;
+    int a = e / ow, b = e - a * ow;
+    const double* p = arr + (size_t)(2 * a) * w2 + 2 * b;
+    if (jit) {
+        float s4 = __fadd_rn(__fadd_rn(__fadd_rn(__double2float_rn(p[0]), __double2float_rn(p[1])), __double2float_rn(p[w2])),
+                             __double2float_rn(p[w2 + 1]));
+        out[e] = (double)__fmul_rn(s4, 0.25f);
+    } else {
+        int acc = __double2int_rz(p[0]) + __double2int_rz(p[w2]) + __double2int_rz(p[1]) + __double2int_rz(p[w2 + 1]);
+        out[e] = DM((double)acc, 0.25);
+    }
+}
+
+int subsample_impl(fic_handle* h, const double* d_arr, int h2, int w2, int jit, double* d_out, cudaStream_t st)
+{
+    int n = (h2 / 2) * (w2 / 2);
+    subsample_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_arr, h2, w2, jit, d_out);
+    FIC_CHECK_LAUNCH(h, "subsample_kernel");
+    return FIC_OK;
+}

@@ -1,0 +1,68 @@
+"""`QuadtreeEncoder` (reference: quadtree/encoder.py:34-384) on the B200.
+
+The constructor signature and the returned `QuadtreeImage` are the reference's.  The work --
+integral-image classification of every domain and range (`_classify`), the 3x24 class pools
+(`_build_domain_list`), the per-level batched search with the float32-sequential scorer
+(`_find_min_err_domain`, `_find_optimal_mean_square_error`, `_calc_mean_square_error`) and the
+split decisions -- happens in `fic_qt_encode` (csrc/tree_encode.cu).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+import fic_b200
+from quadtree.common import EncodingInfo, QuadtreeImage, stream_to_forest
+
+NUM_MEAN_CLASSES = 3
+NUM_VARIANCE_CLASSES = 24
+POSITIVE = 1
+NEGATIVE = -1
+ZERO_TOLERANCE = 1e-6
+SAME_AS_SIDE = -1
+
+
+class QuadtreeEncoder:
+    def __init__(self, scale_bits: int, offset_bits: int, max_scale: float, full_class_search: bool,
+                 only_positive_scale: bool, min_range_side: int, max_range_side: int, error_tolerance: float,
+                 domain_hstep: int = SAME_AS_SIDE, domain_vstep: int = SAME_AS_SIDE) -> None:
+        self.scale_bits = scale_bits
+        self.offset_bits = offset_bits
+        self.max_scale = max_scale
+        self.full_class_search = full_class_search
+        self.only_positive_scale = only_positive_scale
+        self.min_range_side = min_range_side
+        self.max_range_side = max_range_side
+        self.min_range_exponent = int(np.log2(min_range_side))
+        self.max_range_exponent = int(np.log2(max_range_side))
+        self.error_tolerance = error_tolerance
+        self.domain_hstep = domain_hstep
+        self.domain_vstep = domain_vstep
+        # filled by encode(), kept for parity with the reference's attributes
+        self.max_square_exponent = None
+        self.last_stream = None
+
+    def encode(self, img: np.ndarray) -> QuadtreeImage:
+        height, width = img.shape
+        self.max_square_exponent = min(int(np.log2(height)), int(np.log2(width)))
+        nodes, vals, n_roots = fic_b200.qt_encode(
+            img, self.scale_bits, self.offset_bits, self.max_scale, self.full_class_search, self.only_positive_scale,
+            2 ** self.min_range_exponent, 2 ** self.max_range_exponent, self.error_tolerance, self.domain_hstep,
+            self.domain_vstep)
+        self.last_stream = (nodes, vals, n_roots)
+        info = EncodingInfo(self.scale_bits, self.offset_bits, self.max_scale, width, height)
+        return QuadtreeImage(info, stream_to_forest(nodes, vals, n_roots))
+
+
+def _classify(img: np.ndarray, start_i: int, start_j: int, side: int) -> tuple[int, int, int, int]:
+    """Mean class, variance class, rotation, orientation of one block (reference `_classify`, encoder.py:195-259).
+    A signed int32 image (the reference passes ``-(img.astype(int32))`` for negative scales) is classified
+    through the `negate` flag of `fic_qt_classify`."""
+    a = np.asarray(img)
+    neg = 0
+    if a.dtype != np.uint8:
+        if (a <= 0).all():
+            a, neg = (-a).astype(np.uint8), 1
+        else:
+            a = a.astype(np.uint8)
+    mc, vc, rot, orient = fic_b200.qt_classify(a, [(start_i, start_j, side, neg)])[0].tolist()
+    return mc, vc, rot, orient

@@ -1,0 +1,175 @@
+/*
+ * fic.h -- C ABI of libfic_b200.so: the B200 (sm_100a) implementation of the
+ * range->domain block-matching hot path of Fl0k3n/fractal-image-compression.
+ *
+ * The reference exposes no FFI of its own (it is pure Python + numba); the drop-in
+ * boundary is its Python class API.  Each entry point below is what a
+ * ctypes stub inside the reference's class would bind; the reference interface it
+ * replaces is cited as file:line relative to the reference's src/ directory.
+ * INTEGRATION.md shows the stubs.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  No torch / numpy types.
+ *  - Every function returns >= 0 on success and a negative FIC_E* code on failure;
+ *    fic_last_error() returns a human-readable message for the calling thread.
+ *  - Buffers are caller-allocated.  By default pointers are HOST pointers and the
+ *    library performs the host<->device copies itself; pass FIC_DEVICE_PTRS in
+ *    `flags` when every buffer argument of the call is a device pointer on the
+ *    handle's GPU.  The library owns only internal workspaces (cached in the handle).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
+ *    With host pointers the call returns after the results are in the host buffers;
+ *    with device pointers the work is enqueued on `stream` and the call returns
+ *    without synchronising unless it needs a size from the device (tree encoders).
+ *  - A handle is used by one host thread at a time; one handle per GPU.
+ *  - There is NO CPU fallback: without a usable sm_100 GPU fic_create fails.
+ */
+#ifndef FIC_H_
+#define FIC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FIC_OK 0
+#define FIC_EINVAL (-1)   /* bad argument (the reference would raise / crash on it) */
+#define FIC_ECAP (-2)     /* caller-provided output capacity too small */
+#define FIC_ECUDA (-3)    /* CUDA runtime / driver error, see fic_last_error() */
+#define FIC_ENOGPU (-4)   /* no usable sm_100 device */
+#define FIC_ENOMEM (-5)
+
+#define FIC_DEVICE_PTRS 1u  /* all buffer arguments are device pointers */
+#define FIC_BF_EXACT_ONLY 2u /* brute force: skip the tensor-core screen, run the exact scan only */
+#define FIC_BF_NO_FALLBACK 4u /* brute force (testing): fail instead of re-scanning ranges the screen could not decide */
+
+#define FIC_BF_MODE_NUMPY 0 /* BruteForceEncoder semantics  (bruteforce/bf_encoder.py)      */
+#define FIC_BF_MODE_JIT 1   /* JitedBruteForceEncoder semantics (bruteforce/jit_bfencoder.py) */
+
+#define FIC_TREE_QUADTREE 0
+#define FIC_TREE_HV 1
+#define FIC_ITER_AUTO (-1) /* quadtree/decoder.py:11 */
+
+typedef struct fic_handle fic_handle;
+
+/* ---- library / handle ------------------------------------------------------------------ */
+const char* fic_version(void);
+const char* fic_last_error(void);
+int fic_device_count(void);
+/* Creates a handle bound to CUDA device `device`.  Fails with FIC_ENOGPU when the device is
+ * missing or is not compute capability 10.x. */
+int fic_create(int device, fic_handle** out);
+int fic_destroy(fic_handle* h);
+/* Counters since creation / last reset: [0] kernels launched by this library,
+ * [1] brute-force ranges decided by the tensor-core screen, [2] ranges re-scanned exactly,
+ * [3] screen survivors rescored, [4] bytes copied H2D, [5] bytes copied D2H, [6..7] reserved. */
+int fic_get_counters(fic_handle* h, int64_t out[8]);
+int fic_reset_counters(fic_handle* h);
+int fic_synchronize(fic_handle* h);
+/* Device-side timing of the dominant kernel of each path (the brute-force scan / screen kernel): when enabled,
+ * every launch of it is bracketed by CUDA events on the launching stream.  fic_profile_read synchronises those
+ * events, returns their summed duration and launch count since the last read, and clears them.  Used by
+ * bench.py for the roofline figure; off by default (two event records per launch). */
+int fic_profile(fic_handle* h, int enable);
+int fic_profile_read(fic_handle* h, double* total_ms, int64_t* launches);
+
+/* ---- brute force ----------------------------------------------------------------------- */
+/*
+ * Replaces BruteForceEncoder._find_best_domain + _calc_rms_error over all ranges
+ *   (bruteforce/bf_encoder.py:18-71, mode FIC_BF_MODE_NUMPY) and
+ * JitedBruteForceEncoder.encode -> _find_best_domain / _calc_rms_error / _calc_R_error
+ *   (bruteforce/jit_bfencoder.py:18-95, mode FIC_BF_MODE_JIT).
+ * img: uint8 [H,W] row-major; H, W multiples of `range`; domain must equal 2*range.
+ * Ranges are numbered row-major (jit_bfencoder.py:22-23); the call encodes ranges
+ * [range_begin, range_end) -- the slice a rank owns when range blocks are sharded.
+ * out_idx [n,4] int32 = (start_i, start_j, orientation, rotation); out_so [n,2] float64 =
+ * (s, o); out_R [n] float64 = collage error R of the winner (may be NULL).
+ */
+int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, int domain, int stride_i,
+                  int stride_j, int mode, int range_begin, int range_end, int32_t* out_idx, double* out_so,
+                  double* out_R, unsigned flags, void* stream);
+
+/*
+ * Batch form: imgs uint8 [B,H,W]; all ranges of every image; outputs [B,n,...].
+ * This is the image-parallel path (one call per rank on its share of the batch).
+ */
+int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W, int range, int domain,
+                        int mode, int32_t* out_idx, double* out_so, double* out_R, unsigned flags,
+                        void* stream);
+
+/*
+ * Replaces Decoder.decode (bruteforce/decoder.py:12-32), including its buffer aliasing after the
+ * first sweep, int-truncating pool and unclipped uint8 cast.  idx [n,4], so [n,2] as above, n =
+ * number of transforms in range order; out uint8 [height,width].  Range 8 / domain 16 are
+ * hard-coded as in the reference (decoder.py:9-10).
+ */
+int fic_bf_decode(fic_handle* h, const int32_t* idx, const double* so, int n, int width, int height,
+                  int iterations, uint8_t* out, unsigned flags, void* stream);
+
+/* ---- pooling --------------------------------------------------------------------------- */
+/* utils.average_subsample (utils.py:13-25, jit=0: int32-truncating, float64 result) and
+ * utils.average_subsample_jit (utils.py:27-34, jit=1: float32 adds).  arr float64 [h2,w2] ->
+ * out float64 [h2/2,w2/2] (jit results are float32 values widened). */
+int fic_average_subsample(fic_handle* h, const double* arr, int h2, int w2, int jit, double* out,
+                          unsigned flags, void* stream);
+
+/* ---- quadtree -------------------------------------------------------------------------- */
+/*
+ * Replaces QuadtreeEncoder.encode and everything under it (quadtree/encoder.py:67-384):
+ * domain classification and 72-class pools, per-level batched range search, quantised scorer,
+ * split decisions.  Output is the forest as a PREORDER node stream, roots concatenated in
+ * _partition_image order (encoder.py:111-125), children TL,TR,BL,BR (encoder.py:141-146):
+ *   nodes[k] = { kind (0 internal, 1 leaf), start_i, start_j, orientation, rotation,
+ *                quantized_scale, quantized_offset, size_exponent }
+ *   vals[k]  = { scale, offset, best_err }      (pre-quantisation s, o; MSE of the winner)
+ * Returns the node count, FIC_ECAP if cap is too small (2*H*W+64 always suffices), FIC_EINVAL
+ * where the reference raises (a searched range whose 2x domain does not fit the image).
+ * nodes / vals / n_roots are HOST pointers even with FIC_DEVICE_PTRS (img may be on device).
+ */
+int fic_qt_encode(fic_handle* h, const uint8_t* img, int H, int W, int scale_bits, int offset_bits,
+                  double max_scale, int full_class_search, int only_positive_scale, int min_range_side,
+                  int max_range_side, double error_tolerance, int domain_hstep, int domain_vstep,
+                  int32_t* nodes, double* vals, int cap, int32_t* n_roots, unsigned flags, void* stream);
+
+/* _classify (quadtree/encoder.py:195-259) for `count` blocks: blocks[k] = {start_i, start_j, side, negate};
+ * out[k] = {mean_class, variance_class, rotation, orientation}.  blocks/out follow `flags`. */
+int fic_qt_classify(fic_handle* h, const uint8_t* img, int H, int W, const int32_t* blocks, int count,
+                    int32_t* out, unsigned flags, void* stream);
+
+/* ---- HV -------------------------------------------------------------------------------- */
+/*
+ * Replaces HVEncoder.encode (hvv2/encoder.py:24-188).  Preorder stream of the binary tree:
+ *   leaf     nodes[k] = { 1, start_i, start_j, orientation, rotation, qs, qo, 0 }
+ *   internal nodes[k] = { 0, vertical_split, split_idx, 0, 0, 0, 0, 0 }  then child 1, child 2
+ *   vals[k] = { scale, offset, err }
+ * Host output pointers as for fic_qt_encode.
+ */
+int fic_hv_encode(fic_handle* h, const uint8_t* img, int H, int W, int min_range_height, int min_range_width,
+                  int max_range_height, int max_range_width, int scale_bits, int offset_bits,
+                  double err_threshold, double max_scale, int32_t* nodes, double* vals, int cap,
+                  unsigned flags, void* stream);
+
+/* One _run_domain_search (hvv2/encoder.py:97-126) per rect: rects[k] = {i, j, w, h};
+ * rec[k] = {start_i, start_j, orientation, rotation, qs, qo}; vals[k] = {scale, offset, err}. */
+int fic_hv_search(fic_handle* h, const uint8_t* img, int H, int W, const int32_t* rects, int count,
+                  int scale_bits, int offset_bits, double max_scale, int32_t* rec, double* vals,
+                  unsigned flags, void* stream);
+
+/* ---- tree decoders --------------------------------------------------------------------- */
+/*
+ * Replaces QuadtreeDecoder.decode (quadtree/decoder.py:34-116, kind FIC_TREE_QUADTREE) and
+ * HVDecoder.decode (hvv2/decoder.py:29-89, kind FIC_TREE_HV) after the host has flattened the
+ * tree: leaves[k] = { range_i, range_j, height, width, start_i, start_j, orientation, rotation },
+ * so[k] = { scale, offset } (already de-quantised by the caller, decoder.py:90-98).
+ * iterations = FIC_ITER_AUTO reproduces the 2 + <=8 sweep rule with the Frobenius stop test.
+ * f32_affine != 0: HV only, `pooled*scale+offset` evaluated in float32 (python-float scale, i.e.
+ * using_not_quantized_values()).  out uint8 [H,W]; *iters_done (host, may be NULL) = sweeps run.
+ */
+int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double* so, int n, int H, int W,
+                    int iterations, double stop_on_relative_error, int min_iterations, int max_iterations,
+                    int f32_affine, uint8_t* out, int32_t* iters_done, unsigned flags, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FIC_H_ */

@@ -1,0 +1,152 @@
+"""GPU: quadtree and HV encoders/decoders through the C ABI against the reference's golden outputs
+(tests/golden) and the CPU oracle.  All integer fields, float64 scale/offset and decoded bytes bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import synthetic_image
+from test_oracle_golden import HV_CASES, QT_CASES, hv_params, qt_image, qt_params
+
+pytestmark = pytest.mark.gpu
+
+
+def qt_flat(qimg):
+    nodes, vals = [], []
+    for root in qimg.forest:
+        stack = [root]
+        while stack:
+            n = stack.pop()
+            if n.is_leaf():
+                d = n.domain
+                nodes.append([1, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset])
+                vals.append([d.scale, d.offset])
+            else:
+                nodes.append([0] * 7)
+                vals.append([0.0, 0.0])
+                stack.extend(reversed(n.children))
+    return np.array(nodes, np.int32), np.array(vals, np.float64)
+
+
+def hv_flat(root):
+    nodes, vals = [], []
+    stack = [root]
+    while stack:
+        n = stack.pop()
+        if n.is_leaf():
+            d = n.domain
+            nodes.append([1, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset])
+            vals.append([d.scale, d.offset])
+        else:
+            nodes.append([0, int(n.split_info.vertical_split), n.split_info.split_idx, 0, 0, 0, 0])
+            vals.append([0.0, 0.0])
+            stack.append(n.c2)
+            stack.append(n.c1)
+    return np.array(nodes, np.int32), np.array(vals, np.float64)
+
+
+@pytest.mark.parametrize("name", QT_CASES)
+def test_quadtree_encoder_and_decoder_match_reference(fic, golden, images, name):
+    from quadtree.decoder import QuadtreeDecoder
+    from quadtree.encoder import QuadtreeEncoder
+    g = golden["qt_golden"]
+    img = qt_image(images, name)
+    q = QuadtreeEncoder(*qt_params(g, name)).encode(img)
+    nodes, vals = qt_flat(q)
+    assert len(q.forest) == int(g[f"{name}_nroots"])
+    assert np.array_equal(nodes, g[f"{name}_nodes"])
+    assert np.array_equal(vals, g[f"{name}_vals"])
+    assert (q.info.img_width, q.info.img_height) == (img.shape[1], img.shape[0])
+    assert np.array_equal(QuadtreeDecoder().decode(q), g[f"{name}_dec"])
+    if f"{name}_dec4" in g.files:
+        assert np.array_equal(QuadtreeDecoder(iterations=4).decode(q), g[f"{name}_dec4"])
+
+
+@pytest.mark.parametrize("params", [(7, 5, 1.0, False, False, 4, 8, 2.0), (6, 6, 1.0, True, False, 2, 8, 1.0),
+                                    (7, 5, 0.75, False, True, 2, 16, 0.5, 2, 4)])
+@pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96))])
+def test_quadtree_against_oracle(fic, orc, params, seed, shape):
+    img = synthetic_image(seed, *shape)
+    want = orc.qt_encode(img, *params)
+    got = fic.qt_encode(img, *params)
+    assert got[2] == want[2]
+    assert np.array_equal(got[0], want[0])
+    assert np.array_equal(got[1], want[1])
+
+
+def test_quadtree_flat_image_and_placeholders(fic, orc):
+    img = np.full((64, 64), 200, np.uint8)
+    img[16:24, 40:48] = 13
+    params = (7, 5, 1.0, False, False, 4, 16, 0.5)
+    want = orc.qt_encode(img, *params)
+    got = fic.qt_encode(img, *params)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+def test_quadtree_domain_does_not_fit_raises(fic):
+    from quadtree.encoder import QuadtreeEncoder
+    with pytest.raises(ValueError):
+        QuadtreeEncoder(7, 5, 1.0, False, False, 4, 64, 2.0).encode(synthetic_image(1, 64, 64))
+
+
+def test_classify_against_oracle(fic, orc):
+    img = synthetic_image(8, 96, 80)
+    rng = np.random.default_rng(0)
+    blocks = []
+    for _ in range(300):
+        side = int(2 ** rng.integers(1, 6))
+        blocks.append((int(rng.integers(0, 96 - side + 1)), int(rng.integers(0, 80 - side + 1)), side, int(rng.integers(0, 2))))
+    got = fic.qt_classify(img, blocks)
+    for b, gt in zip(blocks, got):
+        assert tuple(gt.tolist()) == orc.qt_classify(img, b[0], b[1], b[2], bool(b[3]))
+
+
+@pytest.mark.parametrize("name", HV_CASES)
+def test_hv_encoder_and_decoder_match_reference(fic, golden, name):
+    from hvv2.decoder import HVDecoder
+    from hvv2.encoder import HVEncoder
+    g = golden["hv_golden"]
+    img = g[f"{name}_img"]
+    h = HVEncoder(*hv_params(g, name)).encode(img)
+    nodes, vals = hv_flat(h.root)
+    assert np.array_equal(nodes, g[f"{name}_nodes"])
+    assert np.array_equal(vals, g[f"{name}_vals"])
+    assert np.array_equal(HVDecoder().decode(h), g[f"{name}_dec"])
+    assert np.array_equal(HVDecoder(iterations=5).using_not_quantized_values().decode(h), g[f"{name}_dec5nq"])
+
+
+@pytest.mark.parametrize("name", ["lena256", "lena512"])
+def test_hv_large_images_match_reference(fic, golden, name):
+    from hvv2.decoder import HVDecoder
+    from hvv2.encoder import HVEncoder
+    g = golden["hv_golden"]
+    if f"{name}_nodes" not in g.files:
+        pytest.skip("slow HV golden not generated")
+    h = HVEncoder(*hv_params(g, name)).encode(g[f"{name}_img"])
+    nodes, vals = hv_flat(h.root)
+    assert np.array_equal(nodes, g[f"{name}_nodes"])
+    assert np.array_equal(vals, g[f"{name}_vals"])
+    assert np.array_equal(HVDecoder().decode(h), g[f"{name}_dec"])
+
+
+def test_hv_search_against_oracle(fic, orc):
+    img = synthetic_image(6, 64, 80)
+    rects = [(0, 0, 4, 4), (10, 7, 1, 4), (3, 60, 5, 1), (20, 20, 16, 16), (40, 8, 13, 7), (0, 0, 40, 32), (5, 5, 39, 2)]
+    rec, vals = fic.hv_search(img, rects, 5, 7, 1.0)
+    for (i, j, w, h), r, v in zip(rects, rec, vals):
+        wr, wv = orc.hv_search(img, i, j, w, h, 5, 7, 1.0)
+        assert np.array_equal(r, wr)
+        assert np.array_equal(v, wv)
+
+
+@pytest.mark.parametrize("params", [(4, 4, 16, 16, 5, 7, 25.0), (1, 1, 8, 8, 6, 6, 4.0, 0.9), (2, 3, 64, 64, 5, 7, 60.0)])
+def test_hv_against_oracle(fic, orc, params):
+    img = synthetic_image(12, 56, 72)
+    want = orc.hv_encode(img, *params)
+    got = fic.hv_encode(img, *params)
+    assert np.array_equal(got[0], want[0])
+    assert np.array_equal(got[1], want[1])
+
+
+def test_tree_decoder_argument_checks(fic):
+    leaves = np.array([[0, 0, 8, 8, 60, 60, 0, 0]], np.int32)
+    with pytest.raises(ValueError):
+        fic.tree_decode(fic.TREE_QUADTREE, leaves, np.zeros((1, 2)), 64, 64)
