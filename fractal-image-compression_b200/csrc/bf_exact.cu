@@ -478,3 +478,121 @@ int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int rang
     FIC_CHECK_LAUNCH(h, "bf_scan_generic_kernel");
     return FIC_OK;
 }
+
+// ---- fic_bf_encode_static: the exact 8x8 scan with no allocation at all ------------------------
+// Some hosts of this library may not allocate device memory when they call it: a codec plugin running inside an
+// application that handed the whole GPU memory budget to its own pool allocator, a capture or inference server
+// whose steady-state loop must not touch the driver's allocator (cudaMalloc / cudaFree synchronise the device and
+// can fail under fragmentation), or a sandboxed worker that is only given pre-allocated buffers.  For them this
+// entry point runs the same four kernels as the exact scan above (box sums, per-position statistics, scan,
+// finalize) but takes every byte of scratch from one array that is part of the loaded module.
+//
+// Limits and rules (also in include/fic.h):
+//   * image at most FIC_STATIC_MAX_SIDE x FIC_STATIC_MAX_SIDE pixels (8x8 ranges, 16x16 domains); larger images
+//     are rejected with FIC_EINVAL -- nothing is truncated;
+//   * the scratch costs FIC_STATIC_SCRATCH_BYTES of device memory on every GPU that loads the library, from load
+//     until process exit, whether or not this entry point is ever called;
+//   * all calls on one GPU share that array.  Nothing in it has to start at zero: every element a kernel reads was
+//     written earlier in the same call (box sums and statistics cover exactly the positions the scan visits, and
+//     every (range, chunk) slot of the partial-winner table is written by the CTA that owns it), so the previous
+//     call's leftovers are harmless.  But two calls that overlap in time on the same GPU (different streams or
+//     host threads) would overwrite each other's scratch: run them one after the other;
+//   * the first call on each device looks up the array's device address.  That lookup may initialise the CUDA
+//     context / load the module, so make the first call before starting any stream capture.
+#define FIC_STATIC_MAX_SIDE 256
+#define FIC_STATIC_BOX_BYTES 131072u                                   /* u16 255*255 rounded up   */
+#define FIC_STATIC_NP_MAX ((FIC_STATIC_MAX_SIDE - 16) * (FIC_STATIC_MAX_SIDE - 16))
+#define FIC_STATIC_STATS_BYTES (FIC_STATIC_NP_MAX * 40u)               /* sd4 + sq4 + 8 x sdd      */
+#define FIC_STATIC_PARTIAL_RECS 65536u                                 /* BestRec, 16 bytes each   */
+#define FIC_STATIC_SCRATCH_BYTES (FIC_STATIC_BOX_BYTES + FIC_STATIC_STATS_BYTES + FIC_STATIC_PARTIAL_RECS * 16u)
+
+static __device__ __align__(256) unsigned char g_static_scratch[FIC_STATIC_SCRATCH_BYTES];
+
+// Host-side bookkeeping, one slot per device ordinal: the scratch's DEVICE address (the symbol name itself is only
+// a host-side handle and must never be handed to a kernel) and the SM count used to size the grid.
+#define FIC_STATIC_MAX_DEVICES 64
+static unsigned char* g_static_ptr[FIC_STATIC_MAX_DEVICES];
+static int g_static_sms[FIC_STATIC_MAX_DEVICES];
+
+extern "C" int fic_bf_encode_static(const uint8_t* d_img, int H, int W, int stride_i, int stride_j, int mode,
+                                    int range_begin, int range_end, int32_t* d_idx, double* d_so, double* d_R,
+                                    void* stream)
+{
+    FIC_REQUIRE(d_img && d_idx && d_so && d_R, "fic_bf_encode_static: NULL argument (all buffers are device pointers)");
+    FIC_REQUIRE(H > 0 && W > 0 && H % 8 == 0 && W % 8 == 0, "fic_bf_encode_static: image %dx%d is not a multiple of 8", H, W);
+    FIC_REQUIRE(H <= FIC_STATIC_MAX_SIDE && W <= FIC_STATIC_MAX_SIDE,
+                "fic_bf_encode_static: image %dx%d exceeds the built-in scratch (at most %dx%d); use fic_bf_encode",
+                H, W, FIC_STATIC_MAX_SIDE, FIC_STATIC_MAX_SIDE);
+    FIC_REQUIRE(stride_i > 0 && stride_j > 0, "fic_bf_encode_static: strides must be positive");
+    FIC_REQUIRE(mode == FIC_BF_MODE_NUMPY || mode == FIC_BF_MODE_JIT, "fic_bf_encode_static: unknown mode %d", mode);
+    const int total = (H / 8) * (W / 8);
+    FIC_REQUIRE(0 <= range_begin && range_begin <= range_end && range_end <= total,
+                "fic_bf_encode_static: range slice [%d,%d) outside [0,%d)", range_begin, range_end, total);
+    const int n_ranges = range_end - range_begin;
+    if (n_ranges == 0) return FIC_OK;
+
+    int dev = -1;
+    FIC_CUDA(cudaGetDevice(&dev));
+    FIC_REQUIRE(dev >= 0 && dev < FIC_STATIC_MAX_DEVICES, "fic_bf_encode_static: device ordinal %d not supported", dev);
+    if (!g_static_ptr[dev]) {  // once per device, with that device current
+        unsigned char* p = nullptr;
+        FIC_CUDA(cudaGetSymbolAddress((void**)&p, g_static_scratch));
+        int sms = 0;
+        FIC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g_static_sms[dev] = sms;
+        g_static_ptr[dev] = p;
+    }
+    unsigned char* base = g_static_ptr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+
+    uint16_t* P = reinterpret_cast<uint16_t*>(base);
+    const size_t NP = (size_t)(W - 16 > 0 ? W - 16 : 0) * (size_t)(H - 16 > 0 ? H - 16 : 0);
+    uint32_t* sd4 = reinterpret_cast<uint32_t*>(base + FIC_STATIC_BOX_BYTES);
+    uint32_t* sq4 = sd4 + NP;
+    float* sdd = reinterpret_cast<float*>(sq4 + NP);
+    BestRec* partial = reinterpret_cast<BestRec*>(base + FIC_STATIC_BOX_BYTES + FIC_STATIC_STATS_BYTES);
+
+    dim3 gb(ceil_div(W - 1, 256), H - 1);
+    bf_boxsum_kernel<<<gb, 256, 0, st>>>(d_img, H, W, P);
+    FIC_TRY(fic_check_launch("bf_boxsum_kernel (static)"));
+    if (NP) {
+        bf_stats_kernel<<<ceil_div(NP, 128), 128, 0, st>>>(P, H, W, sd4, sq4, sdd);
+        FIC_TRY(fic_check_launch("bf_stats_kernel (static)"));
+    }
+    BfGeom g;
+    g.H = H; g.W = W; g.si = stride_i; g.sj = stride_j; g.PW = W - 16; g.BW = W - 1;
+    g.npi = H - 16 > 0 ? ceil_div(H - 16, stride_i) : 0;
+    g.npj = W - 16 > 0 ? ceil_div(W - 16, stride_j) : 0;
+    const long long nq = (long long)g.npi * g.npj;
+    const int groups = ceil_div(n_ranges, BF_G);
+    int n_chunks = 1;
+    if (nq > 0) {
+        long long want = (long long)g_static_sms[dev] * 16;
+        n_chunks = (int)((want + groups - 1) / groups);
+        int max_chunks = ceil_div(nq, BF_THREADS * 4);
+        if (n_chunks > max_chunks) n_chunks = max_chunks;
+        int fit = (int)(FIC_STATIC_PARTIAL_RECS / (unsigned)n_ranges);  // the partial table is fixed-size here
+        if (n_chunks > fit) n_chunks = fit;
+        if (n_chunks < 1) n_chunks = 1;
+    }
+    int chunk_len = nq > 0 ? ceil_div(nq, n_chunks) : 1;
+    chunk_len = ceil_div(chunk_len, BF_THREADS) * BF_THREADS;
+    n_chunks = nq > 0 ? ceil_div(nq, chunk_len) : 1;
+    dim3 grid(groups, n_chunks);
+    if (mode == FIC_BF_MODE_JIT) {
+        bf_scan8_kernel<FIC_BF_MODE_JIT><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                                     nullptr, chunk_len, n_chunks, partial);
+        FIC_TRY(fic_check_launch("bf_scan8_kernel<jit> (static)"));
+        bf_finalize8_kernel<FIC_BF_MODE_JIT><<<ceil_div(n_ranges, 128), 128, 0, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                                      nullptr, n_chunks, partial, d_idx, d_so, d_R);
+        FIC_TRY(fic_check_launch("bf_finalize8_kernel<jit> (static)"));
+    } else {
+        bf_scan8_kernel<FIC_BF_MODE_NUMPY><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                                       nullptr, chunk_len, n_chunks, partial);
+        FIC_TRY(fic_check_launch("bf_scan8_kernel<numpy> (static)"));
+        bf_finalize8_kernel<FIC_BF_MODE_NUMPY><<<ceil_div(n_ranges, 128), 128, 0, st>>>(d_img, P, sd4, sq4, sdd, g, range_begin, n_ranges,
+                                                                                        nullptr, n_chunks, partial, d_idx, d_so, d_R);
+        FIC_TRY(fic_check_launch("bf_finalize8_kernel<numpy> (static)"));
+    }
+    return FIC_OK;
+}

@@ -50,6 +50,8 @@ SIGNATURES = {
                                 C.c_int, _vp, _vp, _vp, C.c_uint, _vp]),
     "fic_bf_encode_batch": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp,
                                       C.c_uint, _vp]),
+    "fic_bf_encode_static": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp,
+                                       _vp, _vp]),
     "fic_bf_decode": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_average_subsample": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_qt_encode": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int,
@@ -209,6 +211,21 @@ def bf_encode_dev(h: Handle, img_ptr: int, H: int, W: int, idx_ptr: int, so_ptr:
                                int(strides[1]), int(mode), int(range_begin), int(range_end), _vp(idx_ptr), _vp(so_ptr),
                                _vp(R_ptr) if R_ptr else None, int(flags) | DEVICE_PTRS, _vp(stream) if stream else None),
            "fic_bf_encode")
+
+
+def bf_encode_static_dev(img_ptr: int, H: int, W: int, idx_ptr: int, so_ptr: int, R_ptr: int, strides=(1, 1),
+                         mode=BF_MODE_JIT, range_begin=0, range_end=None, stream=0):
+    """`fic_bf_encode_static`: the exact 8x8 encode for callers that must not allocate device memory.
+
+    Takes raw device pointers only (image, idx[n,4] int32, so[n,2] float64, R[n] float64 on the current CUDA
+    device), needs no Handle, allocates nothing and does not synchronise.  Images up to 256x256; larger ones raise
+    ValueError.  All calls on a GPU share one built-in scratch array, so do not overlap two of them in time, and
+    make the first call on a device before any stream capture (it resolves the scratch address)."""
+    if range_end is None:
+        range_end = (H // 8) * (W // 8)
+    _check(lib().fic_bf_encode_static(_vp(img_ptr), int(H), int(W), int(strides[0]), int(strides[1]), int(mode),
+                                      int(range_begin), int(range_end), _vp(idx_ptr), _vp(so_ptr), _vp(R_ptr),
+                                      _vp(stream) if stream else None), "fic_bf_encode_static")
 
 
 def bf_encode_batch(imgs, range_size=8, domain_size=16, mode=BF_MODE_JIT, flags=0, handle: Handle | None = None):

@@ -98,6 +98,29 @@ int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W,
                         void* stream);
 
 /*
+ * No counterpart in the reference (the reference never manages device memory).
+ *
+ * The same exact 8x8 / 16x16 brute-force encode as fic_bf_encode, for callers that are not allowed to allocate
+ * device memory around the call: plugins inside an application whose own pool allocator owns the GPU's memory,
+ * serving or capture loops that must stay away from cudaMalloc/cudaFree (both synchronise the device and can fail
+ * late), sandboxed workers that only ever see pre-allocated buffers.  It needs no fic_handle and calls neither
+ * cudaMalloc nor cudaFree nor any allocating library routine; its scratch (box sums, per-position statistics,
+ * per-CTA winners) lives in a fixed array inside the loaded module.
+ *   - every buffer is a DEVICE pointer on the current device: d_img uint8 [H,W]; outputs as in fic_bf_encode,
+ *     sized for range_end - range_begin ranges; d_R is mandatory.  Work is enqueued on `stream` (NULL = the
+ *     default stream); the call does not synchronise.
+ *   - limit: H, W <= 256 (multiples of 8).  Anything larger returns FIC_EINVAL with a message; use fic_bf_encode.
+ *   - cost: about 3.4 MB of device memory on every GPU that loads the library, held until the process exits.
+ *   - the array is shared by all calls on a GPU and keeps the previous call's contents; nothing in it needs to
+ *     start at zero (each call writes everything it later reads).  Calls that overlap on the GPU -- two streams,
+ *     two host threads -- race on it: issue them one after the other.
+ *   - the first call on each device resolves the array's device address; do that first call before starting a
+ *     stream capture.
+ */
+int fic_bf_encode_static(const uint8_t* d_img, int H, int W, int stride_i, int stride_j, int mode, int range_begin,
+                         int range_end, int32_t* d_idx, double* d_so, double* d_R, void* stream);
+
+/*
  * Replaces Decoder.decode (bruteforce/decoder.py:12-32), including its buffer aliasing after the
  * first sweep, int-truncating pool and unclipped uint8 cast.  idx [n,4], so [n,2] as above, n =
  * number of transforms in range order; out uint8 [height,width].  Range 8 / domain 16 are
