@@ -1,8 +1,767 @@
-// placeholder until the tcgen05 screen lands
+// Brute-force encoder, tensor-core path: pool kernel -> tcgen05 correlation GEMM with a fused screening
+// epilogue -> exact rescoring of the survivors.  8x8 ranges, 16x16 domains, stride 1, JIT semantics
+// (bruteforce/jit_bfencoder.py:32-95).  The GEMM never decides anything on its own: it only discards candidates
+// that provably cannot win, everything that survives is scored by the exact arithmetic of scorer.cuh, so the
+// records are bit-identical to the exact scan (bf_exact.cu) and to the reference.
+//
+// Math.  With D4 = 4*d (integers), X = sum r_k*D4_k, SD4 = sum D4, the reference's least-squares numerator is
+//     n*ab - sum(r)*sum(d) = (64*X - sum(r)*SD4)/4 = 16*u,        u := X - sum(r)*SD4/64 .
+// Centre both operands by integers: r' = r - m_r, D4' = D4 - m_c (m = round(mean)), rho = sum r', eps = sum D4':
+//     u = sum r'_k*D4'_k - rho*eps/64                              (exact identity)
+// which is one K=80 dot product of fp16-exact operands: 64 products of integers (|r'|<=255, |D4'|<=1020, every
+// partial sum < 2^24, exact in the fp32 accumulator) plus one extension column rho * (-eps/64).
+// For ANY (s,o) the collage error obeys  R >= R_opt = (A_r - 64*u^2/den16)/64  with A_r = sum r^2 - (sum r)^2/64 and
+// den16 = 64*sum(D4^2) - SD4^2 (exact integers); the reference's float32 noise lowers its R by at most G = 0.26
+// ("guard derivation": s^2*delta(sum d^2)/n <= 0.245 for |s| <= 1).  Given an upper bound UB_r
+// on the winner's R (the exact R of any candidate, here the best of a coarse exact pre-scan), candidate c can only
+// win or tie if   64*u^2/den16 >= T_r := A_r - 64*(UB_r + G)   <=>   |u| * h_c >= tau_r,
+// h_c = 8/sqrt(den16), tau_r = sqrt(T_r).  The epilogue evaluates  fma(|u|, h_c, k_c) >= tau_r  with
+// k_c = DELTA*h_c absorbing the accumulator's rounding of the fractional extension term: 2 instructions per output.
+// Ranges with T_r <= 0 (flat ranges: the screen cannot separate anything) and ranges whose survivor list overflows
+// are handed to the exact scan.
+//
+// GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 4-stage ring), N = 256 columns = 32 ranges
+// x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
+// TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
+// tile t.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer + TMEM allocator, warps 2..9 epilogue (two per TMEM
+// lane quadrant, 128 columns each).  Thread = candidate, so h_c/k_c are per-thread registers and the 8 isometry
+// columns of a range share one tau register (16 per thread).
+//
+// HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
+//   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
+//   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
+//   hk      float2 [NP]    (h_c, k_c)
+// and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
 #include "fic_common.cuh"
-bool bf_screen_applicable(int, int) { return false; }
-int bf_screen_encode8(fic_handle*, const uint8_t*, int, int, int, int, int32_t*, double*, double*, unsigned, cudaStream_t)
+#include "scorer.cuh"
+
+int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int mode, int range_begin,
+                   int n_ranges, const int32_t* d_range_list, int32_t* d_idx, double* d_so, double* d_R,
+                   cudaStream_t st);
+
+namespace {
+
+constexpr int BM = 128;      // candidates per tile
+constexpr int BN = 256;      // columns per unit (32 ranges x 8 isometries)
+constexpr int KMAIN = 64;
+constexpr int KEXT = 16;
+constexpr int STAGES = 4;
+constexpr int EPI_WARPS = 8;
+constexpr int SCREEN_THREADS = 64 + EPI_WARPS * 32;
+constexpr uint32_t A_MAIN_BYTES = BM * KMAIN * 2;   // 16384
+constexpr uint32_t A_EXT_BYTES = BM * KEXT * 2;     // 4096
+constexpr uint32_t B_MAIN_BYTES = BN * KMAIN * 2;   // 32768
+constexpr uint32_t B_EXT_BYTES = BN * KEXT * 2;     // 8192
+constexpr uint32_t OFF_B_MAIN = 0;
+constexpr uint32_t OFF_B_EXT = OFF_B_MAIN + B_MAIN_BYTES;
+constexpr uint32_t OFF_A_MAIN = OFF_B_EXT + B_EXT_BYTES;
+constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
+constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
+constexpr uint32_t SCREEN_SMEM = OFF_BARS + 256 + 1024;  // + slack to align the base to 1024
+
+constexpr float GUARD_R = 0.26f;     // reference float32 noise, in R (MSE) units
+constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
+
+// ---- PTX wrappers ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
 {
-    fic_set_error("screen path not built");
-    return FIC_EINVAL;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, P1;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a broken pipeline must not hang the GPU.  ~4 s at 2 GHz, then flag + trap.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* err_flag, int code)
+{
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 8000000000ll) {
+            if (err_flag) atomicExch(err_flag, code);
+            __threadfence_system();
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major operand tile in shared memory (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): start address >> 4 in
+// bits [0,14), LBO (unused for swizzled K-major, = 1) in [16,30), SBO >> 4 in [32,46), version 1 in [46,48),
+// layout type in [61,64): 2 = SWIZZLE_128B (rows of 128 B, 8-row groups 1024 B apart), 6 = SWIZZLE_32B (rows of 32 B,
+// 8-row groups 256 B apart).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout_type)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)layout_type << 61;
+    return d;
+}
+// cute::UMMA::InstrDescriptor: c_format F32 (1) at bit 4, a/b format F16 (0), K-major both, N>>3 at bit 17, M>>4 at bit 24
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+struct ScreenParams {
+    const float2* hk;        // [NP]
+    const float* tau;        // [slots padded to 32]
+    const int* n_elig;       // device scalar
+    uint32_t* cnt;           // [slots] survivors found
+    uint32_t* list;          // [slots][cap] entries = position*8 + isometry
+    uint32_t cap;
+    int NP;
+    int n_tiles;
+    int n_chunks;
+    float* dump;             // probe mode: [n_tiles*128][256] raw accumulators of column group 0 (else nullptr)
+    int* err_flag;
+};
+
+__device__ __forceinline__ void unit_range(const ScreenParams& p, int unit, int& grp, int& t0, int& t1)
+{
+    grp = unit / p.n_chunks;
+    const int c = unit - grp * p.n_chunks;
+    const int per = (p.n_tiles + p.n_chunks - 1) / p.n_chunks;
+    t0 = c * per;
+    t1 = min(p.n_tiles, t0 + per);
+}
+
+// ---- the screen ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(SCREEN_THREADS, 1)
+bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapAx,
+                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapBx, ScreenParams p)
+{
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B tiles want 1024-byte alignment
+    unsigned char* gbase = smem_raw + (base - raw);
+    const uint32_t bars = base + OFF_BARS;
+    // barrier slots (8 bytes each): full[STAGES], empty[STAGES], b_full, b_empty, tmem_full[2], tmem_empty[2]
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+    const uint32_t b_full = bars + 8u * (2 * STAGES), b_empty = bars + 8u * (2 * STAGES + 1);
+    auto tfull_bar = [&](int s) { return bars + 8u * (2 * STAGES + 2 + s); };
+    auto tempty_bar = [&](int s) { return bars + 8u * (2 * STAGES + 4 + s); };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + OFF_BARS + 8 * (2 * STAGES + 6));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_elig = *p.n_elig;
+    const int n_groups = (n_elig + 31) / 32;
+    const int n_units = n_groups * p.n_chunks;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(b_full, 1);
+        mbar_init(b_empty, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM by construction: > 113 KB of shared memory)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0, bph = 0;
+            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+                int grp, t0, t1;
+                unit_range(p, unit, grp, t0, t1);
+                mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
+                mbar_expect_tx(b_full, B_MAIN_BYTES + B_EXT_BYTES);
+                tma_load_2d(base + OFF_B_MAIN, &mapB, b_full, 0, grp * BN);
+                tma_load_2d(base + OFF_B_EXT, &mapBx, b_full, 0, grp * BN);
+                bph ^= 1;
+                for (int t = t0; t < t1; ++t) {
+                    mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
+                    mbar_expect_tx(full_bar(s), A_MAIN_BYTES + A_EXT_BYTES);
+                    tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t * BM);
+                    tma_load_2d(base + OFF_A_EXT + s * A_EXT_BYTES, &mapAx, full_bar(s), 0, t * BM);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            int s = 0, as = 0;
+            uint32_t ph = 0, aph = 0, bph = 0;
+            const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
+            const uint64_t bxdesc = make_desc(base + OFF_B_EXT, 256, 6);
+            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+                int grp, t0, t1;
+                unit_range(p, unit, grp, t0, t1);
+                mbar_wait(b_full, bph, p.err_flag, 3);
+                bph ^= 1;
+                for (int t = t0; t < t1; ++t) {
+                    mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
+                    mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
+                    tcgen05_fence_after();
+                    const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
+                    const uint64_t adesc = make_desc(base + OFF_A_MAIN + s * A_MAIN_BYTES, 1024, 2);
+                    const uint64_t axdesc = make_desc(base + OFF_A_EXT + s * A_EXT_BYTES, 256, 6);
+#pragma unroll
+                    for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
+                        umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
+                    umma_f16(d_tmem, axdesc, bxdesc, IDESC, 1);
+                    tcgen05_commit(empty_bar(s));   // frees the A stage once the MMAs above have completed
+                    tcgen05_commit(tfull_bar(as));  // accumulator ready for the epilogue
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                    if (++as == 2) { as = 0; aph ^= 1; }
+                }
+                tcgen05_commit(b_empty);
+            }
+        }
+    } else {
+        // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
+        const int ew = warp - 2;
+        const int quad = warp & 3;        // TMEM lane quadrant this warp may touch
+        const int half = ew >> 2;         // which 128 of the 256 columns
+        int as = 0;
+        uint32_t aph = 0;
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+            int grp, t0, t1;
+            unit_range(p, unit, grp, t0, t1);
+            float tau[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) tau[j] = p.tau[grp * 32 + half * 16 + j];
+            const int slot0 = grp * 32 + half * 16;
+            int cand = t0 * BM + quad * 32 + lane;
+            float2 hk_next = cand < p.NP && t0 < t1 ? p.hk[cand] : make_float2(0.f, 0.f);
+            for (int t = t0; t < t1; ++t) {
+                const float2 hk = hk_next;
+                const int my_cand = cand;
+                cand += BM;
+                if (t + 1 < t1) hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
+                mbar_wait(tfull_bar(as), aph, p.err_flag, 6);
+                tcgen05_fence_after();
+                const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN + half * 128);
+#pragma unroll 1
+                for (int c4 = 0; c4 < 4; ++c4) {
+                    uint32_t v[32];
+                    tmem_ld32(taddr0 + c4 * 32, v);
+                    tmem_ld_wait();
+                    if (p.dump) {
+                        if (grp == 0 && my_cand < p.n_tiles * BM) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                p.dump[(size_t)my_cand * BN + half * 128 + c4 * 32 + j] = __uint_as_float(v[j]);
+                        }
+                        continue;
+                    }
+                    bool any = false;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float val = fmaf(fabsf(__uint_as_float(v[j])), hk.x, hk.y);
+                        any |= val >= tau[c4 * 4 + (j >> 3)];
+                    }
+                    if (__any_sync(0xffffffffu, any)) {
+                        if (any) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const float val = fmaf(fabsf(__uint_as_float(v[j])), hk.x, hk.y);
+                                if (val >= tau[c4 * 4 + (j >> 3)]) {
+                                    const int slot = slot0 + c4 * 4 + (j >> 3);
+                                    const uint32_t at = atomicAdd(&p.cnt[slot], 1u);
+                                    if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)my_cand * 8u + (uint32_t)(j & 7);
+                                }
+                            }
+                        }
+                    }
+                }
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(tempty_bar(as));
+                if (++as == 2) { as = 0; aph ^= 1; }
+            }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    }
+}
+
+// ---- pool kernel: 2x pooling + centring + statistics, one thread per stride-1 position ------------------------
+__global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
+                               __half* __restrict__ poolAx, float2* __restrict__ hk)
+{
+    const int PW = W - 16, PH = H - 16, BW = W - 1;
+    const int NP = PW * PH;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= NP) return;
+    const int di = p / PW, dj = p - di * PW;
+    int v[64];
+    int s = 0;
+    long long s2 = 0;
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            int x = P[(size_t)(di + 2 * a) * BW + dj + 2 * b];
+            v[a * 8 + b] = x;
+            s += x;
+            s2 += x * x;
+        }
+    const int m = (s + 32) >> 6;  // round(SD4 / 64)
+    const int eps = s - 64 * m;   // in [-32, 31]
+    uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)p * 64);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        __half2 h0 = __halves2half2(__int2half_rn(v[8 * q + 0] - m), __int2half_rn(v[8 * q + 1] - m));
+        __half2 h1 = __halves2half2(__int2half_rn(v[8 * q + 2] - m), __int2half_rn(v[8 * q + 3] - m));
+        __half2 h2 = __halves2half2(__int2half_rn(v[8 * q + 4] - m), __int2half_rn(v[8 * q + 5] - m));
+        __half2 h3 = __halves2half2(__int2half_rn(v[8 * q + 6] - m), __int2half_rn(v[8 * q + 7] - m));
+        uint4 o;
+        o.x = *reinterpret_cast<uint32_t*>(&h0);
+        o.y = *reinterpret_cast<uint32_t*>(&h1);
+        o.z = *reinterpret_cast<uint32_t*>(&h2);
+        o.w = *reinterpret_cast<uint32_t*>(&h3);
+        dst[q] = o;
+    }
+    uint4* dx = reinterpret_cast<uint4*>(poolAx + (size_t)p * 16);
+    __half2 e0 = __halves2half2(__float2half_rn(-(float)eps * 0.015625f), __float2half_rn(0.f));  // exact: |eps|/64 <= 0.5, 6 bits
+    uint4 ox = make_uint4(*reinterpret_cast<uint32_t*>(&e0), 0u, 0u, 0u);
+    dx[0] = ox;
+    dx[1] = make_uint4(0u, 0u, 0u, 0u);
+    const long long den16 = 64ll * s2 - (long long)s * s;  // >= 0, exact
+    float hc = 0.f, kc = 0.f;
+    if (den16 > 0) {
+        hc = (float)(8.0 / sqrt((double)den16)) * (1.0f + 1.0f / 1048576.0f);  // rounded up a little: never under-estimate
+        kc = DELTA_U * hc;
+    }
+    hk[p] = make_float2(hc, kc);
+}
+
+// ---- thresholds + compaction: which ranges the screen can decide ------------------------------------------------
+// ctrl[0] = n_elig, ctrl[1] = n_fallback (grows again when survivor lists overflow), ctrl[2] = error flag
+__global__ void __launch_bounds__(1024)
+bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, const double* __restrict__ preR,
+                    int32_t* __restrict__ elig, float* __restrict__ tau, int32_t* __restrict__ fallback, int* __restrict__ ctrl,
+                    int tau_pad)
+{
+    __shared__ int warp_e[32], warp_f[32];
+    __shared__ int base_e, base_f;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rw = W / 8;
+    if (tid == 0) { base_e = 0; base_f = 0; }
+    __syncthreads();
+    for (int b0 = 0; b0 < n_ranges; b0 += 1024) {
+        const int slot = b0 + tid;
+        bool is_e = false, is_f = false;
+        float my_tau = 0.f;
+        if (slot < n_ranges) {
+            const int ridx = range_begin + slot;
+            const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+            long long s = 0, q = 0;
+            for (int k = 0; k < 64; ++k) {
+                long long x = img[(size_t)(ri + (k >> 3)) * W + rj + (k & 7)];
+                s += x;
+                q += x * x;
+            }
+            const double A = (double)(64 * q - s * s) * 0.015625;           // sum r^2 - (sum r)^2/64, exact
+            const double ub = preR[slot];
+            const double T = A - 64.0 * (ub + (double)GUARD_R + 1e-9 * (double)q);
+            if (ub == ub && ub < 1e300 && T > 1e-3) {
+                is_e = true;
+                my_tau = (float)sqrt(T) * (1.0f - 1.0f / 1048576.0f);      // rounded down a little: never over-estimate
+            } else {
+                is_f = true;
+            }
+        }
+        const unsigned me = __ballot_sync(0xffffffffu, is_e), mf = __ballot_sync(0xffffffffu, is_f);
+        if (lane == 0) { warp_e[warp] = __popc(me); warp_f[warp] = __popc(mf); }
+        __syncthreads();
+        int pe = base_e, pf = base_f;
+        for (int w = 0; w < warp; ++w) { pe += warp_e[w]; pf += warp_f[w]; }
+        pe += __popc(me & ((1u << lane) - 1u));
+        pf += __popc(mf & ((1u << lane) - 1u));
+        if (is_e) { elig[pe] = range_begin + slot; tau[pe] = my_tau; }
+        if (is_f) fallback[pf] = range_begin + slot;
+        __syncthreads();
+        if (tid == 0) {
+            int te = 0, tf = 0;
+            for (int w = 0; w < 32; ++w) { te += warp_e[w]; tf += warp_f[w]; }
+            base_e += te;
+            base_f += tf;
+        }
+        __syncthreads();
+    }
+    // pad tau so that every column group reads 32 valid entries: +inf never passes
+    for (int k = base_e + tid; k < tau_pad; k += 1024) tau[k] = __int_as_float(0x7f800000);
+    if (tid == 0) { ctrl[0] = base_e; ctrl[1] = base_f; }
+}
+
+// ---- range operand: 8 inverse-transformed, centred copies of every eligible range -------------------------------
+__global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const int32_t* __restrict__ elig,
+                                  const int* __restrict__ ctrl, int n_cols_pad, __half* __restrict__ rngB,
+                                  __half* __restrict__ rngBx)
+{
+    const int col = blockIdx.x * 4 + (threadIdx.x >> 6);  // 4 columns per 256-thread block
+    const int k = threadIdx.x & 63;
+    if (col >= n_cols_pad) return;
+    const int slot = col >> 3, t = col & 7;
+    const int n_elig = ctrl[0];
+    __half out = __float2half_rn(0.f);
+    int rho = 0;
+    if (slot < n_elig) {
+        const int rw = W / 8;
+        const int ridx = elig[slot];
+        const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+        int s = 0;
+        for (int e = 0; e < 64; ++e) s += img[(size_t)(ri + (e >> 3)) * W + rj + (e & 7)];
+        const int m = (s + 32) >> 6;
+        rho = s - 64 * m;
+        // column entry k = (sa,sb) holds r'[i][j] with (sa,sb) = iso_t(i,j): find the (i,j) that maps onto k
+        // by applying the map to every (i,j) would be 64 steps; the isometries are involutive up to rotation
+        // direction, so invert explicitly: iso_t^{-1}(sa,sb)
+        const int sa = k >> 3, sb = k & 7;
+        int a = (t >> 2) ? sb : sa, b = (t >> 2) ? sa : sb;  // undo the transpose: (a,b) index into rot90(.,rot)
+        int i, j;
+        switch (t & 3) {  // a = f_i(i,j), b = f_j(i,j) of fic_iso_bf -> solve for (i,j)
+        case 0: i = a; j = b; break;
+        case 1: j = a; i = 7 - b; break;          // a = j, b = 7 - i
+        case 2: i = 7 - a; j = 7 - b; break;
+        default: j = 7 - a; i = b; break;         // a = 7 - j, b = i
+        }
+        out = __int2half_rn((int)img[(size_t)(ri + i) * W + rj + j] - m);
+    }
+    rngB[(size_t)col * 64 + k] = out;
+    if (k < 16) rngBx[(size_t)col * 16 + k] = (k == 0 && slot < n_elig) ? __int2half_rn(rho) : __float2half_rn(0.f);
+}
+
+// ---- exact rescoring of the survivors: one CTA per eligible range ------------------------------------------------
+__global__ void __launch_bounds__(256)
+bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
+                  const float* __restrict__ sdd, int H, int W, int range_begin, const int32_t* __restrict__ elig,
+                  int* __restrict__ ctrl, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
+                  int32_t* __restrict__ fallback, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                  double* __restrict__ out_R, unsigned long long* __restrict__ surv_total)
+{
+    const int slot = blockIdx.x;
+    if (slot >= ctrl[0]) return;
+    __shared__ float r_s[64];
+    __shared__ double sh_rs, sh_sq;
+    __shared__ BestRec red[8];
+    __shared__ double red_s[8], red_o[8];
+    const int tid = threadIdx.x;
+    const int ridx = elig[slot];
+    const uint32_t n = cnt[slot];
+    if (n > cap || n == 0) {  // overflow (or, impossibly, nothing): let the exact scan decide this range
+        if (tid == 0) {
+            int at = atomicAdd(&ctrl[1], 1);
+            fallback[at] = ridx;
+        }
+        return;
+    }
+    const int rw = W / 8, PW = W - 16, BW = W - 1;
+    const int NP = PW * (H - 16);
+    const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+    if (tid < 64) r_s[tid] = (float)img[(size_t)(ri + (tid >> 3)) * W + rj + (tid & 7)];
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long s = 0, q = 0;
+        for (int k = 0; k < 64; ++k) { unsigned v = (unsigned)r_s[k]; s += v; q += v * v; }
+        sh_rs = (double)s;
+        sh_sq = (double)q;
+        atomicAdd(surv_total, (unsigned long long)n);
+    }
+    __syncthreads();
+    const double rs = sh_rs, sqr = sh_sq;
+    double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
+    unsigned long long bseq = ~0ull;
+    for (uint32_t e = tid; e < n; e += 256) {
+        const uint32_t ent = list[(size_t)slot * cap + e];
+        const int t = ent & 7;
+        const int p = ent >> 3;
+        const int di = p / PW, dj = p - di * PW;
+        float x = 0.f;
+        for (int i = 0; i < 8; ++i)
+            for (int j = 0; j < 8; ++j) {
+                int sa, sb;
+                fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
+                x = fmaf(r_s[i * 8 + j], (float)P[(size_t)(di + 2 * sa) * BW + dj + 2 * sb], x);  // exact integers < 2^24
+            }
+        const float dsf = __fmul_rn((float)sd4[p], 0.25f);
+        BfScore sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
+                                     (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
+        if (fic_better(sc.R, (unsigned long long)ent, bR, bseq)) { bR = sc.R; bseq = ent; bs = sc.s; bo = sc.o; }
+    }
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        double oR = __shfl_xor_sync(0xffffffffu, bR, off);
+        unsigned long long oS = __shfl_xor_sync(0xffffffffu, bseq, off);
+        double os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
+        if (fic_better(oR, oS, bR, bseq)) { bR = oR; bseq = oS; bs = os; bo = oo; }
+    }
+    if (lane == 0) { red[warp].R = bR; red[warp].seq = bseq; red_s[warp] = bs; red_o[warp] = bo; }
+    __syncthreads();
+    if (tid == 0) {
+        BestRec b = red[0];
+        double s = red_s[0], o = red_o[0];
+        for (int w = 1; w < 8; ++w)
+            if (fic_better(red[w].R, red[w].seq, b.R, b.seq)) { b = red[w]; s = red_s[w]; o = red_o[w]; }
+        const size_t os_ = (size_t)(ridx - range_begin);
+        if (b.seq == ~0ull) {  // every survivor scored NaN/inf: cannot happen for finite images, but stay exact
+            int at = atomicAdd(&ctrl[1], 1);
+            fallback[at] = ridx;
+            return;
+        }
+        const int t = (int)(b.seq & 7ull), p = (int)(b.seq >> 3);
+        out_idx[4 * os_ + 0] = p / PW;
+        out_idx[4 * os_ + 1] = p % PW;
+        out_idx[4 * os_ + 2] = t >> 2;
+        out_idx[4 * os_ + 3] = t & 3;
+        out_so[2 * os_] = s;
+        out_so[2 * os_ + 1] = o;
+        out_R[os_] = b.R;
+    }
+}
+
+// ---- host ---------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_tmapEncodeTiled get_encode()
+{
+    static PFN_tmapEncodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (PFN_tmapEncodeTiled)p;
+    }
+    return fn;
+}
+
+// fp16 matrix [rows][cols] row-major, box = cols x box_rows
+int make_map(CUtensorMap* m, void* base, uint64_t rows, uint32_t cols, uint32_t box_rows, CUtensorMapSwizzle sw)
+{
+    PFN_tmapEncodeTiled enc = get_encode();
+    if (!enc) { fic_set_error("cuTensorMapEncodeTiled is not available from this driver"); return FIC_ECUDA; }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { fic_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows %llu cols %u)", (int)r, (unsigned long long)rows, cols); return FIC_ECUDA; }
+    return FIC_OK;
+}
+
+inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+}  // namespace
+
+bool bf_screen_applicable(int H, int W)
+{
+    // below ~32 tiles of candidates the fixed costs of the pipeline exceed the exact scan
+    return H > 16 && W > 16 && (long long)(H - 16) * (W - 16) >= 4096;
+}
+
+// `probe` != nullptr: debugging/validation mode -- only column group 0 is run and the raw accumulators are written
+// to probe[NP_pad][256]; all ranges are treated as eligible (tau = +inf) so nothing is appended.
+int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+                  double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st)
+{
+    const int PW = W - 16, PH = H - 16;
+    const int NP = PW * PH;
+    const int n_tiles = cdiv(NP, BM);
+    const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
+    const int tau_pad = n_cols_pad / 8;
+    const uint16_t* P = h->bf_boxsum.as<uint16_t>();
+    const uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    const float* sdd = reinterpret_cast<const float*>(sd4 + 2 * (size_t)NP);
+
+    // survivor capacity per range: bounded by a 1 GiB list
+    uint32_t cap = 8192;
+    while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
+
+    FIC_TRY(h->bf_pool.reserve((size_t)NP * 64 * 2 + 256));
+    FIC_TRY(h->bf_poolx.reserve((size_t)NP * 16 * 2 + 256));
+    FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
+    FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 80 * 2 + 256));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * 4 + (size_t)n_ranges * 4 * 2 + 256));
+    FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
+    FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
+    FIC_TRY(h->bf_ctrl.reserve(256));
+    FIC_TRY(h->bf_best.reserve((size_t)n_ranges * (16 + 16 + 8) + 256));
+    FIC_TRY(h->pin_a.reserve(256));
+
+    __half* poolA = h->bf_pool.as<__half>();
+    __half* poolAx = h->bf_poolx.as<__half>();
+    float2* hk = h->bf_cand.as<float2>();
+    __half* rngB = h->bf_A.as<__half>();
+    __half* rngBx = rngB + (size_t)n_cols_pad * 64;
+    float* tau = h->bf_thr.as<float>();
+    int32_t* elig = reinterpret_cast<int32_t*>(tau + tau_pad);
+    int32_t* fallback = elig + n_ranges;
+    uint32_t* cnt = h->bf_surv.as<uint32_t>();
+    uint32_t* list = h->bf_list.as<uint32_t>();
+    int* ctrl = h->bf_ctrl.as<int>();
+    unsigned long long* surv_total = reinterpret_cast<unsigned long long*>(ctrl + 8);
+    int32_t* pre_idx = h->bf_best.as<int32_t>();
+    double* pre_so = reinterpret_cast<double*>(pre_idx + (size_t)n_ranges * 4);
+    double* pre_R = pre_so + (size_t)n_ranges * 2;
+
+    FIC_CUDA(cudaMemsetAsync(ctrl, 0, 64, st));
+    FIC_CUDA(cudaMemsetAsync(cnt, 0, (size_t)n_ranges * 4, st));
+
+    // 1. pool (independent of the ranges)
+    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
+    FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
+
+    // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range)
+    if (!probe) {
+        int S = (int)floor(sqrt((double)NP / 1000.0) + 0.5);
+        if (S < 1) S = 1;
+        h->prof_suppress = true;  // fic_profile times the screen kernel on this path, not the helper scans
+        int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
+        h->prof_suppress = false;
+        FIC_TRY(rc_pre);
+        bf_threshold_kernel<<<1, 1024, 0, st>>>(d_img, W, range_begin, n_ranges, pre_R, elig, tau, fallback, ctrl, tau_pad);
+        FIC_CHECK_LAUNCH(h, "bf_threshold_kernel");
+    } else {
+        // probe: every range eligible in natural order, infinite thresholds
+        std::vector<int32_t> e(n_ranges);
+        for (int k = 0; k < n_ranges; ++k) e[k] = range_begin + k;
+        std::vector<float> t(tau_pad, __builtin_inff());
+        int c[2] = {n_ranges, 0};
+        FIC_CUDA(cudaMemcpyAsync(elig, e.data(), (size_t)n_ranges * 4, cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaMemcpyAsync(tau, t.data(), (size_t)tau_pad * 4, cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaMemcpyAsync(ctrl, c, 8, cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaStreamSynchronize(st));
+    }
+
+    // 3. range operand
+    bf_rangeop_kernel<<<cdiv(n_cols_pad, 4), 256, 0, st>>>(d_img, W, elig, ctrl, n_cols_pad, rngB, rngBx);
+    FIC_CHECK_LAUNCH(h, "bf_rangeop_kernel");
+
+    // 4. the screen
+    CUtensorMap mapA, mapAx, mapB, mapBx;
+    FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
+    FIC_TRY(make_map(&mapAx, poolAx, (uint64_t)NP, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
+    FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B));
+    FIC_TRY(make_map(&mapBx, rngBx, (uint64_t)n_cols_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B));
+    ScreenParams sp;
+    sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
+    const int max_groups = n_cols_pad / BN;
+    int n_chunks = cdiv((long long)h->num_sms * 4, max_groups);
+    if (n_chunks > n_tiles / 8) n_chunks = n_tiles / 8;
+    if (n_chunks < 1) n_chunks = 1;
+    if (probe) n_chunks = 1;
+    sp.n_chunks = n_chunks;
+    sp.dump = probe;
+    sp.err_flag = ctrl + 2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        attr_set = true;
+    }
+    int grid = max_groups * n_chunks;
+    if (grid > h->num_sms) grid = h->num_sms;
+    if (probe) grid = 1;
+    {
+        ProfScope prof(h, st);
+        bf_screen_kernel<<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+    }
+    FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
+    if (probe) return FIC_OK;
+
+    // 5. exact rescoring of the survivors
+    bf_rescore_kernel<<<n_ranges, 256, 0, st>>>(d_img, P, sd4, sdd, H, W, range_begin, elig, ctrl, cnt, list, cap, fallback, d_idx,
+                                                d_so, d_R, surv_total);
+    FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
+
+    // 6. whatever the screen could not decide goes through the exact scan
+    int* hc = h->pin_a.as<int>();
+    FIC_CUDA(cudaMemcpyAsync(hc, ctrl, 64, cudaMemcpyDeviceToHost, st));
+    FIC_CUDA(cudaStreamSynchronize(st));
+    h->counters[CNT_D2H] += 64;
+    if (hc[2] != 0) { fic_set_error("bf_screen_kernel: pipeline wait %d timed out", hc[2]); return FIC_ECUDA; }
+    const int n_elig = hc[0], n_fb = hc[1];
+    unsigned long long st_total;
+    memcpy(&st_total, hc + 8, sizeof(st_total));  // surv_total sits at ctrl + 8 ints
+    h->counters[CNT_SURVIVORS] += (int64_t)st_total;
+    h->counters[CNT_SCREEN_RANGES] += n_elig - (n_fb - (n_ranges - n_elig));
+    h->counters[CNT_RESCAN_RANGES] += n_fb;
+    if (n_fb > 0) {
+        if (flags & FIC_BF_NO_FALLBACK) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
+        h->prof_suppress = true;
+        int rc_fb = bf_exact_scan8(h, d_img, H, W, 1, 1, FIC_BF_MODE_JIT, range_begin, n_fb, fallback, d_idx, d_so, d_R, st);
+        h->prof_suppress = false;
+        FIC_TRY(rc_fb);
+    }
+    return FIC_OK;
+}
+
+int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+                      double* d_so, double* d_R, unsigned flags, cudaStream_t st)
+{
+    return bf_screen_run(h, d_img, H, W, range_begin, n_ranges, d_idx, d_so, d_R, flags, nullptr, st);
 }

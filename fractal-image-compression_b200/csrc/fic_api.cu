@@ -3,6 +3,10 @@
 
 #include "fic_common.cuh"
 
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st);
+int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+                  double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st);
+
 static thread_local char g_err[512] = "";
 
 void fic_set_error(const char* fmt, ...)
@@ -189,6 +193,38 @@ int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, in
         FIC_TRY(fic_copy_out(h, out_idx, d_idx, (size_t)n * 4 * sizeof(int32_t), false, st));
         FIC_TRY(fic_copy_out(h, out_so, d_so, (size_t)n * 2 * sizeof(double), false, st));
         if (out_R) FIC_TRY(fic_copy_out(h, out_R, d_R, (size_t)n * sizeof(double), false, st));
+        FIC_CUDA(cudaStreamSynchronize(st));
+    }
+    return FIC_OK;
+}
+
+int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int range_begin, int n_ranges, float* out_u,
+                        unsigned flags, void* stream)
+{
+    FIC_REQUIRE(h && img && out_u, "fic_bf_screen_probe: NULL argument");
+    FIC_REQUIRE(H > 16 && W > 16 && H % 8 == 0 && W % 8 == 0, "fic_bf_screen_probe: image %dx%d unsupported", H, W);
+    const int total = (H / 8) * (W / 8);
+    FIC_REQUIRE(n_ranges >= 1 && n_ranges <= 32 && range_begin >= 0 && range_begin + n_ranges <= total,
+                "fic_bf_screen_probe: at most 32 ranges inside [0,%d)", total);
+    FIC_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = fic_stream(h, stream);
+    const bool dev = flags & FIC_DEVICE_PTRS;
+    const size_t NP = (size_t)(H - 16) * (W - 16);
+    const size_t rows = (NP + 127) / 128 * 128;
+    const uint8_t* d_img = img;
+    float* d_out = out_u;
+    if (!dev) {
+        FIC_TRY(h->d_img.reserve((size_t)H * W));
+        FIC_TRY(fic_copy_in(h, h->d_img.p, img, (size_t)H * W, false, st));
+        d_img = h->d_img.as<uint8_t>();
+        FIC_TRY(h->d_out_a.reserve(rows * 256 * sizeof(float)));
+        d_out = h->d_out_a.as<float>();
+    }
+    FIC_CUDA(cudaMemsetAsync(d_out, 0, rows * 256 * sizeof(float), st));
+    FIC_TRY(bf_prepare8(h, d_img, H, W, st));
+    FIC_TRY(bf_screen_run(h, d_img, H, W, range_begin, n_ranges, nullptr, nullptr, nullptr, flags, d_out, st));
+    if (!dev) {
+        FIC_TRY(fic_copy_out(h, out_u, d_out, rows * 256 * sizeof(float), false, st));
         FIC_CUDA(cudaStreamSynchronize(st));
     }
     return FIC_OK;

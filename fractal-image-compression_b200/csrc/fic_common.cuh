@@ -102,6 +102,7 @@ struct fic_handle {
     int64_t counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     // optional event timing of the dominant kernel (fic_profile)
     bool prof_on = false;
+    bool prof_suppress = false;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     // generic staging
     DevBuf d_img, d_out_a, d_out_b, d_out_c, d_in_a, d_in_b;
@@ -129,7 +130,7 @@ struct ProfScope {
     cudaStream_t st;
     ProfScope(fic_handle* h_, cudaStream_t st_) : h(h_), st(st_)
     {
-        if (!h->prof_on) return;
+        if (!h->prof_on || h->prof_suppress) { h = nullptr; return; }
         cudaEvent_t a, b;
         if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { h = nullptr; return; }
         h->prof_events.push_back(a);

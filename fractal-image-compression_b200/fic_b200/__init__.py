@@ -52,6 +52,7 @@ SIGNATURES = {
                                       C.c_uint, _vp]),
     "fic_bf_encode_static": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp,
                                        _vp, _vp]),
+    "fic_bf_screen_probe": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_bf_decode": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_average_subsample": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_qt_encode": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int,
@@ -226,6 +227,19 @@ def bf_encode_static_dev(img_ptr: int, H: int, W: int, idx_ptr: int, so_ptr: int
     _check(lib().fic_bf_encode_static(_vp(img_ptr), int(H), int(W), int(strides[0]), int(strides[1]), int(mode),
                                       int(range_begin), int(range_end), _vp(idx_ptr), _vp(so_ptr), _vp(R_ptr),
                                       _vp(stream) if stream else None), "fic_bf_encode_static")
+
+
+def bf_screen_probe(img, range_begin=0, n_ranges=32, handle: Handle | None = None) -> np.ndarray:
+    """Raw tensor-core correlation values u[position, range*8 + isometry] for up to 32 ranges (diagnostic)."""
+    h = handle or default_handle()
+    a = _img(img)
+    H, W = a.shape
+    NP = (H - 16) * (W - 16)
+    rows = (NP + 127) // 128 * 128
+    out = np.zeros((rows, 256), np.float32)
+    _check(lib().fic_bf_screen_probe(h.ptr, _ptr(a), H, W, int(range_begin), int(n_ranges), _ptr(out), 0, None),
+           "fic_bf_screen_probe")
+    return out[:NP, :n_ranges * 8]
 
 
 def bf_encode_batch(imgs, range_size=8, domain_size=16, mode=BF_MODE_JIT, flags=0, handle: Handle | None = None):

@@ -98,6 +98,17 @@ int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W,
                         void* stream);
 
 /*
+ * Diagnostic hook for the tensor-core path of fic_bf_encode (no counterpart in the reference; the quantity it
+ * exposes is the cross-correlation numerator of bruteforce/jit_bfencoder.py:76): runs the pool kernel, the range
+ * operand kernel and the tcgen05 correlation GEMM for the n_ranges <= 32 ranges starting at range_begin and returns
+ * the raw fp32 accumulators  u = sum_k r'_k*D4'_k - rho*eps/64  (= (64*ab - sum(r)*sum(d))/4 in the reference's terms):
+ * out_u float32 [ceil(NP/128)*128][256], row = stride-1 domain position di*(W-16)+dj, column = range*8 + orientation*4
+ * + rotation.  Tests use it to check TMA / descriptor / MMA plumbing and the accumulator's exactness.
+ */
+int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int range_begin, int n_ranges, float* out_u,
+                        unsigned flags, void* stream);
+
+/*
  * No counterpart in the reference (the reference never manages device memory).
  *
  * The same exact 8x8 / 16x16 brute-force encode as fic_bf_encode, for callers that are not allowed to allocate

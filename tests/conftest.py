@@ -17,11 +17,9 @@ def pytest_configure(config):
 
 
 def _has_gpu() -> bool:
-    try:
-        import fic_b200
-        return fic_b200.lib().fic_device_count() > 0
-    except Exception:
-        return False
+    # a library that does not load is a build error, not "no GPU": let it propagate so the run fails loudly
+    import fic_b200
+    return fic_b200.lib().fic_device_count() > 0
 
 
 def pytest_collection_modifyitems(config, items):

@@ -1,0 +1,117 @@
+"""GPU: the tensor-core screen of the brute-force encoder.
+
+(1) `fic_bf_screen_probe` returns the raw tcgen05 accumulators; they must equal the exact rational value
+    u = sum r'_k D4'_k - rho*eps/64 computed with integers here (this pins the TMA tensor maps, the UMMA shared-memory
+    and instruction descriptors, the TMEM lane/column mapping and the fp32 accumulation all at once).
+(2) The full pipeline (pool -> screen -> exact rescoring [-> exact re-scan]) must return the same records as the
+    exhaustive exact scan, bit for bit, on natural, synthetic, saturated and flat-heavy images.
+"""
+import numpy as np
+import pytest
+
+from conftest import synthetic_image
+
+pytestmark = pytest.mark.gpu
+
+
+def exact_u(img, range_begin, n_ranges):
+    img = img.astype(np.int64)
+    H, W = img.shape
+    box = img[:-1, :-1] + img[:-1, 1:] + img[1:, :-1] + img[1:, 1:]          # P[y][x]
+    PH, PW = H - 16, W - 16
+    # D4[p, a, b] = P[di + 2a, dj + 2b]
+    D4 = np.empty((PH, PW, 8, 8), np.int64)
+    for a in range(8):
+        for b in range(8):
+            D4[:, :, a, b] = box[2 * a:2 * a + PH, 2 * b:2 * b + PW]
+    D4 = D4.reshape(PH * PW, 8, 8)
+    sd4 = D4.sum((1, 2))
+    m_c = (sd4 + 32) >> 6
+    eps = sd4 - 64 * m_c
+    Dc = D4 - m_c[:, None, None]
+    rw = W // 8
+    out = np.empty((PH * PW, n_ranges * 8), np.float64)
+    for k in range(n_ranges):
+        ridx = range_begin + k
+        ri, rj = (ridx // rw) * 8, (ridx % rw) * 8
+        r = img[ri:ri + 8, rj:rj + 8]
+        s = int(r.sum())
+        m_r = (s + 32) >> 6
+        rho = s - 64 * m_r
+        rc = r - m_r
+        for orient in range(2):
+            base = Dc.transpose(0, 2, 1) if orient else Dc
+            for rot in range(4):
+                Y = np.rot90(base, rot, axes=(1, 2))                             # jit_bfencoder.py:44-49
+                out[:, k * 8 + orient * 4 + rot] = (Y * rc[None]).sum((1, 2)) - rho * eps / 64.0
+    return out
+
+
+@pytest.mark.parametrize("case", ["synthetic", "extremes", "lena_offset"])
+def test_probe_accumulators_are_exact(fic, images, case):
+    if case == "synthetic":
+        img, begin, n = synthetic_image(3, 96, 96), 0, 32
+    elif case == "extremes":
+        rng = np.random.default_rng(5)
+        img = (np.indices((96, 112)).sum(0) % 2 * 255).astype(np.uint8)   # 0/255 checkerboard: largest products
+        img[:32] = 255
+        img[32:48, :48] = 0
+        img[60:, 50:] = rng.integers(0, 256, (36, 62))
+        begin, n = 7, 32
+    else:
+        img, begin, n = np.ascontiguousarray(images["lena256"][:128, :160]), 100, 17
+    got = fic.bf_screen_probe(img, begin, n).astype(np.float64)
+    want = exact_u(img, begin, n)
+    err = np.abs(got - want)
+    # integers below 2^24 plus one multiple of 1/64: the fp32 accumulator is exact whenever |u| < 2^17 and never
+    # off by more than the DELTA_U = 2 the screen allows for
+    assert err.max() <= 2.0, f"max |u_tc - u| = {err.max()}"
+    small = np.abs(want) < 2 ** 17
+    assert (err[small] == 0).all(), f"inexact below 2^17: max {err[small].max()}"
+
+
+@pytest.mark.parametrize("seed,shape", [(1, (96, 96)), (2, (128, 200)), (3, (160, 96))])
+def test_pipeline_equals_exact_scan(fic, seed, shape):
+    img = synthetic_image(seed, *shape)
+    if seed == 3:
+        img[:40] = 255          # saturated: flat ranges the screen must hand to the exact scan
+        img[100:120, 10:60] = 0
+    h = fic.default_handle()
+    h.reset_counters()
+    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
+    c = h.counters()
+    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    n = (shape[0] // 8) * (shape[1] // 8)
+    assert c["screen_ranges"] + c["rescan_ranges"] == n
+    if seed != 3:
+        assert c["screen_ranges"] > 0
+
+
+def test_pipeline_noise_image(fic):
+    """White noise: every candidate is about equally bad, the survivor lists are long."""
+    rng = np.random.default_rng(17)
+    img = rng.integers(0, 256, (96, 96), dtype=np.uint8)
+    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
+    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def test_pipeline_range_slice(fic, images):
+    img = np.ascontiguousarray(images["lena256"][64:192, 64:192])
+    full = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    part = fic.bf_encode(img, mode=fic.BF_MODE_JIT, range_begin=37, range_end=201)
+    for x, y in zip(part, full):
+        assert np.array_equal(x, y[37:201])
+
+
+def test_pipeline_counts_on_lena512(fic, images):
+    h = fic.default_handle()
+    h.reset_counters()
+    fic.bf_encode(images["lena512"], mode=fic.BF_MODE_JIT)
+    c = h.counters()
+    assert c["screen_ranges"] + c["rescan_ranges"] == 4096
+    assert c["screen_ranges"] >= 3500, c          # natural image: nearly every range is decided by the screen
+    print("lena512 screen counters:", c)
