@@ -10,27 +10,36 @@
 //     u = sum r'_k*D4'_k - rho*eps/64                              (exact identity)
 // which is one K=80 dot product of fp16-exact operands: 64 products of integers (|r'|<=255, |D4'|<=1020, every
 // partial sum < 2^24, exact in the fp32 accumulator) plus one extension column rho * (-eps/64).
-// For ANY (s,o) the collage error obeys  R >= R_opt = (A_r - 64*u^2/den16)/64  with A_r = sum r^2 - (sum r)^2/64 and
-// den16 = 64*sum(D4^2) - SD4^2 (exact integers); the reference's float32 noise lowers its R by at most G = 0.26
-// ("guard derivation": s^2*delta(sum d^2)/n <= 0.245 for |s| <= 1).  Given an upper bound UB_r
-// on the winner's R (the exact R of any candidate, here the best of a coarse exact pre-scan), candidate c can only
-// win or tie if   64*u^2/den16 >= T_r := A_r - 64*(UB_r + G)   <=>   |u| * h_c >= tau_r,
-// h_c = 8/sqrt(den16), tau_r = sqrt(T_r).  The epilogue evaluates  fma(|u|, h_c, k_c) >= tau_r  with
-// k_c = DELTA*h_c absorbing the accumulator's rounding of the fractional extension term: 2 instructions per output.
-// Ranges with T_r <= 0 (flat ranges: the screen cannot separate anything) and ranges whose survivor list overflows
-// are handed to the exact scan.
+//
+// Bound.  For ANY (s,o) the exact-arithmetic collage error obeys R >= R_opt = (A_r - 64*u^2/den16)/64 with
+// A_r = sum r^2 - (sum r)^2/64, den16 = 64*sum(D4^2) - SD4^2 (integers).  The reference's R differs from exact
+// arithmetic only through its float32 sequential sum of d^2 (every other input is exact for 8x8 blocks):
+//     R_ref(c) >= R_opt(c) - kappa_c * s_ref^2,   kappa_c = 1.02 * 63 * 2^-24 / 64 * sum d^2   (<= 0.25)
+// and |s_ref| <= 1 (clamp).  For a well-conditioned domain (den16 >= 5e-4 * sum D4^2, i.e. the float32 noise in the
+// denominator is below half of it) |s_ref| <= 2|s_opt| = 512|u|/den16, so the guard is proportional to u^2 and folds
+// into the per-candidate scale:  candidate c can win or tie only if
+//     u^2 * h_c^2 >= A_r - 64*UB_r,     h_c^2 = 64/den16 * (1 + 1e-3 * sum D4^2 / den16)          (tau_A)
+// For the (rare) ill-conditioned domains the constant guard is used:  u^2 * 64/den16 >= A_r - 64*(UB_r + 0.26)  (tau_B).
+// UB_r is the exact R of some candidate (any exactly scored candidate bounds the winner from above).
+// The epilogue evaluates  fma(|u|, h_c, k_c) >= tau  with k_c = DELTA*h_c absorbing the accumulator's rounding of the
+// fractional extension term: 2 instructions per output, tau chosen per (thread, range) from {tau_A, tau_B}.
+//
+// Two rounds: round 1 screens every 8th candidate tile against bounds from a coarse exact pre-scan (~1000 positions
+// per range); its survivors are rescored exactly and give much tighter bounds for round 2 over the remaining tiles.
+// Ranges the screen cannot decide (bound not below the range's own variance, survivor list overflow) go to the
+// exact scan; constant ranges are decided directly (every candidate ties at R = 0, the first one wins).
 //
 // GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 4-stage ring), N = 256 columns = 32 ranges
 // x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
 // TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
 // tile t.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer + TMEM allocator, warps 2..9 epilogue (two per TMEM
 // lane quadrant, 128 columns each).  Thread = candidate, so h_c/k_c are per-thread registers and the 8 isometry
-// columns of a range share one tau register (16 per thread).
+// columns of a range share one tau.  The (group, tile) space is cut into equal contiguous spans, one per CTA.
 //
 // HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
 //   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
 //   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
-//   hk      float2 [NP]    (h_c, k_c)
+//   hk      float2 [NP]    (+-h_c, k_c); a negative h marks an ill-conditioned domain
 // and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -62,8 +71,9 @@ constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
 constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
 constexpr uint32_t SCREEN_SMEM = OFF_BARS + 256 + 1024;  // + slack to align the base to 1024
 
-constexpr float GUARD_R = 0.26f;     // reference float32 noise, in R (MSE) units
+constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
 constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
+constexpr int ROUND_ALL = 0, ROUND_EIGHTH = 1, ROUND_REST = 2;
 
 // ---- PTX wrappers ----------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -156,29 +166,97 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
           "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
         : "r"(taddr));
 }
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait for the outstanding TMEM loads; the registers are tied to the asm so no consumer can be scheduled above it
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
+                   "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                   "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+                 :
+                 : "memory");
+}
 
 struct ScreenParams {
     const float2* hk;        // [NP]
-    const float* tau;        // [slots padded to 32]
+    const float2* tau;       // [slots padded to 32] = (tau_A, tau_B)
     const int* n_elig;       // device scalar
-    uint32_t* cnt;           // [slots] survivors found
+    uint32_t* cnt;           // [slots] survivors found this round
     uint32_t* list;          // [slots][cap] entries = position*8 + isometry
     uint32_t cap;
     int NP;
-    int n_tiles;
-    int n_chunks;
+    int n_tiles;             // candidate tiles in the whole pool
+    int round;               // ROUND_ALL / ROUND_EIGHTH / ROUND_REST
+    int n_round_tiles;       // tiles visited in this round
     float* dump;             // probe mode: [n_tiles*128][256] raw accumulators of column group 0 (else nullptr)
     int* err_flag;
 };
 
-__device__ __forceinline__ void unit_range(const ScreenParams& p, int unit, int& grp, int& t0, int& t1)
+__device__ __forceinline__ int tile_of(int round, int j)
 {
-    grp = unit / p.n_chunks;
-    const int c = unit - grp * p.n_chunks;
-    const int per = (p.n_tiles + p.n_chunks - 1) / p.n_chunks;
-    t0 = c * per;
-    t1 = min(p.n_tiles, t0 + per);
+    if (round == ROUND_EIGHTH) return j * 8;
+    if (round == ROUND_REST) return j + j / 7 + 1;  // skips the multiples of 8
+    return j;
+}
+
+// Contiguous span of the linearised (group, round tile) space owned by this CTA.
+struct Span {
+    long long lin, end;
+    int n_round_tiles;
+    __device__ Span(const ScreenParams& p, int n_groups)
+    {
+        const long long total = (long long)n_groups * p.n_round_tiles;
+        const long long per = (total + gridDim.x - 1) / gridDim.x;
+        lin = per * blockIdx.x;
+        end = lin + per < total ? lin + per : total;
+        n_round_tiles = p.n_round_tiles;
+    }
+    __device__ bool next(int& grp, int& j0, int& j1)
+    {
+        if (lin >= end) return false;
+        grp = (int)(lin / n_round_tiles);
+        j0 = (int)(lin - (long long)grp * n_round_tiles);
+        const long long room = end - lin;
+        j1 = (long long)n_round_tiles - j0 < room ? n_round_tiles : j0 + (int)room;
+        lin += j1 - j0;
+        return true;
+    }
+};
+
+// screen one 32-column chunk held in registers; `c4` and all indices are compile-time after unrolling
+template <int C4>
+__device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float hx, const float ky, const bool ill,
+                                             const float (&tauA)[16], const float (&tauB)[16], const ScreenParams& p, int slot0,
+                                             int my_cand)
+{
+    float th[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) th[g] = ill ? tauB[C4 * 4 + g] : tauA[C4 * 4 + g];
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) any |= fmaf(fabsf(__uint_as_float(v[j])), hx, ky) >= th[j >> 3];
+    if (__any_sync(0xffffffffu, any)) {
+        if (any) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                unsigned m8 = 0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    m8 |= (fmaf(fabsf(__uint_as_float(v[g * 8 + i])), hx, ky) >= th[g] ? 1u : 0u) << i;
+                if (m8) {  // one reservation for all isometries of this (candidate, range)
+                    const int slot = slot0 + C4 * 4 + g;
+                    uint32_t at = atomicAdd(&p.cnt[slot], (uint32_t)__popc(m8));
+                    while (m8) {
+                        const int i = __ffs(m8) - 1;
+                        m8 &= m8 - 1;
+                        if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)my_cand * 8u + (uint32_t)i;
+                        ++at;
+                    }
+                }
+            }
+        }
+    }
 }
 
 // ---- the screen ---------------------------------------------------------------------------------------------
@@ -202,7 +280,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
     const int n_groups = (n_elig + 31) / 32;
-    const int n_units = n_groups * p.n_chunks;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -225,15 +302,16 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0, bph = 0;
-            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-                int grp, t0, t1;
-                unit_range(p, unit, grp, t0, t1);
+            Span span(p, n_groups);
+            int grp, j0, j1;
+            while (span.next(grp, j0, j1)) {
                 mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
                 mbar_expect_tx(b_full, B_MAIN_BYTES + B_EXT_BYTES);
                 tma_load_2d(base + OFF_B_MAIN, &mapB, b_full, 0, grp * BN);
                 tma_load_2d(base + OFF_B_EXT, &mapBx, b_full, 0, grp * BN);
                 bph ^= 1;
-                for (int t = t0; t < t1; ++t) {
+                for (int j = j0; j < j1; ++j) {
+                    const int t = tile_of(p.round, j);
                     mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
                     mbar_expect_tx(full_bar(s), A_MAIN_BYTES + A_EXT_BYTES);
                     tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t * BM);
@@ -249,12 +327,12 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             uint32_t ph = 0, aph = 0, bph = 0;
             const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
             const uint64_t bxdesc = make_desc(base + OFF_B_EXT, 256, 6);
-            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-                int grp, t0, t1;
-                unit_range(p, unit, grp, t0, t1);
+            Span span(p, n_groups);
+            int grp, j0, j1;
+            while (span.next(grp, j0, j1)) {
                 mbar_wait(b_full, bph, p.err_flag, 3);
                 bph ^= 1;
-                for (int t = t0; t < t1; ++t) {
+                for (int j = j0; j < j1; ++j) {
                     mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
                     mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
                     tcgen05_fence_after();
@@ -280,55 +358,56 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         const int half = ew >> 2;         // which 128 of the 256 columns
         int as = 0;
         uint32_t aph = 0;
-        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-            int grp, t0, t1;
-            unit_range(p, unit, grp, t0, t1);
-            float tau[16];
+        Span span(p, n_groups);
+        int grp, j0, j1;
+        while (span.next(grp, j0, j1)) {
+            float tauA[16], tauB[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) tau[j] = p.tau[grp * 32 + half * 16 + j];
+            for (int j = 0; j < 16; ++j) {
+                const float2 tt = p.tau[grp * 32 + half * 16 + j];
+                tauA[j] = tt.x;
+                tauB[j] = tt.y;
+            }
             const int slot0 = grp * 32 + half * 16;
-            int cand = t0 * BM + quad * 32 + lane;
-            float2 hk_next = cand < p.NP && t0 < t1 ? p.hk[cand] : make_float2(0.f, 0.f);
-            for (int t = t0; t < t1; ++t) {
+            const int lane_off = quad * 32 + lane;
+            int cand = tile_of(p.round, j0) * BM + lane_off;
+            float2 hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
+            for (int j = j0; j < j1; ++j) {
                 const float2 hk = hk_next;
                 const int my_cand = cand;
-                cand += BM;
-                if (t + 1 < t1) hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
+                if (j + 1 < j1) {
+                    cand = tile_of(p.round, j + 1) * BM + lane_off;
+                    hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
+                }
+                const bool ill = hk.x < 0.f;
+                const float hx = fabsf(hk.x), ky = hk.y;
                 mbar_wait(tfull_bar(as), aph, p.err_flag, 6);
                 tcgen05_fence_after();
                 const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN + half * 128);
-#pragma unroll 1
-                for (int c4 = 0; c4 < 4; ++c4) {
-                    uint32_t v[32];
-                    tmem_ld32(taddr0 + c4 * 32, v);
-                    tmem_ld_wait();
-                    if (p.dump) {
-                        if (grp == 0 && my_cand < p.n_tiles * BM) {
+                uint32_t va[32], vb[32];
+                if (p.dump) {
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        tmem_ld32(taddr0 + c4 * 32, va);
+                        tmem_ld_wait(va);
+                        if (grp == 0) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                p.dump[(size_t)my_cand * BN + half * 128 + c4 * 32 + j] = __uint_as_float(v[j]);
-                        }
-                        continue;
-                    }
-                    bool any = false;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float val = fmaf(fabsf(__uint_as_float(v[j])), hk.x, hk.y);
-                        any |= val >= tau[c4 * 4 + (j >> 3)];
-                    }
-                    if (__any_sync(0xffffffffu, any)) {
-                        if (any) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                const float val = fmaf(fabsf(__uint_as_float(v[j])), hk.x, hk.y);
-                                if (val >= tau[c4 * 4 + (j >> 3)]) {
-                                    const int slot = slot0 + c4 * 4 + (j >> 3);
-                                    const uint32_t at = atomicAdd(&p.cnt[slot], 1u);
-                                    if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)my_cand * 8u + (uint32_t)(j & 7);
-                                }
-                            }
+                            for (int q = 0; q < 32; ++q)
+                                p.dump[(size_t)my_cand * BN + half * 128 + c4 * 32 + q] = __uint_as_float(va[q]);
                         }
                     }
+                } else {
+                    tmem_ld32(taddr0, va);
+                    tmem_ld32(taddr0 + 32, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    screen_chunk<0>(va, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
+                    tmem_ld32(taddr0 + 64, va);       // in flight while chunk 1 is screened
+                    screen_chunk<1>(vb, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
+                    tmem_ld32(taddr0 + 96, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    screen_chunk<2>(va, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
+                    screen_chunk<3>(vb, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
                 }
                 tcgen05_fence_before();
                 __syncwarp();
@@ -390,18 +469,33 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
     const long long den16 = 64ll * s2 - (long long)s * s;  // >= 0, exact
     float hc = 0.f, kc = 0.f;
     if (den16 > 0) {
-        hc = (float)(8.0 / sqrt((double)den16)) * (1.0f + 1.0f / 1048576.0f);  // rounded up a little: never under-estimate
+        const double d = (double)den16, q = (double)s2;
+        const bool well = d >= 5e-4 * q;
+        const double h2 = well ? 64.0 / d * (1.0 + 1.0e-3 * q / d) : 64.0 / d;
+        hc = (float)sqrt(h2) * (1.0f + 1.0f / 1048576.0f);  // rounded up a little: never under-estimate
         kc = DELTA_U * hc;
+        if (!well) hc = -hc;                                   // sign flags the ill-conditioned class
     }
+    // den16 == 0: constant domain, u == 0 exactly, s_ref == 0, R_ref == A_r/64 with no noise: (0,0) with tau_A is exact
     hk[p] = make_float2(hc, kc);
 }
 
-// ---- thresholds + compaction: which ranges the screen can decide ------------------------------------------------
-// ctrl[0] = n_elig, ctrl[1] = n_fallback (grows again when survivor lists overflow), ctrl[2] = error flag
+// ---- per-range state --------------------------------------------------------------------------------------------
+// The running winner of every range (exact R, scan index, s, o), seeded by the coarse pre-scan, improved by every
+// rescoring round; plus the bound ingredients.
+struct RangeState {
+    double R, s, o, TA0;           // TA0 = A_r - 64e-9*sum r^2  (threshold numerator before the bound is applied)
+    unsigned long long seq;        // position*8 + isometry of the running winner
+    int ridx;                      // absolute range index
+    int flags;                     // 1 = sent to the exact scan, 2 = constant range (decided)
+};
+
+// ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
 __global__ void __launch_bounds__(1024)
-bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, const double* __restrict__ preR,
-                    int32_t* __restrict__ elig, float* __restrict__ tau, int32_t* __restrict__ fallback, int* __restrict__ ctrl,
-                    int tau_pad)
+bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int PW, int range_begin, int n_ranges,
+                    const int32_t* __restrict__ pre_idx, const double* __restrict__ pre_so, const double* __restrict__ pre_R,
+                    RangeState* __restrict__ state, float2* __restrict__ tau, int32_t* __restrict__ fallback,
+                    int* __restrict__ ctrl, int tau_pad)
 {
     __shared__ int warp_e[32], warp_f[32];
     __shared__ int base_e, base_f;
@@ -412,7 +506,8 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int
     for (int b0 = 0; b0 < n_ranges; b0 += 1024) {
         const int slot = b0 + tid;
         bool is_e = false, is_f = false;
-        float my_tau = 0.f;
+        float2 my_tau = make_float2(0.f, 0.f);
+        RangeState rs_;
         if (slot < n_ranges) {
             const int ridx = range_begin + slot;
             const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
@@ -422,12 +517,23 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int
                 s += x;
                 q += x * x;
             }
-            const double A = (double)(64 * q - s * s) * 0.015625;           // sum r^2 - (sum r)^2/64, exact
-            const double ub = preR[slot];
-            const double T = A - 64.0 * (ub + (double)GUARD_R + 1e-9 * (double)q);
-            if (ub == ub && ub < 1e300 && T > 1e-3) {
+            const long long A64 = 64 * q - s * s;                             // 64 * A_r, exact
+            const double ub = pre_R[slot];
+            rs_.R = ub; rs_.s = pre_so[2 * slot]; rs_.o = pre_so[2 * slot + 1];
+            rs_.seq = ((unsigned long long)pre_idx[4 * slot] * PW + pre_idx[4 * slot + 1]) * 8ull + pre_idx[4 * slot + 2] * 4 + pre_idx[4 * slot + 3];
+            rs_.ridx = ridx; rs_.flags = 0;
+            rs_.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
+            const double TA = rs_.TA0 - 64.0 * ub, TB = TA - 64.0 * GUARD_ILL;
+            if (A64 == 0) {
+                // constant range: every candidate scores R = 0 exactly, the first in scan order wins; the pre-scan
+                // always visits position 0, isometry 0, so the seeded state already holds the winner
                 is_e = true;
-                my_tau = (float)sqrt(T) * (1.0f - 1.0f / 1048576.0f);      // rounded down a little: never over-estimate
+                rs_.flags = 2;
+                my_tau = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+            } else if (ub == ub && ub < 1e300 && TA > 1e-3) {
+                is_e = true;
+                my_tau.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);     // rounded down a little: never over-estimate
+                my_tau.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
             } else {
                 is_f = true;
             }
@@ -439,7 +545,7 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int
         for (int w = 0; w < warp; ++w) { pe += warp_e[w]; pf += warp_f[w]; }
         pe += __popc(me & ((1u << lane) - 1u));
         pf += __popc(mf & ((1u << lane) - 1u));
-        if (is_e) { elig[pe] = range_begin + slot; tau[pe] = my_tau; }
+        if (is_e) { state[pe] = rs_; tau[pe] = my_tau; }
         if (is_f) fallback[pf] = range_begin + slot;
         __syncthreads();
         if (tid == 0) {
@@ -451,12 +557,28 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int
         __syncthreads();
     }
     // pad tau so that every column group reads 32 valid entries: +inf never passes
-    for (int k = base_e + tid; k < tau_pad; k += 1024) tau[k] = __int_as_float(0x7f800000);
+    for (int k = base_e + tid; k < tau_pad; k += 1024) tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
     if (tid == 0) { ctrl[0] = base_e; ctrl[1] = base_f; }
 }
 
+// thresholds for round 2 from the improved winners
+__global__ void bf_retau_kernel(const RangeState* __restrict__ state, const int* __restrict__ ctrl, float2* __restrict__ tau)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= ctrl[0]) return;
+    const RangeState st = state[slot];
+    float2 t = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+    if (st.flags == 0) {
+        const double TA = st.TA0 - 64.0 * st.R, TB = TA - 64.0 * GUARD_ILL;
+        // TA can only have grown since round 1 (R decreased), so it is still positive
+        t.x = TA > 0.0 ? (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+        t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+    }
+    tau[slot] = t;
+}
+
 // ---- range operand: 8 inverse-transformed, centred copies of every eligible range -------------------------------
-__global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const int32_t* __restrict__ elig,
+__global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const RangeState* __restrict__ state,
                                   const int* __restrict__ ctrl, int n_cols_pad, __half* __restrict__ rngB,
                                   __half* __restrict__ rngBx)
 {
@@ -469,19 +591,17 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
     int rho = 0;
     if (slot < n_elig) {
         const int rw = W / 8;
-        const int ridx = elig[slot];
+        const int ridx = state[slot].ridx;
         const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
         int s = 0;
         for (int e = 0; e < 64; ++e) s += img[(size_t)(ri + (e >> 3)) * W + rj + (e & 7)];
         const int m = (s + 32) >> 6;
         rho = s - 64 * m;
-        // column entry k = (sa,sb) holds r'[i][j] with (sa,sb) = iso_t(i,j): find the (i,j) that maps onto k
-        // by applying the map to every (i,j) would be 64 steps; the isometries are involutive up to rotation
-        // direction, so invert explicitly: iso_t^{-1}(sa,sb)
+        // entry k = (sa,sb) of column t holds r'[i][j] with (sa,sb) = iso_t(i,j): invert fic_iso_bf
         const int sa = k >> 3, sb = k & 7;
-        int a = (t >> 2) ? sb : sa, b = (t >> 2) ? sa : sb;  // undo the transpose: (a,b) index into rot90(.,rot)
+        const int a = (t >> 2) ? sb : sa, b = (t >> 2) ? sa : sb;  // undo the transpose
         int i, j;
-        switch (t & 3) {  // a = f_i(i,j), b = f_j(i,j) of fic_iso_bf -> solve for (i,j)
+        switch (t & 3) {
         case 0: i = a; j = b; break;
         case 1: j = a; i = 7 - b; break;          // a = j, b = 7 - i
         case 2: i = 7 - a; j = 7 - b; break;
@@ -493,13 +613,13 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
     if (k < 16) rngBx[(size_t)col * 16 + k] = (k == 0 && slot < n_elig) ? __int2half_rn(rho) : __float2half_rn(0.f);
 }
 
-// ---- exact rescoring of the survivors: one CTA per eligible range ------------------------------------------------
+// ---- exact rescoring of the survivors: one CTA per eligible range, merges into the range state -------------------
 __global__ void __launch_bounds__(256)
 bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
-                  const float* __restrict__ sdd, int H, int W, int range_begin, const int32_t* __restrict__ elig,
-                  int* __restrict__ ctrl, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
-                  int32_t* __restrict__ fallback, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
-                  double* __restrict__ out_R, unsigned long long* __restrict__ surv_total)
+                  const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
+                  int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
+                  int32_t* __restrict__ fallback, int emit, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                  double* __restrict__ out_R)
 {
     const int slot = blockIdx.x;
     if (slot >= ctrl[0]) return;
@@ -507,18 +627,24 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ 
     __shared__ double sh_rs, sh_sq;
     __shared__ BestRec red[8];
     __shared__ double red_s[8], red_o[8];
+    __shared__ RangeState st;
     const int tid = threadIdx.x;
-    const int ridx = elig[slot];
+    if (tid == 0) st = state[slot];
+    __syncthreads();
+    const int ridx = st.ridx;
     const uint32_t n = cnt[slot];
-    if (n > cap || n == 0) {  // overflow (or, impossibly, nothing): let the exact scan decide this range
+    const int rw = W / 8, PW = W - 16, BW = W - 1;
+    const int NP = PW * (H - 16);
+    if (st.flags & 1) return;  // already handed to the exact scan
+    if (n > cap) {             // survivor list overflowed: let the exact scan decide this range
         if (tid == 0) {
             int at = atomicAdd(&ctrl[1], 1);
             fallback[at] = ridx;
+            state[slot].flags = 1;
+            cnt[slot] = 0;
         }
         return;
     }
-    const int rw = W / 8, PW = W - 16, BW = W - 1;
-    const int NP = PW * (H - 16);
     const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
     if (tid < 64) r_s[tid] = (float)img[(size_t)(ri + (tid >> 3)) * W + rj + (tid & 7)];
     __syncthreads();
@@ -527,12 +653,13 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ 
         for (int k = 0; k < 64; ++k) { unsigned v = (unsigned)r_s[k]; s += v; q += v * v; }
         sh_rs = (double)s;
         sh_sq = (double)q;
-        atomicAdd(surv_total, (unsigned long long)n);
+        if (n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
     }
     __syncthreads();
     const double rs = sh_rs, sqr = sh_sq;
     double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
     unsigned long long bseq = ~0ull;
+    if (tid == 0) { bR = st.R; bseq = st.seq; bs = st.s; bo = st.o; }  // the running winner competes too
     for (uint32_t e = tid; e < n; e += 256) {
         const uint32_t ent = list[(size_t)slot * cap + e];
         const int t = ent & 7;
@@ -565,20 +692,25 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ 
         double s = red_s[0], o = red_o[0];
         for (int w = 1; w < 8; ++w)
             if (fic_better(red[w].R, red[w].seq, b.R, b.seq)) { b = red[w]; s = red_s[w]; o = red_o[w]; }
-        const size_t os_ = (size_t)(ridx - range_begin);
-        if (b.seq == ~0ull) {  // every survivor scored NaN/inf: cannot happen for finite images, but stay exact
+        cnt[slot] = 0;  // the next round starts from an empty list
+        if (b.seq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
             int at = atomicAdd(&ctrl[1], 1);
             fallback[at] = ridx;
+            state[slot].flags = 1;
             return;
         }
-        const int t = (int)(b.seq & 7ull), p = (int)(b.seq >> 3);
-        out_idx[4 * os_ + 0] = p / PW;
-        out_idx[4 * os_ + 1] = p % PW;
-        out_idx[4 * os_ + 2] = t >> 2;
-        out_idx[4 * os_ + 3] = t & 3;
-        out_so[2 * os_] = s;
-        out_so[2 * os_ + 1] = o;
-        out_R[os_] = b.R;
+        state[slot].R = b.R; state[slot].seq = b.seq; state[slot].s = s; state[slot].o = o;
+        if (emit) {
+            const size_t os_ = (size_t)(ridx - range_begin);
+            const int t = (int)(b.seq & 7ull), p = (int)(b.seq >> 3);
+            out_idx[4 * os_ + 0] = p / PW;
+            out_idx[4 * os_ + 1] = p % PW;
+            out_idx[4 * os_ + 2] = t >> 2;
+            out_idx[4 * os_ + 3] = t & 3;
+            out_so[2 * os_] = s;
+            out_so[2 * os_ + 1] = o;
+            out_R[os_] = b.R;
+        }
     }
 }
 
@@ -624,8 +756,8 @@ bool bf_screen_applicable(int H, int W)
     return H > 16 && W > 16 && (long long)(H - 16) * (W - 16) >= 4096;
 }
 
-// `probe` != nullptr: debugging/validation mode -- only column group 0 is run and the raw accumulators are written
-// to probe[NP_pad][256]; all ranges are treated as eligible (tau = +inf) so nothing is appended.
+// `probe` != nullptr: debugging/validation mode -- one column group is run over all tiles with infinite thresholds and
+// the raw accumulators are written to probe[n_tiles*128][256].
 int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
                   double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st)
 {
@@ -646,7 +778,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_TRY(h->bf_poolx.reserve((size_t)NP * 16 * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 80 * 2 + 256));
-    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * 4 + (size_t)n_ranges * 4 * 2 + 256));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (sizeof(int32_t) + sizeof(RangeState)) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_ctrl.reserve(256));
@@ -658,13 +790,12 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     float2* hk = h->bf_cand.as<float2>();
     __half* rngB = h->bf_A.as<__half>();
     __half* rngBx = rngB + (size_t)n_cols_pad * 64;
-    float* tau = h->bf_thr.as<float>();
-    int32_t* elig = reinterpret_cast<int32_t*>(tau + tau_pad);
-    int32_t* fallback = elig + n_ranges;
+    RangeState* state = h->bf_thr.as<RangeState>();                                   // 8-byte aligned members first
+    float2* tau = reinterpret_cast<float2*>(state + n_ranges);
+    int32_t* fallback = reinterpret_cast<int32_t*>(tau + tau_pad);
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
-    unsigned long long* surv_total = reinterpret_cast<unsigned long long*>(ctrl + 8);
     int32_t* pre_idx = h->bf_best.as<int32_t>();
     double* pre_so = reinterpret_cast<double*>(pre_idx + (size_t)n_ranges * 4);
     double* pre_R = pre_so + (size_t)n_ranges * 2;
@@ -676,7 +807,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
-    // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range)
+    // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
     if (!probe) {
         int S = (int)floor(sqrt((double)NP / 1000.0) + 0.5);
         if (S < 1) S = 1;
@@ -684,59 +815,62 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
         h->prof_suppress = false;
         FIC_TRY(rc_pre);
-        bf_threshold_kernel<<<1, 1024, 0, st>>>(d_img, W, range_begin, n_ranges, pre_R, elig, tau, fallback, ctrl, tau_pad);
+        bf_threshold_kernel<<<1, 1024, 0, st>>>(d_img, W, PW, range_begin, n_ranges, pre_idx, pre_so, pre_R, state, tau, fallback, ctrl, tau_pad);
         FIC_CHECK_LAUNCH(h, "bf_threshold_kernel");
     } else {
         // probe: every range eligible in natural order, infinite thresholds
-        std::vector<int32_t> e(n_ranges);
-        for (int k = 0; k < n_ranges; ++k) e[k] = range_begin + k;
-        std::vector<float> t(tau_pad, __builtin_inff());
+        std::vector<RangeState> e(n_ranges);
+        for (int k = 0; k < n_ranges; ++k) { memset(&e[k], 0, sizeof(RangeState)); e[k].ridx = range_begin + k; }
+        std::vector<float2> t(tau_pad, make_float2(__builtin_inff(), __builtin_inff()));
         int c[2] = {n_ranges, 0};
-        FIC_CUDA(cudaMemcpyAsync(elig, e.data(), (size_t)n_ranges * 4, cudaMemcpyHostToDevice, st));
-        FIC_CUDA(cudaMemcpyAsync(tau, t.data(), (size_t)tau_pad * 4, cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaMemcpyAsync(state, e.data(), (size_t)n_ranges * sizeof(RangeState), cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaMemcpyAsync(tau, t.data(), (size_t)tau_pad * sizeof(float2), cudaMemcpyHostToDevice, st));
         FIC_CUDA(cudaMemcpyAsync(ctrl, c, 8, cudaMemcpyHostToDevice, st));
         FIC_CUDA(cudaStreamSynchronize(st));
     }
 
     // 3. range operand
-    bf_rangeop_kernel<<<cdiv(n_cols_pad, 4), 256, 0, st>>>(d_img, W, elig, ctrl, n_cols_pad, rngB, rngBx);
+    bf_rangeop_kernel<<<cdiv(n_cols_pad, 4), 256, 0, st>>>(d_img, W, state, ctrl, n_cols_pad, rngB, rngBx);
     FIC_CHECK_LAUNCH(h, "bf_rangeop_kernel");
 
-    // 4. the screen
+    // 4. the screen, in two rounds
     CUtensorMap mapA, mapAx, mapB, mapBx;
     FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
     FIC_TRY(make_map(&mapAx, poolAx, (uint64_t)NP, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
     FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B));
     FIC_TRY(make_map(&mapBx, rngBx, (uint64_t)n_cols_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B));
-    ScreenParams sp;
-    sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
-    const int max_groups = n_cols_pad / BN;
-    int n_chunks = cdiv((long long)h->num_sms * 4, max_groups);
-    if (n_chunks > n_tiles / 8) n_chunks = n_tiles / 8;
-    if (n_chunks < 1) n_chunks = 1;
-    if (probe) n_chunks = 1;
-    sp.n_chunks = n_chunks;
-    sp.dump = probe;
-    sp.err_flag = ctrl + 2;
     static bool attr_set = false;
     if (!attr_set) {
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         attr_set = true;
     }
-    int grid = max_groups * n_chunks;
-    if (grid > h->num_sms) grid = h->num_sms;
-    if (probe) grid = 1;
-    {
-        ProfScope prof(h, st);
-        bf_screen_kernel<<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+    ScreenParams sp;
+    sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
+    sp.dump = probe;
+    sp.err_flag = ctrl + 2;
+    const bool two_rounds = !probe && n_tiles >= 64;
+    const int rounds[2] = {two_rounds ? ROUND_EIGHTH : ROUND_ALL, ROUND_REST};
+    const int n_first = two_rounds ? cdiv(n_tiles, 8) : n_tiles;
+    for (int r = 0; r < (two_rounds ? 2 : 1); ++r) {
+        sp.round = rounds[r];
+        sp.n_round_tiles = r == 0 ? n_first : n_tiles - n_first;
+        if (r == 1) {
+            bf_retau_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(state, ctrl, tau);
+            FIC_CHECK_LAUNCH(h, "bf_retau_kernel");
+        }
+        int grid = probe ? 1 : h->num_sms;
+        {
+            ProfScope prof(h, st);
+            bf_screen_kernel<<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+        }
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
+        if (probe) return FIC_OK;
+        // 5. exact rescoring of this round's survivors, merged into the range states
+        const int emit = (r == (two_rounds ? 1 : 0));
+        bf_rescore_kernel<<<n_ranges, 256, 0, st>>>(d_img, P, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit,
+                                                    d_idx, d_so, d_R);
+        FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }
-    FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
-    if (probe) return FIC_OK;
-
-    // 5. exact rescoring of the survivors
-    bf_rescore_kernel<<<n_ranges, 256, 0, st>>>(d_img, P, sd4, sdd, H, W, range_begin, elig, ctrl, cnt, list, cap, fallback, d_idx,
-                                                d_so, d_R, surv_total);
-    FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
 
     // 6. whatever the screen could not decide goes through the exact scan
     int* hc = h->pin_a.as<int>();
@@ -744,11 +878,11 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_CUDA(cudaStreamSynchronize(st));
     h->counters[CNT_D2H] += 64;
     if (hc[2] != 0) { fic_set_error("bf_screen_kernel: pipeline wait %d timed out", hc[2]); return FIC_ECUDA; }
-    const int n_elig = hc[0], n_fb = hc[1];
+    const int n_fb = hc[1];
     unsigned long long st_total;
-    memcpy(&st_total, hc + 8, sizeof(st_total));  // surv_total sits at ctrl + 8 ints
+    memcpy(&st_total, hc + 8, sizeof(st_total));
     h->counters[CNT_SURVIVORS] += (int64_t)st_total;
-    h->counters[CNT_SCREEN_RANGES] += n_elig - (n_fb - (n_ranges - n_elig));
+    h->counters[CNT_SCREEN_RANGES] += n_ranges - n_fb;
     h->counters[CNT_RESCAN_RANGES] += n_fb;
     if (n_fb > 0) {
         if (flags & FIC_BF_NO_FALLBACK) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
