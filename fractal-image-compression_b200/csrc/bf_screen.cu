@@ -21,8 +21,9 @@
 //     u^2 * h_c^2 >= A_r - 64*UB_r,     h_c^2 = 64/den16 * (1 + 1e-3 * sum D4^2 / den16)          (tau_A)
 // For the (rare) ill-conditioned domains the constant guard is used:  u^2 * 64/den16 >= A_r - 64*(UB_r + 0.26)  (tau_B).
 // UB_r is the exact R of some candidate (any exactly scored candidate bounds the winner from above).
-// The epilogue evaluates  fma(|u|, h_c, k_c) >= tau  with k_c = DELTA*h_c absorbing the accumulator's rounding of the
-// fractional extension term: 2 instructions per output, tau chosen per (thread, range) from {tau_A, tau_B}.
+// The epilogue evaluates  (|u| + DELTA)*h_c >= tau  as  |u| >= theta := tau/h_c - DELTA  (DELTA absorbs the accumulator's
+// rounding of the fractional extension term); theta is one FFMA per (thread, range, tile), the 8 isometry columns of a
+// range are max-reduced first, so the common case is ~5 instructions per 8 outputs.
 //
 // Two rounds: round 1 screens every 8th candidate tile against bounds from a coarse exact pre-scan (~1000 positions
 // per range); its survivors are rescored exactly and give much tighter bounds for round 2 over the remaining tiles.
@@ -32,17 +33,18 @@
 // GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 4-stage ring), N = 256 columns = 32 ranges
 // x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
 // TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
-// tile t.  Warp roles: warp 0 TMA producer, warp 1 MMA issuer + TMEM allocator, warps 2..9 epilogue (two per TMEM
-// lane quadrant, 128 columns each).  Thread = candidate, so h_c/k_c are per-thread registers and the 8 isometry
+// tile t.  Warp roles: warps 0..15 epilogue, warp 16 TMA producer, warp 17 MMA issuer + TMEM allocator; epilogue in two groups of
+// eight, one group per accumulator stage (two warps per TMEM lane quadrant, 128 columns each).  Thread = candidate, so h_c/k_c are per-thread registers and the 8 isometry
 // columns of a range share one tau.  The (group, tile) space is cut into equal contiguous spans, one per CTA.
 //
 // HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
 //   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
 //   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
-//   hk      float2 [NP]    (+-h_c, k_c); a negative h marks an ill-conditioned domain
+//   hk      float2 [NP]    (+-1/h_c, 0); a negative value marks an ill-conditioned domain
 // and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
 #include <cuda.h>
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "fic_common.cuh"
 #include "scorer.cuh"
@@ -58,7 +60,11 @@ constexpr int BN = 256;      // columns per unit (32 ranges x 8 isometries)
 constexpr int KMAIN = 64;
 constexpr int KEXT = 16;
 constexpr int STAGES = 4;
-constexpr int EPI_WARPS = 8;
+constexpr int WARPS_PER_STAGE = 8;                    // epilogue warps per accumulator stage (two per TMEM lane quadrant)
+constexpr int EPI_WARPS = 2 * WARPS_PER_STAGE;
+// the scheduler favours high warp ids: the two single-thread roles sit ABOVE the epilogue warps so that the busy
+// epilogue can never delay a TMA issue or an MMA issue
+constexpr int TMA_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
 constexpr int SCREEN_THREADS = 64 + EPI_WARPS * 32;
 constexpr uint32_t A_MAIN_BYTES = BM * KMAIN * 2;   // 16384
 constexpr uint32_t A_EXT_BYTES = BM * KEXT * 2;     // 4096
@@ -69,7 +75,9 @@ constexpr uint32_t OFF_B_EXT = OFF_B_MAIN + B_MAIN_BYTES;
 constexpr uint32_t OFF_A_MAIN = OFF_B_EXT + B_EXT_BYTES;
 constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
 constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
-constexpr uint32_t SCREEN_SMEM = OFF_BARS + 256 + 1024;  // + slack to align the base to 1024
+constexpr uint32_t OFF_TAU = OFF_BARS + 256;                        // per epilogue warp: 16 x float2 thresholds
+constexpr uint32_t OFF_QUEUE = OFF_TAU + EPI_WARPS * 16 * 8;          // per epilogue warp: survivor queue (784 B)
+constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * 784 + 1024;  // + slack to align the base to 1024
 
 constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
 constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
@@ -191,6 +199,7 @@ struct ScreenParams {
     int n_round_tiles;       // tiles visited in this round
     float* dump;             // probe mode: [n_tiles*128][256] raw accumulators of column group 0 (else nullptr)
     int* err_flag;
+    int debug_mode;          // 0 = normal; 1/2 = timing experiments (FIC_SCREEN_DEBUG), results invalid
 };
 
 __device__ __forceinline__ int tile_of(int round, int j)
@@ -224,42 +233,86 @@ struct Span {
     }
 };
 
-// screen one 32-column chunk held in registers; `c4` and all indices are compile-time after unrolling
-template <int C4>
-__device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float hx, const float ky, const bool ill,
-                                             const float (&tauA)[16], const float (&tauB)[16], const ScreenParams& p, int slot0,
-                                             int my_cand)
+// Screen one 32-column chunk held in registers.  theta[g] = tau_g/h_c - DELTA is this thread's threshold on |u| for
+// the g-th range of the chunk:  (|u| + DELTA)*h_c >= tau  <=>  |u| >= theta.  The 8 isometry columns of a range are
+// reduced with max first, so the common case costs ~5 instructions per 8 outputs.
+// rare path, kept out of line so the hot loop stays small: one reservation for all passing isometries of a
+// (candidate, range) pair, then the entries
+__device__ __noinline__ void append_hits(uint32_t* __restrict__ cnt, uint32_t* __restrict__ list, uint32_t cap, int slot,
+                                         uint32_t cand, unsigned m8)
 {
-    float th[4];
-#pragma unroll
-    for (int g = 0; g < 4; ++g) th[g] = ill ? tauB[C4 * 4 + g] : tauA[C4 * 4 + g];
+    uint32_t at = atomicAdd(&cnt[slot], (uint32_t)__popc(m8));
+    while (m8) {
+        const int i = __ffs(m8) - 1;
+        m8 &= m8 - 1;
+        if (at < cap) list[(size_t)slot * cap + at] = cand * 8u + (uint32_t)i;
+        ++at;
+    }
+}
+
+// Per-warp survivor queue in shared memory: a hit costs one shared-memory atomic and one store; the global
+// reservations (one atomicAdd per entry, a full round trip to L2) are issued 32 at a time when the queue is flushed.
+constexpr int QCAP = 96;
+struct WarpQueue {
+    uint32_t count;
+    uint32_t pad;
+    uint2 e[QCAP];   // x = (slot << 8) | isometry mask, y = candidate position
+};
+
+__device__ __forceinline__ void queue_push(WarpQueue* q, const ScreenParams& p, int slot, uint32_t cand, unsigned m8)
+{
+    const uint32_t pos = atomicAdd(&q->count, 1u);
+    if (pos < QCAP) q->e[pos] = make_uint2(((uint32_t)slot << 8) | m8, cand);
+    else append_hits(p.cnt, p.list, p.cap, slot, cand, m8);   // queue full (pathological burst): go direct
+}
+
+__device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, int lane)
+{
+    __syncwarp();
+    const uint32_t n = min(q->count, (uint32_t)QCAP);
+    for (uint32_t k = lane; k < n; k += 32) {
+        const uint2 ent = q->e[k];
+        append_hits(p.cnt, p.list, p.cap, (int)(ent.x >> 8), ent.y, ent.x & 0xffu);
+    }
+    __syncwarp();
+    if (lane == 0) q->count = 0;
+    __syncwarp();
+}
+
+template <bool APPEND>
+__device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float (&theta)[4], const ScreenParams& p, int slot0,
+                                             int my_cand, WarpQueue* q)
+{
+    float m[4];
     bool any = false;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) any |= fmaf(fabsf(__uint_as_float(v[j])), hx, ky) >= th[j >> 3];
-    if (__any_sync(0xffffffffu, any)) {
-        if (any) {
+    for (int g = 0; g < 4; ++g) {
+        m[g] = fabsf(__uint_as_float(v[g * 8]));
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+        for (int i = 1; i < 8; ++i) m[g] = fmaxf(m[g], fabsf(__uint_as_float(v[g * 8 + i])));
+        any |= m[g] >= theta[g];
+    }
+    if (!APPEND) {  // timing experiment: the screening math without the survivor path
+        if (any && m[0] == 1.2345e-30f) p.cnt[0] = 1;
+        return;
+    }
+    if (any) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (m[g] >= theta[g]) {
                 unsigned m8 = 0;
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    m8 |= (fmaf(fabsf(__uint_as_float(v[g * 8 + i])), hx, ky) >= th[g] ? 1u : 0u) << i;
-                if (m8) {  // one reservation for all isometries of this (candidate, range)
-                    const int slot = slot0 + C4 * 4 + g;
-                    uint32_t at = atomicAdd(&p.cnt[slot], (uint32_t)__popc(m8));
-                    while (m8) {
-                        const int i = __ffs(m8) - 1;
-                        m8 &= m8 - 1;
-                        if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)my_cand * 8u + (uint32_t)i;
-                        ++at;
-                    }
-                }
+                for (int i = 0; i < 8; ++i) m8 |= (fabsf(__uint_as_float(v[g * 8 + i])) >= theta[g] ? 1u : 0u) << i;
+                queue_push(q, p, slot0 + g, (uint32_t)my_cand, m8);
             }
         }
     }
 }
 
 // ---- the screen ---------------------------------------------------------------------------------------------
+// MODE 0 = production; MODE 1 = probe (dump raw accumulators of group 0); MODE 2 / 3 = timing experiments selected by
+// FIC_SCREEN_DEBUG (2: TMEM loads but no screening, 3: no epilogue work at all) -- their results are wrong on purpose.
+template <int MODE>
 __global__ void __launch_bounds__(SCREEN_THREADS, 1)
 bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapAx,
                  const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapBx, ScreenParams p)
@@ -285,10 +338,10 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         mbar_init(b_full, 1);
         mbar_init(b_empty, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), EPI_WARPS); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), WARPS_PER_STAGE); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM by construction: > 113 KB of shared memory)
+    if (warp == MMA_WARP) {  // TMEM: all 512 columns (one CTA per SM by construction: > 113 KB of shared memory)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -297,7 +350,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp == TMA_WARP) {
         // ===== TMA producer =====
         if (lane == 0) {
             int s = 0;
@@ -320,7 +373,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == MMA_WARP) {
         // ===== MMA issuer =====
         if (lane == 0) {
             int s = 0, as = 0;
@@ -353,39 +406,50 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
     } else {
         // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
-        const int ew = warp - 2;
-        const int quad = warp & 3;        // TMEM lane quadrant this warp may touch
-        const int half = ew >> 2;         // which 128 of the 256 columns
-        int as = 0;
+        // Two warp groups of WARPS_PER_STAGE warps; group g owns accumulator stage g, i.e. every second tile of the CTA's
+        // span, so the two groups work on different tiles at the same time and only ever wait on their own stage.  Inside
+        // a group two warps share each TMEM lane quadrant and take 128 columns (16 ranges) each.
+        const int ew = warp;
+        const int stage = ew / WARPS_PER_STAGE;
+        const int quad = warp & 3;                           // TMEM lane quadrant this warp may touch
+        const int half = (ew % WARPS_PER_STAGE) >> 2;        // which 128 of the 256 columns
+        const int lane_off = quad * 32 + lane;
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(stage * BN + half * 128);
         uint32_t aph = 0;
+        int n = 0;  // tiles issued so far by this CTA (all units): tile n uses stage n & 1
+        float2* my_tau = reinterpret_cast<float2*>(gbase + OFF_TAU) + ew * 16;
+        WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + ew;
+        if (lane == 0) queue->count = 0;
+        __syncwarp();
         Span span(p, n_groups);
         int grp, j0, j1;
         while (span.next(grp, j0, j1)) {
-            float tauA[16], tauB[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float2 tt = p.tau[grp * 32 + half * 16 + j];
-                tauA[j] = tt.x;
-                tauB[j] = tt.y;
-            }
+            if (MODE == 0) queue_flush(queue, p, lane);   // entries carry absolute slots, but keep units separate
+            // this warp's 16 (tau_A, tau_B) pairs live in a private slice of shared memory (registers are needed for two
+            // accumulator chunks in flight); broadcast reads, no bank conflicts
+            __syncwarp();
+            if (lane < 16) my_tau[lane] = p.tau[grp * 32 + half * 16 + lane];
+            __syncwarp();
             const int slot0 = grp * 32 + half * 16;
-            const int lane_off = quad * 32 + lane;
-            int cand = tile_of(p.round, j0) * BM + lane_off;
-            float2 hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
-            for (int j = j0; j < j1; ++j) {
-                const float2 hk = hk_next;
-                const int my_cand = cand;
-                if (j + 1 < j1) {
-                    cand = tile_of(p.round, j + 1) * BM + lane_off;
-                    hk_next = cand < p.NP ? p.hk[cand] : make_float2(0.f, 0.f);
-                }
-                const bool ill = hk.x < 0.f;
-                const float hx = fabsf(hk.x), ky = hk.y;
-                mbar_wait(tfull_bar(as), aph, p.err_flag, 6);
+            int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that lands in my stage
+            n += j1 - j0;
+            for (; j < j1; j += 2) {
+                const int my_cand = tile_of(p.round, j) * BM + lane_off;
+                const float hq = my_cand < p.NP ? p.hk[my_cand].x : 0.f;   // +-1/h_c, sign = conditioning class
+                const bool ill = hq < 0.f;
+                const float qx = fabsf(hq);
+                mbar_wait(tfull_bar(stage), aph, p.err_flag, 6);
+                aph ^= 1;
                 tcgen05_fence_after();
-                const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN + half * 128);
                 uint32_t va[32], vb[32];
-                if (p.dump) {
+                auto thetas = [&](int c4, float (&theta)[4]) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const float2 t = my_tau[c4 * 4 + g];
+                        theta[g] = fmaf(ill ? t.y : t.x, qx, -DELTA_U);
+                    }
+                };
+                if (MODE == 1) {
                     for (int c4 = 0; c4 < 4; ++c4) {
                         tmem_ld32(taddr0 + c4 * 32, va);
                         tmem_ld_wait(va);
@@ -395,30 +459,37 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                                 p.dump[(size_t)my_cand * BN + half * 128 + c4 * 32 + q] = __uint_as_float(va[q]);
                         }
                     }
-                } else {
+                } else if (MODE != 3) {
+                    float theta[4];
                     tmem_ld32(taddr0, va);
                     tmem_ld32(taddr0 + 32, vb);
+                    thetas(0, theta);
                     tmem_ld_wait(va);
                     tmem_ld_wait(vb);
-                    screen_chunk<0>(va, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
-                    tmem_ld32(taddr0 + 64, va);       // in flight while chunk 1 is screened
-                    screen_chunk<1>(vb, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
-                    tmem_ld32(taddr0 + 96, vb);
+                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(va, theta, p, slot0, my_cand, queue);
+                    tmem_ld32(taddr0 + 64, va);        // in flight while chunk 1 is screened
+                    thetas(1, theta);
+                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(vb, theta, p, slot0 + 4, my_cand, queue);
+                    tmem_ld32(taddr0 + 96, vb);        // in flight while chunk 2 is screened
+                    thetas(2, theta);
                     tmem_ld_wait(va);
                     tmem_ld_wait(vb);
-                    screen_chunk<2>(va, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
-                    screen_chunk<3>(vb, hx, ky, ill, tauA, tauB, p, slot0, my_cand);
+                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(va, theta, p, slot0 + 8, my_cand, queue);
+                    thetas(3, theta);
+                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(vb, theta, p, slot0 + 12, my_cand, queue);
+                    if (MODE != 0 && MODE != 4 && (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u)) p.cnt[0] = 1;
                 }
                 tcgen05_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(tempty_bar(as));
-                if (++as == 2) { as = 0; aph ^= 1; }
+                if (lane == 0) mbar_arrive(tempty_bar(stage));
+                if (MODE == 0 && queue->count >= QCAP / 2) queue_flush(queue, p, lane);   // warp-uniform: read after __syncwarp
             }
         }
+        if (MODE == 0) queue_flush(queue, p, lane);
     }
     tcgen05_fence_before();
     __syncthreads();
-    if (warp == 1) {
+    if (warp == MMA_WARP) {
         tcgen05_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
     }
@@ -467,16 +538,16 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
     dx[0] = ox;
     dx[1] = make_uint4(0u, 0u, 0u, 0u);
     const long long den16 = 64ll * s2 - (long long)s * s;  // >= 0, exact
-    float hc = 0.f, kc = 0.f;
+    // q_c = 1/h_c, rounded DOWN a little so that theta = tau*q - DELTA never over-estimates; +inf for a constant domain
+    // (den16 == 0: u == 0 exactly, s_ref == 0, R_ref == A_r/64 without noise -> it can never beat tau_A > 0)
+    float hc = __int_as_float(0x7f800000), kc = 0.f;
     if (den16 > 0) {
         const double d = (double)den16, q = (double)s2;
         const bool well = d >= 5e-4 * q;
         const double h2 = well ? 64.0 / d * (1.0 + 1.0e-3 * q / d) : 64.0 / d;
-        hc = (float)sqrt(h2) * (1.0f + 1.0f / 1048576.0f);  // rounded up a little: never under-estimate
-        kc = DELTA_U * hc;
+        hc = (float)(1.0 / sqrt(h2)) * (1.0f - 1.0f / 1048576.0f);
         if (!well) hc = -hc;                                   // sign flags the ill-conditioned class
     }
-    // den16 == 0: constant domain, u == 0 exactly, s_ref == 0, R_ref == A_r/64 with no noise: (0,0) with tau_A is exact
     hk[p] = make_float2(hc, kc);
 }
 
@@ -841,13 +912,21 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_TRY(make_map(&mapBx, rngBx, (uint64_t)n_cols_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B));
     static bool attr_set = false;
     if (!attr_set) {
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         attr_set = true;
     }
     ScreenParams sp;
     sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
     sp.dump = probe;
     sp.err_flag = ctrl + 2;
+    {
+        const char* dbg = getenv("FIC_SCREEN_DEBUG");  // kernel timing experiments only; records are wrong when set
+        sp.debug_mode = dbg ? atoi(dbg) : 0;
+    }
     const bool two_rounds = !probe && n_tiles >= 64;
     const int rounds[2] = {two_rounds ? ROUND_EIGHTH : ROUND_ALL, ROUND_REST};
     const int n_first = two_rounds ? cdiv(n_tiles, 8) : n_tiles;
@@ -861,7 +940,11 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         int grid = probe ? 1 : h->num_sms;
         {
             ProfScope prof(h, st);
-            bf_screen_kernel<<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            if (probe) bf_screen_kernel<1><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            else if (sp.debug_mode == 1) bf_screen_kernel<2><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            else if (sp.debug_mode == 2) bf_screen_kernel<3><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            else if (sp.debug_mode == 3) bf_screen_kernel<4><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            else bf_screen_kernel<0><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
         }
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
         if (probe) return FIC_OK;
