@@ -684,31 +684,27 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
     if (k < 16) rngBx[(size_t)col * 16 + k] = (k == 0 && slot < n_elig) ? __int2half_rn(rho) : __float2half_rn(0.f);
 }
 
-// ---- exact rescoring of the survivors: one CTA per eligible range, merges into the range state -------------------
-__global__ void __launch_bounds__(256)
-bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
+// ---- exact rescoring of the survivors: one warp per eligible range, merges into the range state -------------------
+// The survivor's pooled block is read back from the TMA pool (one 128-byte row, D4 = D4' + m_c), the dot product is
+// an exact integer sum in fp32, the score is the float64 restatement of jit_bfencoder.py:64-95 (scorer.cuh).
+#define RESCORE_WARPS 8
+__global__ void __launch_bounds__(RESCORE_WARPS * 32)
+bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
                   int32_t* __restrict__ fallback, int emit, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
                   double* __restrict__ out_R)
 {
-    const int slot = blockIdx.x;
+    __shared__ float rv[RESCORE_WARPS][8][65];   // inverse-transformed range per isometry, padded against bank conflicts
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * RESCORE_WARPS + warp;
     if (slot >= ctrl[0]) return;
-    __shared__ float r_s[64];
-    __shared__ double sh_rs, sh_sq;
-    __shared__ BestRec red[8];
-    __shared__ double red_s[8], red_o[8];
-    __shared__ RangeState st;
-    const int tid = threadIdx.x;
-    if (tid == 0) st = state[slot];
-    __syncthreads();
-    const int ridx = st.ridx;
-    const uint32_t n = cnt[slot];
-    const int rw = W / 8, PW = W - 16, BW = W - 1;
-    const int NP = PW * (H - 16);
+    const RangeState st = state[slot];
     if (st.flags & 1) return;  // already handed to the exact scan
+    const uint32_t n = cnt[slot];
+    const int ridx = st.ridx;
     if (n > cap) {             // survivor list overflowed: let the exact scan decide this range
-        if (tid == 0) {
+        if (lane == 0) {
             int at = atomicAdd(&ctrl[1], 1);
             fallback[at] = ridx;
             state[slot].flags = 1;
@@ -716,39 +712,54 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ 
         }
         return;
     }
+    const int rw = W / 8, PW = W - 16;
+    const int NP = PW * (H - 16);
     const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
-    if (tid < 64) r_s[tid] = (float)img[(size_t)(ri + (tid >> 3)) * W + rj + (tid & 7)];
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long s = 0, q = 0;
-        for (int k = 0; k < 64; ++k) { unsigned v = (unsigned)r_s[k]; s += v; q += v * v; }
-        sh_rs = (double)s;
-        sh_sq = (double)q;
-        if (n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
+    // lane holds range pixels k = lane and k = lane + 32
+    const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
+    const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
+    unsigned s = r0 + r1, q = r0 * r0 + r1 * r1;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
+    const double rs = (double)s, sqr = (double)q;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        int sa, sb;
+        fic_iso_bf(t >> 2, t & 3, 8, lane >> 3, lane & 7, sa, sb);
+        rv[warp][t][sa * 8 + sb] = (float)r0;
+        fic_iso_bf(t >> 2, t & 3, 8, 4 + (lane >> 3), lane & 7, sa, sb);
+        rv[warp][t][sa * 8 + sb] = (float)r1;
     }
-    __syncthreads();
-    const double rs = sh_rs, sqr = sh_sq;
+    __syncwarp();
+    if (lane == 0 && n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
     double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
     unsigned long long bseq = ~0ull;
-    if (tid == 0) { bR = st.R; bseq = st.seq; bs = st.s; bo = st.o; }  // the running winner competes too
-    for (uint32_t e = tid; e < n; e += 256) {
+    if (lane == 0) { bR = st.R; bseq = st.seq; bs = st.s; bo = st.o; }  // the running winner competes too
+    for (uint32_t e = lane; e < n; e += 32) {
         const uint32_t ent = list[(size_t)slot * cap + e];
         const int t = ent & 7;
         const int p = ent >> 3;
-        const int di = p / PW, dj = p - di * PW;
+        const uint32_t sd = sd4[p];
+        const float mc = (float)((sd + 32u) >> 6);          // the pool stores D4 - m_c
+        const uint4* row = reinterpret_cast<const uint4*>(poolA + (size_t)p * 64);
+        const float* rvt = rv[warp][t];
         float x = 0.f;
-        for (int i = 0; i < 8; ++i)
-            for (int j = 0; j < 8; ++j) {
-                int sa, sb;
-                fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
-                x = fmaf(r_s[i * 8 + j], (float)P[(size_t)(di + 2 * sa) * BW + dj + 2 * sb], x);  // exact integers < 2^24
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const uint4 u = row[c];
+            const __half2* h2 = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = __half22float2(h2[k]);
+                x = fmaf(rvt[c * 8 + 2 * k], f.x + mc, x);        // exact: integers, every partial sum < 2^24
+                x = fmaf(rvt[c * 8 + 2 * k + 1], f.y + mc, x);
             }
-        const float dsf = __fmul_rn((float)sd4[p], 0.25f);
+        }
+        const float dsf = __fmul_rn((float)sd, 0.25f);
         BfScore sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
                                      (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
         if (fic_better(sc.R, (unsigned long long)ent, bR, bseq)) { bR = sc.R; bseq = ent; bs = sc.s; bo = sc.o; }
     }
-    const int lane = tid & 31, warp = tid >> 5;
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
         double oR = __shfl_xor_sync(0xffffffffu, bR, off);
@@ -756,31 +767,25 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ 
         double os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
         if (fic_better(oR, oS, bR, bseq)) { bR = oR; bseq = oS; bs = os; bo = oo; }
     }
-    if (lane == 0) { red[warp].R = bR; red[warp].seq = bseq; red_s[warp] = bs; red_o[warp] = bo; }
-    __syncthreads();
-    if (tid == 0) {
-        BestRec b = red[0];
-        double s = red_s[0], o = red_o[0];
-        for (int w = 1; w < 8; ++w)
-            if (fic_better(red[w].R, red[w].seq, b.R, b.seq)) { b = red[w]; s = red_s[w]; o = red_o[w]; }
+    if (lane == 0) {
         cnt[slot] = 0;  // the next round starts from an empty list
-        if (b.seq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
+        if (bseq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
             int at = atomicAdd(&ctrl[1], 1);
             fallback[at] = ridx;
             state[slot].flags = 1;
             return;
         }
-        state[slot].R = b.R; state[slot].seq = b.seq; state[slot].s = s; state[slot].o = o;
+        state[slot].R = bR; state[slot].seq = bseq; state[slot].s = bs; state[slot].o = bo;
         if (emit) {
             const size_t os_ = (size_t)(ridx - range_begin);
-            const int t = (int)(b.seq & 7ull), p = (int)(b.seq >> 3);
+            const int t = (int)(bseq & 7ull), p = (int)(bseq >> 3);
             out_idx[4 * os_ + 0] = p / PW;
             out_idx[4 * os_ + 1] = p % PW;
             out_idx[4 * os_ + 2] = t >> 2;
             out_idx[4 * os_ + 3] = t & 3;
-            out_so[2 * os_] = s;
-            out_so[2 * os_ + 1] = o;
-            out_R[os_] = b.R;
+            out_so[2 * os_] = bs;
+            out_so[2 * os_ + 1] = bo;
+            out_R[os_] = bR;
         }
     }
 }
@@ -880,7 +885,9 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
 
     // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
     if (!probe) {
-        int S = (int)floor(sqrt((double)NP / 1000.0) + 0.5);
+        double want_positions = 1000.0;
+        if (const char* e = getenv("FIC_PRESCAN_POSITIONS")) want_positions = atof(e) > 1.0 ? atof(e) : want_positions;  // tuning knob
+        int S = (int)floor(sqrt((double)NP / want_positions) + 0.5);
         if (S < 1) S = 1;
         h->prof_suppress = true;  // fic_profile times the screen kernel on this path, not the helper scans
         int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
@@ -950,7 +957,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         if (probe) return FIC_OK;
         // 5. exact rescoring of this round's survivors, merged into the range states
         const int emit = (r == (two_rounds ? 1 : 0));
-        bf_rescore_kernel<<<n_ranges, 256, 0, st>>>(d_img, P, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }

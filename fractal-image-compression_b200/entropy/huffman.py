@@ -1,0 +1,138 @@
+"""Huffman coder of one coding dimension (reference: entropy/huffman.py:20-122).
+
+Byte compatibility with the reference's files hinges on the tree SHAPE, which depends on how ties between equal
+frequencies are broken: the reference pushes `Counter(symbols).items()` (first-occurrence order) through the standard
+library `heapq` with nodes that compare by frequency only.  The same data structure with the same comparison is
+used here, so the sift order -- and with it every code word -- is identical.
+"""
+from __future__ import annotations
+
+import heapq
+from collections import Counter, deque
+from typing import Optional
+
+from bitbuffer import BitBuffer
+from entropy.abccodec import Code, CodeWidth, EntropyEncoder
+
+LEFT_BIT = 0
+RIGHT_BIT = 1
+INTERNAL_NODE_BIT = 0
+LEAF_BIT = 1
+UNAVAILABLE = -1
+TABLE_VAL_BITS_ENCODING_SIZE_BITS = 8
+
+CodingTable = dict[int, tuple[Code, CodeWidth]]
+
+
+class HuffmanNode:
+    """Tree node ordered by `freq` alone (the reference's dataclass(order=True) with compare=False on the rest)."""
+
+    __slots__ = ("freq", "val", "left", "right")
+
+    def __init__(self, freq: int, val: Optional[int], left: Optional["HuffmanNode"], right: Optional["HuffmanNode"]):
+        self.freq = freq
+        self.val = val
+        self.left = left
+        self.right = right
+
+    def __lt__(self, other: "HuffmanNode") -> bool:
+        return self.freq < other.freq
+
+    def __le__(self, other: "HuffmanNode") -> bool:
+        return self.freq <= other.freq
+
+    def __eq__(self, other) -> bool:
+        return isinstance(other, HuffmanNode) and self.freq == other.freq
+
+    __hash__ = None
+
+    @staticmethod
+    def Leaf(val: int, freq: int) -> "HuffmanNode":
+        return HuffmanNode(freq, val, None, None)
+
+    @staticmethod
+    def Inner(left: "HuffmanNode", right: "HuffmanNode") -> "HuffmanNode":
+        return HuffmanNode(left.freq + right.freq, None, left, right)
+
+    def is_leaf(self) -> bool:
+        return self.left is None
+
+
+class HuffmanEncoder(EntropyEncoder):
+    def __init__(self) -> None:
+        self.root: Optional[HuffmanNode] = None
+        self.coding_table: Optional[CodingTable] = None
+
+    def prepare_for_encoding(self, symbols: list[int]) -> CodingTable:
+        heap = [HuffmanNode.Leaf(sym, freq) for sym, freq in Counter(symbols).items()]
+        heapq.heapify(heap)
+        while len(heap) > 1:
+            first = heapq.heappop(heap)       # becomes the left child: code bit 0
+            second = heapq.heappop(heap)
+            heapq.heappush(heap, HuffmanNode.Inner(first, second))
+        self.root = heap[0]
+        self.coding_table = self._build_coding_table(self.root)
+        return self.coding_table
+
+    def encode(self, symbol: int) -> tuple[Code, CodeWidth]:
+        return self.coding_table[symbol]
+
+    def _build_coding_table(self, root: HuffmanNode) -> CodingTable:
+        table: CodingTable = {}
+        stack = [(root, 0, 0)]
+        while stack:                          # a single-symbol alphabet gets the empty code (0, 0)
+            node, code, depth = stack.pop()
+            if node.is_leaf():
+                table[node.val] = (code, depth)
+            else:
+                stack.append((node.right, (code << 1) | RIGHT_BIT, depth + 1))
+                stack.append((node.left, (code << 1) | LEFT_BIT, depth + 1))
+        return table
+
+
+class HuffmanDecoder:
+    def __init__(self, root: HuffmanNode) -> None:
+        self.root = root
+
+    def decode(self, read_buff: BitBuffer) -> int:
+        node = self.root
+        while not node.is_leaf():
+            node = node.left if read_buff.read(1) == LEFT_BIT else node.right
+        return node.val
+
+
+class HuffmanSerializer:
+    """Breadth-first dump: `0` for an inner node, `1` + value in `val_bits` bits for a leaf (huffman.py:83-98)."""
+
+    def serialize(self, root: HuffmanNode, val_bits: int, write_buff: BitBuffer):
+        pending = deque([root])
+        while pending:
+            node = pending.popleft()
+            if node.is_leaf():
+                write_buff.write(LEAF_BIT, 1)
+                write_buff.write(node.val, val_bits)
+            else:
+                write_buff.write(INTERNAL_NODE_BIT, 1)
+                pending.append(node.left)
+                pending.append(node.right)
+
+
+class HuffmanDeserializer:
+    def deserialize(self, read_buff: BitBuffer, val_bits: int) -> HuffmanNode:
+        def read_node() -> HuffmanNode:
+            if read_buff.read(1) == LEAF_BIT:
+                return HuffmanNode.Leaf(read_buff.read(val_bits), UNAVAILABLE)
+            return HuffmanNode(UNAVAILABLE, None, None, None)
+
+        root = read_node()
+        if root.is_leaf() and root.val is not None:
+            return root
+        waiting = deque([root])              # inner nodes whose children are still to come, in stream order
+        while waiting:
+            parent = waiting.popleft()
+            parent.left = read_node()
+            parent.right = read_node()
+            for child in (parent.left, parent.right):
+                if child.val is None:
+                    waiting.append(child)
+        return root

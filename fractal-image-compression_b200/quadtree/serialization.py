@@ -1,0 +1,136 @@
+"""`.fqt` writer and reader (reference: quadtree/serialization.py:26-223), byte-compatible with the reference's
+files: the two bundled fixtures round-trip identically (tests/test_serialization.py).
+
+Node stream, breadth-first per root: leaf = `1`, row, col, orientation (1 bit), rotation (2 bits), quantised scale,
+quantised offset; internal node = `0` followed (later in the stream) by its four children.
+"""
+from __future__ import annotations
+
+from collections import deque
+from typing import BinaryIO
+
+from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_preamble
+from bitbuffer import EOF, BitBuffer
+from entropy.processor import CodingDimension, EntropyProcessor
+from quadtree.common import (Domain, QuadtreeImage, QuadtreeNode, get_dimension_bit_widths,
+                             get_domain_dimension_extractors, iter_root_squares)
+
+QUADTREE_MAGIC = "quadtree".encode(encoding='ascii')
+INTERNAL_NODE_BIT = 0
+LEAF_BIT = 1
+STRUCT_BYTE_ORDER = BYTE_ORDER
+HEADER_SIZE = len(QUADTREE_MAGIC) + 14
+UNSUPPORTED = 0.
+
+
+def _leaves_breadth_first(forest):
+    """Leaf domains in the order the reference collects them for the Huffman statistics: ONE queue over all roots
+    (serialization.py:62-78), which differs from the per-root order of the node stream."""
+    pending = deque(forest)
+    while pending:
+        node = pending.popleft()
+        if node.is_leaf():
+            yield node.domain
+        else:
+            pending.extend(node.children)
+
+
+class QuadtreeSerializer:
+    def __init__(self, entropy_processor: EntropyProcessor, entropy_coding_dimensions: set[CodingDimension],
+                 required_entropy_coding_gain=1) -> None:
+        self.entropy_processor = entropy_processor
+        self.entropy_coding_dimensions = entropy_coding_dimensions
+        self.required_entropy_coding_gain = required_entropy_coding_gain
+        self.file: BinaryIO = None
+
+    def serialize(self, quadtree_img: QuadtreeImage, output: str | BinaryIO):
+        self.img = quadtree_img
+        self._choose_coded_dimensions()
+        with open_target(output, 'wb') as f:
+            self.file = f
+            start = f.tell()
+            bits = BitBuffer(f, BYTE_ORDER)
+            write_preamble(f, bits, QUADTREE_MAGIC, quadtree_img.info, self.entropy_processor, self.entropy_coding_dimensions)
+            self._write_nodes(bits)
+            patch_size(f, start, QUADTREE_MAGIC)
+
+    def _choose_coded_dimensions(self):
+        values: dict[CodingDimension, list[int]] = {}
+        if self.entropy_coding_dimensions:
+            extract = get_domain_dimension_extractors()
+            wanted = [dim for dim in CodingDimension if dim in self.entropy_coding_dimensions]
+            values = {dim: [] for dim in wanted}
+            for dom in _leaves_breadth_first(self.img.forest):
+                for dim in wanted:
+                    values[dim].append(extract[dim.value](dom))
+        gains = self.entropy_processor.prepare_for_encoding(values, get_dimension_bit_widths(self.img.info))
+        # the reference overwrites the requested set with the profitable one (serialization.py:60)
+        self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}
+
+    def _write_nodes(self, bits: BitBuffer):
+        enc = self.entropy_processor.encode
+        for root in self.img.forest:
+            pending = deque([root])
+            while pending:
+                node = pending.popleft()
+                if node.is_leaf():
+                    d = node.domain
+                    bits.write(LEAF_BIT, 1)
+                    bits.write(*enc(d.start_i, CodingDimension.DOMAIN_ROW))
+                    bits.write(*enc(d.start_j, CodingDimension.DOMAIN_COL))
+                    bits.write(d.orientation, 1)
+                    bits.write(d.rotation, 2)
+                    bits.write(*enc(d.quantized_scale, CodingDimension.SCALE))
+                    bits.write(*enc(d.quantized_offset, CodingDimension.OFFSET))
+                else:
+                    bits.write(INTERNAL_NODE_BIT, 1)
+                    pending.extend(node.children)
+        if not bits.is_empty():
+            bits.flush()
+
+
+class QuadtreeDeserializer:
+    def __init__(self) -> None:
+        self.file: BinaryIO = None
+        self.img: QuadtreeImage = None
+        self.entropy_processor: EntropyProcessor = None
+        self.size = 0
+
+    def deserialize(self, input: str | BinaryIO) -> QuadtreeImage:
+        with open_target(input, 'rb') as f:
+            self.file = f
+            bits = BitBuffer(f, BYTE_ORDER)
+            info, self.size, self.entropy_processor = read_preamble(f, bits, QUADTREE_MAGIC, 'quadtree')
+            self.img = QuadtreeImage(info, self._read_forest(bits, info))
+            return self.img
+
+    def _read_forest(self, bits: BitBuffer, info) -> list[QuadtreeNode]:
+        dec = self.entropy_processor.decode
+        forest = []
+        # the image geometry fixes the number of roots (encoder.py:111-125); each root is a breadth-first stream
+        for _ in iter_root_squares(info.img_width, info.img_height):
+            root = None
+            waiting = deque()          # (parent, child index) slots still to be filled, in stream order
+            while root is None or waiting:
+                kind = bits.read(1)
+                assert kind != EOF, "Invalid size encoding, buffer returned EOF"
+                if kind == LEAF_BIT:
+                    start_i = dec(bits, CodingDimension.DOMAIN_ROW)
+                    start_j = dec(bits, CodingDimension.DOMAIN_COL)
+                    orientation = bits.read(1)
+                    rotation = bits.read(2)
+                    qs = dec(bits, CodingDimension.SCALE)
+                    qo = dec(bits, CodingDimension.OFFSET)
+                    node = QuadtreeNode.Leaf(Domain(start_i, start_j, orientation, rotation, scale=UNSUPPORTED,
+                                                    offset=UNSUPPORTED, quantized_scale=qs, quantized_offset=qo))
+                else:
+                    node = QuadtreeNode.ParentOf(None, None, None, None)
+                if root is None:
+                    root = node
+                else:
+                    parent, k = waiting.popleft()
+                    parent.children[k] = node
+                if not node.is_leaf():
+                    waiting.extend((node, k) for k in range(4))
+            forest.append(root)
+        return forest

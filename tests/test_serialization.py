@@ -1,0 +1,174 @@
+"""CPU: the bit buffer / Huffman / `.fqt` + HV file formats stay byte-compatible with the reference.
+
+Known answers: the two bundled `.fqt` files (tests/golden, copies of the reference's imgs/compressed), the reference's
+own self-check vectors for BitBuffer (bitbuffer.py:70-105) and Huffman (huffman.py:124-157) as observed by the survey.
+"""
+import io
+import struct
+
+import numpy as np
+import pytest
+
+from test_oracle_golden import hv_params, qt_params
+
+
+def qt_image_from_golden(g, name, shape):
+    from quadtree.common import EncodingInfo, QuadtreeImage, stream_to_forest
+    p = qt_params(g, name)
+    nodes = np.c_[g[f"{name}_nodes"], np.zeros(len(g[f"{name}_nodes"]), np.int32)]
+    vals = np.c_[g[f"{name}_vals"], np.zeros(len(g[f"{name}_vals"]))]
+    forest = stream_to_forest(nodes, vals, int(g[f"{name}_nroots"]))
+    return QuadtreeImage(EncodingInfo(p[0], p[1], p[2], shape[1], shape[0]), forest)
+
+
+def test_bitbuffer_known_answers():
+    from bitbuffer import BitBuffer
+    out = io.BytesIO()
+    bb = BitBuffer(out)
+    emitted = [bb.write(346, 16), bb.write(200, 8), bb.write(3434, 16), bb.write(1, 24), bb.write(1, 32),
+               bb.write(0x4FF, 11), bb.write(0xFFFFF, 21), bb.write(0xFFFFFFFF, 32)]
+    words = [e.hex() for e in emitted if e is not None]
+    assert words == ["015ac80d", "6a000001", "00000001", "9fefffff", "ffffffff"]
+    src = io.BytesIO(struct.pack('!III', 0b0110101011, 0b0111 << 28, 12))
+    bb = BitBuffer(src)
+    got = [bb.read(22), bb.read(1), bb.read(1), bb.read(1), bb.read(1)]
+    bb.read(5)
+    got.append(bb.read(3))
+    assert got == [0, 0, 1, 1, 0, 5]
+    assert BitBuffer(io.BytesIO(b"\x00\x01")).read(3) == -1                         # EOF on a short tail
+    out = io.BytesIO(); bb = BitBuffer(out); bb.write(5, 3); assert not bb.is_empty(); bb.flush()
+    assert out.getvalue() == bytes([0b10100000, 0, 0, 0]) and bb.is_empty()
+
+
+def test_huffman_round_trip_and_tree_serialisation():
+    from bitbuffer import BitBuffer
+    from entropy.huffman import HuffmanDecoder, HuffmanDeserializer, HuffmanEncoder, HuffmanSerializer
+    symbols = [5, 5, 5, 5, 5, 1, 2, 3, 1, 1, 2, 2, 3]
+    enc = HuffmanEncoder()
+    table = enc.prepare_for_encoding(symbols)
+    # known answer produced by the reference's HuffmanEncoder on its own self-check input (huffman.py:125)
+    assert table == {3: (0, 2), 2: (1, 2), 1: (2, 2), 5: (3, 2)}
+    buf = io.BytesIO()
+    bb = BitBuffer(buf)
+    for s in symbols:
+        bb.write(*enc.encode(s))
+    bb.flush()
+    buf.seek(0)
+    dec = HuffmanDecoder(enc.root)
+    rb = BitBuffer(buf)
+    assert [dec.decode(rb) for _ in symbols] == symbols
+    buf = io.BytesIO()
+    bb = BitBuffer(buf)
+    HuffmanSerializer().serialize(enc.root, 8, bb)
+    bb.flush()
+    buf.seek(0)
+    root = HuffmanDeserializer().deserialize(BitBuffer(buf), 8)
+    assert HuffmanEncoder()._build_coding_table(root) == table
+    single = HuffmanEncoder()
+    assert single.prepare_for_encoding([7, 7, 7]) == {7: (0, 0)}                    # one symbol: empty code
+
+
+@pytest.mark.parametrize("name,fqt", [("cauliflower256", "kalafior256.fqt"), ("lena313x413", "lena313x413.fqt")])
+def test_fqt_files_are_reproduced_byte_for_byte(golden, images, name, fqt):
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from quadtree.serialization import QuadtreeDeserializer, QuadtreeSerializer
+    want = open(golden.path(fqt), "rb").read()
+    q = qt_image_from_golden(golden["qt_golden"], name, images[name].shape)
+    out = io.BytesIO()
+    QuadtreeSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(q, out)
+    assert out.getvalue() == want
+    back = QuadtreeDeserializer().deserialize(io.BytesIO(want))
+    assert (back.info.img_width, back.info.img_height, back.info.scale_bits, back.info.offset_bits) == \
+        (q.info.img_width, q.info.img_height, 7, 5)
+    again = io.BytesIO()
+    QuadtreeSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(back, again)
+    assert again.getvalue() == want
+    plain = io.BytesIO()
+    QuadtreeSerializer(HuffmanEntropyProcessor(), set()).serialize(q, plain)
+    if name == "cauliflower256":
+        assert len(plain.getvalue()) == 16566
+
+
+def test_legacy_fqt_header_is_rejected_like_the_reference():
+    from quadtree.serialization import QuadtreeDeserializer
+    legacy = struct.pack("!8sfBBHHI", b"quadtree", 1.0, 7, 5, 380, 322, 0) + b"\x00" * 8   # entropy id 0
+    with pytest.raises(ValueError):
+        QuadtreeDeserializer().deserialize(io.BytesIO(legacy))
+    with pytest.raises(Exception, match="magic"):
+        QuadtreeDeserializer().deserialize(io.BytesIO(b"notquadt" + b"\x00" * 30))
+    with pytest.raises(Exception, match="too short"):
+        QuadtreeDeserializer().deserialize(io.BytesIO(b"abc"))
+
+
+@pytest.mark.parametrize("name", ["lena64", "cauliflower240x92"])
+def test_hv_stream_round_trip(golden, name):
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from hvv2.common import HVImage, stream_to_tree
+    from hvv2.serialization import HVDeserializer, HVSerializer
+    from quadtree.common import EncodingInfo
+    g = golden["hv_golden"]
+    p = hv_params(g, name)
+    img = g[f"{name}_img"]
+    nodes = np.c_[g[f"{name}_nodes"], np.zeros(len(g[f"{name}_nodes"]), np.int32)]
+    vals = np.c_[g[f"{name}_vals"], np.zeros(len(g[f"{name}_vals"]))]
+    hv = HVImage(EncodingInfo(p[4], p[5], 1.0, img.shape[1], img.shape[0]), stream_to_tree(nodes, vals))
+    out = io.BytesIO()
+    HVSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(hv, out)
+    data = out.getvalue()
+    assert data[:2] == b"hv" and struct.unpack("!I", data[12:16])[0] == len(data) and len(data) % 4 == 0
+    back = HVDeserializer().deserialize(io.BytesIO(data))
+
+    def flat(root):
+        rows, stack = [], [root]
+        while stack:
+            n = stack.pop()
+            if n.is_leaf():
+                d = n.domain
+                rows.append((1, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset))
+            else:
+                rows.append((0, int(n.split_info.vertical_split), n.split_info.split_idx, 0, 0, 0, 0))
+                stack += [n.c2, n.c1]
+        return rows
+    assert flat(back.root) == flat(hv.root)
+    again = io.BytesIO()
+    HVSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(back, again)
+    assert again.getvalue() == data
+
+
+def test_rgb_stream_is_three_fqt_streams(golden, images):
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from quadtree.common import ColoredQuadtreeImage
+    from quadtree.rgb import RGBQuadtreeDeserializer, RGBQuadtreeSerializer
+    from quadtree.serialization import QuadtreeDeserializer, QuadtreeSerializer
+    g = golden["qt_golden"]
+    q1 = qt_image_from_golden(g, "cauliflower64", images["cauliflower64"].shape)
+    q2 = qt_image_from_golden(g, "cauliflower64step4", images["cauliflower64"].shape)
+    out = io.BytesIO()
+    # planes of equal size (4:4:4): like the reference, one serialiser object keeps its field widths and coders from
+    # the first plane (entropy/processor.py:88-98), so differently sized planes need separate serialisers
+    RGBQuadtreeSerializer(QuadtreeSerializer(HuffmanEntropyProcessor(), set())).serialize(ColoredQuadtreeImage(q1, q2, q1), out)
+    data = out.getvalue()
+    back = RGBQuadtreeDeserializer(QuadtreeDeserializer()).deserialize(io.BytesIO(data))
+    one = io.BytesIO()
+    QuadtreeSerializer(HuffmanEntropyProcessor(), set()).serialize(q1, one)
+    assert data.startswith(one.getvalue()) and data.endswith(one.getvalue())
+    for plane, src in ((back.encoded_Y, q1), (back.encoded_Cb, q2), (back.encoded_Cr, q1)):
+        again = io.BytesIO()
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set()).serialize(plane, again)
+        ref = io.BytesIO()
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set()).serialize(src, ref)
+        assert again.getvalue() == ref.getvalue()
+
+
+def test_colour_conversion_round_trip_shapes():
+    import utils
+    rng = np.random.default_rng(0)
+    for shape in ((8, 12, 3), (7, 9, 3), (4, 7, 3)):
+        rgb = rng.integers(0, 256, shape, dtype=np.uint8)
+        y, cb, cr = utils.rgb_to_ycbcr(rgb, "4:4:4")
+        assert y.shape == cb.shape == cr.shape == shape[:2]
+        back = utils.ycbcr_to_rgb((y, cb, cr), "4:4:4")
+        assert np.abs(back.astype(int) - rgb.astype(int)).max() <= 6
+    rgb = rng.integers(0, 256, (8, 12, 3), dtype=np.uint8)
+    y, cb, cr = utils.rgb_to_ycbcr(rgb, "4:2:0")
+    assert cb.shape == (4, 6) and utils.ycbcr_to_rgb((y, cb, cr), "4:2:0").shape == (8, 12, 3)
