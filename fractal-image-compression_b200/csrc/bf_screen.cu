@@ -687,7 +687,81 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
 // ---- exact rescoring of the survivors: one warp per eligible range, merges into the range state -------------------
 // The survivor's pooled block is read back from the TMA pool (one 128-byte row, D4 = D4' + m_c), the dot product is
 // an exact integer sum in fp32, the score is the float64 restatement of jit_bfencoder.py:64-95 (scorer.cuh).
+// Ranges with a short list (the common case) are handled by their own warp; the few with a long list are then
+// worked through by the whole CTA one after the other, so a single crowded range cannot become a 256-iteration tail.
 #define RESCORE_WARPS 8
+#define RESCORE_WARP_LIMIT 256u
+
+struct RescoreBest {
+    double R, s, o;
+    unsigned long long seq;
+};
+
+__device__ __forceinline__ void rescore_entry(uint32_t ent, const float (*rvw)[65], double rs, double sqr,
+                                              const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
+                                              const float* __restrict__ sdd, int NP, RescoreBest& b)
+{
+    const int t = ent & 7;
+    const int p = ent >> 3;
+    const uint32_t sd = sd4[p];
+    const float mc = (float)((sd + 32u) >> 6);          // the pool stores D4 - m_c
+    const uint4* row = reinterpret_cast<const uint4*>(poolA + (size_t)p * 64);
+    const float* rvt = rvw[t];
+    float x = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const uint4 u = row[c];
+        const __half2* h2 = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 f = __half22float2(h2[k]);
+            x = fmaf(rvt[c * 8 + 2 * k], f.x + mc, x);        // exact: integers, every partial sum < 2^24
+            x = fmaf(rvt[c * 8 + 2 * k + 1], f.y + mc, x);
+        }
+    }
+    const float dsf = __fmul_rn((float)sd, 0.25f);
+    BfScore sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
+                                 (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
+    if (fic_better(sc.R, (unsigned long long)ent, b.R, b.seq)) { b.R = sc.R; b.seq = ent; b.s = sc.s; b.o = sc.o; }
+}
+
+__device__ __forceinline__ void rescore_warp_reduce(RescoreBest& b)
+{
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        double oR = __shfl_xor_sync(0xffffffffu, b.R, off);
+        unsigned long long oS = __shfl_xor_sync(0xffffffffu, b.seq, off);
+        double os = __shfl_xor_sync(0xffffffffu, b.s, off), oo = __shfl_xor_sync(0xffffffffu, b.o, off);
+        if (fic_better(oR, oS, b.R, b.seq)) { b.R = oR; b.seq = oS; b.s = os; b.o = oo; }
+    }
+}
+
+// one thread: store the winner of `slot` (and emit the record in the last round)
+__device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeState* __restrict__ state, int* __restrict__ ctrl,
+                               uint32_t* __restrict__ cnt, int32_t* __restrict__ fallback, int emit, int range_begin, int PW,
+                               int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+{
+    cnt[slot] = 0;  // the next round starts from an empty list
+    if (b.seq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
+        int at = atomicAdd(&ctrl[1], 1);
+        fallback[at] = ridx;
+        state[slot].flags = 1;
+        return;
+    }
+    state[slot].R = b.R; state[slot].seq = b.seq; state[slot].s = b.s; state[slot].o = b.o;
+    if (emit) {
+        const size_t os_ = (size_t)(ridx - range_begin);
+        const int t = (int)(b.seq & 7ull), p = (int)(b.seq >> 3);
+        out_idx[4 * os_ + 0] = p / PW;
+        out_idx[4 * os_ + 1] = p % PW;
+        out_idx[4 * os_ + 2] = t >> 2;
+        out_idx[4 * os_ + 3] = t & 3;
+        out_so[2 * os_] = b.s;
+        out_so[2 * os_ + 1] = b.o;
+        out_R[os_] = b.R;
+    }
+}
+
 __global__ void __launch_bounds__(RESCORE_WARPS * 32)
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
@@ -696,97 +770,85 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
                   double* __restrict__ out_R)
 {
     __shared__ float rv[RESCORE_WARPS][8][65];   // inverse-transformed range per isometry, padded against bank conflicts
+    __shared__ double s_rs[RESCORE_WARPS], s_sq[RESCORE_WARPS];
+    __shared__ uint32_t s_big[RESCORE_WARPS];    // list length of a range left to the whole CTA (0 = nothing to do)
+    __shared__ RescoreBest s_red[RESCORE_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * RESCORE_WARPS + warp;
-    if (slot >= ctrl[0]) return;
-    const RangeState st = state[slot];
-    if (st.flags & 1) return;  // already handed to the exact scan
-    const uint32_t n = cnt[slot];
-    const int ridx = st.ridx;
-    if (n > cap) {             // survivor list overflowed: let the exact scan decide this range
-        if (lane == 0) {
-            int at = atomicAdd(&ctrl[1], 1);
-            fallback[at] = ridx;
-            state[slot].flags = 1;
-            cnt[slot] = 0;
-        }
-        return;
-    }
+    const int n_elig = ctrl[0];
     const int rw = W / 8, PW = W - 16;
     const int NP = PW * (H - 16);
-    const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
-    // lane holds range pixels k = lane and k = lane + 32
-    const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
-    const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
-    unsigned s = r0 + r1, q = r0 * r0 + r1 * r1;
+    if (lane == 0) s_big[warp] = 0;
+    // ---- phase A: every warp prepares its range and finishes it when the list is short -----------------------------
+    if (slot < n_elig) {
+        const RangeState st = state[slot];
+        const uint32_t n = cnt[slot];
+        const int ridx = st.ridx;
+        if (st.flags & 1) {
+            // already handed to the exact scan
+        } else if (n > cap) {  // survivor list overflowed: let the exact scan decide this range
+            if (lane == 0) {
+                int at = atomicAdd(&ctrl[1], 1);
+                fallback[at] = ridx;
+                state[slot].flags = 1;
+                cnt[slot] = 0;
+            }
+        } else {
+            const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+            // lane holds range pixels k = lane and k = lane + 32
+            const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
+            const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
+            unsigned s = r0 + r1, q = r0 * r0 + r1 * r1;
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
-    const double rs = (double)s, sqr = (double)q;
+            for (int off = 16; off > 0; off >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
+            const double rs = (double)s, sqr = (double)q;
 #pragma unroll
-    for (int t = 0; t < 8; ++t) {
-        int sa, sb;
-        fic_iso_bf(t >> 2, t & 3, 8, lane >> 3, lane & 7, sa, sb);
-        rv[warp][t][sa * 8 + sb] = (float)r0;
-        fic_iso_bf(t >> 2, t & 3, 8, 4 + (lane >> 3), lane & 7, sa, sb);
-        rv[warp][t][sa * 8 + sb] = (float)r1;
-    }
-    __syncwarp();
-    if (lane == 0 && n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
-    double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
-    unsigned long long bseq = ~0ull;
-    if (lane == 0) { bR = st.R; bseq = st.seq; bs = st.s; bo = st.o; }  // the running winner competes too
-    for (uint32_t e = lane; e < n; e += 32) {
-        const uint32_t ent = list[(size_t)slot * cap + e];
-        const int t = ent & 7;
-        const int p = ent >> 3;
-        const uint32_t sd = sd4[p];
-        const float mc = (float)((sd + 32u) >> 6);          // the pool stores D4 - m_c
-        const uint4* row = reinterpret_cast<const uint4*>(poolA + (size_t)p * 64);
-        const float* rvt = rv[warp][t];
-        float x = 0.f;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const uint4 u = row[c];
-            const __half2* h2 = reinterpret_cast<const __half2*>(&u);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float2 f = __half22float2(h2[k]);
-                x = fmaf(rvt[c * 8 + 2 * k], f.x + mc, x);        // exact: integers, every partial sum < 2^24
-                x = fmaf(rvt[c * 8 + 2 * k + 1], f.y + mc, x);
+            for (int t = 0; t < 8; ++t) {
+                int sa, sb;
+                fic_iso_bf(t >> 2, t & 3, 8, lane >> 3, lane & 7, sa, sb);
+                rv[warp][t][sa * 8 + sb] = (float)r0;
+                fic_iso_bf(t >> 2, t & 3, 8, 4 + (lane >> 3), lane & 7, sa, sb);
+                rv[warp][t][sa * 8 + sb] = (float)r1;
+            }
+            __syncwarp();
+            if (lane == 0 && n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
+            if (n <= RESCORE_WARP_LIMIT) {
+                RescoreBest b;
+                b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
+                if (lane == 0) { b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }  // the running winner competes too
+                for (uint32_t e = lane; e < n; e += 32)
+                    rescore_entry(list[(size_t)slot * cap + e], rv[warp], rs, sqr, poolA, sd4, sdd, NP, b);
+                rescore_warp_reduce(b);
+                if (lane == 0) rescore_commit(slot, ridx, b, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
+            } else if (lane == 0) {
+                s_rs[warp] = rs;
+                s_sq[warp] = sqr;
+                s_big[warp] = n;
             }
         }
-        const float dsf = __fmul_rn((float)sd, 0.25f);
-        BfScore sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
-                                     (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
-        if (fic_better(sc.R, (unsigned long long)ent, bR, bseq)) { bR = sc.R; bseq = ent; bs = sc.s; bo = sc.o; }
     }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        double oR = __shfl_xor_sync(0xffffffffu, bR, off);
-        unsigned long long oS = __shfl_xor_sync(0xffffffffu, bseq, off);
-        double os = __shfl_xor_sync(0xffffffffu, bs, off), oo = __shfl_xor_sync(0xffffffffu, bo, off);
-        if (fic_better(oR, oS, bR, bseq)) { bR = oR; bseq = oS; bs = os; bo = oo; }
-    }
-    if (lane == 0) {
-        cnt[slot] = 0;  // the next round starts from an empty list
-        if (bseq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
-            int at = atomicAdd(&ctrl[1], 1);
-            fallback[at] = ridx;
-            state[slot].flags = 1;
-            return;
+    __syncthreads();
+    // ---- phase B: long lists, all warps on one range at a time --------------------------------------------------------
+    for (int r = 0; r < RESCORE_WARPS; ++r) {
+        const uint32_t n = s_big[r];
+        if (n == 0) continue;   // uniform across the CTA
+        const int bslot = blockIdx.x * RESCORE_WARPS + r;
+        const double rs = s_rs[r], sqr = s_sq[r];
+        RescoreBest b;
+        b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
+        if (threadIdx.x == 0) { const RangeState st = state[bslot]; b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }
+        for (uint32_t e = threadIdx.x; e < n; e += RESCORE_WARPS * 32)
+            rescore_entry(list[(size_t)bslot * cap + e], rv[r], rs, sqr, poolA, sd4, sdd, NP, b);
+        rescore_warp_reduce(b);
+        if (lane == 0) s_red[warp] = b;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            RescoreBest w = s_red[0];
+            for (int k = 1; k < RESCORE_WARPS; ++k)
+                if (fic_better(s_red[k].R, s_red[k].seq, w.R, w.seq)) w = s_red[k];
+            rescore_commit(bslot, state[bslot].ridx, w, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
         }
-        state[slot].R = bR; state[slot].seq = bseq; state[slot].s = bs; state[slot].o = bo;
-        if (emit) {
-            const size_t os_ = (size_t)(ridx - range_begin);
-            const int t = (int)(bseq & 7ull), p = (int)(bseq >> 3);
-            out_idx[4 * os_ + 0] = p / PW;
-            out_idx[4 * os_ + 1] = p % PW;
-            out_idx[4 * os_ + 2] = t >> 2;
-            out_idx[4 * os_ + 3] = t & 3;
-            out_so[2 * os_] = bs;
-            out_so[2 * os_ + 1] = bo;
-            out_R[os_] = bR;
-        }
+        __syncthreads();
     }
 }
 
@@ -885,7 +947,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
 
     // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
     if (!probe) {
-        double want_positions = 1000.0;
+        double want_positions = 250.0;   // measured on B200: a sparser pre-scan costs less than the extra survivors it causes
         if (const char* e = getenv("FIC_PRESCAN_POSITIONS")) want_positions = atof(e) > 1.0 ? atof(e) : want_positions;  // tuning knob
         int S = (int)floor(sqrt((double)NP / want_positions) + 0.5);
         if (S < 1) S = 1;
