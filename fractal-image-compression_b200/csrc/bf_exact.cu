@@ -67,9 +67,13 @@ __global__ void bf_stats_kernel(const uint16_t* __restrict__ P, int H, int W, ui
         }
     sd4[p] = s;
     sq4[p] = s2;
+    // fully unrolled: the isometry index maps become compile-time constants and sq[] stays in registers
+#pragma unroll
     for (int t = 0; t < 8; ++t) {
         float acc = 0.f;
+#pragma unroll
         for (int i = 0; i < 8; ++i)
+#pragma unroll
             for (int j = 0; j < 8; ++j) {
                 int sa, sb;
                 fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);

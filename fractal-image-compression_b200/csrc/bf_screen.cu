@@ -417,7 +417,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(stage * BN + half * 128);
         uint32_t aph = 0;
         int n = 0;  // tiles issued so far by this CTA (all units): tile n uses stage n & 1
-        float2* my_tau = reinterpret_cast<float2*>(gbase + OFF_TAU) + ew * 16;
+        float* my_tau = reinterpret_cast<float*>(gbase + OFF_TAU) + ew * 32;   // [0,16) = tau_A, [16,32) = tau_B
         WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + ew;
         if (lane == 0) queue->count = 0;
         __syncwarp();
@@ -428,7 +428,11 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             // this warp's 16 (tau_A, tau_B) pairs live in a private slice of shared memory (registers are needed for two
             // accumulator chunks in flight); broadcast reads, no bank conflicts
             __syncwarp();
-            if (lane < 16) my_tau[lane] = p.tau[grp * 32 + half * 16 + lane];
+            if (lane < 16) {
+                const float2 tt = p.tau[grp * 32 + half * 16 + lane];
+                my_tau[lane] = tt.x;
+                my_tau[16 + lane] = tt.y;
+            }
             __syncwarp();
             const int slot0 = grp * 32 + half * 16;
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that lands in my stage
@@ -442,12 +446,13 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 aph ^= 1;
                 tcgen05_fence_after();
                 uint32_t va[32], vb[32];
+                const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (ill ? 16 : 0));   // class picks the array
                 auto thetas = [&](int c4, float (&theta)[4]) {
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        const float2 t = my_tau[c4 * 4 + g];
-                        theta[g] = fmaf(ill ? t.y : t.x, qx, -DELTA_U);
-                    }
+                    const float4 t = tau4[c4];                                                   // one broadcast LDS.128
+                    theta[0] = fmaf(t.x, qx, -DELTA_U);
+                    theta[1] = fmaf(t.y, qx, -DELTA_U);
+                    theta[2] = fmaf(t.z, qx, -DELTA_U);
+                    theta[3] = fmaf(t.w, qx, -DELTA_U);
                 };
                 if (MODE == 1) {
                     for (int c4 = 0; c4 < 4; ++c4) {
@@ -559,11 +564,27 @@ struct RangeState {
     unsigned long long seq;        // position*8 + isometry of the running winner
     int ridx;                      // absolute range index
     int flags;                     // 1 = sent to the exact scan, 2 = constant range (decided)
+    int rsum, pad_;                // sum of the range's 64 pixels
 };
+
+// sum and sum of squares of every range of the slice, one warp per range (the serial consumers below only read them)
+__global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, uint2* __restrict__ sums)
+{
+    const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (slot >= n_ranges) return;
+    const int rw = W / 8, ridx = range_begin + slot;
+    const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
+    const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
+    const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
+    unsigned sm = r0 + r1, q = r0 * r0 + r1 * r1;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) { sm += __shfl_xor_sync(0xffffffffu, sm, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
+    if (lane == 0) sums[slot] = make_uint2(sm, q);
+}
 
 // ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
 __global__ void __launch_bounds__(1024)
-bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int PW, int range_begin, int n_ranges,
+bf_threshold_kernel(const uint2* __restrict__ sums, int PW, int range_begin, int n_ranges,
                     const int32_t* __restrict__ pre_idx, const double* __restrict__ pre_so, const double* __restrict__ pre_R,
                     RangeState* __restrict__ state, float2* __restrict__ tau, int32_t* __restrict__ fallback,
                     int* __restrict__ ctrl, int tau_pad)
@@ -571,7 +592,6 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int PW, int range_be
     __shared__ int warp_e[32], warp_f[32];
     __shared__ int base_e, base_f;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int rw = W / 8;
     if (tid == 0) { base_e = 0; base_f = 0; }
     __syncthreads();
     for (int b0 = 0; b0 < n_ranges; b0 += 1024) {
@@ -581,18 +601,13 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int PW, int range_be
         RangeState rs_;
         if (slot < n_ranges) {
             const int ridx = range_begin + slot;
-            const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
-            long long s = 0, q = 0;
-            for (int k = 0; k < 64; ++k) {
-                long long x = img[(size_t)(ri + (k >> 3)) * W + rj + (k & 7)];
-                s += x;
-                q += x * x;
-            }
+            const uint2 sq_ = sums[slot];
+            const long long s = sq_.x, q = sq_.y;
             const long long A64 = 64 * q - s * s;                             // 64 * A_r, exact
             const double ub = pre_R[slot];
             rs_.R = ub; rs_.s = pre_so[2 * slot]; rs_.o = pre_so[2 * slot + 1];
             rs_.seq = ((unsigned long long)pre_idx[4 * slot] * PW + pre_idx[4 * slot + 1]) * 8ull + pre_idx[4 * slot + 2] * 4 + pre_idx[4 * slot + 3];
-            rs_.ridx = ridx; rs_.flags = 0;
+            rs_.ridx = ridx; rs_.flags = 0; rs_.rsum = (int)s; rs_.pad_ = 0;
             rs_.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
             const double TA = rs_.TA0 - 64.0 * ub, TB = TA - 64.0 * GUARD_ILL;
             if (A64 == 0) {
@@ -632,6 +647,21 @@ bf_threshold_kernel(const uint8_t* __restrict__ img, int W, int PW, int range_be
     if (tid == 0) { ctrl[0] = base_e; ctrl[1] = base_f; }
 }
 
+// probe mode: every range eligible in natural order, nothing ever passes
+__global__ void bf_probe_state_kernel(const uint2* __restrict__ sums, int range_begin, int n_ranges, RangeState* __restrict__ state,
+                                      float2* __restrict__ tau, int* __restrict__ ctrl, int tau_pad)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k == 0) { ctrl[0] = n_ranges; ctrl[1] = 0; }
+    if (k < tau_pad) tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+    if (k < n_ranges) {
+        RangeState st;
+        st.R = 0.0; st.s = 0.0; st.o = 0.0; st.TA0 = 0.0; st.seq = 0; st.ridx = range_begin + k; st.flags = 0;
+        st.rsum = (int)sums[k].x; st.pad_ = 0;
+        state[k] = st;
+    }
+}
+
 // thresholds for round 2 from the improved winners
 __global__ void bf_retau_kernel(const RangeState* __restrict__ state, const int* __restrict__ ctrl, float2* __restrict__ tau)
 {
@@ -664,8 +694,7 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
         const int rw = W / 8;
         const int ridx = state[slot].ridx;
         const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
-        int s = 0;
-        for (int e = 0; e < 64; ++e) s += img[(size_t)(ri + (e >> 3)) * W + rj + (e & 7)];
+        const int s = state[slot].rsum;
         const int m = (s + 32) >> 6;
         rho = s - 64 * m;
         // entry k = (sa,sb) of column t holds r'[i][j] with (sa,sb) = iso_t(i,j): invert fic_iso_bf
@@ -916,7 +945,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_TRY(h->bf_poolx.reserve((size_t)NP * 16 * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 80 * 2 + 256));
-    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (sizeof(int32_t) + sizeof(RangeState)) + 512));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (sizeof(int32_t) + sizeof(uint2) + sizeof(RangeState)) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_ctrl.reserve(256));
@@ -930,7 +959,8 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     __half* rngBx = rngB + (size_t)n_cols_pad * 64;
     RangeState* state = h->bf_thr.as<RangeState>();                                   // 8-byte aligned members first
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
-    int32_t* fallback = reinterpret_cast<int32_t*>(tau + tau_pad);
+    uint2* rsums = reinterpret_cast<uint2*>(tau + tau_pad);
+    int32_t* fallback = reinterpret_cast<int32_t*>(rsums + n_ranges);
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
@@ -945,6 +975,9 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
+    bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums);
+    FIC_CHECK_LAUNCH(h, "bf_rangesum_kernel");
+
     // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
     if (!probe) {
         double want_positions = 250.0;   // measured on B200: a sparser pre-scan costs less than the extra survivors it causes
@@ -955,18 +988,12 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
         h->prof_suppress = false;
         FIC_TRY(rc_pre);
-        bf_threshold_kernel<<<1, 1024, 0, st>>>(d_img, W, PW, range_begin, n_ranges, pre_idx, pre_so, pre_R, state, tau, fallback, ctrl, tau_pad);
+        bf_threshold_kernel<<<1, 1024, 0, st>>>(rsums, PW, range_begin, n_ranges, pre_idx, pre_so, pre_R, state, tau, fallback, ctrl, tau_pad);
         FIC_CHECK_LAUNCH(h, "bf_threshold_kernel");
     } else {
         // probe: every range eligible in natural order, infinite thresholds
-        std::vector<RangeState> e(n_ranges);
-        for (int k = 0; k < n_ranges; ++k) { memset(&e[k], 0, sizeof(RangeState)); e[k].ridx = range_begin + k; }
-        std::vector<float2> t(tau_pad, make_float2(__builtin_inff(), __builtin_inff()));
-        int c[2] = {n_ranges, 0};
-        FIC_CUDA(cudaMemcpyAsync(state, e.data(), (size_t)n_ranges * sizeof(RangeState), cudaMemcpyHostToDevice, st));
-        FIC_CUDA(cudaMemcpyAsync(tau, t.data(), (size_t)tau_pad * sizeof(float2), cudaMemcpyHostToDevice, st));
-        FIC_CUDA(cudaMemcpyAsync(ctrl, c, 8, cudaMemcpyHostToDevice, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        bf_probe_state_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, ctrl, tau_pad);
+        FIC_CHECK_LAUNCH(h, "bf_probe_state_kernel");
     }
 
     // 3. range operand
