@@ -25,8 +25,9 @@
 // rounding of the fractional extension term); theta is one FFMA per (thread, range, tile), the 8 isometry columns of a
 // range are max-reduced first, so the common case is ~5 instructions per 8 outputs.
 //
-// Two rounds: round 1 screens every 8th candidate tile against bounds from a coarse exact pre-scan (~1000 positions
-// per range); its survivors are rescored exactly and give much tighter bounds for round 2 over the remaining tiles.
+// Rounds: a coarse exact pre-scan (~250 positions per range) gives the first bounds; round 1 screens a sparse subset of
+// the candidate tiles (every 8th for 512x512, every 512th for 4096x4096), its survivors are rescored exactly and give much
+// tighter bounds for the next, ~128x larger, round, and so on until every tile has been screened once.
 // Ranges the screen cannot decide (bound not below the range's own variance, survivor list overflow) go to the
 // exact scan; constant ranges are decided directly (every candidate ties at R = 0, the first one wins).
 //
@@ -81,7 +82,6 @@ constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * 784 + 1024;  // + slack
 
 constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
 constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
-constexpr int ROUND_ALL = 0, ROUND_EIGHTH = 1, ROUND_REST = 2;
 
 // ---- PTX wrappers ----------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -195,40 +195,55 @@ struct ScreenParams {
     uint32_t cap;
     int NP;
     int n_tiles;             // candidate tiles in the whole pool
-    int round;               // ROUND_ALL / ROUND_EIGHTH / ROUND_REST
+    int m_cur;               // this round visits the tiles t with t % m_cur == 0 ...
+    int r_prev;              // ... that were not visited before: (t / m_cur) % r_prev != 0   (0 = first round: all of them)
     int n_round_tiles;       // tiles visited in this round
+    int window_tiles;        // round tiles per L2-sized window: all CTAs sweep one window before the next
     float* dump;             // probe mode: [n_tiles*128][256] raw accumulators of column group 0 (else nullptr)
     int* err_flag;
-    int debug_mode;          // 0 = normal; 1/2 = timing experiments (FIC_SCREEN_DEBUG), results invalid
+    int debug_mode;          // 0 = normal; 1/2/3 = timing experiments (FIC_SCREEN_DEBUG), results invalid
 };
 
-__device__ __forceinline__ int tile_of(int round, int j)
+// j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
+// the previous one): round k takes the multiples of m_k that are not multiples of m_{k-1}.
+__device__ __forceinline__ int tile_of(const ScreenParams& p, int j)
 {
-    if (round == ROUND_EIGHTH) return j * 8;
-    if (round == ROUND_REST) return j + j / 7 + 1;  // skips the multiples of 8
-    return j;
+    if (p.r_prev == 0) return j * p.m_cur;
+    const int r1 = p.r_prev - 1;
+    const int q = j / r1;
+    return (q * p.r_prev + (j - q * r1) + 1) * p.m_cur;
 }
 
-// Contiguous span of the linearised (group, round tile) space owned by this CTA.
+// Work split.  The round's tiles are cut into windows (a window's slice of the pool fits L2); inside a window the
+// linearised (group, tile) space is cut into equal contiguous spans, one per CTA, so the load is balanced to one tile
+// and all CTAs read the same part of the pool at about the same time.
 struct Span {
     long long lin, end;
-    int n_round_tiles;
-    __device__ Span(const ScreenParams& p, int n_groups)
+    int w0, wn;            // current window: first round tile, number of round tiles
+    int n_round_tiles, window_tiles, n_groups;
+    __device__ Span(const ScreenParams& p, int n_groups_)
     {
-        const long long total = (long long)n_groups * p.n_round_tiles;
-        const long long per = (total + gridDim.x - 1) / gridDim.x;
-        lin = per * blockIdx.x;
-        end = lin + per < total ? lin + per : total;
-        n_round_tiles = p.n_round_tiles;
+        n_round_tiles = p.n_round_tiles; window_tiles = p.window_tiles; n_groups = n_groups_;
+        w0 = -window_tiles; wn = 0; lin = 0; end = 0;
     }
     __device__ bool next(int& grp, int& j0, int& j1)
     {
-        if (lin >= end) return false;
-        grp = (int)(lin / n_round_tiles);
-        j0 = (int)(lin - (long long)grp * n_round_tiles);
+        while (lin >= end) {   // open the next window
+            w0 += window_tiles;
+            if (w0 >= n_round_tiles || n_groups == 0) return false;
+            wn = min(window_tiles, n_round_tiles - w0);
+            const long long total = (long long)n_groups * wn;
+            const long long per = (total + gridDim.x - 1) / gridDim.x;
+            lin = per * blockIdx.x;
+            end = lin + per < total ? lin + per : total;
+        }
+        grp = (int)(lin / wn);
+        const int o = (int)(lin - (long long)grp * wn);
         const long long room = end - lin;
-        j1 = (long long)n_round_tiles - j0 < room ? n_round_tiles : j0 + (int)room;
-        lin += j1 - j0;
+        const int o1 = (long long)wn - o < room ? wn : o + (int)room;
+        j0 = w0 + o;
+        j1 = w0 + o1;
+        lin += o1 - o;
         return true;
     }
 };
@@ -364,7 +379,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 tma_load_2d(base + OFF_B_EXT, &mapBx, b_full, 0, grp * BN);
                 bph ^= 1;
                 for (int j = j0; j < j1; ++j) {
-                    const int t = tile_of(p.round, j);
+                    const int t = tile_of(p, j);
                     mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
                     mbar_expect_tx(full_bar(s), A_MAIN_BYTES + A_EXT_BYTES);
                     tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t * BM);
@@ -438,7 +453,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that lands in my stage
             n += j1 - j0;
             for (; j < j1; j += 2) {
-                const int my_cand = tile_of(p.round, j) * BM + lane_off;
+                const int my_cand = tile_of(p, j) * BM + lane_off;
                 const float hq = my_cand < p.NP ? p.hk[my_cand].x : 0.f;   // +-1/h_c, sign = conditioning class
                 const bool ill = hq < 0.f;
                 const float qx = fabsf(hq);
@@ -978,12 +993,14 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums);
     FIC_CHECK_LAUNCH(h, "bf_rangesum_kernel");
 
+    double prescan_fraction = 0.0;
     // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
     if (!probe) {
         double want_positions = 250.0;   // measured on B200: a sparser pre-scan costs less than the extra survivors it causes
         if (const char* e = getenv("FIC_PRESCAN_POSITIONS")) want_positions = atof(e) > 1.0 ? atof(e) : want_positions;  // tuning knob
         int S = (int)floor(sqrt((double)NP / want_positions) + 0.5);
         if (S < 1) S = 1;
+        prescan_fraction = (double)cdiv(PH, S) * cdiv(PW, S) / (double)NP;
         h->prof_suppress = true;  // fic_profile times the screen kernel on this path, not the helper scans
         int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
         h->prof_suppress = false;
@@ -1023,13 +1040,28 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         const char* dbg = getenv("FIC_SCREEN_DEBUG");  // kernel timing experiments only; records are wrong when set
         sp.debug_mode = dbg ? atoi(dbg) : 0;
     }
-    const bool two_rounds = !probe && n_tiles >= 64;
-    const int rounds[2] = {two_rounds ? ROUND_EIGHTH : ROUND_ALL, ROUND_REST};
-    const int n_first = two_rounds ? cdiv(n_tiles, 8) : n_tiles;
-    for (int r = 0; r < (two_rounds ? 2 : 1); ++r) {
-        sp.round = rounds[r];
-        sp.n_round_tiles = r == 0 ? n_first : n_tiles - n_first;
-        if (r == 1) {
+    // Round plan: nested strides m_1 > m_2 > ... > 1 over the candidate tiles.  A round's survivor count per range is
+    // about (fraction screened now) / (fraction scored exactly before), so each round may look at ~128x more candidates
+    // than everything before it; the first one is sized against the pre-scan sample.
+    std::vector<int> strides;
+    if (probe || n_tiles < 64) {
+        strides.push_back(1);
+    } else {
+        double f_prev = prescan_fraction > 0.0 ? prescan_fraction : 1e-3;
+        int m = 1;
+        while (1.0 / m > 128.0 * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
+        for (;;) {
+            strides.push_back(m);
+            if (m == 1) break;
+            m = m / 128 > 1 ? m / 128 : 1;
+        }
+    }
+    sp.window_tiles = (64 << 20) / (BM * (KMAIN + KEXT) * 2);   // 64 MiB of pool per window: stays in the 126 MB L2
+    for (size_t r = 0; r < strides.size(); ++r) {
+        sp.m_cur = strides[r];
+        sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
+        sp.n_round_tiles = cdiv(n_tiles, strides[r]) - (r == 0 ? 0 : cdiv(n_tiles, strides[r - 1]));
+        if (r > 0) {
             bf_retau_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(state, ctrl, tau);
             FIC_CHECK_LAUNCH(h, "bf_retau_kernel");
         }
@@ -1045,7 +1077,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
         if (probe) return FIC_OK;
         // 5. exact rescoring of this round's survivors, merged into the range states
-        const int emit = (r == (two_rounds ? 1 : 0));
+        const int emit = r + 1 == strides.size();
         bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");

@@ -115,3 +115,22 @@ def test_pipeline_counts_on_lena512(fic, images):
     assert c["screen_ranges"] + c["rescan_ranges"] == 4096
     assert c["screen_ranges"] >= 3500, c          # natural image: nearly every range is decided by the screen
     print("lena512 screen counters:", c)
+
+
+def test_three_round_plan_on_a_large_image(fic):
+    """1024 x 1536: 1.5 M candidate positions -> the round plan has an extra sparse round and several L2 windows.
+    The full pipeline over all ranges is compared with the exhaustive exact scan on two range slices."""
+    img = synthetic_image(41, 1024, 1536)
+    img[200:264, 300:420] = 17                 # a constant patch: constant ranges are decided directly
+    h = fic.default_handle()
+    h.reset_counters()
+    idx, so, R = fic.bf_encode(img, mode=fic.BF_MODE_JIT)
+    c = h.counters()
+    n = (1024 // 8) * (1536 // 8)
+    assert c["screen_ranges"] + c["rescan_ranges"] == n
+    for b, e in ((0, 192), (5000, 5256), (n - 64, n)):
+        want = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY, range_begin=b, range_end=e)
+        assert np.array_equal(idx[b:e], want[0]) and np.array_equal(so[b:e], want[1]) and np.array_equal(R[b:e], want[2])
+    # the same slice through the pipeline on its own (range-slice sharding of a big image)
+    part = fic.bf_encode(img, mode=fic.BF_MODE_JIT, range_begin=5000, range_end=5256)
+    assert np.array_equal(part[0], idx[5000:5256]) and np.array_equal(part[1], so[5000:5256])
