@@ -310,8 +310,8 @@ def qt_encode(img, scale_bits, offset_bits, max_scale, full_class_search, only_p
         H, W = a.shape
         p = _ptr(a)
     cap = 2 * H * W + 64
-    nodes = np.zeros((cap, 8), np.int32)
-    vals = np.zeros((cap, 3), np.float64)
+    nodes = np.empty((cap, 8), np.int32)     # written by the library up to the returned count
+    vals = np.empty((cap, 3), np.float64)
     nroots = C.c_int32(0)
     n = _check(lib().fic_qt_encode(h.ptr, p, H, W, int(scale_bits), int(offset_bits), float(max_scale),
                                    int(bool(full_class_search)), int(bool(only_positive_scale)), int(min_range_side),
@@ -333,8 +333,8 @@ def hv_encode(img, min_range_height, min_range_width, max_range_height, max_rang
         H, W = a.shape
         p = _ptr(a)
     cap = 2 * H * W + 64
-    nodes = np.zeros((cap, 8), np.int32)
-    vals = np.zeros((cap, 3), np.float64)
+    nodes = np.empty((cap, 8), np.int32)
+    vals = np.empty((cap, 3), np.float64)
     n = _check(lib().fic_hv_encode(h.ptr, p, H, W, int(min_range_height), int(min_range_width), int(max_range_height),
                                    int(max_range_width), int(scale_bits), int(offset_bits), float(err_threshold),
                                    float(max_scale), _ptr(nodes), _ptr(vals), cap, flags, None), "fic_hv_encode")

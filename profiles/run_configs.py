@@ -1,0 +1,93 @@
+#!/usr/bin/env python
+"""Times the five BASELINE.json configs on one B200 and checks each against the exact path / the CPU oracle.
+Run on the GPU box:  python profiles/run_configs.py > gpurun_out/configs.jsonl
+(Not a bench.py replacement: bench.py holds the headline contract; this records the other configs for the notes.)"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "fractal-image-compression_b200"), ROOT, os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+
+import fic_b200  # noqa: E402
+from conftest import synthetic_image  # noqa: E402
+from oracle import oracle as orc  # noqa: E402
+
+imgs = np.load(os.path.join(ROOT, "tests/golden/images.npz"))
+h = fic_b200.default_handle(0)
+
+
+def timed(fn, reps=3):
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t = time.perf_counter(); out = fn(); best = min(best, time.perf_counter() - t)
+    return best, out
+
+
+def psnr(a, b):
+    return float(10 * np.log10(255.0 ** 2 / np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)))
+
+
+def emit(**kw):
+    print(json.dumps(kw), flush=True)
+
+
+# config 1: 256x256 brute force encode + decode
+img = imgs["lena256"]
+t_enc, (idx, so, R) = timed(lambda: fic_b200.bf_encode(img, mode=1))
+t_dec, dec = timed(lambda: fic_b200.bf_decode(idx, so, 256, 256, 32))
+emit(config=1, what="bruteforce-jit 256x256 encode+decode (host buffers)", encode_ms=t_enc * 1e3, decode_ms=t_dec * 1e3,
+     psnr_db=psnr(dec, img), matches_per_s=1024 * 240 * 240 * 8 / t_enc, reference_cpu_s="415.5 (1 core, BASELINE.md)")
+
+# config 2: quadtree 512x512
+from quadtree.decoder import QuadtreeDecoder  # noqa: E402
+from quadtree.encoder import QuadtreeEncoder  # noqa: E402
+img = imgs["lena512"]
+qp = (7, 5, 1.0, False, False, 4, 8, 2.0)
+t_gpu, q = timed(lambda: QuadtreeEncoder(*qp).encode(img))
+t_raw, _ = timed(lambda: fic_b200.qt_encode(img, *qp))
+t_cpu, ref = timed(lambda: orc.qt_encode(img, *qp), reps=1)
+t_qdec, qdec = timed(lambda: QuadtreeDecoder().decode(q))
+emit(config=2, what="quadtree 512x512 (7,5,1.0,False,False,4,8,2.0)", encode_ms_class_api=t_gpu * 1e3, encode_ms_c_abi=t_raw * 1e3,
+     oracle_cpu_ms=t_cpu * 1e3, decode_ms=t_qdec * 1e3, psnr_db=psnr(qdec, img), nodes=int(len(ref[0])),
+     reference_cpu_s="3.74 (BASELINE.md)")
+
+# config 3: HV 512x512
+from hvv2.decoder import HVDecoder  # noqa: E402
+from hvv2.encoder import HVEncoder  # noqa: E402
+hp = (4, 4, 16, 16, 5, 7, 25.0)
+t_gpu, hv = timed(lambda: HVEncoder(*hp).encode(img), reps=2)
+t_hdec, hdec = timed(lambda: HVDecoder().decode(hv))
+g = np.load(os.path.join(ROOT, "tests/golden/hv_golden.npz"))
+leaves = int((g["lena512_nodes"][:, 0] == 1).sum()) if "lena512_nodes" in g.files else None
+emit(config=3, what="HV 512x512 (4,4,16,16,5,7,25.0)", encode_ms=t_gpu * 1e3, decode_ms=t_hdec * 1e3, psnr_db=psnr(hdec, img),
+     leaves_reference=leaves, reference_cpu_s="1688 (BASELINE.md), 1578 when the golden file was made")
+
+# config 4: synthetic 4096x4096 brute force on one GPU (+ a 1/8 range slice as one rank of eight would run it)
+big = synthetic_image(0, 4096, 4096)
+n = 512 * 512
+h.reset_counters()
+t0 = time.perf_counter(); idx, so, R = fic_b200.bf_encode(big, mode=1); t_full = time.perf_counter() - t0
+c = h.counters()
+t0 = time.perf_counter(); part = fic_b200.bf_encode(big, mode=1, range_begin=3 * n // 8, range_end=4 * n // 8); t_slice = time.perf_counter() - t0
+ok = np.array_equal(part[0], idx[3 * n // 8:4 * n // 8]) and np.array_equal(part[1], so[3 * n // 8:4 * n // 8])
+sel = [0, 777, 131071, 200000, n - 1]
+exact_ok = True
+for k in sel:
+    w = fic_b200.bf_encode(big, mode=1, flags=fic_b200.BF_EXACT_ONLY, range_begin=k, range_end=k + 1)
+    exact_ok &= bool(np.array_equal(w[0][0], idx[k]) and w[1][0, 0] == so[k, 0] and w[1][0, 1] == so[k, 1] and w[2][0] == R[k])
+matches = n * 4080 * 4080 * 8
+emit(config=4, what="bruteforce-jit synthetic 4096x4096, all 262144 ranges on ONE GPU", seconds=t_full, matches_per_s=matches / t_full,
+     slice_1_of_8_seconds=t_slice, slice_equals_full=bool(ok), five_ranges_equal_exact_scan=exact_ok, counters=c)
+
+# config 5: one 1024x1024 RGB image, per channel brute force (batch of 256 = 256x this, image-parallel)
+rgb = np.stack([synthetic_image(100 + k, 1024, 1024) for k in range(3)])
+t_img, out = timed(lambda: fic_b200.bf_encode_batch(rgb, mode=1), reps=2)
+t_dec3, _ = timed(lambda: [fic_b200.bf_decode(out[0][k], out[1][k], 1024, 1024, 32) for k in range(3)], reps=1)
+emit(config=5, what="one synthetic 1024x1024x3 image, 3 planes brute force", encode_s=t_img, decode_s=t_dec3,
+     matches_per_s=3 * 16384 * 1008 * 1008 * 8 / t_img, batch_of_256_on_8_gpus_estimate_s=256 * (t_img + t_dec3) / 8)
