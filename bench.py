@@ -243,8 +243,15 @@ def run_ours(args):
             per_launch_s = kern_ms * 1e-3 / kern_launches
             matches_per_launch = MATCHES_PER_IMAGE * args.steps / kern_launches
             achieved = matches_per_launch * FLOP_PER_MATCH / per_launch_s / 1e12
+            screen_path = not (args.exact_only or not cnt["screen_ranges"])
+            traffic = None
+            ncu_json = os.path.join(ROOT, "profiles", "r1_screen_ncu.json")
+            if screen_path and os.path.exists(ncu_json):   # dram bytes per launch from the committed ncu --set full capture
+                traffic = json.load(open(ncu_json)).get("traffic_bytes_per_launch_avg")
             roof = {"bound": "tensor", "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
-                    "frac": achieved / pk["tflops"], "traffic": None,
+                    "frac": achieved / pk["tflops"], "traffic": traffic,
+                    "algorithmic": "2*64 flop per candidate match (SURVEY 8(d)); the kernel issues K=80 MMAs, i.e. 1.25x that",
+                    "launches_per_step": kern_launches / args.steps,
                     "kernel": "bf_scan8_kernel (exact CUDA-core scan)" if args.exact_only or not cnt["screen_ranges"]
                     else "bf_screen_kernel (tcgen05 correlation GEMM + screen epilogue)",
                     "kernel_ms_per_launch": per_launch_s * 1e3, "kernel_share_of_step": kern_ms / total_ms,
