@@ -95,9 +95,18 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_cores() -> int:
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which would hide them)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_sample(img, n_ranges_sample, threads=0):
     """Oracle (CPU restatement of jit_bfencoder.py) on a seeded spread of ranges; returns matches/s."""
     from oracle import oracle as orc
+    threads = threads or host_cores()
     rng = np.random.default_rng(1234)
     sel = np.sort(rng.choice(N_RANGES, n_ranges_sample, replace=False))
     # contiguous calls of one range each would serialise; the oracle parallelises over a contiguous slice, so take
@@ -106,7 +115,7 @@ def cpu_sample(img, n_ranges_sample, threads=0):
     t0 = time.perf_counter()
     orc.bf_encode(img, mode=1, range_begin=start, range_end=start + n_ranges_sample, nthreads=threads)
     dt = time.perf_counter() - t0
-    return n_ranges_sample * N_POS * 8 / dt, dt, orc.num_threads(), start
+    return n_ranges_sample * N_POS * 8 / dt, dt, threads, start
 
 
 def run_reference(args):
@@ -116,7 +125,7 @@ def run_reference(args):
     from oracle import oracle as orc
     orc.lib()
     img = load_image(0)
-    cores = orc.num_threads()
+    cores = host_cores()
     sample = max(cores * 8, 32)
     for _ in range(max(args.warmup, 0) and 1):  # one short warm-up is enough for compiled C
         cpu_sample(img, max(cores, 4))
@@ -259,7 +268,7 @@ def run_ours(args):
         cpu = None
         if world == 1 and not args.no_cpu:
             from oracle import oracle as orc
-            cores = orc.num_threads()
+            cores = host_cores()
             sample = max(8 * cores, 32)
             cpu_sample(img, max(cores, 4))
             v, dt, cores, start = cpu_sample(img, sample)
