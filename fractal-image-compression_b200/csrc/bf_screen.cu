@@ -66,7 +66,7 @@ constexpr int EPI_WARPS = 2 * WARPS_PER_STAGE;
 // the scheduler favours high warp ids: the two single-thread roles sit ABOVE the epilogue warps so that the busy
 // epilogue can never delay a TMA issue or an MMA issue
 constexpr int TMA_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
-constexpr int SCREEN_THREADS = 64 + EPI_WARPS * 32;
+constexpr int SCREEN_THREADS = 64 + EPI_WARPS * 32;   // registers are allocated per four warps: 576 threads -> 96 each
 constexpr uint32_t A_MAIN_BYTES = BM * KMAIN * 2;   // 16384
 constexpr uint32_t A_EXT_BYTES = BM * KEXT * 2;     // 4096
 constexpr uint32_t B_MAIN_BYTES = BN * KMAIN * 2;   // 32768
@@ -77,8 +77,9 @@ constexpr uint32_t OFF_A_MAIN = OFF_B_EXT + B_EXT_BYTES;
 constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
 constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
 constexpr uint32_t OFF_TAU = OFF_BARS + 256;                        // per epilogue warp: 16 x float2 thresholds
-constexpr uint32_t OFF_QUEUE = OFF_TAU + EPI_WARPS * 16 * 8;          // per epilogue warp: survivor queue (784 B)
-constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * 784 + 1024;  // + slack to align the base to 1024
+constexpr uint32_t OFF_QUEUE = OFF_TAU + EPI_WARPS * 16 * 8;          // per epilogue warp: survivor queue
+constexpr uint32_t QUEUE_BYTES = (32 + 512) * 8;                     // sizeof(WarpQueue), checked below
+constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * QUEUE_BYTES + 1024;  // + slack to align the base to 1024
 
 constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
 constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
@@ -115,8 +116,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* er
 {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
+    uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 8000000000ll) {
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 8000000000ll) {   // look at the clock only now and then
             if (err_flag) atomicExch(err_flag, code);
             __threadfence_system();
             __trap();
@@ -265,38 +267,32 @@ __device__ __noinline__ void append_hits(uint32_t* __restrict__ cnt, uint32_t* _
     }
 }
 
-// Per-warp survivor queue in shared memory: a hit costs one shared-memory atomic and one store; the global
-// reservations (one atomicAdd per entry, a full round trip to L2) are issued 32 at a time when the queue is flushed.
-constexpr int QCAP = 96;
+// Per-warp survivor queue in shared memory.  The fill level lives in a (warp-uniform) register and hits are placed
+// with a ballot + prefix count, so a hit costs one vote and one store -- no atomics, no divergent lanes.  The global
+// reservations (one atomicAdd per entry, a full round trip to L2) are issued 32 at a time when the queue is flushed
+// between tiles.  A tile can add at most 4 chunks x 4 ranges x 32 lanes = 512 entries per warp, and the queue is
+// flushed whenever a tile ends with QFLUSH or more entries, so QCAP = QFLUSH + 512 can never overflow.
+constexpr int QFLUSH = 32;
+constexpr int QCAP = QFLUSH + 512;
 struct WarpQueue {
-    uint32_t count;
-    uint32_t pad;
     uint2 e[QCAP];   // x = (slot << 8) | isometry mask, y = candidate position
 };
+static_assert(sizeof(WarpQueue) == QUEUE_BYTES, "QUEUE_BYTES must match WarpQueue");
 
-__device__ __forceinline__ void queue_push(WarpQueue* q, const ScreenParams& p, int slot, uint32_t cand, unsigned m8)
-{
-    const uint32_t pos = atomicAdd(&q->count, 1u);
-    if (pos < QCAP) q->e[pos] = make_uint2(((uint32_t)slot << 8) | m8, cand);
-    else append_hits(p.cnt, p.list, p.cap, slot, cand, m8);   // queue full (pathological burst): go direct
-}
-
-__device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, int lane)
+__device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, int lane, uint32_t n)
 {
     __syncwarp();
-    const uint32_t n = min(q->count, (uint32_t)QCAP);
+    for (int rep = 0; rep < (p.debug_mode == 5 ? 2 : 1); ++rep)   // timing experiment: 5 = every append twice
     for (uint32_t k = lane; k < n; k += 32) {
         const uint2 ent = q->e[k];
         append_hits(p.cnt, p.list, p.cap, (int)(ent.x >> 8), ent.y, ent.x & 0xffu);
     }
     __syncwarp();
-    if (lane == 0) q->count = 0;
-    __syncwarp();
 }
 
 template <bool APPEND>
-__device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float (&theta)[4], const ScreenParams& p, int slot0,
-                                             int my_cand, WarpQueue* q)
+__device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float* theta, const ScreenParams& p, int slot0,
+                                             int my_cand, WarpQueue* q, uint32_t& qn, int lane)
 {
     float m[4];
     bool any = false;
@@ -311,14 +307,19 @@ __device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const floa
         if (any && m[0] == 1.2345e-30f) p.cnt[0] = 1;
         return;
     }
-    if (any) {
+    if (__any_sync(0xffffffffu, any)) {   // warp-uniform from here on
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-            if (m[g] >= theta[g]) {
-                unsigned m8 = 0;
+            const bool hit = m[g] >= theta[g];
+            const unsigned mask = __ballot_sync(0xffffffffu, hit);
+            if (mask) {
+                if (hit) {
+                    unsigned m8 = 0;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) m8 |= (fabsf(__uint_as_float(v[g * 8 + i])) >= theta[g] ? 1u : 0u) << i;
-                queue_push(q, p, slot0 + g, (uint32_t)my_cand, m8);
+                    for (int i = 0; i < 8; ++i) m8 |= (fabsf(__uint_as_float(v[g * 8 + i])) >= theta[g] ? 1u : 0u) << i;
+                    q->e[qn + __popc(mask & ((1u << lane) - 1u))] = make_uint2(((uint32_t)(slot0 + g) << 8) | m8, (uint32_t)my_cand);
+                }
+                qn += __popc(mask);
             }
         }
     }
@@ -342,8 +343,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
     const uint32_t b_full = bars + 8u * (2 * STAGES), b_empty = bars + 8u * (2 * STAGES + 1);
     auto tfull_bar = [&](int s) { return bars + 8u * (2 * STAGES + 2 + s); };
-    auto tempty_bar = [&](int s) { return bars + 8u * (2 * STAGES + 4 + s); };
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + OFF_BARS + 8 * (2 * STAGES + 6));
+    auto tempty_bar = [&](int s) { return bars + 8u * (2 * STAGES + 6 + s); };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + OFF_BARS + 8 * (2 * STAGES + 10));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
@@ -401,12 +402,12 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 mbar_wait(b_full, bph, p.err_flag, 3);
                 bph ^= 1;
                 for (int j = j0; j < j1; ++j) {
+                    const uint64_t adesc = make_desc(base + OFF_A_MAIN + s * A_MAIN_BYTES, 1024, 2);
+                    const uint64_t axdesc = make_desc(base + OFF_A_EXT + s * A_EXT_BYTES, 256, 6);
                     mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
                     mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
                     tcgen05_fence_after();
                     const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
-                    const uint64_t adesc = make_desc(base + OFF_A_MAIN + s * A_MAIN_BYTES, 1024, 2);
-                    const uint64_t axdesc = make_desc(base + OFF_A_EXT + s * A_EXT_BYTES, 256, 6);
 #pragma unroll
                     for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
@@ -419,56 +420,84 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 tcgen05_commit(b_empty);
             }
         }
-    } else {
+    } else if (warp < EPI_WARPS) {
         // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
         // Two warp groups of WARPS_PER_STAGE warps; group g owns accumulator stage g, i.e. every second tile of the CTA's
         // span, so the two groups work on different tiles at the same time and only ever wait on their own stage.  Inside
         // a group two warps share each TMEM lane quadrant and take 128 columns (16 ranges) each.
         const int ew = warp;
-        const int stage = ew / WARPS_PER_STAGE;
+        const int stage = ew / WARPS_PER_STAGE;              // the accumulator stage this warp owns
         const int quad = warp & 3;                           // TMEM lane quadrant this warp may touch
-        const int half = (ew % WARPS_PER_STAGE) >> 2;        // which 128 of the 256 columns
+        const int part = (ew % WARPS_PER_STAGE) >> 2;        // which 128-column half of the 256 columns
         const int lane_off = quad * 32 + lane;
-        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(stage * BN + half * 128);
+        // address of this warp's slice of its accumulator stage; pinned so it is not rebuilt from %tid after the wait
+        uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(stage * BN + part * 128);
+        asm volatile("" : "+r"(taddr0));
+        uint32_t lane0 = lane == 0;
+        asm volatile("" : "+r"(lane0));
+        const uint32_t my_tfull = tfull_bar(stage), my_tempty = tempty_bar(stage);
         uint32_t aph = 0;
         int n = 0;  // tiles issued so far by this CTA (all units): tile n uses stage n & 1
         float* my_tau = reinterpret_cast<float*>(gbase + OFF_TAU) + ew * 32;   // [0,16) = tau_A, [16,32) = tau_B
         WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + ew;
-        if (lane == 0) queue->count = 0;
-        __syncwarp();
+        uint32_t qn = 0;   // queue fill, warp-uniform
         Span span(p, n_groups);
         int grp, j0, j1;
         while (span.next(grp, j0, j1)) {
-            if (MODE == 0) queue_flush(queue, p, lane);   // entries carry absolute slots, but keep units separate
-            // this warp's 16 (tau_A, tau_B) pairs live in a private slice of shared memory (registers are needed for two
-            // accumulator chunks in flight); broadcast reads, no bank conflicts
+            if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
+            // this warp's (tau_A, tau_B) pairs live in a private slice of shared memory; broadcast reads, no bank conflicts
             __syncwarp();
             if (lane < 16) {
-                const float2 tt = p.tau[grp * 32 + half * 16 + lane];
+                const float2 tt = p.tau[grp * 32 + part * 16 + lane];
                 my_tau[lane] = tt.x;
                 my_tau[16 + lane] = tt.y;
             }
             __syncwarp();
-            const int slot0 = grp * 32 + half * 16;
-            int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that lands in my stage
+            const int slot0 = grp * 32 + part * 16;
+            int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
+            // tile index of j without a division per tile: t = (j + j / (r_prev - 1) + 1) * m_cur, advanced by 2
+            int t_cur = j < j1 ? tile_of(p, j) : 0;
+            const int r1 = p.r_prev > 0 ? p.r_prev - 1 : 0x7fffffff;
+            int rem = p.r_prev > 0 && j < j1 ? j % r1 : 0;
+            // +-1/h_c of this lane's candidate, fetched one tile ahead; sign = conditioning class; +inf (threshold never
+            // met) for the padding rows of the last tile
+            const float hk_pad = __int_as_float(0x7f800000);
+            float hq_next = (j < j1 && t_cur * BM + lane_off < p.NP) ? p.hk[t_cur * BM + lane_off].x : hk_pad;
             for (; j < j1; j += 2) {
-                const int my_cand = tile_of(p, j) * BM + lane_off;
-                const float hq = my_cand < p.NP ? p.hk[my_cand].x : 0.f;   // +-1/h_c, sign = conditioning class
-                const bool ill = hq < 0.f;
+                // ---- everything up to the wait is off the accumulator's critical path (MMA -> epilogue -> MMA) ----
+                const int my_cand = t_cur * BM + lane_off;
+                {   // advance (t_cur, rem) to j + 2
+                    rem += 2;
+                    int wraps = 0;
+                    if (rem >= r1) { rem -= r1; wraps = 1; }
+                    if (rem >= r1) { rem -= r1; wraps = 2; }   // r1 == 1 (r_prev == 2)
+                    t_cur += (2 + wraps) * p.m_cur;
+                }
+                const float hq = hq_next;
+                {
+                    const int next_cand = t_cur * BM + lane_off;
+                    hq_next = (j + 2 < j1 && next_cand < p.NP) ? p.hk[next_cand].x : hk_pad;
+                }
                 const float qx = fabsf(hq);
-                mbar_wait(tfull_bar(stage), aph, p.err_flag, 6);
-                aph ^= 1;
+                // thresholds on |u| for the 16 ranges: theta = tau/h_c - DELTA, tau picked by the candidate's class
+                float theta[16];
+                {
+                    const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq < 0.f ? 16 : 0));
+#pragma unroll
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        const float4 t = tau4[c4];   // one broadcast LDS.128
+                        theta[c4 * 4 + 0] = fmaf(t.x, qx, -DELTA_U);
+                        theta[c4 * 4 + 1] = fmaf(t.y, qx, -DELTA_U);
+                        theta[c4 * 4 + 2] = fmaf(t.z, qx, -DELTA_U);
+                        theta[c4 * 4 + 3] = fmaf(t.w, qx, -DELTA_U);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) asm volatile("" : "+f"(theta[i]));   // materialise before the wait
+                }
+                mbar_wait(my_tfull, aph, p.err_flag, 6);
                 tcgen05_fence_after();
                 uint32_t va[32], vb[32];
-                const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (ill ? 16 : 0));   // class picks the array
-                auto thetas = [&](int c4, float (&theta)[4]) {
-                    const float4 t = tau4[c4];                                                   // one broadcast LDS.128
-                    theta[0] = fmaf(t.x, qx, -DELTA_U);
-                    theta[1] = fmaf(t.y, qx, -DELTA_U);
-                    theta[2] = fmaf(t.z, qx, -DELTA_U);
-                    theta[3] = fmaf(t.w, qx, -DELTA_U);
-                };
                 if (MODE == 1) {
                     for (int c4 = 0; c4 < 4; ++c4) {
                         tmem_ld32(taddr0 + c4 * 32, va);
@@ -476,36 +505,41 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         if (grp == 0) {
 #pragma unroll
                             for (int q = 0; q < 32; ++q)
-                                p.dump[(size_t)my_cand * BN + half * 128 + c4 * 32 + q] = __uint_as_float(va[q]);
+                                p.dump[(size_t)my_cand * BN + part * 128 + c4 * 32 + q] = __uint_as_float(va[q]);
                         }
                     }
-                } else if (MODE != 3) {
-                    float theta[4];
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                } else if (MODE == 3) {
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                } else {
+                    constexpr bool SCREEN = MODE == 0 || MODE == 4;
                     tmem_ld32(taddr0, va);
                     tmem_ld32(taddr0 + 32, vb);
-                    thetas(0, theta);
                     tmem_ld_wait(va);
                     tmem_ld_wait(vb);
-                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(va, theta, p, slot0, my_cand, queue);
+                    if (SCREEN) screen_chunk<MODE == 0>(va, theta + 0, p, slot0, my_cand, queue, qn, lane);
                     tmem_ld32(taddr0 + 64, va);        // in flight while chunk 1 is screened
-                    thetas(1, theta);
-                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(vb, theta, p, slot0 + 4, my_cand, queue);
-                    tmem_ld32(taddr0 + 96, vb);        // in flight while chunk 2 is screened
-                    thetas(2, theta);
+                    if (SCREEN) screen_chunk<MODE == 0>(vb, theta + 4, p, slot0 + 4, my_cand, queue, qn, lane);
+                    tmem_ld32(taddr0 + 96, vb);
                     tmem_ld_wait(va);
                     tmem_ld_wait(vb);
-                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(va, theta, p, slot0 + 8, my_cand, queue);
-                    thetas(3, theta);
-                    if (MODE == 0 || MODE == 4) screen_chunk<MODE == 0>(vb, theta, p, slot0 + 12, my_cand, queue);
-                    if (MODE != 0 && MODE != 4 && (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u)) p.cnt[0] = 1;
+                    // the whole slice is in registers now: hand the accumulator back before screening the second half
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                    if (SCREEN) screen_chunk<MODE == 0>(va, theta + 8, p, slot0 + 8, my_cand, queue, qn, lane);
+                    if (SCREEN) screen_chunk<MODE == 0>(vb, theta + 12, p, slot0 + 12, my_cand, queue, qn, lane);
+                    if (!SCREEN && (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u)) p.cnt[0] = 1;
                 }
-                tcgen05_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(tempty_bar(stage));
-                if (MODE == 0 && queue->count >= QCAP / 2) queue_flush(queue, p, lane);   // warp-uniform: read after __syncwarp
+                aph ^= 1;
+                if (MODE == 0 && qn >= QFLUSH) { queue_flush(queue, p, lane, qn); qn = 0; }
             }
         }
-        if (MODE == 0) queue_flush(queue, p, lane);
+        if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
     }
     tcgen05_fence_before();
     __syncthreads();

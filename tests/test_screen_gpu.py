@@ -134,3 +134,33 @@ def test_three_round_plan_on_a_large_image(fic):
     # the same slice through the pipeline on its own (range-slice sharding of a big image)
     part = fic.bf_encode(img, mode=fic.BF_MODE_JIT, range_begin=5000, range_end=5256)
     assert np.array_equal(part[0], idx[5000:5256]) and np.array_equal(part[1], so[5000:5256])
+
+
+def _stress_images():
+    rng = np.random.default_rng(2024)
+    yy, xx = np.mgrid[0:160, 0:192]
+    out = {}
+    out["gradient"] = ((yy * 1.3 + xx * 0.4) % 256).astype(np.uint8)                       # smooth ramps: near-flat domains
+    out["low_contrast"] = (120 + rng.integers(0, 4, (160, 192))).astype(np.uint8)            # variance below the guard
+    out["steps"] = ((xx // 24) * 36 % 256).astype(np.uint8)                                  # piecewise constant: den16 == 0 often
+    out["steps_noise"] = np.clip(out["steps"].astype(int) + rng.integers(-1, 2, (160, 192)), 0, 255).astype(np.uint8)
+    out["saturated"] = np.where(rng.random((160, 192)) < 0.5, 0, 255).astype(np.uint8)       # largest magnitudes
+    out["sparse_dots"] = np.zeros((160, 192), np.uint8)
+    out["sparse_dots"][rng.integers(0, 160, 300), rng.integers(0, 192, 300)] = 255
+    s = synthetic_image(77, 160, 192).astype(int)
+    out["dark"] = (s // 16).astype(np.uint8)                                                 # tiny dynamic range
+    out["bright_clip"] = np.clip(s * 2, 0, 255).astype(np.uint8)                             # half the image clipped to 255
+    out["texture_tiles"] = np.tile(rng.integers(0, 256, (16, 16), dtype=np.uint8), (10, 12)) # exact repeats: many exact ties
+    out["self_similar"] = np.kron(rng.integers(0, 256, (20, 24)), np.ones((8, 8))).astype(np.uint8)  # every range constant
+    return out
+
+
+@pytest.mark.parametrize("name", sorted(_stress_images()))
+def test_screen_is_conservative_on_adversarial_images(fic, name):
+    """The screen may only drop candidates that cannot win or tie.  Images chosen to attack the bound: domains with
+    (almost) zero variance, ranges flatter than the float32 noise guard, saturated pixels, exact repeats (ties)."""
+    img = _stress_images()[name]
+    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
+    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y), name
