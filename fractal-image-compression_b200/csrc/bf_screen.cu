@@ -132,6 +132,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_commit(uint32_t bar)
@@ -367,58 +373,77 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == TMA_WARP) {
-        // ===== TMA producer =====
-        if (lane == 0) {
-            int s = 0;
-            uint32_t ph = 0, bph = 0;
-            Span span(p, n_groups);
-            int grp, j0, j1;
-            while (span.next(grp, j0, j1)) {
-                mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
+        // ===== TMA producer =====  (whole warp in lock step, one elected lane issues -- see the MMA issuer)
+        int s = 0;
+        uint32_t ph = 0, bph = 0;
+        const bool issuer = elect_one();
+        Span span(p, n_groups);
+        int grp, j0, j1;
+        while (span.next(grp, j0, j1)) {
+            mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
+            if (issuer) {
                 mbar_expect_tx(b_full, B_MAIN_BYTES + B_EXT_BYTES);
                 tma_load_2d(base + OFF_B_MAIN, &mapB, b_full, 0, grp * BN);
                 tma_load_2d(base + OFF_B_EXT, &mapBx, b_full, 0, grp * BN);
-                bph ^= 1;
-                for (int j = j0; j < j1; ++j) {
-                    const int t = tile_of(p, j);
-                    mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
+            }
+            bph ^= 1;
+            // tile index without a division per tile (same walk as the epilogue's)
+            int t_cur = tile_of(p, j0);
+            const int r1 = p.r_prev > 0 ? p.r_prev - 1 : 0x7fffffff;
+            int rem = p.r_prev > 0 ? j0 % r1 : 0;
+            for (int j = j0; j < j1; ++j) {
+                mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
+                if (issuer) {
                     mbar_expect_tx(full_bar(s), A_MAIN_BYTES + A_EXT_BYTES);
-                    tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t * BM);
-                    tma_load_2d(base + OFF_A_EXT + s * A_EXT_BYTES, &mapAx, full_bar(s), 0, t * BM);
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                    tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t_cur * BM);
+                    tma_load_2d(base + OFF_A_EXT + s * A_EXT_BYTES, &mapAx, full_bar(s), 0, t_cur * BM);
                 }
+                __syncwarp();
+                int step = 1;
+                if (++rem >= r1) { rem = 0; step = 2; }
+                t_cur += step * p.m_cur;
+                if (++s == STAGES) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == MMA_WARP) {
         // ===== MMA issuer =====
-        if (lane == 0) {
-            int s = 0, as = 0;
-            uint32_t ph = 0, aph = 0, bph = 0;
-            const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
-            const uint64_t bxdesc = make_desc(base + OFF_B_EXT, 256, 6);
-            Span span(p, n_groups);
-            int grp, j0, j1;
-            while (span.next(grp, j0, j1)) {
-                mbar_wait(b_full, bph, p.err_flag, 3);
-                bph ^= 1;
-                for (int j = j0; j < j1; ++j) {
-                    const uint64_t adesc = make_desc(base + OFF_A_MAIN + s * A_MAIN_BYTES, 1024, 2);
-                    const uint64_t axdesc = make_desc(base + OFF_A_EXT + s * A_EXT_BYTES, 256, 6);
-                    mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
-                    mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
-                    tcgen05_fence_after();
-                    const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
+        // The issue loop is the pacemaker of the whole CTA: every cycle it spends between "accumulator free" and the
+        // last tcgen05.mma is a cycle the tensor pipe idles.  All 32 lanes run it in lock step (so ptxas keeps
+        // descriptors and barrier addresses in uniform registers instead of broadcasting them out of a divergent lane
+        // before every instruction), one elected lane issues, and the descriptors are advanced by additions.
+        int s = 0, as = 0;
+        uint32_t ph = 0, aph = 0, bph = 0;
+        const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
+        const uint64_t bxdesc = make_desc(base + OFF_B_EXT, 256, 6);
+        const uint64_t adesc0 = make_desc(base + OFF_A_MAIN, 1024, 2);
+        const uint64_t axdesc0 = make_desc(base + OFF_A_EXT, 256, 6);
+        const bool issuer = elect_one();
+        Span span(p, n_groups);
+        int grp, j0, j1;
+        while (span.next(grp, j0, j1)) {
+            mbar_wait(b_full, bph, p.err_flag, 3);
+            bph ^= 1;
+            for (int j = j0; j < j1; ++j) {
+                const uint64_t adesc = adesc0 + (uint64_t)(s * (A_MAIN_BYTES >> 4));
+                const uint64_t axdesc = axdesc0 + (uint64_t)(s * (A_EXT_BYTES >> 4));
+                const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
+                mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
+                mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
+                tcgen05_fence_after();
+                if (issuer) {
 #pragma unroll
                     for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
                     umma_f16(d_tmem, axdesc, bxdesc, IDESC, 1);
                     tcgen05_commit(empty_bar(s));   // frees the A stage once the MMAs above have completed
                     tcgen05_commit(tfull_bar(as));  // accumulator ready for the epilogue
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
-                    if (++as == 2) { as = 0; aph ^= 1; }
                 }
-                tcgen05_commit(b_empty);
+                __syncwarp();
+                if (++s == STAGES) { s = 0; ph ^= 1; }
+                if (++as == 2) { as = 0; aph ^= 1; }
             }
+            if (issuer) tcgen05_commit(b_empty);
+            __syncwarp();
         }
     } else if (warp < EPI_WARPS) {
         // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
