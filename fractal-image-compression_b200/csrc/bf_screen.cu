@@ -41,7 +41,7 @@
 // HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
 //   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
 //   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
-//   hk      float2 [NP]    (+-1/h_c, 0); a negative value marks an ill-conditioned domain
+//   hk      float2 [NP]    (+-1/h_c, den16); a negative .x marks an ill-conditioned domain, .y only ranks seed candidates
 // and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -210,6 +210,7 @@ struct ScreenParams {
     float* dump;             // probe mode: [n_tiles*128][256] raw accumulators of column group 0 (else nullptr)
     int* err_flag;
     int debug_mode;          // 0 = normal; 1/2/3 = timing experiments (FIC_SCREEN_DEBUG), results invalid
+    unsigned long long* seed_best;   // seed mode: [slots] max of (gain bits << 32 | ~local candidate)
 };
 
 // j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
@@ -504,6 +505,40 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     const int next_cand = t_cur * BM + lane_off;
                     hq_next = (j + 2 < j1 && next_cand < p.NP) ? p.hk[next_cand].x : hk_pad;
                 }
+                if (MODE == 5) {
+                    // seed mode: no thresholds yet.  Rank the (few) candidates of the seed pool by the collage-error
+                    // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
+                    // one per range; it is scored exactly afterwards and provides the first upper bound.
+                    const float den = my_cand < p.NP ? p.hk[my_cand].y : 0.f;
+                    uint32_t vs[32];
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        tmem_ld32(taddr0 + c4 * 32, vs);
+                        tmem_ld_wait(vs);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float m = fabsf(__uint_as_float(vs[g * 8]));
+#pragma unroll
+                            for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(vs[g * 8 + i])));
+                            float gain = 0.f;
+                            if (den > 0.f) gain = 256.f * m <= den ? 64.f * m * m / den : 0.5f * m - den * (1.0f / 1024.0f);
+                            const uint32_t bits = gain > 0.f ? __float_as_uint(gain) : 0u;
+                            const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
+                            if (wmax != 0u) {
+                                const unsigned who = __ballot_sync(0xffffffffu, bits == wmax);
+                                if (lane == __ffs(who) - 1)
+                                    atomicMax(&p.seed_best[slot0 + c4 * 4 + g],
+                                              ((unsigned long long)bits << 32) | (0xffffffffu - (uint32_t)my_cand));
+                            }
+                        }
+                    }
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                    aph ^= 1;
+                    continue;
+                }
                 const float qx = fabsf(hq);
                 // thresholds on |u| for the 16 ranges: theta = tau/h_c - DELTA, tau picked by the candidate's class
                 float theta[16];
@@ -626,6 +661,7 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
         const double h2 = well ? 64.0 / d * (1.0 + 1.0e-3 * q / d) : 64.0 / d;
         hc = (float)(1.0 / sqrt(h2)) * (1.0f - 1.0f / 1048576.0f);
         if (!well) hc = -hc;                                   // sign flags the ill-conditioned class
+        kc = (float)d;                                         // den16, only used to rank seed candidates
     }
     hk[p] = make_float2(hc, kc);
 }
@@ -657,68 +693,77 @@ __global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int r
 }
 
 // ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
-__global__ void __launch_bounds__(1024)
-bf_threshold_kernel(const uint2* __restrict__ sums, int PW, int range_begin, int n_ranges,
-                    const int32_t* __restrict__ pre_idx, const double* __restrict__ pre_so, const double* __restrict__ pre_R,
-                    RangeState* __restrict__ state, float2* __restrict__ tau, int32_t* __restrict__ fallback,
-                    int* __restrict__ ctrl, int tau_pad)
+// Every range of the slice gets a slot in natural order.  Nothing is known about the winners yet: R = +inf, no
+// candidate, thresholds +inf (nothing passes); constant ranges are flagged, they are decided by the seed list alone
+// (every candidate scores R = 0 exactly, the first in scan order -- position 0, isometry 0 -- wins).
+__global__ void bf_init_kernel(const uint2* __restrict__ sums, int range_begin, int n_ranges, RangeState* __restrict__ state,
+                               float2* __restrict__ tau, unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl,
+                               int tau_pad)
 {
-    __shared__ int warp_e[32], warp_f[32];
-    __shared__ int base_e, base_f;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { base_e = 0; base_f = 0; }
-    __syncthreads();
-    for (int b0 = 0; b0 < n_ranges; b0 += 1024) {
-        const int slot = b0 + tid;
-        bool is_e = false, is_f = false;
-        float2 my_tau = make_float2(0.f, 0.f);
-        RangeState rs_;
-        if (slot < n_ranges) {
-            const int ridx = range_begin + slot;
-            const uint2 sq_ = sums[slot];
-            const long long s = sq_.x, q = sq_.y;
-            const long long A64 = 64 * q - s * s;                             // 64 * A_r, exact
-            const double ub = pre_R[slot];
-            rs_.R = ub; rs_.s = pre_so[2 * slot]; rs_.o = pre_so[2 * slot + 1];
-            rs_.seq = ((unsigned long long)pre_idx[4 * slot] * PW + pre_idx[4 * slot + 1]) * 8ull + pre_idx[4 * slot + 2] * 4 + pre_idx[4 * slot + 3];
-            rs_.ridx = ridx; rs_.flags = 0; rs_.rsum = (int)s; rs_.pad_ = 0;
-            rs_.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
-            const double TA = rs_.TA0 - 64.0 * ub, TB = TA - 64.0 * GUARD_ILL;
-            if (A64 == 0) {
-                // constant range: every candidate scores R = 0 exactly, the first in scan order wins; the pre-scan
-                // always visits position 0, isometry 0, so the seeded state already holds the winner
-                is_e = true;
-                rs_.flags = 2;
-                my_tau = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-            } else if (ub == ub && ub < 1e300 && TA > 1e-3) {
-                is_e = true;
-                my_tau.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);     // rounded down a little: never over-estimate
-                my_tau.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
-            } else {
-                is_f = true;
-            }
-        }
-        const unsigned me = __ballot_sync(0xffffffffu, is_e), mf = __ballot_sync(0xffffffffu, is_f);
-        if (lane == 0) { warp_e[warp] = __popc(me); warp_f[warp] = __popc(mf); }
-        __syncthreads();
-        int pe = base_e, pf = base_f;
-        for (int w = 0; w < warp; ++w) { pe += warp_e[w]; pf += warp_f[w]; }
-        pe += __popc(me & ((1u << lane) - 1u));
-        pf += __popc(mf & ((1u << lane) - 1u));
-        if (is_e) { state[pe] = rs_; tau[pe] = my_tau; }
-        if (is_f) fallback[pf] = range_begin + slot;
-        __syncthreads();
-        if (tid == 0) {
-            int te = 0, tf = 0;
-            for (int w = 0; w < 32; ++w) { te += warp_e[w]; tf += warp_f[w]; }
-            base_e += te;
-            base_f += tf;
-        }
-        __syncthreads();
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k == 0) { ctrl[0] = n_ranges; ctrl[1] = 0; }
+    if (k < tau_pad) {
+        tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+        seed_best[k] = 0ull;
     }
-    // pad tau so that every column group reads 32 valid entries: +inf never passes
-    for (int k = base_e + tid; k < tau_pad; k += 1024) tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-    if (tid == 0) { ctrl[0] = base_e; ctrl[1] = base_f; }
+    if (k < n_ranges) {
+        const uint2 sq_ = sums[k];
+        const long long s = sq_.x, q = sq_.y;
+        const long long A64 = 64 * q - s * s;                             // 64 * A_r, exact
+        RangeState st;
+        st.R = __longlong_as_double(0x7ff0000000000000ll); st.s = 0.0; st.o = 0.0;
+        st.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
+        st.seq = ~0ull; st.ridx = range_begin + k; st.flags = A64 == 0 ? 2 : 0;
+        st.rsum = (int)s; st.pad_ = 0;
+        state[k] = st;
+    }
+}
+
+// ---- seed pool: a coarse lattice of candidate positions, gathered into its own small TMA pool ----------------------
+// seed candidate k sits at lattice node (k / gx, k % gx) * S; rows beyond n_seed are padding (zero rows, den16 = 0)
+__global__ void bf_seed_gather_kernel(const __half* __restrict__ poolA, const __half* __restrict__ poolAx,
+                                      const float2* __restrict__ hk, int PW, int S, int gx, int n_seed, int n_seed_pad,
+                                      __half* __restrict__ seedA, __half* __restrict__ seedAx, float2* __restrict__ seedhk)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_seed_pad) return;
+    uint4* da = reinterpret_cast<uint4*>(seedA + (size_t)k * 64);
+    uint4* dx = reinterpret_cast<uint4*>(seedAx + (size_t)k * 16);
+    if (k < n_seed) {
+        const size_t p = (size_t)(k / gx) * S * PW + (size_t)(k % gx) * S;
+        const uint4* sa = reinterpret_cast<const uint4*>(poolA + p * 64);
+        const uint4* sx = reinterpret_cast<const uint4*>(poolAx + p * 16);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) da[q] = sa[q];
+        dx[0] = sx[0];
+        dx[1] = sx[1];
+        seedhk[k] = hk[p];
+    } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) da[q] = make_uint4(0u, 0u, 0u, 0u);
+        dx[0] = make_uint4(0u, 0u, 0u, 0u);
+        dx[1] = make_uint4(0u, 0u, 0u, 0u);
+        seedhk[k] = make_float2(__int_as_float(0x7f800000), 0.f);
+    }
+}
+
+// first survivor list of every range: position 0 / isometry 0 (decides constant ranges, and the exact scan visits it
+// first anyway) plus the eight isometries of the best-ranked seed candidate
+__global__ void bf_seed_list_kernel(const unsigned long long* __restrict__ seed_best, int n_ranges, int PW, int S, int gx,
+                                    uint32_t* __restrict__ cnt, uint32_t* __restrict__ list, uint32_t cap)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_ranges) return;
+    uint32_t* l = list + (size_t)slot * cap;
+    uint32_t n = 0;
+    l[n++] = 0u;
+    const unsigned long long key = seed_best[slot];
+    if (key != 0ull) {
+        const uint32_t k = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+        const uint32_t p = (k / (uint32_t)gx) * (uint32_t)S * (uint32_t)PW + (k % (uint32_t)gx) * (uint32_t)S;
+        for (uint32_t t = 0; t < 8; ++t) l[n++] = p * 8u + t;
+    }
+    cnt[slot] = n;
 }
 
 // probe mode: every range eligible in natural order, nothing ever passes
@@ -736,18 +781,25 @@ __global__ void bf_probe_state_kernel(const uint2* __restrict__ sums, int range_
     }
 }
 
-// thresholds for round 2 from the improved winners
-__global__ void bf_retau_kernel(const RangeState* __restrict__ state, const int* __restrict__ ctrl, float2* __restrict__ tau)
+// thresholds of the next round from the running winners.  A range whose bound is not clearly below its own variance
+// (or that has no finite winner) cannot be screened: it is handed to the exact scan and never passes anything.
+__global__ void bf_retau_kernel(RangeState* __restrict__ state, int* __restrict__ ctrl, float2* __restrict__ tau,
+                                int32_t* __restrict__ fallback)
 {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= ctrl[0]) return;
     const RangeState st = state[slot];
     float2 t = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
     if (st.flags == 0) {
-        const double TA = st.TA0 - 64.0 * st.R, TB = TA - 64.0 * GUARD_ILL;
-        // TA can only have grown since round 1 (R decreased), so it is still positive
-        t.x = TA > 0.0 ? (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f) : 0.f;
-        t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+        const double ub = st.R;
+        const double TA = st.TA0 - 64.0 * ub, TB = TA - 64.0 * GUARD_ILL;
+        if (ub == ub && ub < 1e300 && TA > 1e-3) {
+            t.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);     // rounded down a little: never over-estimate
+            t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+        } else {
+            state[slot].flags = 1;
+            fallback[atomicAdd(&ctrl[1], 1)] = st.ridx;
+        }
     }
     tau[slot] = t;
 }
@@ -1023,7 +1075,23 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_ctrl.reserve(256));
-    FIC_TRY(h->bf_best.reserve((size_t)n_ranges * (16 + 16 + 8) + 256));
+    // seed lattice: about NP/100 positions (at least 256, at most 4096), a whole number of candidate tiles
+    int seed_S, seed_gx, n_seed, n_seed_pad;
+    {
+        double want = (double)NP / 100.0;
+        if (want < 256.0) want = 256.0;
+        if (want > 4096.0) want = 4096.0;
+        if (const char* e = getenv("FIC_SEED_POSITIONS")) want = atof(e) > 1.0 ? atof(e) : want;  // tuning knob
+        seed_S = (int)floor(sqrt((double)NP / want) + 0.5);
+        if (seed_S < 1) seed_S = 1;
+        seed_gx = cdiv(PW, seed_S);
+        n_seed = seed_gx * cdiv(PH, seed_S);
+        n_seed_pad = cdiv(n_seed, BM) * BM;
+    }
+    const size_t off_seedhk = ((size_t)tau_pad * 8 + 255) & ~(size_t)255;
+    const size_t off_seedA = (off_seedhk + (size_t)n_seed_pad * 8 + 255) & ~(size_t)255;
+    const size_t off_seedAx = off_seedA + (size_t)n_seed_pad * 128;
+    FIC_TRY(h->bf_best.reserve(off_seedAx + (size_t)n_seed_pad * 32 + 256));
     FIC_TRY(h->pin_a.reserve(256));
 
     __half* poolA = h->bf_pool.as<__half>();
@@ -1038,9 +1106,11 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
-    int32_t* pre_idx = h->bf_best.as<int32_t>();
-    double* pre_so = reinterpret_cast<double*>(pre_idx + (size_t)n_ranges * 4);
-    double* pre_R = pre_so + (size_t)n_ranges * 2;
+    unsigned char* seed_raw = h->bf_best.as<unsigned char>();
+    unsigned long long* seed_best = reinterpret_cast<unsigned long long*>(seed_raw);
+    float2* seedhk = reinterpret_cast<float2*>(seed_raw + off_seedhk);
+    __half* seedA = reinterpret_cast<__half*>(seed_raw + off_seedA);
+    __half* seedAx = reinterpret_cast<__half*>(seed_raw + off_seedAx);
 
     FIC_CUDA(cudaMemsetAsync(ctrl, 0, 64, st));
     FIC_CUDA(cudaMemsetAsync(cnt, 0, (size_t)n_ranges * 4, st));
@@ -1052,22 +1122,11 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums);
     FIC_CHECK_LAUNCH(h, "bf_rangesum_kernel");
 
-    double prescan_fraction = 0.0;
-    // 2. upper bounds: exact scan of a coarse sub-lattice (~1000 positions per range), seeds the range states
+    // 2. range states: all eligible in natural order, nothing known yet (probe: same, thresholds stay +inf)
     if (!probe) {
-        double want_positions = 250.0;   // measured on B200: a sparser pre-scan costs less than the extra survivors it causes
-        if (const char* e = getenv("FIC_PRESCAN_POSITIONS")) want_positions = atof(e) > 1.0 ? atof(e) : want_positions;  // tuning knob
-        int S = (int)floor(sqrt((double)NP / want_positions) + 0.5);
-        if (S < 1) S = 1;
-        prescan_fraction = (double)cdiv(PH, S) * cdiv(PW, S) / (double)NP;
-        h->prof_suppress = true;  // fic_profile times the screen kernel on this path, not the helper scans
-        int rc_pre = bf_exact_scan8(h, d_img, H, W, S, S, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, pre_idx, pre_so, pre_R, st);
-        h->prof_suppress = false;
-        FIC_TRY(rc_pre);
-        bf_threshold_kernel<<<1, 1024, 0, st>>>(rsums, PW, range_begin, n_ranges, pre_idx, pre_so, pre_R, state, tau, fallback, ctrl, tau_pad);
-        FIC_CHECK_LAUNCH(h, "bf_threshold_kernel");
+        bf_init_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, seed_best, ctrl, tau_pad);
+        FIC_CHECK_LAUNCH(h, "bf_init_kernel");
     } else {
-        // probe: every range eligible in natural order, infinite thresholds
         bf_probe_state_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, ctrl, tau_pad);
         FIC_CHECK_LAUNCH(h, "bf_probe_state_kernel");
     }
@@ -1089,15 +1148,39 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         attr_set = true;
     }
     ScreenParams sp;
     sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
     sp.dump = probe;
+    sp.seed_best = nullptr;
     sp.err_flag = ctrl + 2;
     {
         const char* dbg = getenv("FIC_SCREEN_DEBUG");  // kernel timing experiments only; records are wrong when set
         sp.debug_mode = dbg ? atoi(dbg) : 0;
+    }
+    // 4a. seed round: the GEMM ranks the lattice candidates per range (no thresholds exist yet), the best one and
+    // position 0 are scored exactly and give every range its first upper bound
+    if (!probe) {
+        bf_seed_gather_kernel<<<cdiv(n_seed_pad, 128), 128, 0, st>>>(poolA, poolAx, hk, PW, seed_S, seed_gx, n_seed, n_seed_pad, seedA, seedAx, seedhk);
+        FIC_CHECK_LAUNCH(h, "bf_seed_gather_kernel");
+        CUtensorMap mapS, mapSx;
+        FIC_TRY(make_map(&mapS, seedA, (uint64_t)n_seed_pad, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
+        FIC_TRY(make_map(&mapSx, seedAx, (uint64_t)n_seed_pad, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
+        ScreenParams ss = sp;
+        ss.hk = seedhk; ss.NP = n_seed; ss.n_tiles = n_seed_pad / BM; ss.m_cur = 1; ss.r_prev = 0;
+        ss.n_round_tiles = ss.n_tiles; ss.window_tiles = ss.n_tiles; ss.seed_best = seed_best;
+        {
+            ProfScope prof(h, st);
+            bf_screen_kernel<5><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapSx, mapB, mapBx, ss);
+        }
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
+        bf_seed_list_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(seed_best, n_ranges, PW, seed_S, seed_gx, cnt, list, cap);
+        FIC_CHECK_LAUNCH(h, "bf_seed_list_kernel");
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0,
+                                                    d_idx, d_so, d_R);
+        FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
     // Round plan: nested strides m_1 > m_2 > ... > 1 over the candidate tiles.  A round's survivor count per range is
     // about (fraction screened now) / (fraction scored exactly before), so each round may look at ~128x more candidates
@@ -1106,13 +1189,15 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     if (probe || n_tiles < 64) {
         strides.push_back(1);
     } else {
-        double f_prev = prescan_fraction > 0.0 ? prescan_fraction : 1e-3;
+        double f_prev = (double)n_seed / (double)NP;
+        int growth = 16;
+        if (const char* e = getenv("FIC_ROUND_GROWTH")) growth = atoi(e) >= 2 ? atoi(e) : growth;  // tuning knob
         int m = 1;
-        while (1.0 / m > 128.0 * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
+        while (1.0 / m > (double)growth * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
         for (;;) {
             strides.push_back(m);
             if (m == 1) break;
-            m = m / 128 > 1 ? m / 128 : 1;
+            m = m / growth > 1 ? m / growth : 1;
         }
     }
     sp.window_tiles = (64 << 20) / (BM * (KMAIN + KEXT) * 2);   // 64 MiB of pool per window: stays in the 126 MB L2
@@ -1120,8 +1205,8 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         sp.m_cur = strides[r];
         sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
         sp.n_round_tiles = cdiv(n_tiles, strides[r]) - (r == 0 ? 0 : cdiv(n_tiles, strides[r - 1]));
-        if (r > 0) {
-            bf_retau_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(state, ctrl, tau);
+        if (!probe) {
+            bf_retau_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(state, ctrl, tau, fallback);
             FIC_CHECK_LAUNCH(h, "bf_retau_kernel");
         }
         int grid = probe ? 1 : h->num_sms;
