@@ -332,6 +332,44 @@ __device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const floa
     }
 }
 
+// Two chunks at once (both already in registers, no load depends on them): eight independent reductions, one vote.
+template <bool APPEND>
+__device__ __forceinline__ void screen_pair(const uint32_t (&va)[32], const uint32_t (&vb)[32], const float* theta,
+                                            const ScreenParams& p, int slot0, int my_cand, WarpQueue* q, uint32_t& qn, int lane)
+{
+    float m[8];
+    bool any = false;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+        const uint32_t* v = g < 4 ? va + g * 8 : vb + (g - 4) * 8;
+        m[g] = fabsf(__uint_as_float(v[0]));
+#pragma unroll
+        for (int i = 1; i < 8; ++i) m[g] = fmaxf(m[g], fabsf(__uint_as_float(v[i])));
+        any |= m[g] >= theta[g];
+    }
+    if (!APPEND) {
+        if (any && m[0] == 1.2345e-30f) p.cnt[0] = 1;
+        return;
+    }
+    if (__any_sync(0xffffffffu, any)) {   // warp-uniform from here on
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            const bool hit = m[g] >= theta[g];
+            const unsigned mask = __ballot_sync(0xffffffffu, hit);
+            if (mask) {
+                if (hit) {
+                    const uint32_t* v = g < 4 ? va + g * 8 : vb + (g - 4) * 8;
+                    unsigned m8 = 0;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) m8 |= (fabsf(__uint_as_float(v[i])) >= theta[g] ? 1u : 0u) << i;
+                    q->e[qn + __popc(mask & ((1u << lane) - 1u))] = make_uint2(((uint32_t)(slot0 + g) << 8) | m8, (uint32_t)my_cand);
+                }
+                qn += __popc(mask);
+            }
+        }
+    }
+}
+
 // ---- the screen ---------------------------------------------------------------------------------------------
 // MODE 0 = production; MODE 1 = probe (dump raw accumulators of group 0); MODE 2 / 3 = timing experiments selected by
 // FIC_SCREEN_DEBUG (2: TMEM loads but no screening, 3: no epilogue work at all) -- their results are wrong on purpose.
@@ -510,6 +548,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
                     // one per range; it is scored exactly afterwards and provides the first upper bound.
                     const float den = my_cand < p.NP ? p.hk[my_cand].y : 0.f;
+                    const float inv64 = den > 0.f ? 64.f / den : 0.f, den1024 = den * (1.0f / 1024.0f);
                     uint32_t vs[32];
                     mbar_wait(my_tfull, aph, p.err_flag, 6);
                     tcgen05_fence_after();
@@ -521,8 +560,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                             float m = fabsf(__uint_as_float(vs[g * 8]));
 #pragma unroll
                             for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(vs[g * 8 + i])));
-                            float gain = 0.f;
-                            if (den > 0.f) gain = 256.f * m <= den ? 64.f * m * m / den : 0.5f * m - den * (1.0f / 1024.0f);
+                            const float gain = 256.f * m <= den ? m * m * inv64 : 0.5f * m - den1024;   // den == 0: m == 0
                             const uint32_t bits = gain > 0.f ? __float_as_uint(gain) : 0u;
                             const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
                             if (wmax != 0u) {
@@ -591,8 +629,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     tcgen05_fence_before();
                     __syncwarp();
                     if (lane0) mbar_arrive(my_tempty);
-                    if (SCREEN) screen_chunk<MODE == 0>(va, theta + 8, p, slot0 + 8, my_cand, queue, qn, lane);
-                    if (SCREEN) screen_chunk<MODE == 0>(vb, theta + 12, p, slot0 + 12, my_cand, queue, qn, lane);
+                    if (SCREEN) screen_pair<MODE == 0>(va, vb, theta + 8, p, slot0 + 8, my_cand, queue, qn, lane);
                     if (!SCREEN && (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u)) p.cnt[0] = 1;
                 }
                 aph ^= 1;
