@@ -113,7 +113,7 @@ struct fic_handle {
     // decoders
     DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red;
     // quadtree / hv
-    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux;
+    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part;
 };
 
 static inline cudaStream_t fic_stream(fic_handle* h, void* s) { return s ? (cudaStream_t)s : h->own_stream; }

@@ -179,7 +179,8 @@ __device__ __forceinline__ void te_init(TeBest& b)
     b.s = 0.0; b.o = 0.0;
     b.di = b.dj = b.orient = b.rot = b.qs = b.qo = 0;
 }
-__device__ void te_block_reduce(TeBest& b, int32_t* __restrict__ rec6, double* __restrict__ vals3)
+__device__ void te_block_reduce(TeBest& b, int32_t* __restrict__ rec6, double* __restrict__ vals3,
+                                unsigned long long* __restrict__ seq_out = nullptr)
 {
     __shared__ double sR[TE_THREADS / 32];
     __shared__ unsigned long long sSeq[TE_THREADS / 32];
@@ -207,10 +208,12 @@ __device__ void te_block_reduce(TeBest& b, int32_t* __restrict__ rec6, double* _
             for (int k = 0; k < 6; ++k) rec6[k] = 0;
             vals3[0] = 0.0; vals3[1] = 0.0;
             vals3[2] = __longlong_as_double(0x7ff0000000000000ll);
+            if (seq_out) *seq_out = ~0ull;
         }
     } else if (tid == winner) {
         rec6[0] = b.di; rec6[1] = b.dj; rec6[2] = b.orient; rec6[3] = b.rot; rec6[4] = b.qs; rec6[5] = b.qo;
         vals3[0] = b.s; vals3[1] = b.o; vals3[2] = b.R;
+        if (seq_out) *seq_out = b.seq;
     }
 }
 
@@ -300,20 +303,40 @@ qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __rest
 }
 
 // ---- HV domain search (hvv2/encoder.py:97-126) -----------------------------------------------------
-__global__ void __launch_bounds__(TE_THREADS)
-hv_search_kernel(const uint8_t* __restrict__ img, int H, int W, const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/,
-                 double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ rec, double* __restrict__ vals)
+// 2x2-pooled image at every pixel offset: Dp[y][x] = (img[y][x] + img[y][x+1] + img[y+1][x] + img[y+1][x+1]) * 0.25,
+// exact in float32 (the reference's average_subsample of a domain block reads every second entry of it).
+__global__ void hv_pool_kernel(const uint8_t* __restrict__ img, int H, int W, float* __restrict__ Dp)
 {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W - 1 || y >= H - 1) return;
+    const uint8_t* p = img + (size_t)y * W + x;
+    Dp[(size_t)y * (W - 1) + x] = __fmul_rn((float)((int)p[0] + p[1] + p[W] + p[W + 1]), 0.25f);
+}
+
+// One rectangle per blockIdx.x; its candidate list (domain position x 4 isometries, scan order = seq) is cut into
+// gridDim.y contiguous chunks so that the deep, narrow levels of the tree (a handful of rectangles) still fill the
+// GPU.  Each CTA writes the first minimum of its chunk; hv_pick_kernel merges the chunks with the same rule.
+// The three sums run in the reference's order (row-major over the oriented block, float32, no FMA).
+__global__ void __launch_bounds__(TE_THREADS)
+hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
+                 const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
+                 int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs, int smem_px)
+{
+    extern __shared__ float s_range[];   // the rectangle's pixels (when they fit)
     __shared__ float s_rs, s_sqr;
     const int tid = threadIdx.x;
     const int ri = rects[4 * blockIdx.x], rj = rects[4 * blockIdx.x + 1], w = rects[4 * blockIdx.x + 2],
               hgt = rects[4 * blockIdx.x + 3];
     const int nn = w * hgt;
+    const bool in_smem = nn <= smem_px;
+    if (in_smem)
+        for (int t = tid; t < nn; t += TE_THREADS) s_range[t] = (float)img[(size_t)(ri + t / w) * W + rj + t % w];
+    __syncthreads();
     if (tid == 0) {
         float rs = 0.f, sq = 0.f;
-        for (int t = 0; t < nn; ++t) rs = __fadd_rn(rs, (float)img[(size_t)(ri + t / w) * W + rj + t % w]);
         for (int t = 0; t < nn; ++t) {
-            float v = (float)img[(size_t)(ri + t / w) * W + rj + t % w];
+            const float v = in_smem ? s_range[t] : (float)img[(size_t)(ri + t / w) * W + rj + t % w];
+            rs = __fadd_rn(rs, v);
             sq = __fadd_rn(sq, __fmul_rn(v, v));
         }
         s_rs = rs;
@@ -323,33 +346,107 @@ hv_search_kernel(const uint8_t* __restrict__ img, int H, int W, const int32_t* _
     const float rs = s_rs, sqr = s_sqr;
     const int ndi = H - 2 * hgt > 0 ? (H - 2 * hgt + hgt - 1) / hgt : 0;  // range(0, H-2h, h): exclusive
     const int ndj = W - 2 * w > 0 ? (W - 2 * w + w - 1) / w : 0;
-    const long long total = (long long)ndi * ndj * 4;
+    const long long npos = (long long)ndi * ndj;
+    const long long per = (npos + gridDim.y - 1) / gridDim.y;
+    const long long p0 = per * blockIdx.y, p1 = p0 + per < npos ? p0 + per : npos;
+    const int PW = W - 1;
     TeBest best;
     te_init(best);
-    for (long long c = tid; c < total; c += TE_THREADS) {
-        const int iso = (int)(c & 3);
-        const long long pos = c >> 2;
+    // One thread takes the four isometries of a domain position together: candidate index c = pos * 4 + iso with
+    // iso = orient * 2 + (rot == 2); the four traversals read the block from its four corners (fic_iso_hv: rot180
+    // flips rows and columns, flipud flips the rows again), which gives twelve independent float chains per thread.
+    for (long long pos = p0 + tid; pos < p1; pos += TE_THREADS) {
         const int di = (int)(pos / ndj) * hgt, dj = (int)(pos % ndj) * w;
-        const int orient = iso >> 1, rot = (iso & 1) * 2;
-        float ds = 0.f, sds = 0.f, ab = 0.f;
-        for (int i = 0; i < hgt; ++i)
-            for (int j = 0; j < w; ++j) {
-                int sa, sb;
-                fic_iso_hv(orient, rot, hgt, w, i, j, sa, sb);
-                const uint8_t* p = img + (size_t)(di + 2 * sa) * W + dj + 2 * sb;
-                float d = __fmul_rn((float)((int)p[0] + p[1] + p[W] + p[W + 1]), 0.25f);
-                float r = (float)img[(size_t)(ri + i) * W + rj + j];
-                ds = __fadd_rn(ds, d);
-                sds = __fadd_rn(sds, __fmul_rn(d, d));
-                ab = __fadd_rn(ab, __fmul_rn(d, r));
+        const float* top = Dp + (size_t)di * PW + dj;                       // row 0 of the pooled block
+        const float* bot = top + (size_t)(2 * (hgt - 1)) * PW;              // its last row
+        const int last = 2 * (w - 1);
+        float ds0 = 0.f, sq0 = 0.f, ab0 = 0.f;   // iso 0: identity               rows down, columns forward
+        float ds1 = 0.f, sq1 = 0.f, ab1 = 0.f;   // iso 1: rot180                 rows up,   columns backward
+        float ds2 = 0.f, sq2 = 0.f, ab2 = 0.f;   // iso 2: flipud                 rows up,   columns forward
+        float ds3 = 0.f, sq3 = 0.f, ab3 = 0.f;   // iso 3: flipud after rot180    rows down, columns backward
+        int t = 0;
+        for (int i = 0; i < hgt; ++i) {
+            const float* rd = top + (size_t)(2 * i) * PW;
+            const float* ru = bot - (size_t)(2 * i) * PW;
+            for (int j = 0; j < w; ++j, ++t) {
+                const float r = in_smem ? s_range[t] : (float)img[(size_t)(ri + i) * W + rj + j];
+                const float d0 = rd[2 * j], d1 = ru[last - 2 * j], d2 = ru[2 * j], d3 = rd[last - 2 * j];
+                ds0 = __fadd_rn(ds0, d0); sq0 = __fadd_rn(sq0, __fmul_rn(d0, d0)); ab0 = __fadd_rn(ab0, __fmul_rn(d0, r));
+                ds1 = __fadd_rn(ds1, d1); sq1 = __fadd_rn(sq1, __fmul_rn(d1, d1)); ab1 = __fadd_rn(ab1, __fmul_rn(d1, r));
+                ds2 = __fadd_rn(ds2, d2); sq2 = __fadd_rn(sq2, __fmul_rn(d2, d2)); ab2 = __fadd_rn(ab2, __fmul_rn(d2, r));
+                ds3 = __fadd_rn(ds3, d3); sq3 = __fadd_rn(sq3, __fmul_rn(d3, d3)); ab3 = __fadd_rn(ab3, __fmul_rn(d3, r));
             }
-        QScore sc = fic_q_score(nn, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
-        if (fic_better(sc.R, (unsigned long long)c, best.R, best.seq)) {
-            best.R = sc.R; best.seq = c; best.s = sc.s; best.o = sc.o; best.qs = sc.qs; best.qo = sc.qo;
-            best.di = di; best.dj = dj; best.orient = orient; best.rot = rot;
+        }
+        const float dsv[4] = {ds0, ds1, ds2, ds3}, sqv[4] = {sq0, sq1, sq2, sq3}, abv[4] = {ab0, ab1, ab2, ab3};
+#pragma unroll
+        for (int iso = 0; iso < 4; ++iso) {
+            const unsigned long long c = (unsigned long long)pos * 4ull + (unsigned)iso;
+            QScore sc = fic_q_score(nn, rs, sqr, dsv[iso], sqv[iso], abv[iso], max_scale, scale_bits, offset_bits);
+            if (fic_better(sc.R, c, best.R, best.seq)) {
+                best.R = sc.R; best.seq = c; best.s = sc.s; best.o = sc.o; best.qs = sc.qs; best.qo = sc.qo;
+                best.di = di; best.dj = dj; best.orient = iso >> 1; best.rot = (iso & 1) * 2;
+            }
         }
     }
-    te_block_reduce(best, rec + 6 * (size_t)blockIdx.x, vals + 3 * (size_t)blockIdx.x);
+    const size_t slot = (size_t)blockIdx.x * gridDim.y + blockIdx.y;
+    te_block_reduce(best, rec + 6 * slot, vals + 3 * slot, seqs ? seqs + slot : nullptr);
+}
+
+// merge the chunk winners of every rectangle: first strict minimum in scan order
+__global__ void hv_pick_kernel(const int32_t* __restrict__ prec, const double* __restrict__ pvals,
+                               const unsigned long long* __restrict__ pseq, int count, int S, int32_t* __restrict__ rec,
+                               double* __restrict__ vals)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    int bs = 0;
+    double bR = pvals[3 * ((size_t)k * S) + 2];
+    unsigned long long bq = pseq[(size_t)k * S];
+    for (int s = 1; s < S; ++s) {
+        const double R = pvals[3 * ((size_t)k * S + s) + 2];
+        const unsigned long long q = pseq[(size_t)k * S + s];
+        if (fic_better(R, q, bR, bq)) { bR = R; bq = q; bs = s; }
+    }
+    const size_t src = (size_t)k * S + bs;
+    for (int t = 0; t < 6; ++t) rec[6 * (size_t)k + t] = prec[6 * src + t];
+    for (int t = 0; t < 3; ++t) vals[3 * (size_t)k + t] = pvals[3 * src + t];
+}
+
+// launches the search for `count` rectangles already on the device; results in d_rec / d_vals
+static int hv_search_launch(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_rects, int count, int max_px,
+                            int scale_bits, int offset_bits, double max_scale, int32_t* d_rec, double* d_vals, cudaStream_t st)
+{
+    if (count == 0) return FIC_OK;
+    const float* Dp = h->t_hvpool.as<float>();
+    int smem_px = max_px <= 10240 ? max_px : 0;      // range pixels in shared memory when they fit (40 KB)
+    int S = (4 * h->num_sms + count - 1) / count;      // aim at >= 4 CTAs per SM
+    if (S > 64) S = 64;
+    if (S < 1) S = 1;
+    if (S == 1) {
+        hv_search_kernel<<<dim3(count, 1), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
+                                                                                     offset_bits, d_rec, d_vals, nullptr, smem_px);
+        FIC_CHECK_LAUNCH(h, "hv_search_kernel");
+        return FIC_OK;
+    }
+    const size_t np_ = (size_t)count * S;
+    FIC_TRY(h->t_part.reserve(np_ * (6 * sizeof(int32_t) + 3 * sizeof(double) + sizeof(unsigned long long)) + 64));
+    double* pvals = h->t_part.as<double>();
+    unsigned long long* pseq = reinterpret_cast<unsigned long long*>(pvals + 3 * np_);
+    int32_t* prec = reinterpret_cast<int32_t*>(pseq + np_);
+    hv_search_kernel<<<dim3(count, S), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
+                                                                                 offset_bits, prec, pvals, pseq, smem_px);
+    FIC_CHECK_LAUNCH(h, "hv_search_kernel");
+    hv_pick_kernel<<<(count + 127) / 128, 128, 0, st>>>(prec, pvals, pseq, count, S, d_rec, d_vals);
+    FIC_CHECK_LAUNCH(h, "hv_pick_kernel");
+    return FIC_OK;
+}
+
+static int hv_build_pool(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st)
+{
+    FIC_TRY(h->t_hvpool.reserve((size_t)(H - 1) * (W - 1) * sizeof(float) + 64));
+    hv_pool_kernel<<<dim3((W - 1 + 255) / 256, H - 1), 256, 0, st>>>(d_img, H, W, h->t_hvpool.as<float>());
+    FIC_CHECK_LAUNCH(h, "hv_pool_kernel");
+    return FIC_OK;
 }
 
 // ---- HV split (hvv2/encoder.py:45-63, 77-82): one warp per rectangle --------------------------------
@@ -400,9 +497,10 @@ int hv_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int3
                    int offset_bits, double max_scale, int32_t* d_rec, double* d_vals, cudaStream_t st)
 {
     if (count == 0) return FIC_OK;
-    hv_search_kernel<<<count, TE_THREADS, 0, st>>>(d_img, H, W, d_rects, max_scale, scale_bits, offset_bits, d_rec, d_vals);
-    FIC_CHECK_LAUNCH(h, "hv_search_kernel");
-    return FIC_OK;
+    FIC_TRY(hv_build_pool(h, d_img, H, W, st));
+    // the rectangles may live on the device only: 4096 pixels of shared memory cover every rectangle up to 64x64, larger
+    // ones read the image directly
+    return hv_search_launch(h, d_img, H, W, d_rects, count, 4096, scale_bits, offset_bits, max_scale, d_rec, d_vals, st);
 }
 
 // ---- host drivers -----------------------------------------------------------------------------------
@@ -626,6 +724,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
                    int cap, cudaStream_t st)
 {
     FIC_TRY(build_integrals(h, d_img, H, W, st));
+    FIC_TRY(hv_build_pool(h, d_img, H, W, st));
     const long long* I1 = h->t_int1.as<long long>();
     std::vector<HvNode> nodes;
     {
@@ -659,8 +758,9 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
         double* d_vals = h->t_aux.as<double>();
         double* d_splitv = d_vals + (size_t)ns * 3;
         if (ns) {
-            hv_search_kernel<<<ns, TE_THREADS, 0, st>>>(d_img, H, W, d_rects, max_scale, scale_bits, offset_bits, d_rec, d_vals);
-            FIC_CHECK_LAUNCH(h, "hv_search_kernel");
+            int max_px = 1;
+            for (int q = 0; q < ns; ++q) { const HvNode& nd = nodes[search[q]]; if (nd.w * nd.h > max_px) max_px = nd.w * nd.h; }
+            FIC_TRY(hv_search_launch(h, d_img, H, W, d_rects, ns, max_px, scale_bits, offset_bits, max_scale, d_rec, d_vals, st));
         }
         if (np) {
             hv_split_kernel<<<(np * 32 + 127) / 128, 128, 0, st>>>(I1, W + 1, d_rects + (size_t)ns * 4, np, min_w, min_h, d_split, d_splitv);
