@@ -19,96 +19,131 @@
 // brute-force decoder
 // ------------------------------------------------------------------------------------------------
 #define BFD_THREADS 1024
-#define BFD_RANGES_PER_STEP (BFD_THREADS / 64)
+#define BFD_RANGES_PER_STEP (BFD_THREADS / 32)
 
+// One transform in execution order; a step is BFD_RANGES_PER_STEP consecutive records (levels are padded with dst = -1).
+struct BfdRec {
+    int32_t di, dj, iso, dst;   // iso = orient * 4 + rot; dst = pixel index of the target block's corner, -1 = padding
+    double s, o;
+};
+
+// One CTA per plane, one warp per range (two pixels per lane), one CTA-wide barrier per step.  A range may read its own
+// target block, so its reads are separated from its writes by a warp barrier; no other range of the same level touches
+// what it writes (RAW / WAR / WAW edges are all cross-level), so the CTA barrier is only needed between steps.  The
+// record of the next step is fetched while the current one is gathered.
 __global__ void __launch_bounds__(BFD_THREADS)
-bf_decode_kernel(const int32_t* __restrict__ idx, const double* __restrict__ so, const int32_t* __restrict__ order,
-                 const int32_t* __restrict__ level_start, int n_levels, int width, int height, int iterations,
-                 float* __restrict__ buf, uint8_t* __restrict__ out)
+bf_decode_kernel(const BfdRec* __restrict__ recs_all, const long long* __restrict__ step_off, int width, int height,
+                 int iterations, float* __restrict__ buf_all, uint8_t* __restrict__ out_all)
 {
-    const int tid = threadIdx.x;
-    const int sub = tid >> 6, px = tid & 63;
-    const int a = px >> 3, b = px & 7;
-    for (int it = 0; it < iterations; ++it) {
-        for (int lv = 0; lv < n_levels; ++lv) {
-            const int l0 = level_start[lv], l1 = level_start[lv + 1];
-            for (int base = l0; base < l1; base += BFD_RANGES_PER_STEP) {
-                const int e = base + sub;
-                float val = 0.f;
-                int dst = -1;
-                if (e < l1) {
-                    const int k = order[e];
-                    const int range_i = (k / (width / 8)) * 8;   // decoder.py:19
-                    const int range_j = (k % (height / 8)) * 8;  // decoder.py:20 (sic)
-                    const int di = idx[4 * k], dj = idx[4 * k + 1], orient = idx[4 * k + 2], rot = idx[4 * k + 3];
-                    int acc = 0;
-                    if (it > 0) {  // sweep 1 reads the all-zero image
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const BfdRec* recs = recs_all + step_off[blockIdx.x] * BFD_RANGES_PER_STEP;
+    const int n_steps = (int)(step_off[blockIdx.x + 1] - step_off[blockIdx.x]);
+    float* buf = buf_all + (size_t)blockIdx.x * width * height;
+    uint8_t* out = out_all + (size_t)blockIdx.x * width * height;
+    if (n_steps > 0) {
+        BfdRec cur = recs[warp];
+        for (int it = 0; it < iterations; ++it) {
+            for (int st = 0; st < n_steps; ++st) {
+                const int nx = st + 1 < n_steps ? st + 1 : 0;
+                const BfdRec nxt = recs[(size_t)nx * BFD_RANGES_PER_STEP + warp];
+                if (cur.dst >= 0) {
+                    float val[2];
 #pragma unroll
-                        for (int u = 0; u < 2; ++u)
+                    for (int half = 0; half < 2; ++half) {
+                        const int px = lane + 32 * half, a = px >> 3, b = px & 7;
+                        int acc = 0;
+                        if (it > 0) {  // sweep 1 reads the all-zero image
 #pragma unroll
-                            for (int v = 0; v < 2; ++v) {
-                                int sa, sb;
-                                fic_iso_bf(orient, rot, 16, 2 * a + u, 2 * b + v, sa, sb);
-                                acc += __float2int_rz(buf[(size_t)(di + sa) * width + dj + sb]);  // astype(int32), utils.py:22
-                            }
+                            for (int u = 0; u < 2; ++u)
+#pragma unroll
+                                for (int v = 0; v < 2; ++v) {
+                                    int sa, sb;
+                                    fic_iso_bf(cur.iso >> 2, cur.iso & 3, 16, 2 * a + u, 2 * b + v, sa, sb);
+                                    acc += __float2int_rz(buf[(size_t)(cur.di + sa) * width + cur.dj + sb]);  // astype(int32), utils.py:22
+                                }
+                        }
+                        val[half] = __double2float_rn(DA(DM(DM((double)acc, 0.25), cur.s), cur.o));
                     }
-                    double v64 = DA(DM(DM((double)acc, 0.25), so[2 * k]), so[2 * k + 1]);
-                    val = __double2float_rn(v64);
-                    dst = (range_i + a) * width + range_j + b;
+                    __syncwarp();  // every read of this range happens before any of its writes
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        const int px = lane + 32 * half;
+                        buf[cur.dst + (px >> 3) * width + (px & 7)] = val[half];
+                    }
                 }
-                __syncthreads();  // every read of this step happens before any write of it
-                if (dst >= 0) buf[dst] = val;
                 __syncthreads();
+                cur = nxt;
             }
         }
     }
+    __syncthreads();
     for (int p = tid; p < width * height; p += BFD_THREADS) out[p] = (uint8_t)__float2int_rz(buf[p]);
 }
 
-int bf_decode_impl(fic_handle* h, const int32_t* h_idx, const int32_t* d_idx, const double* d_so, int n, int width,
-                   int height, int iterations, uint8_t* d_out, cudaStream_t st)
+// h_idx [planes][n][4], h_so [planes][n][2] on the host; d_out [planes][height*width] on the device
+int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double* h_so, int n, int width, int height,
+                   int iterations, uint8_t* d_out, cudaStream_t st)
 {
     const int bw = width / 8, bh = height / 8;
-    // level schedule over 8x8 blocks
-    std::vector<int> last_write((size_t)bw * bh, -1), last_read((size_t)bw * bh, -1), level(n, 0);
-    int n_levels = 0;
-    for (int k = 0; k < n; ++k) {
-        const int wi = k / bw, wj = k % bh;  // block coordinates of the target
-        const int di = h_idx[4 * k], dj = h_idx[4 * k + 1];
-        const int b0i = di / 8, b1i = (di + 15) / 8, b0j = dj / 8, b1j = (dj + 15) / 8;
-        int lv = 0;
-        for (int bi = b0i; bi <= b1i; ++bi)
-            for (int bj = b0j; bj <= b1j; ++bj) lv = std::max(lv, last_write[(size_t)bi * bw + bj] + 1);  // RAW
-        const size_t wb = (size_t)wi * bw + wj;
-        lv = std::max(lv, last_read[wb] + 1);   // WAR (reads of this very range do not count: registered below)
-        lv = std::max(lv, last_write[wb] + 1);  // WAW
-        level[k] = lv;
-        for (int bi = b0i; bi <= b1i; ++bi)
-            for (int bj = b0j; bj <= b1j; ++bj) last_read[(size_t)bi * bw + bj] = std::max(last_read[(size_t)bi * bw + bj], lv);
-        last_write[wb] = lv;
-        n_levels = std::max(n_levels, lv + 1);
+    std::vector<BfdRec> recs;
+    std::vector<long long> step_off(planes + 1, 0);
+    std::vector<int> last_write, last_read, level(n), count, cursor;
+    for (int pl = 0; pl < planes; ++pl) {
+        const int32_t* idx = h_idx + (size_t)pl * n * 4;
+        const double* so = h_so + (size_t)pl * n * 2;
+        // level schedule over 8x8 blocks
+        last_write.assign((size_t)bw * bh, -1);
+        last_read.assign((size_t)bw * bh, -1);
+        int n_levels = 0;
+        for (int k = 0; k < n; ++k) {
+            const int wi = k / bw, wj = k % bh;  // block coordinates of the target
+            const int di = idx[4 * k], dj = idx[4 * k + 1];
+            const int b0i = di / 8, b1i = (di + 15) / 8, b0j = dj / 8, b1j = (dj + 15) / 8;
+            int lv = 0;
+            for (int bi = b0i; bi <= b1i; ++bi)
+                for (int bj = b0j; bj <= b1j; ++bj) lv = std::max(lv, last_write[(size_t)bi * bw + bj] + 1);  // RAW
+            const size_t wb = (size_t)wi * bw + wj;
+            lv = std::max(lv, last_read[wb] + 1);   // WAR (reads of this very range do not count: registered below)
+            lv = std::max(lv, last_write[wb] + 1);  // WAW
+            level[k] = lv;
+            for (int bi = b0i; bi <= b1i; ++bi)
+                for (int bj = b0j; bj <= b1j; ++bj) last_read[(size_t)bi * bw + bj] = std::max(last_read[(size_t)bi * bw + bj], lv);
+            last_write[wb] = lv;
+            n_levels = std::max(n_levels, lv + 1);
+        }
+        // records in (level, range) order, every level padded to whole steps
+        count.assign(n_levels, 0);
+        for (int k = 0; k < n; ++k) count[level[k]]++;
+        cursor.assign(n_levels, 0);
+        long long total = 0;
+        for (int l = 0; l < n_levels; ++l) {
+            cursor[l] = (int)total;
+            total += (long long)((count[l] + BFD_RANGES_PER_STEP - 1) / BFD_RANGES_PER_STEP) * BFD_RANGES_PER_STEP;
+        }
+        const size_t base = recs.size();
+        BfdRec pad{};
+        pad.dst = -1;
+        recs.resize(base + (size_t)total, pad);
+        for (int k = 0; k < n; ++k) {
+            BfdRec& r = recs[base + (size_t)cursor[level[k]]++];
+            r.di = idx[4 * k]; r.dj = idx[4 * k + 1]; r.iso = idx[4 * k + 2] * 4 + idx[4 * k + 3];
+            r.dst = (k / bw) * 8 * width + (k % bh) * 8;   // decoder.py:19-20 (sic)
+            r.s = so[2 * k]; r.o = so[2 * k + 1];
+        }
+        step_off[pl + 1] = step_off[pl] + total / BFD_RANGES_PER_STEP;
     }
-    // a range that reads its own target block: its reads precede its write inside one step, which the kernel
-    // guarantees; but a LATER range in the same level must not read that block -- excluded by RAW above.
-    std::vector<int32_t> sched((size_t)n + n_levels + 1);
-    int32_t* level_start = sched.data();
-    int32_t* order = sched.data() + n_levels + 1;
-    std::fill(level_start, level_start + n_levels + 1, 0);
-    for (int k = 0; k < n; ++k) level_start[level[k] + 1]++;
-    for (int l = 0; l < n_levels; ++l) level_start[l + 1] += level_start[l];
-    {
-        std::vector<int32_t> cur(level_start, level_start + n_levels);
-        for (int k = 0; k < n; ++k) order[cur[level[k]]++] = k;
-    }
-    FIC_TRY(h->dec_sched.reserve(sched.size() * sizeof(int32_t) + 16));
-    FIC_TRY(h->pin_b.reserve(sched.size() * sizeof(int32_t) + 16));
-    memcpy(h->pin_b.p, sched.data(), sched.size() * sizeof(int32_t));
-    FIC_TRY(fic_copy_in(h, h->dec_sched.p, h->pin_b.p, sched.size() * sizeof(int32_t), false, st));
-    FIC_TRY(h->dec_img.reserve((size_t)width * height * sizeof(float)));
-    FIC_CUDA(cudaMemsetAsync(h->dec_img.p, 0, (size_t)width * height * sizeof(float), st));
-    const int32_t* d_sched = h->dec_sched.as<int32_t>();
-    bf_decode_kernel<<<1, BFD_THREADS, 0, st>>>(d_idx, d_so, d_sched + n_levels + 1, d_sched, n_levels, width, height,
-                                                iterations, h->dec_img.as<float>(), d_out);
+    const size_t rec_bytes = recs.size() * sizeof(BfdRec), off_bytes = step_off.size() * sizeof(long long);
+    FIC_TRY(h->dec_sched.reserve(rec_bytes + off_bytes + 64));
+    FIC_TRY(h->pin_b.reserve(rec_bytes + off_bytes + 64));
+    memcpy(h->pin_b.p, step_off.data(), off_bytes);
+    const size_t rec_at = (off_bytes + 31) & ~(size_t)31;
+    if (rec_bytes) memcpy((char*)h->pin_b.p + rec_at, recs.data(), rec_bytes);
+    FIC_TRY(fic_copy_in(h, h->dec_sched.p, h->pin_b.p, rec_at + rec_bytes, false, st));
+    FIC_TRY(h->dec_img.reserve((size_t)planes * width * height * sizeof(float)));
+    FIC_CUDA(cudaMemsetAsync(h->dec_img.p, 0, (size_t)planes * width * height * sizeof(float), st));
+    const long long* d_off = h->dec_sched.as<long long>();
+    const BfdRec* d_recs = reinterpret_cast<const BfdRec*>(h->dec_sched.as<char>() + rec_at);
+    bf_decode_kernel<<<planes, BFD_THREADS, 0, st>>>(d_recs, d_off, width, height, iterations, h->dec_img.as<float>(), d_out);
     FIC_CHECK_LAUNCH(h, "bf_decode_kernel");
     // pin_b is reused by the next call: make sure the upload has been consumed
     FIC_CUDA(cudaStreamSynchronize(st));

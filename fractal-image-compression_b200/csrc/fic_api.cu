@@ -245,51 +245,63 @@ int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W,
     return FIC_OK;
 }
 
-int fic_bf_decode(fic_handle* h, const int32_t* idx, const double* so, int n, int width, int height, int iterations,
-                  uint8_t* out, unsigned flags, void* stream)
+static int bf_decode_common(const char* who, fic_handle* h, int planes, const int32_t* idx, const double* so, int n, int width,
+                            int height, int iterations, uint8_t* out, unsigned flags, void* stream)
 {
-    FIC_REQUIRE(h && idx && so && out, "fic_bf_decode: NULL argument");
-    FIC_REQUIRE(n >= 0 && width > 0 && height > 0 && iterations >= 0, "fic_bf_decode: bad sizes");
-    FIC_REQUIRE(width % 8 == 0 && height % 8 == 0, "fic_bf_decode: sides must be multiples of the hard-coded range size 8");
+    FIC_REQUIRE(h && idx && so && out, "%s: NULL argument", who);
+    FIC_REQUIRE(planes >= 1 && n >= 0 && width > 0 && height > 0 && iterations >= 0, "%s: bad sizes", who);
+    FIC_REQUIRE(width % 8 == 0 && height % 8 == 0, "%s: sides must be multiples of the hard-coded range size 8", who);
     FIC_CUDA(cudaSetDevice(h->device));
     cudaStream_t st = fic_stream(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
-    // the level schedule is built on the host from the transforms, so a host copy of idx is needed either way
-    FIC_TRY(h->pin_a.reserve((size_t)n * 4 * sizeof(int32_t) + 16));
-    int32_t* h_idx = h->pin_a.as<int32_t>();
-    const int32_t* d_idx = idx;
-    const double* d_so = so;
+    // the execution schedule is built on the host from the transforms, so host copies are needed either way
+    const size_t n_all = (size_t)planes * n;
+    const int32_t* h_idx = idx;
+    const double* h_so = so;
     uint8_t* d_out = out;
     if (dev) {
-        FIC_CUDA(cudaMemcpyAsync(h_idx, idx, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        FIC_TRY(h->pin_a.reserve(n_all * (4 * sizeof(int32_t) + 2 * sizeof(double)) + 64));
+        double* ps = h->pin_a.as<double>();
+        int32_t* pi = reinterpret_cast<int32_t*>(ps + n_all * 2);
+        FIC_CUDA(cudaMemcpyAsync(pi, idx, n_all * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        FIC_CUDA(cudaMemcpyAsync(ps, so, n_all * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
         FIC_CUDA(cudaStreamSynchronize(st));
+        h->counters[CNT_D2H] += (int64_t)(n_all * (4 * sizeof(int32_t) + 2 * sizeof(double)));
+        h_idx = pi;
+        h_so = ps;
     } else {
-        memcpy(h_idx, idx, (size_t)n * 4 * sizeof(int32_t));
-        FIC_TRY(h->d_in_a.reserve((size_t)n * 4 * sizeof(int32_t) + 16));
-        FIC_TRY(h->d_in_b.reserve((size_t)n * 2 * sizeof(double) + 16));
-        FIC_TRY(h->d_out_a.reserve((size_t)width * height));
-        FIC_TRY(fic_copy_in(h, h->d_in_a.p, idx, (size_t)n * 4 * sizeof(int32_t), false, st));
-        FIC_TRY(fic_copy_in(h, h->d_in_b.p, so, (size_t)n * 2 * sizeof(double), false, st));
-        d_idx = h->d_in_a.as<int32_t>();
-        d_so = h->d_in_b.as<double>();
+        FIC_TRY(h->d_out_a.reserve((size_t)planes * width * height));
         d_out = h->d_out_a.as<uint8_t>();
     }
-    for (int k = 0; k < n; ++k) {
-        const int32_t* r = h_idx + 4 * k;
+    for (size_t q = 0; q < n_all; ++q) {
+        const int k = (int)(q % (size_t)(n ? n : 1));
+        const int32_t* r = h_idx + 4 * q;
         FIC_REQUIRE(r[0] >= 0 && r[1] >= 0 && r[0] + 16 <= height && r[1] + 16 <= width && (unsigned)r[2] < 2u && (unsigned)r[3] < 4u,
-                    "fic_bf_decode: transform %d (%d,%d,%d,%d) is outside the image", k, r[0], r[1], r[2], r[3]);
+                    "%s: transform %d (%d,%d,%d,%d) is outside the image", who, k, r[0], r[1], r[2], r[3]);
         // decoder.py:19-20 mixes width and height; numpy raises when the 8x8 target slice leaves the image
         const int range_i = (k / (width / 8)) * 8, range_j = (k % (height / 8)) * 8;
         FIC_REQUIRE(range_i + 8 <= height && range_j + 8 <= width,
-                    "fic_bf_decode: transform %d maps to range block (%d,%d) outside the %dx%d image "
-                    "(the reference's index arithmetic, bruteforce/decoder.py:19-20)", k, range_i, range_j, height, width);
+                    "%s: transform %d maps to range block (%d,%d) outside the %dx%d image "
+                    "(the reference's index arithmetic, bruteforce/decoder.py:19-20)", who, k, range_i, range_j, height, width);
     }
-    FIC_TRY(bf_decode_impl(h, h_idx, d_idx, d_so, n, width, height, iterations, d_out, st));
+    FIC_TRY(bf_decode_impl(h, planes, h_idx, h_so, n, width, height, iterations, d_out, st));
     if (!dev) {
-        FIC_TRY(fic_copy_out(h, out, d_out, (size_t)width * height, false, st));
+        FIC_TRY(fic_copy_out(h, out, d_out, (size_t)planes * width * height, false, st));
         FIC_CUDA(cudaStreamSynchronize(st));
     }
     return FIC_OK;
+}
+
+int fic_bf_decode(fic_handle* h, const int32_t* idx, const double* so, int n, int width, int height, int iterations,
+                  uint8_t* out, unsigned flags, void* stream)
+{
+    return bf_decode_common("fic_bf_decode", h, 1, idx, so, n, width, height, iterations, out, flags, stream);
+}
+
+int fic_bf_decode_batch(fic_handle* h, int planes, const int32_t* idx, const double* so, int n, int width, int height,
+                        int iterations, uint8_t* out, unsigned flags, void* stream)
+{
+    return bf_decode_common("fic_bf_decode_batch", h, planes, idx, so, n, width, height, iterations, out, flags, stream);
 }
 
 int fic_average_subsample(fic_handle* h, const double* arr, int h2, int w2, int jit, double* out, unsigned flags, void* stream)

@@ -168,8 +168,8 @@ static inline int fic_check_launch(const char* what)
 int bf_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
                    int range_begin, int range_end, int32_t* d_idx, double* d_so, double* d_R, unsigned flags,
                    cudaStream_t st);
-int bf_decode_impl(fic_handle* h, const int32_t* h_idx, const int32_t* d_idx, const double* d_so, int n, int width,
-                   int height, int iterations, uint8_t* d_out, cudaStream_t st);
+int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double* h_so, int n, int width, int height,
+                   int iterations, uint8_t* d_out, cudaStream_t st);
 int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const double* d_so, int n, int H, int W,
                      int iterations, double stop, int min_it, int max_it, int f32_affine, uint8_t* d_out,
                      int32_t* iters_done, cudaStream_t st);

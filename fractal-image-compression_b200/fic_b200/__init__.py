@@ -54,6 +54,7 @@ SIGNATURES = {
                                        _vp, _vp]),
     "fic_bf_screen_probe": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_bf_decode": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
+    "fic_bf_decode_batch": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_average_subsample": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_qt_encode": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_double, C.c_int, C.c_int, _vp, _vp, C.c_int, _i32p, C.c_uint, _vp]),
@@ -266,6 +267,21 @@ def bf_decode(idx, so, width, height, iterations=32, handle: Handle | None = Non
     out = np.zeros((int(height), int(width)), np.uint8)
     _check(lib().fic_bf_decode(h.ptr, _ptr(idx), _ptr(so), idx.shape[0], int(width), int(height), int(iterations),
                                _ptr(out), 0, None), "fic_bf_decode")
+    return out
+
+
+def bf_decode_batch(idx, so, width, height, iterations=32, handle: Handle | None = None) -> np.ndarray:
+    """idx [planes,n,4], so [planes,n,2] -> uint8 [planes,height,width]; all planes decode concurrently (one CTA each)."""
+    h = handle or default_handle()
+    idx = np.ascontiguousarray(idx, np.int32)
+    so = np.ascontiguousarray(so, np.float64)
+    if idx.ndim != 3 or idx.shape[2] != 4 or so.shape != idx.shape[:2] + (2,):
+        raise ValueError("idx must be [planes,n,4] and so [planes,n,2]")
+    out = np.zeros((idx.shape[0], int(height), int(width)), np.uint8)
+    if idx.shape[0] == 0:
+        return out
+    _check(lib().fic_bf_decode_batch(h.ptr, idx.shape[0], _ptr(idx), _ptr(so), idx.shape[1], int(width), int(height),
+                                     int(iterations), _ptr(out), 0, None), "fic_bf_decode_batch")
     return out
 
 

@@ -81,3 +81,21 @@ def encode_batch(imgs: np.ndarray, encode_image: Callable[[np.ndarray], tuple], 
     dev = device if device is not None else "cpu"
     return (_gather_rows(idx.astype(np.int32), counts, dist, dev), _gather_rows(so, counts, dist, dev),
             _gather_rows(R, counts, dist, dev))
+
+
+def decode_batch(idx: np.ndarray, so: np.ndarray, width: int, height: int,
+                 decode_planes: Callable[[np.ndarray, np.ndarray], np.ndarray], device=None) -> np.ndarray:
+    """Image-parallel decode of a batch of records idx[B,n,4], so[B,n,2]: each rank decodes its share of planes in one
+    call (`decode_planes(idx_share, so_share)` -> uint8 [b,height,width]; fic_b200.bf_decode_batch on a GPU rank, which
+    runs the planes concurrently), the pixels are gathered.  Returns uint8 [B,height,width] on every rank."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    B = idx.shape[0]
+    mine = image_shares(B, rank, world)
+    if mine:
+        local = np.asarray(decode_planes(idx[mine[0]:mine[-1] + 1], so[mine[0]:mine[-1] + 1]), np.uint8)
+    else:
+        local = np.zeros((0, height, width), np.uint8)
+    counts = [len(image_shares(B, r, world)) for r in range(world)]
+    dev = device if device is not None else "cpu"
+    return _gather_rows(local, counts, dist, dev)

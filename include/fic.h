@@ -140,6 +140,14 @@ int fic_bf_encode_static(const uint8_t* d_img, int H, int W, int stride_i, int s
 int fic_bf_decode(fic_handle* h, const int32_t* idx, const double* so, int n, int width, int height,
                   int iterations, uint8_t* out, unsigned flags, void* stream);
 
+/*
+ * `planes` independent decodes of equal shape in one launch (one CTA per plane): the colour fan-out of
+ * quadtree/rgb.py-style per-channel coding and image batches (BASELINE.json configs[4]).  No single-call counterpart
+ * in the reference, which loops over Decoder.decode.  idx [planes,n,4], so [planes,n,2], out uint8 [planes,height,width].
+ */
+int fic_bf_decode_batch(fic_handle* h, int planes, const int32_t* idx, const double* so, int n, int width, int height,
+                        int iterations, uint8_t* out, unsigned flags, void* stream);
+
 /* ---- pooling --------------------------------------------------------------------------- */
 /* utils.average_subsample (utils.py:13-25, jit=0: int32-truncating, float64 result) and
  * utils.average_subsample_jit (utils.py:27-34, jit=1: float32 adds).  arr float64 [h2,w2] ->

@@ -88,6 +88,10 @@ emit(config=4, what="bruteforce-jit synthetic 4096x4096, all 262144 ranges on ON
 # config 5: one 1024x1024 RGB image, per channel brute force (batch of 256 = 256x this, image-parallel)
 rgb = np.stack([synthetic_image(100 + k, 1024, 1024) for k in range(3)])
 t_img, out = timed(lambda: fic_b200.bf_encode_batch(rgb, mode=1), reps=2)
-t_dec3, _ = timed(lambda: [fic_b200.bf_decode(out[0][k], out[1][k], 1024, 1024, 32) for k in range(3)], reps=1)
+t_dec3, dec3 = timed(lambda: fic_b200.bf_decode_batch(out[0], out[1], 1024, 1024, 32), reps=1)
+# a rank's share of the 256-image batch on 8 GPUs: 32 images = 96 planes, decoded by one batched call
+share_idx = np.concatenate([out[0]] * 32); share_so = np.concatenate([out[1]] * 32)
+t_dec96, dec96 = timed(lambda: fic_b200.bf_decode_batch(share_idx, share_so, 1024, 1024, 32), reps=1)
 emit(config=5, what="one synthetic 1024x1024x3 image, 3 planes brute force", encode_s=t_img, decode_s=t_dec3,
-     matches_per_s=3 * 16384 * 1008 * 1008 * 8 / t_img, batch_of_256_on_8_gpus_estimate_s=256 * (t_img + t_dec3) / 8)
+     decode_96_planes_s=t_dec96, planes_equal=bool(np.array_equal(dec96[3:6], dec3)),
+     matches_per_s=3 * 16384 * 1008 * 1008 * 8 / t_img, batch_of_256_on_8_gpus_estimate_s=32 * t_img + t_dec96)

@@ -178,6 +178,22 @@ def test_encode_decode_round_trip_psnr(fic, images, golden):
     assert abs(psnr - 29.96704623) < 1e-6
 
 
+def test_batch_decode_planes_run_concurrently_and_match(fic, orc):
+    """fic_bf_decode_batch: independent planes in one launch, each equal to its own single decode and to the oracle;
+    mixes contractive (JIT) and non-contractive (NumPy mode) transforms and an odd number of sweeps."""
+    imgs = [synthetic_image(30 + k, 64, 64) for k in range(5)]
+    recs = [orc.bf_encode(im, mode=k % 2) for k, im in enumerate(imgs)]
+    idx = np.stack([r[0] for r in recs]); so = np.stack([r[1] for r in recs])
+    for it in (1, 2, 9):
+        got = fic.bf_decode_batch(idx, so, 64, 64, it)
+        for k in range(5):
+            assert np.array_equal(got[k], orc.bf_decode(idx[k], so[k], 64, 64, it))
+            assert np.array_equal(got[k], fic.bf_decode(idx[k], so[k], 64, 64, it))
+    assert fic.bf_decode_batch(idx[:0], so[:0], 64, 64, 3).shape == (0, 64, 64)
+    with pytest.raises(ValueError):
+        fic.bf_decode_batch(idx, so[:, :10], 64, 64, 3)
+
+
 def test_batch_entry_point(fic, orc):
     imgs = np.stack([synthetic_image(20 + k, 48, 48) for k in range(3)])
     idx, so, R = fic.bf_encode_batch(imgs)

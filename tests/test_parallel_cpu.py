@@ -30,7 +30,7 @@ WORKER = textwrap.dedent('''
     import os, sys
     sys.path.insert(0, {pkg!r}); sys.path.insert(0, {root!r})
     import numpy as np, torch.distributed as dist
-    from fic_b200.parallel import encode_sharded, encode_batch
+    from fic_b200.parallel import encode_sharded, encode_batch, decode_batch
     from oracle import oracle as orc
     dist.init_process_group("gloo")
     rng = np.random.default_rng(3)
@@ -43,6 +43,9 @@ WORKER = textwrap.dedent('''
     idx, so, R = encode_batch(imgs, lambda im: orc.bf_encode(im, mode=1, nthreads=1))
     for b in range(3):
         assert np.array_equal(idx[b], want[b][0]) and np.array_equal(so[b], want[b][1]) and np.array_equal(R[b], want[b][2])
+    dec = decode_batch(idx, so, 32, 32, lambda i, s: np.stack([orc.bf_decode(a, b_, 32, 32, 8) for a, b_ in zip(i, s)]))
+    for b in range(3):
+        assert np.array_equal(dec[b], orc.bf_decode(want[b][0], want[b][1], 32, 32, 8)), "batch decode != single"
     dist.destroy_process_group()
     print("rank", dist.get_rank() if dist.is_initialized() else os.environ["RANK"], "ok")
 ''')
