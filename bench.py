@@ -339,7 +339,7 @@ def run_ours(args):
         if world == 1 and not args.no_cpu:
             from oracle import oracle as orc
             cores = host_cores()
-            sample = max(8 * cores, 32)
+            sample = max(24 * cores, 64)   # about 10-20 s of host work
             cpu_sample(img, max(cores, 4))
             v, dt, cores, start = cpu_sample(img, sample)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
