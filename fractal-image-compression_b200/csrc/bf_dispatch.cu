@@ -8,7 +8,7 @@ int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, in
                    cudaStream_t st);
 int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
                      int range_begin, int n_ranges, int32_t* d_idx, double* d_so, double* d_R, cudaStream_t st);
-int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_ranges, int32_t* d_idx,
                       double* d_so, double* d_R, unsigned flags, cudaStream_t st);
 bool bf_screen_applicable(int H, int W);
 
@@ -21,8 +21,8 @@ int bf_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int range,
     const long long nq = (long long)(H - 16 > 0 ? (H - 16 + si - 1) / si : 0) * (W - 16 > 0 ? (W - 16 + sj - 1) / sj : 0);
     FIC_REQUIRE(nq * 8 < 0xffffffffll, "fic_bf_encode: %lld candidates per range exceed the 32-bit scan index", nq * 8);
     FIC_TRY(bf_prepare8(h, d_img, H, W, st));
-    const bool screen = mode == FIC_BF_MODE_JIT && si == 1 && sj == 1 && !(flags & FIC_BF_EXACT_ONLY) &&
+    const bool screen = si == 1 && sj == 1 && !(flags & FIC_BF_EXACT_ONLY) &&
                         bf_screen_applicable(H, W);
-    if (screen) return bf_screen_encode8(h, d_img, H, W, range_begin, n, d_idx, d_so, d_R, flags, st);
+    if (screen) return bf_screen_encode8(h, d_img, H, W, mode, range_begin, n, d_idx, d_so, d_R, flags, st);
     return bf_exact_scan8(h, d_img, H, W, si, sj, mode, range_begin, n, nullptr, d_idx, d_so, d_R, st);
 }

@@ -715,7 +715,9 @@ struct RangeState {
 };
 
 // sum and sum of squares of every range of the slice, one warp per range (the serial consumers below only read them)
-__global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, uint2* __restrict__ sums)
+// sqw = the NumPy encoder's sum of squares: bf_encoder.py:33 squares the uint8 pixels in uint8, every term wraps mod 256
+__global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, uint2* __restrict__ sums,
+                                   uint32_t* __restrict__ sqw)
 {
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (slot >= n_ranges) return;
@@ -723,19 +725,25 @@ __global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int r
     const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
     const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
     const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
-    unsigned sm = r0 + r1, q = r0 * r0 + r1 * r1;
+    unsigned sm = r0 + r1, q = r0 * r0 + r1 * r1, qw = ((r0 * r0) & 255u) + ((r1 * r1) & 255u);
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) { sm += __shfl_xor_sync(0xffffffffu, sm, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
-    if (lane == 0) sums[slot] = make_uint2(sm, q);
+    for (int off = 16; off > 0; off >>= 1) {
+        sm += __shfl_xor_sync(0xffffffffu, sm, off);
+        q += __shfl_xor_sync(0xffffffffu, q, off);
+        qw += __shfl_xor_sync(0xffffffffu, qw, off);
+    }
+    if (lane == 0) { sums[slot] = make_uint2(sm, q); sqw[slot] = qw; }
 }
 
 // ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
 // Every range of the slice gets a slot in natural order.  Nothing is known about the winners yet: R = +inf, no
 // candidate, thresholds +inf (nothing passes); constant ranges are flagged, they are decided by the seed list alone
 // (every candidate scores R = 0 exactly, the first in scan order -- position 0, isometry 0 -- wins).
-__global__ void bf_init_kernel(const uint2* __restrict__ sums, int range_begin, int n_ranges, RangeState* __restrict__ state,
-                               float2* __restrict__ tau, unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl,
-                               int tau_pad)
+// NumPy mode: the reference's R carries the wrapped sum of squares, R_ref = R_true - (q - qw)/64 for every candidate of
+// the range alike; the bound is on R_true, so the shift goes into the threshold numerator once.
+__global__ void bf_init_kernel(const uint2* __restrict__ sums, const uint32_t* __restrict__ sqw, int mode, int range_begin,
+                               int n_ranges, RangeState* __restrict__ state, float2* __restrict__ tau,
+                               unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad)
 {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k == 0) { ctrl[0] = n_ranges; ctrl[1] = 0; }
@@ -750,6 +758,7 @@ __global__ void bf_init_kernel(const uint2* __restrict__ sums, int range_begin, 
         RangeState st;
         st.R = __longlong_as_double(0x7ff0000000000000ll); st.s = 0.0; st.o = 0.0;
         st.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
+        if (mode == FIC_BF_MODE_NUMPY) st.TA0 -= (double)(q - (long long)sqw[k]);
         st.seq = ~0ull; st.ridx = range_begin + k; st.flags = A64 == 0 ? 2 : 0;
         st.rsum = (int)s; st.pad_ = 0;
         state[k] = st;
@@ -891,7 +900,7 @@ struct RescoreBest {
 
 __device__ __forceinline__ void rescore_entry(uint32_t ent, const float (*rvw)[65], double rs, double sqr,
                                               const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
-                                              const float* __restrict__ sdd, int NP, RescoreBest& b)
+                                              const float* __restrict__ sdd, int NP, int mode, RescoreBest& b)
 {
     const int t = ent & 7;
     const int p = ent >> 3;
@@ -912,8 +921,13 @@ __device__ __forceinline__ void rescore_entry(uint32_t ent, const float (*rvw)[6
         }
     }
     const float dsf = __fmul_rn((float)sd, 0.25f);
-    BfScore sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
-                                 (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
+    BfScore sc;
+    if (mode == FIC_BF_MODE_JIT)
+        sc = fic_bfjit_score(64.0, 0.015625, rs, sqr, (double)dsf, (double)sdd[(size_t)t * NP + p],
+                             (double)__fmul_rn(dsf, dsf), DM((double)x, 0.25));
+    else   // bf_encoder.py:56-71: float64 throughout, exact sums (sq4 = sum of D4^2 sits behind sd4)
+        sc = fic_bfnp_score(64.0, 0.015625, rs, sqr, DM((double)sd, 0.25), DM((double)sd4[(size_t)NP + p], 0.0625),
+                            DM((double)x, 0.25));
     if (fic_better(sc.R, (unsigned long long)ent, b.R, b.seq)) { b.R = sc.R; b.seq = ent; b.s = sc.s; b.o = sc.o; }
 }
 
@@ -958,7 +972,7 @@ __global__ void __launch_bounds__(RESCORE_WARPS * 32)
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
-                  int32_t* __restrict__ fallback, int emit, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                  int32_t* __restrict__ fallback, int emit, int mode, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
                   double* __restrict__ out_R)
 {
     __shared__ float rv[RESCORE_WARPS][8][65];   // inverse-transformed range per isometry, padded against bank conflicts
@@ -990,7 +1004,8 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
             // lane holds range pixels k = lane and k = lane + 32
             const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
             const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
-            unsigned s = r0 + r1, q = r0 * r0 + r1 * r1;
+            unsigned s = r0 + r1;
+            unsigned q = mode == FIC_BF_MODE_JIT ? r0 * r0 + r1 * r1 : ((r0 * r0) & 255u) + ((r1 * r1) & 255u);  // bf_encoder.py:33
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
             const double rs = (double)s, sqr = (double)q;
@@ -1009,7 +1024,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
                 b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
                 if (lane == 0) { b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }  // the running winner competes too
                 for (uint32_t e = lane; e < n; e += 32)
-                    rescore_entry(list[(size_t)slot * cap + e], rv[warp], rs, sqr, poolA, sd4, sdd, NP, b);
+                    rescore_entry(list[(size_t)slot * cap + e], rv[warp], rs, sqr, poolA, sd4, sdd, NP, mode, b);
                 rescore_warp_reduce(b);
                 if (lane == 0) rescore_commit(slot, ridx, b, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
             } else if (lane == 0) {
@@ -1030,7 +1045,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
         b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
         if (threadIdx.x == 0) { const RangeState st = state[bslot]; b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }
         for (uint32_t e = threadIdx.x; e < n; e += RESCORE_WARPS * 32)
-            rescore_entry(list[(size_t)bslot * cap + e], rv[r], rs, sqr, poolA, sd4, sdd, NP, b);
+            rescore_entry(list[(size_t)bslot * cap + e], rv[r], rs, sqr, poolA, sd4, sdd, NP, mode, b);
         rescore_warp_reduce(b);
         if (lane == 0) s_red[warp] = b;
         __syncthreads();
@@ -1088,7 +1103,7 @@ bool bf_screen_applicable(int H, int W)
 
 // `probe` != nullptr: debugging/validation mode -- one column group is run over all tiles with infinite thresholds and
 // the raw accumulators are written to probe[n_tiles*128][256].
-int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_ranges, int32_t* d_idx,
                   double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st)
 {
     const int PW = W - 16, PH = H - 16;
@@ -1108,7 +1123,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     FIC_TRY(h->bf_poolx.reserve((size_t)NP * 16 * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 80 * 2 + 256));
-    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (sizeof(int32_t) + sizeof(uint2) + sizeof(RangeState)) + 512));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (2 * sizeof(int32_t) + sizeof(uint2) + sizeof(RangeState)) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_ctrl.reserve(256));
@@ -1140,6 +1155,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
     uint2* rsums = reinterpret_cast<uint2*>(tau + tau_pad);
     int32_t* fallback = reinterpret_cast<int32_t*>(rsums + n_ranges);
+    uint32_t* rsqw = reinterpret_cast<uint32_t*>(fallback + n_ranges);
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
@@ -1156,12 +1172,12 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
-    bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums);
+    bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums, rsqw);
     FIC_CHECK_LAUNCH(h, "bf_rangesum_kernel");
 
     // 2. range states: all eligible in natural order, nothing known yet (probe: same, thresholds stay +inf)
     if (!probe) {
-        bf_init_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, seed_best, ctrl, tau_pad);
+        bf_init_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, rsqw, mode, range_begin, n_ranges, state, tau, seed_best, ctrl, tau_pad);
         FIC_CHECK_LAUNCH(h, "bf_init_kernel");
     } else {
         bf_probe_state_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, ctrl, tau_pad);
@@ -1215,7 +1231,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
         bf_seed_list_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(seed_best, n_ranges, PW, seed_S, seed_gx, cnt, list, cap);
         FIC_CHECK_LAUNCH(h, "bf_seed_list_kernel");
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
@@ -1259,7 +1275,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
         if (probe) return FIC_OK;
         // 5. exact rescoring of this round's survivors, merged into the range states
         const int emit = r + 1 == strides.size();
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }
@@ -1279,15 +1295,15 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int range_b
     if (n_fb > 0) {
         if (flags & FIC_BF_NO_FALLBACK) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
         h->prof_suppress = true;
-        int rc_fb = bf_exact_scan8(h, d_img, H, W, 1, 1, FIC_BF_MODE_JIT, range_begin, n_fb, fallback, d_idx, d_so, d_R, st);
+        int rc_fb = bf_exact_scan8(h, d_img, H, W, 1, 1, mode, range_begin, n_fb, fallback, d_idx, d_so, d_R, st);
         h->prof_suppress = false;
         FIC_TRY(rc_fb);
     }
     return FIC_OK;
 }
 
-int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int range_begin, int n_ranges, int32_t* d_idx,
+int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_ranges, int32_t* d_idx,
                       double* d_so, double* d_R, unsigned flags, cudaStream_t st)
 {
-    return bf_screen_run(h, d_img, H, W, range_begin, n_ranges, d_idx, d_so, d_R, flags, nullptr, st);
+    return bf_screen_run(h, d_img, H, W, mode, range_begin, n_ranges, d_idx, d_so, d_R, flags, nullptr, st);
 }

@@ -70,17 +70,18 @@ def test_probe_accumulators_are_exact(fic, images, case):
     assert (err[small] == 0).all(), f"inexact below 2^17: max {err[small].max()}"
 
 
+@pytest.mark.parametrize("mode", [1, 0], ids=["jit", "numpy"])
 @pytest.mark.parametrize("seed,shape", [(1, (96, 96)), (2, (128, 200)), (3, (160, 96))])
-def test_pipeline_equals_exact_scan(fic, seed, shape):
+def test_pipeline_equals_exact_scan(fic, seed, shape, mode):
     img = synthetic_image(seed, *shape)
     if seed == 3:
         img[:40] = 255          # saturated: flat ranges the screen must hand to the exact scan
         img[100:120, 10:60] = 0
     h = fic.default_handle()
     h.reset_counters()
-    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
+    a = fic.bf_encode(img, mode=mode, flags=0)
     c = h.counters()
-    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    b = fic.bf_encode(img, mode=mode, flags=fic.BF_EXACT_ONLY)
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
     n = (shape[0] // 8) * (shape[1] // 8)
@@ -89,13 +90,27 @@ def test_pipeline_equals_exact_scan(fic, seed, shape):
         assert c["screen_ranges"] > 0
 
 
-def test_pipeline_noise_image(fic):
+@pytest.mark.parametrize("mode", [1, 0], ids=["jit", "numpy"])
+def test_pipeline_noise_image(fic, mode):
     """White noise: every candidate is about equally bad, the survivor lists are long."""
     rng = np.random.default_rng(17)
     img = rng.integers(0, 256, (96, 96), dtype=np.uint8)
-    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
-    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    a = fic.bf_encode(img, mode=mode, flags=0)
+    b = fic.bf_encode(img, mode=mode, flags=fic.BF_EXACT_ONLY)
     for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def test_numpy_mode_pipeline_equals_oracle(fic, orc, images):
+    """BruteForceEncoder semantics (float64, no clamp, uint8-wrapped sum of squares) through the tensor-core screen:
+    the records equal the CPU restatement of bf_encoder.py, which is pinned to the reference in tests/golden."""
+    img = np.ascontiguousarray(images["lena256"][96:192, 64:176])       # 96 x 112: 6 400 candidate positions
+    h = fic.default_handle()
+    h.reset_counters()
+    got = fic.bf_encode(img, mode=fic.BF_MODE_NUMPY)
+    assert h.counters()["screen_ranges"] > 0
+    want = orc.bf_encode(img, mode=0)
+    for x, y in zip(got, want):
         assert np.array_equal(x, y)
 
 
@@ -155,12 +170,13 @@ def _stress_images():
     return out
 
 
+@pytest.mark.parametrize("mode", [1, 0], ids=["jit", "numpy"])
 @pytest.mark.parametrize("name", sorted(_stress_images()))
-def test_screen_is_conservative_on_adversarial_images(fic, name):
+def test_screen_is_conservative_on_adversarial_images(fic, name, mode):
     """The screen may only drop candidates that cannot win or tie.  Images chosen to attack the bound: domains with
     (almost) zero variance, ranges flatter than the float32 noise guard, saturated pixels, exact repeats (ties)."""
     img = _stress_images()[name]
-    a = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=0)
-    b = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY)
+    a = fic.bf_encode(img, mode=mode, flags=0)
+    b = fic.bf_encode(img, mode=mode, flags=fic.BF_EXACT_ONLY)
     for x, y in zip(a, b):
         assert np.array_equal(x, y), name
