@@ -2,6 +2,7 @@
 the C ABI (include/fic.h: fic_hv_encode, fic_tree_decode)."""
 from __future__ import annotations
 
+import gc
 from dataclasses import dataclass
 from typing import Optional
 
@@ -10,7 +11,7 @@ import numpy as np
 from quadtree.common import MAX_GRAY, EncodingInfo
 
 
-@dataclass
+@dataclass(slots=True)
 class Domain:
     start_i: int
     start_j: int
@@ -22,7 +23,7 @@ class Domain:
     quantized_offset: int
 
 
-@dataclass
+@dataclass(slots=True)
 class SplitInfo:
     vertical_split: bool
     split_idx: int
@@ -60,61 +61,80 @@ class HVImage:
 
 def stream_to_tree(nodes: np.ndarray, vals: np.ndarray) -> HVNode:
     """Rebuild the binary tree from the preorder stream of fic_hv_encode."""
-    rows = nodes.tolist()
-    vv = vals.tolist()
+    nodes = np.asarray(nodes)
+    n = len(nodes)
+    if n == 0:
+        raise ValueError("truncated HV node stream")
+    cols = [nodes[:, c].tolist() for c in range(7)]
+    sc, of = vals[:, 0].tolist(), vals[:, 1].tolist()
+    gc_was_on = gc.isenabled()
+    gc.disable()   # tens of thousands of small acyclic objects: the generational collector only gets in the way
+    try:
+        return _build_tree(cols, sc, of, n)
+    finally:
+        if gc_was_on:
+            gc.enable()
+
+
+def _build_tree(cols, sc, of, n) -> HVNode:
+    kind, c1, c2, c3, c4, c5, c6 = cols
     root = None
-    stack: list[list] = []  # [node, children attached]
-    for r, v in zip(rows, vv):
-        if r[0] == 1:
-            node = HVNode.Leaf(Domain(r[1], r[2], r[3], r[4], v[0], v[1], r[5], r[6]))
+    stack: list[HVNode] = []   # open splits: c1 is None until the first child arrives, c2 until the second
+    new_node, new_domain, new_split = HVNode, Domain, SplitInfo
+    for k in range(n):
+        if root is not None and not stack:
+            raise ValueError("HV node stream continues after the tree is complete")
+        if kind[k] == 1:
+            node = new_node(None, None, None, new_domain(c1[k], c2[k], c3[k], c4[k], sc[k], of[k], c5[k], c6[k]))
         else:
-            node = HVNode(None, None, SplitInfo(bool(r[1]), int(r[2])), None)
+            node = new_node(None, None, new_split(bool(c1[k]), c2[k]), None)
         if stack:
             top = stack[-1]
-            if top[1] == 0:
-                top[0].c1 = node
+            if top.c1 is None:
+                top.c1 = node
             else:
-                top[0].c2 = node
-            top[1] += 1
+                top.c2 = node
+                stack.pop()
         else:
             root = node
-        if not node.is_leaf():
-            stack.append([node, 0])
-        while stack and stack[-1][1] == 2:
-            stack.pop()
+        if kind[k] != 1:
+            stack.append(node)
     if stack or root is None:
         raise ValueError("truncated HV node stream")
     return root
 
 
 def tree_to_leaves(hv_img: HVImage, use_quantized_values: bool = True):
-    """leaves[k] = (ri, rj, h, w, di, dj, orient, rot), so[k] = (scale, offset) as hvv2/decoder.py:59-74."""
+    """leaves[k] = (ri, rj, h, w, di, dj, orient, rot), so[k] = (scale, offset) as hvv2/decoder.py:59-74 (the same float64
+    operations in the same order, applied to whole columns)."""
     info = hv_img.info
     max_encoded_scale = np.float64(2 ** info.scale_bits)
     max_encoded_offset = np.float64(2 ** info.offset_bits)
     max_scale = info.max_scale
-    leaves, so = [], []
+    leaves, doms = [], []
     stack = [(hv_img.root, 0, 0, info.img_width, info.img_height)]
+    pop, push = stack.pop, stack.append
     while stack:
-        node, i, j, w, h = stack.pop()
-        if node.is_leaf():
-            d = node.domain
-            if use_quantized_values:
-                scale = np.float64(d.quantized_scale) * (2 * max_scale) / max_encoded_scale - max_scale
-                mul_coef = float(MAX_GRAY)
-                if scale < 0:
-                    mul_coef *= (1 + scale)
-                offset = np.float64(d.quantized_offset) / max_encoded_offset * mul_coef - MAX_GRAY * scale
-            else:
-                scale, offset = d.scale, d.offset
+        node, i, j, w, h = pop()
+        d = node.domain
+        if d is not None:
             leaves.append((i, j, h, w, d.start_i, d.start_j, d.orientation, d.rotation))
-            so.append((float(scale), float(offset)))
+            doms.append(d)
         else:
             s = node.split_info.split_idx
             if node.split_info.vertical_split:
-                stack.append((node.c2, i, j + s + 1, w - s - 1, h))
-                stack.append((node.c1, i, j, s + 1, h))
+                push((node.c2, i, j + s + 1, w - s - 1, h))
+                push((node.c1, i, j, s + 1, h))
             else:
-                stack.append((node.c2, i + s + 1, j, w, h - s - 1))
-                stack.append((node.c1, i, j, w, s + 1))
-    return np.array(leaves, np.int32).reshape(-1, 8), np.array(so, np.float64).reshape(-1, 2)
+                push((node.c2, i + s + 1, j, w, h - s - 1))
+                push((node.c1, i, j, w, s + 1))
+    if use_quantized_values:
+        qs = np.array([d.quantized_scale for d in doms], np.float64)
+        qo = np.array([d.quantized_offset for d in doms], np.float64)
+        scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
+        mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
+        offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
+        so = np.stack([scale, offset], axis=1) if len(doms) else np.zeros((0, 2))
+    else:
+        so = np.array([(float(d.scale), float(d.offset)) for d in doms], np.float64)
+    return np.array(leaves, np.int32).reshape(-1, 8), np.ascontiguousarray(so, np.float64).reshape(-1, 2)

@@ -6,6 +6,7 @@ objects and the flat arrays of the C ABI (include/fic.h: fic_qt_encode, fic_tree
 """
 from __future__ import annotations
 
+import gc
 from dataclasses import dataclass, replace
 from typing import Callable, Optional
 
@@ -18,7 +19,7 @@ TRANSPOSED_ORIENTATION = 1
 MAX_GRAY = 255
 
 
-@dataclass
+@dataclass(slots=True)
 class Domain:
     start_i: int
     start_j: int
@@ -98,33 +99,59 @@ def get_domain_dimension_extractors() -> list[Callable[[Domain], int]]:
 # ---- flat stream <-> tree ------------------------------------------------------------------------
 def stream_to_forest(nodes: np.ndarray, vals: np.ndarray, n_roots: int) -> list[QuadtreeNode]:
     """Rebuild the forest from the preorder stream of fic_qt_encode (kind, di, dj, orient, rot, qs, qo, exp)."""
-    rows = nodes.tolist()
-    vv = vals.tolist()
+    nodes = np.asarray(nodes)
+    n = len(nodes)
+    kind, di, dj, ori, rot, qs, qo = (nodes[:, c].tolist() for c in range(7)) if n else ([],) * 7
+    sc, of = (vals[:, 0].tolist(), vals[:, 1].tolist()) if n else ([], [])
     pos = 0
     forest: list[QuadtreeNode] = []
+    new_node, new_domain = QuadtreeNode, Domain
+    gc_was_on = gc.isenabled()
+    gc.disable()   # tens of thousands of small acyclic objects: the generational collector only gets in the way
+    try:
+        return _build_forest(kind, di, dj, ori, rot, qs, qo, sc, of, n, n_roots)
+    finally:
+        if gc_was_on:
+            gc.enable()
+
+
+def _build_forest(kind, di, dj, ori, rot, qs, qo, sc, of, n, n_roots):
+    pos = 0
+    forest: list[QuadtreeNode] = []
+    new_node, new_domain = QuadtreeNode, Domain
     for _ in range(n_roots):
-        # iterative preorder rebuild: stack of (parent, children filled so far)
+        # iterative preorder rebuild: stack of open internal nodes' child lists
         root = None
-        stack: list[QuadtreeNode] = []
+        stack: list[list] = []
         while True:
-            r = rows[pos]
-            if r[0] == 1:
-                node = QuadtreeNode.Leaf(Domain(r[1], r[2], r[3], r[4], vv[pos][0], vv[pos][1], r[5], r[6]))
+            if pos >= n:
+                raise ValueError("node stream does not match the root count")
+            if kind[pos] == 1:
+                node = new_node(new_domain(di[pos], dj[pos], ori[pos], rot[pos], sc[pos], of[pos], qs[pos], qo[pos]), None)
+                pos += 1
+                if not stack:
+                    root = node
+                    break
+                top = stack[-1]
+                top.append(node)
+                while len(top) == 4:
+                    stack.pop()
+                    if not stack:
+                        break
+                    top = stack[-1]
+                if not stack:
+                    break
             else:
-                node = QuadtreeNode(None, [])
-            pos += 1
-            if stack:
-                stack[-1].children.append(node)
-            else:
-                root = node
-            if not node.is_leaf():
-                stack.append(node)
-            while stack and len(stack[-1].children) == 4:
-                stack.pop()
-            if not stack:
-                break
+                children: list = []
+                node = new_node(None, children)
+                pos += 1
+                if stack:
+                    stack[-1].append(node)
+                else:
+                    root = node
+                stack.append(children)
         forest.append(root)
-    if pos != len(rows):
+    if pos != n:
         raise ValueError("node stream does not match the root count")
     return forest
 
@@ -143,37 +170,40 @@ def iter_root_squares(width: int, height: int, i: int = 0, j: int = 0):
 
 def forest_to_leaves(qimg: QuadtreeImage, use_quantized_values: bool = True):
     """Flatten to the arrays fic_tree_decode takes: leaves[k] = (ri, rj, size, size, di, dj, orient, rot),
-    so[k] = (scale, offset) de-quantised exactly as quadtree/decoder.py:90-98 does."""
+    so[k] = (scale, offset) de-quantised exactly as quadtree/decoder.py:90-98 does (the same float64 operations in
+    the same order, applied to whole columns)."""
     info = qimg.info
     max_encoded_scale = np.float64(2 ** info.scale_bits)
     max_encoded_offset = np.float64(2 ** info.offset_bits)
     max_scale = info.max_scale
     leaves: list[tuple] = []
-    so: list[tuple] = []
+    doms: list[Domain] = []
     roots = list(iter_root_squares(info.img_width, info.img_height))
     if len(roots) != len(qimg.forest):
         raise ValueError(f"forest has {len(qimg.forest)} roots, the image geometry needs {len(roots)}")
     for (ri, rj, e), root in zip(roots, qimg.forest):
         stack = [(root, ri, rj, 2 ** e)]
+        pop, push = stack.pop, stack.append
         while stack:
-            node, i, j, size = stack.pop()
-            if node.is_leaf():
-                d = node.domain
-                if use_quantized_values:
-                    scale = np.float64(d.quantized_scale) * (2 * max_scale) / max_encoded_scale - max_scale
-                    mul_coef = float(MAX_GRAY)
-                    if scale < 0:
-                        mul_coef *= (1 + scale)
-                    offset = np.float64(d.quantized_offset) / max_encoded_offset * mul_coef - MAX_GRAY * scale
-                else:
-                    scale, offset = d.scale, d.offset
+            node, i, j, size = pop()
+            d = node.domain
+            if d is not None:
                 leaves.append((i, j, size, size, d.start_i, d.start_j, d.orientation, d.rotation))
-                so.append((float(scale), float(offset)))
+                doms.append(d)
             else:
                 half = size // 2
                 c = node.children
-                stack.append((c[3], i + half, j + half, half))
-                stack.append((c[2], i + half, j, half))
-                stack.append((c[1], i, j + half, half))
-                stack.append((c[0], i, j, half))
-    return np.array(leaves, np.int32).reshape(-1, 8), np.array(so, np.float64).reshape(-1, 2)
+                push((c[3], i + half, j + half, half))
+                push((c[2], i + half, j, half))
+                push((c[1], i, j + half, half))
+                push((c[0], i, j, half))
+    if use_quantized_values:
+        qs = np.array([d.quantized_scale for d in doms], np.float64)
+        qo = np.array([d.quantized_offset for d in doms], np.float64)
+        scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
+        mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
+        offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
+        so = np.stack([scale, offset], axis=1) if len(doms) else np.zeros((0, 2))
+    else:
+        so = np.array([(float(d.scale), float(d.offset)) for d in doms], np.float64)
+    return np.array(leaves, np.int32).reshape(-1, 8), np.ascontiguousarray(so, np.float64).reshape(-1, 2)
