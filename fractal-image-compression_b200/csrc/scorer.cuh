@@ -89,12 +89,20 @@ __device__ __forceinline__ double fic_q_mse(double n, double inv_n, double sqr, 
                                             double ds, double rs, double max_scale, int scale_bits, int offset_bits,
                                             int* oqs, int* oqo)
 {
+    // Divisions by a power of two are exact multiplications by its reciprocal (same IEEE result, a fraction of the
+    // instructions of a float64 division): 2^scale_bits and 2^offset_bits always, 2*max_scale when it is one.
     const double sb2 = (double)(1ll << scale_bits), ob2 = (double)(1ll << offset_bits);
+    const double inv_sb2 = __longlong_as_double((long long)(1023 - scale_bits) << 52);
+    const double inv_ob2 = __longlong_as_double((long long)(1023 - offset_bits) << 52);
     const double two_ms = DM(2.0, max_scale);
-    long long qs = (long long)DM(DD(DA(s, max_scale), two_ms), sb2);  // int(): truncation toward zero
+    const long long tm_bits = __double_as_longlong(two_ms);
+    const bool tm_pow2 = (tm_bits & 0x000fffffffffffffll) == 0 && tm_bits > (2ll << 52) && tm_bits < (2044ll << 52);
+    const double inv_tm = __longlong_as_double((2046ll << 52) - tm_bits);
+    const double sn = DA(s, max_scale);
+    long long qs = (long long)DM(tm_pow2 ? DM(sn, inv_tm) : DD(sn, two_ms), sb2);  // int(): truncation toward zero
     if (qs < 0) qs = 0;
     if (qs > (1ll << scale_bits) - 1) qs = (1ll << scale_bits) - 1;
-    s = DS(DD(DM((double)qs, two_ms), sb2), max_scale);
+    s = DS(DM(DM((double)qs, two_ms), inv_sb2), max_scale);
     double coef = 255.0;
     if (s < 0.0) {
         coef = DM(coef, DA(1.0, s));
@@ -103,7 +111,7 @@ __device__ __forceinline__ double fic_q_mse(double n, double inv_n, double sqr, 
     long long qo = (long long)DM(DD(DA(o, DM(255.0, s)), coef), ob2);
     if (qo < 0) qo = 0;
     if (qo > (1ll << offset_bits) - 1) qo = (1ll << offset_bits) - 1;
-    o = DS(DM(DD((double)qo, ob2), coef), DM(255.0, s));
+    o = DS(DM(DM((double)qo, inv_ob2), coef), DM(255.0, s));
     *oqs = (int)qs;
     *oqo = (int)qo;
     return fic_R(inv_n, n, sqr, s, sds, ab, o, ds, rs);
