@@ -215,6 +215,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+
     img = load_image(rank)
     h = fic_b200.Handle(local)
     # an explicit (non-default) stream: the library launches on it and torch's events are recorded on it
@@ -229,25 +230,55 @@ def run_ours(args):
     d_so = d_so2[0]
     d_R = torch.zeros((N_RANGES,), dtype=torch.float64, device=dev)
     gathered = [[torch.zeros_like(d_so) for _ in range(world)] for _ in range(2)] if world > 1 else None
-    pending = [None]   # the all_gather still in flight
-    parity_k = [0]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     flags = fic_b200.BF_EXACT_ONLY if args.exact_only else 0
+    parity_k = [0]
+    # The gather is enqueued by a helper thread while the main thread is already inside the next encode call (ctypes
+    # releases the GIL): the NCCL launch overhead of image k then overlaps the kernels of image k+1 as well.
+    import queue
+    gq: "queue.Queue" = queue.Queue()
+    submitted = [None, None]      # per buffer: (threading.Event set once enqueued, [work handle])
+
+    def gather_worker():
+        torch.cuda.set_device(local)
+        side = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(side):
+            while True:
+                item = gq.get()
+                if item is None:
+                    return
+                k, ev, box = item
+                box.append(dist.all_gather(gathered[k], d_so2[k], async_op=True))
+                ev.set()
+
+    worker = None
+    if world > 1:
+        worker = threading.Thread(target=gather_worker, daemon=True)
+        worker.start()
+
+    def wait_buffer(k):
+        if submitted[k] is not None:
+            ev, box = submitted[k]
+            ev.wait()
+            box[0].wait()              # stream-level: the encode about to overwrite the buffer waits for its gather
+            submitted[k] = None
 
     def step():
         k = parity_k[0]
         parity_k[0] ^= 1
+        if world > 1:
+            wait_buffer(k)
         fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, d_idx.data_ptr(), d_so2[k].data_ptr(), d_R.data_ptr(),
                                flags=flags, stream=stream)
-        if world > 1:  # the only exchange of the path: winner records
-            if pending[0] is not None:
-                pending[0].wait()          # the previous image's gather ran next to this encode
-            pending[0] = dist.all_gather(gathered[k], d_so2[k], async_op=True)
+        if world > 1:  # the only exchange of the path: winner records; the encode above has completed
+            ev, box = threading.Event(), []
+            submitted[k] = (ev, box)
+            gq.put((k, ev, box))
 
     def drain():
-        if pending[0] is not None:
-            pending[0].wait()
-            pending[0] = None
+        if world > 1:
+            wait_buffer(0)
+            wait_buffer(1)
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -367,6 +398,8 @@ def run_ours(args):
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     if world > 1:
+        gq.put(None)
+        worker.join(timeout=5)
         dist.destroy_process_group()
 
 
