@@ -21,38 +21,62 @@
 #define TE_THREADS 128
 
 // ---- integral images ----------------------------------------------------------------------------
+// rows: one warp per image row, 32 pixels per step, warp inclusive scan plus a running carry (coalesced reads and writes)
 __global__ void integral_rows_kernel(const uint8_t* __restrict__ img, int H, int W, long long* __restrict__ I1,
                                      long long* __restrict__ I2)
 {
-    int y = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (y > H) return;
     const int W1 = W + 1;
+    long long* r1 = I1 + (size_t)y * W1;
+    long long* r2 = I2 + (size_t)y * W1;
     if (y == 0) {
-        for (int x = 0; x <= W; ++x) { I1[x] = 0; I2[x] = 0; }
+        for (int x = lane; x <= W; x += 32) { r1[x] = 0; r2[x] = 0; }
         return;
     }
-    long long s = 0, q = 0;
-    I1[(size_t)y * W1] = 0;
-    I2[(size_t)y * W1] = 0;
-    for (int x = 0; x < W; ++x) {
-        long long v = img[(size_t)(y - 1) * W + x];
-        s += v;
-        q += v * v;
-        I1[(size_t)y * W1 + x + 1] = s;
-        I2[(size_t)y * W1 + x + 1] = q;
+    if (lane == 0) { r1[0] = 0; r2[0] = 0; }
+    const uint8_t* src = img + (size_t)(y - 1) * W;
+    long long cs = 0, cq = 0;   // carries: sums of everything left of this step
+    for (int x0 = 0; x0 < W; x0 += 32) {
+        const int x = x0 + lane;
+        const long long v = x < W ? src[x] : 0;
+        long long s = v, q = v * v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const long long ts = __shfl_up_sync(0xffffffffu, s, off), tq = __shfl_up_sync(0xffffffffu, q, off);
+            if (lane >= off) { s += ts; q += tq; }
+        }
+        if (x < W) { r1[x + 1] = cs + s; r2[x + 1] = cq + q; }
+        cs += __shfl_sync(0xffffffffu, s, 31);
+        cq += __shfl_sync(0xffffffffu, q, 31);
     }
 }
+// columns: one thread per column (coalesced across the warp), sixteen rows loaded before any is stored so that the
+// loads are not serialised behind the in-place stores
 __global__ void integral_cols_kernel(int H, int W, long long* __restrict__ I1, long long* __restrict__ I2)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x > W) return;
     const int W1 = W + 1;
+    constexpr int U = 16;
     long long s = 0, q = 0;
-    for (int y = 1; y <= H; ++y) {
-        s += I1[(size_t)y * W1 + x];
-        q += I2[(size_t)y * W1 + x];
-        I1[(size_t)y * W1 + x] = s;
-        I2[(size_t)y * W1 + x] = q;
+    for (int y0 = 1; y0 <= H; y0 += U) {
+        long long a[U], b[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const bool in = y0 + u <= H;
+            a[u] = in ? I1[(size_t)(y0 + u) * W1 + x] : 0;
+            b[u] = in ? I2[(size_t)(y0 + u) * W1 + x] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (y0 + u <= H) {
+                s += a[u];
+                q += b[u];
+                I1[(size_t)(y0 + u) * W1 + x] = s;
+                I2[(size_t)(y0 + u) * W1 + x] = q;
+            }
+        }
     }
 }
 __device__ __forceinline__ long long box(const long long* __restrict__ I, int W1, int y0, int x0, int y1, int x1)
@@ -65,9 +89,9 @@ static int build_integrals(fic_handle* h, const uint8_t* d_img, int H, int W, cu
     size_t n = (size_t)(H + 1) * (W + 1);
     FIC_TRY(h->t_int1.reserve(n * sizeof(long long)));
     FIC_TRY(h->t_int2.reserve(n * sizeof(long long)));
-    integral_rows_kernel<<<(H + 1 + 63) / 64, 64, 0, st>>>(d_img, H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
+    integral_rows_kernel<<<((H + 1) * 32 + 127) / 128, 128, 0, st>>>(d_img, H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
     FIC_CHECK_LAUNCH(h, "integral_rows_kernel");
-    integral_cols_kernel<<<(W + 1 + 63) / 64, 64, 0, st>>>(H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
+    integral_cols_kernel<<<(W + 1 + 31) / 32, 32, 0, st>>>(H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
     FIC_CHECK_LAUNCH(h, "integral_cols_kernel");
     return FIC_OK;
 }
