@@ -173,9 +173,12 @@ def run_reference(args):
     orc.lib()
     img = load_image(0)
     cores = host_cores()
-    sample = max(cores * 8, 32)
-    for _ in range(max(args.warmup, 0) and 1):  # one short warm-up is enough for compiled C
-        cpu_sample(img, max(cores, 4))
+    # one short warm-up is enough for compiled C; it also gives the rate that sizes the per-step sample so that the
+    # whole run stays near two minutes whatever --steps is
+    _, dt0, _, _ = cpu_sample(img, max(cores, 4))
+    rate = max(cores, 4) / max(dt0, 1e-6)                       # ranges per second
+    sample = int(min(cores * 8, max(cores, 120.0 * rate / max(args.steps, 1))))
+    sample = max(sample, 4)
     t_tot, m_tot = 0.0, 0
     for _ in range(args.steps):
         v, dt, cores, start = cpu_sample(img, sample)
