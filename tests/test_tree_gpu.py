@@ -137,6 +137,19 @@ def test_hv_search_against_oracle(fic, orc):
         assert np.array_equal(v, wv)
 
 
+def test_hv_search_large_rectangles_and_chunked_candidates(fic, orc):
+    """Rectangles above 4 096 pixels are read straight from the image instead of shared memory, and a call with few
+    rectangles cuts each candidate list into chunks over several CTAs (hv_pick_kernel merges them): both against the
+    oracle, including a rectangle with a single domain position and one with none."""
+    img = synthetic_image(9, 288, 320)
+    rects = [(0, 0, 70, 66), (16, 8, 96, 80), (100, 40, 159, 100), (3, 5, 9, 143), (0, 0, 160, 144), (7, 7, 3, 2)]
+    rec, vals = fic.hv_search(img, rects, 5, 7, 1.0)
+    for (i, j, w, h), r, v in zip(rects, rec, vals):
+        wr, wv = orc.hv_search(img, i, j, w, h, 5, 7, 1.0)
+        assert np.array_equal(r, wr), (i, j, w, h)
+        assert np.array_equal(v, wv), (i, j, w, h)
+
+
 @pytest.mark.parametrize("params", [(4, 4, 16, 16, 5, 7, 25.0), (1, 1, 8, 8, 6, 6, 4.0, 0.9), (2, 3, 64, 64, 5, 7, 60.0)])
 def test_hv_against_oracle(fic, orc, params):
     img = synthetic_image(12, 56, 72)
