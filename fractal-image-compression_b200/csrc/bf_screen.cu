@@ -979,7 +979,10 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
     __shared__ double s_rs[RESCORE_WARPS], s_sq[RESCORE_WARPS];
     __shared__ uint32_t s_big[RESCORE_WARPS];    // list length of a range left to the whole CTA (0 = nothing to do)
     __shared__ RescoreBest s_red[RESCORE_WARPS];
+    __shared__ unsigned int s_total;             // survivors rescored by this CTA
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) s_total = 0;
+    __syncthreads();
     const int slot = blockIdx.x * RESCORE_WARPS + warp;
     const int n_elig = ctrl[0];
     const int rw = W / 8, PW = W - 16;
@@ -1018,7 +1021,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
                 rv[warp][t][sa * 8 + sb] = (float)r1;
             }
             __syncwarp();
-            if (lane == 0 && n) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)n);
+            if (lane == 0 && n) atomicAdd(&s_total, n);   // one global update per CTA, not one per range
             if (n <= RESCORE_WARP_LIMIT) {
                 RescoreBest b;
                 b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
@@ -1035,6 +1038,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
         }
     }
     __syncthreads();
+    if (threadIdx.x == 0 && s_total) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)s_total);
     // ---- phase B: long lists, all warps on one range at a time --------------------------------------------------------
     for (int r = 0; r < RESCORE_WARPS; ++r) {
         const uint32_t n = s_big[r];
