@@ -25,17 +25,20 @@
 // rounding of the fractional extension term); theta is one FFMA per (thread, range, tile), the 8 isometry columns of a
 // range are max-reduced first, so the common case is ~5 instructions per 8 outputs.
 //
-// Rounds: a coarse exact pre-scan (~250 positions per range) gives the first bounds; round 1 screens a sparse subset of
-// the candidate tiles (every 8th for 512x512, every 512th for 4096x4096), its survivors are rescored exactly and give much
-// tighter bounds for the next, ~128x larger, round, and so on until every tile has been screened once.
+// Rounds: a seed round ranks a coarse lattice of candidates (~NP/100 positions) per range with the same GEMM and a
+// ranking epilogue; the best one and position 0 are scored exactly and give the first bounds.  Round 1 then screens a
+// sparse subset of the candidate tiles (every 8th for 512x512, every 256th for 4096x4096), its survivors are rescored
+// exactly and give much tighter bounds for the next, ~16x larger, round, and so on until every tile has been screened once.
 // Ranges the screen cannot decide (bound not below the range's own variance, survivor list overflow) go to the
-// exact scan; constant ranges are decided directly (every candidate ties at R = 0, the first one wins).
+// exact scan; constant ranges are decided by the seed list (every candidate ties at R = 0, the first one wins).
+// The NumPy encoder's semantics (bf_encoder.py) go through the same screen: see bf_init_kernel.
 //
 // GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 4-stage ring), N = 256 columns = 32 ranges
 // x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
 // TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
-// tile t.  Warp roles: warps 0..15 epilogue, warp 16 TMA producer, warp 17 MMA issuer + TMEM allocator; epilogue in two groups of
-// eight, one group per accumulator stage (two warps per TMEM lane quadrant, 128 columns each).  Thread = candidate, so h_c/k_c are per-thread registers and the 8 isometry
+// tile t.  Warp roles: warps 0..15 epilogue, warp 16 TMA producer, warp 17 MMA issuer + TMEM allocator (both run in
+// lock step with one elected lane issuing); epilogue in two groups of eight, one group per accumulator stage (two warps
+// per TMEM lane quadrant, 128 columns each).  Thread = candidate, so h_c is a per-thread register and the 8 isometry
 // columns of a range share one tau.  The (group, tile) space is cut into equal contiguous spans, one per CTA.
 //
 // HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
