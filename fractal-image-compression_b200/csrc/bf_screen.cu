@@ -531,6 +531,13 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             // met) for the padding rows of the last tile
             const float hk_pad = __int_as_float(0x7f800000);
             float hq_next = (j < j1 && t_cur * BM + lane_off < p.NP) ? p.hk[t_cur * BM + lane_off].x : hk_pad;
+            // the sixteen tau of the next tile (class picked by the sign of its hq) are fetched at the END of the current
+            // tile, when both chunk buffers are dead, so the shared-memory latency is paid under the index arithmetic
+            float4 tq0, tq1, tq2, tq3;
+            {
+                const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 16 : 0));
+                tq0 = tau4[0]; tq1 = tau4[1]; tq2 = tau4[2]; tq3 = tau4[3];
+            }
             for (; j < j1; j += 2) {
                 // ---- everything up to the wait is off the accumulator's critical path (MMA -> epilogue -> MMA) ----
                 const int my_cand = t_cur * BM + lane_off;
@@ -583,19 +590,16 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 const float qx = fabsf(hq);
                 // thresholds on |u| for the 16 ranges: theta = tau/h_c - DELTA, tau picked by the candidate's class
                 float theta[16];
-                {
-                    const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq < 0.f ? 16 : 0));
+                theta[0] = fmaf(tq0.x, qx, -DELTA_U); theta[1] = fmaf(tq0.y, qx, -DELTA_U);
+                theta[2] = fmaf(tq0.z, qx, -DELTA_U); theta[3] = fmaf(tq0.w, qx, -DELTA_U);
+                theta[4] = fmaf(tq1.x, qx, -DELTA_U); theta[5] = fmaf(tq1.y, qx, -DELTA_U);
+                theta[6] = fmaf(tq1.z, qx, -DELTA_U); theta[7] = fmaf(tq1.w, qx, -DELTA_U);
+                theta[8] = fmaf(tq2.x, qx, -DELTA_U); theta[9] = fmaf(tq2.y, qx, -DELTA_U);
+                theta[10] = fmaf(tq2.z, qx, -DELTA_U); theta[11] = fmaf(tq2.w, qx, -DELTA_U);
+                theta[12] = fmaf(tq3.x, qx, -DELTA_U); theta[13] = fmaf(tq3.y, qx, -DELTA_U);
+                theta[14] = fmaf(tq3.z, qx, -DELTA_U); theta[15] = fmaf(tq3.w, qx, -DELTA_U);
 #pragma unroll
-                    for (int c4 = 0; c4 < 4; ++c4) {
-                        const float4 t = tau4[c4];   // one broadcast LDS.128
-                        theta[c4 * 4 + 0] = fmaf(t.x, qx, -DELTA_U);
-                        theta[c4 * 4 + 1] = fmaf(t.y, qx, -DELTA_U);
-                        theta[c4 * 4 + 2] = fmaf(t.z, qx, -DELTA_U);
-                        theta[c4 * 4 + 3] = fmaf(t.w, qx, -DELTA_U);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) asm volatile("" : "+f"(theta[i]));   // materialise before the wait
-                }
+                for (int i = 0; i < 16; ++i) asm volatile("" : "+f"(theta[i]));   // materialise before the wait
                 mbar_wait(my_tfull, aph, p.err_flag, 6);
                 tcgen05_fence_after();
                 uint32_t va[32], vb[32];
@@ -636,6 +640,10 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     if (!SCREEN && (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u)) p.cnt[0] = 1;
                 }
                 aph ^= 1;
+                {   // next tile's tau (see above); harmless after the last tile
+                    const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 16 : 0));
+                    tq0 = tau4[0]; tq1 = tau4[1]; tq2 = tau4[2]; tq3 = tau4[3];
+                }
                 if (MODE == 0 && qn >= QFLUSH) { queue_flush(queue, p, lane, qn); qn = 0; }
             }
         }
