@@ -81,7 +81,7 @@ constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
 constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
 constexpr uint32_t OFF_TAU = OFF_BARS + 256;                        // per epilogue warp: 16 x float2 thresholds
 constexpr uint32_t OFF_QUEUE = OFF_TAU + EPI_WARPS * 16 * 8;          // per epilogue warp: survivor queue
-constexpr uint32_t QUEUE_BYTES = (32 + 512) * 8;                     // sizeof(WarpQueue), checked below
+constexpr uint32_t QUEUE_BYTES = (128 + 512) * 8;                    // sizeof(WarpQueue), checked below
 constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * QUEUE_BYTES + 1024;  // + slack to align the base to 1024
 
 constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
@@ -282,7 +282,7 @@ __device__ __noinline__ void append_hits(uint32_t* __restrict__ cnt, uint32_t* _
 // reservations (one atomicAdd per entry, a full round trip to L2) are issued 32 at a time when the queue is flushed
 // between tiles.  A tile can add at most 4 chunks x 4 ranges x 32 lanes = 512 entries per warp, and the queue is
 // flushed whenever a tile ends with QFLUSH or more entries, so QCAP = QFLUSH + 512 can never overflow.
-constexpr int QFLUSH = 32;
+constexpr int QFLUSH = 128;
 constexpr int QCAP = QFLUSH + 512;
 struct WarpQueue {
     uint2 e[QCAP];   // x = (slot << 8) | isometry mask, y = candidate position
