@@ -902,7 +902,7 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
 // Ranges with a short list (the common case) are handled by their own warp; the few with a long list are then
 // worked through by the whole CTA one after the other, so a single crowded range cannot become a 256-iteration tail.
 #define RESCORE_WARPS 8
-#define RESCORE_WARP_LIMIT 256u
+#define RESCORE_WARP_LIMIT 64u
 
 struct RescoreBest {
     double R, s, o;
@@ -979,7 +979,7 @@ __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeSt
     }
 }
 
-__global__ void __launch_bounds__(RESCORE_WARPS * 32)
+__global__ void __launch_bounds__(RESCORE_WARPS * 32, 4)   // 4 CTAs per SM: the 512 CTAs of a 512x512 image fit in one wave
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
