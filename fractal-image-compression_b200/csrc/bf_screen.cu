@@ -46,6 +46,8 @@
 //   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
 //   hk      float2 [NP]    (+-1/h_c, den16); a negative .x marks an ill-conditioned domain, .y only ranks seed candidates
 // and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
+#include <algorithm>
+#include <vector>
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <stdlib.h>
@@ -901,13 +903,21 @@ __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const 
 // an exact integer sum in fp32, the score is the float64 restatement of jit_bfencoder.py:64-95 (scorer.cuh).
 // Ranges with a short list (the common case) are handled by their own warp; the few with a long list are then
 // worked through by the whole CTA one after the other, so a single crowded range cannot become a 256-iteration tail.
-#define RESCORE_WARPS 8
-#define RESCORE_WARP_LIMIT 64u
+#define RESCORE_WARPS 32
+#define RESCORE_SMEM (RESCORE_WARPS * 8 * 65 * 4)   // dynamic: the oriented range copies
 
 struct RescoreBest {
     double R, s, o;
     unsigned long long seq;
 };
+
+// order-preserving map of a double onto uint64 (R may be negative with the NumPy encoder's wrapped sum of squares);
+// -0.0 and +0.0 compare equal in the reference, so they share a key
+__device__ __forceinline__ unsigned long long rescore_key(double R)
+{
+    const long long bits = __double_as_longlong(R + 0.0);
+    return bits < 0 ? ~(unsigned long long)bits : (unsigned long long)bits | 0x8000000000000000ull;
+}
 
 __device__ __forceinline__ void rescore_entry(uint32_t ent, const float (*rvw)[65], double rs, double sqr,
                                               const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
@@ -979,27 +989,27 @@ __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeSt
     }
 }
 
-__global__ void __launch_bounds__(RESCORE_WARPS * 32, 4)   // 4 CTAs per SM: the 512 CTAs of a 512x512 image fit in one wave
+__global__ void __launch_bounds__(RESCORE_WARPS * 32, 1)   // 1024 threads x 64 registers: a long list is walked 1024 entries at a time
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
                   int32_t* __restrict__ fallback, int emit, int mode, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
                   double* __restrict__ out_R)
 {
-    __shared__ float rv[RESCORE_WARPS][8][65];   // inverse-transformed range per isometry, padded against bank conflicts
+    extern __shared__ float rv_raw[];
+    float (*rv)[8][65] = reinterpret_cast<float (*)[8][65]>(rv_raw);   // inverse-transformed range per isometry, padded against bank conflicts
     __shared__ double s_rs[RESCORE_WARPS], s_sq[RESCORE_WARPS];
-    __shared__ uint32_t s_big[RESCORE_WARPS];    // list length of a range left to the whole CTA (0 = nothing to do)
-    __shared__ RescoreBest s_red[RESCORE_WARPS];
-    __shared__ unsigned int s_total;             // survivors rescored by this CTA
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) s_total = 0;
-    __syncthreads();
+    __shared__ double s_R[RESCORE_WARPS], s_s[RESCORE_WARPS], s_o[RESCORE_WARPS];   // running winner of each range
+    __shared__ unsigned long long s_key[RESCORE_WARPS], s_prev[RESCORE_WARPS], s_seq[RESCORE_WARPS];
+    __shared__ uint32_t s_n[RESCORE_WARPS + 1];   // list lengths, then their exclusive prefix
+    __shared__ int s_ridx[RESCORE_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
     const int slot = blockIdx.x * RESCORE_WARPS + warp;
     const int n_elig = ctrl[0];
     const int rw = W / 8, PW = W - 16;
     const int NP = PW * (H - 16);
-    if (lane == 0) s_big[warp] = 0;
-    // ---- phase A: every warp prepares its range and finishes it when the list is short -----------------------------
+    // ---- phase A: warp w prepares range w of the CTA (pixels, sums, the eight oriented copies, its running winner) ----
+    if (lane == 0) { s_n[warp] = 0; s_ridx[warp] = -1; }
     if (slot < n_elig) {
         const RangeState st = state[slot];
         const uint32_t n = cnt[slot];
@@ -1022,7 +1032,6 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
             unsigned q = mode == FIC_BF_MODE_JIT ? r0 * r0 + r1 * r1 : ((r0 * r0) & 255u) + ((r1 * r1) & 255u);  // bf_encoder.py:33
 #pragma unroll
             for (int off = 16; off > 0; off >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, off); q += __shfl_xor_sync(0xffffffffu, q, off); }
-            const double rs = (double)s, sqr = (double)q;
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
                 int sa, sb;
@@ -1031,46 +1040,58 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
                 fic_iso_bf(t >> 2, t & 3, 8, 4 + (lane >> 3), lane & 7, sa, sb);
                 rv[warp][t][sa * 8 + sb] = (float)r1;
             }
-            __syncwarp();
-            if (lane == 0 && n) atomicAdd(&s_total, n);   // one global update per CTA, not one per range
-            if (n <= RESCORE_WARP_LIMIT) {
-                RescoreBest b;
-                b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
-                if (lane == 0) { b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }  // the running winner competes too
-                for (uint32_t e = lane; e < n; e += 32)
-                    rescore_entry(list[(size_t)slot * cap + e], rv[warp], rs, sqr, poolA, sd4, sdd, NP, mode, b);
-                rescore_warp_reduce(b);
-                if (lane == 0) rescore_commit(slot, ridx, b, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
-            } else if (lane == 0) {
-                s_rs[warp] = rs;
-                s_sq[warp] = sqr;
-                s_big[warp] = n;
+            if (lane == 0) {
+                s_rs[warp] = (double)s; s_sq[warp] = (double)q;
+                s_n[warp] = n; s_ridx[warp] = ridx;
+                s_R[warp] = st.R; s_s[warp] = st.s; s_o[warp] = st.o; s_seq[warp] = st.seq;   // the running winner competes too
+                s_key[warp] = s_prev[warp] = rescore_key(st.R);
             }
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0 && s_total) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)s_total);
-    // ---- phase B: long lists, all warps on one range at a time --------------------------------------------------------
-    for (int r = 0; r < RESCORE_WARPS; ++r) {
-        const uint32_t n = s_big[r];
-        if (n == 0) continue;   // uniform across the CTA
-        const int bslot = blockIdx.x * RESCORE_WARPS + r;
-        const double rs = s_rs[r], sqr = s_sq[r];
+    // ---- phase B: the CTA's lists laid end to end, one entry per thread and pass --------------------------------------
+    // (a warp per range would leave most lanes idle on the short lists and make one long list a serial tail.)
+    // Winner of a range = first strict minimum in scan order: minimum of the order-preserving key of R, then, among
+    // the entries that reach it, minimum of the scan index.  Non-finite R never takes part (fic_better).
+    if (tid == 0) {
+        uint32_t acc = 0;
+        for (int r = 0; r < RESCORE_WARPS; ++r) { const uint32_t n = s_n[r]; s_n[r] = acc; acc += n; }
+        s_n[RESCORE_WARPS] = acc;
+        if (acc) atomicAdd(reinterpret_cast<unsigned long long*>(ctrl + 8), (unsigned long long)acc);
+    }
+    __syncthreads();
+    const uint32_t total = s_n[RESCORE_WARPS];
+    for (uint32_t base = 0; base < total; base += RESCORE_WARPS * 32) {
+        const uint32_t e = base + tid;
+        int r = -1;
         RescoreBest b;
         b.R = __longlong_as_double(0x7ff0000000000000ll); b.s = 0.0; b.o = 0.0; b.seq = ~0ull;
-        if (threadIdx.x == 0) { const RangeState st = state[bslot]; b.R = st.R; b.seq = st.seq; b.s = st.s; b.o = st.o; }
-        for (uint32_t e = threadIdx.x; e < n; e += RESCORE_WARPS * 32)
-            rescore_entry(list[(size_t)bslot * cap + e], rv[r], rs, sqr, poolA, sd4, sdd, NP, mode, b);
-        rescore_warp_reduce(b);
-        if (lane == 0) s_red[warp] = b;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            RescoreBest w = s_red[0];
-            for (int k = 1; k < RESCORE_WARPS; ++k)
-                if (fic_better(s_red[k].R, s_red[k].seq, w.R, w.seq)) w = s_red[k];
-            rescore_commit(bslot, state[bslot].ridx, w, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
+        unsigned long long key = ~0ull;
+        if (e < total) {
+            r = 0;   // last range whose offset is <= e (binary search over the 32 offsets; empty ranges share an offset)
+#pragma unroll
+            for (int step = RESCORE_WARPS / 2; step > 0; step >>= 1)
+                if (e >= s_n[r + step]) r += step;
+            const int rslot = blockIdx.x * RESCORE_WARPS + r;
+            rescore_entry(list[(size_t)rslot * cap + (e - s_n[r])], rv[r], s_rs[r], s_sq[r], poolA, sd4, sdd, NP, mode, b);
+            if (b.seq != ~0ull) {   // finite R
+                key = rescore_key(b.R);
+                atomicMin(&s_key[r], key);
+            }
         }
         __syncthreads();
+        if (tid < RESCORE_WARPS && s_key[tid] != s_prev[tid]) { s_prev[tid] = s_key[tid]; s_seq[tid] = ~0ull; }  // a better R: forget the old index
+        __syncthreads();
+        const bool contender = r >= 0 && b.seq != ~0ull && key == s_key[r];
+        if (contender) atomicMin(&s_seq[r], b.seq);
+        __syncthreads();
+        if (contender && s_seq[r] == b.seq) { s_R[r] = b.R; s_s[r] = b.s; s_o[r] = b.o; }   // duplicates write the same values
+        __syncthreads();
+    }
+    if (lane == 0 && s_ridx[warp] >= 0) {
+        RescoreBest w;
+        w.R = s_R[warp]; w.s = s_s[warp]; w.o = s_o[warp]; w.seq = s_seq[warp];
+        rescore_commit(slot, s_ridx[warp], w, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
     }
 }
 
@@ -1217,6 +1238,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RESCORE_SMEM));
         attr_set = true;
     }
     ScreenParams sp;
@@ -1246,10 +1268,11 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
         bf_seed_list_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(seed_best, n_ranges, PW, seed_S, seed_gx, cnt, list, cap);
         FIC_CHECK_LAUNCH(h, "bf_seed_list_kernel");
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0, mode,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
+    const bool prof_rescore = getenv("FIC_PROFILE_RESCORE") != nullptr;   // measurement knob: time the rescoring kernels instead
     // Round plan: nested strides m_1 > m_2 > ... > 1 over the candidate tiles.  A round's survivor count per range is
     // about (fraction screened now) / (fraction scored exactly before), so each round may look at ~128x more candidates
     // than everything before it; the first one is sized against the pre-scan sample.
@@ -1279,6 +1302,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         }
         int grid = probe ? 1 : h->num_sms;
         {
+            h->prof_suppress = prof_rescore;
             ProfScope prof(h, st);
             if (probe) bf_screen_kernel<1><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
             else if (sp.debug_mode == 1) bf_screen_kernel<2><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
@@ -1290,10 +1314,23 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         if (probe) return FIC_OK;
         // 5. exact rescoring of this round's survivors, merged into the range states
         const int emit = r + 1 == strides.size();
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, 0, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit, mode,
+        if (getenv("FIC_DBG_LISTS")) {   // measurement knob: survivor list lengths before this rescoring
+            std::vector<uint32_t> hc_(n_ranges);
+            cudaStreamSynchronize(st);
+            cudaMemcpy(hc_.data(), cnt, (size_t)n_ranges * 4, cudaMemcpyDeviceToHost);
+            std::sort(hc_.begin(), hc_.end());
+            unsigned long long sum = 0;
+            for (uint32_t v : hc_) sum += v;
+            fprintf(stderr, "round %zu lists: total %llu median %u p90 %u p99 %u max %u (cap %u)\n", r, sum, hc_[n_ranges / 2],
+                    hc_[(size_t)n_ranges * 9 / 10], hc_[(size_t)n_ranges * 99 / 100], hc_.back(), cap);
+        }
+        h->prof_suppress = !prof_rescore;
+        ProfScope prof_rs(h, st);
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }
+    h->prof_suppress = false;
 
     // 6. whatever the screen could not decide goes through the exact scan
     int* hc = h->pin_a.as<int>();
