@@ -467,42 +467,24 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         while (span.next(grp, j0, j1)) {
             mbar_wait(b_full, bph, p.err_flag, 3);
             bph ^= 1;
-            // one tile: wait for a free accumulator stage and for the A tile, issue the five MMAs, commit
-            auto issue_tile = [&](int s_, int as_, uint32_t ph_, uint32_t aph_) {
-                const uint64_t adesc = adesc0 + (uint64_t)(s_ * (A_MAIN_BYTES >> 4));
-                const uint64_t axdesc = axdesc0 + (uint64_t)(s_ * (A_EXT_BYTES >> 4));
-                const uint32_t d_tmem = tmem_base + (uint32_t)as_ * BN;
-                mbar_wait(tempty_bar(as_), aph_ ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
-                mbar_wait(full_bar(s_), ph_, p.err_flag, 5);          // TMA bytes have landed
+            for (int j = j0; j < j1; ++j) {
+                const uint64_t adesc = adesc0 + (uint64_t)(s * (A_MAIN_BYTES >> 4));
+                const uint64_t axdesc = axdesc0 + (uint64_t)(s * (A_EXT_BYTES >> 4));
+                const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
+                mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
+                mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
                 tcgen05_fence_after();
                 if (issuer) {
 #pragma unroll
                     for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
                     umma_f16(d_tmem, axdesc, bxdesc, IDESC, 1);
-                    tcgen05_commit(empty_bar(s_));   // frees the A stage once the MMAs above have completed
-                    tcgen05_commit(tfull_bar(as_));  // accumulator ready for the epilogue
+                    tcgen05_commit(empty_bar(s));   // frees the A stage once the MMAs above have completed
+                    tcgen05_commit(tfull_bar(as));  // accumulator ready for the epilogue
                 }
                 __syncwarp();
-            };
-            int j = j0;
-            while (j < j1) {
-                if (s == 0 && j + STAGES <= j1) {
-                    // a whole pass over the A ring with compile-time stage numbers: descriptors and barrier addresses are
-                    // loop invariants instead of per-tile arithmetic (this warp shares its scheduler with four epilogue
-                    // warps, which wait for every instruction it spends)
-                    issue_tile(0, 0, ph, aph);
-                    issue_tile(1, 1, ph, aph);
-                    issue_tile(2, 0, ph, aph ^ 1);
-                    issue_tile(3, 1, ph, aph ^ 1);
-                    ph ^= 1;
-                    j += STAGES;
-                } else {
-                    issue_tile(s, as, ph, aph);
-                    if (++s == STAGES) { s = 0; ph ^= 1; }
-                    if (++as == 2) { as = 0; aph ^= 1; }
-                    ++j;
-                }
+                if (++s == STAGES) { s = 0; ph ^= 1; }
+                if (++as == 2) { as = 0; aph ^= 1; }
             }
             if (issuer) tcgen05_commit(b_empty);
             __syncwarp();
