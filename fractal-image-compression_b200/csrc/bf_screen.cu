@@ -33,7 +33,7 @@
 // exact scan; constant ranges are decided by the seed list (every candidate ties at R = 0, the first one wins).
 // The NumPy encoder's semantics (bf_encoder.py) go through the same screen: see bf_init_kernel.
 //
-// GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 4-stage ring), N = 256 columns = 32 ranges
+// GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 5-stage ring), N = 256 columns = 32 ranges
 // x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
 // TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
 // tile t.  Warp roles: warps 0..15 epilogue, warp 16 TMA producer, warp 17 MMA issuer + TMEM allocator (both run in
@@ -65,7 +65,7 @@ constexpr int BM = 128;      // candidates per tile
 constexpr int BN = 256;      // columns per unit (32 ranges x 8 isometries)
 constexpr int KMAIN = 64;
 constexpr int KEXT = 16;
-constexpr int STAGES = 4;
+constexpr int STAGES = 5;
 constexpr int WARPS_PER_STAGE = 8;                    // epilogue warps per accumulator stage (two per TMEM lane quadrant)
 constexpr int EPI_WARPS = 2 * WARPS_PER_STAGE;
 // the scheduler favours high warp ids: the two single-thread roles sit ABOVE the epilogue warps so that the busy
@@ -526,13 +526,16 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
             // tile index of j without a division per tile: t = (j + j / (r_prev - 1) + 1) * m_cur, advanced by 2
-            int t_cur = j < j1 ? tile_of(p, j) : 0;
+            // The loop carries this lane's candidate index (tile * 128 + quadrant * 32 + lane) rather than the tile:
+            // the lane is then a mask away from a live register where it is needed (release, queue slot) and the
+            // compiler has less reason to re-read %tid.x -- a ~50-cycle S2R -- in the middle of a tile.
+            int cand = (j < j1 ? tile_of(p, j) : 0) * BM + lane_off;
             const int r1 = p.r_prev > 0 ? p.r_prev - 1 : 0x7fffffff;
             int rem = p.r_prev > 0 && j < j1 ? j % r1 : 0;
             // +-1/h_c of this lane's candidate, fetched one tile ahead; sign = conditioning class; +inf (threshold never
             // met) for the padding rows of the last tile
             const float hk_pad = __int_as_float(0x7f800000);
-            float hq_next = (j < j1 && t_cur * BM + lane_off < p.NP) ? p.hk[t_cur * BM + lane_off].x : hk_pad;
+            float hq_next = (j < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
             // the sixteen tau of the next tile (class picked by the sign of its hq) are fetched at the END of the current
             // tile, when both chunk buffers are dead, so the shared-memory latency is paid under the index arithmetic
             float4 tq0, tq1, tq2, tq3;
@@ -542,19 +545,18 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
             for (; j < j1; j += 2) {
                 // ---- everything up to the wait is off the accumulator's critical path (MMA -> epilogue -> MMA) ----
-                const int my_cand = t_cur * BM + lane_off;
-                {   // advance (t_cur, rem) to j + 2
+                const int my_cand = cand;
+                {   // advance to tile j + 2:  t = (j + j / (r_prev - 1) + 1) * m_cur without a division per tile
                     rem += 2;
                     int wraps = 0;
                     if (rem >= r1) { rem -= r1; wraps = 1; }
                     if (rem >= r1) { rem -= r1; wraps = 2; }   // r1 == 1 (r_prev == 2)
-                    t_cur += (2 + wraps) * p.m_cur;
+                    cand += (2 + wraps) * p.m_cur * BM;
                 }
                 const float hq = hq_next;
-                {
-                    const int next_cand = t_cur * BM + lane_off;
-                    hq_next = (j + 2 < j1 && next_cand < p.NP) ? p.hk[next_cand].x : hk_pad;
-                }
+                hq_next = (j + 2 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+                const int lane = my_cand & 31;            // shadows the outer lane on purpose
+                const uint32_t lane0 = lane == 0;
                 if (MODE == 5) {
                     // seed mode: no thresholds yet.  Rank the (few) candidates of the seed pool by the collage-error
                     // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
@@ -1163,12 +1165,12 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_ctrl.reserve(256));
-    // seed lattice: about NP/100 positions (at least 256, at most 4096), a whole number of candidate tiles
+    // seed lattice: about NP/50 positions (at least 256, at most 8192), a whole number of candidate tiles
     int seed_S, seed_gx, n_seed, n_seed_pad;
     {
-        double want = (double)NP / 100.0;
+        double want = (double)NP / 50.0;       // same-box sweeps on lena 512x512: 5 000 positions beat 2 500 and 7 500
         if (want < 256.0) want = 256.0;
-        if (want > 4096.0) want = 4096.0;
+        if (want > 8192.0) want = 8192.0;
         if (const char* e = getenv("FIC_SEED_POSITIONS")) want = atof(e) > 1.0 ? atof(e) : want;  // tuning knob
         seed_S = (int)floor(sqrt((double)NP / want) + 0.5);
         if (seed_S < 1) seed_S = 1;
