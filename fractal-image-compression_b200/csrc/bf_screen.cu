@@ -543,6 +543,10 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 16 : 0));
                 tq0 = tau4[0]; tq1 = tau4[1]; tq2 = tau4[2]; tq3 = tau4[3];
             }
+            float seed_gain[16];   // seed mode only: this lane's best candidate per range over the unit's tiles
+            int seed_cand[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { seed_gain[i] = 0.f; seed_cand[i] = 0; }
             for (; j < j1; j += 2) {
                 // ---- everything up to the wait is off the accumulator's critical path (MMA -> epilogue -> MMA) ----
                 const int my_cand = cand;
@@ -560,34 +564,38 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 if (MODE == 5) {
                     // seed mode: no thresholds yet.  Rank the (few) candidates of the seed pool by the collage-error
                     // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
-                    // one per range; it is scored exactly afterwards and provides the first upper bound.
+                    // one per range; it is scored exactly afterwards and provides the first upper bound.  Every lane keeps
+                    // its own best per range over the tiles of the unit; the warps merge them once, after the last tile.
                     const float den = my_cand < p.NP ? p.hk[my_cand].y : 0.f;
                     const float inv64 = den > 0.f ? 64.f / den : 0.f, den1024 = den * (1.0f / 1024.0f);
-                    uint32_t vs[32];
-                    mbar_wait(my_tfull, aph, p.err_flag, 6);
-                    tcgen05_fence_after();
-                    for (int c4 = 0; c4 < 4; ++c4) {
-                        tmem_ld32(taddr0 + c4 * 32, vs);
-                        tmem_ld_wait(vs);
+                    uint32_t va[32], vb[32];
+                    auto rank4 = [&](const uint32_t (&v)[32], int c4) {
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
-                            float m = fabsf(__uint_as_float(vs[g * 8]));
+                            float m = fabsf(__uint_as_float(v[g * 8]));
 #pragma unroll
-                            for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(vs[g * 8 + i])));
+                            for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v[g * 8 + i])));
                             const float gain = 256.f * m <= den ? m * m * inv64 : 0.5f * m - den1024;   // den == 0: m == 0
-                            const uint32_t bits = gain > 0.f ? __float_as_uint(gain) : 0u;
-                            const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
-                            if (wmax != 0u) {
-                                const unsigned who = __ballot_sync(0xffffffffu, bits == wmax);
-                                if (lane == __ffs(who) - 1)
-                                    atomicMax(&p.seed_best[slot0 + c4 * 4 + g],
-                                              ((unsigned long long)bits << 32) | (0xffffffffu - (uint32_t)my_cand));
-                            }
+                            if (gain > seed_gain[c4 * 4 + g]) { seed_gain[c4 * 4 + g] = gain; seed_cand[c4 * 4 + g] = my_cand; }
                         }
-                    }
+                    };
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    tmem_ld32(taddr0, va);
+                    tmem_ld32(taddr0 + 32, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    rank4(va, 0);
+                    tmem_ld32(taddr0 + 64, va);
+                    rank4(vb, 1);
+                    tmem_ld32(taddr0 + 96, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
                     tcgen05_fence_before();
                     __syncwarp();
                     if (lane0) mbar_arrive(my_tempty);
+                    rank4(va, 2);
+                    rank4(vb, 3);
                     aph ^= 1;
                     continue;
                 }
@@ -649,6 +657,15 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     tq0 = tau4[0]; tq1 = tau4[1]; tq2 = tau4[2]; tq3 = tau4[3];
                 }
                 if (MODE == 0 && qn >= QFLUSH) { queue_flush(queue, p, lane, qn); qn = 0; }
+            }
+            if (MODE == 5) {   // merge the lanes' seed candidates of this unit: warp maximum, then one atomic per range
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const uint32_t bits = seed_gain[i] > 0.f ? __float_as_uint(seed_gain[i]) : 0u;
+                    const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
+                    if (wmax != 0u && bits == wmax)   // ties (rare): every tied lane offers its candidate, the smaller index wins
+                        atomicMax(&p.seed_best[slot0 + i], ((unsigned long long)bits << 32) | (0xffffffffu - (uint32_t)seed_cand[i]));
+                }
             }
         }
         if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
