@@ -859,29 +859,6 @@ __global__ void bf_probe_state_kernel(const uint2* __restrict__ sums, int range_
     }
 }
 
-// thresholds of the next round from the running winners.  A range whose bound is not clearly below its own variance
-// (or that has no finite winner) cannot be screened: it is handed to the exact scan and never passes anything.
-__global__ void bf_retau_kernel(RangeState* __restrict__ state, int* __restrict__ ctrl, float2* __restrict__ tau,
-                                int32_t* __restrict__ fallback)
-{
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= ctrl[0]) return;
-    const RangeState st = state[slot];
-    float2 t = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-    if (st.flags == 0) {
-        const double ub = st.R;
-        const double TA = st.TA0 - 64.0 * ub, TB = TA - 64.0 * GUARD_ILL;
-        if (ub == ub && ub < 1e300 && TA > 1e-3) {
-            t.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);     // rounded down a little: never over-estimate
-            t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
-        } else {
-            state[slot].flags = 1;
-            fallback[atomicAdd(&ctrl[1], 1)] = st.ridx;
-        }
-    }
-    tau[slot] = t;
-}
-
 // ---- range operand: 8 inverse-transformed, centred copies of every eligible range -------------------------------
 __global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const RangeState* __restrict__ state,
                                   const int* __restrict__ ctrl, int n_cols_pad, __half* __restrict__ rngB,
@@ -984,14 +961,17 @@ __device__ __forceinline__ void rescore_warp_reduce(RescoreBest& b)
 
 // one thread: store the winner of `slot` (and emit the record in the last round)
 __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeState* __restrict__ state, int* __restrict__ ctrl,
-                               uint32_t* __restrict__ cnt, int32_t* __restrict__ fallback, int emit, int range_begin, int PW,
-                               int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+                               uint32_t* __restrict__ cnt, int32_t* __restrict__ fallback, float2* __restrict__ tau, int emit,
+                               int range_begin, int PW, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                               double* __restrict__ out_R)
 {
+    const float never = __int_as_float(0x7f800000);
     cnt[slot] = 0;  // the next round starts from an empty list
-    if (b.seq == ~0ull) {  // nothing finite at all (the pre-scan found nothing either): exact scan decides
+    if (b.seq == ~0ull) {  // nothing finite at all: exact scan decides
         int at = atomicAdd(&ctrl[1], 1);
         fallback[at] = ridx;
         state[slot].flags = 1;
+        tau[slot] = make_float2(never, never);
         return;
     }
     state[slot].R = b.R; state[slot].seq = b.seq; state[slot].s = b.s; state[slot].o = b.o;
@@ -1005,15 +985,30 @@ __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeSt
         out_so[2 * os_] = b.s;
         out_so[2 * os_ + 1] = b.o;
         out_R[os_] = b.R;
+        return;
     }
+    // Thresholds of the next round from the new winner.  A range whose bound is not clearly below its own variance
+    // cannot be screened: it is handed to the exact scan and never passes anything.
+    float2 t = make_float2(never, never);
+    if (state[slot].flags == 0) {
+        const double TA = state[slot].TA0 - 64.0 * b.R, TB = TA - 64.0 * GUARD_ILL;
+        if (b.R == b.R && b.R < 1e300 && TA > 1e-3) {
+            t.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);     // rounded down a little: never over-estimate
+            t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+        } else {
+            state[slot].flags = 1;
+            fallback[atomicAdd(&ctrl[1], 1)] = ridx;
+        }
+    }
+    tau[slot] = t;
 }
 
 __global__ void __launch_bounds__(RESCORE_WARPS * 32, 1)   // 1024 threads x 64 registers: a long list is walked 1024 entries at a time
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
-                  int32_t* __restrict__ fallback, int emit, int mode, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
-                  double* __restrict__ out_R)
+                  int32_t* __restrict__ fallback, float2* __restrict__ tau, int emit, int mode, int32_t* __restrict__ out_idx,
+                  double* __restrict__ out_so, double* __restrict__ out_R)
 {
     extern __shared__ float rv_raw[];
     float (*rv)[8][65] = reinterpret_cast<float (*)[8][65]>(rv_raw);   // inverse-transformed range per isometry, padded against bank conflicts
@@ -1041,6 +1036,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
                 fallback[at] = ridx;
                 state[slot].flags = 1;
                 cnt[slot] = 0;
+                tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
             }
         } else {
             const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
@@ -1110,7 +1106,7 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
     if (lane == 0 && s_ridx[warp] >= 0) {
         RescoreBest w;
         w.R = s_R[warp]; w.s = s_s[warp]; w.o = s_o[warp]; w.seq = s_seq[warp];
-        rescore_commit(slot, s_ridx[warp], w, state, ctrl, cnt, fallback, emit, range_begin, PW, out_idx, out_so, out_R);
+        rescore_commit(slot, s_ridx[warp], w, state, ctrl, cnt, fallback, tau, emit, range_begin, PW, out_idx, out_so, out_R);
     }
 }
 
@@ -1287,7 +1283,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
         bf_seed_list_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(seed_best, n_ranges, PW, seed_S, seed_gx, cnt, list, cap);
         FIC_CHECK_LAUNCH(h, "bf_seed_list_kernel");
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, 0, mode,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, tau, 0, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
@@ -1315,10 +1311,6 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         sp.m_cur = strides[r];
         sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
         sp.n_round_tiles = cdiv(n_tiles, strides[r]) - (r == 0 ? 0 : cdiv(n_tiles, strides[r - 1]));
-        if (!probe) {
-            bf_retau_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(state, ctrl, tau, fallback);
-            FIC_CHECK_LAUNCH(h, "bf_retau_kernel");
-        }
         int grid = probe ? 1 : h->num_sms;
         {
             h->prof_suppress = prof_rescore;
@@ -1345,7 +1337,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         }
         h->prof_suppress = !prof_rescore;
         ProfScope prof_rs(h, st);
-        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, emit, mode,
+        bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, tau, emit, mode,
                                                     d_idx, d_so, d_R);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }
