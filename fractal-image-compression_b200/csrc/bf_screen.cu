@@ -746,54 +746,49 @@ struct RangeState {
     int rsum, pad_;                // sum of the range's 64 pixels
 };
 
-// sum and sum of squares of every range of the slice, one warp per range (the serial consumers below only read them)
-// sqw = the NumPy encoder's sum of squares: bf_encoder.py:33 squares the uint8 pixels in uint8, every term wraps mod 256
-__global__ void bf_rangesum_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, uint2* __restrict__ sums,
-                                   uint32_t* __restrict__ sqw)
+// ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
+// One warp per slot (the slots are padded to whole column groups).  Every range of the slice gets a slot in natural
+// order; its sum and sums of squares come from a warp reduction over the 64 pixels.  Nothing is known about the winners
+// yet: R = +inf, no candidate, thresholds +inf (nothing passes), empty survivor list; constant ranges are flagged, they
+// are decided by the seed list alone (every candidate scores R = 0 exactly, the first in scan order -- position 0,
+// isometry 0 -- wins).
+// NumPy mode: bf_encoder.py:33 squares the uint8 pixels in uint8, every term wraps mod 256, so the reference's R carries
+// the wrapped sum of squares, R_ref = R_true - (q - qw)/64 for every candidate of the range alike; the bound is on
+// R_true, so the shift goes into the threshold numerator once.
+__global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode, int range_begin, int n_ranges,
+                               RangeState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
+                               unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad)
 {
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (slot >= tau_pad) return;
+    if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
+    if (lane == 0) {
+        tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+        seed_best[slot] = 0ull;
+    }
     if (slot >= n_ranges) return;
     const int rw = W / 8, ridx = range_begin + slot;
     const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
     const unsigned r0 = img[(size_t)(ri + (lane >> 3)) * W + rj + (lane & 7)];
     const unsigned r1 = img[(size_t)(ri + 4 + (lane >> 3)) * W + rj + (lane & 7)];
-    unsigned sm = r0 + r1, q = r0 * r0 + r1 * r1, qw = ((r0 * r0) & 255u) + ((r1 * r1) & 255u);
+    unsigned sm = r0 + r1, q32 = r0 * r0 + r1 * r1, qw = ((r0 * r0) & 255u) + ((r1 * r1) & 255u);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
         sm += __shfl_xor_sync(0xffffffffu, sm, off);
-        q += __shfl_xor_sync(0xffffffffu, q, off);
+        q32 += __shfl_xor_sync(0xffffffffu, q32, off);
         qw += __shfl_xor_sync(0xffffffffu, qw, off);
     }
-    if (lane == 0) { sums[slot] = make_uint2(sm, q); sqw[slot] = qw; }
-}
-
-// ctrl[0] = n_elig, ctrl[1] = n_fallback, ctrl[2] = error flag, ctrl[8..9] = survivors rescored (u64)
-// Every range of the slice gets a slot in natural order.  Nothing is known about the winners yet: R = +inf, no
-// candidate, thresholds +inf (nothing passes); constant ranges are flagged, they are decided by the seed list alone
-// (every candidate scores R = 0 exactly, the first in scan order -- position 0, isometry 0 -- wins).
-// NumPy mode: the reference's R carries the wrapped sum of squares, R_ref = R_true - (q - qw)/64 for every candidate of
-// the range alike; the bound is on R_true, so the shift goes into the threshold numerator once.
-__global__ void bf_init_kernel(const uint2* __restrict__ sums, const uint32_t* __restrict__ sqw, int mode, int range_begin,
-                               int n_ranges, RangeState* __restrict__ state, float2* __restrict__ tau,
-                               unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad)
-{
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k == 0) { ctrl[0] = n_ranges; ctrl[1] = 0; }
-    if (k < tau_pad) {
-        tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-        seed_best[k] = 0ull;
-    }
-    if (k < n_ranges) {
-        const uint2 sq_ = sums[k];
-        const long long s = sq_.x, q = sq_.y;
+    if (lane == 0) {
+        const long long s = sm, q = q32;
         const long long A64 = 64 * q - s * s;                             // 64 * A_r, exact
         RangeState st;
         st.R = __longlong_as_double(0x7ff0000000000000ll); st.s = 0.0; st.o = 0.0;
         st.TA0 = (double)A64 * 0.015625 - 64e-9 * (double)q;
-        if (mode == FIC_BF_MODE_NUMPY) st.TA0 -= (double)(q - (long long)sqw[k]);
-        st.seq = ~0ull; st.ridx = range_begin + k; st.flags = A64 == 0 ? 2 : 0;
+        if (mode == FIC_BF_MODE_NUMPY) st.TA0 -= (double)(q - (long long)qw);
+        st.seq = ~0ull; st.ridx = ridx; st.flags = A64 == 0 ? 2 : 0;
         st.rsum = (int)s; st.pad_ = 0;
-        state[k] = st;
+        state[slot] = st;
+        cnt[slot] = 0;
     }
 }
 
@@ -842,21 +837,6 @@ __global__ void bf_seed_list_kernel(const unsigned long long* __restrict__ seed_
         for (uint32_t t = 0; t < 8; ++t) l[n++] = p * 8u + t;
     }
     cnt[slot] = n;
-}
-
-// probe mode: every range eligible in natural order, nothing ever passes
-__global__ void bf_probe_state_kernel(const uint2* __restrict__ sums, int range_begin, int n_ranges, RangeState* __restrict__ state,
-                                      float2* __restrict__ tau, int* __restrict__ ctrl, int tau_pad)
-{
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k == 0) { ctrl[0] = n_ranges; ctrl[1] = 0; }
-    if (k < tau_pad) tau[k] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-    if (k < n_ranges) {
-        RangeState st;
-        st.R = 0.0; st.s = 0.0; st.o = 0.0; st.TA0 = 0.0; st.seq = 0; st.ridx = range_begin + k; st.flags = 0;
-        st.rsum = (int)sums[k].x; st.pad_ = 0;
-        state[k] = st;
-    }
 }
 
 // ---- range operand: 8 inverse-transformed, centred copies of every eligible range -------------------------------
@@ -1204,9 +1184,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     __half* rngBx = rngB + (size_t)n_cols_pad * 64;
     RangeState* state = h->bf_thr.as<RangeState>();                                   // 8-byte aligned members first
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
-    uint2* rsums = reinterpret_cast<uint2*>(tau + tau_pad);
-    int32_t* fallback = reinterpret_cast<int32_t*>(rsums + n_ranges);
-    uint32_t* rsqw = reinterpret_cast<uint32_t*>(fallback + n_ranges);
+    int32_t* fallback = reinterpret_cast<int32_t*>(tau + tau_pad);
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
@@ -1216,24 +1194,14 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     __half* seedA = reinterpret_cast<__half*>(seed_raw + off_seedA);
     __half* seedAx = reinterpret_cast<__half*>(seed_raw + off_seedAx);
 
-    FIC_CUDA(cudaMemsetAsync(ctrl, 0, 64, st));
-    FIC_CUDA(cudaMemsetAsync(cnt, 0, (size_t)n_ranges * 4, st));
-
     // 1. pool (independent of the ranges)
     bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
-    bf_rangesum_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, rsums, rsqw);
-    FIC_CHECK_LAUNCH(h, "bf_rangesum_kernel");
-
-    // 2. range states: all eligible in natural order, nothing known yet (probe: same, thresholds stay +inf)
-    if (!probe) {
-        bf_init_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, rsqw, mode, range_begin, n_ranges, state, tau, seed_best, ctrl, tau_pad);
-        FIC_CHECK_LAUNCH(h, "bf_init_kernel");
-    } else {
-        bf_probe_state_kernel<<<cdiv(tau_pad, 256), 256, 0, st>>>(rsums, range_begin, n_ranges, state, tau, ctrl, tau_pad);
-        FIC_CHECK_LAUNCH(h, "bf_probe_state_kernel");
-    }
+    // 2. range states: all eligible in natural order, nothing known yet (also clears the control block and the lists;
+    //    the probe keeps these thresholds: nothing ever passes)
+    bf_init_kernel<<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad);
+    FIC_CHECK_LAUNCH(h, "bf_init_kernel");
 
     // 3. range operand
     bf_rangeop_kernel<<<cdiv(n_cols_pad, 4), 256, 0, st>>>(d_img, W, state, ctrl, n_cols_pad, rngB, rngBx);
