@@ -45,7 +45,7 @@
 //   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
 //   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
 //   hk      float2 [NP]    (+-1/h_c, den16); a negative .x marks an ill-conditioned domain, .y only ranks seed candidates
-// and by bf_rangeop_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
+// and by bf_init_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
 #include <algorithm>
 #include <vector>
 #include <cuda.h>
@@ -757,10 +757,19 @@ struct RangeState {
 // R_true, so the shift goes into the threshold numerator once.
 __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode, int range_begin, int n_ranges,
                                RangeState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
-                               unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad)
+                               unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
+                               __half* __restrict__ rngB, __half* __restrict__ rngBx)
 {
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (slot >= tau_pad) return;
+    if (slot >= n_ranges) {   // padding columns of the last group: zero operand
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            rngB[((size_t)slot * 8 + t) * 64 + lane] = __float2half_rn(0.f);
+            rngB[((size_t)slot * 8 + t) * 64 + 32 + lane] = __float2half_rn(0.f);
+            if (lane < 16) rngBx[((size_t)slot * 8 + t) * 16 + lane] = __float2half_rn(0.f);
+        }
+    }
     if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
     if (lane == 0) {
         tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
@@ -777,6 +786,29 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
         sm += __shfl_xor_sync(0xffffffffu, sm, off);
         q32 += __shfl_xor_sync(0xffffffffu, q32, off);
         qw += __shfl_xor_sync(0xffffffffu, qw, off);
+    }
+    {
+        // range operand (rngB fp16 [cols][64], rngBx [cols][16], column = slot * 8 + isometry): eight inverse-transformed
+        // copies of the range centred by the integer m = round(mean); extension column 0 carries rho = sum - 64 m.
+        // Entry k = (sa,sb) of column t holds r'[i][j] with (sa,sb) = iso_t(i,j): invert fic_iso_bf.
+        const int m = ((int)sm + 32) >> 6, rho = (int)sm - 64 * m;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int k = lane + 32 * half, sa = k >> 3, sb = k & 7;
+                const int a = (t >> 2) ? sb : sa, b = (t >> 2) ? sa : sb;  // undo the transpose
+                int i, j;
+                switch (t & 3) {
+                case 0: i = a; j = b; break;
+                case 1: j = a; i = 7 - b; break;          // a = j, b = 7 - i
+                case 2: i = 7 - a; j = 7 - b; break;
+                default: j = 7 - a; i = b; break;         // a = 7 - j, b = i
+                }
+                rngB[((size_t)slot * 8 + t) * 64 + k] = __int2half_rn((int)img[(size_t)(ri + i) * W + rj + j] - m);
+            }
+            if (lane < 16) rngBx[((size_t)slot * 8 + t) * 16 + lane] = lane == 0 ? __int2half_rn(rho) : __float2half_rn(0.f);
+        }
     }
     if (lane == 0) {
         const long long s = sm, q = q32;
@@ -837,41 +869,6 @@ __global__ void bf_seed_list_kernel(const unsigned long long* __restrict__ seed_
         for (uint32_t t = 0; t < 8; ++t) l[n++] = p * 8u + t;
     }
     cnt[slot] = n;
-}
-
-// ---- range operand: 8 inverse-transformed, centred copies of every eligible range -------------------------------
-__global__ void bf_rangeop_kernel(const uint8_t* __restrict__ img, int W, const RangeState* __restrict__ state,
-                                  const int* __restrict__ ctrl, int n_cols_pad, __half* __restrict__ rngB,
-                                  __half* __restrict__ rngBx)
-{
-    const int col = blockIdx.x * 4 + (threadIdx.x >> 6);  // 4 columns per 256-thread block
-    const int k = threadIdx.x & 63;
-    if (col >= n_cols_pad) return;
-    const int slot = col >> 3, t = col & 7;
-    const int n_elig = ctrl[0];
-    __half out = __float2half_rn(0.f);
-    int rho = 0;
-    if (slot < n_elig) {
-        const int rw = W / 8;
-        const int ridx = state[slot].ridx;
-        const int ri = (ridx / rw) * 8, rj = (ridx % rw) * 8;
-        const int s = state[slot].rsum;
-        const int m = (s + 32) >> 6;
-        rho = s - 64 * m;
-        // entry k = (sa,sb) of column t holds r'[i][j] with (sa,sb) = iso_t(i,j): invert fic_iso_bf
-        const int sa = k >> 3, sb = k & 7;
-        const int a = (t >> 2) ? sb : sa, b = (t >> 2) ? sa : sb;  // undo the transpose
-        int i, j;
-        switch (t & 3) {
-        case 0: i = a; j = b; break;
-        case 1: j = a; i = 7 - b; break;          // a = j, b = 7 - i
-        case 2: i = 7 - a; j = 7 - b; break;
-        default: j = 7 - a; i = b; break;         // a = 7 - j, b = i
-        }
-        out = __int2half_rn((int)img[(size_t)(ri + i) * W + rj + j] - m);
-    }
-    rngB[(size_t)col * 64 + k] = out;
-    if (k < 16) rngBx[(size_t)col * 16 + k] = (k == 0 && slot < n_elig) ? __int2half_rn(rho) : __float2half_rn(0.f);
 }
 
 // ---- exact rescoring of the survivors: one warp per eligible range, merges into the range state -------------------
@@ -1198,14 +1195,10 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
-    // 2. range states: all eligible in natural order, nothing known yet (also clears the control block and the lists;
+    // 2. range states and the range operand: all eligible in natural order, nothing known yet (also clears the control block and the lists;
     //    the probe keeps these thresholds: nothing ever passes)
-    bf_init_kernel<<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad);
+    bf_init_kernel<<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad, rngB, rngBx);
     FIC_CHECK_LAUNCH(h, "bf_init_kernel");
-
-    // 3. range operand
-    bf_rangeop_kernel<<<cdiv(n_cols_pad, 4), 256, 0, st>>>(d_img, W, state, ctrl, n_cols_pad, rngB, rngBx);
-    FIC_CHECK_LAUNCH(h, "bf_rangeop_kernel");
 
     // 4. the screen, in two rounds
     CUtensorMap mapA, mapAx, mapB, mapBx;
