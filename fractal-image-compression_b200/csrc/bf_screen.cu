@@ -852,25 +852,6 @@ __global__ void bf_seed_gather_kernel(const __half* __restrict__ poolA, const __
     }
 }
 
-// first survivor list of every range: position 0 / isometry 0 (decides constant ranges, and the exact scan visits it
-// first anyway) plus the eight isometries of the best-ranked seed candidate
-__global__ void bf_seed_list_kernel(const unsigned long long* __restrict__ seed_best, int n_ranges, int PW, int S, int gx,
-                                    uint32_t* __restrict__ cnt, uint32_t* __restrict__ list, uint32_t cap)
-{
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_ranges) return;
-    uint32_t* l = list + (size_t)slot * cap;
-    uint32_t n = 0;
-    l[n++] = 0u;
-    const unsigned long long key = seed_best[slot];
-    if (key != 0ull) {
-        const uint32_t k = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
-        const uint32_t p = (k / (uint32_t)gx) * (uint32_t)S * (uint32_t)PW + (k % (uint32_t)gx) * (uint32_t)S;
-        for (uint32_t t = 0; t < 8; ++t) l[n++] = p * 8u + t;
-    }
-    cnt[slot] = n;
-}
-
 // ---- exact rescoring of the survivors: one warp per eligible range, merges into the range state -------------------
 // The survivor's pooled block is read back from the TMA pool (one 128-byte row, D4 = D4' + m_c), the dot product is
 // an exact integer sum in fp32, the score is the float64 restatement of jit_bfencoder.py:64-95 (scorer.cuh).
@@ -983,9 +964,10 @@ __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeSt
 __global__ void __launch_bounds__(RESCORE_WARPS * 32, 1)   // 1024 threads x 64 registers: a long list is walked 1024 entries at a time
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
-                  int* __restrict__ ctrl, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
+                  int* __restrict__ ctrl, uint32_t* __restrict__ cnt, uint32_t* list /* written in the seed round */, uint32_t cap,
                   int32_t* __restrict__ fallback, float2* __restrict__ tau, int emit, int mode, int32_t* __restrict__ out_idx,
-                  double* __restrict__ out_so, double* __restrict__ out_R)
+                  double* __restrict__ out_so, double* __restrict__ out_R, const unsigned long long* __restrict__ seed_best,
+                  int seed_S, int seed_gx)
 {
     extern __shared__ float rv_raw[];
     float (*rv)[8][65] = reinterpret_cast<float (*)[8][65]>(rv_raw);   // inverse-transformed range per isometry, padded against bank conflicts
@@ -1003,7 +985,25 @@ bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ po
     if (lane == 0) { s_n[warp] = 0; s_ridx[warp] = -1; }
     if (slot < n_elig) {
         const RangeState st = state[slot];
-        const uint32_t n = cnt[slot];
+        uint32_t n;
+        if (seed_best) {
+            // seed round: the list is written here -- position 0 / isometry 0 (decides constant ranges, and the exact scan
+            // visits it first anyway) plus the eight isometries of the best-ranked seed candidate (lattice node k / gx,
+            // k % gx); same-CTA readers see it after the barrier below
+            const unsigned long long key = seed_best[slot];
+            n = key != 0ull ? 9u : 1u;
+            if (lane < n) {
+                uint32_t ent = 0u;
+                if (lane > 0) {
+                    const uint32_t k = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+                    const uint32_t pos = (k / (uint32_t)seed_gx) * (uint32_t)seed_S * (uint32_t)PW + (k % (uint32_t)seed_gx) * (uint32_t)seed_S;
+                    ent = pos * 8u + (uint32_t)(lane - 1);
+                }
+                list[(size_t)slot * cap + lane] = ent;
+            }
+        } else {
+            n = cnt[slot];
+        }
         const int ridx = st.ridx;
         if (st.flags & 1) {
             // already handed to the exact scan
@@ -1242,10 +1242,8 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
             bf_screen_kernel<5><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapSx, mapB, mapBx, ss);
         }
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
-        bf_seed_list_kernel<<<cdiv(n_ranges, 256), 256, 0, st>>>(seed_best, n_ranges, PW, seed_S, seed_gx, cnt, list, cap);
-        FIC_CHECK_LAUNCH(h, "bf_seed_list_kernel");
         bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, tau, 0, mode,
-                                                    d_idx, d_so, d_R);
+                                                    d_idx, d_so, d_R, seed_best, seed_S, seed_gx);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
     const bool prof_rescore = getenv("FIC_PROFILE_RESCORE") != nullptr;   // measurement knob: time the rescoring kernels instead
@@ -1299,7 +1297,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         h->prof_suppress = !prof_rescore;
         ProfScope prof_rs(h, st);
         bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, tau, emit, mode,
-                                                    d_idx, d_so, d_R);
+                                                    d_idx, d_so, d_R, nullptr, 0, 0);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel");
     }
     h->prof_suppress = false;
