@@ -2,7 +2,7 @@
 // CUDA-core scan (bf_exact.cu).  Both produce the reference's records bit for bit; the screen is only a filter.
 #include "fic_common.cuh"
 
-int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st);
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
 int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int mode, int range_begin,
                    int n_ranges, const int32_t* d_range_list, int32_t* d_idx, double* d_so, double* d_R,
                    cudaStream_t st);
@@ -20,9 +20,9 @@ int bf_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int range,
     if (range != 8) return bf_exact_generic(h, d_img, H, W, range, si, sj, mode, range_begin, n, d_idx, d_so, d_R, st);
     const long long nq = (long long)(H - 16 > 0 ? (H - 16 + si - 1) / si : 0) * (W - 16 > 0 ? (W - 16 + sj - 1) / sj : 0);
     FIC_REQUIRE(nq * 8 < 0xffffffffll, "fic_bf_encode: %lld candidates per range exceed the 32-bit scan index", nq * 8);
-    FIC_TRY(bf_prepare8(h, d_img, H, W, st));
     const bool screen = si == 1 && sj == 1 && !(flags & FIC_BF_EXACT_ONLY) &&
                         bf_screen_applicable(H, W);
+    FIC_TRY(bf_prepare8(h, d_img, H, W, !screen, st));   // the screen's pool kernel computes the position statistics itself
     if (screen) return bf_screen_encode8(h, d_img, H, W, mode, range_begin, n, d_idx, d_so, d_R, flags, st);
     return bf_exact_scan8(h, d_img, H, W, si, sj, mode, range_begin, n, nullptr, d_idx, d_so, d_R, st);
 }

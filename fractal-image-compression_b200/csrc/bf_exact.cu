@@ -393,7 +393,8 @@ bf_scan_generic_kernel(const uint8_t* __restrict__ img, int H, int W, int R, int
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 // Builds boxsum + stats for an 8x8 encode (shared with the screen path).
-int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st)
+// with_stats = false: the caller's own pool kernel fills sd4 / sq4 / sdd (bf_screen.cu), only the buffers are reserved
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st)
 {
     const int PW = W - 16, PH = H - 16;
     FIC_TRY(h->bf_boxsum.reserve((size_t)(H - 1) * (W - 1) * sizeof(uint16_t)));
@@ -406,8 +407,10 @@ int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t 
         uint32_t* sd4 = h->bf_stats.as<uint32_t>();
         uint32_t* sq4 = sd4 + NP;
         float* sdd = reinterpret_cast<float*>(sq4 + NP);
-        bf_stats_kernel<<<ceil_div(NP, 128), 128, 0, st>>>(h->bf_boxsum.as<uint16_t>(), H, W, sd4, sq4, sdd);
-        FIC_CHECK_LAUNCH(h, "bf_stats_kernel");
+        if (with_stats) {
+            bf_stats_kernel<<<ceil_div(NP, 128), 128, 0, st>>>(h->bf_boxsum.as<uint16_t>(), H, W, sd4, sq4, sdd);
+            FIC_CHECK_LAUNCH(h, "bf_stats_kernel");
+        }
     }
     return FIC_OK;
 }

@@ -679,8 +679,11 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 }
 
 // ---- pool kernel: 2x pooling + centring + statistics, one thread per stride-1 position ------------------------
+// Also the per-position statistics of the exact scorer (the same values bf_stats_kernel of bf_exact.cu produces: this
+// path skips that launch): sd4 = sum D4, sq4 = sum D4^2, sdd[t] = float32 sequential sum of d^2 in the order of isometry t.
 __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
-                               __half* __restrict__ poolAx, float2* __restrict__ hk)
+                               __half* __restrict__ poolAx, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
+                               uint32_t* __restrict__ sq4, float* __restrict__ sdd)
 {
     const int PW = W - 16, PH = H - 16, BW = W - 1;
     const int NP = PW * PH;
@@ -733,6 +736,28 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
         kc = (float)d;                                         // den16, only used to rank seed candidates
     }
     hk[p] = make_float2(hc, kc);
+    sd4[p] = (uint32_t)s;
+    sq4[p] = (uint32_t)s2;
+    float sq[64];
+#pragma unroll
+    for (int k = 0; k < 64; ++k) {
+        const float d = __fmul_rn((float)v[k], 0.25f);
+        sq[k] = __fmul_rn(d, d);  // exact: v^2/16 < 2^24 significant bits
+    }
+    // fully unrolled: the isometry index maps become compile-time constants and sq[] stays in registers
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                int sa, sb;
+                fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
+                acc = __fadd_rn(acc, sq[sa * 8 + sb]);
+            }
+        sdd[(size_t)t * NP + p] = acc;
+    }
 }
 
 // ---- per-range state --------------------------------------------------------------------------------------------
@@ -1140,8 +1165,8 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
     const int tau_pad = n_cols_pad / 8;
     const uint16_t* P = h->bf_boxsum.as<uint16_t>();
-    const uint32_t* sd4 = h->bf_stats.as<uint32_t>();
-    const float* sdd = reinterpret_cast<const float*>(sd4 + 2 * (size_t)NP);
+    uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    float* sdd = reinterpret_cast<float*>(sd4 + 2 * (size_t)NP);
 
     // survivor capacity per range: bounded by a 1 GiB list
     uint32_t cap = 8192;
@@ -1192,7 +1217,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     __half* seedAx = reinterpret_cast<__half*>(seed_raw + off_seedAx);
 
     // 1. pool (independent of the ranges)
-    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk);
+    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk, sd4, sd4 + NP, sdd);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
     // 2. range states and the range operand: all eligible in natural order, nothing known yet (also clears the control block and the lists;

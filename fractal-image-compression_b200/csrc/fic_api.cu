@@ -3,7 +3,7 @@
 
 #include "fic_common.cuh"
 
-int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, cudaStream_t st);
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
 int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_ranges, int32_t* d_idx,
                   double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st);
 
@@ -221,7 +221,7 @@ int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int ran
         d_out = h->d_out_a.as<float>();
     }
     FIC_CUDA(cudaMemsetAsync(d_out, 0, rows * 256 * sizeof(float), st));
-    FIC_TRY(bf_prepare8(h, d_img, H, W, st));
+    FIC_TRY(bf_prepare8(h, d_img, H, W, false, st));
     FIC_TRY(bf_screen_run(h, d_img, H, W, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, nullptr, nullptr, flags, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out_u, d_out, rows * 256 * sizeof(float), false, st));
