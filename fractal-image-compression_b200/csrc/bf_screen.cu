@@ -683,13 +683,30 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 // path skips that launch): sd4 = sum D4, sq4 = sum D4^2, sdd[t] = float32 sequential sum of d^2 in the order of isometry t.
 __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
                                __half* __restrict__ poolAx, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
-                               uint32_t* __restrict__ sq4, float* __restrict__ sdd)
+                               uint32_t* __restrict__ sq4, float* __restrict__ sdd, int seed_S, int seed_gx, int n_seed,
+                               int n_seed_pad, __half* __restrict__ seedA, __half* __restrict__ seedAx,
+                               float2* __restrict__ seedhk)
 {
     const int PW = W - 16, PH = H - 16, BW = W - 1;
     const int NP = PW * PH;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= NP) return;
     const int di = p / PW, dj = p - di * PW;
+    // seed pool: the lattice nodes (every seed_S-th row and column) get a second copy in a small pool of their own; seed
+    // candidate k sits at node (k / gx, k % gx); rows n_seed .. n_seed_pad are padding (zero rows, den16 = 0)
+    int seed_k = -1;
+    if (seedA) {
+        if (di % seed_S == 0 && dj % seed_S == 0) seed_k = (di / seed_S) * seed_gx + dj / seed_S;
+        if (p < n_seed_pad - n_seed) {
+            uint4* za = reinterpret_cast<uint4*>(seedA + (size_t)(n_seed + p) * 64);
+            uint4* zx = reinterpret_cast<uint4*>(seedAx + (size_t)(n_seed + p) * 16);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) za[q] = make_uint4(0u, 0u, 0u, 0u);
+            zx[0] = make_uint4(0u, 0u, 0u, 0u);
+            zx[1] = make_uint4(0u, 0u, 0u, 0u);
+            seedhk[n_seed + p] = make_float2(__int_as_float(0x7f800000), 0.f);
+        }
+    }
     int v[64];
     int s = 0;
     long long s2 = 0;
@@ -717,12 +734,18 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
         o.z = *reinterpret_cast<uint32_t*>(&h2);
         o.w = *reinterpret_cast<uint32_t*>(&h3);
         dst[q] = o;
+        if (seed_k >= 0) reinterpret_cast<uint4*>(seedA + (size_t)seed_k * 64)[q] = o;
     }
     uint4* dx = reinterpret_cast<uint4*>(poolAx + (size_t)p * 16);
     __half2 e0 = __halves2half2(__float2half_rn(-(float)eps * 0.015625f), __float2half_rn(0.f));  // exact: |eps|/64 <= 0.5, 6 bits
     uint4 ox = make_uint4(*reinterpret_cast<uint32_t*>(&e0), 0u, 0u, 0u);
     dx[0] = ox;
     dx[1] = make_uint4(0u, 0u, 0u, 0u);
+    if (seed_k >= 0) {
+        uint4* sx = reinterpret_cast<uint4*>(seedAx + (size_t)seed_k * 16);
+        sx[0] = ox;
+        sx[1] = make_uint4(0u, 0u, 0u, 0u);
+    }
     const long long den16 = 64ll * s2 - (long long)s * s;  // >= 0, exact
     // q_c = 1/h_c, rounded DOWN a little so that theta = tau*q - DELTA never over-estimates; +inf for a constant domain
     // (den16 == 0: u == 0 exactly, s_ref == 0, R_ref == A_r/64 without noise -> it can never beat tau_A > 0)
@@ -736,6 +759,7 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
         kc = (float)d;                                         // den16, only used to rank seed candidates
     }
     hk[p] = make_float2(hc, kc);
+    if (seed_k >= 0) seedhk[seed_k] = make_float2(hc, kc);
     sd4[p] = (uint32_t)s;
     sq4[p] = (uint32_t)s2;
     float sq[64];
@@ -846,34 +870,6 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
         st.rsum = (int)s; st.pad_ = 0;
         state[slot] = st;
         cnt[slot] = 0;
-    }
-}
-
-// ---- seed pool: a coarse lattice of candidate positions, gathered into its own small TMA pool ----------------------
-// seed candidate k sits at lattice node (k / gx, k % gx) * S; rows beyond n_seed are padding (zero rows, den16 = 0)
-__global__ void bf_seed_gather_kernel(const __half* __restrict__ poolA, const __half* __restrict__ poolAx,
-                                      const float2* __restrict__ hk, int PW, int S, int gx, int n_seed, int n_seed_pad,
-                                      __half* __restrict__ seedA, __half* __restrict__ seedAx, float2* __restrict__ seedhk)
-{
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n_seed_pad) return;
-    uint4* da = reinterpret_cast<uint4*>(seedA + (size_t)k * 64);
-    uint4* dx = reinterpret_cast<uint4*>(seedAx + (size_t)k * 16);
-    if (k < n_seed) {
-        const size_t p = (size_t)(k / gx) * S * PW + (size_t)(k % gx) * S;
-        const uint4* sa = reinterpret_cast<const uint4*>(poolA + p * 64);
-        const uint4* sx = reinterpret_cast<const uint4*>(poolAx + p * 16);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) da[q] = sa[q];
-        dx[0] = sx[0];
-        dx[1] = sx[1];
-        seedhk[k] = hk[p];
-    } else {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) da[q] = make_uint4(0u, 0u, 0u, 0u);
-        dx[0] = make_uint4(0u, 0u, 0u, 0u);
-        dx[1] = make_uint4(0u, 0u, 0u, 0u);
-        seedhk[k] = make_float2(__int_as_float(0x7f800000), 0.f);
     }
 }
 
@@ -1217,7 +1213,8 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     __half* seedAx = reinterpret_cast<__half*>(seed_raw + off_seedAx);
 
     // 1. pool (independent of the ranges)
-    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk, sd4, sd4 + NP, sdd);
+    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk, sd4, sd4 + NP, sdd, seed_S, seed_gx, n_seed, n_seed_pad,
+                                                  probe ? nullptr : seedA, seedAx, seedhk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
     // 2. range states and the range operand: all eligible in natural order, nothing known yet (also clears the control block and the lists;
@@ -1254,8 +1251,6 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     // 4a. seed round: the GEMM ranks the lattice candidates per range (no thresholds exist yet), the best one and
     // position 0 are scored exactly and give every range its first upper bound
     if (!probe) {
-        bf_seed_gather_kernel<<<cdiv(n_seed_pad, 128), 128, 0, st>>>(poolA, poolAx, hk, PW, seed_S, seed_gx, n_seed, n_seed_pad, seedA, seedAx, seedhk);
-        FIC_CHECK_LAUNCH(h, "bf_seed_gather_kernel");
         CUtensorMap mapS, mapSx;
         FIC_TRY(make_map(&mapS, seedA, (uint64_t)n_seed_pad, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
         FIC_TRY(make_map(&mapSx, seedAx, (uint64_t)n_seed_pad, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
