@@ -3,8 +3,11 @@ node stream breadth-first from the single root: leaf = `1`, row, col, orientatio
 quantised scale, quantised offset; split = `0`, vertical (1 bit), split index (16 bits), then both children."""
 from __future__ import annotations
 
+import gc
 from collections import deque
 from typing import BinaryIO
+
+import numpy as np
 
 from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_preamble
 from bitbuffer import EOF, BitBuffer
@@ -30,53 +33,85 @@ class HVSerializer:
 
     def serialize(self, hv_img: HVImage, output: str | BinaryIO):
         self.img = hv_img
-        self._choose_coded_dimensions()
-        with open_target(output, 'wb') as f:
-            self.file = f
-            start = f.tell()
-            bits = BitBuffer(f, BYTE_ORDER)
-            write_preamble(f, bits, HV_MAGIC, hv_img.info, self.entropy_processor, self.entropy_coding_dimensions)
-            self._write_nodes(bits)
-            patch_size(f, start, HV_MAGIC)
+        gc_was_on = gc.isenabled()
+        gc.disable()   # tens of thousands of short-lived tuples and nodes, none of them cyclic
+        try:
+            self._walk()
+            self._choose_coded_dimensions()
+            with open_target(output, 'wb') as f:
+                self.file = f
+                start = f.tell()
+                bits = BitBuffer(f, BYTE_ORDER)
+                write_preamble(f, bits, HV_MAGIC, hv_img.info, self.entropy_processor, self.entropy_coding_dimensions)
+                self._write_nodes(bits)
+                patch_size(f, start, HV_MAGIC)
+        finally:
+            if gc_was_on:
+                gc.enable()
+
+    def _walk(self):
+        """One breadth-first pass over the tree (the order of the node stream and of the Huffman statistics alike):
+        per node its kind and raw fields, as columns."""
+        rows = []
+        add = rows.append
+        pending = deque([self.img.root])
+        pop, push = pending.popleft, pending.append
+        while pending:
+            node = pop()
+            d = node.domain
+            if d is not None:
+                add((LEAF_BIT, d.start_i, d.start_j, d.orientation, d.rotation // 2, d.quantized_scale, d.quantized_offset))
+            else:
+                si = node.split_info
+                add((INTERNAL_NODE_BIT, int(si.vertical_split), si.split_idx, 0, 0, 0, 0))
+                push(node.c1)
+                push(node.c2)
+        table = np.array(rows, np.int64).reshape(-1, 7)
+        self._kind = table[:, 0]
+        self._fields = [table[:, c] for c in range(1, 7)]
 
     def _choose_coded_dimensions(self):
         values: dict[CodingDimension, list[int]] = {}
         if self.entropy_coding_dimensions:
-            extract = get_domain_dimension_extractors()
-            wanted = [dim for dim in CodingDimension if dim in self.entropy_coding_dimensions]
-            values = {dim: [] for dim in wanted}
-            pending = deque([self.img.root])
-            while pending:
-                node = pending.popleft()
-                if node.is_leaf():
-                    for dim in wanted:
-                        values[dim].append(extract[dim.value](node.domain))
-                else:
-                    pending.append(node.c1)
-                    pending.append(node.c2)
+            leaf = self._kind == LEAF_BIT
+            column = {CodingDimension.DOMAIN_ROW: 0, CodingDimension.DOMAIN_COL: 1, CodingDimension.SCALE: 4,
+                      CodingDimension.OFFSET: 5}
+            values = {dim: self._fields[column[dim]][leaf].tolist() for dim in CodingDimension
+                      if dim in self.entropy_coding_dimensions}
         gains = self.entropy_processor.prepare_for_encoding(values, get_dimension_bit_widths(self.img.info))
         self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}
 
+    def _coded(self, column: np.ndarray, dim: CodingDimension):
+        """(code, width) of every value of a column through the entropy processor, one call per distinct value."""
+        uniq, inverse = np.unique(column, return_inverse=True)
+        pairs = [self.entropy_processor.encode(int(v), dim) for v in uniq]
+        codes = np.array([p[0] for p in pairs], np.uint64)[inverse]
+        widths = np.array([p[1] for p in pairs], np.int64)[inverse]
+        return codes, widths
+
     def _write_nodes(self, bits: BitBuffer):
-        enc = self.entropy_processor.encode
-        pending = deque([self.img.root])
-        while pending:
-            node = pending.popleft()
-            if node.is_leaf():
-                d = node.domain
-                bits.write(LEAF_BIT, 1)
-                bits.write(*enc(d.start_i, CodingDimension.DOMAIN_ROW))
-                bits.write(*enc(d.start_j, CodingDimension.DOMAIN_COL))
-                bits.write(d.orientation, 1)
-                bits.write(d.rotation // 2, 1)
-                bits.write(*enc(d.quantized_scale, CodingDimension.SCALE))
-                bits.write(*enc(d.quantized_offset, CodingDimension.OFFSET))
-            else:
-                bits.write(INTERNAL_NODE_BIT, 1)
-                bits.write(int(node.split_info.vertical_split), 1)
-                bits.write(node.split_info.split_idx, 16)
-                pending.append(node.c1)
-                pending.append(node.c2)
+        # leaf = 1, row, col, orientation (1), rotation // 2 (1), scale, offset; split = 0, vertical (1), index (16)
+        kind, f = self._kind, self._fields
+        leaf = kind == LEAF_BIT
+        n = kind.size
+        vals = np.zeros((n, 7), np.uint64)
+        wid = np.zeros((n, 7), np.int64)
+        vals[:, 0] = kind
+        wid[:, 0] = 1
+        row_c, row_w = self._coded(f[0][leaf], CodingDimension.DOMAIN_ROW)
+        col_c, col_w = self._coded(f[1][leaf], CodingDimension.DOMAIN_COL)
+        sc_c, sc_w = self._coded(f[4][leaf], CodingDimension.SCALE)
+        of_c, of_w = self._coded(f[5][leaf], CodingDimension.OFFSET)
+        vals[leaf, 1], wid[leaf, 1] = row_c, row_w
+        vals[leaf, 2], wid[leaf, 2] = col_c, col_w
+        vals[leaf, 3], wid[leaf, 3] = f[2][leaf], 1
+        vals[leaf, 4], wid[leaf, 4] = f[3][leaf], 1
+        vals[leaf, 5], wid[leaf, 5] = sc_c, sc_w
+        vals[leaf, 6], wid[leaf, 6] = of_c, of_w
+        split = ~leaf
+        vals[split, 1], wid[split, 1] = f[0][split], 1
+        vals[split, 2], wid[split, 2] = f[1][split], 16
+        bits.write_many(vals.ravel(), wid.ravel())      # zero-width slots vanish
         if not bits.is_empty():
             bits.flush()
 

@@ -6,8 +6,11 @@ quantised offset; internal node = `0` followed (later in the stream) by its four
 """
 from __future__ import annotations
 
+import gc
 from collections import deque
 from typing import BinaryIO
+
+import numpy as np
 
 from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_preamble
 from bitbuffer import EOF, BitBuffer
@@ -45,46 +48,69 @@ class QuadtreeSerializer:
 
     def serialize(self, quadtree_img: QuadtreeImage, output: str | BinaryIO):
         self.img = quadtree_img
-        self._choose_coded_dimensions()
-        with open_target(output, 'wb') as f:
-            self.file = f
-            start = f.tell()
-            bits = BitBuffer(f, BYTE_ORDER)
-            write_preamble(f, bits, QUADTREE_MAGIC, quadtree_img.info, self.entropy_processor, self.entropy_coding_dimensions)
-            self._write_nodes(bits)
-            patch_size(f, start, QUADTREE_MAGIC)
+        gc_was_on = gc.isenabled()
+        gc.disable()   # tens of thousands of short-lived tuples and nodes, none of them cyclic
+        try:
+            self._choose_coded_dimensions()
+            with open_target(output, 'wb') as f:
+                self.file = f
+                start = f.tell()
+                bits = BitBuffer(f, BYTE_ORDER)
+                write_preamble(f, bits, QUADTREE_MAGIC, quadtree_img.info, self.entropy_processor, self.entropy_coding_dimensions)
+                self._write_nodes(bits)
+                patch_size(f, start, QUADTREE_MAGIC)
+        finally:
+            if gc_was_on:
+                gc.enable()
 
     def _choose_coded_dimensions(self):
         values: dict[CodingDimension, list[int]] = {}
         if self.entropy_coding_dimensions:
-            extract = get_domain_dimension_extractors()
-            wanted = [dim for dim in CodingDimension if dim in self.entropy_coding_dimensions]
-            values = {dim: [] for dim in wanted}
-            for dom in _leaves_breadth_first(self.img.forest):
-                for dim in wanted:
-                    values[dim].append(extract[dim.value](dom))
+            rows = [(d.start_i, d.start_j, d.quantized_scale, d.quantized_offset) for d in _leaves_breadth_first(self.img.forest)]
+            table = np.array(rows, np.int64).reshape(-1, 4)
+            column = {CodingDimension.DOMAIN_ROW: 0, CodingDimension.DOMAIN_COL: 1, CodingDimension.SCALE: 2,
+                      CodingDimension.OFFSET: 3}
+            values = {dim: table[:, column[dim]].tolist() for dim in CodingDimension if dim in self.entropy_coding_dimensions}
         gains = self.entropy_processor.prepare_for_encoding(values, get_dimension_bit_widths(self.img.info))
         # the reference overwrites the requested set with the profitable one (serialization.py:60)
         self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}
 
+    def _coded(self, column: np.ndarray, dim: CodingDimension):
+        """(code, width) of every value of a column through the entropy processor, one call per distinct value."""
+        uniq, inverse = np.unique(column, return_inverse=True)
+        pairs = [self.entropy_processor.encode(int(v), dim) for v in uniq]
+        codes = np.array([p[0] for p in pairs], np.uint64)[inverse]
+        widths = np.array([p[1] for p in pairs], np.int64)[inverse]
+        return codes, widths
+
     def _write_nodes(self, bits: BitBuffer):
-        enc = self.entropy_processor.encode
+        # node stream, breadth-first per root: leaf = 1, row, col, orientation (1), rotation (2), scale, offset; inner = 0
+        rows = []
+        add = rows.append
         for root in self.img.forest:
             pending = deque([root])
+            pop = pending.popleft
             while pending:
-                node = pending.popleft()
-                if node.is_leaf():
-                    d = node.domain
-                    bits.write(LEAF_BIT, 1)
-                    bits.write(*enc(d.start_i, CodingDimension.DOMAIN_ROW))
-                    bits.write(*enc(d.start_j, CodingDimension.DOMAIN_COL))
-                    bits.write(d.orientation, 1)
-                    bits.write(d.rotation, 2)
-                    bits.write(*enc(d.quantized_scale, CodingDimension.SCALE))
-                    bits.write(*enc(d.quantized_offset, CodingDimension.OFFSET))
+                node = pop()
+                d = node.domain
+                if d is not None:
+                    add((LEAF_BIT, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset))
                 else:
-                    bits.write(INTERNAL_NODE_BIT, 1)
+                    add((INTERNAL_NODE_BIT, 0, 0, 0, 0, 0, 0))
                     pending.extend(node.children)
+        table = np.array(rows, np.int64).reshape(-1, 7)
+        leaf = table[:, 0] == LEAF_BIT
+        n = table.shape[0]
+        vals = np.zeros((n, 7), np.uint64)
+        wid = np.zeros((n, 7), np.int64)
+        vals[:, 0] = table[:, 0]
+        wid[:, 0] = 1
+        for col, dim in ((1, CodingDimension.DOMAIN_ROW), (2, CodingDimension.DOMAIN_COL), (5, CodingDimension.SCALE),
+                         (6, CodingDimension.OFFSET)):
+            vals[leaf, col], wid[leaf, col] = self._coded(table[leaf, col], dim)
+        vals[leaf, 3], wid[leaf, 3] = table[leaf, 3], 1
+        vals[leaf, 4], wid[leaf, 4] = table[leaf, 4], 2
+        bits.write_many(vals.ravel(), wid.ravel())      # zero-width slots vanish
         if not bits.is_empty():
             bits.flush()
 

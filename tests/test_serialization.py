@@ -172,3 +172,26 @@ def test_colour_conversion_round_trip_shapes():
     rgb = rng.integers(0, 256, (8, 12, 3), dtype=np.uint8)
     y, cb, cr = utils.rgb_to_ycbcr(rgb, "4:2:0")
     assert cb.shape == (4, 6) and utils.ycbcr_to_rgb((y, cb, cr), "4:2:0").shape == (8, 12, 3)
+
+
+def test_bitbuffer_write_many_equals_single_writes():
+    """The vectorised field writer the serialisers use leaves the same bytes and the same pending state as one
+    `write` per field, whatever is already pending (widths 0..32, values wider than their field are masked)."""
+    import random
+    from bitbuffer import BitBuffer
+    rnd = random.Random(7)
+    for _ in range(60):
+        fields = [(rnd.getrandbits(40), rnd.choice([0, 1, 1, 2, 3, 5, 7, 9, 16, 24, 31, 32])) for _ in range(rnd.randint(0, 400))]
+        pre = [(rnd.getrandbits(12), rnd.randint(1, 12)) for _ in range(rnd.randint(0, 3))]
+        a, b = io.BytesIO(), io.BytesIO()
+        A, B = BitBuffer(a), BitBuffer(b)
+        for v, w in pre:
+            A.write(v, w)
+            B.write(v, w)
+        for v, w in fields:
+            A.write(v, w)
+        B.write_many([v for v, _ in fields], [w for _, w in fields])
+        assert a.getvalue() == b.getvalue() and (A.buff, A.accumulated_size) == (B.buff, B.accumulated_size)
+        A.flush()
+        B.flush()
+        assert a.getvalue() == b.getvalue()
