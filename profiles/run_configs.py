@@ -65,7 +65,20 @@ t_gpu, hv = timed(lambda: HVEncoder(*hp).encode(img), reps=2)
 t_hdec, hdec = timed(lambda: HVDecoder().decode(hv))
 g = np.load(os.path.join(ROOT, "tests/golden/hv_golden.npz"))
 leaves = int((g["lena512_nodes"][:, 0] == 1).sum()) if "lena512_nodes" in g.files else None
-emit(config=3, what="HV 512x512 (4,4,16,16,5,7,25.0)", encode_ms=t_gpu * 1e3, decode_ms=t_hdec * 1e3, psnr_db=psnr(hdec, img),
+import io  # noqa: E402
+from entropy.processor import CodingDimension, HuffmanEntropyProcessor  # noqa: E402
+from hvv2.serialization import HVSerializer  # noqa: E402
+
+
+def hv_to_bytes():
+    out = io.BytesIO()
+    HVSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(hv, out)
+    return out.getvalue()
+
+
+t_ser, blob = timed(hv_to_bytes, reps=3)
+emit(config=3, what="HV 512x512 (4,4,16,16,5,7,25.0)", encode_ms=t_gpu * 1e3, entropy_coded_stream_ms=t_ser * 1e3,
+     stream_bytes=len(blob), decode_ms=t_hdec * 1e3, psnr_db=psnr(hdec, img),
      leaves_reference=leaves, reference_cpu_s="1688 (BASELINE.md), 1578 when the golden file was made")
 
 # config 4: synthetic 4096x4096 brute force on one GPU (+ a 1/8 range slice as one rank of eight would run it)
