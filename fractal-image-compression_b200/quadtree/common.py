@@ -103,9 +103,6 @@ def stream_to_forest(nodes: np.ndarray, vals: np.ndarray, n_roots: int) -> list[
     n = len(nodes)
     kind, di, dj, ori, rot, qs, qo = (nodes[:, c].tolist() for c in range(7)) if n else ([],) * 7
     sc, of = (vals[:, 0].tolist(), vals[:, 1].tolist()) if n else ([], [])
-    pos = 0
-    forest: list[QuadtreeNode] = []
-    new_node, new_domain = QuadtreeNode, Domain
     gc_was_on = gc.isenabled()
     gc.disable()   # tens of thousands of small acyclic objects: the generational collector only gets in the way
     try:

@@ -61,7 +61,9 @@ def test_quadtree_encoder_and_decoder_match_reference(fic, golden, images, name)
 
 
 @pytest.mark.parametrize("params", [(7, 5, 1.0, False, False, 4, 8, 2.0), (6, 6, 1.0, True, False, 2, 8, 1.0),
-                                    (7, 5, 0.75, False, True, 2, 16, 0.5, 2, 4)])
+                                    (7, 5, 0.75, False, True, 2, 16, 0.5, 2, 4),
+                                    (7, 5, 1.0, False, False, 4, 8, 2.0, 1, 1), (6, 6, 1.0, True, False, 2, 8, 1.0, 1, 1)],
+                         ids=["default", "full_class_search", "any_domain_steps_2_4", "dense_pools", "dense_full_class"])
 @pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96))])
 def test_quadtree_against_oracle(fic, orc, params, seed, shape):
     img = synthetic_image(seed, *shape)
@@ -70,6 +72,33 @@ def test_quadtree_against_oracle(fic, orc, params, seed, shape):
     assert got[2] == want[2]
     assert np.array_equal(got[0], want[0])
     assert np.array_equal(got[1], want[1])
+
+
+def test_rgb_quadtree_is_three_independent_planes(fic, orc):
+    """the colour wrapper (reference quadtree/rgb.py:14-56) is three grayscale problems; every plane
+    of the fan-out must equal the oracle's encode of that plane and the decode must be the planes' decodes recombined."""
+    from quadtree.decoder import QuadtreeDecoder
+    from quadtree.encoder import QuadtreeEncoder
+    from quadtree.rgb import RGBQuadtreeDecoder, RGBQuadtreeEncoder
+    from utils import rgb_to_ycbcr, ycbcr_to_rgb
+    rgb = np.stack([synthetic_image(s, 64, 96) for s in (11, 12, 13)], axis=-1)
+    params = (7, 5, 1.0, False, False, 4, 16, 0.5)
+    for subsampling in ("4:4:4", "4:2:0"):
+        col = RGBQuadtreeEncoder(QuadtreeEncoder(*params), QuadtreeEncoder(*params)).encode(rgb, subsampling)
+        planes = rgb_to_ycbcr(rgb, subsampling)
+        decoded = []
+        for plane, enc in zip(planes, (col.encoded_Y, col.encoded_Cb, col.encoded_Cr)):
+            plane = np.ascontiguousarray(plane)
+            want = orc.qt_encode(plane, *params)
+            nodes, vals = qt_flat(enc)
+            leaf = want[0][:, 0] == 1
+            assert len(enc.forest) == want[2] and np.array_equal(nodes[:, 0] == 1, leaf)
+            assert np.array_equal(nodes[leaf], want[0][leaf, :7]) and np.array_equal(vals[leaf], want[1][leaf, :2])
+            decoded.append(QuadtreeDecoder().decode(enc))
+            assert decoded[-1].shape == plane.shape
+        out = RGBQuadtreeDecoder(QuadtreeDecoder()).decode(col)
+        assert out.shape == rgb.shape and out.dtype == np.uint8
+        assert np.array_equal(out, ycbcr_to_rgb(tuple(decoded), subsampling))
 
 
 def test_quadtree_flat_image_and_placeholders(fic, orc):
