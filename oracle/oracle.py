@@ -152,20 +152,110 @@ def hv_search(img, i, j, w, h, scale_bits, offset_bits, max_scale=1.0):
     return rec, vals  # (di,dj,orient,rot,qs,qo), (s,o,err)
 
 
-def tree_decode(kind, leaves, so, H, W, iterations=-1, stop_rel_err=5e-3, min_it=2, max_it=10, f32_affine=False):
-    """kind 0 = quadtree, 1 = HV.  leaves[k] = (ri,rj,h,w,di,dj,orient,rot); so[k] = (scale, offset)."""
+def tree_decode(kind, leaves, so, H, W, iterations=-1, stop_rel_err=5e-3, min_it=2, max_it=10, f32_affine=False,
+                deblock=False):
+    """kind 0 = quadtree, 1 = HV.  leaves[k] = (ri,rj,h,w,di,dj,orient,rot); so[k] = (scale, offset).
+    deblock: quadtree only, leaves in the reference's visiting order (see qt_visit_order)."""
     leaves = np.ascontiguousarray(leaves, np.int32)
     so = np.ascontiguousarray(so, np.float64)
     out = np.zeros((H, W), np.uint8)
     done = C.c_int32(0)
-    f = lib().orc_tree_decode
+    f = lib().orc_tree_decode_post
     f.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.c_int,
-                  C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_int32)]
+                  C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_int32)]
     rc = f(kind, _p(leaves, C.c_int32), _p(so, C.c_double), leaves.shape[0], H, W, iterations, float(stop_rel_err),
-           min_it, max_it, int(f32_affine), _p(out, C.c_uint8), C.byref(done))
+           min_it, max_it, int(f32_affine), int(bool(deblock)), _p(out, C.c_uint8), C.byref(done))
     if rc != 0:
         raise ValueError("orc_tree_decode failed")
     return out, int(done.value)
+
+
+def qt_visit_order(nodes, n_roots, H, W):
+    """Leaf rectangles (ri, rj, size) of a preorder quadtree stream in the order the reference's decoder and
+    post-processor visit them (quadtree/postprocessing.py:29-71): roots in _de_partition order, each root breadth
+    first.  Returns (rects[k,3], stream_index[k])."""
+    from collections import deque
+    kinds = np.asarray(nodes)[:, 0].tolist()
+    roots = []
+
+    def part(i, j, w, h):
+        e = min(w.bit_length(), h.bit_length()) - 1
+        side = 1 << e
+        roots.append((i, j, side))
+        if side < w:
+            part(i, j + side, w - side, h)
+        if side < h:
+            part(i + side, j, side, h - side)
+
+    part(0, 0, W, H)
+    assert len(roots) == n_roots
+    # subtree extents in the stream, so a child's stream index can be found without rebuilding objects
+    n = len(kinds)
+    end = [0] * n
+    for k in range(n - 1, -1, -1):
+        if kinds[k]:
+            end[k] = k + 1
+        else:
+            c = k + 1
+            for _ in range(4):
+                c = end[c]
+            end[k] = c
+    rects, index = [], []
+    pos = 0
+    for (ri, rj, side) in roots:
+        queue = deque([(pos, ri, rj, side)])
+        pos = end[pos]
+        while queue:
+            k, i, j, size = queue.popleft()
+            if kinds[k]:
+                rects.append((i, j, size))
+                index.append(k)
+            else:
+                half = size // 2
+                c = k + 1
+                for (di, dj) in ((0, 0), (0, half), (half, 0), (half, half)):
+                    queue.append((c, i + di, j + dj, half))
+                    c = end[c]
+    return np.array(rects, np.int32).reshape(-1, 3), np.array(index, np.int64)
+
+
+def qt_deblock(img, rects, weights=(5. / 6., 1. - 5. / 6., 2. / 3., 1. - 2. / 3.), small_side=4):
+    """DeblockingQuadtreePostprocessor.postprocess on a float64 image; rects[k] = (ri, rj, size) in visiting order."""
+    a = np.ascontiguousarray(img, np.float64)
+    r = np.asarray(rects, np.int32).reshape(-1, 3)
+    leaves = np.zeros((r.shape[0], 8), np.int32)
+    leaves[:, 0], leaves[:, 1], leaves[:, 2], leaves[:, 3] = r[:, 0], r[:, 1], r[:, 2], r[:, 2]
+    w = np.array(weights, np.float64)
+    out = np.empty_like(a)
+    f = lib().orc_qt_deblock
+    f.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int,
+                  C.POINTER(C.c_double)]
+    f(_p(a, C.c_double), _p(leaves, C.c_int32), leaves.shape[0], a.shape[0], a.shape[1], _p(w, C.c_double),
+      int(small_side), _p(out, C.c_double))
+    return out
+
+
+def rgb_to_ycbcr(rgb, subsample=False):
+    a = np.ascontiguousarray(rgb, np.uint8)
+    N, M, _ = a.shape
+    cs = (N // 2, M // 2 + M % 2) if subsample else (N, M)
+    y, cb, cr = np.zeros((N, M), np.uint8), np.zeros(cs, np.uint8), np.zeros(cs, np.uint8)
+    f = lib().orc_rgb_to_ycbcr
+    f.argtypes = [C.POINTER(C.c_uint8), C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_uint8)] * 3
+    if f(_p(a, C.c_uint8), N, M, int(bool(subsample)), _p(y, C.c_uint8), _p(cb, C.c_uint8), _p(cr, C.c_uint8)) != 0:
+        raise ValueError("orc_rgb_to_ycbcr: 4:2:0 needs an even height")
+    return y, cb, cr
+
+
+def ycbcr_to_rgb(y, cb, cr, subsample=False):
+    y, cb, cr = (np.ascontiguousarray(p, np.uint8) for p in (y, cb, cr))
+    N, M = y.shape
+    out = np.zeros((N, M, 3), np.uint8)
+    f = lib().orc_ycbcr_to_rgb
+    f.argtypes = [C.POINTER(C.c_uint8)] * 3 + [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]
+    if f(_p(y, C.c_uint8), _p(cb, C.c_uint8), _p(cr, C.c_uint8), N, M, int(bool(subsample)), _p(out, C.c_uint8)) != 0:
+        raise ValueError("orc_ycbcr_to_rgb: 4:2:0 needs a height that is a multiple of 4")
+    return out
 
 
 def average_subsample(arr, jit=False):
