@@ -8,7 +8,7 @@ post_golden.npz (committed):
   <case>_decdb / _decdb4   QuadtreeDecoder(AUTO / iterations=4).decode(q, DeblockingQuadtreePostprocessor()) of the
                            quadtree cases of qt_golden.npz (re-encoded here by the reference; the node streams are
                            checked against the stored ones first)
-  <case>_deblock_in/_out   DeblockingQuadtreePostprocessor().postprocess(x, q) for a seeded float64 image x
+  <case>_deblock_out       DeblockingQuadtreePostprocessor().postprocess(deblock_input(case), q), small cases only
   rgb<k>                   seeded RGB inputs; rgb<k>_<444|420>_{y,cb,cr} = utils.rgb_to_ycbcr, rgb<k>_<444|420>_back =
                            utils.ycbcr_to_rgb of those planes; rgb<k>_<mode>_raises = 1 where the reference raises
 """
@@ -21,6 +21,11 @@ REF = "/root/reference"
 sys.path.insert(0, os.path.join(REF, "src"))
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
+
+
+def deblock_input(name, shape):
+    """Seeded float64 image with values outside 0..255 too (the filter runs before the clip)."""
+    return np.random.default_rng(len(name)).uniform(-20.0, 280.0, size=shape)
 
 
 def main():
@@ -41,10 +46,9 @@ def main():
         assert np.array_equal(nodes, g[f"{name}_nodes"]) and np.array_equal(vals, g[f"{name}_vals"]), name
         out[f"{name}_decdb"] = QuadtreeDecoder().decode(q, DeblockingQuadtreePostprocessor())
         out[f"{name}_decdb4"] = QuadtreeDecoder(iterations=4).decode(q, DeblockingQuadtreePostprocessor())
-        rng = np.random.default_rng(len(name))
-        x = rng.uniform(-20.0, 280.0, size=imgs[name].shape)
-        out[f"{name}_deblock_in"] = x
-        out[f"{name}_deblock_out"] = DeblockingQuadtreePostprocessor().postprocess(x, q)
+        if imgs[name].size <= 240 * 92:   # float64 fixtures only for the small cases (the input is re-derived from its seed)
+            x = deblock_input(name, imgs[name].shape)
+            out[f"{name}_deblock_out"] = DeblockingQuadtreePostprocessor().postprocess(x, q)
         print(name, "deblocked")
 
     shapes = [(16, 24), (64, 48), (12, 17), (8, 9), (6, 8), (9, 8), (7, 7), (40, 33)]
