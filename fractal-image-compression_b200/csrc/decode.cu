@@ -267,6 +267,167 @@ __global__ void tree_finish_kernel(const double* __restrict__ img, size_t npx, u
     out[p] = (uint8_t)__double2int_rz(v);
 }
 
+// ------------------------------------------------------------------------------------------------
+// DeblockingQuadtreePostprocessor (quadtree/postprocessing.py:15-71)
+// ------------------------------------------------------------------------------------------------
+// The reference visits the roots in _de_partition order and each root breadth first; every leaf overwrites four lines
+// of the result from the untouched input (its first row and column, and the row and column just past it), so where
+// lines of two leaves coincide the LAST leaf visited wins.  Here every pixel pulls instead: at most four writers can
+// reach it (its own leaf through its first row / first column, the leaf above through the row past its end, the leaf
+// to the left through the column past its end) and the one with the largest visiting key is applied.
+// Key = root index | depth | Morton code of the leaf's corner inside its root (row bit above column bit: the children
+// are queued TL, TR, BL, BR, so one level of the breadth-first order is the Morton order) | line (0 top, 1 past-bottom,
+// 2 left, 3 past-right: the order of the four assignments, postprocessing.py:59-66).
+struct DeblockWeights {
+    double w[4];      // { own, neighbour } for sides <= small_side, then for larger blocks (postprocessing.py:17-21)
+    int small_side;
+};
+
+__device__ __forceinline__ unsigned fic_spread16(unsigned v)
+{
+    v &= 0xffffu;
+    v = (v | (v << 8)) & 0x00ff00ffu;
+    v = (v | (v << 4)) & 0x0f0f0f0fu;
+    v = (v | (v << 2)) & 0x33333333u;
+    v = (v | (v << 1)) & 0x55555555u;
+    return v;
+}
+
+__global__ void qt_leaf_key_kernel(const int32_t* __restrict__ leaves, int n, const int32_t* __restrict__ roots, int n_roots,
+                                   unsigned long long* __restrict__ keys)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int ri = leaves[8 * (size_t)k], rj = leaves[8 * (size_t)k + 1], size = leaves[8 * (size_t)k + 2];
+    unsigned long long key = 0;
+    for (int r = 0; r < n_roots; ++r) {
+        const int oi = roots[3 * r], oj = roots[3 * r + 1], side = roots[3 * r + 2];
+        if (ri >= oi && ri < oi + side && rj >= oj && rj < oj + side) {
+            const int depth = (31 - __clz(side)) - (31 - __clz(size));
+            const unsigned morton = (fic_spread16((unsigned)(ri - oi)) << 1) | fic_spread16((unsigned)(rj - oj));
+            key = ((unsigned long long)(r + 1) << 39) | ((unsigned long long)depth << 34) | ((unsigned long long)morton << 2);
+            break;
+        }
+    }
+    keys[k] = key;
+}
+
+template <bool TO_U8>
+__global__ void qt_deblock_kernel(const double* __restrict__ img, const int32_t* __restrict__ leaves,
+                                  const unsigned long long* __restrict__ keys, const int32_t* __restrict__ leaf_map, int H,
+                                  int W, DeblockWeights dw, double* __restrict__ res, uint8_t* __restrict__ out)
+{
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= (size_t)H * W) return;
+    const int y = (int)(p / W), x = (int)(p - (size_t)y * W);
+    const double own = img[p];
+    double v = own;
+    unsigned long long best = 0;
+    auto offer = [&](unsigned long long key, int size, size_t q) {
+        if (key > best) {
+            best = key;
+            const int c = size <= dw.small_side ? 0 : 2;
+            v = DA(DM(dw.w[c], own), DM(dw.w[c + 1], img[q]));
+        }
+    };
+    const int k = leaf_map[p];
+    if (k >= 0) {
+        const int ri = leaves[8 * (size_t)k], rj = leaves[8 * (size_t)k + 1], size = leaves[8 * (size_t)k + 2];
+        if (y == ri && ri >= 1) offer(keys[k] | 0ull, size, p - W);
+        if (x == rj && rj >= 1) offer(keys[k] | 2ull, size, p - 1);
+    }
+    if (y >= 1 && y + 1 < H) {
+        const int a = leaf_map[p - W];
+        if (a >= 0 && a != k) {
+            const int size = leaves[8 * (size_t)a + 2];
+            if (leaves[8 * (size_t)a] + size == y) offer(keys[a] | 1ull, size, p + W);
+        }
+    }
+    if (x >= 1 && x + 1 < W) {
+        const int b = leaf_map[p - 1];
+        if (b >= 0 && b != k) {
+            const int size = leaves[8 * (size_t)b + 2];
+            if (leaves[8 * (size_t)b + 1] + size == x) offer(keys[b] | 3ull, size, p + 1);
+        }
+    }
+    if (TO_U8) {
+        v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);  // clip(0., 255.), decoder.py:61
+        out[p] = (uint8_t)__double2int_rz(v);
+    } else {
+        res[p] = v;
+    }
+}
+
+// _de_partition (postprocessing.py:29-41): the largest power-of-two square at the corner, then the strip to its right
+// (full height), then the strip below it (square width)
+static void qt_root_squares(int i, int j, int w, int h, std::vector<int32_t>& out)
+{
+    int e = 0;
+    while ((2 << e) <= (w < h ? w : h)) ++e;
+    const int side = 1 << e;
+    out.push_back(i);
+    out.push_back(j);
+    out.push_back(side);
+    if (side < w) qt_root_squares(i, j + side, w - side, h, out);
+    if (side < h) qt_root_squares(i + side, j, side, h - side, out);
+}
+
+// d_img float64 [H,W] -> d_res float64 (or, d_out8 != nullptr, the clipped uint8 image).  leaf_map must already hold
+// the leaf index of every pixel (tree_paint_kernel).
+static int qt_deblock_run(fic_handle* h, const double* d_img, const int32_t* d_leaves, int n, int H, int W,
+                          const DeblockWeights& dw, const int32_t* leaf_map, double* d_res, uint8_t* d_out8, cudaStream_t st)
+{
+    std::vector<int32_t> roots;
+    qt_root_squares(0, 0, W, H, roots);
+    const int n_roots = (int)(roots.size() / 3);
+    FIC_TRY(h->dec_roots.reserve(roots.size() * sizeof(int32_t)));
+    FIC_TRY(h->dec_keys.reserve(((size_t)n + 1) * sizeof(unsigned long long)));
+    FIC_TRY(fic_copy_in(h, h->dec_roots.p, roots.data(), roots.size() * sizeof(int32_t), false, st));
+    FIC_CUDA(cudaStreamSynchronize(st));  // `roots` is pageable and goes out of scope
+    if (n > 0) {
+        qt_leaf_key_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_leaves, n, h->dec_roots.as<int32_t>(), n_roots,
+                                                            h->dec_keys.as<unsigned long long>());
+        FIC_CHECK_LAUNCH(h, "qt_leaf_key_kernel");
+    }
+    const size_t npx = (size_t)H * W;
+    const unsigned grid = (unsigned)((npx + 255) / 256);
+    if (d_out8)
+        qt_deblock_kernel<true><<<grid, 256, 0, st>>>(d_img, d_leaves, h->dec_keys.as<unsigned long long>(), leaf_map, H, W, dw,
+                                                      nullptr, d_out8);
+    else
+        qt_deblock_kernel<false><<<grid, 256, 0, st>>>(d_img, d_leaves, h->dec_keys.as<unsigned long long>(), leaf_map, H, W, dw,
+                                                       d_res, nullptr);
+    FIC_CHECK_LAUNCH(h, "qt_deblock_kernel");
+    return FIC_OK;
+}
+
+static DeblockWeights qt_default_weights()
+{
+    DeblockWeights dw;
+    dw.w[0] = 5. / 6.;           // own_weight_max_depth
+    dw.w[1] = 1. - 5. / 6.;      // neigh_weight_max_depth
+    dw.w[2] = 2. / 3.;           // own_weight_not_max_depth
+    dw.w[3] = 1. - 2. / 3.;      // neigh_weight_not_max_depth
+    dw.small_side = 4;           // max_depth_range_size
+    return dw;
+}
+
+int qt_deblock_impl(fic_handle* h, const double* d_img, const int32_t* d_leaves, int n, int H, int W, const double* w4,
+                    int small_side, double* d_res, cudaStream_t st)
+{
+    const size_t npx = (size_t)H * W;
+    FIC_TRY(h->dec_map.reserve(npx * sizeof(int32_t)));
+    FIC_CUDA(cudaMemsetAsync(h->dec_map.p, 0xff, npx * sizeof(int32_t), st));
+    if (n > 0) {
+        tree_paint_kernel<<<n, 64, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
+        FIC_CHECK_LAUNCH(h, "tree_paint_kernel");
+    }
+    DeblockWeights dw = qt_default_weights();
+    if (w4) for (int c = 0; c < 4; ++c) dw.w[c] = w4[c];
+    if (small_side >= 0) dw.small_side = small_side;
+    return qt_deblock_run(h, d_img, d_leaves, n, H, W, dw, h->dec_map.as<int32_t>(), d_res, nullptr, st);
+}
+
 template <int KIND>
 static int launch_sweep(fic_handle* h, bool reduce, const int32_t* leaves, const double* so, const int32_t* map, int H,
                         int W, int f32_affine, const double* img, double* next, double* red, int nblocks, cudaStream_t st)
@@ -279,8 +440,10 @@ static int launch_sweep(fic_handle* h, bool reduce, const int32_t* leaves, const
     return FIC_OK;
 }
 
+// post & FIC_QT_DEBLOCK: the float image goes through the deblocking filter before the clip (decoder.py:58-61);
+// post & FIC_TREE_OUT_F64: d_out receives the float64 image (filtered or not) instead of the clipped bytes.
 int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const double* d_so, int n, int H, int W,
-                     int iterations, double stop, int min_it, int max_it, int f32_affine, uint8_t* d_out,
+                     int iterations, double stop, int min_it, int max_it, int f32_affine, unsigned post, void* d_out,
                      int32_t* iters_done, cudaStream_t st)
 {
     const size_t npx = (size_t)H * W;
@@ -326,9 +489,14 @@ int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const dou
     } else {
         for (int it = 0; it < iterations; ++it) FIC_TRY(sweep(false));
     }
-    tree_finish_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(img, npx, d_out);
-    FIC_CHECK_LAUNCH(h, "tree_finish_kernel");
     if (iters_done) *iters_done = done;
+    const bool f64 = post & FIC_TREE_OUT_F64;
+    if (post & FIC_QT_DEBLOCK)
+        return qt_deblock_run(h, img, d_leaves, n, H, W, qt_default_weights(), map, f64 ? (double*)d_out : nullptr,
+                              f64 ? nullptr : (uint8_t*)d_out, st);
+    if (f64) return fic_copy_out(h, d_out, img, npx * sizeof(double), true, st);
+    tree_finish_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(img, npx, (uint8_t*)d_out);
+    FIC_CHECK_LAUNCH(h, "tree_finish_kernel");
     return FIC_OK;
 }
 

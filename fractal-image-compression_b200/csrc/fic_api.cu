@@ -442,6 +442,19 @@ int fic_hv_encode(fic_handle* h, const uint8_t* img, int H, int W, int min_range
                           offset_bits, err_threshold, max_scale, nodes, vals, cap, st);
 }
 
+static int check_leaves(fic_handle* h, const char* who, int kind, const int32_t* leaves, int n, int H, int W, bool domains)
+{
+    for (int k = 0; k < n; ++k) {
+        const int32_t* L = leaves + 8 * k;
+        FIC_REQUIRE(L[0] >= 0 && L[1] >= 0 && L[2] >= 1 && L[3] >= 1 && L[0] + L[2] <= H && L[1] + L[3] <= W,
+                    "%s: leaf %d range (%d,%d,%dx%d) outside the image", who, k, L[0], L[1], L[2], L[3]);
+        FIC_REQUIRE(!domains || (L[4] >= 0 && L[5] >= 0 && L[4] + 2 * L[2] <= H && L[5] + 2 * L[3] <= W),
+                    "%s: leaf %d domain (%d,%d) does not fit the image", who, k, L[4], L[5]);
+        FIC_REQUIRE(kind == FIC_TREE_HV || L[2] == L[3], "%s: quadtree leaf %d is not square", who, k);
+    }
+    return FIC_OK;
+}
+
 int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double* so, int n, int H, int W, int iterations,
                     double stop_on_relative_error, int min_iterations, int max_iterations, int f32_affine, uint8_t* out,
                     int32_t* iters_done, unsigned flags, void* stream)
@@ -449,34 +462,130 @@ int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double
     FIC_REQUIRE(h && leaves && so && out, "fic_tree_decode: NULL argument");
     FIC_REQUIRE(kind == FIC_TREE_QUADTREE || kind == FIC_TREE_HV, "fic_tree_decode: unknown tree kind %d", kind);
     FIC_REQUIRE(n >= 0 && H > 0 && W > 0 && (iterations >= 0 || iterations == FIC_ITER_AUTO), "fic_tree_decode: bad sizes");
+    FIC_REQUIRE(!(flags & FIC_QT_DEBLOCK) || kind == FIC_TREE_QUADTREE,
+                "fic_tree_decode: the deblocking post-processor exists for the quadtree codec only");
     FIC_CUDA(cudaSetDevice(h->device));
     cudaStream_t st = fic_stream(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
+    const unsigned post = flags & (FIC_QT_DEBLOCK | FIC_TREE_OUT_F64);
+    const size_t out_bytes = (size_t)H * W * ((flags & FIC_TREE_OUT_F64) ? sizeof(double) : 1);
     const int32_t* d_leaves = leaves;
     const double* d_so = so;
-    uint8_t* d_out = out;
+    void* d_out = out;
     if (!dev) {
-        for (int k = 0; k < n; ++k) {
-            const int32_t* L = leaves + 8 * k;
-            FIC_REQUIRE(L[0] >= 0 && L[1] >= 0 && L[2] >= 1 && L[3] >= 1 && L[0] + L[2] <= H && L[1] + L[3] <= W,
-                        "fic_tree_decode: leaf %d range (%d,%d,%dx%d) outside the image", k, L[0], L[1], L[2], L[3]);
-            FIC_REQUIRE(L[4] >= 0 && L[5] >= 0 && L[4] + 2 * L[2] <= H && L[5] + 2 * L[3] <= W,
-                        "fic_tree_decode: leaf %d domain (%d,%d) does not fit the image", k, L[4], L[5]);
-            FIC_REQUIRE(kind == FIC_TREE_HV || L[2] == L[3], "fic_tree_decode: quadtree leaf %d is not square", k);
-        }
+        FIC_TRY(check_leaves(h, "fic_tree_decode", kind, leaves, n, H, W, true));
         FIC_TRY(h->d_in_a.reserve((size_t)n * 32 + 16));
         FIC_TRY(h->d_in_b.reserve((size_t)n * 16 + 16));
-        FIC_TRY(h->d_out_a.reserve((size_t)H * W));
+        FIC_TRY(h->d_out_a.reserve(out_bytes));
         FIC_TRY(fic_copy_in(h, h->d_in_a.p, leaves, (size_t)n * 32, false, st));
         FIC_TRY(fic_copy_in(h, h->d_in_b.p, so, (size_t)n * 16, false, st));
         d_leaves = h->d_in_a.as<int32_t>();
         d_so = h->d_in_b.as<double>();
-        d_out = h->d_out_a.as<uint8_t>();
+        d_out = h->d_out_a.p;
     }
     FIC_TRY(tree_decode_impl(h, kind, d_leaves, d_so, n, H, W, iterations, stop_on_relative_error, min_iterations,
-                             max_iterations, f32_affine, d_out, iters_done, st));
+                             max_iterations, f32_affine, post, d_out, iters_done, st));
     if (!dev) {
-        FIC_TRY(fic_copy_out(h, out, d_out, (size_t)H * W, false, st));
+        FIC_TRY(fic_copy_out(h, out, d_out, out_bytes, false, st));
+        FIC_CUDA(cudaStreamSynchronize(st));
+    }
+    return FIC_OK;
+}
+
+int fic_qt_deblock(fic_handle* h, const double* img, const int32_t* leaves, int n, int H, int W, const double* weights,
+                   int max_depth_range_size, double* out, unsigned flags, void* stream)
+{
+    FIC_REQUIRE(h && img && leaves && out, "fic_qt_deblock: NULL argument");
+    FIC_REQUIRE(n >= 0 && H > 0 && W > 0, "fic_qt_deblock: bad sizes");
+    FIC_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = fic_stream(h, stream);
+    const bool dev = flags & FIC_DEVICE_PTRS;
+    const size_t bytes = (size_t)H * W * sizeof(double);
+    const double* d_img = img;
+    const int32_t* d_leaves = leaves;
+    double* d_out = out;
+    if (!dev) {
+        FIC_TRY(check_leaves(h, "fic_qt_deblock", FIC_TREE_QUADTREE, leaves, n, H, W, false));
+        FIC_TRY(h->d_in_a.reserve((size_t)n * 32 + 16));
+        FIC_TRY(h->d_in_b.reserve(bytes));
+        FIC_TRY(h->d_out_a.reserve(bytes));
+        FIC_TRY(fic_copy_in(h, h->d_in_a.p, leaves, (size_t)n * 32, false, st));
+        FIC_TRY(fic_copy_in(h, h->d_in_b.p, img, bytes, false, st));
+        d_leaves = h->d_in_a.as<int32_t>();
+        d_img = h->d_in_b.as<double>();
+        d_out = h->d_out_a.as<double>();
+    }
+    FIC_TRY(qt_deblock_impl(h, d_img, d_leaves, n, H, W, weights, max_depth_range_size, d_out, st));
+    if (!dev) {
+        FIC_TRY(fic_copy_out(h, out, d_out, bytes, false, st));
+        FIC_CUDA(cudaStreamSynchronize(st));
+    }
+    return FIC_OK;
+}
+
+int fic_rgb_to_ycbcr(fic_handle* h, const uint8_t* rgb, int N, int M, int subsample, uint8_t* y, uint8_t* cb, uint8_t* cr,
+                     unsigned flags, void* stream)
+{
+    FIC_REQUIRE(h && rgb && y && cb && cr, "fic_rgb_to_ycbcr: NULL argument");
+    FIC_REQUIRE(N > 0 && M > 0 && (subsample == 0 || subsample == 1), "fic_rgb_to_ycbcr: bad sizes or subsampling mode");
+    FIC_REQUIRE(!subsample || N % 2 == 0,
+                "fic_rgb_to_ycbcr: 4:2:0 with an odd height %d (the reference raises or leaves the last chroma row unset)", N);
+    FIC_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = fic_stream(h, stream);
+    const bool dev = flags & FIC_DEVICE_PTRS;
+    const size_t npx = (size_t)N * M, nc = subsample ? (size_t)(N / 2) * ((M + 1) / 2) : npx;
+    const uint8_t* d_rgb = rgb;
+    uint8_t *d_y = y, *d_cb = cb, *d_cr = cr;
+    if (!dev) {
+        FIC_TRY(h->d_in_a.reserve(3 * npx));
+        FIC_TRY(h->d_out_a.reserve(npx));
+        FIC_TRY(h->d_out_b.reserve(nc));
+        FIC_TRY(h->d_out_c.reserve(nc));
+        FIC_TRY(fic_copy_in(h, h->d_in_a.p, rgb, 3 * npx, false, st));
+        d_rgb = h->d_in_a.as<uint8_t>();
+        d_y = h->d_out_a.as<uint8_t>();
+        d_cb = h->d_out_b.as<uint8_t>();
+        d_cr = h->d_out_c.as<uint8_t>();
+    }
+    FIC_TRY(rgb_to_ycbcr_impl(h, d_rgb, N, M, subsample, d_y, d_cb, d_cr, st));
+    if (!dev) {
+        FIC_TRY(fic_copy_out(h, y, d_y, npx, false, st));
+        FIC_TRY(fic_copy_out(h, cb, d_cb, nc, false, st));
+        FIC_TRY(fic_copy_out(h, cr, d_cr, nc, false, st));
+        FIC_CUDA(cudaStreamSynchronize(st));
+    }
+    return FIC_OK;
+}
+
+int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const uint8_t* cr, int N, int M, int subsample,
+                     uint8_t* rgb, unsigned flags, void* stream)
+{
+    FIC_REQUIRE(h && rgb && y && cb && cr, "fic_ycbcr_to_rgb: NULL argument");
+    FIC_REQUIRE(N > 0 && M > 0 && (subsample == 0 || subsample == 1), "fic_ycbcr_to_rgb: bad sizes or subsampling mode");
+    FIC_REQUIRE(!subsample || N % 4 == 0,
+                "fic_ycbcr_to_rgb: 4:2:0 with height %d not a multiple of 4 (the reference raises, utils.py:73-76)", N);
+    FIC_CUDA(cudaSetDevice(h->device));
+    cudaStream_t st = fic_stream(h, stream);
+    const bool dev = flags & FIC_DEVICE_PTRS;
+    const size_t npx = (size_t)N * M, nc = subsample ? (size_t)(N / 2) * ((M + 1) / 2) : npx;
+    const uint8_t *d_y = y, *d_cb = cb, *d_cr = cr;
+    uint8_t* d_rgb = rgb;
+    if (!dev) {
+        FIC_TRY(h->d_in_a.reserve(npx));
+        FIC_TRY(h->d_in_b.reserve(nc));
+        FIC_TRY(h->d_img.reserve(nc));
+        FIC_TRY(h->d_out_a.reserve(3 * npx));
+        FIC_TRY(fic_copy_in(h, h->d_in_a.p, y, npx, false, st));
+        FIC_TRY(fic_copy_in(h, h->d_in_b.p, cb, nc, false, st));
+        FIC_TRY(fic_copy_in(h, h->d_img.p, cr, nc, false, st));
+        d_y = h->d_in_a.as<uint8_t>();
+        d_cb = h->d_in_b.as<uint8_t>();
+        d_cr = h->d_img.as<uint8_t>();
+        d_rgb = h->d_out_a.as<uint8_t>();
+    }
+    FIC_TRY(ycbcr_to_rgb_impl(h, d_y, d_cb, d_cr, N, M, subsample, d_rgb, st));
+    if (!dev) {
+        FIC_TRY(fic_copy_out(h, rgb, d_rgb, 3 * npx, false, st));
         FIC_CUDA(cudaStreamSynchronize(st));
     }
     return FIC_OK;

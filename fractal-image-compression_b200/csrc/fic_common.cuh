@@ -111,7 +111,7 @@ struct fic_handle {
     DevBuf bf_boxsum, bf_stats, bf_partial, bf_ranges;
     DevBuf bf_pool, bf_poolx, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list;
     // decoders
-    DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red;
+    DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red, dec_keys, dec_roots;
     // quadtree / hv
     DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part;
 };
@@ -171,8 +171,14 @@ int bf_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int range,
 int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double* h_so, int n, int width, int height,
                    int iterations, uint8_t* d_out, cudaStream_t st);
 int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const double* d_so, int n, int H, int W,
-                     int iterations, double stop, int min_it, int max_it, int f32_affine, uint8_t* d_out,
+                     int iterations, double stop, int min_it, int max_it, int f32_affine, unsigned post, void* d_out,
                      int32_t* iters_done, cudaStream_t st);
+int qt_deblock_impl(fic_handle* h, const double* d_img, const int32_t* d_leaves, int n, int H, int W, const double* w4,
+                    int small_side, double* d_res, cudaStream_t st);
+int rgb_to_ycbcr_impl(fic_handle* h, const uint8_t* d_rgb, int N, int M, int subsample, uint8_t* d_y, uint8_t* d_cb,
+                      uint8_t* d_cr, cudaStream_t st);
+int ycbcr_to_rgb_impl(fic_handle* h, const uint8_t* d_y, const uint8_t* d_cb, const uint8_t* d_cr, int N, int M,
+                      int subsample, uint8_t* d_rgb, cudaStream_t st);
 int subsample_impl(fic_handle* h, const double* d_arr, int h2, int w2, int jit, double* d_out, cudaStream_t st);
 int qt_classify_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_blocks, int count,
                      int32_t* d_out, cudaStream_t st);

@@ -22,6 +22,8 @@ LIB_PATH = os.path.join(_HERE, "libfic_b200.so")
 DEVICE_PTRS = 1
 BF_EXACT_ONLY = 2
 BF_NO_FALLBACK = 4
+QT_DEBLOCK = 8
+TREE_OUT_F64 = 16
 BF_MODE_NUMPY = 0
 BF_MODE_JIT = 1
 TREE_QUADTREE = 0
@@ -65,6 +67,9 @@ SIGNATURES = {
                                 C.c_uint, _vp]),
     "fic_tree_decode": (C.c_int, [_vp, C.c_int, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int,
                                   C.c_int, C.c_int, _vp, _i32p, C.c_uint, _vp]),
+    "fic_qt_deblock": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_uint, _vp]),
+    "fic_rgb_to_ycbcr": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_uint, _vp]),
+    "fic_ycbcr_to_rgb": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
 }
 
 _lib = None
@@ -370,17 +375,95 @@ def hv_search(img, rects, scale_bits, offset_bits, max_scale=1.0, handle: Handle
 
 
 def tree_decode(kind, leaves, so, H, W, iterations=ITER_AUTO, stop_on_relative_error=5e-3, min_iterations=2,
-                max_iterations=10, f32_affine=False, handle: Handle | None = None):
+                max_iterations=10, f32_affine=False, handle: Handle | None = None, deblock=False, out_f64=False):
     """leaves[k] = (range_i, range_j, height, width, start_i, start_j, orientation, rotation); so[k] = (scale, offset).
-    Returns (uint8 image, sweeps run)."""
+    Returns (uint8 image, sweeps run).  deblock (quadtree): the reference's deblocking post-processor runs on the
+    float image before the clip; out_f64: the float64 image is returned unclipped instead of the bytes."""
     h = handle or default_handle()
     L = np.ascontiguousarray(leaves, np.int32).reshape(-1, 8)
     s = np.ascontiguousarray(so, np.float64).reshape(-1, 2)
     if L.shape[0] != s.shape[0]:
         raise ValueError("leaves and so disagree on the number of leaves")
-    out = np.zeros((int(H), int(W)), np.uint8)
+    out = np.zeros((int(H), int(W)), np.float64 if out_f64 else np.uint8)
     done = C.c_int32(0)
+    flags = (QT_DEBLOCK if deblock else 0) | (TREE_OUT_F64 if out_f64 else 0)
     _check(lib().fic_tree_decode(h.ptr, int(kind), _ptr(L), _ptr(s), L.shape[0], int(H), int(W), int(iterations),
                                  float(stop_on_relative_error), int(min_iterations), int(max_iterations),
-                                 int(bool(f32_affine)), _ptr(out), C.byref(done), 0, None), "fic_tree_decode")
+                                 int(bool(f32_affine)), _ptr(out), C.byref(done), flags, None), "fic_tree_decode")
     return out, int(done.value)
+
+
+def tree_decode_dev(h: Handle, kind, leaves_ptr: int, so_ptr: int, n: int, H: int, W: int, out_ptr: int,
+                    iterations=ITER_AUTO, stop_on_relative_error=5e-3, min_iterations=2, max_iterations=10,
+                    f32_affine=False, flags=0) -> int:
+    """fic_tree_decode on device buffers (leaves int32 [n,8], so float64 [n,2], out uint8 [H,W] or float64 with
+    TREE_OUT_F64); returns the sweeps run.  The AUTO stop rule still reads its two norms back every sweep."""
+    done = C.c_int32(0)
+    _check(lib().fic_tree_decode(h.ptr, int(kind), _vp(leaves_ptr), _vp(so_ptr), int(n), int(H), int(W), int(iterations),
+                                 float(stop_on_relative_error), int(min_iterations), int(max_iterations),
+                                 int(bool(f32_affine)), _vp(out_ptr), C.byref(done), DEVICE_PTRS | flags, None),
+           "fic_tree_decode")
+    return int(done.value)
+
+
+def qt_deblock(img, leaves, weights=None, max_depth_range_size=-1, handle: Handle | None = None) -> np.ndarray:
+    """DeblockingQuadtreePostprocessor.postprocess on a float64 image; leaves as for tree_decode, in any order."""
+    h = handle or default_handle()
+    a = np.ascontiguousarray(img, np.float64)
+    if a.ndim != 2:
+        raise ValueError("expected a 2-D image")
+    L = np.ascontiguousarray(leaves, np.int32).reshape(-1, 8)
+    w = None if weights is None else np.ascontiguousarray(weights, np.float64).reshape(4)
+    out = np.empty_like(a)
+    _check(lib().fic_qt_deblock(h.ptr, _ptr(a), _ptr(L), L.shape[0], a.shape[0], a.shape[1], None if w is None else _ptr(w),
+                                int(max_depth_range_size), _ptr(out), 0, None), "fic_qt_deblock")
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# colour planes
+# ----------------------------------------------------------------------------------------------
+def _subsample_flag(chroma_subsampling) -> int:
+    if chroma_subsampling in ("4:4:4", 0, False):
+        return 0
+    if chroma_subsampling in ("4:2:0", 1, True):
+        return 1
+    raise Exception("Unsupported chroma subsampling")
+
+
+def rgb_to_ycbcr(rgb, chroma_subsampling="4:2:0", handle: Handle | None = None):
+    """uint8 [N,M,3] -> (y, cb, cr) uint8 planes (utils.rgb_to_ycbcr)."""
+    h = handle or default_handle()
+    a = np.ascontiguousarray(rgb, np.uint8)
+    if a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("expected an [N, M, 3] uint8 image")
+    sub = _subsample_flag(chroma_subsampling)
+    N, M = a.shape[:2]
+    cs = (N // 2, (M + 1) // 2) if sub else (N, M)
+    y, cb, cr = np.empty((N, M), np.uint8), np.empty(cs, np.uint8), np.empty(cs, np.uint8)
+    _check(lib().fic_rgb_to_ycbcr(h.ptr, _ptr(a), N, M, sub, _ptr(y), _ptr(cb), _ptr(cr), 0, None), "fic_rgb_to_ycbcr")
+    return y, cb, cr
+
+
+def rgb_to_ycbcr_dev(h: Handle, rgb_ptr: int, N: int, M: int, chroma_subsampling, y_ptr: int, cb_ptr: int, cr_ptr: int):
+    _check(lib().fic_rgb_to_ycbcr(h.ptr, _vp(rgb_ptr), int(N), int(M), _subsample_flag(chroma_subsampling), _vp(y_ptr),
+                                  _vp(cb_ptr), _vp(cr_ptr), DEVICE_PTRS, None), "fic_rgb_to_ycbcr")
+
+
+def ycbcr_to_rgb_dev(h: Handle, y_ptr: int, cb_ptr: int, cr_ptr: int, N: int, M: int, chroma_subsampling, rgb_ptr: int):
+    _check(lib().fic_ycbcr_to_rgb(h.ptr, _vp(y_ptr), _vp(cb_ptr), _vp(cr_ptr), int(N), int(M),
+                                  _subsample_flag(chroma_subsampling), _vp(rgb_ptr), DEVICE_PTRS, None), "fic_ycbcr_to_rgb")
+
+
+def ycbcr_to_rgb(y, cb, cr, chroma_subsampling="4:2:0", handle: Handle | None = None) -> np.ndarray:
+    """(y, cb, cr) uint8 planes -> uint8 [N,M,3] (utils.ycbcr_to_rgb)."""
+    h = handle or default_handle()
+    y, cb, cr = (np.ascontiguousarray(p, np.uint8) for p in (y, cb, cr))
+    sub = _subsample_flag(chroma_subsampling)
+    N, M = y.shape
+    cs = (N // 2, (M + 1) // 2) if sub else (N, M)
+    if cb.shape != cs or cr.shape != cs:
+        raise ValueError(f"chroma planes {cb.shape}, {cr.shape} do not match a {N}x{M} image at this subsampling")
+    out = np.empty((N, M, 3), np.uint8)
+    _check(lib().fic_ycbcr_to_rgb(h.ptr, _ptr(y), _ptr(cb), _ptr(cr), N, M, sub, _ptr(out), 0, None), "fic_ycbcr_to_rgb")
+    return out

@@ -42,12 +42,19 @@ class QuadtreeEncoder:
         self.last_stream = None
 
     def encode(self, img: np.ndarray) -> QuadtreeImage:
-        height, width = img.shape
+        return self._encode(img, 0, img.shape)
+
+    def encode_device(self, img_ptr: int, height: int, width: int) -> QuadtreeImage:
+        """`encode` of a uint8 [height, width] plane that already lives in device memory (the colour wrapper's planes)."""
+        return self._encode(None, img_ptr, (height, width))
+
+    def _encode(self, img, img_ptr: int, shape) -> QuadtreeImage:
+        height, width = shape
         self.max_square_exponent = min(int(np.log2(height)), int(np.log2(width)))
         nodes, vals, n_roots = fic_b200.qt_encode(
             img, self.scale_bits, self.offset_bits, self.max_scale, self.full_class_search, self.only_positive_scale,
             2 ** self.min_range_exponent, 2 ** self.max_range_exponent, self.error_tolerance, self.domain_hstep,
-            self.domain_vstep)
+            self.domain_vstep, img_ptr=img_ptr, shape=shape)
         self.last_stream = (nodes, vals, n_roots)
         info = EncodingInfo(self.scale_bits, self.offset_bits, self.max_scale, width, height)
         return QuadtreeImage(info, stream_to_forest(nodes, vals, n_roots))

@@ -42,6 +42,8 @@ extern "C" {
 #define FIC_DEVICE_PTRS 1u  /* all buffer arguments are device pointers */
 #define FIC_BF_EXACT_ONLY 2u /* brute force: skip the tensor-core screen, run the exact scan only */
 #define FIC_BF_NO_FALLBACK 4u /* brute force (testing): fail instead of re-scanning ranges the screen could not decide */
+#define FIC_QT_DEBLOCK 8u     /* fic_tree_decode, quadtree: DeblockingQuadtreePostprocessor before the clip (decoder.py:58-59) */
+#define FIC_TREE_OUT_F64 16u  /* fic_tree_decode: `out` is double[H*W], the float image decoder.py:61 clips (not clipped here) */
 
 #define FIC_BF_MODE_NUMPY 0 /* BruteForceEncoder semantics  (bruteforce/bf_encoder.py)      */
 #define FIC_BF_MODE_JIT 1   /* JitedBruteForceEncoder semantics (bruteforce/jit_bfencoder.py) */
@@ -206,10 +208,39 @@ int fic_hv_search(fic_handle* h, const uint8_t* img, int H, int W, const int32_t
  * iterations = FIC_ITER_AUTO reproduces the 2 + <=8 sweep rule with the Frobenius stop test.
  * f32_affine != 0: HV only, `pooled*scale+offset` evaluated in float32 (python-float scale, i.e.
  * using_not_quantized_values()).  out uint8 [H,W]; *iters_done (host, may be NULL) = sweeps run.
+ * flags & FIC_QT_DEBLOCK (quadtree only): decode(qimg, DeblockingQuadtreePostprocessor()) -- the filter of
+ * fic_qt_deblock with the reference's default weights runs on the float image before the clip
+ * (decoder.py:58-61).  flags & FIC_TREE_OUT_F64: out is double[H*W] and receives that float image unclipped,
+ * which is what a caller-side QuadtreePostprocessor subclass is handed by the reference (decoder.py:59).
  */
 int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double* so, int n, int H, int W,
                     int iterations, double stop_on_relative_error, int min_iterations, int max_iterations,
                     int f32_affine, uint8_t* out, int32_t* iters_done, unsigned flags, void* stream);
+
+/* ---- quadtree post-processing ------------------------------------------------------------ */
+/*
+ * Replaces DeblockingQuadtreePostprocessor.postprocess (quadtree/postprocessing.py:24-71): img float64 [H,W] ->
+ * out float64 [H,W].  leaves as for fic_tree_decode (only range_i, range_j, size are read) in ANY order: the
+ * order-dependent overwrites of the reference (roots in _de_partition order, breadth first inside a root, four
+ * line assignments per leaf) are reproduced from the geometry.  weights = { own, neighbour } for blocks of side
+ * <= max_depth_range_size, then { own, neighbour } for larger ones (postprocessing.py:17-21); NULL and a negative
+ * max_depth_range_size select the reference's defaults { 5/6, 1-5/6, 2/3, 1-2/3 } and 4.
+ */
+int fic_qt_deblock(fic_handle* h, const double* img, const int32_t* leaves, int n, int H, int W, const double* weights,
+                   int max_depth_range_size, double* out, unsigned flags, void* stream);
+
+/* ---- colour planes ---------------------------------------------------------------------- */
+/*
+ * Replace utils.rgb_to_ycbcr (utils.py:36-63) and utils.ycbcr_to_rgb (utils.py:65-97), the plane fan-out either
+ * side of RGBQuadtreeEncoder / RGBQuadtreeDecoder (quadtree/rgb.py:24-27, 35-48).  rgb uint8 [N,M,3] interleaved;
+ * y uint8 [N,M]; subsample 0 = "4:4:4" (cb, cr [N,M]), 1 = "4:2:0" (cb, cr [N/2, (M+1)/2]).
+ * "4:2:0" is defined where the reference is: forward for even N (an odd N makes utils.py:58 raise or leave the last
+ * chroma row uninitialised), backward for N % 4 == 0 (otherwise utils.py:73-76 raises); FIC_EINVAL elsewhere.
+ */
+int fic_rgb_to_ycbcr(fic_handle* h, const uint8_t* rgb, int N, int M, int subsample, uint8_t* y, uint8_t* cb, uint8_t* cr,
+                     unsigned flags, void* stream);
+int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const uint8_t* cr, int N, int M, int subsample,
+                     uint8_t* rgb, unsigned flags, void* stream);
 
 #ifdef __cplusplus
 }

@@ -160,20 +160,6 @@ def test_rgb_stream_is_three_fqt_streams(golden, images):
         assert again.getvalue() == ref.getvalue()
 
 
-def test_colour_conversion_round_trip_shapes():
-    import utils
-    rng = np.random.default_rng(0)
-    for shape in ((8, 12, 3), (7, 9, 3), (4, 7, 3)):
-        rgb = rng.integers(0, 256, shape, dtype=np.uint8)
-        y, cb, cr = utils.rgb_to_ycbcr(rgb, "4:4:4")
-        assert y.shape == cb.shape == cr.shape == shape[:2]
-        back = utils.ycbcr_to_rgb((y, cb, cr), "4:4:4")
-        assert np.abs(back.astype(int) - rgb.astype(int)).max() <= 6
-    rgb = rng.integers(0, 256, (8, 12, 3), dtype=np.uint8)
-    y, cb, cr = utils.rgb_to_ycbcr(rgb, "4:2:0")
-    assert cb.shape == (4, 6) and utils.ycbcr_to_rgb((y, cb, cr), "4:2:0").shape == (8, 12, 3)
-
-
 def test_bitbuffer_write_many_equals_single_writes():
     """The vectorised field writer the serialisers use leaves the same bytes and the same pending state as one
     `write` per field, whatever is already pending (widths 0..32, values wider than their field are masked)."""
