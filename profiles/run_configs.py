@@ -108,3 +108,21 @@ t_dec96, dec96 = timed(lambda: fic_b200.bf_decode_batch(share_idx, share_so, 102
 emit(config=5, what="one synthetic 1024x1024x3 image, 3 planes brute force", encode_s=t_img, decode_s=t_dec3,
      decode_96_planes_s=t_dec96, planes_equal=bool(np.array_equal(dec96[3:6], dec3)),
      matches_per_s=3 * 16384 * 1008 * 1008 * 8 / t_img, batch_of_256_on_8_gpus_estimate_s=32 * t_img + t_dec96)
+
+# config 5 (ii): the reference's own colour entry point (quadtree/rgb.py:20-27) with the config-2 parameters, planes kept
+# in device memory; decode plain and with the stock deblocking filter fused into the decoder
+from quadtree.common import forest_to_leaves  # noqa: E402
+from quadtree.postprocessing import DeblockingQuadtreePostprocessor  # noqa: E402
+from quadtree.rgb import RGBQuadtreeDecoder, RGBQuadtreeEncoder  # noqa: E402
+rgb_hwc = np.ascontiguousarray(rgb.transpose(1, 2, 0))
+for mode in ("4:4:4", "4:2:0"):
+    enc = RGBQuadtreeEncoder(QuadtreeEncoder(*qp), QuadtreeEncoder(*qp))
+    t_enc, col = timed(lambda: enc.encode(rgb_hwc, mode), reps=2)
+    dec = RGBQuadtreeDecoder(QuadtreeDecoder())
+    t_dec, back = timed(lambda: dec.decode(col), reps=2)
+    t_decdb, backdb = timed(lambda: dec.decode(col, DeblockingQuadtreePostprocessor()), reps=2)
+    t_conv, planes = timed(lambda: fic_b200.rgb_to_ycbcr(rgb_hwc, mode), reps=3)
+    emit(config="5(ii)", what=f"RGBQuadtreeEncoder(7,5,1.0,..,4,8,2.0) 1024x1024x3 {mode}", encode_ms=t_enc * 1e3,
+         decode_ms=t_dec * 1e3, decode_deblocked_ms=t_decdb * 1e3, colour_conversion_host_arrays_ms=t_conv * 1e3,
+         leaves=[int(forest_to_leaves(p)[0].shape[0]) for p in (col.encoded_Y, col.encoded_Cb, col.encoded_Cr)],
+         psnr_db=psnr(back.astype(np.float64), rgb_hwc), psnr_deblocked_db=psnr(backdb.astype(np.float64), rgb_hwc))
