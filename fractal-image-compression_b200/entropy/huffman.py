@@ -11,6 +11,8 @@ import heapq
 from collections import Counter, deque
 from typing import Optional
 
+import numpy as np
+
 from bitbuffer import BitBuffer
 from entropy.abccodec import Code, CodeWidth, EntropyEncoder
 
@@ -58,13 +60,23 @@ class HuffmanNode:
         return self.left is None
 
 
+def ordered_counts(symbols) -> list[tuple[int, int]]:
+    """(symbol, frequency) in order of first occurrence -- what `Counter(symbols).items()` yields -- for a list or, without
+    a Python-level pass over the elements, for a numpy array."""
+    if isinstance(symbols, np.ndarray):
+        uniq, first, counts = np.unique(symbols, return_index=True, return_counts=True)
+        order = np.argsort(first, kind="stable")
+        return list(zip(uniq[order].tolist(), counts[order].tolist()))
+    return list(Counter(symbols).items())
+
+
 class HuffmanEncoder(EntropyEncoder):
     def __init__(self) -> None:
         self.root: Optional[HuffmanNode] = None
         self.coding_table: Optional[CodingTable] = None
 
     def prepare_for_encoding(self, symbols: list[int]) -> CodingTable:
-        heap = [HuffmanNode.Leaf(sym, freq) for sym, freq in Counter(symbols).items()]
+        heap = [HuffmanNode.Leaf(sym, freq) for sym, freq in ordered_counts(symbols)]
         heapq.heapify(heap)
         while len(heap) > 1:
             first = heapq.heappop(heap)       # becomes the left child: code bit 0

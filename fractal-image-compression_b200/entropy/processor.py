@@ -9,12 +9,12 @@ reused for the Y, Cb and Cr planes (quadtree/rgb.py:62-64).
 from __future__ import annotations
 
 from abc import ABC, abstractmethod
-from collections import Counter
 from enum import Enum
 
 from bitbuffer import BitBuffer
 from entropy.abccodec import Code, CodeWidth, EntropyEncoder, IdentityEncoder
-from entropy.huffman import CodingTable, HuffmanDecoder, HuffmanDeserializer, HuffmanEncoder, HuffmanSerializer
+from entropy.huffman import (CodingTable, HuffmanDecoder, HuffmanDeserializer, HuffmanEncoder, HuffmanSerializer,
+                             ordered_counts)
 
 
 class CodingDimension(Enum):
@@ -88,7 +88,7 @@ class HuffmanEntropyProcessor(EntropyProcessor):
 
     @staticmethod
     def _payload_bits_saved(table: CodingTable, values: list[int], raw_width: int) -> int:
-        return sum(count * (raw_width - table[sym][1]) for sym, count in Counter(values).items())
+        return sum(count * (raw_width - table[sym][1]) for sym, count in ordered_counts(values))
 
     def serialize_dimension_coding_structures(self, write_buff, dimension):
         coder = self.dimension_encoders[dimension.value]

@@ -76,7 +76,7 @@ class HVSerializer:
             leaf = self._kind == LEAF_BIT
             column = {CodingDimension.DOMAIN_ROW: 0, CodingDimension.DOMAIN_COL: 1, CodingDimension.SCALE: 4,
                       CodingDimension.OFFSET: 5}
-            values = {dim: self._fields[column[dim]][leaf].tolist() for dim in CodingDimension
+            values = {dim: np.ascontiguousarray(self._fields[column[dim]][leaf]) for dim in CodingDimension
                       if dim in self.entropy_coding_dimensions}
         gains = self.entropy_processor.prepare_for_encoding(values, get_dimension_bit_widths(self.img.info))
         self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}

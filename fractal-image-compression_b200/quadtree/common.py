@@ -64,10 +64,45 @@ class QuadtreeNode:
         return QuadtreeNode(None, [c1, c2, c3, c4])
 
 
-@dataclass
 class QuadtreeImage:
-    info: EncodingInfo
-    forest: list[QuadtreeNode]
+    """`info` + `forest`, as in the reference (common.py:45-48).
+
+    An image made by this package's encoder also carries the flat preorder stream `fic_qt_encode` returned.  The
+    `QuadtreeNode` / `Domain` objects of `forest` are created when somebody first asks for them -- and from that moment
+    the stream is dropped, because the objects may be edited.  Until then the decoder and the serialiser of this package
+    work on the stream with array operations (`flat_stream()`), which is what keeps encode -> decode and encode -> file at
+    kernel speed instead of at the speed of building and walking ~10^5 Python objects."""
+
+    __slots__ = ("info", "_forest", "_stream")
+
+    def __init__(self, info: EncodingInfo, forest: Optional[list[QuadtreeNode]] = None, *, stream=None) -> None:
+        if forest is None and stream is None:
+            raise TypeError("QuadtreeImage needs a forest")
+        self.info = info
+        self._forest = forest
+        self._stream = stream if forest is None else None
+
+    @property
+    def forest(self) -> list[QuadtreeNode]:
+        if self._forest is None:
+            self._forest = stream_to_forest(*self._stream)
+            self._stream = None
+        return self._forest
+
+    @forest.setter
+    def forest(self, value: list[QuadtreeNode]) -> None:
+        self._forest = value
+        self._stream = None
+
+    def flat_stream(self):
+        """(nodes[k,8] int32, vals[k,3] float64, n_roots) while nobody has seen the node objects, else None."""
+        return self._stream
+
+    def __eq__(self, other) -> bool:
+        return isinstance(other, QuadtreeImage) and self.info == other.info and self.forest == other.forest
+
+    def __repr__(self) -> str:
+        return f"QuadtreeImage(info={self.info!r}, forest=<{len(self.forest)} roots>)"
 
 
 @dataclass
@@ -165,14 +200,71 @@ def iter_root_squares(width: int, height: int, i: int = 0, j: int = 0):
         yield from iter_root_squares(side, height - side, i + side, j)
 
 
-def forest_to_leaves(qimg: QuadtreeImage, use_quantized_values: bool = True):
-    """Flatten to the arrays fic_tree_decode takes: leaves[k] = (ri, rj, size, size, di, dj, orient, rot),
-    so[k] = (scale, offset) de-quantised exactly as quadtree/decoder.py:90-98 does (the same float64 operations in
-    the same order, applied to whole columns)."""
-    info = qimg.info
+def _compact_even_bits(v: np.ndarray) -> np.ndarray:
+    """Bits 0, 2, 4, ... of v packed together (inverse of the Morton interleave), v < 2^32."""
+    v = v & np.uint64(0x55555555)
+    v = (v | (v >> np.uint64(1))) & np.uint64(0x33333333)
+    v = (v | (v >> np.uint64(2))) & np.uint64(0x0f0f0f0f)
+    v = (v | (v >> np.uint64(4))) & np.uint64(0x00ff00ff)
+    v = (v | (v >> np.uint64(8))) & np.uint64(0x0000ffff)
+    return v
+
+
+def stream_geometry(nodes: np.ndarray, n_roots: int, width: int, height: int):
+    """Where every node of a preorder stream sits: (root index, row, col, exponent, offset) per node, as int64 arrays.
+
+    Children are emitted TL, TR, BL, BR, so inside a root the leaves appear in Morton order and a node starts at the
+    Morton offset equal to the leaf area emitted before it; de-interleaving that offset gives its corner.  `offset` is
+    that Morton offset inside the root (breadth-first order of one level = ascending offset)."""
+    nodes = np.asarray(nodes)
+    roots = list(iter_root_squares(width, height))
+    if len(roots) != n_roots:
+        raise ValueError(f"forest has {n_roots} roots, the image geometry needs {len(roots)}")
+    e = nodes[:, 7].astype(np.int64)
+    area = np.where(nodes[:, 0] == 1, np.int64(1) << (2 * e), np.int64(0))
+    before = np.cumsum(area) - area
+    root_area = np.array([np.int64(1) << (2 * re) for _, _, re in roots], np.int64)
+    root_start = np.cumsum(root_area) - root_area
+    if int(area.sum()) != int(root_area.sum()):
+        raise ValueError("node stream does not cover the image")
+    root_of = np.searchsorted(root_start, before, side='right') - 1
+    off = before - root_start[root_of]
+    u = off.astype(np.uint64)
+    row = np.array([r[0] for r in roots], np.int64)[root_of] + _compact_even_bits(u >> np.uint64(1)).astype(np.int64)
+    col = np.array([r[1] for r in roots], np.int64)[root_of] + _compact_even_bits(u).astype(np.int64)
+    return root_of, row, col, e, off
+
+
+def _dequantise(qs: np.ndarray, qo: np.ndarray, info: EncodingInfo) -> np.ndarray:
+    """quadtree/decoder.py:90-98 on whole columns: the same float64 operations in the same order."""
     max_encoded_scale = np.float64(2 ** info.scale_bits)
     max_encoded_offset = np.float64(2 ** info.offset_bits)
     max_scale = info.max_scale
+    scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
+    mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
+    offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
+    return np.stack([scale, offset], axis=1) if len(qs) else np.zeros((0, 2))
+
+
+def forest_to_leaves(qimg: QuadtreeImage, use_quantized_values: bool = True):
+    """Flatten to the arrays fic_tree_decode takes: leaves[k] = (ri, rj, size, size, di, dj, orient, rot),
+    so[k] = (scale, offset) de-quantised exactly as quadtree/decoder.py:90-98 does (the same float64 operations in
+    the same order, applied to whole columns).  Leaves come out in preorder."""
+    info = qimg.info
+    flat = qimg.flat_stream()
+    if flat is not None:
+        nodes, vals, n_roots = flat
+        _, row, col, e, _ = stream_geometry(nodes, n_roots, info.img_width, info.img_height)
+        leaf = nodes[:, 0] == 1
+        side = (np.int64(1) << e[leaf])
+        leaves = np.empty((int(leaf.sum()), 8), np.int32)
+        leaves[:, 0], leaves[:, 1], leaves[:, 2], leaves[:, 3] = row[leaf], col[leaf], side, side
+        leaves[:, 4:8] = nodes[leaf, 1:5]
+        if use_quantized_values:
+            so = _dequantise(nodes[leaf, 5].astype(np.float64), nodes[leaf, 6].astype(np.float64), info)
+        else:
+            so = vals[leaf, :2]
+        return leaves, np.ascontiguousarray(so, np.float64).reshape(-1, 2)
     leaves: list[tuple] = []
     doms: list[Domain] = []
     roots = list(iter_root_squares(info.img_width, info.img_height))
@@ -195,12 +287,8 @@ def forest_to_leaves(qimg: QuadtreeImage, use_quantized_values: bool = True):
                 push((c[1], i, j + half, half))
                 push((c[0], i, j, half))
     if use_quantized_values:
-        qs = np.array([d.quantized_scale for d in doms], np.float64)
-        qo = np.array([d.quantized_offset for d in doms], np.float64)
-        scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
-        mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
-        offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
-        so = np.stack([scale, offset], axis=1) if len(doms) else np.zeros((0, 2))
+        so = _dequantise(np.array([d.quantized_scale for d in doms], np.float64),
+                         np.array([d.quantized_offset for d in doms], np.float64), info)
     else:
         so = np.array([(float(d.scale), float(d.offset)) for d in doms], np.float64)
     return np.array(leaves, np.int32).reshape(-1, 8), np.ascontiguousarray(so, np.float64).reshape(-1, 2)

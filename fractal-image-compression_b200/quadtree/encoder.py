@@ -11,7 +11,7 @@ from __future__ import annotations
 import numpy as np
 
 import fic_b200
-from quadtree.common import EncodingInfo, QuadtreeImage, stream_to_forest
+from quadtree.common import EncodingInfo, QuadtreeImage
 
 NUM_MEAN_CLASSES = 3
 NUM_VARIANCE_CLASSES = 24
@@ -57,7 +57,7 @@ class QuadtreeEncoder:
             self.domain_vstep, img_ptr=img_ptr, shape=shape)
         self.last_stream = (nodes, vals, n_roots)
         info = EncodingInfo(self.scale_bits, self.offset_bits, self.max_scale, width, height)
-        return QuadtreeImage(info, stream_to_forest(nodes, vals, n_roots))
+        return QuadtreeImage(info, stream=(nodes, vals, n_roots))   # node objects are built on first access
 
 
 def _classify(img: np.ndarray, start_i: int, start_j: int, side: int) -> tuple[int, int, int, int]:

@@ -16,7 +16,7 @@ from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_pr
 from bitbuffer import EOF, BitBuffer
 from entropy.processor import CodingDimension, EntropyProcessor
 from quadtree.common import (Domain, QuadtreeImage, QuadtreeNode, get_dimension_bit_widths,
-                             get_domain_dimension_extractors, iter_root_squares)
+                             get_domain_dimension_extractors, iter_root_squares, stream_geometry)
 
 QUADTREE_MAGIC = "quadtree".encode(encoding='ascii')
 INTERNAL_NODE_BIT = 0
@@ -65,12 +65,27 @@ class QuadtreeSerializer:
 
     def _choose_coded_dimensions(self):
         values: dict[CodingDimension, list[int]] = {}
+        flat = self.img.flat_stream()
+        self._geometry = None
+        if flat is not None:
+            info = self.img.info
+            self._geometry = stream_geometry(flat[0], flat[2], info.img_width, info.img_height)
         if self.entropy_coding_dimensions:
-            rows = [(d.start_i, d.start_j, d.quantized_scale, d.quantized_offset) for d in _leaves_breadth_first(self.img.forest)]
-            table = np.array(rows, np.int64).reshape(-1, 4)
+            if flat is not None:
+                # the single queue over all roots = level by level (relative to each root), roots in order, Morton inside
+                nodes = flat[0]
+                root_of, _, _, e, off = self._geometry
+                leaf = np.flatnonzero(nodes[:, 0] == LEAF_BIT)
+                depth = e[np.searchsorted(root_of, root_of[leaf])] - e[leaf]     # a root's node is its first in the stream
+                order = leaf[np.lexsort((off[leaf], root_of[leaf], depth))]
+                table = nodes[order][:, [1, 2, 5, 6]].astype(np.int64)
+            else:
+                rows = [(d.start_i, d.start_j, d.quantized_scale, d.quantized_offset)
+                        for d in _leaves_breadth_first(self.img.forest)]
+                table = np.array(rows, np.int64).reshape(-1, 4)
             column = {CodingDimension.DOMAIN_ROW: 0, CodingDimension.DOMAIN_COL: 1, CodingDimension.SCALE: 2,
                       CodingDimension.OFFSET: 3}
-            values = {dim: table[:, column[dim]].tolist() for dim in CodingDimension if dim in self.entropy_coding_dimensions}
+            values = {dim: np.ascontiguousarray(table[:, column[dim]]) for dim in CodingDimension if dim in self.entropy_coding_dimensions}
         gains = self.entropy_processor.prepare_for_encoding(values, get_dimension_bit_widths(self.img.info))
         # the reference overwrites the requested set with the profitable one (serialization.py:60)
         self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}
@@ -85,20 +100,26 @@ class QuadtreeSerializer:
 
     def _write_nodes(self, bits: BitBuffer):
         # node stream, breadth-first per root: leaf = 1, row, col, orientation (1), rotation (2), scale, offset; inner = 0
-        rows = []
-        add = rows.append
-        for root in self.img.forest:
-            pending = deque([root])
-            pop = pending.popleft
-            while pending:
-                node = pop()
-                d = node.domain
-                if d is not None:
-                    add((LEAF_BIT, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset))
-                else:
-                    add((INTERNAL_NODE_BIT, 0, 0, 0, 0, 0, 0))
-                    pending.extend(node.children)
-        table = np.array(rows, np.int64).reshape(-1, 7)
+        flat = self.img.flat_stream()
+        if flat is not None and self._geometry is not None:
+            # preorder stream -> breadth first per root: by root, then level (larger blocks first), then Morton offset
+            root_of, _, _, e, off = self._geometry
+            table = flat[0][np.lexsort((off, -e, root_of))][:, :7].astype(np.int64)
+        else:
+            rows = []
+            add = rows.append
+            for root in self.img.forest:
+                pending = deque([root])
+                pop = pending.popleft
+                while pending:
+                    node = pop()
+                    d = node.domain
+                    if d is not None:
+                        add((LEAF_BIT, d.start_i, d.start_j, d.orientation, d.rotation, d.quantized_scale, d.quantized_offset))
+                    else:
+                        add((INTERNAL_NODE_BIT, 0, 0, 0, 0, 0, 0))
+                        pending.extend(node.children)
+            table = np.array(rows, np.int64).reshape(-1, 7)
         leaf = table[:, 0] == LEAF_BIT
         n = table.shape[0]
         vals = np.zeros((n, 7), np.uint64)

@@ -89,6 +89,42 @@ def test_fqt_files_are_reproduced_byte_for_byte(golden, images, name, fqt):
         assert len(plain.getvalue()) == 16566
 
 
+@pytest.mark.parametrize("name,fqt", [("cauliflower256", "kalafior256.fqt"), ("lena313x413", "lena313x413.fqt"),
+                                      ("cauliflower240x92", None), ("cauliflower64", None)])
+def test_flat_stream_paths_equal_object_paths(orc, golden, images, name, fqt):
+    """An image that still carries the encoder's flat stream is flattened for the decoder and written to a file with
+    array operations; both must give exactly what walking the node objects gives (and the bundled files)."""
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from quadtree.common import EncodingInfo, QuadtreeImage, forest_to_leaves, stream_to_forest
+    from quadtree.serialization import QuadtreeSerializer
+    p = qt_params(golden["qt_golden"], name)
+    img = images[name]
+    nodes, vals, n_roots = orc.qt_encode(img, *p)           # the stream layout of fic_qt_encode, exponent column included
+    info = EncodingInfo(p[0], p[1], p[2], img.shape[1], img.shape[0])
+
+    def lazy():
+        return QuadtreeImage(info, stream=(nodes, vals, n_roots))
+
+    objects = QuadtreeImage(info, stream_to_forest(nodes, vals, n_roots))
+    assert objects.flat_stream() is None
+    for quantised in (True, False):
+        a, b = forest_to_leaves(lazy(), quantised), forest_to_leaves(objects, quantised)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    for dims in (set(CodingDimension), set(), {CodingDimension.SCALE}):
+        fast, slow = io.BytesIO(), io.BytesIO()
+        q = lazy()
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(q, fast)
+        assert q.flat_stream() is not None                  # writing a file does not build the objects
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(objects, slow)
+        assert fast.getvalue() == slow.getvalue()
+        if fqt and dims == set(CodingDimension):
+            assert fast.getvalue() == open(golden.path(fqt), "rb").read()
+    q = lazy()
+    assert len(q.forest) == n_roots and q.flat_stream() is None      # first look at the objects drops the stream
+    q.forest = objects.forest
+    assert q == objects
+
+
 def test_legacy_fqt_header_is_rejected_like_the_reference():
     from quadtree.serialization import QuadtreeDeserializer
     legacy = struct.pack("!8sfBBHHI", b"quadtree", 1.0, 7, 5, 380, 322, 0) + b"\x00" * 8   # entropy id 0
