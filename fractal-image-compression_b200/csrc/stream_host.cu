@@ -2,6 +2,7 @@
 // decoder kernels without one Python call per bit:
 //   fic_tree_read_nodes   QuadtreeDeserializer._read_data (quadtree/serialization.py:182-223) and
 //                         HVDeserializer._read_data (hvv2/serialization.py:186-224)
+//   fic_pack_fields       BitBuffer.write applied to a whole column of fields (bitbuffer.py:18-37)
 //   fic_hv_layout         the rectangle of every node of an HV preorder stream (hvv2/decoder.py:59-88 walks the same
 //                         splits) and its depth -- what the decoder's leaf table and the writer's breadth-first order need
 // No device work here; the file is a .cu only so that it builds with the rest of the library.
@@ -126,6 +127,43 @@ int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t b
     }
     *end_bit = br.pos;
     return count;
+}
+
+int64_t fic_pack_fields(const uint64_t* values, const int64_t* widths, int64_t n, uint32_t pending, int pending_bits,
+                        uint8_t* out, int64_t out_cap, uint32_t* rest, int* rest_bits)
+{
+    if (!values || !widths || !out || !rest || !rest_bits || n < 0 || pending_bits < 0 || pending_bits > 31) {
+        fic_set_error("fic_pack_fields: bad arguments");
+        return FIC_EINVAL;
+    }
+    // bitbuffer.py:18-37: fields are appended most significant bit first; a big-endian 32-bit word leaves the moment it fills
+    uint64_t acc = pending_bits ? (pending & ((1u << pending_bits) - 1u)) : 0;   // pending bits, right-aligned
+    int have = pending_bits;
+    int64_t written = 0;
+    for (int64_t k = 0; k < n; ++k) {
+        int w = (int)widths[k];
+        if (w < 0 || w > 64) { fic_set_error("fic_pack_fields: field %lld has width %d", (long long)k, w); return FIC_EINVAL; }
+        uint64_t v = values[k];
+        while (w > 0) {
+            const int take = w < 32 - have ? w : 32 - have;
+            const uint64_t piece = (v >> (w - take)) & ((take == 64) ? ~0ull : ((1ull << take) - 1ull));
+            acc = (acc << take) | piece;
+            have += take;
+            w -= take;
+            if (have == 32) {
+                if (written + 4 > out_cap) { fic_set_error("fic_pack_fields: output capacity too small"); return FIC_ECAP; }
+                out[written++] = (uint8_t)(acc >> 24);
+                out[written++] = (uint8_t)(acc >> 16);
+                out[written++] = (uint8_t)(acc >> 8);
+                out[written++] = (uint8_t)acc;
+                acc = 0;
+                have = 0;
+            }
+        }
+    }
+    *rest = (uint32_t)acc;
+    *rest_bits = have;
+    return written;
 }
 
 int fic_hv_layout(const int32_t* nodes, int n, int H, int W, int32_t* rects, int32_t* depth)

@@ -70,6 +70,10 @@ SIGNATURES = {
     "fic_qt_deblock": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_uint, _vp]),
     "fic_rgb_to_ycbcr": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_uint, _vp]),
     "fic_ycbcr_to_rgb": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
+    "fic_tree_read_nodes": (C.c_int, [C.c_int, _vp, C.c_int64, C.c_int64, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int, _i64p]),
+    "fic_hv_layout": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "fic_pack_fields": (C.c_int64, [_vp, _vp, C.c_int64, C.c_uint32, C.c_int, _vp, C.c_int64, C.POINTER(C.c_uint32),
+                                    C.POINTER(C.c_int)]),
 }
 
 _lib = None
@@ -467,3 +471,45 @@ def ycbcr_to_rgb(y, cb, cr, chroma_subsampling="4:2:0", handle: Handle | None = 
     out = np.empty((N, M, 3), np.uint8)
     _check(lib().fic_ycbcr_to_rgb(h.ptr, _ptr(y), _ptr(cb), _ptr(cr), N, M, sub, _ptr(out), 0, None), "fic_ycbcr_to_rgb")
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# container files (host only)
+# ----------------------------------------------------------------------------------------------
+def tree_read_nodes(kind, data: bytes, bit_pos: int, root_exps, raw_width, huff_root, huff_table, cap: int):
+    """Node section of a `.fqt` / HV stream -> (preorder nodes[k,8] int32, first bit after the section)."""
+    buf = np.frombuffer(data, np.uint8)
+    exps = np.ascontiguousarray(root_exps if root_exps is not None else [0], np.int32)
+    rw = np.ascontiguousarray(raw_width, np.int32).reshape(4)
+    hr = np.ascontiguousarray(huff_root, np.int32).reshape(4)
+    ht = np.ascontiguousarray(huff_table, np.int32).reshape(-1, 3)
+    if ht.shape[0] == 0:
+        ht = np.zeros((1, 3), np.int32)
+    nodes = np.empty((int(cap), 8), np.int32)
+    end = C.c_int64(0)
+    n = _check(lib().fic_tree_read_nodes(int(kind), buf.ctypes.data_as(_vp), buf.size, int(bit_pos), _ptr(exps),
+                                         exps.shape[0] if kind == TREE_QUADTREE else 1, _ptr(rw), _ptr(hr), _ptr(ht),
+                                         _ptr(nodes), int(cap), C.byref(end)), "fic_tree_read_nodes")
+    return nodes[:n].copy(), int(end.value)
+
+
+def pack_fields(values, widths, pending: int = 0, pending_bits: int = 0):
+    """BitBuffer.write for whole columns: returns (bytes of the completed 32-bit words, pending value, pending bit count)."""
+    v = np.ascontiguousarray(values, np.uint64).ravel()
+    w = np.ascontiguousarray(widths, np.int64).ravel()
+    if v.size != w.size:
+        raise ValueError("values and widths differ in length")
+    out = np.empty(((int(w.sum()) + int(pending_bits)) // 32 + 1) * 4, np.uint8)
+    rest, rest_bits = C.c_uint32(0), C.c_int(0)
+    n = _check(lib().fic_pack_fields(_ptr(v), _ptr(w), v.size, int(pending) & 0xffffffff, int(pending_bits), _ptr(out), out.size,
+                                     C.byref(rest), C.byref(rest_bits)), "fic_pack_fields")
+    return out[:n].tobytes(), int(rest.value), int(rest_bits.value)
+
+
+def hv_layout(nodes, H: int, W: int):
+    """(rects[k,4] = i, j, w, h ; depth[k]) of every node of an HV preorder stream."""
+    a = np.ascontiguousarray(nodes, np.int32).reshape(-1, 8)
+    rects = np.empty((a.shape[0], 4), np.int32)
+    depth = np.empty(a.shape[0], np.int32)
+    _check(lib().fic_hv_layout(_ptr(a), a.shape[0], int(H), int(W), _ptr(rects), _ptr(depth)), "fic_hv_layout")
+    return rects, depth

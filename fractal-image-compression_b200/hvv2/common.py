@@ -53,10 +53,41 @@ class HVNode:
         return HVNode(None, None, None, domain)
 
 
-@dataclass
 class HVImage:
-    info: EncodingInfo
-    root: HVNode
+    """`info` + `root`, as in the reference (hvv2/common.py:42-45).  An image made by this package's encoder or reader
+    also carries the flat preorder stream; the `HVNode` objects are built when `root` is first read, and from then on the
+    stream is dropped (the objects may be edited).  Until then decoder and writer work on the stream (`flat_stream()`)."""
+
+    __slots__ = ("info", "_root", "_stream")
+
+    def __init__(self, info: EncodingInfo, root: Optional[HVNode] = None, *, stream=None) -> None:
+        if root is None and stream is None:
+            raise TypeError("HVImage needs a root")
+        self.info = info
+        self._root = root
+        self._stream = stream if root is None else None
+
+    @property
+    def root(self) -> HVNode:
+        if self._root is None:
+            self._root = stream_to_tree(*self._stream)
+            self._stream = None
+        return self._root
+
+    @root.setter
+    def root(self, value: HVNode) -> None:
+        self._root = value
+        self._stream = None
+
+    def flat_stream(self):
+        """(nodes[k,8] int32, vals[k,>=2] float64) while nobody has seen the node objects, else None."""
+        return self._stream
+
+    def __eq__(self, other) -> bool:
+        return isinstance(other, HVImage) and self.info == other.info and self.root == other.root
+
+    def __repr__(self) -> str:
+        return f"HVImage(info={self.info!r})"
 
 
 def stream_to_tree(nodes: np.ndarray, vals: np.ndarray) -> HVNode:
@@ -104,13 +135,35 @@ def _build_tree(cols, sc, of, n) -> HVNode:
     return root
 
 
-def tree_to_leaves(hv_img: HVImage, use_quantized_values: bool = True):
-    """leaves[k] = (ri, rj, h, w, di, dj, orient, rot), so[k] = (scale, offset) as hvv2/decoder.py:59-74 (the same float64
-    operations in the same order, applied to whole columns)."""
-    info = hv_img.info
+def _dequantise(qs: np.ndarray, qo: np.ndarray, info: EncodingInfo) -> np.ndarray:
+    """hvv2/decoder.py:64-71 on whole columns: the same float64 operations in the same order."""
     max_encoded_scale = np.float64(2 ** info.scale_bits)
     max_encoded_offset = np.float64(2 ** info.offset_bits)
     max_scale = info.max_scale
+    scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
+    mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
+    offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
+    return np.stack([scale, offset], axis=1) if len(qs) else np.zeros((0, 2))
+
+
+def tree_to_leaves(hv_img: HVImage, use_quantized_values: bool = True):
+    """leaves[k] = (ri, rj, h, w, di, dj, orient, rot), so[k] = (scale, offset) as hvv2/decoder.py:59-88 (the same float64
+    operations in the same order, applied to whole columns).  Leaves come out in preorder."""
+    info = hv_img.info
+    flat = hv_img.flat_stream()
+    if flat is not None:
+        import fic_b200
+        nodes, vals = flat
+        rects, _ = fic_b200.hv_layout(nodes, info.img_height, info.img_width)
+        leaf = nodes[:, 0] == 1
+        leaves = np.empty((int(leaf.sum()), 8), np.int32)
+        leaves[:, 0], leaves[:, 1], leaves[:, 2], leaves[:, 3] = rects[leaf, 0], rects[leaf, 1], rects[leaf, 3], rects[leaf, 2]
+        leaves[:, 4:8] = nodes[leaf, 1:5]
+        if use_quantized_values:
+            so = _dequantise(nodes[leaf, 5].astype(np.float64), nodes[leaf, 6].astype(np.float64), info)
+        else:
+            so = vals[leaf, :2]
+        return leaves, np.ascontiguousarray(so, np.float64).reshape(-1, 2)
     leaves, doms = [], []
     stack = [(hv_img.root, 0, 0, info.img_width, info.img_height)]
     pop, push = stack.pop, stack.append
@@ -129,12 +182,8 @@ def tree_to_leaves(hv_img: HVImage, use_quantized_values: bool = True):
                 push((node.c2, i + s + 1, j, w, h - s - 1))
                 push((node.c1, i, j, w, s + 1))
     if use_quantized_values:
-        qs = np.array([d.quantized_scale for d in doms], np.float64)
-        qo = np.array([d.quantized_offset for d in doms], np.float64)
-        scale = qs * (2 * max_scale) / max_encoded_scale - max_scale
-        mul_coef = np.where(scale < 0, float(MAX_GRAY) * (1 + scale), float(MAX_GRAY))
-        offset = qo / max_encoded_offset * mul_coef - MAX_GRAY * scale
-        so = np.stack([scale, offset], axis=1) if len(doms) else np.zeros((0, 2))
+        so = _dequantise(np.array([d.quantized_scale for d in doms], np.float64),
+                         np.array([d.quantized_offset for d in doms], np.float64), info)
     else:
         so = np.array([(float(d.scale), float(d.offset)) for d in doms], np.float64)
     return np.array(leaves, np.int32).reshape(-1, 8), np.ascontiguousarray(so, np.float64).reshape(-1, 2)

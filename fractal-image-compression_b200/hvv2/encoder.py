@@ -7,7 +7,7 @@ from __future__ import annotations
 import numpy as np
 
 import fic_b200
-from hvv2.common import HVImage, stream_to_tree
+from hvv2.common import HVImage
 from quadtree.common import EncodingInfo
 
 
@@ -31,4 +31,4 @@ class HVEncoder:
         self.last_stream = (nodes, vals)
         info = EncodingInfo(scale_bits=self.scale_bits, offset_bits=self.offset_bits, max_scale=self.max_scale,
                             img_width=img.shape[1], img_height=img.shape[0])
-        return HVImage(info=info, root=stream_to_tree(nodes, vals))
+        return HVImage(info=info, stream=(nodes, vals))   # node objects are built on first access

@@ -9,7 +9,7 @@ from typing import BinaryIO
 
 import numpy as np
 
-from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_preamble
+from _stream import BYTE_ORDER, open_target, patch_size, read_nodes_native, read_preamble, write_preamble
 from bitbuffer import EOF, BitBuffer
 from entropy.processor import CodingDimension, EntropyProcessor
 from hvv2.common import Domain, HVImage, HVNode, SplitInfo
@@ -52,6 +52,19 @@ class HVSerializer:
     def _walk(self):
         """One breadth-first pass over the tree (the order of the node stream and of the Huffman statistics alike):
         per node its kind and raw fields, as columns."""
+        flat = self.img.flat_stream()
+        if flat is not None:
+            # nodes of one level appear in a preorder stream from left to right: breadth-first = stable sort by depth
+            import fic_b200
+            nodes = flat[0]
+            info = self.img.info
+            _, depth = fic_b200.hv_layout(nodes, info.img_height, info.img_width)
+            table = nodes[np.argsort(depth, kind="stable")][:, :7].astype(np.int64)
+            leaf = table[:, 0] == LEAF_BIT
+            table[leaf, 4] //= 2                       # rotation is stored as rotation // 2 (one bit)
+            self._kind = table[:, 0]
+            self._fields = [table[:, c] for c in range(1, 7)]
+            return
         rows = []
         add = rows.append
         pending = deque([self.img.root])
@@ -128,7 +141,12 @@ class HVDeserializer:
             self.file = f
             bits = BitBuffer(f, BYTE_ORDER)
             info, self.size, self.entropy_processor = read_preamble(f, bits, HV_MAGIC, 'hv')
-            self.img = HVImage(info, self._read_tree(bits))
+            nodes = read_nodes_native(f, bits, self.entropy_processor, fic_tree_kind=1, root_exps=None,
+                                      cap=2 * info.img_width * info.img_height + 64)
+            if nodes is not None:
+                self.img = HVImage(info, stream=(nodes, np.zeros((nodes.shape[0], 2))))
+            else:
+                self.img = HVImage(info, self._read_tree(bits))
             return self.img
 
     def _read_tree(self, bits: BitBuffer) -> HVNode:

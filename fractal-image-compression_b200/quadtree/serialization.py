@@ -12,7 +12,7 @@ from typing import BinaryIO
 
 import numpy as np
 
-from _stream import BYTE_ORDER, open_target, patch_size, read_preamble, write_preamble
+from _stream import BYTE_ORDER, open_target, patch_size, read_nodes_native, read_preamble, write_preamble
 from bitbuffer import EOF, BitBuffer
 from entropy.processor import CodingDimension, EntropyProcessor
 from quadtree.common import (Domain, QuadtreeImage, QuadtreeNode, get_dimension_bit_widths,
@@ -148,7 +148,13 @@ class QuadtreeDeserializer:
             self.file = f
             bits = BitBuffer(f, BYTE_ORDER)
             info, self.size, self.entropy_processor = read_preamble(f, bits, QUADTREE_MAGIC, 'quadtree')
-            self.img = QuadtreeImage(info, self._read_forest(bits, info))
+            exps = [e for _, _, e in iter_root_squares(info.img_width, info.img_height)]
+            nodes = read_nodes_native(f, bits, self.entropy_processor, fic_tree_kind=0, root_exps=exps,
+                                      cap=2 * info.img_width * info.img_height + 64)
+            if nodes is not None:
+                self.img = QuadtreeImage(info, stream=(nodes, np.zeros((nodes.shape[0], 3)), len(exps)))
+            else:
+                self.img = QuadtreeImage(info, self._read_forest(bits, info))
             return self.img
 
     def _read_forest(self, bits: BitBuffer, info) -> list[QuadtreeNode]:

@@ -242,6 +242,34 @@ int fic_rgb_to_ycbcr(fic_handle* h, const uint8_t* rgb, int N, int M, int subsam
 int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const uint8_t* cr, int N, int M, int subsample,
                      uint8_t* rgb, unsigned flags, void* stream);
 
+/* ---- container files (host only, no device work) ------------------------------------------ */
+/*
+ * Replaces the node loops of QuadtreeDeserializer._read_data (quadtree/serialization.py:182-223) and
+ * HVDeserializer._read_data (hvv2/serialization.py:186-224): reads the node section of a `.fqt` / HV stream -- per
+ * root a breadth-first list of `1` + row, col, orientation (1 bit), rotation (quadtree 2 bits; HV 1 bit, doubled),
+ * scale, offset for a leaf, `0` (HV: + vertical flag + 16-bit split index) for an inner node -- and returns it as
+ * the PREORDER stream fic_qt_encode / fic_hv_encode produce (nodes[k][8]; quadtree: size exponent in column 7).
+ * data/nbytes: the file from any word boundary on; bit_pos: first bit of the node section, bits counted MSB first
+ * (bitbuffer.py:39-56).  Fields are coded per CodingDimension (entropy/processor.py:11-16: row, col, scale, offset):
+ * huff_root[d] < 0 = raw_width[d] plain bits, else the index of the root of a Huffman tree in huff_table[m][3] =
+ * { left, right, value }, left < 0 marking a leaf (entropy/huffman.py:100-124).  root_exps: the quadtree roots' size
+ * exponents in _de_partition order (HV: n_roots = 1, root_exps unused).  *end_bit = first bit after the section.
+ * Returns the node count, FIC_ECAP, or FIC_EINVAL when the data ends early (the reference's "buffer returned EOF").
+ */
+int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t bit_pos, const int32_t* root_exps,
+                        int n_roots, const int32_t* raw_width, const int32_t* huff_root, const int32_t* huff_table,
+                        int32_t* nodes, int cap, int64_t* end_bit);
+
+/* BitBuffer.write (bitbuffer.py:18-37) for n fields at once: the low widths[k] bits of values[k], most significant bit
+ * first, appended to `pending_bits` (< 32) pending bits; every completed big-endian 32-bit word goes to `out`.
+ * Returns the bytes written (a multiple of 4); *rest / *rest_bits = the bits still pending afterwards. */
+int64_t fic_pack_fields(const uint64_t* values, const int64_t* widths, int64_t n, uint32_t pending, int pending_bits,
+                        uint8_t* out, int64_t out_cap, uint32_t* rest, int* rest_bits);
+
+/* Rectangle rects[k] = { i, j, w, h } and depth of every node of an HV preorder stream over an H x W image: the split
+ * walk of HVDecoder (hvv2/decoder.py:59-88; child 1 keeps split_idx + 1 columns / rows). */
+int fic_hv_layout(const int32_t* nodes, int n, int H, int W, int32_t* rects, int32_t* depth);
+
 #ifdef __cplusplus
 }
 #endif

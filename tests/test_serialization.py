@@ -125,6 +125,83 @@ def test_flat_stream_paths_equal_object_paths(orc, golden, images, name, fqt):
     assert q == objects
 
 
+def _preorder(node, out, children):
+    out.append(node)
+    for c in children(node):
+        _preorder(c, out, children)
+    return out
+
+
+@pytest.mark.parametrize("fqt", ["kalafior256.fqt", "lena313x413.fqt"])
+def test_native_fqt_reader_equals_bit_by_bit_reader(golden, fqt):
+    """`fic_tree_read_nodes` (the reader the deserialiser uses) against the field-by-field Python loop on the bundled files."""
+    from _stream import read_preamble
+    from bitbuffer import BitBuffer
+    from quadtree.serialization import QUADTREE_MAGIC, QuadtreeDeserializer
+    blob = open(golden.path(fqt), "rb").read()
+    fast = QuadtreeDeserializer().deserialize(io.BytesIO(blob))
+    assert fast.flat_stream() is not None
+    f = io.BytesIO(blob)
+    bits = BitBuffer(f, "!")
+    slow = QuadtreeDeserializer()
+    info, slow.size, slow.entropy_processor = read_preamble(f, bits, QUADTREE_MAGIC, 'quadtree')
+    forest = slow._read_forest(bits, info)
+    assert info == fast.info and len(forest) == len(fast.forest)
+    for a, b in zip(forest, fast.forest):
+        na = _preorder(a, [], lambda n: n.children or [])
+        nb = _preorder(b, [], lambda n: n.children or [])
+        assert len(na) == len(nb)
+        assert all((x.domain is None) == (y.domain is None) and x.domain == y.domain for x, y in zip(na, nb))
+
+
+def test_native_reader_reports_truncated_files(golden):
+    from quadtree.serialization import QuadtreeDeserializer
+    blob = open(golden.path("kalafior256.fqt"), "rb").read()
+    with pytest.raises(AssertionError, match="EOF"):        # the reference asserts (serialization.py:188)
+        QuadtreeDeserializer().deserialize(io.BytesIO(blob[:len(blob) // 2]))
+
+
+@pytest.mark.parametrize("name", ["lena64", "lena48x80", "cauliflower240x92", "lena256"])
+def test_hv_flat_stream_paths_equal_object_paths(golden, name):
+    """HV images that still carry their flat stream: leaf table, file writer and native reader against the object walks."""
+    from _stream import read_preamble
+    from bitbuffer import BitBuffer
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from hvv2.common import HVImage, stream_to_tree, tree_to_leaves
+    from hvv2.serialization import HV_MAGIC, HVDeserializer, HVSerializer
+    from quadtree.common import EncodingInfo
+    g = golden["hv_golden"]
+    p = hv_params(g, name)
+    H, W = g[f"{name}_dec"].shape
+    nodes = np.ascontiguousarray(np.c_[g[f"{name}_nodes"], np.zeros(len(g[f"{name}_nodes"]), np.int32)], np.int32)
+    vals = np.c_[g[f"{name}_vals"], np.zeros(len(g[f"{name}_vals"]))]
+    info = EncodingInfo(p[4], p[5], 1.0, W, H)
+    objects = HVImage(info, stream_to_tree(nodes, vals))
+    assert objects.flat_stream() is None
+    for quantised in (True, False):
+        a, b = tree_to_leaves(HVImage(info, stream=(nodes, vals)), quantised), tree_to_leaves(objects, quantised)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    blobs = []
+    for dims in (set(CodingDimension), set()):
+        fast, slow = io.BytesIO(), io.BytesIO()
+        lazy = HVImage(info, stream=(nodes, vals))
+        HVSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(lazy, fast)
+        assert lazy.flat_stream() is not None
+        HVSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(objects, slow)
+        assert fast.getvalue() == slow.getvalue()
+        blobs.append(fast.getvalue())
+    for blob in blobs:
+        back = HVDeserializer().deserialize(io.BytesIO(blob))
+        got = back.flat_stream()
+        assert got is not None and np.array_equal(got[0][:, :7], nodes[:, :7])
+        f = io.BytesIO(blob)
+        bits = BitBuffer(f, "!")
+        slow = HVDeserializer()
+        _, slow.size, slow.entropy_processor = read_preamble(f, bits, HV_MAGIC, 'hv')
+        a, b = tree_to_leaves(HVImage(info, slow._read_tree(bits))), tree_to_leaves(back)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
 def test_legacy_fqt_header_is_rejected_like_the_reference():
     from quadtree.serialization import QuadtreeDeserializer
     legacy = struct.pack("!8sfBBHHI", b"quadtree", 1.0, 7, 5, 380, 322, 0) + b"\x00" * 8   # entropy id 0
