@@ -53,7 +53,22 @@ t_gpu, q = timed(lambda: QuadtreeEncoder(*qp).encode(img))
 t_raw, _ = timed(lambda: fic_b200.qt_encode(img, *qp))
 t_cpu, ref = timed(lambda: orc.qt_encode(img, *qp), reps=1)
 t_qdec, qdec = timed(lambda: QuadtreeDecoder().decode(q))
+from quadtree.serialization import QuadtreeDeserializer, QuadtreeSerializer  # noqa: E402
+import io  # noqa: E402
+from entropy.processor import CodingDimension, HuffmanEntropyProcessor  # noqa: E402
+
+
+def qt_to_file():
+    out = io.BytesIO()
+    QuadtreeSerializer(HuffmanEntropyProcessor(), set(CodingDimension)).serialize(QuadtreeEncoder(*qp).encode(img), out)
+    return out.getvalue()
+
+
+t_file, qblob = timed(qt_to_file)
+t_back, qback = timed(lambda: QuadtreeDecoder().decode(QuadtreeDeserializer().deserialize(io.BytesIO(qblob))))
 emit(config=2, what="quadtree 512x512 (7,5,1.0,False,False,4,8,2.0)", encode_ms_class_api=t_gpu * 1e3, encode_ms_c_abi=t_raw * 1e3,
+     image_to_fqt_bytes_ms=t_file * 1e3, fqt_bytes=len(qblob), fqt_bytes_to_image_ms=t_back * 1e3,
+     file_round_trip_equals_decode=bool(np.array_equal(qback, qdec)),
      oracle_cpu_ms=t_cpu * 1e3, decode_ms=t_qdec * 1e3, psnr_db=psnr(qdec, img), nodes=int(len(ref[0])),
      reference_cpu_s="3.74 (BASELINE.md)")
 
@@ -77,8 +92,11 @@ def hv_to_bytes():
 
 
 t_ser, blob = timed(hv_to_bytes, reps=3)
+from hvv2.serialization import HVDeserializer  # noqa: E402
+t_hback, hback = timed(lambda: HVDecoder().decode(HVDeserializer().deserialize(io.BytesIO(blob))))
 emit(config=3, what="HV 512x512 (4,4,16,16,5,7,25.0)", encode_ms=t_gpu * 1e3, entropy_coded_stream_ms=t_ser * 1e3,
-     stream_bytes=len(blob), decode_ms=t_hdec * 1e3, psnr_db=psnr(hdec, img),
+     stream_bytes=len(blob), decode_ms=t_hdec * 1e3, file_bytes_to_image_ms=t_hback * 1e3,
+     file_round_trip_equals_decode=bool(np.array_equal(hback, hdec)), psnr_db=psnr(hdec, img),
      leaves_reference=leaves, reference_cpu_s="1688 (BASELINE.md), 1578 when the golden file was made")
 
 # config 4: synthetic 4096x4096 brute force on one GPU (+ a 1/8 range slice as one rank of eight would run it)
