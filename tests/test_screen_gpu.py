@@ -151,6 +151,28 @@ def test_three_round_plan_on_a_large_image(fic):
     assert np.array_equal(part[0], idx[5000:5256]) and np.array_equal(part[1], so[5000:5256])
 
 
+def test_full_size_4096_properties(fic):
+    """BASELINE configs[3] at its full size (4096 x 4096, 262 144 ranges x 16.6 M candidates x 8 isometries -- out of any
+    CPU oracle's reach): size-independent properties.  Scattered ranges equal the exhaustive exact scan, a 1/8 range slice
+    run on its own (what one rank of eight does) equals the same rows of the full encode, every record points inside the
+    image, and no range was left undecided."""
+    img = synthetic_image(0, 4096, 4096)
+    n = 512 * 512
+    h = fic.default_handle()
+    h.reset_counters()
+    idx, so, R = fic.bf_encode(img, mode=fic.BF_MODE_JIT)
+    c = h.counters()
+    assert c["screen_ranges"] + c["rescan_ranges"] == n
+    assert idx[:, 0].min() >= 0 and idx[:, 1].min() >= 0 and idx[:, 0].max() <= 4096 - 16 and idx[:, 1].max() <= 4096 - 16
+    assert np.isfinite(so).all() and np.isfinite(R).all() and (np.abs(so[:, 0]) <= 1.0).all() and (R >= 0).all()
+    for k in (0, 777, 131071, 200000, n - 1):
+        w = fic.bf_encode(img, mode=fic.BF_MODE_JIT, flags=fic.BF_EXACT_ONLY, range_begin=k, range_end=k + 1)
+        assert np.array_equal(w[0][0], idx[k]) and np.array_equal(w[1][0], so[k]) and w[2][0] == R[k]
+    b, e = 3 * n // 8, 4 * n // 8
+    part = fic.bf_encode(img, mode=fic.BF_MODE_JIT, range_begin=b, range_end=e)
+    assert np.array_equal(part[0], idx[b:e]) and np.array_equal(part[1], so[b:e]) and np.array_equal(part[2], R[b:e])
+
+
 def _stress_images():
     rng = np.random.default_rng(2024)
     yy, xx = np.mgrid[0:160, 0:192]
