@@ -20,6 +20,7 @@
 // ------------------------------------------------------------------------------------------------
 #define BFD_THREADS 1024
 #define BFD_RANGES_PER_STEP (BFD_THREADS / 32)
+#define BFD_SHADOW_PIXELS 102400   // 200 KB of int16 next to the CTA's static shared memory (256 x 256, 320 x 320, ...)
 
 // One transform in execution order; a step is BFD_RANGES_PER_STEP consecutive records (levels are padded with dst = -1).
 struct BfdRec {
@@ -31,53 +32,94 @@ struct BfdRec {
 // target block, so its reads are separated from its writes by a warp barrier; no other range of the same level touches
 // what it writes (RAW / WAR / WAW edges are all cross-level), so the CTA barrier is only needed between steps.  The
 // record of the next step is fetched while the current one is gathered.
+//
+// SHADOW: a step is one dependent round trip to the image (gather -> affine -> scatter), ~1.9 us through L2.  The gather
+// only ever uses the int32-truncated pixel (utils.py:22), so for images of up to BFD_SHADOW_PIXELS pixels the CTA keeps a
+// truncated int16 copy in shared memory and gathers from there; the float32 values are only needed from the last sweep
+// (every range is rewritten in every sweep) and go to global memory then.  A value outside int16 raises a flag and the
+// plane is decoded again from zeros through global memory, in the same launch.
+template <bool SHADOW>
+__device__ __forceinline__ void bfd_sweeps(const BfdRec* __restrict__ recs, int n_steps, int width, int iterations,
+                                           float* __restrict__ buf, int16_t* __restrict__ shadow, int* overflow)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    BfdRec cur = recs[warp];
+    for (int it = 0; it < iterations; ++it) {
+        const bool last = it + 1 == iterations;
+        for (int st = 0; st < n_steps; ++st) {
+            const int nx = st + 1 < n_steps ? st + 1 : 0;
+            const BfdRec nxt = recs[(size_t)nx * BFD_RANGES_PER_STEP + warp];
+            if (cur.dst >= 0) {
+                float val[2];
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int px = lane + 32 * half, a = px >> 3, b = px & 7;
+                    int acc = 0;
+                    if (it > 0) {  // sweep 1 reads the all-zero image
+                        // an isometry of the 16x16 block maps 2x2 cells onto 2x2 cells and the pool is an integer sum,
+                        // so the cell of output pixel (a, b) is located once, on the 8x8 grid of cells
+                        int ca, cb;
+                        fic_iso_bf(cur.iso >> 2, cur.iso & 3, 8, a, b, ca, cb);
+                        const size_t at = (size_t)(cur.di + 2 * ca) * width + cur.dj + 2 * cb;
+#pragma unroll
+                        for (int u = 0; u < 2; ++u)
+#pragma unroll
+                            for (int v = 0; v < 2; ++v) {
+                                const size_t q = at + (size_t)u * width + v;
+                                acc += SHADOW ? (int)shadow[q] : __float2int_rz(buf[q]);  // astype(int32), utils.py:22
+                            }
+                    }
+                    val[half] = __double2float_rn(DA(DM(DM((double)acc, 0.25), cur.s), cur.o));
+                }
+                __syncwarp();  // every read of this range happens before any of its writes
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int px = lane + 32 * half;
+                    const int at = cur.dst + (px >> 3) * width + (px & 7);
+                    if (!SHADOW || last) buf[at] = val[half];
+                    if (SHADOW) {
+                        if (!(fabsf(val[half]) < 32768.0f)) *overflow = 1;
+                        shadow[at] = (int16_t)__float2int_rz(val[half]);
+                    }
+                }
+            }
+            __syncthreads();
+            cur = nxt;
+        }
+    }
+}
+
+template <bool SHADOW>
 __global__ void __launch_bounds__(BFD_THREADS)
 bf_decode_kernel(const BfdRec* __restrict__ recs_all, const long long* __restrict__ step_off, int width, int height,
                  int iterations, float* __restrict__ buf_all, uint8_t* __restrict__ out_all)
 {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    extern __shared__ int16_t bfd_shadow[];
+    __shared__ int s_overflow;
+    const int tid = threadIdx.x;
     const BfdRec* recs = recs_all + step_off[blockIdx.x] * BFD_RANGES_PER_STEP;
     const int n_steps = (int)(step_off[blockIdx.x + 1] - step_off[blockIdx.x]);
-    float* buf = buf_all + (size_t)blockIdx.x * width * height;
-    uint8_t* out = out_all + (size_t)blockIdx.x * width * height;
+    const int npx = width * height;
+    float* buf = buf_all + (size_t)blockIdx.x * npx;
+    uint8_t* out = out_all + (size_t)blockIdx.x * npx;
     if (n_steps > 0) {
-        BfdRec cur = recs[warp];
-        for (int it = 0; it < iterations; ++it) {
-            for (int st = 0; st < n_steps; ++st) {
-                const int nx = st + 1 < n_steps ? st + 1 : 0;
-                const BfdRec nxt = recs[(size_t)nx * BFD_RANGES_PER_STEP + warp];
-                if (cur.dst >= 0) {
-                    float val[2];
-#pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        const int px = lane + 32 * half, a = px >> 3, b = px & 7;
-                        int acc = 0;
-                        if (it > 0) {  // sweep 1 reads the all-zero image
-#pragma unroll
-                            for (int u = 0; u < 2; ++u)
-#pragma unroll
-                                for (int v = 0; v < 2; ++v) {
-                                    int sa, sb;
-                                    fic_iso_bf(cur.iso >> 2, cur.iso & 3, 16, 2 * a + u, 2 * b + v, sa, sb);
-                                    acc += __float2int_rz(buf[(size_t)(cur.di + sa) * width + cur.dj + sb]);  // astype(int32), utils.py:22
-                                }
-                        }
-                        val[half] = __double2float_rn(DA(DM(DM((double)acc, 0.25), cur.s), cur.o));
-                    }
-                    __syncwarp();  // every read of this range happens before any of its writes
-#pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        const int px = lane + 32 * half;
-                        buf[cur.dst + (px >> 3) * width + (px & 7)] = val[half];
-                    }
-                }
+        if (SHADOW) {
+            for (int p = tid; p < npx; p += BFD_THREADS) bfd_shadow[p] = 0;
+            if (tid == 0) s_overflow = 0;
+            __syncthreads();
+            bfd_sweeps<true>(recs, n_steps, width, iterations, buf, bfd_shadow, &s_overflow);
+            __syncthreads();
+            if (s_overflow) {   // some pixel left the int16 range: decode this plane again through global memory
+                for (int p = tid; p < npx; p += BFD_THREADS) buf[p] = 0.0f;
                 __syncthreads();
-                cur = nxt;
+                bfd_sweeps<false>(recs, n_steps, width, iterations, buf, nullptr, nullptr);
             }
+        } else {
+            bfd_sweeps<false>(recs, n_steps, width, iterations, buf, nullptr, nullptr);
         }
     }
     __syncthreads();
-    for (int p = tid; p < width * height; p += BFD_THREADS) out[p] = (uint8_t)__float2int_rz(buf[p]);
+    for (int p = tid; p < npx; p += BFD_THREADS) out[p] = (uint8_t)__float2int_rz(buf[p]);
 }
 
 // h_idx [planes][n][4], h_so [planes][n][2] on the host; d_out [planes][height*width] on the device
@@ -143,7 +185,19 @@ int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double
     FIC_CUDA(cudaMemsetAsync(h->dec_img.p, 0, (size_t)planes * width * height * sizeof(float), st));
     const long long* d_off = h->dec_sched.as<long long>();
     const BfdRec* d_recs = reinterpret_cast<const BfdRec*>(h->dec_sched.as<char>() + rec_at);
-    bf_decode_kernel<<<planes, BFD_THREADS, 0, st>>>(d_recs, d_off, width, height, iterations, h->dec_img.as<float>(), d_out);
+    const size_t shadow_bytes = (size_t)width * height * sizeof(int16_t);
+    if ((size_t)width * height <= BFD_SHADOW_PIXELS) {
+        if (!h->dec_shadow_ready) {     // once per handle, i.e. per device
+            FIC_CUDA(cudaFuncSetAttribute(bf_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(BFD_SHADOW_PIXELS * sizeof(int16_t))));
+            h->dec_shadow_ready = true;
+        }
+        bf_decode_kernel<true><<<planes, BFD_THREADS, shadow_bytes, st>>>(d_recs, d_off, width, height, iterations,
+                                                                        h->dec_img.as<float>(), d_out);
+    } else {
+        bf_decode_kernel<false><<<planes, BFD_THREADS, 0, st>>>(d_recs, d_off, width, height, iterations,
+                                                               h->dec_img.as<float>(), d_out);
+    }
     FIC_CHECK_LAUNCH(h, "bf_decode_kernel");
     // pin_b is reused by the next call: make sure the upload has been consumed
     FIC_CUDA(cudaStreamSynchronize(st));

@@ -112,6 +112,7 @@ struct fic_handle {
     DevBuf bf_pool, bf_poolx, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list;
     // decoders
     DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red, dec_keys, dec_roots;
+    bool dec_shadow_ready = false;   // bf_decode_kernel<true> has its dynamic shared memory limit raised on this device
     // quadtree / hv
     DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part;
 };

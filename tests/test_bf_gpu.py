@@ -168,6 +168,30 @@ def test_decoder_against_oracle_unbounded_scale(fic, orc):
         assert np.array_equal(fic.bf_decode(idx, so, 64, 64, it), orc.bf_decode(idx, so, 64, 64, it))
 
 
+def test_decoder_values_beyond_int16_take_the_global_memory_path(fic, orc):
+    """Small images are decoded against an int16 copy of the truncated pixels in shared memory; transforms that push
+    pixels past +-32767 must fall back (inside the same launch) to the float image in global memory and still agree with
+    the oracle.  One plane of the batch overflows, its neighbours do not."""
+    rng = np.random.default_rng(5)
+    n = 64
+    idx = np.stack([np.c_[rng.integers(0, 49, (n, 2)), rng.integers(0, 2, n), rng.integers(0, 4, n)] for _ in range(3)]).astype(np.int32)
+    so = np.zeros((3, n, 2))
+    so[0] = (0.6, 40.0)
+    so[1] = (2.0, 10.0)            # doubles every sweep: ~2.6e5 after ten sweeps
+    so[2] = (-0.9, 200.0)
+    for it in (1, 5, 9, 12):
+        got = fic.bf_decode_batch(idx, so, 64, 64, it)
+        for k in range(3):
+            assert np.array_equal(got[k], orc.bf_decode(idx[k], so[k], 64, 64, it)), (it, k)
+    # the image just above the shared-memory limit (328 x 328 > 102 400 pixels) runs the global-memory kernel from the start
+    img = synthetic_image(6, 328, 328)
+    e = fic.bf_encode(img, mode=1)
+    assert np.array_equal(fic.bf_decode(e[0], e[1], 328, 328, 6), orc.bf_decode(e[0], e[1], 328, 328, 6))
+    img = synthetic_image(7, 320, 320)
+    e = fic.bf_encode(img, mode=1)
+    assert np.array_equal(fic.bf_decode(e[0], e[1], 320, 320, 6), orc.bf_decode(e[0], e[1], 320, 320, 6))
+
+
 def test_encode_decode_round_trip_psnr(fic, images, golden):
     """PSNR of GPU encode -> GPU decode equals the reference's 29.967 dB on lena 256."""
     img = images["lena256"]
