@@ -45,6 +45,7 @@ emit(config=1, what="bruteforce-jit 256x256 encode+decode (host buffers)", encod
      psnr_db=psnr(dec, img), matches_per_s=1024 * 240 * 240 * 8 / t_enc, reference_cpu_s="415.5 (1 core, BASELINE.md)")
 
 # config 2: quadtree 512x512
+from quadtree.common import forest_to_leaves  # noqa: E402
 from quadtree.decoder import QuadtreeDecoder  # noqa: E402
 from quadtree.encoder import QuadtreeEncoder  # noqa: E402
 img = imgs["lena512"]
@@ -71,6 +72,15 @@ emit(config=2, what="quadtree 512x512 (7,5,1.0,False,False,4,8,2.0)", encode_ms_
      file_round_trip_equals_decode=bool(np.array_equal(qback, qdec)),
      oracle_cpu_ms=t_cpu * 1e3, decode_ms=t_qdec * 1e3, psnr_db=psnr(qdec, img), nodes=int(len(ref[0])),
      reference_cpu_s="3.74 (BASELINE.md)")
+
+# config 2 stress rows: full class search, and dense domain pools (step 1)
+for tag, params in (("full_class_search", (7, 5, 1.0, True, False, 4, 8, 2.0)),
+                    ("dense_pools_step1", (7, 5, 1.0, False, False, 4, 8, 2.0, 1, 1)),
+                    ("dense_pools_step1_full_class_search", (7, 5, 1.0, True, False, 4, 8, 2.0, 1, 1))):
+    t_s, qs = timed(lambda: QuadtreeEncoder(*params).encode(img), reps=2)
+    t_d, ds = timed(lambda: QuadtreeDecoder().decode(qs), reps=2)
+    emit(config="2-stress", what=f"quadtree 512x512 {tag} {params}", encode_ms=t_s * 1e3, decode_ms=t_d * 1e3,
+         psnr_db=psnr(ds, img), leaves=int(forest_to_leaves(qs)[0].shape[0]))
 
 # config 3: HV 512x512
 from hvv2.decoder import HVDecoder  # noqa: E402
