@@ -228,14 +228,20 @@ def run_ours(args):
     assert stream != 0
     d_img = torch.from_numpy(img).to(dev)
     d_idx = torch.zeros((N_RANGES, 4), dtype=torch.int32, device=dev)
-    # two record buffers: the gather of image k overlaps the encode of image k+1 (the images of a batch are independent)
-    d_so2 = [torch.zeros((N_RANGES, 2), dtype=torch.float64, device=dev) for _ in range(2)]
-    d_so = d_so2[0]
+    # The images of a batch are independent, so their winner records are exchanged in chunks of G images (SURVEY 8(e):
+    # "no collective except the final gather of records"): two chunk buffers, the all-gather of a full chunk overlaps the
+    # encodes that fill the other one.  A collective after EVERY image locks all ranks to the pace of the slowest GPU plus
+    # the launch jitter of eight processes (measured: 1.11 ms per image on every rank against 0.98-1.07 ms alone).
+    G = max(1, int(os.environ.get("FIC_BENCH_GATHER_EVERY", "16")))
+    d_so2 = [torch.zeros((G, N_RANGES, 2), dtype=torch.float64, device=dev) for _ in range(2)]
+    d_so = d_so2[0][0]
     d_R = torch.zeros((N_RANGES,), dtype=torch.float64, device=dev)
-    gathered = [[torch.zeros_like(d_so) for _ in range(world)] for _ in range(2)] if world > 1 else None
+    gathered = [[torch.zeros_like(d_so2[0]) for _ in range(world)] for _ in range(2)] if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     flags = fic_b200.BF_EXACT_ONLY if args.exact_only else 0
-    parity_k = [0]
+    cursor = [0, 0]               # chunk being filled, next free slot in it
+    last_slot = [0, 0]
+    last_gather = [0, 0]          # chunk and image count of the most recent all-gather
     # The gather is enqueued by a helper thread while the main thread is already inside the next encode call (ctypes
     # releases the GIL): the NCCL launch overhead of image k then overlaps the kernels of image k+1 as well.
     import queue
@@ -250,8 +256,8 @@ def run_ours(args):
                 item = gq.get()
                 if item is None:
                     return
-                k, ev, box = item
-                box.append(dist.all_gather(gathered[k], d_so2[k], async_op=True))
+                k, count, ev, box = item
+                box.append(dist.all_gather([g[:count] for g in gathered[k]], d_so2[k][:count], async_op=True))
                 ev.set()
 
     worker = None
@@ -266,20 +272,33 @@ def run_ours(args):
             box[0].wait()              # stream-level: the encode about to overwrite the buffer waits for its gather
             submitted[k] = None
 
-    def step():
-        k = parity_k[0]
-        parity_k[0] ^= 1
-        if world > 1:
-            wait_buffer(k)
-        fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, d_idx.data_ptr(), d_so2[k].data_ptr(), d_R.data_ptr(),
-                               flags=flags, stream=stream)
-        if world > 1:  # the only exchange of the path: winner records; the encode above has completed
+    def submit_gather(k, count):
+        if world > 1 and count > 0 and not os.environ.get("FIC_BENCH_NO_GATHER"):   # (the env switch is a diagnostic)
             ev, box = threading.Event(), []
             submitted[k] = (ev, box)
-            gq.put((k, ev, box))
+            last_gather[0], last_gather[1] = k, count
+            gq.put((k, count, ev, box))
+
+    def step():
+        k, slot = cursor
+        if world > 1 and slot == 0:
+            wait_buffer(k)        # the chunk about to be refilled has been gathered
+        fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, d_idx.data_ptr(), d_so2[k][slot].data_ptr(), d_R.data_ptr(),
+                               flags=flags, stream=stream)
+        last_slot[0], last_slot[1] = k, slot
+        if slot + 1 == G:         # the only exchange of the path: winner records
+            submit_gather(k, G)
+            cursor[0], cursor[1] = k ^ 1, 0
+        else:
+            cursor[1] = slot + 1
 
     def drain():
         if world > 1:
+            k, slot = cursor
+            if slot > 0:          # a partly filled chunk: gather what is there
+                wait_buffer(k)
+                submit_gather(k, slot)
+                cursor[0], cursor[1] = k ^ 1, 0
             wait_buffer(0)
             wait_buffer(1)
 
@@ -287,7 +306,11 @@ def run_ours(args):
         step()
     drain()
     torch.cuda.synchronize()
-    d_so = d_so2[parity_k[0] ^ 1]   # the records of the last warm-up image
+    d_so = d_so2[last_slot[0]][last_slot[1]]   # the records of the last warm-up image
+    if world > 1 and last_gather[1] and not os.environ.get("FIC_BENCH_NO_GATHER"):
+        k, count = last_gather    # the exchange delivered this rank's records unchanged, and every rank's are there
+        assert torch.equal(gathered[k][rank][:count], d_so2[k][:count]), "record gather corrupted this rank's records"
+        assert all(bool(g[:count].abs().sum() > 0) for g in gathered[k]), "record gather left a rank's records empty"
 
     # parity spot check against the reference's own records (tests/golden, rank 0 image only)
     parity = "skipped"
@@ -313,7 +336,7 @@ def run_ours(args):
         step()
         b.record()
     tail[0].record()
-    drain()               # the last image's gather is timed in full
+    drain()               # the gather of the last chunk is timed in full
     tail[1].record()
     barrier()
     clocks = sampler.stop()
@@ -386,6 +409,7 @@ def run_ours(args):
             "data": "bundled image lena_512x512 (grayscale), rolled by 8*rank rows per rank",
             "config": {"workload": "bruteforce-jit 512x512 r8/d16 stride1 8iso, one image per GPU",
                        "l2": "256 MiB buffer rewritten between timed steps", "path": "exact-only" if args.exact_only else "screen+exact",
+                       "exchange": f"winner records all-gathered over NCCL every {G} images, inside the timed region" if world > 1 else "none (one GPU)",
                        "parity": parity},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": H * W,
                     "d2h_bytes_per_step": N_RANGES * (16 + 16 + 8)},
