@@ -1323,6 +1323,13 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     h->prof_suppress = false;
 
     // 6. whatever the screen could not decide goes through the exact scan
+    if (h->eager.armed) {   // host-buffer call: the records ride in front of the synchronisation below
+        for (int k = 0; k < 3; ++k)
+            if (h->eager.bytes[k])
+                FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + h->eager.at[k], h->eager.src[k], h->eager.bytes[k],
+                                         cudaMemcpyDeviceToHost, st));
+        h->eager.done = true;
+    }
     int* hc = h->pin_a.as<int>();
     FIC_CUDA(cudaMemcpyAsync(hc, ctrl, 64, cudaMemcpyDeviceToHost, st));
     FIC_CUDA(cudaStreamSynchronize(st));
@@ -1335,6 +1342,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     h->counters[CNT_SCREEN_RANGES] += n_ranges - n_fb;
     h->counters[CNT_RESCAN_RANGES] += n_fb;
     if (n_fb > 0) {
+        h->eager.done = false;   // the exact scan below rewrites some records: the caller copies again
         if (flags & FIC_BF_NO_FALLBACK) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
         h->prof_suppress = true;
         int rc_fb = bf_exact_scan8(h, d_img, H, W, 1, 1, mode, range_begin, n_fb, fallback, d_idx, d_so, d_R, st);

@@ -94,6 +94,7 @@ int fic_destroy(fic_handle* h)
     for (DevBuf* b : bufs) b->release();
     h->pin_a.release();
     h->pin_b.release();
+    h->pin_out.release();
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
     cudaStreamDestroy(h->own_stream);
     delete h;
@@ -187,13 +188,31 @@ int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, in
         FIC_TRY(h->d_out_c.reserve((size_t)n * sizeof(double)));
         d_R = h->d_out_c.as<double>();
     }
-    FIC_TRY(bf_encode_impl(h, d_img, H, W, range, stride_i, stride_j, mode, range_begin, range_end, d_idx, d_so, d_R,
-                           flags, st));
+    const size_t b_idx = (size_t)n * 4 * sizeof(int32_t), b_so = (size_t)n * 2 * sizeof(double),
+                 b_R = out_R ? (size_t)n * sizeof(double) : 0;
     if (!dev) {
-        FIC_TRY(fic_copy_out(h, out_idx, d_idx, (size_t)n * 4 * sizeof(int32_t), false, st));
-        FIC_TRY(fic_copy_out(h, out_so, d_so, (size_t)n * 2 * sizeof(double), false, st));
-        if (out_R) FIC_TRY(fic_copy_out(h, out_R, d_R, (size_t)n * sizeof(double), false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(h->pin_out.reserve(b_idx + b_so + b_R));
+        h->eager.armed = true;
+        h->eager.done = false;
+        h->eager.src[0] = d_idx; h->eager.bytes[0] = b_idx; h->eager.at[0] = 0;
+        h->eager.src[1] = d_so;  h->eager.bytes[1] = b_so;  h->eager.at[1] = b_idx;
+        h->eager.src[2] = d_R;   h->eager.bytes[2] = b_R;   h->eager.at[2] = b_idx + b_so;
+    }
+    const int rc = bf_encode_impl(h, d_img, H, W, range, stride_i, stride_j, mode, range_begin, range_end, d_idx, d_so, d_R,
+                                  flags, st);
+    h->eager.armed = false;
+    FIC_TRY(rc);
+    if (!dev) {
+        if (!h->eager.done) {   // paths without the in-pipeline copy (exact scan, fallback ranges)
+            FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>(), d_idx, b_idx, cudaMemcpyDeviceToHost, st));
+            FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + b_idx, d_so, b_so, cudaMemcpyDeviceToHost, st));
+            if (b_R) FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + b_idx + b_so, d_R, b_R, cudaMemcpyDeviceToHost, st));
+            FIC_CUDA(cudaStreamSynchronize(st));
+        }
+        h->counters[CNT_D2H] += (int64_t)(b_idx + b_so + b_R);
+        memcpy(out_idx, h->pin_out.as<char>(), b_idx);
+        memcpy(out_so, h->pin_out.as<char>() + b_idx, b_so);
+        if (b_R) memcpy(out_R, h->pin_out.as<char>() + b_idx + b_so, b_R);
     }
     return FIC_OK;
 }

@@ -106,7 +106,15 @@ struct fic_handle {
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     // generic staging
     DevBuf d_img, d_out_a, d_out_b, d_out_c, d_in_a, d_in_b;
-    PinnedBuf pin_a, pin_b;
+    PinnedBuf pin_a, pin_b, pin_out;
+    // Host-buffer encodes: the records are copied to pinned memory by the pipeline itself, in front of the one host
+    // synchronisation it needs anyway (control-block read-back), instead of by the entry point after it.
+    struct EagerOut {
+        bool armed = false, done = false;
+        const void* src[3] = {nullptr, nullptr, nullptr};
+        size_t bytes[3] = {0, 0, 0};
+        size_t at[3] = {0, 0, 0};   // offsets into pin_out
+    } eager;
     // brute force
     DevBuf bf_boxsum, bf_stats, bf_partial, bf_ranges;
     DevBuf bf_pool, bf_poolx, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list;
