@@ -1332,7 +1332,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     }
     int* hc = h->pin_a.as<int>();
     FIC_CUDA(cudaMemcpyAsync(hc, ctrl, 64, cudaMemcpyDeviceToHost, st));
-    FIC_CUDA(cudaStreamSynchronize(st));
+    FIC_TRY(fic_sync(h, st));
     h->counters[CNT_D2H] += 64;
     if (hc[2] != 0) { fic_set_error("bf_screen_kernel: pipeline wait %d timed out", hc[2]); return FIC_ECUDA; }
     const int n_fb = hc[1];

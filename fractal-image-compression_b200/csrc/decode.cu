@@ -200,7 +200,7 @@ int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double
     }
     FIC_CHECK_LAUNCH(h, "bf_decode_kernel");
     // pin_b is reused by the next call: make sure the upload has been consumed
-    FIC_CUDA(cudaStreamSynchronize(st));
+    FIC_TRY(fic_sync(h, st));
     return FIC_OK;
 }
 
@@ -437,7 +437,7 @@ static int qt_deblock_run(fic_handle* h, const double* d_img, const int32_t* d_l
     FIC_TRY(h->dec_roots.reserve(roots.size() * sizeof(int32_t)));
     FIC_TRY(h->dec_keys.reserve(((size_t)n + 1) * sizeof(unsigned long long)));
     FIC_TRY(fic_copy_in(h, h->dec_roots.p, roots.data(), roots.size() * sizeof(int32_t), false, st));
-    FIC_CUDA(cudaStreamSynchronize(st));  // `roots` is pageable and goes out of scope
+    FIC_TRY(fic_sync(h, st));  // `roots` is pageable and goes out of scope
     if (n > 0) {
         qt_leaf_key_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_leaves, n, h->dec_roots.as<int32_t>(), n_roots,
                                                             h->dec_keys.as<unsigned long long>());
@@ -537,7 +537,7 @@ int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const dou
             FIC_CHECK_LAUNCH(h, "tree_reduce_kernel");
             double* hp = h->pin_b.as<double>();
             FIC_TRY(fic_copy_out(h, hp, red_out, 2 * sizeof(double), false, st));
-            FIC_CUDA(cudaStreamSynchronize(st));
+            FIC_TRY(fic_sync(h, st));
             if (sqrt(hp[0]) / sqrt(hp[1]) < stop) break;  // decoder.py:45-49
         }
     } else {

@@ -25,11 +25,32 @@ int fic_copy_in(fic_handle* h, void* dst_dev, const void* src, size_t bytes, boo
     return FIC_OK;
 }
 
+int fic_sync(fic_handle* h, cudaStream_t st)
+{
+    FIC_CUDA(cudaStreamSynchronize(st));
+    for (const fic_handle::PendingOut& po : h->pending_out) memcpy(po.dst, h->pin_stage.as<char>() + po.at, po.bytes);
+    h->pending_out.clear();
+    h->stage_used = 0;
+    return FIC_OK;
+}
+
 int fic_copy_out(fic_handle* h, void* dst, const void* src_dev, size_t bytes, bool dst_is_dev, cudaStream_t st)
 {
     if (bytes == 0) return FIC_OK;
-    FIC_CUDA(cudaMemcpyAsync(dst, src_dev, bytes, dst_is_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
-    if (!dst_is_dev) h->counters[CNT_D2H] += (int64_t)bytes;
+    if (dst_is_dev) {
+        FIC_CUDA(cudaMemcpyAsync(dst, src_dev, bytes, cudaMemcpyDeviceToDevice, st));
+        return FIC_OK;
+    }
+    const size_t at = (h->stage_used + 255) & ~(size_t)255;
+    if (at + bytes > h->pin_stage.cap) {
+        FIC_TRY(fic_sync(h, st));   // the staging area moves: deliver what is in it first
+        FIC_TRY(h->pin_stage.reserve(bytes + bytes / 2 + (1 << 20)));
+        return fic_copy_out(h, dst, src_dev, bytes, false, st);
+    }
+    FIC_CUDA(cudaMemcpyAsync(h->pin_stage.as<char>() + at, src_dev, bytes, cudaMemcpyDeviceToHost, st));
+    h->pending_out.push_back(fic_handle::PendingOut{dst, at, bytes});
+    h->stage_used = at + bytes;
+    h->counters[CNT_D2H] += (int64_t)bytes;
     return FIC_OK;
 }
 
@@ -95,6 +116,7 @@ int fic_destroy(fic_handle* h)
     h->pin_a.release();
     h->pin_b.release();
     h->pin_out.release();
+    h->pin_stage.release();
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
     cudaStreamDestroy(h->own_stream);
     delete h;
@@ -207,7 +229,7 @@ int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, in
             FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>(), d_idx, b_idx, cudaMemcpyDeviceToHost, st));
             FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + b_idx, d_so, b_so, cudaMemcpyDeviceToHost, st));
             if (b_R) FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + b_idx + b_so, d_R, b_R, cudaMemcpyDeviceToHost, st));
-            FIC_CUDA(cudaStreamSynchronize(st));
+            FIC_TRY(fic_sync(h, st));
         }
         h->counters[CNT_D2H] += (int64_t)(b_idx + b_so + b_R);
         memcpy(out_idx, h->pin_out.as<char>(), b_idx);
@@ -244,7 +266,7 @@ int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int ran
     FIC_TRY(bf_screen_run(h, d_img, H, W, FIC_BF_MODE_JIT, range_begin, n_ranges, nullptr, nullptr, nullptr, flags, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out_u, d_out, rows * 256 * sizeof(float), false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -284,7 +306,7 @@ static int bf_decode_common(const char* who, fic_handle* h, int planes, const in
         int32_t* pi = reinterpret_cast<int32_t*>(ps + n_all * 2);
         FIC_CUDA(cudaMemcpyAsync(pi, idx, n_all * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         FIC_CUDA(cudaMemcpyAsync(ps, so, n_all * 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
         h->counters[CNT_D2H] += (int64_t)(n_all * (4 * sizeof(int32_t) + 2 * sizeof(double)));
         h_idx = pi;
         h_so = ps;
@@ -306,7 +328,7 @@ static int bf_decode_common(const char* who, fic_handle* h, int planes, const in
     FIC_TRY(bf_decode_impl(h, planes, h_idx, h_so, n, width, height, iterations, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out, d_out, (size_t)planes * width * height, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -343,7 +365,7 @@ int fic_average_subsample(fic_handle* h, const double* arr, int h2, int w2, int 
     FIC_TRY(subsample_impl(h, d_arr, h2, w2, jit, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out, d_out, nout, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -385,7 +407,7 @@ int fic_qt_classify(fic_handle* h, const uint8_t* img, int H, int W, const int32
     FIC_TRY(qt_classify_impl(h, d_img, H, W, d_blocks, count, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out, d_out, nb, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -440,7 +462,7 @@ int fic_hv_search(fic_handle* h, const uint8_t* img, int H, int W, const int32_t
     if (!dev) {
         FIC_TRY(fic_copy_out(h, rec, d_rec, (size_t)count * 24, false, st));
         FIC_TRY(fic_copy_out(h, vals, d_vals, (size_t)count * 24, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -506,7 +528,7 @@ int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double
                              max_iterations, f32_affine, post, d_out, iters_done, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out, d_out, out_bytes, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -537,7 +559,7 @@ int fic_qt_deblock(fic_handle* h, const double* img, const int32_t* leaves, int 
     FIC_TRY(qt_deblock_impl(h, d_img, d_leaves, n, H, W, weights, max_depth_range_size, d_out, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, out, d_out, bytes, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -571,7 +593,7 @@ int fic_rgb_to_ycbcr(fic_handle* h, const uint8_t* rgb, int N, int M, int subsam
         FIC_TRY(fic_copy_out(h, y, d_y, npx, false, st));
         FIC_TRY(fic_copy_out(h, cb, d_cb, nc, false, st));
         FIC_TRY(fic_copy_out(h, cr, d_cr, nc, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }
@@ -605,7 +627,7 @@ int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const u
     FIC_TRY(ycbcr_to_rgb_impl(h, d_y, d_cb, d_cr, N, M, subsample, d_rgb, st));
     if (!dev) {
         FIC_TRY(fic_copy_out(h, rgb, d_rgb, 3 * npx, false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
     return FIC_OK;
 }

@@ -106,7 +106,12 @@ struct fic_handle {
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     // generic staging
     DevBuf d_img, d_out_a, d_out_b, d_out_c, d_in_a, d_in_b;
-    PinnedBuf pin_a, pin_b, pin_out;
+    PinnedBuf pin_a, pin_b, pin_out, pin_stage;
+    // Device -> host results are staged in pinned memory (a copy into pageable memory is a blocking, driver-staged transfer)
+    // and handed to the caller's buffers at the next fic_sync() of the stream.
+    struct PendingOut { void* dst; size_t at, bytes; };
+    std::vector<PendingOut> pending_out;
+    size_t stage_used = 0;
     // Host-buffer encodes: the records are copied to pinned memory by the pipeline itself, in front of the one host
     // synchronisation it needs anyway (control-block read-back), instead of by the entry point after it.
     struct EagerOut {
@@ -130,6 +135,8 @@ static inline cudaStream_t fic_stream(fic_handle* h, void* s) { return s ? (cuda
 // copy helpers that account traffic; `dev` selects device-to-device when the caller passed device pointers
 int fic_copy_in(fic_handle* h, void* dst_dev, const void* src, size_t bytes, bool src_is_dev, cudaStream_t st);
 int fic_copy_out(fic_handle* h, void* dst, const void* src_dev, size_t bytes, bool dst_is_dev, cudaStream_t st);
+// cudaStreamSynchronize + delivery of the staged results of fic_copy_out; every host wait of the library goes through it
+int fic_sync(fic_handle* h, cudaStream_t st);
 
 #define FIC_LAUNCHED(h) ((h)->counters[CNT_LAUNCHES]++)
 

@@ -604,7 +604,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             classify_grid_kernel<<<(unsigned)((cnt + 127) / 128), 128, 0, st>>>(I1, I2, W + 1, side, nv, nh, vs, hs, h->t_cls.as<int32_t>());
             FIC_CHECK_LAUNCH(h, "classify_grid_kernel");
             FIC_TRY(fic_copy_out(h, cls.data(), h->t_cls.p, cnt * 3 * sizeof(int32_t), false, st));
-            FIC_CUDA(cudaStreamSynchronize(st));
+            FIC_TRY(fic_sync(h, st));
         }
         std::vector<int32_t>& off = pool_off[k];
         off.assign(73, 0);
@@ -634,7 +634,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
         }
         FIC_CUDA(cudaMemcpyAsync(h->t_lists.p, flat.data(), flat.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
         h->counters[CNT_H2D] += (int64_t)(flat.size() * sizeof(int32_t));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
     }
 
     // ---- level-synchronous partition (encoder.py:127-146) ----
@@ -683,7 +683,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             std::vector<double> vals((size_t)n * 3);
             FIC_TRY(fic_copy_out(h, rec.data(), h->t_res.p, rec.size() * sizeof(int32_t), false, st));
             FIC_TRY(fic_copy_out(h, vals.data(), h->t_aux.p, vals.size() * sizeof(double), false, st));
-            FIC_CUDA(cudaStreamSynchronize(st));  // also keeps `rng` alive until the upload is consumed
+            FIC_TRY(fic_sync(h, st));  // also keeps `rng` alive until the upload is consumed
             for (int q = 0; q < n; ++q) {
                 QtNode& nd = nodes[cur[q]];
                 const double rms = sqrt(vals[3 * q + 2]);  // NaN for a negative error -> comparison false -> leaf
@@ -794,7 +794,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
         std::vector<double> vals((size_t)ns * 3 + (size_t)np * 2);
         FIC_TRY(fic_copy_out(h, rec.data(), d_rec, rec.size() * sizeof(int32_t), false, st));
         FIC_TRY(fic_copy_out(h, vals.data(), d_vals, vals.size() * sizeof(double), false, st));
-        FIC_CUDA(cudaStreamSynchronize(st));
+        FIC_TRY(fic_sync(h, st));
         std::vector<char> is_leaf(nodes.size(), 0);
         for (int q = 0; q < ns; ++q) {
             HvNode& nd = nodes[search[q]];
