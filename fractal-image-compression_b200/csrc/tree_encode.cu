@@ -348,7 +348,9 @@ hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
 {
     extern __shared__ float s_range[];   // the rectangle's pixels (when they fit)
     __shared__ float s_rs, s_sqr;
+    __shared__ unsigned long long s_bound;   // bit pattern of the best score found so far by this CTA (+inf at start)
     const int tid = threadIdx.x;
+    if (tid == 0) s_bound = 0x7ff0000000000000ull;
     const int ri = rects[4 * blockIdx.x], rj = rects[4 * blockIdx.x + 1], w = rects[4 * blockIdx.x + 2],
               hgt = rects[4 * blockIdx.x + 3];
     const int nn = w * hgt;
@@ -368,6 +370,8 @@ hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
     }
     __syncthreads();
     const float rs = s_rs, sqr = s_sqr;
+    const double dn = (double)nn;
+    const double slack_a = DS((double)sqr, DD(DM((double)rs, (double)rs), dn));   // sqr - rs^2 / n
     const int ndi = H - 2 * hgt > 0 ? (H - 2 * hgt + hgt - 1) / hgt : 0;  // range(0, H-2h, h): exclusive
     const int ndj = W - 2 * w > 0 ? (W - 2 * w + w - 1) / w : 0;
     const long long npos = (long long)ndi * ndj;
@@ -402,13 +406,29 @@ hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
             }
         }
         const float dsv[4] = {ds0, ds1, ds2, ds3}, sqv[4] = {sq0, sq1, sq2, sq3}, abv[4] = {ab0, ab1, ab2, ab3};
+        // Lower bound before the expensive quantising scorer.  The score is the quadratic form
+        //   R(s, o) = (sqr + s^2 sds - 2 s ab + 2 s o ds + n o^2 - 2 o rs) / n
+        // of the five sums evaluated at the QUANTISED (s, o); for n sds - ds^2 > 0 its minimum over all real (s, o) is
+        //   (sqr - rs^2/n - num^2 / (n den)) / n,   num = n ab - rs ds,  den = n sds - ds^2,
+        // so a candidate with  num^2 < (sqr - rs^2/n - n B) n den  cannot score below B, the best score any thread of
+        // the CTA has found so far.  The 1e-9 relative slack is six orders above the rounding of either side.
+        const double bound = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound);
+        const double room = DS(slack_a, DM(dn, bound));   // sqr - rs^2/n - n B
 #pragma unroll
         for (int iso = 0; iso < 4; ++iso) {
             const unsigned long long c = (unsigned long long)pos * 4ull + (unsigned)iso;
+            if (room > 0.0) {
+                const double dsd = (double)dsv[iso];
+                const double den = DS(DM(dn, (double)sqv[iso]), DM(dsd, dsd));
+                const double num = DS(DM(dn, (double)abv[iso]), DM((double)rs, dsd));
+                if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
+            }
             QScore sc = fic_q_score(nn, rs, sqr, dsv[iso], sqv[iso], abv[iso], max_scale, scale_bits, offset_bits);
             if (fic_better(sc.R, c, best.R, best.seq)) {
                 best.R = sc.R; best.seq = c; best.s = sc.s; best.o = sc.o; best.qs = sc.qs; best.qo = sc.qo;
                 best.di = di; best.dj = dj; best.orient = iso >> 1; best.rot = (iso & 1) * 2;
+                // publish as a bound for the whole CTA (bit pattern order = numeric order for non-negative doubles)
+                atomicMin(&s_bound, (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
             }
         }
     }
