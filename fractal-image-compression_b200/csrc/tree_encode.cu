@@ -258,10 +258,12 @@ qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __rest
     __shared__ int seg_list[2 * 72];       // class index of the segment
     __shared__ int seg_rot[2], seg_orient[2];
     __shared__ int n_seg;
+    __shared__ unsigned long long s_bound;   // bit pattern of the best score found so far by this CTA (+inf at start)
     const int tid = threadIdx.x;
     const int si = ranges[2 * blockIdx.x], sj = ranges[2 * blockIdx.x + 1];
     const int nn = side * side;
     if (tid == 0) {
+        s_bound = 0x7ff0000000000000ull;
         float rs = 0.f, sq = 0.f;
         for (int t = 0; t < nn; ++t) rs = __fadd_rn(rs, (float)img[(size_t)(si + t / side) * W + sj + t % side]);
         for (int t = 0; t < nn; ++t) {
@@ -289,6 +291,8 @@ qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __rest
     }
     __syncthreads();
     const float rs = s_rs, sqr = s_sqr;
+    const double dn = (double)nn;
+    const double slack_a = DS((double)sqr, DD(DM((double)rs, (double)rs), dn));   // sqr - rs^2 / n
     const int total = seg_begin[n_seg];
     TeBest best;
     te_init(best);
@@ -317,10 +321,21 @@ qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __rest
                 sds = __fadd_rn(sds, __fmul_rn(d, d));
                 ab = __fadd_rn(ab, __fmul_rn(d, r));
             }
+        {   // exact lower bound of the score (minimum of its quadratic form, see hv_search_kernel) against the CTA's best
+            const double bound = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound);
+            const double room = DS(slack_a, DM(dn, bound));
+            if (room > 0.0) {
+                const double dsd = (double)ds;
+                const double den = DS(DM(dn, (double)sds), DM(dsd, dsd));
+                const double num = DS(DM(dn, (double)ab), DM((double)rs, dsd));
+                if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
+            }
+        }
         QScore sc = fic_q_score(nn, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
         if (fic_better(sc.R, (unsigned long long)c, best.R, best.seq)) {
             best.R = sc.R; best.seq = c; best.s = sc.s; best.o = sc.o; best.qs = sc.qs; best.qo = sc.qo;
             best.di = di; best.dj = dj; best.orient = d_orient; best.rot = d_rot;
+            atomicMin(&s_bound, (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
         }
     }
     te_block_reduce(best, rec + 6 * (size_t)blockIdx.x, vals + 3 * (size_t)blockIdx.x);
