@@ -46,6 +46,14 @@ class EntropyProcessor(ABC):
     def encode(self, value: int, dimension: CodingDimension) -> tuple[Code, CodeWidth]:
         ...
 
+    def encode_column(self, values, dimension: CodingDimension):
+        """(code words uint64, widths int64) for a numpy column of one dimension's symbols; processors with per-dimension
+        encoders override this with the encoder's own column method."""
+        import numpy as np
+        uniq, inverse = np.unique(np.asarray(values), return_inverse=True)
+        pairs = [self.encode(int(v), dimension) for v in uniq]
+        return (np.array([p[0] for p in pairs], np.uint64)[inverse], np.array([p[1] for p in pairs], np.int64)[inverse])
+
     @abstractmethod
     def prepare_for_decoding(self, dimension_default_bit_widths: list[int]):
         ...
@@ -97,6 +105,9 @@ class HuffmanEntropyProcessor(EntropyProcessor):
 
     def encode(self, value, dimension):
         return self.dimension_encoders[dimension.value].encode(value)
+
+    def encode_column(self, values, dimension):
+        return self.dimension_encoders[dimension.value].encode_column(values)
 
     def prepare_for_decoding(self, dimension_default_bit_widths):
         self.dimension_default_bit_widths = dimension_default_bit_widths

@@ -95,12 +95,8 @@ class HVSerializer:
         self.entropy_coding_dimensions = {dim for dim, gain in gains.items() if gain >= self.required_entropy_coding_gain}
 
     def _coded(self, column: np.ndarray, dim: CodingDimension):
-        """(code, width) of every value of a column through the entropy processor, one call per distinct value."""
-        uniq, inverse = np.unique(column, return_inverse=True)
-        pairs = [self.entropy_processor.encode(int(v), dim) for v in uniq]
-        codes = np.array([p[0] for p in pairs], np.uint64)[inverse]
-        widths = np.array([p[1] for p in pairs], np.int64)[inverse]
-        return codes, widths
+        """(code, width) of every value of a column through the entropy processor."""
+        return self.entropy_processor.encode_column(column, dim)
 
     def _write_nodes(self, bits: BitBuffer):
         # leaf = 1, row, col, orientation (1), rotation // 2 (1), scale, offset; split = 0, vertical (1), index (16)
