@@ -64,6 +64,16 @@ def ordered_counts(symbols) -> list[tuple[int, int]]:
     """(symbol, frequency) in order of first occurrence -- what `Counter(symbols).items()` yields -- for a list or, without
     a Python-level pass over the elements, for a numpy array."""
     if isinstance(symbols, np.ndarray):
+        n = symbols.size
+        if n and symbols.dtype.kind in "iu" and int(symbols.min()) >= 0 and int(symbols.max()) < (1 << 20):
+            # small non-negative symbols: histogram + first position by a reversed scatter (the last write wins), no sort
+            # over the elements
+            counts = np.bincount(symbols)
+            first = np.full(counts.size, n, np.int64)
+            first[symbols[::-1]] = np.arange(n - 1, -1, -1, dtype=np.int64)
+            present = np.flatnonzero(counts)
+            order = present[np.argsort(first[present], kind="stable")]
+            return list(zip(order.tolist(), counts[order].tolist()))
         uniq, first, counts = np.unique(symbols, return_index=True, return_counts=True)
         order = np.argsort(first, kind="stable")
         return list(zip(uniq[order].tolist(), counts[order].tolist()))
@@ -88,6 +98,21 @@ class HuffmanEncoder(EntropyEncoder):
 
     def encode(self, symbol: int) -> tuple[Code, CodeWidth]:
         return self.coding_table[symbol]
+
+    def encode_column(self, values: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+        """Table lookup for a whole column (symbols are small non-negative integers: field values of a few bits)."""
+        v = np.asarray(values)
+        top = max(self.coding_table) if self.coding_table else -1
+        if v.size == 0 or v.dtype.kind not in "iu" or top >= (1 << 20) or int(v.min()) < 0 or int(v.max()) > top:
+            return super().encode_column(v)
+        codes = np.zeros(top + 1, np.uint64)
+        widths = np.full(top + 1, -1, np.int64)
+        for sym, (code, width) in self.coding_table.items():
+            codes[sym], widths[sym] = code, width
+        w = widths[v]
+        if (w < 0).any():
+            raise KeyError(int(v[w < 0][0]))      # a symbol the tree was not built for, as `encode` would raise
+        return codes[v], w
 
     def _build_coding_table(self, root: HuffmanNode) -> CodingTable:
         table: CodingTable = {}

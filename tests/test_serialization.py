@@ -273,6 +273,30 @@ def test_rgb_stream_is_three_fqt_streams(golden, images):
         assert again.getvalue() == ref.getvalue()
 
 
+def test_symbol_statistics_and_column_encoding_equal_the_scalar_forms():
+    """`ordered_counts` on arrays = `Counter(list).items()` (first-occurrence order decides the Huffman tree shape), and
+    `encode_column` = one `encode` per element, for the Huffman and the identity encoder."""
+    from collections import Counter
+    from entropy.abccodec import IdentityEncoder
+    from entropy.huffman import HuffmanEncoder, ordered_counts
+    rng = np.random.default_rng(11)
+    for hi, n in ((2, 50), (37, 5000), (512, 20000), (1, 9)):
+        v = rng.integers(0, hi, n)
+        assert ordered_counts(v) == list(Counter(v.tolist()).items())
+        assert ordered_counts(v.astype(np.int64) - 3) == list(Counter((v - 3).tolist()).items())   # negative symbols: generic path
+        enc = HuffmanEncoder()
+        enc.prepare_for_encoding(v)
+        codes, widths = enc.encode_column(v)
+        want = [enc.encode(int(x)) for x in v]
+        assert codes.tolist() == [c for c, _ in want] and widths.tolist() == [w for _, w in want]
+        codes, widths = IdentityEncoder(9).encode_column(v)
+        assert codes.tolist() == v.tolist() and set(widths.tolist()) == {9}
+    enc = HuffmanEncoder()
+    enc.prepare_for_encoding(np.array([1, 2, 2, 5]))
+    with pytest.raises(KeyError):
+        enc.encode_column(np.array([1, 3]))
+
+
 def test_bitbuffer_write_many_equals_single_writes():
     """The vectorised field writer the serialisers use leaves the same bytes and the same pending state as one
     `write` per field, whatever is already pending (widths 0..32, values wider than their field are masked)."""
