@@ -41,7 +41,12 @@ def emit(**kw):
 img = imgs["lena256"]
 t_enc, (idx, so, R) = timed(lambda: fic_b200.bf_encode(img, mode=1))
 t_dec, dec = timed(lambda: fic_b200.bf_decode(idx, so, 256, 256, 32))
+from bruteforce.decoder import Decoder  # noqa: E402
+from bruteforce.jit_bfencoder import JitedBruteForceEncoder  # noqa: E402
+t_cls_enc, (enc_obj, errs) = timed(lambda: JitedBruteForceEncoder(img, 8, 16).encode())
+t_cls_dec, dec_cls = timed(lambda: Decoder().decode(enc_obj, 32))
 emit(config=1, what="bruteforce-jit 256x256 encode+decode (host buffers)", encode_ms=t_enc * 1e3, decode_ms=t_dec * 1e3,
+     class_api_encode_ms=t_cls_enc * 1e3, class_api_decode_ms=t_cls_dec * 1e3, class_api_equals_c_abi=bool(np.array_equal(dec_cls, dec)),
      psnr_db=psnr(dec, img), matches_per_s=1024 * 240 * 240 * 8 / t_enc, reference_cpu_s="415.5 (1 core, BASELINE.md)")
 
 # config 2: quadtree 512x512

@@ -273,6 +273,27 @@ def test_rgb_stream_is_three_fqt_streams(golden, images):
         assert again.getvalue() == ref.getvalue()
 
 
+def test_bruteforce_encoded_image_builds_domains_on_demand():
+    from bruteforce.model import Domain, EncodedImage
+    rng = np.random.default_rng(3)
+    idx = rng.integers(0, 40, (16, 4)).astype(np.int32)
+    so = rng.normal(size=(16, 2))
+    enc = EncodedImage.from_arrays(32, 32, 8, idx, so)
+    assert len(enc) == 16
+    a, b = enc.to_arrays()
+    assert np.array_equal(a, idx) and np.array_equal(b, so) and enc._domains is None     # no objects were needed
+    doms = enc.domains
+    assert enc._arrays is None and len(doms) == 16 and isinstance(doms[3], Domain)
+    assert (doms[3].start_i, doms[3].rotation, doms[3].o) == (int(idx[3, 0]), int(idx[3, 3]), float(so[3, 1]))
+    doms[0].s = 0.25                                                                        # edits are seen by to_arrays
+    assert enc.to_arrays()[1][0, 0] == 0.25
+    fresh = EncodedImage(32, 32, 8)
+    fresh.domains.append(Domain(1, 2, 0, 3, 0.5, 7.0))                                      # the reference's own usage
+    assert fresh.to_arrays()[0].tolist() == [[1, 2, 0, 3]] and len(fresh) == 1
+    fresh.domains = []
+    assert fresh.to_arrays()[0].shape == (0, 4)
+
+
 def test_symbol_statistics_and_column_encoding_equal_the_scalar_forms():
     """`ordered_counts` on arrays = `Counter(list).items()` (first-occurrence order decides the Huffman tree shape), and
     `encode_column` = one `encode` per element, for the Huffman and the identity encoder."""
