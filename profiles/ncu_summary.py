@@ -13,11 +13,12 @@ def launches(src, dst):
     rows = [r for r in csv.reader(open(src)) if len(r) > 5]
     h = rows[0]
     ki, vi, ui = h.index("Kernel Name"), h.index("Metric Value"), h.index("Metric Unit")
-    with open(dst, "w") as f:
-        f.write("id,kernel,gpu__time_duration.sum,unit\n")
+    with open(dst, "w", newline="") as f:
+        w = csv.writer(f)   # kernel names of library kernels contain commas (template arguments)
+        w.writerow(["id", "kernel", "gpu__time_duration.sum", "unit"])
         for n, r in enumerate(rows[1:]):
             name = r[ki].split("(")[0].replace("void ", "").replace("<unnamed>::", "")
-            f.write(f"{n},{name},{r[vi].replace(',', '')},{r[ui]}\n")
+            w.writerow([n, name, r[vi].replace(",", ""), r[ui]])
 
 
 def screen(src, dst):
