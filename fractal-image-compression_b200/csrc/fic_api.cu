@@ -41,6 +41,11 @@ int fic_copy_out(fic_handle* h, void* dst, const void* src_dev, size_t bytes, bo
         FIC_CUDA(cudaMemcpyAsync(dst, src_dev, bytes, cudaMemcpyDeviceToDevice, st));
         return FIC_OK;
     }
+    if (bytes > ((size_t)128 << 20)) {   // not worth holding that much pinned memory: let the driver stage it
+        FIC_CUDA(cudaMemcpyAsync(dst, src_dev, bytes, cudaMemcpyDeviceToHost, st));
+        h->counters[CNT_D2H] += (int64_t)bytes;
+        return FIC_OK;
+    }
     const size_t at = (h->stage_used + 255) & ~(size_t)255;
     if (at + bytes > h->pin_stage.cap) {
         FIC_TRY(fic_sync(h, st));   // the staging area moves: deliver what is in it first
