@@ -192,6 +192,28 @@ def test_decoder_values_beyond_int16_take_the_global_memory_path(fic, orc):
     assert np.array_equal(fic.bf_decode(e[0], e[1], 320, 320, 6), orc.bf_decode(e[0], e[1], 320, 320, 6))
 
 
+@pytest.mark.parametrize("shape", [(512, 512), (328, 328), (1024, 1024), (776, 776)])
+def test_decoder_large_images_match_oracle(fic, orc, shape):
+    """Images above the shared-memory limit of 102 400 pixels (global-memory path): random contractive records, records
+    of a real encode, and non-contractive records next to contractive ones in one batch, against the oracle."""
+    H, W = shape
+    img = synthetic_image(9, H, W)
+    n = (H // 8) * (W // 8)
+    rng = np.random.default_rng(H)
+    idx = np.c_[rng.integers(0, H - 15, n), rng.integers(0, W - 15, n), rng.integers(0, 2, n), rng.integers(0, 4, n)].astype(np.int32)
+    so = np.c_[rng.uniform(-0.9, 0.9, n), rng.uniform(0, 255, n)]
+    for it in (1, 2, 5):
+        assert np.array_equal(fic.bf_decode(idx, so, W, H, it), orc.bf_decode(idx, so, W, H, it)), it
+    if H <= 512:
+        e = fic.bf_encode(img, mode=1)
+        assert np.array_equal(fic.bf_decode(e[0], e[1], W, H, 8), orc.bf_decode(e[0], e[1], W, H, 8))
+    so2 = so.copy()
+    so2[:, 0] = 2.0
+    both = fic.bf_decode_batch(np.stack([idx, idx]), np.stack([so, so2]), W, H, 11)
+    assert np.array_equal(both[0], orc.bf_decode(idx, so, W, H, 11))
+    assert np.array_equal(both[1], orc.bf_decode(idx, so2, W, H, 11))
+
+
 def test_encode_decode_round_trip_psnr(fic, images, golden):
     """PSNR of GPU encode -> GPU decode equals the reference's 29.967 dB on lena 256."""
     img = images["lena256"]
