@@ -273,6 +273,116 @@ def test_rgb_stream_is_three_fqt_streams(golden, images):
         assert again.getvalue() == ref.getvalue()
 
 
+def _random_quadtree_stream(rng, width, height, min_side=2, p_split=0.6):
+    """A random forest over a (possibly ragged) image as the preorder stream of fic_qt_encode."""
+    from quadtree.common import iter_root_squares
+    nodes = []
+
+    def grow(e):
+        side = 1 << e
+        if side > min_side and rng.random() < p_split:
+            nodes.append([0, 0, 0, 0, 0, 0, 0, e])
+            for _ in range(4):
+                grow(e - 1)
+        else:
+            nodes.append([1, int(rng.integers(0, max(1, height - 2 * side + 1))), int(rng.integers(0, max(1, width - 2 * side + 1))),
+                          int(rng.integers(0, 2)), int(rng.integers(0, 4)), int(rng.integers(0, 128)), int(rng.integers(0, 32)), e])
+
+    roots = list(iter_root_squares(width, height))
+    for _, _, e in roots:
+        grow(e)
+    nodes = np.array(nodes, np.int32)
+    vals = np.c_[rng.normal(size=(len(nodes), 2)), np.zeros(len(nodes))]
+    vals[nodes[:, 0] == 0] = 0.0
+    return nodes, vals, len(roots)
+
+
+@pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96)), (4, (128, 40)), (5, (17, 23)), (6, (256, 256))])
+def test_random_forests_flat_paths_equal_object_paths_and_round_trip(seed, shape):
+    """Random quadtree forests (ragged images, uneven depths): array-based flattening, file writer and native reader
+    against the object walks, and writer -> reader -> writer reproduces the bytes."""
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from quadtree.common import EncodingInfo, QuadtreeImage, forest_to_leaves, stream_to_forest
+    from quadtree.serialization import QuadtreeDeserializer, QuadtreeSerializer
+    rng = np.random.default_rng(seed)
+    H, W = shape
+    nodes, vals, n_roots = _random_quadtree_stream(rng, W, H)
+    info = EncodingInfo(7, 5, 1.0, W, H)
+    objects = QuadtreeImage(info, stream_to_forest(nodes, vals, n_roots))
+    for quantised in (True, False):
+        a = forest_to_leaves(QuadtreeImage(info, stream=(nodes, vals, n_roots)), quantised)
+        b = forest_to_leaves(objects, quantised)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    leaves = forest_to_leaves(objects)[0]
+    cover = np.zeros((H, W), np.int32)
+    for ri, rj, hh, ww in leaves[:, :4]:
+        cover[ri:ri + hh, rj:rj + ww] += 1
+    assert (cover == 1).all()                                   # the leaves tile the image exactly
+    for dims in (set(CodingDimension), {CodingDimension.DOMAIN_ROW, CodingDimension.OFFSET}, set()):
+        fast, slow = io.BytesIO(), io.BytesIO()
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(QuadtreeImage(info, stream=(nodes, vals, n_roots)), fast)
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(objects, slow)
+        assert fast.getvalue() == slow.getvalue()
+        back = QuadtreeDeserializer().deserialize(io.BytesIO(fast.getvalue()))
+        got = back.flat_stream()
+        assert got is not None and np.array_equal(got[0], nodes) and got[2] == n_roots
+        again = io.BytesIO()
+        QuadtreeSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(back, again)
+        assert again.getvalue() == fast.getvalue()
+
+
+def _random_hv_stream(rng, width, height, min_side=2, p_split=0.7):
+    nodes = []
+
+    def grow(w, h):
+        can_v, can_h = w >= 2 * min_side, h >= 2 * min_side
+        if (can_v or can_h) and rng.random() < p_split:
+            vertical = can_v and (not can_h or rng.random() < 0.5)
+            size = w if vertical else h
+            s = int(rng.integers(min_side - 1, size - min_side))   # first child keeps s + 1 columns / rows
+            nodes.append([0, int(vertical), s, 0, 0, 0, 0, 0])
+            if vertical:
+                grow(s + 1, h); grow(w - s - 1, h)
+            else:
+                grow(w, s + 1); grow(w, h - s - 1)
+        else:
+            nodes.append([1, int(rng.integers(0, max(1, height - 2 * h + 1))), int(rng.integers(0, max(1, width - 2 * w + 1))),
+                          int(rng.integers(0, 2)), 2 * int(rng.integers(0, 2)), int(rng.integers(0, 32)), int(rng.integers(0, 128)), 0])
+
+    grow(width, height)
+    nodes = np.array(nodes, np.int32)
+    vals = np.c_[rng.normal(size=(len(nodes), 2)), np.zeros(len(nodes))]
+    return nodes, vals
+
+
+@pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96)), (4, (200, 120))])
+def test_random_hv_trees_flat_paths_equal_object_paths_and_round_trip(seed, shape):
+    from entropy.processor import CodingDimension, HuffmanEntropyProcessor
+    from hvv2.common import HVImage, stream_to_tree, tree_to_leaves
+    from hvv2.serialization import HVDeserializer, HVSerializer
+    from quadtree.common import EncodingInfo
+    rng = np.random.default_rng(seed)
+    H, W = shape
+    nodes, vals = _random_hv_stream(rng, W, H)
+    info = EncodingInfo(5, 7, 1.0, W, H)
+    objects = HVImage(info, stream_to_tree(nodes, vals))
+    for quantised in (True, False):
+        a = tree_to_leaves(HVImage(info, stream=(nodes, vals)), quantised)
+        b = tree_to_leaves(objects, quantised)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    cover = np.zeros((H, W), np.int32)
+    for ri, rj, hh, ww in tree_to_leaves(objects)[0][:, :4]:
+        cover[ri:ri + hh, rj:rj + ww] += 1
+    assert (cover == 1).all()
+    for dims in (set(CodingDimension), set()):
+        fast, slow = io.BytesIO(), io.BytesIO()
+        HVSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(HVImage(info, stream=(nodes, vals)), fast)
+        HVSerializer(HuffmanEntropyProcessor(), set(dims)).serialize(objects, slow)
+        assert fast.getvalue() == slow.getvalue()
+        back = HVDeserializer().deserialize(io.BytesIO(fast.getvalue()))
+        assert np.array_equal(back.flat_stream()[0][:, :7], nodes[:, :7])
+
+
 def test_bruteforce_encoded_image_builds_domains_on_demand():
     from bruteforce.model import Domain, EncodedImage
     rng = np.random.default_rng(3)
