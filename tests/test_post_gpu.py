@@ -60,6 +60,34 @@ def test_deblocking_custom_weights_and_user_postprocessor(fic, orc, golden, imag
     assert np.array_equal(QuadtreeDecoder().decode(q, Invert()), (255.0 - flt).clip(0., 255.).astype(np.uint8))
 
 
+@pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96)), (4, (128, 40)), (5, (17, 23)), (6, (250, 131))])
+def test_deblocking_and_decode_on_random_forests(fic, orc, seed, shape):
+    """Random forests over ragged images with uneven depths: the visiting-order keys of the deblocking kernel (root index,
+    depth, Morton code) against the oracle's sequential replay, standalone and fused into the decoder."""
+    from quadtree.common import EncodingInfo, QuadtreeImage, forest_to_leaves
+    from test_serialization import _random_quadtree_stream
+    rng = np.random.default_rng(100 + seed)
+    H, W = shape
+    nodes, vals, n_roots = _random_quadtree_stream(rng, W, H, min_side=2, p_split=0.65)
+    q = QuadtreeImage(EncodingInfo(7, 5, 1.0, W, H), stream=(nodes, vals, n_roots))
+    leaves, so = forest_to_leaves(q)
+    so[:, 0] *= 0.5                                           # keep the iteration tame
+    rects, index = orc.qt_visit_order(nodes, n_roots, H, W)
+    perm = (np.cumsum(nodes[:, 0] == 1) - 1)[index]
+    assert np.array_equal(leaves[perm][:, :3], rects)
+    x = rng.uniform(-30.0, 290.0, (H, W))
+    want = orc.qt_deblock(x, rects)
+    assert np.array_equal(fic.qt_deblock(x, leaves), want)
+    assert np.array_equal(fic.qt_deblock(x, leaves[rng.permutation(len(leaves))]), want)
+    for it in (3, fic.ITER_AUTO):
+        got, n_it = fic.tree_decode(fic.TREE_QUADTREE, leaves, so, H, W, iterations=it, deblock=True)
+        ref, n_ref = orc.tree_decode(0, leaves[perm], so[perm], H, W, iterations=it, deblock=True)
+        assert n_it == n_ref and np.array_equal(got, ref)
+        got, _ = fic.tree_decode(fic.TREE_QUADTREE, leaves, so, H, W, iterations=it)
+        ref, _ = orc.tree_decode(0, leaves, so, H, W, iterations=it)
+        assert np.array_equal(got, ref)
+
+
 def test_deblocking_rejected_for_hv(fic):
     leaves = np.array([[0, 0, 4, 4, 0, 0, 0, 0]], np.int32)
     with pytest.raises(ValueError):

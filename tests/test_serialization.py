@@ -280,7 +280,7 @@ def _random_quadtree_stream(rng, width, height, min_side=2, p_split=0.6):
 
     def grow(e):
         side = 1 << e
-        if side > min_side and rng.random() < p_split:
+        if side > min_side and (2 * side > min(width, height) or rng.random() < p_split):   # a leaf's 2x domain must fit
             nodes.append([0, 0, 0, 0, 0, 0, 0, e])
             for _ in range(4):
                 grow(e - 1)
