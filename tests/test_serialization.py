@@ -336,8 +336,13 @@ def _random_hv_stream(rng, width, height, min_side=2, p_split=0.7):
 
     def grow(w, h):
         can_v, can_h = w >= 2 * min_side, h >= 2 * min_side
-        if (can_v or can_h) and rng.random() < p_split:
+        too_wide, too_tall = 2 * w > width, 2 * h > height       # a leaf's 2x domain must fit the image
+        if (can_v or can_h) and (too_wide or too_tall or rng.random() < p_split):
             vertical = can_v and (not can_h or rng.random() < 0.5)
+            if too_wide and can_v:
+                vertical = True
+            elif too_tall and can_h:
+                vertical = False
             size = w if vertical else h
             s = int(rng.integers(min_side - 1, size - min_side))   # first child keeps s + 1 columns / rows
             nodes.append([0, int(vertical), s, 0, 0, 0, 0, 0])

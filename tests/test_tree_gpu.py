@@ -192,3 +192,24 @@ def test_tree_decoder_argument_checks(fic):
     leaves = np.array([[0, 0, 8, 8, 60, 60, 0, 0]], np.int32)
     with pytest.raises(ValueError):
         fic.tree_decode(fic.TREE_QUADTREE, leaves, np.zeros((1, 2)), 64, 64)
+
+
+@pytest.mark.parametrize("seed,shape", [(1, (64, 64)), (2, (70, 45)), (3, (33, 96)), (4, (200, 120))])
+def test_hv_decode_on_random_trees(fic, orc, seed, shape):
+    """Random HV trees (arbitrary split positions, ragged images): leaf table from the flat stream (`fic_hv_layout`), Jacobi
+    decode on the GPU against the oracle, quantised and float32-affine variants, fixed and AUTO sweeps."""
+    from hvv2.common import HVImage, tree_to_leaves
+    from quadtree.common import EncodingInfo
+    from test_serialization import _random_hv_stream
+    rng = np.random.default_rng(200 + seed)
+    H, W = shape
+    nodes, vals = _random_hv_stream(rng, W, H)
+    vals[:, 0] = np.clip(vals[:, 0], -0.9, 0.9)
+    vals[:, 1] = rng.uniform(0, 255, len(vals))
+    hv = HVImage(EncodingInfo(5, 7, 1.0, W, H), stream=(nodes, vals))
+    for quantised in (True, False):
+        leaves, so = tree_to_leaves(hv, quantised)
+        for it in (2, 6, fic.ITER_AUTO):
+            got, n_it = fic.tree_decode(fic.TREE_HV, leaves, so, H, W, iterations=it, f32_affine=not quantised)
+            ref, n_ref = orc.tree_decode(1, leaves, so, H, W, iterations=it, f32_affine=not quantised)
+            assert n_it == n_ref and np.array_equal(got, ref)
