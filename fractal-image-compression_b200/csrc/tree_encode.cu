@@ -356,7 +356,7 @@ __global__ void hv_pool_kernel(const uint8_t* __restrict__ img, int H, int W, fl
 // gridDim.y contiguous chunks so that the deep, narrow levels of the tree (a handful of rectangles) still fill the
 // GPU.  Each CTA writes the first minimum of its chunk; hv_pick_kernel merges the chunks with the same rule.
 // The three sums run in the reference's order (row-major over the oriented block, float32, no FMA).
-__global__ void __launch_bounds__(TE_THREADS)
+__global__ void __launch_bounds__(TE_THREADS, 4)
 hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
                  const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
                  int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs, int smem_px)
