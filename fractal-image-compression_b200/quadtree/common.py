@@ -6,6 +6,7 @@ objects and the flat arrays of the C ABI (include/fic.h: fic_qt_encode, fic_tree
 """
 from __future__ import annotations
 
+import functools
 import gc
 from dataclasses import dataclass, replace
 from typing import Callable, Optional
@@ -188,16 +189,29 @@ def _build_forest(kind, di, dj, ori, rot, qs, qo, sc, of, n, n_roots):
     return forest
 
 
+@functools.lru_cache(maxsize=64)
+def _root_squares(width: int, height: int) -> tuple:
+    """(i, j, exponent) of every root for a width x height image, in the reference's order."""
+    out = []
+    stack = [(0, 0, width, height)]
+    while stack:                                   # preorder: the square, then the strip to its right, then the one below
+        i, j, w, h = stack.pop()
+        e = min(w.bit_length(), h.bit_length()) - 1   # int(min(log2 w, log2 h)) without float rounding
+        side = 1 << e
+        out.append((i, j, e))
+        if side < h:
+            stack.append((i + side, j, side, h - side))
+        if side < w:
+            stack.append((i, j + side, w - side, h))
+    return tuple(out)
+
+
 def iter_root_squares(width: int, height: int, i: int = 0, j: int = 0):
     """Yield (i, j, exponent) of the forest's roots in the reference's order: largest 2^k square, then
-    the strip to its right, then the strip below (encoder.py:111-125, decoder.py:63-75)."""
-    e = int(min(np.log2(width), np.log2(height)))
-    side = 2 ** e
-    yield i, j, e
-    if side < width:
-        yield from iter_root_squares(width - side, height, i, j + side)
-    if side < height:
-        yield from iter_root_squares(side, height - side, i + side, j)
+    the strip to its right, then the strip below (encoder.py:111-125, decoder.py:63-75).  A ragged image has hundreds of
+    roots (313 x 413: 950), so the list is built iteratively and cached per image size."""
+    for ri, rj, e in _root_squares(int(width), int(height)):
+        yield ri + i, rj + j, e
 
 
 def _compact_even_bits(v: np.ndarray) -> np.ndarray:
