@@ -85,53 +85,43 @@ def read_preamble(f: BinaryIO, bits: BitBuffer, magic: bytes, what: str):
     return info, size, processor
 
 
-def _flatten_huffman(root, table: list) -> int:
-    """Append a decoder tree to `table` as rows (left, right, value), left < 0 marking a leaf; returns the root's row."""
-    index = {}
-    order = []
-    stack = [root]
-    while stack:
-        node = stack.pop()
-        index[id(node)] = len(table) + len(order)
-        order.append(node)
-        if node.left is not None:
-            stack.append(node.right)
-            stack.append(node.left)
-    for node in order:
-        if node.left is None:
-            table.append((-1, -1, int(node.val) if node.val is not None else 0))
-        else:
-            table.append((index[id(node.left)], index[id(node.right)], 0))
-    return index[id(root)]
-
-
 def read_nodes_native(f: BinaryIO, bits: BitBuffer, processor: EntropyProcessor, fic_tree_kind: int, root_exps, cap: int):
     """The node section that follows the preamble, read by `fic_tree_read_nodes` (csrc/stream_host.cu) instead of one
     Python call per field: returns the preorder stream nodes[k,8] and leaves `f` where the reference's word-wise
     reader would have left it (the next stream of an RGB file starts there).  None if this entropy processor has no
     table form (the caller then runs the bit-by-bit loop)."""
     from entropy.processor import HuffmanEntropyProcessor
-    if type(processor) is not HuffmanEntropyProcessor or not f.seekable():
+    if type(processor) is not HuffmanEntropyProcessor:
         return None
+    window = bits.native_window()
+    if window is None:
+        return None
+    import numpy as np
+
     import fic_b200
-    table: list = []
+    start, data, bit_pos = window
+    tables, rows = [], 0
     raw_width, huff_root = [], []
     for dim in CodingDimension:
         decoder = processor.dimension_decoders[dim.value]
         raw_width.append(int(processor.dimension_default_bit_widths[dim.value]))
-        huff_root.append(_flatten_huffman(decoder.root, table) if decoder is not None else -1)
-    pending = bits.accumulated_size                       # unread bits of the word the preamble ended in
-    start = f.tell() - (BitBuffer.MAX_BYTE_WIDTH if pending else 0)
-    f.seek(start)
-    data = f.read()
-    bit_pos = (BitBuffer.MAX_BIT_WIDTH - pending) if pending else 0
+        if decoder is None:
+            huff_root.append(-1)
+            continue
+        t = decoder.table.copy()
+        inner = t[:, 0] >= 0
+        t[inner, 0] += rows              # rows of all trees share one table: shift the child links
+        t[inner, 1] += rows
+        huff_root.append(rows)
+        rows += t.shape[0]
+        tables.append(t)
+    table = np.concatenate(tables) if tables else np.zeros((0, 3), np.int32)
     try:
         nodes, end_bit = fic_b200.tree_read_nodes(fic_tree_kind, data, bit_pos, root_exps, raw_width, huff_root, table, cap)
     except ValueError as e:
+        bits.resume_at(start, data, bit_pos)
         if "buffer returned EOF" in str(e):     # the reference's `assert node_type != EOF` (serialization.py:188)
             raise AssertionError("Invalid size encoding, buffer returned EOF") from None
         raise
-    words = (end_bit + BitBuffer.MAX_BIT_WIDTH - 1) // BitBuffer.MAX_BIT_WIDTH
-    f.seek(start + words * BitBuffer.MAX_BYTE_WIDTH)
-    bits.buff, bits.accumulated_size = 0, 0
+    bits.resume_at(start, data, end_bit)
     return nodes

@@ -86,3 +86,31 @@ class BitBuffer:
 
     def is_empty(self) -> bool:
         return self.accumulated_size == 0
+
+    # ---- hand-over to the native readers ---------------------------------------------------------
+    def native_window(self):
+        """(start, data, bit_pos) for the native stream readers, or None when the backing buffer cannot seek: `data` is
+        the rest of the file from the word the next unread bit lies in, `bit_pos` that bit's offset inside `data`."""
+        f = self.backing_buff
+        try:
+            if not f.seekable():
+                return None
+        except AttributeError:
+            return None
+        pending = self.accumulated_size
+        start = f.tell() - (self.MAX_BYTE_WIDTH if pending else 0)
+        f.seek(start)
+        data = f.read()
+        return start, data, (self.MAX_BIT_WIDTH - pending) if pending else 0
+
+    def resume_at(self, start: int, data: bytes, end_bit: int) -> None:
+        """Put buffer and file where bit-by-bit reading up to `end_bit` of a `native_window` would have left them."""
+        words, rem = divmod(end_bit, self.MAX_BIT_WIDTH)
+        if rem:
+            at = words * self.MAX_BYTE_WIDTH
+            self.buff = self._word.unpack(data[at:at + self.MAX_BYTE_WIDTH])[0]
+            self.accumulated_size = self.MAX_BIT_WIDTH - rem
+            words += 1
+        else:
+            self.buff, self.accumulated_size = 0, 0
+        self.backing_buff.seek(start + words * self.MAX_BYTE_WIDTH)

@@ -2,6 +2,7 @@
 // decoder kernels without one Python call per bit:
 //   fic_tree_read_nodes   QuadtreeDeserializer._read_data (quadtree/serialization.py:182-223) and
 //                         HVDeserializer._read_data (hvv2/serialization.py:186-224)
+//   fic_huffman_read_tree HuffmanDeserializer.deserialize (entropy/huffman.py:100-124)
 //   fic_pack_fields       BitBuffer.write applied to a whole column of fields (bitbuffer.py:18-37)
 //   fic_hv_layout         the rectangle of every node of an HV preorder stream (hvv2/decoder.py:59-88 walks the same
 //                         splits) and its depth -- what the decoder's leaf table and the writer's breadth-first order need
@@ -23,8 +24,20 @@ struct BitReader {
     uint32_t read(int width)
     {
         if (pos + width > nbits) { eof = true; return 0; }
-        uint32_t v = 0;
-        for (int k = 0; k < width; ++k, ++pos) v = (v << 1) | ((data[pos >> 3] >> (7 - (pos & 7))) & 1u);
+        if (width == 0) return 0;
+        if (width == 1) { const uint32_t b = (data[pos >> 3] >> (7 - (pos & 7))) & 1u; ++pos; return b; }
+        const int64_t byte = pos >> 3;
+        const int off = (int)(pos & 7);
+        uint32_t v;
+        if ((byte + 8) * 8 <= nbits) {   // eight bytes are there: one big-endian window, the field is cut out of it
+            uint64_t w = 0;
+            for (int k = 0; k < 8; ++k) w = (w << 8) | data[byte + k];
+            v = (uint32_t)((w << off) >> (64 - width));
+        } else {
+            v = 0;
+            for (int64_t p = pos; p < pos + width; ++p) v = (v << 1) | ((data[p >> 3] >> (7 - (p & 7))) & 1u);
+        }
+        pos += width;
         return v;
     }
 };
@@ -125,6 +138,35 @@ int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t b
                 }
         }
     }
+    *end_bit = br.pos;
+    return count;
+}
+
+int fic_huffman_read_tree(const uint8_t* data, int64_t nbytes, int64_t bit_pos, int val_bits, int32_t* table, int cap,
+                          int64_t* end_bit)
+{
+    FIC_REQUIRE(data && table && end_bit && nbytes >= 0 && bit_pos >= 0 && val_bits >= 0 && val_bits <= 32 && cap >= 1,
+                "fic_huffman_read_tree: bad arguments");
+    BitReader br{data, (nbytes / 4) * 32, bit_pos};
+    // entropy/huffman.py:100-124: breadth-first, `1` + value for a leaf, `0` for an inner node whose two children follow
+    // once every node read before them has had its turn
+    auto read_node = [&](int k) {
+        int32_t* row = table + 3 * (size_t)k;
+        if (br.read(1) == 1) { row[0] = -1; row[1] = -1; row[2] = (int32_t)br.read(val_bits); }
+        else { row[0] = 0; row[1] = 0; row[2] = 0; }
+    };
+    int count = 1;
+    read_node(0);
+    for (int k = 0; k < count && !br.eof; ++k) {
+        if (table[3 * (size_t)k] < 0) continue;      // a leaf has no children to wait for
+        if (count + 2 > cap) { fic_set_error("fic_huffman_read_tree: more than %d nodes", cap); return FIC_ECAP; }
+        table[3 * (size_t)k] = count;
+        table[3 * (size_t)k + 1] = count + 1;
+        read_node(count);
+        read_node(count + 1);
+        count += 2;
+    }
+    FIC_REQUIRE(!br.eof, "Invalid size encoding, buffer returned EOF");
     *end_bit = br.pos;
     return count;
 }

@@ -128,8 +128,40 @@ class HuffmanEncoder(EntropyEncoder):
 
 
 class HuffmanDecoder:
-    def __init__(self, root: HuffmanNode) -> None:
-        self.root = root
+    """Walks the tree bit by bit (huffman.py:120-124).  A decoder made by the native file reader holds the tree as a
+    table of (left, right, value) rows; the node objects are built when `root` (or `decode`) is first used."""
+
+    def __init__(self, root: Optional[HuffmanNode] = None, table: Optional[np.ndarray] = None) -> None:
+        self._root = root
+        self._table = table
+
+    @property
+    def root(self) -> HuffmanNode:
+        if self._root is None:
+            rows = self._table.tolist()
+            made = [HuffmanNode.Leaf(v, UNAVAILABLE) if left < 0 else HuffmanNode(UNAVAILABLE, None, None, None)
+                    for left, _, v in rows]
+            for node, (left, right, _) in zip(made, rows):
+                if left >= 0:
+                    node.left, node.right = made[left], made[right]
+            self._root = made[0]
+        return self._root
+
+    @property
+    def table(self) -> np.ndarray:
+        """Rows (left, right, value), row 0 the root, left < 0 marking a leaf."""
+        if self._table is None:
+            index, order, stack = {}, [], [self._root]
+            while stack:
+                node = stack.pop()
+                index[id(node)] = len(order)
+                order.append(node)
+                if node.left is not None:
+                    stack.append(node.right)
+                    stack.append(node.left)
+            self._table = np.array([(-1, -1, int(n.val) if n.val is not None else 0) if n.left is None
+                                    else (index[id(n.left)], index[id(n.right)], 0) for n in order], np.int32).reshape(-1, 3)
+        return self._table
 
     def decode(self, read_buff: BitBuffer) -> int:
         node = self.root

@@ -113,7 +113,23 @@ class HuffmanEntropyProcessor(EntropyProcessor):
         self.dimension_default_bit_widths = dimension_default_bit_widths
 
     def deserialize_dimension_coding_structures(self, read_buff, dimension):
-        root = HuffmanDeserializer().deserialize(read_buff, self.dimension_default_bit_widths[dimension.value])
+        val_bits = self.dimension_default_bit_widths[dimension.value]
+        window = read_buff.native_window()
+        if window is not None:      # the tree dump is read by fic_huffman_read_tree; node objects only on demand
+            import fic_b200
+            start, data, bit_pos = window
+            try:
+                table, end_bit = fic_b200.huffman_read_tree(data, bit_pos, val_bits)
+            except ValueError as e:
+                read_buff.resume_at(start, data, bit_pos)
+                if "buffer returned EOF" not in str(e):
+                    raise
+                table = None            # truncated file: let the bit-by-bit reader fail the way the reference does
+            if table is not None:
+                read_buff.resume_at(start, data, end_bit)
+                self.dimension_decoders[dimension.value] = HuffmanDecoder(table=table)
+                return
+        root = HuffmanDeserializer().deserialize(read_buff, val_bits)
         self.dimension_decoders[dimension.value] = HuffmanDecoder(root)
 
     def decode(self, read_buff, dimension):

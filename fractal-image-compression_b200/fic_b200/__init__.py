@@ -72,6 +72,7 @@ SIGNATURES = {
     "fic_ycbcr_to_rgb": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
     "fic_tree_read_nodes": (C.c_int, [C.c_int, _vp, C.c_int64, C.c_int64, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int, _i64p]),
     "fic_hv_layout": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "fic_huffman_read_tree": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, _vp, C.c_int, _i64p]),
     "fic_pack_fields": (C.c_int64, [_vp, _vp, C.c_int64, C.c_uint32, C.c_int, _vp, C.c_int64, C.POINTER(C.c_uint32),
                                     C.POINTER(C.c_int)]),
 }
@@ -491,6 +492,17 @@ def tree_read_nodes(kind, data: bytes, bit_pos: int, root_exps, raw_width, huff_
                                          exps.shape[0] if kind == TREE_QUADTREE else 1, _ptr(rw), _ptr(hr), _ptr(ht),
                                          _ptr(nodes), int(cap), C.byref(end)), "fic_tree_read_nodes")
     return nodes[:n].copy(), int(end.value)
+
+
+def huffman_read_tree(data: bytes, bit_pos: int, val_bits: int):
+    """One serialised Huffman tree -> (table[m,3] = left, right, value ; first bit after it)."""
+    buf = np.frombuffer(data, np.uint8)
+    cap = 2 * (1 << min(int(val_bits), 20)) + 2          # a tree over val_bits-bit symbols has at most 2^(bits+1) - 1 nodes
+    table = np.empty((cap, 3), np.int32)
+    end = C.c_int64(0)
+    n = _check(lib().fic_huffman_read_tree(buf.ctypes.data_as(_vp), buf.size, int(bit_pos), int(val_bits), _ptr(table), cap,
+                                           C.byref(end)), "fic_huffman_read_tree")
+    return table[:n].copy(), int(end.value)
 
 
 def pack_fields(values, widths, pending: int = 0, pending_bits: int = 0):

@@ -260,6 +260,12 @@ int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t b
                         int n_roots, const int32_t* raw_width, const int32_t* huff_root, const int32_t* huff_table,
                         int32_t* nodes, int cap, int64_t* end_bit);
 
+/* Replaces HuffmanDeserializer.deserialize (entropy/huffman.py:100-124): reads one breadth-first tree dump (`1` + value
+ * in val_bits bits for a leaf, `0` for an inner node) into table[m][3] = { left, right, value } rows in stream order
+ * (row 0 = root, left < 0 = leaf) -- the form fic_tree_read_nodes takes.  Returns the node count. */
+int fic_huffman_read_tree(const uint8_t* data, int64_t nbytes, int64_t bit_pos, int val_bits, int32_t* table, int cap,
+                          int64_t* end_bit);
+
 /* BitBuffer.write (bitbuffer.py:18-37) for n fields at once: the low widths[k] bits of values[k], most significant bit
  * first, appended to `pending_bits` (< 32) pending bits; every completed big-endian 32-bit word goes to `out`.
  * Returns the bytes written (a multiple of 4); *rest / *rest_bits = the bits still pending afterwards. */
