@@ -50,7 +50,7 @@ struct DimCoder {
     {
         if (root < 0) return br.read(raw_width);
         int n = root;
-        while (table[3 * n] >= 0 && !br.eof) n = br.read(1) == 0 ? table[3 * n] : table[3 * n + 1];   // huffman.py:120-124
+        while (table[3 * n] >= 0 && !br.eof) n = br.read(1) == 0 ? table[3 * n] : table[3 * n + 1];   // huffman.py:75-81
         return (uint32_t)table[3 * n + 2];
     }
 };

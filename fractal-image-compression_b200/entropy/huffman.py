@@ -128,7 +128,7 @@ class HuffmanEncoder(EntropyEncoder):
 
 
 class HuffmanDecoder:
-    """Walks the tree bit by bit (huffman.py:120-124).  A decoder made by the native file reader holds the tree as a
+    """Walks the tree bit by bit (huffman.py:75-81).  A decoder made by the native file reader holds the tree as a
     table of (left, right, value) rows; the node objects are built when `root` (or `decode`) is first used."""
 
     def __init__(self, root: Optional[HuffmanNode] = None, table: Optional[np.ndarray] = None) -> None:
