@@ -248,7 +248,8 @@ struct QtPoolDev {
 };
 
 __global__ void __launch_bounds__(TE_THREADS)
-qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __restrict__ I1, const long long* __restrict__ I2,
+qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int W, const long long* __restrict__ I1,
+                 const long long* __restrict__ I2,
                  const int32_t* __restrict__ ranges /*[n][2] = si,sj*/, int side, QtPoolDev pool, int full, int nmodes,
                  double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ rec /*[n][6]*/,
                  double* __restrict__ vals /*[n][3]*/)
@@ -314,8 +315,7 @@ qt_search_kernel(const uint8_t* __restrict__ img, int W, const long long* __rest
             for (int j = 0; j < side; ++j) {
                 int sa, sb;
                 fic_iso_qt_enc(d_orient, d_rot, side, i, j, sa, sb);
-                const uint8_t* p = img + (size_t)(di + 2 * sa) * W + dj + 2 * sb;
-                float d = __fmul_rn((float)((int)p[0] + p[1] + p[W] + p[W + 1]), 0.25f);
+                const float d = Dp[(size_t)(di + 2 * sa) * (W - 1) + dj + 2 * sb];   // 2x2 mean, exact in float32 (hv_pool_kernel)
                 float r = (float)img[(size_t)(si + i) * W + sj + j];
                 ds = __fadd_rn(ds, d);
                 sds = __fadd_rn(sds, __fmul_rn(d, d));
@@ -622,6 +622,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
                     "(the reference fails with 'unable to broadcast')", 1 << e_top, 1 << e_top, 2 << e_top, 2 << e_top, H, W);
     }
     FIC_TRY(build_integrals(h, d_img, H, W, st));
+    FIC_TRY(hv_build_pool(h, d_img, H, W, st));   // 2x2 means at every pixel offset: one load per pooled sample in the search
     const long long* I1 = h->t_int1.as<long long>();
     const long long* I2 = h->t_int2.as<long long>();
 
@@ -710,7 +711,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             QtPoolDev pool;
             pool.offsets = h->t_lists.as<int32_t>() + pool_base[pk];
             pool.rows = pool.offsets + 73;
-            qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, W, I1, I2, h->t_work.as<int32_t>(), 1 << e, pool, full, nmodes,
+            qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, h->t_work.as<int32_t>(), 1 << e, pool, full, nmodes,
                                                        max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
                                                        h->t_aux.as<double>());
             FIC_CHECK_LAUNCH(h, "qt_search_kernel");
