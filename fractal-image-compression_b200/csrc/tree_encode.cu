@@ -247,6 +247,8 @@ struct QtPoolDev {
     const int32_t* rows;     // [offsets[72]][4] = (i, j, rot, orient)
 };
 
+#define QT_RANGE_SMEM 1024
+
 __global__ void __launch_bounds__(TE_THREADS)
 qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int W, const long long* __restrict__ I1,
                  const long long* __restrict__ I2,
@@ -260,9 +262,13 @@ qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
     __shared__ int seg_rot[2], seg_orient[2];
     __shared__ int n_seg;
     __shared__ unsigned long long s_bound;   // bit pattern of the best score found so far by this CTA (+inf at start)
+    __shared__ float s_range[QT_RANGE_SMEM];  // the range block as floats (sides up to 32)
     const int tid = threadIdx.x;
     const int si = ranges[2 * blockIdx.x], sj = ranges[2 * blockIdx.x + 1];
     const int nn = side * side;
+    const bool in_smem = nn <= QT_RANGE_SMEM;
+    if (in_smem)
+        for (int t = tid; t < nn; t += TE_THREADS) s_range[t] = (float)img[(size_t)(si + t / side) * W + sj + t % side];
     if (tid == 0) {
         s_bound = 0x7ff0000000000000ull;
         float rs = 0.f, sq = 0.f;
@@ -310,17 +316,28 @@ qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
         int d_rot, d_orient;
         if (dorient == rorient) { d_rot = (drot - rrot) & 3; d_orient = 0; }
         else { d_rot = (drot - rrot + 2) & 3; d_orient = 1; }
+        // The isometry is affine in (i, j): the pooled sample of range pixel (i, j) sits at  o00 + i * step_i + j * step_j
+        // in the pooled image (2x2 means at every pixel offset, exact in float32 -- hv_pool_kernel), so the map is
+        // evaluated at three corners per candidate instead of once per pixel.
+        int a00, b00, a10, b10, a01, b01;
+        fic_iso_qt_enc(d_orient, d_rot, side, 0, 0, a00, b00);
+        fic_iso_qt_enc(d_orient, d_rot, side, 1, 0, a10, b10);
+        fic_iso_qt_enc(d_orient, d_rot, side, 0, 1, a01, b01);
+        const int PW = W - 1;
+        const int step_i = 2 * ((a10 - a00) * PW + (b10 - b00)), step_j = 2 * ((a01 - a00) * PW + (b01 - b00));
+        const float* drow = Dp + (size_t)(di + 2 * a00) * PW + dj + 2 * b00;
         float ds = 0.f, sds = 0.f, ab = 0.f;
-        for (int i = 0; i < side; ++i)
-            for (int j = 0; j < side; ++j) {
-                int sa, sb;
-                fic_iso_qt_enc(d_orient, d_rot, side, i, j, sa, sb);
-                const float d = Dp[(size_t)(di + 2 * sa) * (W - 1) + dj + 2 * sb];   // 2x2 mean, exact in float32 (hv_pool_kernel)
-                float r = (float)img[(size_t)(si + i) * W + sj + j];
+        int t = 0;
+        for (int i = 0; i < side; ++i, drow += step_i) {
+            const float* q = drow;
+            for (int j = 0; j < side; ++j, q += step_j, ++t) {
+                const float d = *q;
+                const float r = in_smem ? s_range[t] : (float)img[(size_t)(si + i) * W + sj + j];
                 ds = __fadd_rn(ds, d);
                 sds = __fadd_rn(sds, __fmul_rn(d, d));
                 ab = __fadd_rn(ab, __fmul_rn(d, r));
             }
+        }
         {   // exact lower bound of the score (minimum of its quadratic form, see hv_search_kernel) against the CTA's best
             const double bound = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound);
             const double room = DS(slack_a, DM(dn, bound));
