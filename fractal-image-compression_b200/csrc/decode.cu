@@ -239,15 +239,15 @@ tree_sweep_kernel(const int32_t* __restrict__ leaves, const double* __restrict__
             const double scale = so[2 * (size_t)k], offset = so[2 * (size_t)k + 1];
             double val;
             if (KIND == FIC_TREE_QUADTREE) {
-                int acc = 0;
+                // .T then rot90 (decoder.py:102-104) maps 2x2 cells onto 2x2 cells and the pool is an integer sum
+                // (utils.py:22), so the cell of this output pixel is located once, on the hh x hh grid of cells
+                int acc = 0, ca, cb;
+                fic_iso_bf(orient, rot, hh, a, b, ca, cb);
+                const double* cell = img + (size_t)(di + 2 * ca) * W + dj + 2 * cb;
 #pragma unroll
                 for (int u = 0; u < 2; ++u)
 #pragma unroll
-                    for (int v = 0; v < 2; ++v) {
-                        int sa, sb;
-                        fic_iso_bf(orient, rot, 2 * hh, 2 * a + u, 2 * b + v, sa, sb);  // .T then rot90, decoder.py:102-104
-                        acc += __double2int_rz(img[(size_t)(di + sa) * W + dj + sb]);   // utils.py:22
-                    }
+                    for (int v = 0; v < 2; ++v) acc += __double2int_rz(cell[(size_t)u * W + v]);
                 val = DA(DM(DM((double)acc, 0.25), scale), offset);
             } else {
                 float q[4];
