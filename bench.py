@@ -189,7 +189,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "bundled image lena_512x512 (grayscale)",
-        "config": {"workload": "bruteforce-jit 512x512 r8/d16 stride1 8iso", "sample": f"{sample} ranges per step"},
+        "config": {"workload": WORKLOAD},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{sample} contiguous ranges x all {N_POS * 8} candidates per step, "
                                    f"C restatement of jit_bfencoder.py (oracle/fic_oracle.c), OpenMP over ranges"},
@@ -199,11 +199,32 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+WORKLOAD = "bruteforce-jit 512x512 r8/d16 stride1 8iso, one image per GPU"
+REC_BYTES = 32                                 # winner record exchanged between ranks: idx int32[4] + (s, o) float64[2]
+
+
+def records_sha(idx, so, R) -> str:
+    """SHA-256 over idx int32[n,4] | so float64[n,2] | R float64[n] (tests/golden/make_golden_full.py)."""
+    import hashlib
+    hh = hashlib.sha256()
+    hh.update(np.ascontiguousarray(idx, np.int32).tobytes())
+    hh.update(np.ascontiguousarray(so, np.float64).tobytes())
+    hh.update(np.ascontiguousarray(R, np.float64).tobytes())
+    return hh.hexdigest()
+
+
+def synthetic_image(seed, H, W):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import synthetic_image as syn
+    return syn(seed, H, W)
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
     import fic_b200
+    from fic_b200.parallel import image_shares, range_slice
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -218,6 +239,11 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x: float) -> float:
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     img = load_image(rank)
     h = fic_b200.Handle(local)
@@ -227,99 +253,81 @@ def run_ours(args):
     stream = tstream.cuda_stream
     assert stream != 0
     d_img = torch.from_numpy(img).to(dev)
-    d_idx = torch.zeros((N_RANGES, 4), dtype=torch.int32, device=dev)
-    # The images of a batch are independent, so their winner records are exchanged in chunks of G images (SURVEY 8(e):
-    # "no collective except the final gather of records"): two chunk buffers, the all-gather of a full chunk overlaps the
-    # encodes that fill the other one.  A collective after EVERY image locks all ranks to the pace of the slowest GPU plus
-    # the launch jitter of eight processes (measured: 1.11 ms per image on every rank against 0.98-1.07 ms alone).
+    # The images of a batch are independent, so their winner records -- (domain row, column, orientation, rotation) as
+    # int32[4] plus (s, o) as float64[2], 32 bytes per range -- are exchanged in chunks of G images ("no
+    # collective except the final gather of records").  The encode calls do not wait for the GPU, so the host runs
+    # ahead; the all-gather of a full chunk is enqueued between two encodes IN STREAM ORDER (the next encode starts
+    # after it), so its CTAs never share the SMs with the persistent one-CTA-per-SM correlation kernel.
     G = max(1, int(os.environ.get("FIC_BENCH_GATHER_EVERY", "16")))
-    d_so2 = [torch.zeros((G, N_RANGES, 2), dtype=torch.float64, device=dev) for _ in range(2)]
-    d_so = d_so2[0][0]
+    no_gather = bool(os.environ.get("FIC_BENCH_NO_GATHER"))       # diagnostic: drop the exchange
+    IDX_B, SO_B = N_RANGES * 16, N_RANGES * 16
+    chunk = torch.zeros((G, IDX_B + SO_B), dtype=torch.uint8, device=dev)     # per image: idx bytes | so bytes
+    gathered = torch.zeros((world, G, IDX_B + SO_B), dtype=torch.uint8, device=dev) if world > 1 else None
     d_R = torch.zeros((N_RANGES,), dtype=torch.float64, device=dev)
-    gathered = [[torch.zeros_like(d_so2[0]) for _ in range(world)] for _ in range(2)] if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     flags = fic_b200.BF_EXACT_ONLY if args.exact_only else 0
-    cursor = [0, 0]               # chunk being filled, next free slot in it
-    last_slot = [0, 0]
-    last_gather = [0, 0]          # chunk and image count of the most recent all-gather
-    # The gather is enqueued by a helper thread while the main thread is already inside the next encode call (ctypes
-    # releases the GIL): the NCCL launch overhead of image k then overlaps the kernels of image k+1 as well.
-    import queue
-    gq: "queue.Queue" = queue.Queue()
-    submitted = [None, None]      # per buffer: (threading.Event set once enqueued, [work handle])
+    state = {"slot": 0, "last": 0, "gathers": 0}
 
-    def gather_worker():
-        torch.cuda.set_device(local)
-        side = torch.cuda.Stream(device=dev)
-        with torch.cuda.stream(side):
-            while True:
-                item = gq.get()
-                if item is None:
-                    return
-                k, count, ev, box = item
-                box.append(dist.all_gather([g[:count] for g in gathered[k]], d_so2[k][:count], async_op=True))
-                ev.set()
+    def rec_ptrs(slot):
+        base = chunk[slot].data_ptr()
+        return base, base + IDX_B
 
-    worker = None
-    if world > 1:
-        worker = threading.Thread(target=gather_worker, daemon=True)
-        worker.start()
-
-    def wait_buffer(k):
-        if submitted[k] is not None:
-            ev, box = submitted[k]
-            ev.wait()
-            box[0].wait()              # stream-level: the encode about to overwrite the buffer waits for its gather
-            submitted[k] = None
-
-    def submit_gather(k, count):
-        if world > 1 and count > 0 and not os.environ.get("FIC_BENCH_NO_GATHER"):   # (the env switch is a diagnostic)
-            ev, box = threading.Event(), []
-            submitted[k] = (ev, box)
-            last_gather[0], last_gather[1] = k, count
-            gq.put((k, count, ev, box))
+    def exchange(count):
+        if world > 1 and count > 0 and not no_gather:
+            dist.all_gather_into_tensor(gathered, chunk)      # only ever called with a full chunk
+            state["gathers"] += 1
 
     def step():
-        k, slot = cursor
-        if world > 1 and slot == 0:
-            wait_buffer(k)        # the chunk about to be refilled has been gathered
-        fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, d_idx.data_ptr(), d_so2[k][slot].data_ptr(), d_R.data_ptr(),
-                               flags=flags, stream=stream)
-        last_slot[0], last_slot[1] = k, slot
+        slot = state["slot"]
+        p_idx, p_so = rec_ptrs(slot)
+        fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, p_idx, p_so, d_R.data_ptr(), flags=flags, stream=stream)
+        state["last"] = slot
         if slot + 1 == G:         # the only exchange of the path: winner records
-            submit_gather(k, G)
-            cursor[0], cursor[1] = k ^ 1, 0
+            exchange(G)
+            state["slot"] = 0
         else:
-            cursor[1] = slot + 1
+            state["slot"] = slot + 1
 
     def drain():
-        if world > 1:
-            k, slot = cursor
-            if slot > 0:          # a partly filled chunk: gather what is there
-                wait_buffer(k)
-                submit_gather(k, slot)
-                cursor[0], cursor[1] = k ^ 1, 0
-            wait_buffer(0)
-            wait_buffer(1)
+        if state["slot"] > 0:     # a partly filled chunk: gather what is there
+            if world > 1 and not no_gather:
+                part = torch.zeros((world, state["slot"], IDX_B + SO_B), dtype=torch.uint8, device=dev)
+                dist.all_gather_into_tensor(part, chunk[:state["slot"]])
+                state["gathers"] += 1
+            state["slot"] = 0
+
+    def records_of(slot):
+        raw = chunk[slot].cpu().numpy()
+        return raw[:IDX_B].view(np.int32).reshape(-1, 4).copy(), raw[IDX_B:].view(np.float64).reshape(-1, 2).copy()
 
     for _ in range(max(args.warmup, 3)):
         step()
+    if world > 1 and not no_gather:   # one full chunk through the exchange, checked: every rank's records arrive unchanged
+        while state["slot"] != 0:
+            step()
+        for _ in range(G):
+            step()
+        torch.cuda.synchronize()
+        assert torch.equal(gathered[rank], chunk), "record gather corrupted this rank's records"
+        assert all(bool(gathered[r].any()) for r in range(world)), "record gather left a rank's records empty"
     drain()
     torch.cuda.synchronize()
-    d_so = d_so2[last_slot[0]][last_slot[1]]   # the records of the last warm-up image
-    if world > 1 and last_gather[1] and not os.environ.get("FIC_BENCH_NO_GATHER"):
-        k, count = last_gather    # the exchange delivered this rank's records unchanged, and every rank's are there
-        assert torch.equal(gathered[k][rank][:count], d_so2[k][:count]), "record gather corrupted this rank's records"
-        assert all(bool(g[:count].abs().sum() > 0) for g in gathered[k]), "record gather left a rank's records empty"
 
-    # parity spot check against the reference's own records (tests/golden, rank 0 image only)
+    # parity against the CPU oracle's records of the whole image (tests/golden/bf_full_golden.npz: SHA-256 of all 4 096
+    # records, made by tests/golden/make_golden_full.py; the oracle is pinned to the reference) -- rank 0's image only
     parity = "skipped"
     if rank == 0:
-        g = np.load(os.path.join(ROOT, "tests", "golden", "bf_golden.npz"))
-        idx = d_idx.cpu().numpy(); so = d_so.cpu().numpy(); R = d_R.cpu().numpy()
-        ok = all(idx[k].tolist() == [int(v) for v in rec[:4]] and so[k, 0] == rec[4] and so[k, 1] == rec[5]
-                 and R[k] == rec[6] for k, rec in zip(g["jit512_sel"], g["jit512_rec"]))
-        parity = "bit-exact on golden ranges" if ok else "MISMATCH"
+        idx, so = records_of(state["last"])
+        R = d_R.cpu().numpy()
+        gpath = os.path.join(ROOT, "tests", "golden", "bf_full_golden.npz")
+        if os.path.exists(gpath):
+            want = str(np.load(gpath)["jit512_sha256"])
+            parity = "bit-exact, sha256 of 4096 records" if records_sha(idx, so, R) == want else "MISMATCH"
+        else:
+            g = np.load(os.path.join(ROOT, "tests", "golden", "bf_golden.npz"))
+            ok = all(idx[k].tolist() == [int(v) for v in rec[:4]] and so[k, 0] == rec[4] and so[k, 1] == rec[5]
+                     and R[k] == rec[6] for k, rec in zip(g["jit512_sel"], g["jit512_rec"]))
+            parity = "bit-exact on golden ranges" if ok else "MISMATCH"
 
     # ---- device-resident timing -----------------------------------------------------------------
     sampler = ClockSampler(local)
@@ -333,10 +341,10 @@ def run_ours(args):
     for a, b in evs:
         flush.zero_()
         a.record()
-        step()
+        step()                # includes the exchange of a chunk whenever one fills up
         b.record()
     tail[0].record()
-    drain()               # the gather of the last chunk is timed in full
+    drain()                   # the gather of the last, partly filled chunk is timed in full
     tail[1].record()
     barrier()
     clocks = sampler.stop()
@@ -344,32 +352,176 @@ def run_ours(args):
     kern_ms, kern_launches = h.profile_read()
     h.profile(False)
     cnt = h.counters()
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     per_rank_ms = [total_ms / args.steps]
     if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         allt = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
         per_rank_ms = [float(x.item()) / args.steps for x in allt]
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
+    total_ms = max_over_ranks(total_ms)
     value = world * args.steps * MATCHES_PER_IMAGE / (total_ms * 1e-3)
 
     # ---- end to end through the C ABI with HOST buffers (pinned input) ----------------------------
+    # Every step: H2D of the image and D2H of its records inside fic_bf_encode; at N > 1 the records of G images are
+    # then exchanged as well (host -> device staging -> all-gather -> host), so e2e covers everything `value` covers.
     pin = torch.from_numpy(img).pin_memory()
     h_img = pin.numpy()
-    for _ in range(2):
-        fic_b200.bf_encode(h_img, mode=fic_b200.BF_MODE_JIT, flags=flags, handle=h)
+    h_chunk = torch.zeros((G, IDX_B + SO_B), dtype=torch.uint8).pin_memory()
+    h_all = torch.zeros((world, G, IDX_B + SO_B), dtype=torch.uint8).pin_memory() if world > 1 else None
+    e2e_xfer = {"h2d": 0, "d2h": 0}
+
+    def e2e_exchange(count):
+        if world > 1 and count > 0 and not no_gather:
+            chunk[:count].copy_(h_chunk[:count], non_blocking=True)
+            dst = gathered if count == G else torch.empty((world, count, IDX_B + SO_B), dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(dst, chunk[:count])
+            h_all[:, :count].copy_(dst, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            e2e_xfer["h2d"] += count * (IDX_B + SO_B)
+            e2e_xfer["d2h"] += world * count * (IDX_B + SO_B)
+
+    def e2e_steps(n):
+        slot = 0
+        for _ in range(n):
+            idx, so, _R = fic_b200.bf_encode(h_img, mode=fic_b200.BF_MODE_JIT, flags=flags, handle=h)
+            if world > 1:
+                row = h_chunk[slot].numpy()
+                row[:IDX_B] = idx.view(np.uint8).ravel()
+                row[IDX_B:] = so.view(np.uint8).ravel()
+            slot += 1
+            if slot == G:
+                e2e_exchange(G)
+                slot = 0
+        e2e_exchange(slot)
+
+    e2e_steps(2)
     barrier()
+    e2e_xfer["h2d"] = e2e_xfer["d2h"] = 0
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        fic_b200.bf_encode(h_img, mode=fic_b200.BF_MODE_JIT, flags=flags, handle=h)
+    e2e_steps(args.steps)
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = world * args.steps * MATCHES_PER_IMAGE / e2e_s
+
+    # ---- sustained clocks: back-to-back encodes for a few seconds, no flush, no exchange ------------
+    sustained = None
+    if args.sustain > 0:
+        n_loop = max(64, int(args.sustain * 1e3 / (total_ms / args.steps)))
+        p_idx, p_so = rec_ptrs(0)
+        sam2 = ClockSampler(local)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        sam2.start()
+        s0.record()
+        for _ in range(n_loop):
+            fic_b200.bf_encode_dev(h, d_img.data_ptr(), H, W, p_idx, p_so, d_R.data_ptr(), flags=flags, stream=stream)
+        s1.record()
+        torch.cuda.synchronize()
+        clk2 = sam2.stop()
+        sus_ms = max_over_ranks(s0.elapsed_time(s1))
+        sustained = {"seconds": sus_ms * 1e-3, "encodes": n_loop, "ms_per_encode": sus_ms / n_loop,
+                     "matches_per_s": world * n_loop * MATCHES_PER_IMAGE / (sus_ms * 1e-3), "clocks": clk2}
+
+    # ---- configs[3]: ONE synthetic 4096x4096 image, range blocks sharded over the ranks ---------------
+    c4 = None
+    if args.c4_side > 0:
+        side = args.c4_side
+        big = synthetic_image(0, side, side)
+        n4 = (side // 8) ** 2
+        b4, e4 = range_slice(n4, rank, world)
+        pad4 = max(range_slice(n4, r, world)[1] - range_slice(n4, r, world)[0] for r in range(world))
+        d_big = torch.from_numpy(big).to(dev)
+        rec4 = torch.zeros((pad4, REC_BYTES), dtype=torch.uint8, device=dev)      # rows: idx bytes | so bytes, per range
+        idx4 = torch.zeros((pad4, 4), dtype=torch.int32, device=dev)
+        so4 = torch.zeros((pad4, 2), dtype=torch.float64, device=dev)
+        R4 = torch.zeros((pad4,), dtype=torch.float64, device=dev)
+        all4 = torch.zeros((world, pad4, REC_BYTES), dtype=torch.uint8, device=dev) if world > 1 else None
+
+        def run4():
+            fic_b200.bf_encode_dev(h, d_big.data_ptr(), side, side, idx4.data_ptr(), so4.data_ptr(), R4.data_ptr(),
+                                   range_begin=b4, range_end=e4, stream=stream)
+            rec4[:, :16] = idx4.view(torch.uint8).view(pad4, 16)
+            rec4[:, 16:] = so4.view(torch.uint8).view(pad4, 16)
+            if world > 1:
+                dist.all_gather_into_tensor(all4, rec4)
+
+        run4()                # warm-up: workspaces of this size, NCCL buffers
+        barrier()
+        sam4 = ClockSampler(local)
+        sam4.start()
+        a4, z4 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h.reset_counters()
+        a4.record()
+        run4()
+        z4.record()
+        barrier()
+        clk4 = sam4.stop()
+        sec4 = max_over_ranks(a4.elapsed_time(z4)) * 1e-3
+        cnt4 = h.counters()
+        full = (all4 if world > 1 else rec4.unsqueeze(0)).cpu().numpy()
+        counts = [range_slice(n4, r, world)[1] - range_slice(n4, r, world)[0] for r in range(world)]
+        rows = np.concatenate([full[r, :counts[r]] for r in range(world)])
+        g_idx = np.ascontiguousarray(rows[:, :16]).view(np.int32).reshape(-1, 4)
+        g_so = np.ascontiguousarray(rows[:, 16:]).view(np.float64).reshape(-1, 2)
+        # (1) a slice owned by ANOTHER rank, encoded again by this rank alone, must equal what the gather delivered
+        probe_rank = (rank + 1) % world
+        pb, pe = range_slice(n4, probe_rank, world)
+        pe = min(pe, pb + 64)
+        fic_b200.bf_encode_dev(h, d_big.data_ptr(), side, side, idx4.data_ptr(), so4.data_ptr(), R4.data_ptr(),
+                               range_begin=pb, range_end=pe, stream=stream)
+        torch.cuda.synchronize()
+        same = bool(np.array_equal(idx4[:pe - pb].cpu().numpy(), g_idx[pb:pe]) and
+                    np.array_equal(so4[:pe - pb].cpu().numpy(), g_so[pb:pe]))
+        same = bool(max_over_ranks(0.0 if same else 1.0) == 0.0)
+        # (2) the CPU oracle's records of 16 ranges of this image (tests/golden/bf_full_golden.npz)
+        par4 = "skipped"
+        gpath = os.path.join(ROOT, "tests", "golden", "bf_full_golden.npz")
+        if rank == 0 and side == 4096 and os.path.exists(gpath):
+            g = np.load(gpath)
+            ok = all(g_idx[int(k)].tolist() == [int(v) for v in rec[:4]] and g_so[int(k), 0] == rec[4] and
+                     g_so[int(k), 1] == rec[5] for k, rec in zip(g["syn4096_sel"], g["syn4096_rec"]))
+            par4 = "bit-exact on 16 oracle ranges" if ok else "MISMATCH"
+        c4 = {"workload": f"bruteforce-jit synthetic {side}x{side}, {n4} ranges sharded over {world} GPU(s) by range slices, "
+                          f"records all-gathered over NCCL (32 B per range)", "n_gpus": world, "seconds": sec4,
+              "matches_per_s": n4 * (side - 16) ** 2 * 8 / sec4, "ranges_per_rank": e4 - b4,
+              "equals_single_gpu_slice": same, "parity": par4, "rescan_ranges_rank0": cnt4["rescan_ranges"],
+              "scaling": "strong", "clocks": clk4}
+        del d_big, rec4, idx4, so4, R4, all4
+
+    # ---- configs[4], a slice: 8 synthetic 1024x1024 RGB images per rank, per-plane encode + 32-sweep decode ----------
+    c5 = None
+    if args.c5_images > 0:
+        side5, per_rank = 1024, args.c5_images
+        n_images = per_rank * world
+        mine = image_shares(n_images, rank, world)
+        base = np.stack([synthetic_image(100 + k, side5, side5) for k in range(3)])
+        planes = np.stack([np.roll(base[c], 8 * i, axis=0) for i in mine for c in range(3)])
+        n5 = (side5 // 8) ** 2
+        fic_b200.bf_encode(planes[0], mode=1, handle=h)       # warm-up: workspaces of this size
+        t_idx = torch.zeros((len(planes), n5, 4), dtype=torch.int32, device=dev)
+        t_so = torch.zeros((len(planes), n5, 2), dtype=torch.float64, device=dev)
+        g5_idx = torch.zeros((world,) + tuple(t_idx.shape), dtype=torch.int32, device=dev) if world > 1 else None
+        g5_so = torch.zeros((world,) + tuple(t_so.shape), dtype=torch.float64, device=dev) if world > 1 else None
+        barrier()
+        t0 = time.perf_counter()
+        idx5, so5, _R5 = fic_b200.bf_encode_batch(planes, mode=1, handle=h)
+        t_enc = time.perf_counter() - t0
+        dec5 = fic_b200.bf_decode_batch(idx5, so5, side5, side5, 32, handle=h)
+        t_dec = time.perf_counter() - t0 - t_enc
+        if world > 1:
+            t_idx.copy_(torch.from_numpy(idx5))
+            t_so.copy_(torch.from_numpy(so5))
+            dist.all_gather_into_tensor(g5_idx, t_idx)
+            dist.all_gather_into_tensor(g5_so, t_so)
+            torch.cuda.synchronize()
+        sec5 = max_over_ranks(time.perf_counter() - t0)
+        mse = float(np.mean((dec5[0].astype(np.float64) - planes[0].astype(np.float64)) ** 2))
+        c5 = {"workload": f"{n_images} synthetic 1024x1024 RGB images ({per_rank} per GPU), every colour plane brute-force "
+                          f"encoded and decoded with 32 sweeps through the host-buffer C ABI, image-parallel, records "
+                          f"all-gathered over NCCL", "n_gpus": world, "seconds": sec5, "images_per_s": n_images / sec5,
+              "encode_seconds_rank0": t_enc, "decode_seconds_rank0": t_dec,
+              "encode_matches_per_s": n_images * 3 * n5 * (side5 - 16) ** 2 * 8 / sec5,
+              "psnr_plane0_db": float(10 * np.log10(255.0 ** 2 / mse)) if mse > 0 else None, "scaling": "weak"}
 
     if rank == 0:
         pk = peaks()
@@ -381,17 +533,24 @@ def run_ours(args):
             achieved = matches_per_launch * FLOP_PER_MATCH / per_launch_s / 1e12
             screen_path = not (args.exact_only or not cnt["screen_ranges"])
             traffic = None
-            ncu_json = os.path.join(ROOT, "profiles", "r1_screen_ncu.json")
-            if screen_path and os.path.exists(ncu_json):   # dram bytes per launch from the committed ncu --set full capture
-                traffic = json.load(open(ncu_json)).get("traffic_bytes_per_launch_avg")
+            for name in ("r2_screen_ncu.json", "r1_screen_ncu.json"):   # dram bytes per launch from the committed ncu --set full capture
+                ncu_json = os.path.join(ROOT, "profiles", name)
+                if screen_path and os.path.exists(ncu_json):
+                    traffic = json.load(open(ncu_json)).get("traffic_bytes_per_launch_avg")
+                    break
             roof = {"bound": "tensor", "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s",
                     "frac": achieved / pk["tflops"], "traffic": traffic,
-                    "algorithmic": "2*64 flop per candidate match (SURVEY 8(d)); the kernel issues K=80 MMAs, i.e. 1.25x that",
+                    "algorithmic": "2*64 flop per candidate match (SURVEY 8(d))",
                     "launches_per_step": kern_launches / args.steps,
                     "kernel": "bf_scan8_kernel (exact CUDA-core scan)" if args.exact_only or not cnt["screen_ranges"]
                     else "bf_screen_kernel (tcgen05 correlation GEMM + screen epilogue)",
                     "kernel_ms_per_launch": per_launch_s * 1e3, "kernel_share_of_step": kern_ms / total_ms,
                     "peak_source": pk["source"] + ", burst figure (sub-ms kernel timed alone with events)"}
+            if sustained:
+                sustained["tflops"] = sustained["matches_per_s"] / world * FLOP_PER_MATCH / 1e12
+                sustained["peak"] = pk["tflops_sustained"]
+                sustained["frac_of_sustained_peak"] = sustained["tflops"] / pk["tflops_sustained"]
+                sustained["note"] = "whole encode (all nine launches), per GPU, against the sustained bf16 figure"
         cpu = None
         if world == 1 and not args.no_cpu:
             from oracle import oracle as orc
@@ -407,12 +566,15 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "bundled image lena_512x512 (grayscale), rolled by 8*rank rows per rank",
-            "config": {"workload": "bruteforce-jit 512x512 r8/d16 stride1 8iso, one image per GPU",
+            "config": {"workload": WORKLOAD,
                        "l2": "256 MiB buffer rewritten between timed steps", "path": "exact-only" if args.exact_only else "screen+exact",
-                       "exchange": f"winner records all-gathered over NCCL every {G} images, inside the timed region" if world > 1 else "none (one GPU)",
+                       "exchange": (f"winner records (32 B per range) all-gathered over NCCL every {G} images in stream order, "
+                                    f"inside the timed region ({state['gathers']} gathers)") if world > 1 and not no_gather
+                       else "none (one GPU)" if world == 1 else "DISABLED (diagnostic)",
                        "parity": parity},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": H * W,
-                    "d2h_bytes_per_step": N_RANGES * (16 + 16 + 8)},
+            "e2e": {"value": e2e_value, "unit": UNIT,
+                    "h2d_bytes_per_step": H * W + e2e_xfer["h2d"] // max(args.steps, 1),
+                    "d2h_bytes_per_step": N_RANGES * (16 + 16 + 8) + e2e_xfer["d2h"] // max(args.steps, 1)},
             "gpu_launches": cnt["launches"], "gpu_launches_per_step": launches_per_step,
             "encodes_per_s": value / MATCHES_PER_IMAGE, "e2e_encodes_per_s": e2e_value / MATCHES_PER_IMAGE,
             "screen": {"ranges_screened": cnt["screen_ranges"], "ranges_rescanned": cnt["rescan_ranges"],
@@ -423,10 +585,14 @@ def run_ours(args):
             line["roofline"] = roof
         if cpu:
             line["cpu_baseline"] = cpu
+        if sustained:
+            line["sustained"] = sustained
+        if c4:
+            line["c4"] = c4
+        if c5:
+            line["c5"] = c5
         print(json.dumps(line), flush=True)
     if world > 1:
-        gq.put(None)
-        worker.join(timeout=5)
         dist.destroy_process_group()
 
 
@@ -438,6 +604,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--exact-only", action="store_true", help="skip the tensor-core screen (debug)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--sustain", type=float, default=2.0, help="seconds of back-to-back encodes for the sustained-clock key (0 = off)")
+    ap.add_argument("--c4-side", type=int, default=4096, help="side of the range-sharded synthetic image of configs[3] (0 = skip)")
+    ap.add_argument("--c5-images", type=int, default=8, help="1024x1024 RGB images per GPU for the configs[4] slice (0 = skip)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -73,6 +73,10 @@ def read_preamble(f: BinaryIO, bits: BitBuffer, magic: bytes, what: str):
     got_magic, max_scale, scale_bits, offset_bits, width, height, size = hs.unpack(raw)
     if got_magic != magic:
         raise Exception(f'Invalid file format: file is missing {what} magic')
+    if scale_bits > BitBuffer.MAX_BIT_WIDTH or offset_bits > BitBuffer.MAX_BIT_WIDTH:
+        # the header stores both as a byte; the reference's BitBuffer moves at most one 32-bit word per read
+        raise Exception(f'Invalid file format: {scale_bits}/{offset_bits}-bit scale/offset fields exceed the '
+                        f'{BitBuffer.MAX_BIT_WIDTH}-bit words of the bit buffer')
     info = EncodingInfo(scale_bits=scale_bits, offset_bits=offset_bits, max_scale=max_scale, img_width=width,
                         img_height=height)
     processor_id = bits.read(ENTROPY_PROCESSOR_ID_BITS)

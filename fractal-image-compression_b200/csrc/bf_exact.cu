@@ -87,17 +87,17 @@ __global__ void bf_stats_kernel(const uint16_t* __restrict__ P, int H, int W, ui
 // grid = (range groups, chunks).  Each thread walks lattice positions q = chunk*chunk_len + tid + k*256,
 // keeps the 64 D4 values of its position in registers and scores the CTA's BF_G ranges x 8 isometries.
 template <int MODE>
-__global__ void __launch_bounds__(BF_THREADS)
-bf_scan8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
-                const uint32_t* __restrict__ sq4, const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
-                const int32_t* __restrict__ range_list, int chunk_len, int n_chunks, BestRec* __restrict__ partial)
+__device__ __forceinline__ void bf_scan8_body(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
+                                              const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4,
+                                              const float* __restrict__ sdd, const BfGeom& g, int range_begin, int n_ranges,
+                                              const int32_t* __restrict__ range_list, int chunk_len, int n_chunks,
+                                              BestRec* __restrict__ partial, int grp, int chunk)
 {
     __shared__ __align__(16) float rv[BF_G][8][64];  // inverse-transformed range blocks
     __shared__ double r_sum[BF_G], r_sq[BF_G];
     __shared__ BestRec red[BF_G][BF_THREADS / 32];
 
     const int tid = threadIdx.x;
-    const int grp = blockIdx.x, chunk = blockIdx.y;
     const int rw = g.W / 8;
     const int NP = g.PW * (g.H - 16);
 
@@ -230,19 +230,38 @@ bf_scan8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
     }
 }
 
+template <int MODE>
+__global__ void __launch_bounds__(BF_THREADS)
+bf_scan8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
+                const uint32_t* __restrict__ sq4, const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
+                const int32_t* __restrict__ range_list, int chunk_len, int n_chunks, BestRec* __restrict__ partial)
+{
+    bf_scan8_body<MODE>(img, P, sd4, sq4, sdd, g, range_begin, n_ranges, range_list, chunk_len, n_chunks, partial,
+                        blockIdx.x, blockIdx.y);
+}
+
+// L2 load of a partial winner: the records may have been written by other SMs of the same launch (bf_scan8_dyn_kernel)
+__device__ __forceinline__ BestRec ld_rec_cg(const BestRec* p)
+{
+    const ulonglong2 v = __ldcg(reinterpret_cast<const ulonglong2*>(p));
+    BestRec b;
+    b.R = __longlong_as_double((long long)v.x);
+    b.seq = v.y;
+    return b;
+}
+
 // One thread per range: reduce the chunk winners, decode the scan index, re-score the winner for (s, o).
 template <int MODE>
-__global__ void bf_finalize8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
-                                    const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4,
-                                    const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
-                                    const int32_t* __restrict__ range_list, int n_chunks, const BestRec* __restrict__ partial,
-                                    int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+__device__ __forceinline__ void bf_finalize8_slot(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
+                                                  const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4,
+                                                  const float* __restrict__ sdd, const BfGeom& g, int range_begin,
+                                                  const int32_t* __restrict__ range_list, int n_chunks,
+                                                  const BestRec* __restrict__ partial, int32_t* __restrict__ out_idx,
+                                                  double* __restrict__ out_so, double* __restrict__ out_R, int slot)
 {
-    int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_ranges) return;
-    BestRec b = partial[(size_t)slot * n_chunks];
+    BestRec b = ld_rec_cg(partial + (size_t)slot * n_chunks);
     for (int c = 1; c < n_chunks; ++c) {
-        BestRec o = partial[(size_t)slot * n_chunks + c];
+        BestRec o = ld_rec_cg(partial + (size_t)slot * n_chunks + c);
         if (fic_better(o.R, o.seq, b.R, b.seq)) b = o;
     }
     int ridx = range_list ? range_list[slot] : range_begin + slot;
@@ -291,6 +310,79 @@ __global__ void bf_finalize8_kernel(const uint8_t* __restrict__ img, const uint1
     out_so[2 * oslot] = sc.s;
     out_so[2 * oslot + 1] = sc.o;
     if (out_R) out_R[oslot] = sc.R;
+}
+
+template <int MODE>
+__global__ void bf_finalize8_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P,
+                                    const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4,
+                                    const float* __restrict__ sdd, BfGeom g, int range_begin, int n_ranges,
+                                    const int32_t* __restrict__ range_list, int n_chunks, const BestRec* __restrict__ partial,
+                                    int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+{
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_ranges) return;
+    bf_finalize8_slot<MODE>(img, P, sd4, sq4, sdd, g, range_begin, range_list, n_chunks, partial, out_idx, out_so, out_R, slot);
+}
+
+// ---- the scan with a range count that only the device knows ----------------------------------------------------
+// The tensor-core pipeline (bf_screen.cu) leaves the few ranges it cannot decide in a device-side list whose length
+// is ctrl[1].  Reading that length on the host would cost a stream synchronisation per encode, so this kernel is
+// launched unconditionally with a fixed grid: every CTA derives the (group, chunk) decomposition from the count
+// itself -- the formula of bf_exact_scan8 -- walks its share of it, and the CTA that delivers the last chunk of a
+// group reduces that group's winners and writes the records (what bf_finalize8_kernel does).  With an empty list the
+// launch costs a few microseconds.  Thread 0 of CTA 0 also folds the call's counters into the handle's device totals.
+//   done[group]: chunk arrival counters, zero on entry, set back to zero by the finalising CTA.
+//   totals[4] (u64): survivors rescored, ranges decided by the screen, ranges re-scanned, fault code.
+template <int MODE>
+__global__ void __launch_bounds__(BF_THREADS)
+bf_scan8_dyn_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, const uint32_t* __restrict__ sd4,
+                    const uint32_t* __restrict__ sq4, const float* __restrict__ sdd, BfGeom g, int range_begin,
+                    const int* __restrict__ ctrl, int n_total, const int32_t* __restrict__ range_list, int want_ctas,
+                    BestRec* __restrict__ partial, unsigned int* __restrict__ done, unsigned long long* __restrict__ totals,
+                    int32_t* __restrict__ out_idx, double* __restrict__ out_so, double* __restrict__ out_R)
+{
+    __shared__ int s_last;
+    const int n_ranges = ctrl[1];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long surv;
+        memcpy(&surv, ctrl + 8, sizeof(surv));
+        atomicAdd(&totals[0], surv);
+        atomicAdd(&totals[1], (unsigned long long)(n_total - n_ranges));
+        atomicAdd(&totals[2], (unsigned long long)n_ranges);
+        if (ctrl[2]) atomicMax(&totals[3], (unsigned long long)ctrl[2]);
+    }
+    if (n_ranges <= 0) return;
+    const long long nq = (long long)g.npi * g.npj;
+    const int groups = (n_ranges + BF_G - 1) / BF_G;
+    int n_chunks = 1, chunk_len = BF_THREADS;
+    if (nq > 0) {   // bf_exact_scan8's decomposition
+        n_chunks = (want_ctas + groups - 1) / groups;
+        const int max_chunks = (int)((nq + BF_THREADS * 4 - 1) / (BF_THREADS * 4));
+        if (n_chunks > max_chunks) n_chunks = max_chunks;
+        if (n_chunks < 1) n_chunks = 1;
+        chunk_len = (int)((nq + n_chunks - 1) / n_chunks);
+        chunk_len = (chunk_len + BF_THREADS - 1) / BF_THREADS * BF_THREADS;
+        n_chunks = (int)((nq + chunk_len - 1) / chunk_len);
+    }
+    const long long items = (long long)groups * n_chunks;
+    for (long long item = blockIdx.x; item < items; item += gridDim.x) {
+        const int grp = (int)(item / n_chunks), chunk = (int)(item - (long long)grp * n_chunks);
+        __syncthreads();   // the previous item's shared data is dead
+        bf_scan8_body<MODE>(img, P, sd4, sq4, sdd, g, range_begin, n_ranges, range_list, chunk_len, n_chunks, partial, grp, chunk);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();   // this CTA's partial records before its arrival
+            const unsigned int arrived = atomicAdd(&done[grp], 1u);
+            s_last = arrived + 1u == (unsigned)n_chunks;
+            if (s_last) { done[grp] = 0u; __threadfence(); }
+        }
+        __syncthreads();
+        if (s_last && threadIdx.x < BF_G) {
+            const int slot = grp * BF_G + threadIdx.x;
+            if (slot < n_ranges)
+                bf_finalize8_slot<MODE>(img, P, sd4, sq4, sdd, g, range_begin, range_list, n_chunks, partial, out_idx, out_so, out_R, slot);
+        }
+    }
 }
 
 // ---- generic range size: sequential replay straight from the image ----------------------------
@@ -470,6 +562,41 @@ int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, in
     return FIC_OK;
 }
 
+// The scan of the ranges listed in d_range_list[0 .. ctrl[1]) -- a count only the device knows (see
+// bf_scan8_dyn_kernel).  n_total = ranges of the whole call (for the counters).  No host synchronisation.
+int bf_exact_scan8_dyn(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_total,
+                       const int* d_ctrl, const int32_t* d_range_list, unsigned long long* d_totals, int32_t* d_idx,
+                       double* d_so, double* d_R, cudaStream_t st)
+{
+    BfGeom g;
+    g.H = H; g.W = W; g.si = 1; g.sj = 1; g.PW = W - 16; g.BW = W - 1;
+    g.npi = H - 16; g.npj = W - 16;
+    const int want = h->num_sms * 16;
+    // groups * n_chunks <= want + groups, eight ranges per group
+    FIC_TRY(h->bf_partial.reserve(((size_t)want + (size_t)n_total / BF_G + 2) * BF_G * sizeof(BestRec)));
+    const size_t done_bytes = ((size_t)n_total / BF_G + 2) * sizeof(unsigned int);
+    if (done_bytes > h->bf_done.cap) {
+        FIC_TRY(h->bf_done.reserve(done_bytes));
+        FIC_CUDA(cudaMemsetAsync(h->bf_done.p, 0, h->bf_done.cap, st));   // the kernel leaves the counters at zero
+    }
+    const size_t NP = (size_t)g.npi * g.npj;
+    const uint16_t* P = h->bf_boxsum.as<uint16_t>();
+    const uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    const uint32_t* sq4 = sd4 + NP;
+    const float* sdd = reinterpret_cast<const float*>(sq4 + NP);
+    const int grid = h->num_sms * 4;
+    if (mode == FIC_BF_MODE_JIT)
+        bf_scan8_dyn_kernel<FIC_BF_MODE_JIT><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(
+            d_img, P, sd4, sq4, sdd, g, range_begin, d_ctrl, n_total, d_range_list, want, h->bf_partial.as<BestRec>(),
+            h->bf_done.as<unsigned int>(), d_totals, d_idx, d_so, d_R);
+    else
+        bf_scan8_dyn_kernel<FIC_BF_MODE_NUMPY><<<grid, BF_THREADS, BF_SCAN_DYN_SMEM, st>>>(
+            d_img, P, sd4, sq4, sdd, g, range_begin, d_ctrl, n_total, d_range_list, want, h->bf_partial.as<BestRec>(),
+            h->bf_done.as<unsigned int>(), d_totals, d_idx, d_so, d_R);
+    FIC_CHECK_LAUNCH(h, "bf_scan8_dyn_kernel");
+    return FIC_OK;
+}
+
 int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
                      int range_begin, int n_ranges, int32_t* d_idx, double* d_so, double* d_R, cudaStream_t st)
 {
@@ -505,7 +632,8 @@ int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int rang
 //     call's leftovers are harmless.  But two calls that overlap in time on the same GPU (different streams or
 //     host threads) would overwrite each other's scratch: run them one after the other;
 //   * the first call on each device looks up the array's device address.  That lookup may initialise the CUDA
-//     context / load the module, so make the first call before starting any stream capture.
+//     context / load the module, so make the first call before starting any stream capture, and make it from one
+//     host thread: the per-device slot below is filled without a lock.
 #define FIC_STATIC_MAX_SIDE 256
 #define FIC_STATIC_BOX_BYTES 131072u                                   /* u16 255*255 rounded up   */
 #define FIC_STATIC_NP_MAX ((FIC_STATIC_MAX_SIDE - 16) * (FIC_STATIC_MAX_SIDE - 16))

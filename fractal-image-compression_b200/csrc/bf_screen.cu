@@ -8,8 +8,11 @@
 //     n*ab - sum(r)*sum(d) = (64*X - sum(r)*SD4)/4 = 16*u,        u := X - sum(r)*SD4/64 .
 // Centre both operands by integers: r' = r - m_r, D4' = D4 - m_c (m = round(mean)), rho = sum r', eps = sum D4':
 //     u = sum r'_k*D4'_k - rho*eps/64                              (exact identity)
-// which is one K=80 dot product of fp16-exact operands: 64 products of integers (|r'|<=255, |D4'|<=1020, every
-// partial sum < 2^24, exact in the fp32 accumulator) plus one extension column rho * (-eps/64).
+// The first term is one K=64 dot product of fp16-exact integer operands (|r'|<=255, |D4'|<=1020, every partial sum
+// < 2^24: exact in the fp32 accumulator); the second is a rank-1 term of magnitude at most 32*32/64 = 16 that the GEMM
+// does not compute: it is covered by the slack DELTA_U of the threshold (|u| >= |X'| - 16 with X' the accumulator).
+// (An earlier version carried it in a K=16 extension slab: 5 instead of 4 tcgen05.mma per tile, 160 instead of
+// 128 bytes per pool row, for a threshold that was 14 units of u tighter.)
 //
 // Bound.  For ANY (s,o) the exact-arithmetic collage error obeys R >= R_opt = (A_r - 64*u^2/den16)/64 with
 // A_r = sum r^2 - (sum r)^2/64, den16 = 64*sum(D4^2) - SD4^2 (integers).  The reference's R differs from exact
@@ -21,9 +24,9 @@
 //     u^2 * h_c^2 >= A_r - 64*UB_r,     h_c^2 = 64/den16 * (1 + 1e-3 * sum D4^2 / den16)          (tau_A)
 // For the (rare) ill-conditioned domains the constant guard is used:  u^2 * 64/den16 >= A_r - 64*(UB_r + 0.26)  (tau_B).
 // UB_r is the exact R of some candidate (any exactly scored candidate bounds the winner from above).
-// The epilogue evaluates  (|u| + DELTA)*h_c >= tau  as  |u| >= theta := tau/h_c - DELTA  (DELTA absorbs the accumulator's
-// rounding of the fractional extension term); theta is one FFMA per (thread, range, tile), the 8 isometry columns of a
-// range are max-reduced first, so the common case is ~5 instructions per 8 outputs.
+// The epilogue evaluates  (|X'| + DELTA)*h_c >= tau  as  |X'| >= theta := tau/h_c - DELTA  (DELTA = 16 covers the
+// rank-1 centring term); theta is one FFMA per (thread, range, tile), the 8 isometry columns of a range are
+// max-reduced first, so the common case is ~5 instructions per 8 outputs.
 //
 // Rounds: a seed round ranks a coarse lattice of candidates (~NP/100 positions) per range with the same GEMM and a
 // ranking epilogue; the best one and position 0 are scored exactly and give the first bounds.  Round 1 then screens a
@@ -33,8 +36,8 @@
 // exact scan; constant ranges are decided by the seed list (every candidate ties at R = 0, the first one wins).
 // The NumPy encoder's semantics (bf_encoder.py) go through the same screen: see bf_init_kernel.
 //
-// GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA, 5-stage ring), N = 256 columns = 32 ranges
-// x 8 isometries (resident in shared memory), K = 64 + 16.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
+// GEMM shape (per CTA): M = 128 candidates (TMEM lanes, streamed by TMA through a ring of stages), N = 256 columns = 32
+// ranges x 8 isometries (resident in shared memory), K = 64.  tcgen05.mma cta_group::1 kind::f16, fp32 accumulators in
 // TMEM, 2 accumulator stages x 256 columns = all 512 TMEM columns, so the MMA of tile t+1 overlaps the epilogue of
 // tile t.  Warp roles: warps 0..15 epilogue, warp 16 TMA producer, warp 17 MMA issuer + TMEM allocator (both run in
 // lock step with one elected lane issuing); epilogue in two groups of eight, one group per accumulator stage (two warps
@@ -43,9 +46,8 @@
 //
 // HBM/L2 layout written by bf_pool_kernel ("TMA-friendly domain-candidate pool"):
 //   poolA   fp16 [NP][64]  K-major rows (128 B) -> TMA box 64x128, SWIZZLE_128B
-//   poolAx  fp16 [NP][16]  extension columns (32 B rows), col 0 = -eps/64 -> TMA box 16x128, SWIZZLE_32B
 //   hk      float2 [NP]    (+-1/h_c, den16); a negative .x marks an ill-conditioned domain, .y only ranks seed candidates
-// and by bf_init_kernel:  rngB fp16 [Ncols][64], rngBx fp16 [Ncols][16] (col 0 = rho), column = slot*8 + isometry.
+// and by bf_init_kernel:  rngB fp16 [Ncols][64], column = slot*8 + isometry.
 #include <algorithm>
 #include <vector>
 #include <cuda.h>
@@ -55,39 +57,58 @@
 #include "fic_common.cuh"
 #include "scorer.cuh"
 
-int bf_exact_scan8(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int mode, int range_begin,
-                   int n_ranges, const int32_t* d_range_list, int32_t* d_idx, double* d_so, double* d_R,
-                   cudaStream_t st);
+int bf_exact_scan8_dyn(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_total,
+                       const int* d_ctrl, const int32_t* d_range_list, unsigned long long* d_totals, int32_t* d_idx,
+                       double* d_so, double* d_R, cudaStream_t st);
+
+// Measurement knobs (environment variables read per encode, kernel variants whose records are wrong on purpose) exist
+// only in builds made with `make TUNING=1` (-DFIC_TUNING); the shipped library ignores the environment.
+#ifdef FIC_TUNING
+static const char* tuning_env(const char* name) { return getenv(name); }
+#else
+static const char* tuning_env(const char*) { return nullptr; }
+#endif
 
 namespace {
 
 constexpr int BM = 128;      // candidates per tile
 constexpr int BN = 256;      // columns per unit (32 ranges x 8 isometries)
 constexpr int KMAIN = 64;
-constexpr int KEXT = 16;
-constexpr int STAGES = 5;
-constexpr int WARPS_PER_STAGE = 8;                    // epilogue warps per accumulator stage (two per TMEM lane quadrant)
+#ifndef FIC_SCREEN_STAGES
+#define FIC_SCREEN_STAGES 6
+#endif
+constexpr int STAGES = FIC_SCREEN_STAGES;
+// Epilogue organisation.  1: all sixteen epilogue warps work on every tile (64 columns each) and hand the accumulator
+// back as soon as their two TMEM loads have landed; 0: two groups of eight warps, one group per accumulator stage
+// (128 columns per warp, released after the fourth load).
+#ifndef FIC_EPI_ALL
+#define FIC_EPI_ALL 1
+#endif
+constexpr bool EPI_ALL = FIC_EPI_ALL != 0;
+constexpr int WARPS_PER_STAGE = 8;                    // EPI_ALL == 0: epilogue warps per accumulator stage (two per TMEM lane quadrant)
 constexpr int EPI_WARPS = 2 * WARPS_PER_STAGE;
+constexpr int RANGES_PER_WARP = EPI_ALL ? 8 : 16;     // ranges (groups of 8 columns) one epilogue warp looks at per tile
 // the scheduler favours high warp ids: the two single-thread roles sit ABOVE the epilogue warps so that the busy
 // epilogue can never delay a TMA issue or an MMA issue
 constexpr int TMA_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
 constexpr int SCREEN_THREADS = 64 + EPI_WARPS * 32;   // registers are allocated per four warps: 576 threads -> 96 each
 constexpr uint32_t A_MAIN_BYTES = BM * KMAIN * 2;   // 16384
-constexpr uint32_t A_EXT_BYTES = BM * KEXT * 2;     // 4096
 constexpr uint32_t B_MAIN_BYTES = BN * KMAIN * 2;   // 32768
-constexpr uint32_t B_EXT_BYTES = BN * KEXT * 2;     // 8192
 constexpr uint32_t OFF_B_MAIN = 0;
-constexpr uint32_t OFF_B_EXT = OFF_B_MAIN + B_MAIN_BYTES;
-constexpr uint32_t OFF_A_MAIN = OFF_B_EXT + B_EXT_BYTES;
-constexpr uint32_t OFF_A_EXT = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
-constexpr uint32_t OFF_BARS = OFF_A_EXT + STAGES * A_EXT_BYTES;
+constexpr uint32_t OFF_A_MAIN = OFF_B_MAIN + B_MAIN_BYTES;
+constexpr uint32_t OFF_BARS = OFF_A_MAIN + STAGES * A_MAIN_BYTES;
 constexpr uint32_t OFF_TAU = OFF_BARS + 256;                        // per epilogue warp: 16 x float2 thresholds
 constexpr uint32_t OFF_QUEUE = OFF_TAU + EPI_WARPS * 16 * 8;          // per epilogue warp: survivor queue
-constexpr uint32_t QUEUE_BYTES = (128 + 512) * 8;                    // sizeof(WarpQueue), checked below
+constexpr int QFLUSH = 128;                                          // a queue is flushed between tiles once it holds this many entries
+constexpr int QCAP = QFLUSH + RANGES_PER_WARP * 32;                  // ... and a tile adds at most one entry per (range, lane)
+constexpr uint32_t QUEUE_BYTES = QCAP * 8;                           // sizeof(WarpQueue), checked below
 constexpr uint32_t SCREEN_SMEM = OFF_QUEUE + EPI_WARPS * QUEUE_BYTES + 1024;  // + slack to align the base to 1024
+static_assert(SCREEN_SMEM <= 232448, "shared memory of the screen kernel exceeds the 227 KB a CTA can have");
+
+constexpr int BF_CTRL_TOTALS = 16;   // int index inside the control block where the four u64 totals start
 
 constexpr double GUARD_ILL = 0.26;   // constant guard (R units) for ill-conditioned domains: kappa_c <= 0.25
-constexpr float DELTA_U = 2.0f;      // bound on |u_tensorcore - u_exact| (fractional extension term, one rounding)
+constexpr float DELTA_U = 16.0f;     // |u - X'| = |rho*eps|/64 <= 32*32/64: the rank-1 centring term the GEMM leaves out
 
 // ---- PTX wrappers ----------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -282,10 +303,8 @@ __device__ __noinline__ void append_hits(uint32_t* __restrict__ cnt, uint32_t* _
 // Per-warp survivor queue in shared memory.  The fill level lives in a (warp-uniform) register and hits are placed
 // with a ballot + prefix count, so a hit costs one vote and one store -- no atomics, no divergent lanes.  The global
 // reservations (one atomicAdd per entry, a full round trip to L2) are issued 32 at a time when the queue is flushed
-// between tiles.  A tile can add at most 4 chunks x 4 ranges x 32 lanes = 512 entries per warp, and the queue is
-// flushed whenever a tile ends with QFLUSH or more entries, so QCAP = QFLUSH + 512 can never overflow.
-constexpr int QFLUSH = 128;
-constexpr int QCAP = QFLUSH + 512;
+// between tiles.  A tile can add at most RANGES_PER_WARP x 32 lanes entries per warp, and the queue is flushed
+// whenever a tile ends with QFLUSH or more entries, so QCAP can never overflow.
 struct WarpQueue {
     uint2 e[QCAP];   // x = (slot << 8) | isometry mask, y = candidate position
 };
@@ -294,7 +313,6 @@ static_assert(sizeof(WarpQueue) == QUEUE_BYTES, "QUEUE_BYTES must match WarpQueu
 __device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, int lane, uint32_t n)
 {
     __syncwarp();
-    for (int rep = 0; rep < (p.debug_mode == 5 ? 2 : 1); ++rep)   // timing experiment: 5 = every append twice
     for (uint32_t k = lane; k < n; k += 32) {
         const uint2 ent = q->e[k];
         append_hits(p.cnt, p.list, p.cap, (int)(ent.x >> 8), ent.y, ent.x & 0xffu);
@@ -380,8 +398,7 @@ __device__ __forceinline__ void screen_pair(const uint32_t (&va)[32], const uint
 // FIC_SCREEN_DEBUG (2: TMEM loads but no screening, 3: no epilogue work at all) -- their results are wrong on purpose.
 template <int MODE>
 __global__ void __launch_bounds__(SCREEN_THREADS, 1)
-bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapAx,
-                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapBx, ScreenParams p)
+bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, ScreenParams p)
 {
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -404,7 +421,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         mbar_init(b_full, 1);
         mbar_init(b_empty, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), WARPS_PER_STAGE); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), EPI_ALL ? EPI_WARPS : WARPS_PER_STAGE); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == MMA_WARP) {  // TMEM: all 512 columns (one CTA per SM by construction: > 113 KB of shared memory)
@@ -426,9 +443,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         while (span.next(grp, j0, j1)) {
             mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
             if (issuer) {
-                mbar_expect_tx(b_full, B_MAIN_BYTES + B_EXT_BYTES);
+                mbar_expect_tx(b_full, B_MAIN_BYTES);
                 tma_load_2d(base + OFF_B_MAIN, &mapB, b_full, 0, grp * BN);
-                tma_load_2d(base + OFF_B_EXT, &mapBx, b_full, 0, grp * BN);
             }
             bph ^= 1;
             // tile index without a division per tile (same walk as the epilogue's)
@@ -438,9 +454,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             for (int j = j0; j < j1; ++j) {
                 mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
                 if (issuer) {
-                    mbar_expect_tx(full_bar(s), A_MAIN_BYTES + A_EXT_BYTES);
+                    mbar_expect_tx(full_bar(s), A_MAIN_BYTES);
                     tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t_cur * BM);
-                    tma_load_2d(base + OFF_A_EXT + s * A_EXT_BYTES, &mapAx, full_bar(s), 0, t_cur * BM);
                 }
                 __syncwarp();
                 int step = 1;
@@ -458,9 +473,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         int s = 0, as = 0;
         uint32_t ph = 0, aph = 0, bph = 0;
         const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
-        const uint64_t bxdesc = make_desc(base + OFF_B_EXT, 256, 6);
         const uint64_t adesc0 = make_desc(base + OFF_A_MAIN, 1024, 2);
-        const uint64_t axdesc0 = make_desc(base + OFF_A_EXT, 256, 6);
         const bool issuer = elect_one();
         Span span(p, n_groups);
         int grp, j0, j1;
@@ -469,7 +482,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             bph ^= 1;
             for (int j = j0; j < j1; ++j) {
                 const uint64_t adesc = adesc0 + (uint64_t)(s * (A_MAIN_BYTES >> 4));
-                const uint64_t axdesc = axdesc0 + (uint64_t)(s * (A_EXT_BYTES >> 4));
                 const uint32_t d_tmem = tmem_base + (uint32_t)as * BN;
                 mbar_wait(tempty_bar(as), aph ^ 1, p.err_flag, 4);  // epilogue drained this accumulator stage
                 mbar_wait(full_bar(s), ph, p.err_flag, 5);          // TMA bytes have landed
@@ -478,7 +490,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
                     for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
-                    umma_f16(d_tmem, axdesc, bxdesc, IDESC, 1);
                     tcgen05_commit(empty_bar(s));   // frees the A stage once the MMAs above have completed
                     tcgen05_commit(tfull_bar(as));  // accumulator ready for the epilogue
                 }
@@ -489,6 +500,151 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             if (issuer) tcgen05_commit(b_empty);
             __syncwarp();
         }
+    } else if (warp < EPI_WARPS && EPI_ALL) {
+        // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
+        // All sixteen warps work on every tile: four warps share each TMEM lane quadrant and take 64 columns (8 ranges)
+        // each.  A warp's two 32-column loads are all it needs from the accumulator, so the stage goes back to the MMA
+        // issuer as soon as they have landed -- the screening runs on registers while the next tile's MMAs already write
+        // the same stage.  TMEM delivers 64 B per cycle and scheduler; with four warps per scheduler queueing their loads
+        // the read port stays busy while other warps screen.
+        const int quad = warp & 3;                           // TMEM lane quadrant this warp may touch
+        const int part = warp >> 2;                          // which 64-column quarter of the 256 columns
+        const int lane_off = quad * 32 + lane;
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(part * 64);
+        int n = 0;  // tiles seen so far by this CTA (all units): tile n uses accumulator stage n & 1, phase (n >> 1) & 1
+        float* my_tau = reinterpret_cast<float*>(gbase + OFF_TAU) + warp * 32;   // [0,8) = tau_A, [8,16) = tau_B
+        WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + warp;
+        uint32_t qn = 0;   // queue fill, warp-uniform
+        Span span(p, n_groups);
+        int grp, j0, j1;
+        while (span.next(grp, j0, j1)) {
+            if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
+            __syncwarp();
+            if (lane < 8) {
+                const float2 tt = p.tau[grp * 32 + part * 8 + lane];
+                my_tau[lane] = tt.x;
+                my_tau[8 + lane] = tt.y;
+            }
+            // this warp's TMEM address: ptxas would otherwise rebuild it from %tid.x (two ~50-cycle S2R) between the wait on
+            // the accumulator and the first load of every tile; a value that comes out of a volatile load stays in a register
+            if (lane == 0) reinterpret_cast<uint32_t*>(my_tau)[16] = taddr0;
+            __syncwarp();
+            const int slot0 = grp * 32 + part * 8;
+            int j = j0;
+            // The loop carries this lane's candidate index (tile * 128 + quadrant * 32 + lane) rather than the tile:
+            // t = (j + j / (r_prev - 1) + 1) * m_cur is advanced without a division per tile.
+            int cand = tile_of(p, j) * BM + lane_off;
+            const int r1 = p.r_prev > 0 ? p.r_prev - 1 : 0x7fffffff;
+            int rem = p.r_prev > 0 ? j % r1 : 0;
+            const float hk_pad = __int_as_float(0x7f800000);   // padding rows of the last tile: threshold never met
+            float hq_next = cand < p.NP ? p.hk[cand].x : hk_pad;
+            float4 tq0, tq1;
+            {
+                const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 8 : 0));
+                tq0 = tau4[0]; tq1 = tau4[1];
+            }
+            float seed_gain[8];   // seed mode only: this lane's best candidate per range over the unit's tiles
+            int seed_cand[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { seed_gain[i] = 0.f; seed_cand[i] = 0; }
+            for (; j < j1; ++j, ++n) {
+                const int my_cand = cand;
+                {
+                    int wraps = 0;
+                    if (++rem >= r1) { rem = 0; wraps = 1; }
+                    cand += (1 + wraps) * p.m_cur * BM;
+                }
+                const float hq = hq_next;
+                hq_next = (j + 1 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+                const uint32_t stage = (uint32_t)n & 1u, aph = ((uint32_t)n >> 1) & 1u;
+                uint32_t taddr_pinned;
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(taddr_pinned) : "r"(smem_u32(my_tau + 16)));
+                const uint32_t taddr = taddr_pinned + stage * BN;
+                const uint32_t my_tfull = tfull_bar(stage), my_tempty = tempty_bar(stage);
+                uint32_t va[32], vb[32];
+                if (MODE == 5) {
+                    // seed mode: no thresholds yet.  Rank the (few) candidates of the seed pool by the collage-error
+                    // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
+                    // one per range; it is scored exactly afterwards and provides the first upper bound.
+                    const float den = my_cand < p.NP ? p.hk[my_cand].y : 0.f;
+                    const float inv64 = den > 0.f ? 64.f / den : 0.f, den1024 = den * (1.0f / 1024.0f);
+                    auto rank4 = [&](const uint32_t (&v)[32], int c4) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float m = fabsf(__uint_as_float(v[g * 8]));
+#pragma unroll
+                            for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v[g * 8 + i])));
+                            const float gain = 256.f * m <= den ? m * m * inv64 : 0.5f * m - den1024;   // den == 0: m == 0
+                            if (gain > seed_gain[c4 * 4 + g]) { seed_gain[c4 * 4 + g] = gain; seed_cand[c4 * 4 + g] = my_cand; }
+                        }
+                    };
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    tmem_ld32(taddr, va);
+                    tmem_ld32(taddr + 32, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(my_tempty);
+                    rank4(va, 0);
+                    rank4(vb, 1);
+                    continue;
+                }
+                const float qx = fabsf(hq);
+                // thresholds on |X'| for the 8 ranges: theta = tau/h_c - DELTA, tau picked by the candidate's class
+                float theta[8];
+                theta[0] = fmaf(tq0.x, qx, -DELTA_U); theta[1] = fmaf(tq0.y, qx, -DELTA_U);
+                theta[2] = fmaf(tq0.z, qx, -DELTA_U); theta[3] = fmaf(tq0.w, qx, -DELTA_U);
+                theta[4] = fmaf(tq1.x, qx, -DELTA_U); theta[5] = fmaf(tq1.y, qx, -DELTA_U);
+                theta[6] = fmaf(tq1.z, qx, -DELTA_U); theta[7] = fmaf(tq1.w, qx, -DELTA_U);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) asm volatile("" : "+f"(theta[i]));   // materialise before the wait
+                mbar_wait(my_tfull, aph, p.err_flag, 6);
+                tcgen05_fence_after();
+                if (MODE == 3) {
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(my_tempty);
+                    continue;
+                }
+                tmem_ld32(taddr, va);
+                tmem_ld32(taddr + 32, vb);
+                tmem_ld_wait(va);
+                tmem_ld_wait(vb);
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(my_tempty);
+                if (MODE == 1) {
+                    if (grp == 0) {
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) {
+                            p.dump[(size_t)my_cand * BN + part * 64 + q] = __uint_as_float(va[q]);
+                            p.dump[(size_t)my_cand * BN + part * 64 + 32 + q] = __uint_as_float(vb[q]);
+                        }
+                    }
+                } else if (MODE == 0 || MODE == 4) {
+                    screen_pair<MODE == 0>(va, vb, theta, p, slot0, my_cand, queue, qn, lane);
+                } else if (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u) {
+                    p.cnt[0] = 1;
+                }
+                {   // next tile's tau; harmless after the last tile
+                    const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 8 : 0));
+                    tq0 = tau4[0]; tq1 = tau4[1];
+                }
+                if (MODE == 0 && qn >= QFLUSH) { queue_flush(queue, p, lane, qn); qn = 0; }
+            }
+            if (MODE == 5) {   // merge the lanes' seed candidates of this unit: warp maximum, then one atomic per range
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const uint32_t bits = seed_gain[i] > 0.f ? __float_as_uint(seed_gain[i]) : 0u;
+                    const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
+                    if (wmax != 0u && bits == wmax)   // ties (rare): every tied lane offers its candidate, the smaller index wins
+                        atomicMax(&p.seed_best[slot0 + i], ((unsigned long long)bits << 32) | (0xffffffffu - (uint32_t)seed_cand[i]));
+                }
+            }
+        }
+        if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
     } else if (warp < EPI_WARPS) {
         // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
         // Two warp groups of WARPS_PER_STAGE warps; group g owns accumulator stage g, i.e. every second tile of the CTA's
@@ -669,7 +825,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
         }
         if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
-    }
+        }
     tcgen05_fence_before();
     __syncthreads();
     if (warp == MMA_WARP) {
@@ -681,32 +837,45 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 // ---- pool kernel: 2x pooling + centring + statistics, one thread per stride-1 position ------------------------
 // Also the per-position statistics of the exact scorer (the same values bf_stats_kernel of bf_exact.cu produces: this
 // path skips that launch): sd4 = sum D4, sq4 = sum D4^2, sdd[t] = float32 sequential sum of d^2 in the order of isometry t.
-__global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
-                               __half* __restrict__ poolAx, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
-                               uint32_t* __restrict__ sq4, float* __restrict__ sdd, int seed_S, int seed_gx, int n_seed,
-                               int n_seed_pad, __half* __restrict__ seedA, __half* __restrict__ seedAx,
-                               float2* __restrict__ seedhk)
+// HBM-bound: 176 bytes written per position (128 B pool row, 8 B hk, 8 B integer sums, 32 B float sums) against 2 bytes of
+// box sums read.  A CTA covers POOL_TILE consecutive positions of one lattice row: the eight box-sum rows it needs are
+// staged in shared memory once (each value is used by up to eight positions), and the pool rows -- 128 B per thread,
+// which would leave every store instruction touching 32 different lines -- go through a swizzled shared-memory tile and
+// leave the SM as one contiguous 16 KB block, 512 B per warp instruction.
+constexpr int POOL_TILE = 128;
+constexpr int POOL_SP_W = POOL_TILE + 14;      // box-sum columns a tile of positions touches
+
+__global__ void __launch_bounds__(POOL_TILE)
+bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA, float2* __restrict__ hk,
+               uint32_t* __restrict__ sd4, uint32_t* __restrict__ sq4, float* __restrict__ sdd, int seed_S, int seed_gx,
+               int n_seed, int n_seed_pad, __half* __restrict__ seedA, float2* __restrict__ seedhk)
 {
+    __shared__ uint16_t sP[8][POOL_SP_W + 2];
+    __shared__ __align__(16) uint4 sRow[POOL_TILE * 8];     // 128 pool rows of 8 x 16 B, chunk q of row t at q ^ (t & 7)
     const int PW = W - 16, PH = H - 16, BW = W - 1;
     const int NP = PW * PH;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= NP) return;
-    const int di = p / PW, dj = p - di * PW;
+    const int tid = threadIdx.x;
+    const int di = blockIdx.y, dj0 = blockIdx.x * POOL_TILE, dj = dj0 + tid;
+    const bool live = dj < PW;
+    const int p = di * PW + dj;
+    for (int e = tid; e < 8 * POOL_SP_W; e += POOL_TILE) {
+        const int a = e / POOL_SP_W, c = e - a * POOL_SP_W, x = dj0 + c;
+        sP[a][c] = x < BW ? P[(size_t)(di + 2 * a) * BW + x] : (uint16_t)0;
+    }
     // seed pool: the lattice nodes (every seed_S-th row and column) get a second copy in a small pool of their own; seed
     // candidate k sits at node (k / gx, k % gx); rows n_seed .. n_seed_pad are padding (zero rows, den16 = 0)
     int seed_k = -1;
     if (seedA) {
-        if (di % seed_S == 0 && dj % seed_S == 0) seed_k = (di / seed_S) * seed_gx + dj / seed_S;
-        if (p < n_seed_pad - n_seed) {
-            uint4* za = reinterpret_cast<uint4*>(seedA + (size_t)(n_seed + p) * 64);
-            uint4* zx = reinterpret_cast<uint4*>(seedAx + (size_t)(n_seed + p) * 16);
+        if (live && di % seed_S == 0 && dj % seed_S == 0) seed_k = (di / seed_S) * seed_gx + dj / seed_S;
+        const int lin = (blockIdx.y * gridDim.x + blockIdx.x) * POOL_TILE + tid;
+        if (lin < n_seed_pad - n_seed) {
+            uint4* za = reinterpret_cast<uint4*>(seedA + (size_t)(n_seed + lin) * 64);
 #pragma unroll
             for (int q = 0; q < 8; ++q) za[q] = make_uint4(0u, 0u, 0u, 0u);
-            zx[0] = make_uint4(0u, 0u, 0u, 0u);
-            zx[1] = make_uint4(0u, 0u, 0u, 0u);
-            seedhk[n_seed + p] = make_float2(__int_as_float(0x7f800000), 0.f);
+            seedhk[n_seed + lin] = make_float2(__int_as_float(0x7f800000), 0.f);
         }
     }
+    __syncthreads();
     int v[64];
     int s = 0;
     long long s2 = 0;
@@ -714,14 +883,12 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
     for (int a = 0; a < 8; ++a)
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
-            int x = P[(size_t)(di + 2 * a) * BW + dj + 2 * b];
+            int x = sP[a][tid + 2 * b];
             v[a * 8 + b] = x;
             s += x;
             s2 += x * x;
         }
-    const int m = (s + 32) >> 6;  // round(SD4 / 64)
-    const int eps = s - 64 * m;   // in [-32, 31]
-    uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)p * 64);
+    const int m = (s + 32) >> 6;  // round(SD4 / 64); eps = s - 64 m in [-32, 31] is what DELTA_U covers
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         __half2 h0 = __halves2half2(__int2half_rn(v[8 * q + 0] - m), __int2half_rn(v[8 * q + 1] - m));
@@ -733,19 +900,20 @@ __global__ void bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __h
         o.y = *reinterpret_cast<uint32_t*>(&h1);
         o.z = *reinterpret_cast<uint32_t*>(&h2);
         o.w = *reinterpret_cast<uint32_t*>(&h3);
-        dst[q] = o;
+        sRow[tid * 8 + (q ^ (tid & 7))] = o;
         if (seed_k >= 0) reinterpret_cast<uint4*>(seedA + (size_t)seed_k * 64)[q] = o;
     }
-    uint4* dx = reinterpret_cast<uint4*>(poolAx + (size_t)p * 16);
-    __half2 e0 = __halves2half2(__float2half_rn(-(float)eps * 0.015625f), __float2half_rn(0.f));  // exact: |eps|/64 <= 0.5, 6 bits
-    uint4 ox = make_uint4(*reinterpret_cast<uint32_t*>(&e0), 0u, 0u, 0u);
-    dx[0] = ox;
-    dx[1] = make_uint4(0u, 0u, 0u, 0u);
-    if (seed_k >= 0) {
-        uint4* sx = reinterpret_cast<uint4*>(seedAx + (size_t)seed_k * 16);
-        sx[0] = ox;
-        sx[1] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    {   // the tile's rows are contiguous in the pool: positions di*PW + dj0 .. + n_live - 1
+        const int n_live = min(POOL_TILE, PW - dj0);
+        uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)(di * PW + dj0) * 64);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int e = k * POOL_TILE + tid, r = e >> 3, c = e & 7;
+            if (r < n_live) dst[e] = sRow[r * 8 + (c ^ (r & 7))];
+        }
     }
+    if (!live) return;
     const long long den16 = 64ll * s2 - (long long)s * s;  // >= 0, exact
     // q_c = 1/h_c, rounded DOWN a little so that theta = tau*q - DELTA never over-estimates; +inf for a constant domain
     // (den16 == 0: u == 0 exactly, s_ref == 0, R_ref == A_r/64 without noise -> it can never beat tau_A > 0)
@@ -807,7 +975,7 @@ struct RangeState {
 __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode, int range_begin, int n_ranges,
                                RangeState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
                                unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
-                               __half* __restrict__ rngB, __half* __restrict__ rngBx)
+                               __half* __restrict__ rngB)
 {
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (slot >= tau_pad) return;
@@ -816,7 +984,6 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
         for (int t = 0; t < 8; ++t) {
             rngB[((size_t)slot * 8 + t) * 64 + lane] = __float2half_rn(0.f);
             rngB[((size_t)slot * 8 + t) * 64 + 32 + lane] = __float2half_rn(0.f);
-            if (lane < 16) rngBx[((size_t)slot * 8 + t) * 16 + lane] = __float2half_rn(0.f);
         }
     }
     if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
@@ -837,10 +1004,10 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
         qw += __shfl_xor_sync(0xffffffffu, qw, off);
     }
     {
-        // range operand (rngB fp16 [cols][64], rngBx [cols][16], column = slot * 8 + isometry): eight inverse-transformed
-        // copies of the range centred by the integer m = round(mean); extension column 0 carries rho = sum - 64 m.
+        // range operand (rngB fp16 [cols][64], column = slot * 8 + isometry): eight inverse-transformed copies of the
+        // range centred by the integer m = round(mean) (rho = sum - 64 m in [-32, 31] is what DELTA_U covers).
         // Entry k = (sa,sb) of column t holds r'[i][j] with (sa,sb) = iso_t(i,j): invert fic_iso_bf.
-        const int m = ((int)sm + 32) >> 6, rho = (int)sm - 64 * m;
+        const int m = ((int)sm + 32) >> 6;
 #pragma unroll
         for (int t = 0; t < 8; ++t) {
 #pragma unroll
@@ -856,7 +1023,6 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
                 }
                 rngB[((size_t)slot * 8 + t) * 64 + k] = __int2half_rn((int)img[(size_t)(ri + i) * W + rj + j] - m);
             }
-            if (lane < 16) rngBx[((size_t)slot * 8 + t) * 16 + lane] = lane == 0 ? __int2half_rn(rho) : __float2half_rn(0.f);
         }
     }
     if (lane == 0) {
@@ -1169,20 +1335,22 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
 
     FIC_TRY(h->bf_pool.reserve((size_t)NP * 64 * 2 + 256));
-    FIC_TRY(h->bf_poolx.reserve((size_t)NP * 16 * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
-    FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 80 * 2 + 256));
+    FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * 64 * 2 + 256));
     FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * (2 * sizeof(int32_t) + sizeof(uint2) + sizeof(RangeState)) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
-    FIC_TRY(h->bf_ctrl.reserve(256));
+    if (!h->bf_ctrl.p) {   // control block of the call + the totals, which start at zero and live as long as the handle
+        FIC_TRY(h->bf_ctrl.reserve(256));
+        FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
+    }
     // seed lattice: about NP/50 positions (at least 256, at most 8192), a whole number of candidate tiles
     int seed_S, seed_gx, n_seed, n_seed_pad;
     {
         double want = (double)NP / 50.0;       // same-box sweeps on lena 512x512: 5 000 positions beat 2 500 and 7 500
         if (want < 256.0) want = 256.0;
         if (want > 8192.0) want = 8192.0;
-        if (const char* e = getenv("FIC_SEED_POSITIONS")) want = atof(e) > 1.0 ? atof(e) : want;  // tuning knob
+        if (const char* e = tuning_env("FIC_SEED_POSITIONS")) want = atof(e) > 1.0 ? atof(e) : want;  // tuning knob
         seed_S = (int)floor(sqrt((double)NP / want) + 0.5);
         if (seed_S < 1) seed_S = 1;
         seed_gx = cdiv(PW, seed_S);
@@ -1191,15 +1359,12 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     }
     const size_t off_seedhk = ((size_t)tau_pad * 8 + 255) & ~(size_t)255;
     const size_t off_seedA = (off_seedhk + (size_t)n_seed_pad * 8 + 255) & ~(size_t)255;
-    const size_t off_seedAx = off_seedA + (size_t)n_seed_pad * 128;
-    FIC_TRY(h->bf_best.reserve(off_seedAx + (size_t)n_seed_pad * 32 + 256));
+    FIC_TRY(h->bf_best.reserve(off_seedA + (size_t)n_seed_pad * 128 + 256));
     FIC_TRY(h->pin_a.reserve(256));
 
     __half* poolA = h->bf_pool.as<__half>();
-    __half* poolAx = h->bf_poolx.as<__half>();
     float2* hk = h->bf_cand.as<float2>();
     __half* rngB = h->bf_A.as<__half>();
-    __half* rngBx = rngB + (size_t)n_cols_pad * 64;
     RangeState* state = h->bf_thr.as<RangeState>();                                   // 8-byte aligned members first
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
     int32_t* fallback = reinterpret_cast<int32_t*>(tau + tau_pad);
@@ -1210,34 +1375,32 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     unsigned long long* seed_best = reinterpret_cast<unsigned long long*>(seed_raw);
     float2* seedhk = reinterpret_cast<float2*>(seed_raw + off_seedhk);
     __half* seedA = reinterpret_cast<__half*>(seed_raw + off_seedA);
-    __half* seedAx = reinterpret_cast<__half*>(seed_raw + off_seedAx);
 
     // 1. pool (independent of the ranges)
-    bf_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, poolA, poolAx, hk, sd4, sd4 + NP, sdd, seed_S, seed_gx, n_seed, n_seed_pad,
-                                                  probe ? nullptr : seedA, seedAx, seedhk);
+    bf_pool_kernel<<<dim3(cdiv(PW, POOL_TILE), PH), POOL_TILE, 0, st>>>(P, H, W, poolA, hk, sd4, sd4 + NP, sdd, seed_S, seed_gx, n_seed,
+                                                                        n_seed_pad, probe ? nullptr : seedA, seedhk);
     FIC_CHECK_LAUNCH(h, "bf_pool_kernel");
 
     // 2. range states and the range operand: all eligible in natural order, nothing known yet (also clears the control block and the lists;
     //    the probe keeps these thresholds: nothing ever passes)
-    bf_init_kernel<<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad, rngB, rngBx);
+    bf_init_kernel<<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad, rngB);
     FIC_CHECK_LAUNCH(h, "bf_init_kernel");
 
     // 4. the screen, in two rounds
-    CUtensorMap mapA, mapAx, mapB, mapBx;
+    CUtensorMap mapA, mapB;
     FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
-    FIC_TRY(make_map(&mapAx, poolAx, (uint64_t)NP, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
     FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B));
-    FIC_TRY(make_map(&mapBx, rngBx, (uint64_t)n_cols_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B));
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!h->screen_attr_ready) {   // the opt-in is per device: kept in the handle, set with the handle's device current
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+#ifdef FIC_TUNING
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+#endif
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RESCORE_SMEM));
-        attr_set = true;
+        h->screen_attr_ready = true;
     }
     ScreenParams sp;
     sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
@@ -1245,28 +1408,27 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     sp.seed_best = nullptr;
     sp.err_flag = ctrl + 2;
     {
-        const char* dbg = getenv("FIC_SCREEN_DEBUG");  // kernel timing experiments only; records are wrong when set
+        const char* dbg = tuning_env("FIC_SCREEN_DEBUG");  // kernel timing experiments only; records are wrong when set
         sp.debug_mode = dbg ? atoi(dbg) : 0;
     }
     // 4a. seed round: the GEMM ranks the lattice candidates per range (no thresholds exist yet), the best one and
     // position 0 are scored exactly and give every range its first upper bound
     if (!probe) {
-        CUtensorMap mapS, mapSx;
+        CUtensorMap mapS;
         FIC_TRY(make_map(&mapS, seedA, (uint64_t)n_seed_pad, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B));
-        FIC_TRY(make_map(&mapSx, seedAx, (uint64_t)n_seed_pad, 16, BM, CU_TENSOR_MAP_SWIZZLE_32B));
         ScreenParams ss = sp;
         ss.hk = seedhk; ss.NP = n_seed; ss.n_tiles = n_seed_pad / BM; ss.m_cur = 1; ss.r_prev = 0;
         ss.n_round_tiles = ss.n_tiles; ss.window_tiles = ss.n_tiles; ss.seed_best = seed_best;
         {
             ProfScope prof(h, st);
-            bf_screen_kernel<5><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapSx, mapB, mapBx, ss);
+            bf_screen_kernel<5><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapB, ss);
         }
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(seed)");
         bf_rescore_kernel<<<cdiv(n_ranges, RESCORE_WARPS), RESCORE_WARPS * 32, RESCORE_SMEM, st>>>(d_img, poolA, sd4, sdd, H, W, range_begin, state, ctrl, cnt, list, cap, fallback, tau, 0, mode,
                                                     d_idx, d_so, d_R, seed_best, seed_S, seed_gx);
         FIC_CHECK_LAUNCH(h, "bf_rescore_kernel(seed)");
     }
-    const bool prof_rescore = getenv("FIC_PROFILE_RESCORE") != nullptr;   // measurement knob: time the rescoring kernels instead
+    const bool prof_rescore = tuning_env("FIC_PROFILE_RESCORE") != nullptr;   // measurement knob: time the rescoring kernels instead
     // Round plan: nested strides m_1 > m_2 > ... > 1 over the candidate tiles.  A round's survivor count per range is
     // about (fraction screened now) / (fraction scored exactly before), so each round may look at ~128x more candidates
     // than everything before it; the first one is sized against the pre-scan sample.
@@ -1276,7 +1438,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     } else {
         double f_prev = (double)n_seed / (double)NP;
         int growth = 16;
-        if (const char* e = getenv("FIC_ROUND_GROWTH")) growth = atoi(e) >= 2 ? atoi(e) : growth;  // tuning knob
+        if (const char* e = tuning_env("FIC_ROUND_GROWTH")) growth = atoi(e) >= 2 ? atoi(e) : growth;  // tuning knob
         int m = 1;
         while (1.0 / m > (double)growth * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
         for (;;) {
@@ -1285,7 +1447,7 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
             m = m / growth > 1 ? m / growth : 1;
         }
     }
-    sp.window_tiles = (64 << 20) / (BM * (KMAIN + KEXT) * 2);   // 64 MiB of pool per window: stays in the 126 MB L2
+    sp.window_tiles = (64 << 20) / (BM * KMAIN * 2);   // 64 MiB of pool per window: stays in the 126 MB L2
     for (size_t r = 0; r < strides.size(); ++r) {
         sp.m_cur = strides[r];
         sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
@@ -1294,17 +1456,19 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
         {
             h->prof_suppress = prof_rescore;
             ProfScope prof(h, st);
-            if (probe) bf_screen_kernel<1><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
-            else if (sp.debug_mode == 1) bf_screen_kernel<2><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
-            else if (sp.debug_mode == 2) bf_screen_kernel<3><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
-            else if (sp.debug_mode == 3) bf_screen_kernel<4><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
-            else bf_screen_kernel<0><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapAx, mapB, mapBx, sp);
+            if (probe) bf_screen_kernel<1><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+#ifdef FIC_TUNING
+            else if (sp.debug_mode == 1) bf_screen_kernel<2><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+            else if (sp.debug_mode == 2) bf_screen_kernel<3><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+            else if (sp.debug_mode == 3) bf_screen_kernel<4><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+#endif
+            else bf_screen_kernel<0><<<grid, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
         }
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel");
         if (probe) return FIC_OK;
         // 5. exact rescoring of this round's survivors, merged into the range states
         const int emit = r + 1 == strides.size();
-        if (getenv("FIC_DBG_LISTS")) {   // measurement knob: survivor list lengths before this rescoring
+        if (tuning_env("FIC_DBG_LISTS")) {   // measurement knob: survivor list lengths before this rescoring
             std::vector<uint32_t> hc_(n_ranges);
             cudaStreamSynchronize(st);
             cudaMemcpy(hc_.data(), cnt, (size_t)n_ranges * 4, cudaMemcpyDeviceToHost);
@@ -1322,8 +1486,22 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     }
     h->prof_suppress = false;
 
-    // 6. whatever the screen could not decide goes through the exact scan
-    if (h->eager.armed) {   // host-buffer call: the records ride in front of the synchronisation below
+    // 6. whatever the screen could not decide goes through the exact scan.  The number of such ranges is known to the
+    // device only (ctrl[1]); the scan is launched unconditionally and sizes itself (bf_scan8_dyn_kernel), so a call with
+    // device pointers returns without waiting for the GPU and the next call's launches queue up behind this one's.  The
+    // counters are folded into device-side totals by the same kernel (fic_get_counters fetches them).
+    unsigned long long* totals = reinterpret_cast<unsigned long long*>(ctrl + BF_CTRL_TOTALS);
+    h->bf_totals_live = true;
+    if (!(flags & FIC_BF_NO_FALLBACK)) {
+        h->prof_suppress = true;
+        int rc_fb = bf_exact_scan8_dyn(h, d_img, H, W, mode, range_begin, n_ranges, ctrl, fallback, totals, d_idx, d_so, d_R, st);
+        h->prof_suppress = false;
+        FIC_TRY(rc_fb);
+    }
+    if (!h->eager.armed && !(flags & FIC_BF_NO_FALLBACK)) return FIC_OK;
+    // Host-buffer call (the records go to pinned memory in front of the one wait the call needs anyway), or the testing
+    // flag that wants to hear about undecided ranges.
+    if (h->eager.armed) {
         for (int k = 0; k < 3; ++k)
             if (h->eager.bytes[k])
                 FIC_CUDA(cudaMemcpyAsync(h->pin_out.as<char>() + h->eager.at[k], h->eager.src[k], h->eager.bytes[k],
@@ -1335,19 +1513,29 @@ int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, i
     FIC_TRY(fic_sync(h, st));
     h->counters[CNT_D2H] += 64;
     if (hc[2] != 0) { fic_set_error("bf_screen_kernel: pipeline wait %d timed out", hc[2]); return FIC_ECUDA; }
-    const int n_fb = hc[1];
-    unsigned long long st_total;
-    memcpy(&st_total, hc + 8, sizeof(st_total));
-    h->counters[CNT_SURVIVORS] += (int64_t)st_total;
-    h->counters[CNT_SCREEN_RANGES] += n_ranges - n_fb;
-    h->counters[CNT_RESCAN_RANGES] += n_fb;
-    if (n_fb > 0) {
-        h->eager.done = false;   // the exact scan below rewrites some records: the caller copies again
-        if (flags & FIC_BF_NO_FALLBACK) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
-        h->prof_suppress = true;
-        int rc_fb = bf_exact_scan8(h, d_img, H, W, 1, 1, mode, range_begin, n_fb, fallback, d_idx, d_so, d_R, st);
-        h->prof_suppress = false;
-        FIC_TRY(rc_fb);
+    if (flags & FIC_BF_NO_FALLBACK) {
+        const int n_fb = hc[1];
+        unsigned long long st_total;
+        memcpy(&st_total, hc + 8, sizeof(st_total));
+        h->counters[CNT_SURVIVORS] += (int64_t)st_total;
+        h->counters[CNT_SCREEN_RANGES] += n_ranges - n_fb;
+        h->counters[CNT_RESCAN_RANGES] += n_fb;
+        if (n_fb > 0) { fic_set_error("screen left %d of %d ranges undecided", n_fb, n_ranges); return FIC_ECAP; }
+    }
+    return FIC_OK;
+}
+
+// Device totals of the pipeline (see fic_api.cu: fic_get_counters / fic_reset_counters).
+int bf_totals_read(fic_handle* h, unsigned long long* t)
+{
+    if (!h->bf_ctrl.p) return FIC_OK;
+    if (h->tail_valid) FIC_CUDA(cudaEventSynchronize(h->tail));
+    unsigned long long* totals = reinterpret_cast<unsigned long long*>(h->bf_ctrl.as<int>() + BF_CTRL_TOTALS);
+    if (t) {
+        FIC_CUDA(cudaMemcpy(t, totals, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    } else {
+        FIC_CUDA(cudaMemsetAsync(totals, 0, 4 * sizeof(unsigned long long), h->own_stream));
+        FIC_CUDA(cudaStreamSynchronize(h->own_stream));
     }
     return FIC_OK;
 }

@@ -6,6 +6,9 @@
 int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
 int bf_screen_run(fic_handle* h, const uint8_t* d_img, int H, int W, int mode, int range_begin, int n_ranges, int32_t* d_idx,
                   double* d_so, double* d_R, unsigned flags, float* probe, cudaStream_t st);
+// device-side counter totals of the brute-force pipeline: waits for the handle's last call, copies {survivors, ranges
+// screened, ranges re-scanned, fault code} to t[4]; t == nullptr clears them instead
+int bf_totals_read(fic_handle* h, unsigned long long* t);
 
 static thread_local char g_err[512] = "";
 
@@ -93,13 +96,16 @@ int fic_create(int device, fic_handle** out)
         fic_set_error("fic_create: device %d is sm_%d%d; the kernels are built for sm_100a only", device, prop.major, prop.minor);
         return FIC_ENOGPU;
     }
-    FIC_CUDA(cudaSetDevice(device));
+    DeviceScope scope(device);
+    FIC_CUDA(scope.err);
     fic_handle* h = new fic_handle();
     h->device = device;
     h->num_sms = prop.multiProcessorCount;
     e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->tail, cudaEventDisableTiming);
     if (e != cudaSuccess) {
-        fic_set_error("cudaStreamCreate failed: %s", cudaGetErrorString(e));
+        fic_set_error("stream / event creation failed: %s", cudaGetErrorString(e));
+        if (h->own_stream) cudaStreamDestroy(h->own_stream);
         delete h;
         return FIC_ECUDA;
     }
@@ -110,19 +116,21 @@ int fic_create(int device, fic_handle** out)
 int fic_destroy(fic_handle* h)
 {
     if (!h) return FIC_OK;
-    cudaSetDevice(h->device);
+    DeviceScope scope(h->device);
+    if (h->tail_valid) cudaEventSynchronize(h->tail);   // work of the last call, whatever stream it went to
     cudaStreamSynchronize(h->own_stream);
     DevBuf* bufs[] = {&h->d_img, &h->d_out_a, &h->d_out_b, &h->d_out_c, &h->d_in_a, &h->d_in_b, &h->bf_boxsum, &h->bf_stats,
-                      &h->bf_partial, &h->bf_ranges, &h->bf_pool, &h->bf_poolx, &h->bf_cand, &h->bf_A, &h->bf_thr,
+                      &h->bf_partial, &h->bf_ranges, &h->bf_pool, &h->bf_cand, &h->bf_A, &h->bf_thr,
                       &h->bf_surv, &h->bf_ctrl, &h->bf_best, &h->bf_list, &h->dec_img, &h->dec_next, &h->dec_map,
                       &h->dec_sched, &h->dec_red, &h->t_int1, &h->t_int2, &h->t_cls, &h->t_lists, &h->t_work, &h->t_res,
-                      &h->t_aux, &h->t_hvpool, &h->t_part, &h->dec_keys, &h->dec_roots};
+                      &h->t_aux, &h->t_hvpool, &h->t_part, &h->dec_keys, &h->dec_roots, &h->bf_done};
     for (DevBuf* b : bufs) b->release();
     h->pin_a.release();
     h->pin_b.release();
     h->pin_out.release();
     h->pin_stage.release();
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+    cudaEventDestroy(h->tail);
     cudaStreamDestroy(h->own_stream);
     delete h;
     return FIC_OK;
@@ -132,6 +140,18 @@ int fic_get_counters(fic_handle* h, int64_t out[8])
 {
     if (!h || !out) { fic_set_error("fic_get_counters: NULL argument"); return FIC_EINVAL; }
     for (int k = 0; k < 8; ++k) out[k] = h->counters[k];
+    if (h->bf_totals_live) {
+        // The brute-force pipeline counts on the device (its calls do not wait for the GPU): fetch the totals now.
+        // This is one of the library's host-visible points, so a pipeline fault recorded by an earlier call surfaces here.
+        DeviceScope scope(h->device);
+        FIC_CUDA(scope.err);
+        unsigned long long t[4] = {0, 0, 0, 0};
+        FIC_TRY(bf_totals_read(h, t));
+        out[CNT_SURVIVORS] += (int64_t)t[0];
+        out[CNT_SCREEN_RANGES] += (int64_t)t[1];
+        out[CNT_RESCAN_RANGES] += (int64_t)t[2];
+        if (t[3]) { fic_set_error("bf_screen_kernel: pipeline wait %llu timed out in an earlier call", t[3]); return FIC_ECUDA; }
+    }
     return FIC_OK;
 }
 
@@ -139,14 +159,21 @@ int fic_reset_counters(fic_handle* h)
 {
     if (!h) { fic_set_error("fic_reset_counters: NULL handle"); return FIC_EINVAL; }
     for (int k = 0; k < 8; ++k) h->counters[k] = 0;
+    if (h->bf_totals_live) {
+        DeviceScope scope(h->device);
+        FIC_CUDA(scope.err);
+        FIC_TRY(bf_totals_read(h, nullptr));
+    }
     return FIC_OK;
 }
 
 int fic_synchronize(fic_handle* h)
 {
     if (!h) { fic_set_error("fic_synchronize: NULL handle"); return FIC_EINVAL; }
-    FIC_CUDA(cudaSetDevice(h->device));
-    FIC_CUDA(cudaStreamSynchronize(h->own_stream));
+    DeviceScope scope(h->device);
+    FIC_CUDA(scope.err);
+    if (h->tail_valid) FIC_CUDA(cudaEventSynchronize(h->tail));   // the last call's work, whatever stream it was given
+    FIC_TRY(fic_sync(h, h->own_stream));
     return FIC_OK;
 }
 
@@ -160,7 +187,8 @@ int fic_profile(fic_handle* h, int enable)
 int fic_profile_read(fic_handle* h, double* total_ms, int64_t* launches)
 {
     if (!h || !total_ms || !launches) { fic_set_error("fic_profile_read: NULL argument"); return FIC_EINVAL; }
-    FIC_CUDA(cudaSetDevice(h->device));
+    DeviceScope scope(h->device);
+    FIC_CUDA(scope.err);
     double tot = 0.0;
     int64_t n = 0;
     for (size_t k = 0; k + 1 < h->prof_events.size(); k += 2) {
@@ -192,8 +220,7 @@ int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, in
     const int total = (H / range) * (W / range);
     FIC_REQUIRE(0 <= range_begin && range_begin <= range_end && range_end <= total,
                 "fic_bf_encode: range slice [%d,%d) outside [0,%d)", range_begin, range_end, total);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const int n = range_end - range_begin;
     if (n == 0) return FIC_OK;
@@ -252,8 +279,7 @@ int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int ran
     const int total = (H / 8) * (W / 8);
     FIC_REQUIRE(n_ranges >= 1 && n_ranges <= 32 && range_begin >= 0 && range_begin + n_ranges <= total,
                 "fic_bf_screen_probe: at most 32 ranges inside [0,%d)", total);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const size_t NP = (size_t)(H - 16) * (W - 16);
     const size_t rows = (NP + 127) / 128 * 128;
@@ -297,8 +323,7 @@ static int bf_decode_common(const char* who, fic_handle* h, int planes, const in
     FIC_REQUIRE(h && idx && so && out, "%s: NULL argument", who);
     FIC_REQUIRE(planes >= 1 && n >= 0 && width > 0 && height > 0 && iterations >= 0, "%s: bad sizes", who);
     FIC_REQUIRE(width % 8 == 0 && height % 8 == 0, "%s: sides must be multiples of the hard-coded range size 8", who);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     // the execution schedule is built on the host from the transforms, so host copies are needed either way
     const size_t n_all = (size_t)planes * n;
@@ -354,8 +379,7 @@ int fic_average_subsample(fic_handle* h, const double* arr, int h2, int w2, int 
 {
     FIC_REQUIRE(h && arr && out, "fic_average_subsample: NULL argument");
     FIC_REQUIRE(h2 > 0 && w2 > 0 && h2 % 2 == 0 && w2 % 2 == 0, "fic_average_subsample: shape (%d,%d) must be even", h2, w2);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const size_t nin = (size_t)h2 * w2 * sizeof(double), nout = nin / 4;
     const double* d_arr = arr;
@@ -389,8 +413,7 @@ int fic_qt_classify(fic_handle* h, const uint8_t* img, int H, int W, const int32
 {
     FIC_REQUIRE(h && img && blocks && out, "fic_qt_classify: NULL argument");
     FIC_REQUIRE(H > 0 && W > 0 && count >= 0, "fic_qt_classify: bad sizes");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const uint8_t* d_img;
     FIC_TRY(stage_image(h, img, H, W, dev, st, &d_img));
@@ -427,8 +450,7 @@ int fic_qt_encode(fic_handle* h, const uint8_t* img, int H, int W, int scale_bit
     FIC_REQUIRE(min_range_side >= 1 && max_range_side >= 1, "fic_qt_encode: range sides must be >= 1");
     FIC_REQUIRE(scale_bits >= 0 && scale_bits <= 30 && offset_bits >= 0 && offset_bits <= 30, "fic_qt_encode: bit widths out of range");
     FIC_REQUIRE((domain_hstep == -1 || domain_hstep > 0) && (domain_vstep == -1 || domain_vstep > 0), "fic_qt_encode: domain steps must be -1 or positive");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const uint8_t* d_img;
     FIC_TRY(stage_image(h, img, H, W, flags & FIC_DEVICE_PTRS, st, &d_img));
     return qt_encode_impl(h, d_img, H, W, scale_bits, offset_bits, max_scale, full_class_search, only_positive_scale,
@@ -441,8 +463,7 @@ int fic_hv_search(fic_handle* h, const uint8_t* img, int H, int W, const int32_t
 {
     FIC_REQUIRE(h && img && rects && rec && vals, "fic_hv_search: NULL argument");
     FIC_REQUIRE(H > 0 && W > 0 && count >= 0, "fic_hv_search: bad sizes");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const uint8_t* d_img;
     FIC_TRY(stage_image(h, img, H, W, dev, st, &d_img));
@@ -480,8 +501,7 @@ int fic_hv_encode(fic_handle* h, const uint8_t* img, int H, int W, int min_range
     FIC_REQUIRE(H > 0 && W > 0, "fic_hv_encode: empty image");
     FIC_REQUIRE(min_range_height >= 1 && min_range_width >= 1, "fic_hv_encode: minimum range sides must be >= 1");
     FIC_REQUIRE(scale_bits >= 0 && scale_bits <= 30 && offset_bits >= 0 && offset_bits <= 30, "fic_hv_encode: bit widths out of range");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const uint8_t* d_img;
     FIC_TRY(stage_image(h, img, H, W, flags & FIC_DEVICE_PTRS, st, &d_img));
     return hv_encode_impl(h, d_img, H, W, min_range_height, min_range_width, max_range_height, max_range_width, scale_bits,
@@ -510,8 +530,7 @@ int fic_tree_decode(fic_handle* h, int kind, const int32_t* leaves, const double
     FIC_REQUIRE(n >= 0 && H > 0 && W > 0 && (iterations >= 0 || iterations == FIC_ITER_AUTO), "fic_tree_decode: bad sizes");
     FIC_REQUIRE(!(flags & FIC_QT_DEBLOCK) || kind == FIC_TREE_QUADTREE,
                 "fic_tree_decode: the deblocking post-processor exists for the quadtree codec only");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const unsigned post = flags & (FIC_QT_DEBLOCK | FIC_TREE_OUT_F64);
     const size_t out_bytes = (size_t)H * W * ((flags & FIC_TREE_OUT_F64) ? sizeof(double) : 1);
@@ -543,8 +562,7 @@ int fic_qt_deblock(fic_handle* h, const double* img, const int32_t* leaves, int 
 {
     FIC_REQUIRE(h && img && leaves && out, "fic_qt_deblock: NULL argument");
     FIC_REQUIRE(n >= 0 && H > 0 && W > 0, "fic_qt_deblock: bad sizes");
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const size_t bytes = (size_t)H * W * sizeof(double);
     const double* d_img = img;
@@ -576,8 +594,7 @@ int fic_rgb_to_ycbcr(fic_handle* h, const uint8_t* rgb, int N, int M, int subsam
     FIC_REQUIRE(N > 0 && M > 0 && (subsample == 0 || subsample == 1), "fic_rgb_to_ycbcr: bad sizes or subsampling mode");
     FIC_REQUIRE(!subsample || N % 2 == 0,
                 "fic_rgb_to_ycbcr: 4:2:0 with an odd height %d (the reference raises or leaves the last chroma row unset)", N);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const size_t npx = (size_t)N * M, nc = subsample ? (size_t)(N / 2) * ((M + 1) / 2) : npx;
     const uint8_t* d_rgb = rgb;
@@ -610,8 +627,7 @@ int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const u
     FIC_REQUIRE(N > 0 && M > 0 && (subsample == 0 || subsample == 1), "fic_ycbcr_to_rgb: bad sizes or subsampling mode");
     FIC_REQUIRE(!subsample || N % 4 == 0,
                 "fic_ycbcr_to_rgb: 4:2:0 with height %d not a multiple of 4 (the reference raises, utils.py:73-76)", N);
-    FIC_CUDA(cudaSetDevice(h->device));
-    cudaStream_t st = fic_stream(h, stream);
+    FIC_ENTER(h, stream);
     const bool dev = flags & FIC_DEVICE_PTRS;
     const size_t npx = (size_t)N * M, nc = subsample ? (size_t)(N / 2) * ((M + 1) / 2) : npx;
     const uint8_t *d_y = y, *d_cb = cb, *d_cr = cr;

@@ -100,6 +100,11 @@ struct fic_handle {
     int num_sms = 0;
     cudaStream_t own_stream = nullptr;
     int64_t counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // Order between calls: every call records `tail` on its stream when it returns; a call on a DIFFERENT stream first
+    // makes its stream wait for that event, so the shared workspaces are never touched by two streams at once.
+    cudaEvent_t tail = nullptr;
+    cudaStream_t tail_stream = nullptr;
+    bool tail_valid = false;
     // optional event timing of the dominant kernel (fic_profile)
     bool prof_on = false;
     bool prof_suppress = false;
@@ -122,7 +127,9 @@ struct fic_handle {
     } eager;
     // brute force
     DevBuf bf_boxsum, bf_stats, bf_partial, bf_ranges;
-    DevBuf bf_pool, bf_poolx, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list;
+    DevBuf bf_pool, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list, bf_done;
+    bool screen_attr_ready = false;  // the screen / rescoring kernels have their dynamic shared memory limit raised on this device
+    bool bf_totals_live = false;     // bf_ctrl holds device-side counter totals that fic_get_counters has to fetch
     // decoders
     DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red, dec_keys, dec_roots;
     bool dec_shadow_ready = false;   // bf_decode_kernel<true> has its dynamic shared memory limit raised on this device
@@ -131,6 +138,41 @@ struct fic_handle {
 };
 
 static inline cudaStream_t fic_stream(fic_handle* h, void* s) { return s ? (cudaStream_t)s : h->own_stream; }
+
+// Makes the handle's device current for the duration of an entry point and puts the caller's device back afterwards.
+struct DeviceScope {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceScope(int device)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+        if (prev != device) { err = cudaSetDevice(device); switched = err == cudaSuccess && prev >= 0; }
+    }
+    ~DeviceScope() { if (switched) cudaSetDevice(prev); }
+};
+
+// See fic_handle::tail.
+struct StreamOrder {
+    fic_handle* h;
+    cudaStream_t st;
+    StreamOrder(fic_handle* h_, cudaStream_t st_) : h(h_), st(st_)
+    {
+        if (h->tail_valid && h->tail_stream != st) cudaStreamWaitEvent(st, h->tail, 0);
+    }
+    ~StreamOrder()
+    {
+        if (cudaEventRecord(h->tail, st) == cudaSuccess) { h->tail_stream = st; h->tail_valid = true; }
+        else cudaGetLastError();
+    }
+};
+
+// First lines of every entry point that works on a handle: device, stream, ordering behind the previous call.
+#define FIC_ENTER(h, stream)                                  \
+    DeviceScope _fic_dev((h)->device);                        \
+    FIC_CUDA(_fic_dev.err);                                   \
+    cudaStream_t st = fic_stream((h), (stream));              \
+    StreamOrder _fic_order((h), st)
 
 // copy helpers that account traffic; `dev` selects device-to-device when the caller passed device pointers
 int fic_copy_in(fic_handle* h, void* dst_dev, const void* src, size_t bytes, bool src_is_dev, cudaStream_t st);

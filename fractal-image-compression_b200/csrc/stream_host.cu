@@ -65,13 +65,25 @@ struct RawNode {
 extern "C" {
 
 int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t bit_pos, const int32_t* root_exps, int n_roots,
-                        const int32_t* raw_width, const int32_t* huff_root, const int32_t* huff_table, int32_t* nodes, int cap,
-                        int64_t* end_bit)
+                        const int32_t* raw_width, const int32_t* huff_root, const int32_t* huff_table, int huff_rows, int32_t* nodes,
+                        int cap, int64_t* end_bit)
 {
     FIC_REQUIRE(data && raw_width && huff_root && nodes && end_bit, "fic_tree_read_nodes: NULL argument");
     FIC_REQUIRE(kind == FIC_TREE_QUADTREE || kind == FIC_TREE_HV, "fic_tree_read_nodes: unknown tree kind %d", kind);
     FIC_REQUIRE(nbytes >= 0 && bit_pos >= 0 && n_roots >= 1 && (kind == FIC_TREE_HV || root_exps),
                 "fic_tree_read_nodes: bad sizes");
+    // untrusted input: field widths come from the file header (u8), table indices from a serialised tree
+    FIC_REQUIRE(huff_rows >= 0 && (huff_rows == 0 || huff_table), "fic_tree_read_nodes: bad Huffman table");
+    for (int r = 0; r < huff_rows; ++r) {   // children follow their parent in both layouts the library produces
+        const int l = huff_table[3 * r], rt = huff_table[3 * r + 1];
+        FIC_REQUIRE(l < 0 || (l > r && rt > r && l < huff_rows && rt < huff_rows),
+                    "fic_tree_read_nodes: Huffman table row %d links to rows %d and %d of %d", r, l, rt, huff_rows);
+    }
+    for (int d = 0; d < 4; ++d) {
+        FIC_REQUIRE(huff_root[d] >= 0 || (raw_width[d] >= 0 && raw_width[d] <= 32),
+                    "fic_tree_read_nodes: field %d is %d bits wide; the bit buffer holds at most 32 (bitbuffer.py MAX_BIT_WIDTH)", d, raw_width[d]);
+        FIC_REQUIRE(huff_root[d] < huff_rows, "fic_tree_read_nodes: field %d's Huffman root %d is outside the table of %d rows", d, huff_root[d], huff_rows);
+    }
     const int arity = kind == FIC_TREE_QUADTREE ? 4 : 2;
     BitReader br{data, (nbytes / 4) * 32, bit_pos};
     DimCoder dim[4];

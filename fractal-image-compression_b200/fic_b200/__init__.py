@@ -70,7 +70,8 @@ SIGNATURES = {
     "fic_qt_deblock": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_uint, _vp]),
     "fic_rgb_to_ycbcr": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, C.c_uint, _vp]),
     "fic_ycbcr_to_rgb": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_uint, _vp]),
-    "fic_tree_read_nodes": (C.c_int, [C.c_int, _vp, C.c_int64, C.c_int64, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int, _i64p]),
+    "fic_tree_read_nodes": (C.c_int, [C.c_int, _vp, C.c_int64, C.c_int64, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, C.c_int,
+                                      _i64p]),
     "fic_hv_layout": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "fic_huffman_read_tree": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int, _vp, C.c_int, _i64p]),
     "fic_pack_fields": (C.c_int64, [_vp, _vp, C.c_int64, C.c_uint32, C.c_int, _vp, C.c_int64, C.POINTER(C.c_uint32),
@@ -484,13 +485,14 @@ def tree_read_nodes(kind, data: bytes, bit_pos: int, root_exps, raw_width, huff_
     rw = np.ascontiguousarray(raw_width, np.int32).reshape(4)
     hr = np.ascontiguousarray(huff_root, np.int32).reshape(4)
     ht = np.ascontiguousarray(huff_table, np.int32).reshape(-1, 3)
-    if ht.shape[0] == 0:
+    rows = ht.shape[0]
+    if rows == 0:
         ht = np.zeros((1, 3), np.int32)
     nodes = np.empty((int(cap), 8), np.int32)
     end = C.c_int64(0)
     n = _check(lib().fic_tree_read_nodes(int(kind), buf.ctypes.data_as(_vp), buf.size, int(bit_pos), _ptr(exps),
                                          exps.shape[0] if kind == TREE_QUADTREE else 1, _ptr(rw), _ptr(hr), _ptr(ht),
-                                         _ptr(nodes), int(cap), C.byref(end)), "fic_tree_read_nodes")
+                                         rows, _ptr(nodes), int(cap), C.byref(end)), "fic_tree_read_nodes")
     return nodes[:n].copy(), int(end.value)
 
 

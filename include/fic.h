@@ -19,8 +19,20 @@
  *  - `stream` is a cudaStream_t passed as void* (NULL = the handle's own stream).
  *    With host pointers the call returns after the results are in the host buffers;
  *    with device pointers the work is enqueued on `stream` and the call returns
- *    without synchronising unless it needs a size from the device (tree encoders).
- *  - A handle is used by one host thread at a time; one handle per GPU.
+ *    without synchronising unless it needs a size from the device (tree encoders,
+ *    the brute-force decoder's schedule).  fic_bf_encode with device pointers never
+ *    waits: its counters stay on the device until fic_get_counters asks for them, and
+ *    a pipeline fault of an earlier call is reported there or by fic_synchronize.
+ *  - A handle is used by one host thread at a time; one handle per GPU.  Batches and
+ *    range slices on several GPUs use one handle (and one process or thread) per GPU:
+ *    no entry point takes a device list.
+ *  - All calls on a handle share its cached workspaces.  The library orders them itself:
+ *    every call leaves an event on its stream and a call on a different stream first
+ *    waits for the previous call's event, so device-pointer calls on several streams are
+ *    safe but run one after the other.  fic_synchronize waits for the last call
+ *    whatever stream it was given.
+ *  - Every entry point makes the handle's device current while it runs and puts the
+ *    caller's current device back before it returns.
  *  - There is NO CPU fallback: without a usable sm_100 GPU fic_create fails.
  */
 #ifndef FIC_H_
@@ -93,7 +105,8 @@ int fic_bf_encode(fic_handle* h, const uint8_t* img, int H, int W, int range, in
 
 /*
  * Batch form: imgs uint8 [B,H,W]; all ranges of every image; outputs [B,n,...].
- * This is the image-parallel path (one call per rank on its share of the batch).
+ * This is the image-parallel path: one call per rank (= per GPU, per handle) on its share of the batch.  There is
+ * no device-list argument -- a handle is bound to one GPU; fic_b200/parallel.py shows the sharding over ranks.
  */
 int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W, int range, int domain,
                         int mode, int32_t* out_idx, double* out_so, double* out_R, unsigned flags,
@@ -103,7 +116,8 @@ int fic_bf_encode_batch(fic_handle* h, const uint8_t* imgs, int B, int H, int W,
  * Diagnostic hook for the tensor-core path of fic_bf_encode (no counterpart in the reference; the quantity it
  * exposes is the cross-correlation numerator of bruteforce/jit_bfencoder.py:76): runs the pool kernel, the range
  * operand kernel and the tcgen05 correlation GEMM for the n_ranges <= 32 ranges starting at range_begin and returns
- * the raw fp32 accumulators  u = sum_k r'_k*D4'_k - rho*eps/64  (= (64*ab - sum(r)*sum(d))/4 in the reference's terms):
+ * the raw fp32 accumulators  X' = sum_k r'_k*D4'_k  (range and 4x-pooled domain centred by their rounded means;
+ * (64*ab - sum(r)*sum(d))/4 in the reference's terms equals X' - rho*eps/64 with |rho*eps/64| <= 16):
  * out_u float32 [ceil(NP/128)*128][256], row = stride-1 domain position di*(W-16)+dj, column = range*8 + orientation*4
  * + rotation.  Tests use it to check TMA / descriptor / MMA plumbing and the accumulator's exactness.
  */
@@ -128,7 +142,7 @@ int fic_bf_screen_probe(fic_handle* h, const uint8_t* img, int H, int W, int ran
  *     start at zero (each call writes everything it later reads).  Calls that overlap on the GPU -- two streams,
  *     two host threads -- race on it: issue them one after the other.
  *   - the first call on each device resolves the array's device address; do that first call before starting a
- *     stream capture.
+ *     stream capture, and from one host thread (later calls may come from any thread, one at a time).
  */
 int fic_bf_encode_static(const uint8_t* d_img, int H, int W, int stride_i, int stride_j, int mode, int range_begin,
                          int range_end, int32_t* d_idx, double* d_so, double* d_R, void* stream);
@@ -254,11 +268,13 @@ int fic_ycbcr_to_rgb(fic_handle* h, const uint8_t* y, const uint8_t* cb, const u
  * huff_root[d] < 0 = raw_width[d] plain bits, else the index of the root of a Huffman tree in huff_table[m][3] =
  * { left, right, value }, left < 0 marking a leaf (entropy/huffman.py:100-124).  root_exps: the quadtree roots' size
  * exponents in _de_partition order (HV: n_roots = 1, root_exps unused).  *end_bit = first bit after the section.
+ * huff_rows = rows of huff_table.  The stream is untrusted input: a raw width outside 0..32 (the bit buffer's
+ * MAX_BIT_WIDTH), a root or child index outside the table, or a child that does not follow its parent is FIC_EINVAL.
  * Returns the node count, FIC_ECAP, or FIC_EINVAL when the data ends early (the reference's "buffer returned EOF").
  */
 int fic_tree_read_nodes(int kind, const uint8_t* data, int64_t nbytes, int64_t bit_pos, const int32_t* root_exps,
                         int n_roots, const int32_t* raw_width, const int32_t* huff_root, const int32_t* huff_table,
-                        int32_t* nodes, int cap, int64_t* end_bit);
+                        int huff_rows, int32_t* nodes, int cap, int64_t* end_bit);
 
 /* Replaces HuffmanDeserializer.deserialize (entropy/huffman.py:100-124): reads one breadth-first tree dump (`1` + value
  * in val_bits bits for a leaf, `0` for an inner node) into table[m][3] = { left, right, value } rows in stream order

@@ -454,3 +454,25 @@ def test_bitbuffer_write_many_equals_single_writes():
         A.flush()
         B.flush()
         assert a.getvalue() == b.getvalue()
+
+
+def test_native_reader_rejects_hostile_headers():
+    """Field widths and Huffman tables come from the file: widths beyond the bit buffer's 32-bit words, roots and child
+    links outside the table or pointing backwards (a cycle) are refused instead of read."""
+    import fic_b200
+    data = bytes(64)
+    ok_w, no_h = [8, 8, 5, 7], [-1, -1, -1, -1]
+    empty = np.zeros((0, 3), np.int32)
+    with pytest.raises(ValueError, match="bits wide"):
+        fic_b200.tree_read_nodes(fic_b200.TREE_QUADTREE, data, 0, [3], [8, 8, 40, 7], no_h, empty, 64)
+    with pytest.raises(ValueError, match="bits wide"):
+        fic_b200.tree_read_nodes(fic_b200.TREE_HV, data, 0, None, [8, -1, 5, 7], no_h, empty, 64)
+    loop = np.array([[0, 1, 0], [-1, -1, 3]], np.int32)            # row 0 links to itself
+    with pytest.raises(ValueError, match="links to rows"):
+        fic_b200.tree_read_nodes(fic_b200.TREE_QUADTREE, data, 0, [3], ok_w, [0, -1, -1, -1], loop, 64)
+    far = np.array([[1, 7, 0], [-1, -1, 3]], np.int32)             # child outside the table
+    with pytest.raises(ValueError, match="links to rows"):
+        fic_b200.tree_read_nodes(fic_b200.TREE_QUADTREE, data, 0, [3], ok_w, [0, -1, -1, -1], far, 64)
+    good = np.array([[1, 2, 0], [-1, -1, 3], [-1, -1, 4]], np.int32)
+    with pytest.raises(ValueError, match="outside the table"):
+        fic_b200.tree_read_nodes(fic_b200.TREE_QUADTREE, data, 0, [3], ok_w, [5, -1, -1, -1], good, 64)

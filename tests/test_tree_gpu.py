@@ -213,3 +213,20 @@ def test_hv_decode_on_random_trees(fic, orc, seed, shape):
             got, n_it = fic.tree_decode(fic.TREE_HV, leaves, so, H, W, iterations=it, f32_affine=not quantised)
             ref, n_ref = orc.tree_decode(1, leaves, so, H, W, iterations=it, f32_affine=not quantised)
             assert n_it == n_ref and np.array_equal(got, ref)
+
+
+def test_hv_decoder_follows_either_numpy_promotion_rule(fic, orc, golden):
+    """hvv2/decoder.py:79 multiplies a float32 array by an np.float64 scalar: float64 under NumPy >= 2 (the goldens),
+    float32 under the reference's pinned NumPy 1.26.  The class takes the choice explicitly; both against the oracle."""
+    from hvv2.common import tree_to_leaves
+    from hvv2.decoder import HVDecoder
+    from hvv2.encoder import HVEncoder
+    img = synthetic_image(21, 72, 88)
+    hv = HVEncoder(4, 4, 16, 16, 5, 7, 25.0).encode(img)
+    leaves, so = tree_to_leaves(hv, True)
+    for np1 in (False, True):
+        dec = HVDecoder(iterations=6, numpy1_promotion=np1)
+        want, _ = orc.tree_decode(1, leaves, so, 72, 88, iterations=6, f32_affine=np1)
+        assert np.array_equal(dec.decode(hv), want)
+    auto = HVDecoder()          # default: the installed NumPy's rule
+    assert auto.numpy1_promotion == ((np.zeros(1, np.float32) * np.float64(1.0)).dtype == np.float32)
