@@ -82,7 +82,7 @@ constexpr int STAGES = FIC_SCREEN_STAGES;
 // back as soon as their two TMEM loads have landed; 0: two groups of eight warps, one group per accumulator stage
 // (128 columns per warp, released after the fourth load).
 #ifndef FIC_EPI_ALL
-#define FIC_EPI_ALL 1
+#define FIC_EPI_ALL 0
 #endif
 constexpr bool EPI_ALL = FIC_EPI_ALL != 0;
 constexpr int WARPS_PER_STAGE = 8;                    // EPI_ALL == 0: epilogue warps per accumulator stage (two per TMEM lane quadrant)
