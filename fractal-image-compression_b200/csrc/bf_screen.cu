@@ -78,16 +78,9 @@ constexpr int KMAIN = 64;
 #define FIC_SCREEN_STAGES 6
 #endif
 constexpr int STAGES = FIC_SCREEN_STAGES;
-// Epilogue organisation.  1: all sixteen epilogue warps work on every tile (64 columns each) and hand the accumulator
-// back as soon as their two TMEM loads have landed; 0: two groups of eight warps, one group per accumulator stage
-// (128 columns per warp, released after the fourth load).
-#ifndef FIC_EPI_ALL
-#define FIC_EPI_ALL 0
-#endif
-constexpr bool EPI_ALL = FIC_EPI_ALL != 0;
-constexpr int WARPS_PER_STAGE = 8;                    // EPI_ALL == 0: epilogue warps per accumulator stage (two per TMEM lane quadrant)
+constexpr int WARPS_PER_STAGE = 8;                    // epilogue warps per accumulator stage (two per TMEM lane quadrant)
 constexpr int EPI_WARPS = 2 * WARPS_PER_STAGE;
-constexpr int RANGES_PER_WARP = EPI_ALL ? 8 : 16;     // ranges (groups of 8 columns) one epilogue warp looks at per tile
+constexpr int RANGES_PER_WARP = 16;                   // ranges (groups of 8 columns) one epilogue warp looks at per tile
 // the scheduler favours high warp ids: the two single-thread roles sit ABOVE the epilogue warps so that the busy
 // epilogue can never delay a TMA issue or an MMA issue
 constexpr int TMA_WARP = EPI_WARPS, MMA_WARP = EPI_WARPS + 1;
@@ -421,7 +414,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         mbar_init(b_full, 1);
         mbar_init(b_empty, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), EPI_ALL ? EPI_WARPS : WARPS_PER_STAGE); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), WARPS_PER_STAGE); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == MMA_WARP) {  // TMEM: all 512 columns (one CTA per SM by construction: > 113 KB of shared memory)
@@ -500,151 +493,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             if (issuer) tcgen05_commit(b_empty);
             __syncwarp();
         }
-    } else if (warp < EPI_WARPS && EPI_ALL) {
-        // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
-        // All sixteen warps work on every tile: four warps share each TMEM lane quadrant and take 64 columns (8 ranges)
-        // each.  A warp's two 32-column loads are all it needs from the accumulator, so the stage goes back to the MMA
-        // issuer as soon as they have landed -- the screening runs on registers while the next tile's MMAs already write
-        // the same stage.  TMEM delivers 64 B per cycle and scheduler; with four warps per scheduler queueing their loads
-        // the read port stays busy while other warps screen.
-        const int quad = warp & 3;                           // TMEM lane quadrant this warp may touch
-        const int part = warp >> 2;                          // which 64-column quarter of the 256 columns
-        const int lane_off = quad * 32 + lane;
-        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(part * 64);
-        int n = 0;  // tiles seen so far by this CTA (all units): tile n uses accumulator stage n & 1, phase (n >> 1) & 1
-        float* my_tau = reinterpret_cast<float*>(gbase + OFF_TAU) + warp * 32;   // [0,8) = tau_A, [8,16) = tau_B
-        WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + warp;
-        uint32_t qn = 0;   // queue fill, warp-uniform
-        Span span(p, n_groups);
-        int grp, j0, j1;
-        while (span.next(grp, j0, j1)) {
-            if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
-            __syncwarp();
-            if (lane < 8) {
-                const float2 tt = p.tau[grp * 32 + part * 8 + lane];
-                my_tau[lane] = tt.x;
-                my_tau[8 + lane] = tt.y;
-            }
-            // this warp's TMEM address: ptxas would otherwise rebuild it from %tid.x (two ~50-cycle S2R) between the wait on
-            // the accumulator and the first load of every tile; a value that comes out of a volatile load stays in a register
-            if (lane == 0) reinterpret_cast<uint32_t*>(my_tau)[16] = taddr0;
-            __syncwarp();
-            const int slot0 = grp * 32 + part * 8;
-            int j = j0;
-            // The loop carries this lane's candidate index (tile * 128 + quadrant * 32 + lane) rather than the tile:
-            // t = (j + j / (r_prev - 1) + 1) * m_cur is advanced without a division per tile.
-            int cand = tile_of(p, j) * BM + lane_off;
-            const int r1 = p.r_prev > 0 ? p.r_prev - 1 : 0x7fffffff;
-            int rem = p.r_prev > 0 ? j % r1 : 0;
-            const float hk_pad = __int_as_float(0x7f800000);   // padding rows of the last tile: threshold never met
-            float hq_next = cand < p.NP ? p.hk[cand].x : hk_pad;
-            float4 tq0, tq1;
-            {
-                const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 8 : 0));
-                tq0 = tau4[0]; tq1 = tau4[1];
-            }
-            float seed_gain[8];   // seed mode only: this lane's best candidate per range over the unit's tiles
-            int seed_cand[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { seed_gain[i] = 0.f; seed_cand[i] = 0; }
-            for (; j < j1; ++j, ++n) {
-                const int my_cand = cand;
-                {
-                    int wraps = 0;
-                    if (++rem >= r1) { rem = 0; wraps = 1; }
-                    cand += (1 + wraps) * p.m_cur * BM;
-                }
-                const float hq = hq_next;
-                hq_next = (j + 1 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
-                const uint32_t stage = (uint32_t)n & 1u, aph = ((uint32_t)n >> 1) & 1u;
-                uint32_t taddr_pinned;
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(taddr_pinned) : "r"(smem_u32(my_tau + 16)));
-                const uint32_t taddr = taddr_pinned + stage * BN;
-                const uint32_t my_tfull = tfull_bar(stage), my_tempty = tempty_bar(stage);
-                uint32_t va[32], vb[32];
-                if (MODE == 5) {
-                    // seed mode: no thresholds yet.  Rank the (few) candidates of the seed pool by the collage-error
-                    // reduction the exact-arithmetic optimum would give (contrast clamped to |s| <= 1) and keep the best
-                    // one per range; it is scored exactly afterwards and provides the first upper bound.
-                    const float den = my_cand < p.NP ? p.hk[my_cand].y : 0.f;
-                    const float inv64 = den > 0.f ? 64.f / den : 0.f, den1024 = den * (1.0f / 1024.0f);
-                    auto rank4 = [&](const uint32_t (&v)[32], int c4) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            float m = fabsf(__uint_as_float(v[g * 8]));
-#pragma unroll
-                            for (int i = 1; i < 8; ++i) m = fmaxf(m, fabsf(__uint_as_float(v[g * 8 + i])));
-                            const float gain = 256.f * m <= den ? m * m * inv64 : 0.5f * m - den1024;   // den == 0: m == 0
-                            if (gain > seed_gain[c4 * 4 + g]) { seed_gain[c4 * 4 + g] = gain; seed_cand[c4 * 4 + g] = my_cand; }
-                        }
-                    };
-                    mbar_wait(my_tfull, aph, p.err_flag, 6);
-                    tcgen05_fence_after();
-                    tmem_ld32(taddr, va);
-                    tmem_ld32(taddr + 32, vb);
-                    tmem_ld_wait(va);
-                    tmem_ld_wait(vb);
-                    tcgen05_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(my_tempty);
-                    rank4(va, 0);
-                    rank4(vb, 1);
-                    continue;
-                }
-                const float qx = fabsf(hq);
-                // thresholds on |X'| for the 8 ranges: theta = tau/h_c - DELTA, tau picked by the candidate's class
-                float theta[8];
-                theta[0] = fmaf(tq0.x, qx, -DELTA_U); theta[1] = fmaf(tq0.y, qx, -DELTA_U);
-                theta[2] = fmaf(tq0.z, qx, -DELTA_U); theta[3] = fmaf(tq0.w, qx, -DELTA_U);
-                theta[4] = fmaf(tq1.x, qx, -DELTA_U); theta[5] = fmaf(tq1.y, qx, -DELTA_U);
-                theta[6] = fmaf(tq1.z, qx, -DELTA_U); theta[7] = fmaf(tq1.w, qx, -DELTA_U);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) asm volatile("" : "+f"(theta[i]));   // materialise before the wait
-                mbar_wait(my_tfull, aph, p.err_flag, 6);
-                tcgen05_fence_after();
-                if (MODE == 3) {
-                    tcgen05_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(my_tempty);
-                    continue;
-                }
-                tmem_ld32(taddr, va);
-                tmem_ld32(taddr + 32, vb);
-                tmem_ld_wait(va);
-                tmem_ld_wait(vb);
-                tcgen05_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(my_tempty);
-                if (MODE == 1) {
-                    if (grp == 0) {
-#pragma unroll
-                        for (int q = 0; q < 32; ++q) {
-                            p.dump[(size_t)my_cand * BN + part * 64 + q] = __uint_as_float(va[q]);
-                            p.dump[(size_t)my_cand * BN + part * 64 + 32 + q] = __uint_as_float(vb[q]);
-                        }
-                    }
-                } else if (MODE == 0 || MODE == 4) {
-                    screen_pair<MODE == 0>(va, vb, theta, p, slot0, my_cand, queue, qn, lane);
-                } else if (va[0] == 0x7fc12345u || vb[0] == 0x7fc12345u) {
-                    p.cnt[0] = 1;
-                }
-                {   // next tile's tau; harmless after the last tile
-                    const float4* tau4 = reinterpret_cast<const float4*>(my_tau + (hq_next < 0.f ? 8 : 0));
-                    tq0 = tau4[0]; tq1 = tau4[1];
-                }
-                if (MODE == 0 && qn >= QFLUSH) { queue_flush(queue, p, lane, qn); qn = 0; }
-            }
-            if (MODE == 5) {   // merge the lanes' seed candidates of this unit: warp maximum, then one atomic per range
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const uint32_t bits = seed_gain[i] > 0.f ? __float_as_uint(seed_gain[i]) : 0u;
-                    const uint32_t wmax = __reduce_max_sync(0xffffffffu, bits);
-                    if (wmax != 0u && bits == wmax)   // ties (rare): every tied lane offers its candidate, the smaller index wins
-                        atomicMax(&p.seed_best[slot0 + i], ((unsigned long long)bits << 32) | (0xffffffffu - (uint32_t)seed_cand[i]));
-                }
-            }
-        }
-        if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
     } else if (warp < EPI_WARPS) {
         // ===== epilogue: TMEM -> registers -> screen -> (rare) survivor append =====
         // Two warp groups of WARPS_PER_STAGE warps; group g owns accumulator stage g, i.e. every second tile of the CTA's
@@ -658,8 +506,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         // address of this warp's slice of its accumulator stage; pinned so it is not rebuilt from %tid after the wait
         uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(stage * BN + part * 128);
         asm volatile("" : "+r"(taddr0));
-        uint32_t lane0 = lane == 0;
-        asm volatile("" : "+r"(lane0));
         const uint32_t my_tfull = tfull_bar(stage), my_tempty = tempty_bar(stage);
         uint32_t aph = 0;
         int n = 0;  // tiles issued so far by this CTA (all units): tile n uses stage n & 1
@@ -936,20 +782,22 @@ bf_pool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict_
         const float d = __fmul_rn((float)v[k], 0.25f);
         sq[k] = __fmul_rn(d, d);  // exact: v^2/16 < 2^24 significant bits
     }
-    // fully unrolled: the isometry index maps become compile-time constants and sq[] stays in registers
+    // Eight sequential float32 sums of 64 terms, one per isometry, each in its own order: 512 dependent additions are what
+    // this kernel spends its time on (it is bound by them, not by HBM).  Fully unrolled with the eight chains advancing
+    // together: the index maps are compile-time constants, sq[] stays in registers, eight independent additions per step.
+    float acc[8];
 #pragma unroll
-    for (int t = 0; t < 8; ++t) {
-        float acc = 0.f;
+    for (int t = 0; t < 8; ++t) acc[t] = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+    for (int k = 0; k < 64; ++k)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                int sa, sb;
-                fic_iso_bf(t >> 2, t & 3, 8, i, j, sa, sb);
-                acc = __fadd_rn(acc, sq[sa * 8 + sb]);
-            }
-        sdd[(size_t)t * NP + p] = acc;
-    }
+        for (int t = 0; t < 8; ++t) {
+            int sa, sb;
+            fic_iso_bf(t >> 2, t & 3, 8, k >> 3, k & 7, sa, sb);
+            acc[t] = __fadd_rn(acc[t], sq[sa * 8 + sb]);
+        }
+#pragma unroll
+    for (int t = 0; t < 8; ++t) sdd[(size_t)t * NP + p] = acc[t];
 }
 
 // ---- per-range state --------------------------------------------------------------------------------------------

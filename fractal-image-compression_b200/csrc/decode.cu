@@ -207,15 +207,22 @@ int bf_decode_impl(fic_handle* h, int planes, const int32_t* h_idx, const double
 // ------------------------------------------------------------------------------------------------
 // quadtree / HV Jacobi decoder
 // ------------------------------------------------------------------------------------------------
-__global__ void tree_paint_kernel(const int32_t* __restrict__ leaves, int n, int W, int32_t* __restrict__ leaf_map)
+// One warp per leaf (grid-stride over the leaves): most leaves of a real tree are 4x4 .. 16x16 blocks, for which a CTA per
+// leaf is almost all launch overhead (262 144 CTAs of 64 threads for the 8x8 leaves of a 4096x4096 image: 0.14 ms against
+// 0.18 ms for a whole Jacobi sweep).  Lanes walk the leaf row-major, so a row of 8+ pixels is one contiguous store.
+#define TP_THREADS 256
+__global__ void __launch_bounds__(TP_THREADS)
+tree_paint_kernel(const int32_t* __restrict__ leaves, int n, int W, int32_t* __restrict__ leaf_map)
 {
-    const int k = blockIdx.x;
-    if (k >= n) return;
-    const int32_t* L = leaves + 8 * (size_t)k;
-    const int ri = L[0], rj = L[1], hh = L[2], ww = L[3];
-    for (int e = threadIdx.x; e < hh * ww; e += blockDim.x) {
-        int a = e / ww, b = e - a * ww;
-        leaf_map[(size_t)(ri + a) * W + rj + b] = k;
+    const int lane = threadIdx.x & 31;
+    const int warps = gridDim.x * (TP_THREADS / 32);
+    for (int k = blockIdx.x * (TP_THREADS / 32) + (threadIdx.x >> 5); k < n; k += warps) {
+        const int4 L = *reinterpret_cast<const int4*>(leaves + 8 * (size_t)k);
+        const int ri = L.x, rj = L.y, hh = L.z, ww = L.w;
+        for (int e = lane; e < hh * ww; e += 32) {
+            const int a = e / ww, b = e - a * ww;
+            leaf_map[(size_t)(ri + a) * W + rj + b] = k;
+        }
     }
 }
 
@@ -312,13 +319,22 @@ __global__ void tree_reduce_kernel(const double* __restrict__ red, int nblocks, 
     if (threadIdx.x == 0) { out2[0] = se[0]; out2[1] = ss[0]; }
 }
 
+// clip(0., 255.) and the uint8 cast (decoder.py:61): 8 B read, 1 B written per pixel; four pixels per thread so that the
+// bytes leave as one 32-bit store (the image base comes from cudaMalloc, so groups of four stay aligned)
 __global__ void tree_finish_kernel(const double* __restrict__ img, size_t npx, uint8_t* __restrict__ out)
 {
-    size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npx) return;
-    double v = img[p];
-    v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);  // clip(0., 255.), decoder.py:61
-    out[p] = (uint8_t)__double2int_rz(v);
+    const size_t q = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (q >= npx) return;
+    auto clip = [](double v) -> unsigned {
+        v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);
+        return (unsigned)__double2int_rz(v);
+    };
+    if (q + 4 <= npx && (reinterpret_cast<uintptr_t>(out) & 3u) == 0 && (reinterpret_cast<uintptr_t>(img) & 15u) == 0) {
+        const double2 a = *reinterpret_cast<const double2*>(img + q), b = *reinterpret_cast<const double2*>(img + q + 2);
+        *reinterpret_cast<uint32_t*>(out + q) = clip(a.x) | (clip(a.y) << 8) | (clip(b.x) << 16) | (clip(b.y) << 24);
+    } else {
+        for (size_t p = q; p < npx && p < q + 4; ++p) out[p] = (uint8_t)clip(img[p]);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -473,7 +489,7 @@ int qt_deblock_impl(fic_handle* h, const double* d_img, const int32_t* d_leaves,
     FIC_TRY(h->dec_map.reserve(npx * sizeof(int32_t)));
     FIC_CUDA(cudaMemsetAsync(h->dec_map.p, 0xff, npx * sizeof(int32_t), st));
     if (n > 0) {
-        tree_paint_kernel<<<n, 64, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
+        tree_paint_kernel<<<std::min((n + TP_THREADS / 32 - 1) / (TP_THREADS / 32), h->num_sms * 32), TP_THREADS, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
         FIC_CHECK_LAUNCH(h, "tree_paint_kernel");
     }
     DeblockWeights dw = qt_default_weights();
@@ -511,7 +527,7 @@ int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const dou
     FIC_CUDA(cudaMemsetAsync(h->dec_next.p, 0, npx * sizeof(double), st));
     FIC_CUDA(cudaMemsetAsync(h->dec_map.p, 0xff, npx * sizeof(int32_t), st));
     if (n > 0) {
-        tree_paint_kernel<<<n, 64, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
+        tree_paint_kernel<<<std::min((n + TP_THREADS / 32 - 1) / (TP_THREADS / 32), h->num_sms * 32), TP_THREADS, 0, st>>>(d_leaves, n, W, h->dec_map.as<int32_t>());
         FIC_CHECK_LAUNCH(h, "tree_paint_kernel");
     }
     double* img = h->dec_img.as<double>();
@@ -549,7 +565,7 @@ int tree_decode_impl(fic_handle* h, int kind, const int32_t* d_leaves, const dou
         return qt_deblock_run(h, img, d_leaves, n, H, W, qt_default_weights(), map, f64 ? (double*)d_out : nullptr,
                               f64 ? nullptr : (uint8_t*)d_out, st);
     if (f64) return fic_copy_out(h, d_out, img, npx * sizeof(double), true, st);
-    tree_finish_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(img, npx, (uint8_t*)d_out);
+    tree_finish_kernel<<<(unsigned)((npx + 1023) / 1024), 256, 0, st>>>(img, npx, (uint8_t*)d_out);
     FIC_CHECK_LAUNCH(h, "tree_finish_kernel");
     return FIC_OK;
 }

@@ -401,13 +401,14 @@ def tree_decode(kind, leaves, so, H, W, iterations=ITER_AUTO, stop_on_relative_e
 
 def tree_decode_dev(h: Handle, kind, leaves_ptr: int, so_ptr: int, n: int, H: int, W: int, out_ptr: int,
                     iterations=ITER_AUTO, stop_on_relative_error=5e-3, min_iterations=2, max_iterations=10,
-                    f32_affine=False, flags=0) -> int:
+                    f32_affine=False, flags=0, stream=0) -> int:
     """fic_tree_decode on device buffers (leaves int32 [n,8], so float64 [n,2], out uint8 [H,W] or float64 with
     TREE_OUT_F64); returns the sweeps run.  The AUTO stop rule still reads its two norms back every sweep."""
     done = C.c_int32(0)
     _check(lib().fic_tree_decode(h.ptr, int(kind), _vp(leaves_ptr), _vp(so_ptr), int(n), int(H), int(W), int(iterations),
                                  float(stop_on_relative_error), int(min_iterations), int(max_iterations),
-                                 int(bool(f32_affine)), _vp(out_ptr), C.byref(done), DEVICE_PTRS | flags, None),
+                                 int(bool(f32_affine)), _vp(out_ptr), C.byref(done), DEVICE_PTRS | flags,
+                                 _vp(stream) if stream else None),
            "fic_tree_decode")
     return int(done.value)
 

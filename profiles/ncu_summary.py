@@ -49,5 +49,36 @@ def screen(src, dst):
     json.dump({"launches": out, "traffic_bytes_per_launch_avg": tot / max(len(out), 1)}, open(dst, "w"), indent=1)
 
 
+def hbm(src, dst):
+    """ncu --csv log with dram__bytes_read.sum, dram__bytes_write.sum, gpu__time_duration.sum per launch -> per-kernel rows with
+    achieved DRAM GB/s (long format: one row per launch and metric)."""
+    rows = [r for r in csv.reader(open(src)) if len(r) > 5]
+    h = rows[0]
+    ii, ki, mi, vi, ui = h.index("ID"), h.index("Kernel Name"), h.index("Metric Name"), h.index("Metric Value"), h.index("Metric Unit")
+    scale = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0, "ms": 1e-3, "us": 1e-6, "ns": 1e-9, "s": 1.0,
+             "msecond": 1e-3, "usecond": 1e-6, "nsecond": 1e-9, "second": 1.0}
+    by = {}
+    for r in rows[1:]:
+        d = by.setdefault(int(r[ii]), {"kernel": r[ki].split("(")[0].replace("void ", "").replace("<unnamed>::", "")})
+        d[r[mi]] = float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
+    peak = None
+    try:
+        import os
+        peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        pass
+    out = []
+    for k in sorted(by):
+        d = by[k]
+        t = d.get("gpu__time_duration.sum", 0.0)
+        b = d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)
+        if t < 20e-6:       # helpers below 20 us say nothing about bandwidth
+            continue
+        out.append({"id": k, "kernel": d["kernel"], "ms": t * 1e3, "dram_read_MB": d.get("dram__bytes_read.sum", 0.0) / 1e6,
+                    "dram_write_MB": d.get("dram__bytes_write.sum", 0.0) / 1e6, "dram_gbs": b / t / 1e9 if t else None,
+                    "frac_of_peak": (b / t / 1e9 / peak) if (t and peak) else None})
+    json.dump({"peak_gbs": peak, "launches": out}, open(dst, "w"), indent=1)
+
+
 if __name__ == "__main__":
-    {"launches": launches, "screen": screen}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "screen": screen, "hbm": hbm}[sys.argv[1]](sys.argv[2], sys.argv[3])
