@@ -134,7 +134,7 @@ struct fic_handle {
     DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red, dec_keys, dec_roots;
     bool dec_shadow_ready = false;   // bf_decode_kernel<true> has its dynamic shared memory limit raised on this device
     // quadtree / hv
-    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part;
+    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part, t_nodes, t_count;
 };
 
 static inline cudaStream_t fic_stream(fic_handle* h, void* s) { return s ? (cudaStream_t)s : h->own_stream; }

@@ -179,6 +179,94 @@ __global__ void classify_grid_kernel(const long long* __restrict__ I1, const lon
     out[3 * (size_t)k + 2] = orient;
 }
 
+// ---- 72-class domain pools on the device (quadtree/encoder.py:261-283) ------------------------------------------
+// A stable counting sort of the grid positions by class: the reference appends the domains of a pool size to their
+// class lists in row-major grid order, so inside a class the order is the position index.  Three launches per pool
+// size and no host round trip: (1) per-CTA class histograms over contiguous chunks of positions, (2) one CTA turns them
+// into per-chunk start offsets and the CSR offsets[73] -- a class without domains gets one placeholder row (0,0,0,0),
+// encoder.py:279-280 -- (3) every CTA scatters its chunk in order (ranks from warp match masks + running class counters).
+#define QP_THREADS 256
+#define QP_CHUNK 2048     // positions per CTA
+
+__global__ void __launch_bounds__(QP_THREADS)
+qt_pool_count_kernel(const int32_t* __restrict__ cls3, int cnt, int32_t* __restrict__ blockhist /*[nblocks][72]*/)
+{
+    __shared__ int hist[72];
+    if (threadIdx.x < 72) hist[threadIdx.x] = 0;
+    __syncthreads();
+    const int p0 = blockIdx.x * QP_CHUNK;
+    for (int p = p0 + threadIdx.x; p < min(p0 + QP_CHUNK, cnt); p += QP_THREADS) atomicAdd(&hist[cls3[3 * (size_t)p]], 1);
+    __syncthreads();
+    if (threadIdx.x < 72) blockhist[(size_t)blockIdx.x * 72 + threadIdx.x] = hist[threadIdx.x];
+}
+
+__global__ void qt_pool_scan_kernel(int32_t* __restrict__ blockhist, int nblocks, int32_t* __restrict__ offsets /*[73]*/,
+                                    int32_t* __restrict__ rows)
+{
+    __shared__ int total[72], off[73];
+    const int c = threadIdx.x;
+    if (c < 72) {
+        int acc = 0;
+        for (int b = 0; b < nblocks; ++b) {   // exclusive prefix over the chunks, in place
+            const int v = blockhist[(size_t)b * 72 + c];
+            blockhist[(size_t)b * 72 + c] = acc;
+            acc += v;
+        }
+        total[c] = acc;
+    }
+    __syncthreads();
+    if (c == 0) {
+        int acc = 0;
+        for (int k = 0; k < 72; ++k) { off[k] = acc; acc += total[k] > 0 ? total[k] : 1; }
+        off[72] = acc;
+    }
+    __syncthreads();
+    if (c < 73) offsets[c] = off[c];
+    if (c < 72 && total[c] == 0) {   // placeholder row of an empty class
+        int32_t* r = rows + 4 * (size_t)off[c];
+        r[0] = r[1] = r[2] = r[3] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(QP_THREADS)
+qt_pool_scatter_kernel(const int32_t* __restrict__ cls3, int cnt, int nh, int vstep, int hstep,
+                       const int32_t* __restrict__ blockhist, const int32_t* __restrict__ offsets, int32_t* __restrict__ rows)
+{
+    __shared__ int run[72];                         // next free row of every class for this chunk
+    __shared__ int wcnt[QP_THREADS / 32][72];       // this pass: members of every class per warp
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid < 72) run[tid] = offsets[tid] + blockhist[(size_t)blockIdx.x * 72 + tid];
+    const int p0 = blockIdx.x * QP_CHUNK, p1 = min(p0 + QP_CHUNK, cnt);
+    for (int base = p0; base < p1; base += QP_THREADS) {
+        for (int e = tid; e < (QP_THREADS / 32) * 72; e += QP_THREADS) (&wcnt[0][0])[e] = 0;
+        __syncthreads();
+        const int p = base + tid;
+        const bool live = p < p1;
+        int c = 0, rot = 0, orient = 0, rank = 0;
+        if (live) { c = cls3[3 * (size_t)p]; rot = cls3[3 * (size_t)p + 1]; orient = cls3[3 * (size_t)p + 2]; }
+        const unsigned act = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            const unsigned same = __match_any_sync(act, c);
+            rank = __popc(same & ((1u << lane) - 1u));
+            if (rank == 0) wcnt[warp][c] = __popc(same);
+        }
+        __syncthreads();
+        if (live) {
+            int at = run[c] + rank;
+            for (int w = 0; w < warp; ++w) at += wcnt[w][c];
+            int32_t* r = rows + 4 * (size_t)at;
+            r[0] = (p / nh) * vstep; r[1] = (p % nh) * hstep; r[2] = rot; r[3] = orient;
+        }
+        __syncthreads();
+        if (tid < 72) {
+            int add = 0;
+            for (int w = 0; w < QP_THREADS / 32; ++w) add += wcnt[w][tid];
+            run[tid] += add;
+        }
+        __syncthreads();
+    }
+}
+
 int qt_classify_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_blocks, int count, int32_t* d_out,
                      cudaStream_t st)
 {
@@ -252,7 +340,7 @@ struct QtPoolDev {
 __global__ void __launch_bounds__(TE_THREADS)
 qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int W, const long long* __restrict__ I1,
                  const long long* __restrict__ I2,
-                 const int32_t* __restrict__ ranges /*[n][2] = si,sj*/, int side, QtPoolDev pool, int full, int nmodes,
+                 const int32_t* __restrict__ ranges /*[n][4] = si,sj,node,-*/, int side, QtPoolDev pool, int full, int nmodes,
                  double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ rec /*[n][6]*/,
                  double* __restrict__ vals /*[n][3]*/)
 {
@@ -264,7 +352,7 @@ qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
     __shared__ unsigned long long s_bound;   // bit pattern of the best score found so far by this CTA (+inf at start)
     __shared__ float s_range[QT_RANGE_SMEM];  // the range block as floats (sides up to 32)
     const int tid = threadIdx.x;
-    const int si = ranges[2 * blockIdx.x], sj = ranges[2 * blockIdx.x + 1];
+    const int si = ranges[4 * (size_t)blockIdx.x], sj = ranges[4 * (size_t)blockIdx.x + 1];
     const int nn = side * side;
     const bool in_smem = nn <= QT_RANGE_SMEM;
     if (in_smem)
@@ -376,15 +464,17 @@ __global__ void hv_pool_kernel(const uint8_t* __restrict__ img, int H, int W, fl
 __global__ void __launch_bounds__(TE_THREADS, 4)
 hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
                  const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
-                 int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs, int smem_px)
+                 int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs, int smem_px,
+                 const int32_t* __restrict__ slist /* optional: CTA x works on rectangle slist[x] (results stay indexed by x) */)
 {
     extern __shared__ float s_range[];   // the rectangle's pixels (when they fit)
+    const int rq = slist ? slist[blockIdx.x] : (int)blockIdx.x;
     __shared__ float s_rs, s_sqr;
     __shared__ unsigned long long s_bound;   // bit pattern of the best score found so far by this CTA (+inf at start)
     const int tid = threadIdx.x;
     if (tid == 0) s_bound = 0x7ff0000000000000ull;
-    const int ri = rects[4 * blockIdx.x], rj = rects[4 * blockIdx.x + 1], w = rects[4 * blockIdx.x + 2],
-              hgt = rects[4 * blockIdx.x + 3];
+    const int ri = rects[4 * (size_t)rq], rj = rects[4 * (size_t)rq + 1], w = rects[4 * (size_t)rq + 2],
+              hgt = rects[4 * (size_t)rq + 3];
     const int nn = w * hgt;
     const bool in_smem = nn <= smem_px;
     if (in_smem)
@@ -500,7 +590,7 @@ static int hv_search_launch(fic_handle* h, const uint8_t* d_img, int H, int W, c
     if (S < 1) S = 1;
     if (S == 1) {
         hv_search_kernel<<<dim3(count, 1), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
-                                                                                     offset_bits, d_rec, d_vals, nullptr, smem_px);
+                                                                                     offset_bits, d_rec, d_vals, nullptr, smem_px, nullptr);
         FIC_CHECK_LAUNCH(h, "hv_search_kernel");
         return FIC_OK;
     }
@@ -510,7 +600,7 @@ static int hv_search_launch(fic_handle* h, const uint8_t* d_img, int H, int W, c
     unsigned long long* pseq = reinterpret_cast<unsigned long long*>(pvals + 3 * np_);
     int32_t* prec = reinterpret_cast<int32_t*>(pseq + np_);
     hv_search_kernel<<<dim3(count, S), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
-                                                                                 offset_bits, prec, pvals, pseq, smem_px);
+                                                                                 offset_bits, prec, pvals, pseq, smem_px, nullptr);
     FIC_CHECK_LAUNCH(h, "hv_search_kernel");
     hv_pick_kernel<<<(count + 127) / 128, 128, 0, st>>>(prec, pvals, pseq, count, S, d_rec, d_vals);
     FIC_CHECK_LAUNCH(h, "hv_pick_kernel");
@@ -523,50 +613,6 @@ static int hv_build_pool(fic_handle* h, const uint8_t* d_img, int H, int W, cuda
     hv_pool_kernel<<<dim3((W - 1 + 255) / 256, H - 1), 256, 0, st>>>(d_img, H, W, h->t_hvpool.as<float>());
     FIC_CHECK_LAUNCH(h, "hv_pool_kernel");
     return FIC_OK;
-}
-
-// ---- HV split (hvv2/encoder.py:45-63, 77-82): one warp per rectangle --------------------------------
-// out[k] = {have_v, best_v, have_h, best_h}; outv[k] = {value_v, value_h}
-__global__ void hv_split_kernel(const long long* __restrict__ I1, int W1, const int32_t* __restrict__ rects, int count,
-                                int min_w, int min_h, int32_t* __restrict__ out, double* __restrict__ outv)
-{
-    const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (k >= count) return;
-    const int ri = rects[4 * k], rj = rects[4 * k + 1], w = rects[4 * k + 2], hgt = rects[4 * k + 3];
-    for (int axis = 0; axis < 2; ++axis) {
-        const bool have = axis == 0 ? w > min_w : hgt > min_h;
-        const int L = axis == 0 ? w : hgt;
-        double bv = -__longlong_as_double(0x7ff0000000000000ll);
-        int bk = 0x7fffffff;
-        if (have) {
-            for (int t = lane; t < L - 1; t += 32) {
-                long long s0, s1;
-                if (axis == 0) {  // column sums (np.sum(axis=0))
-                    s0 = box(I1, W1, ri, rj + t, ri + hgt, rj + t + 1);
-                    s1 = box(I1, W1, ri, rj + t + 1, ri + hgt, rj + t + 2);
-                } else {
-                    s0 = box(I1, W1, ri + t, rj, ri + t + 1, rj + w);
-                    s1 = box(I1, W1, ri + t + 1, rj, ri + t + 2, rj + w);
-                }
-                double bt = (double)t, other = DS((double)(L - 1), bt);
-                double bias = DD(bt < other ? bt : other, (double)(L - 1));
-                double v = DM((double)(s0 - s1), bias);
-                if (v > bv || (v == bv && t < bk)) { bv = v; bk = t; }
-            }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                double ov = __shfl_xor_sync(0xffffffffu, bv, off);
-                int ok = __shfl_xor_sync(0xffffffffu, bk, off);
-                if (ov > bv || (ov == bv && ok < bk)) { bv = ov; bk = ok; }
-            }
-        }
-        if (lane == 0) {
-            out[4 * (size_t)k + 2 * axis] = have ? 1 : 0;
-            out[4 * (size_t)k + 2 * axis + 1] = have ? bk : 0;
-            outv[2 * (size_t)k + axis] = have ? bv : 0.0;
-        }
-    }
 }
 
 int hv_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_rects, int count, int scale_bits,
@@ -601,25 +647,74 @@ static int qt_smallest_range(int width, int height)
     return std::min(min_bottom, min_right);
 }
 
-struct QtNode {
-    int si, sj, exp;
-    int kind;       // 0 internal, 1 leaf
-    int child[4];
+// ---- quadtree partition on the device (quadtree/encoder.py:127-146) ----------------------------------------------
+// Node table and one work queue per size exponent live in device memory.  A level = all pending ranges of one size:
+// one search launch, then qt_decide_kernel applies `rms > tolerance and exponent > min_exponent` (encoder.py:134),
+// stores the leaf records or appends the four children (TL, TR, BL, BR) to the node table and to the queue of the next
+// smaller size.  The host reads back one integer per level (how many ranges the next launch has) and, at the end, the
+// node table, from which it emits the preorder stream.
+struct QtNodeDev {
+    int32_t si, sj, exp, kind;    // kind: -1 pending, 0 internal, 1 leaf
+    int32_t child0, pad_;         // the four children are consecutive nodes
     int32_t rec[6];
     double vals[3];
 };
+static_assert(sizeof(QtNodeDev) == 72, "QtNodeDev layout");
+
+// mode 0: decide from the search results; 1: split unconditionally (sizes above max_range_side); 2: side-1 dummy leaves
+__global__ void qt_decide_kernel(const int32_t* __restrict__ queue /*[n][4]*/, int n, int e, int mode, double tol, int min_exp,
+                                 const int32_t* __restrict__ rec, const double* __restrict__ vals, QtNodeDev* __restrict__ nodes,
+                                 int* __restrict__ counts /*[0] = nodes, [1 + e] = queue length of exponent e*/,
+                                 int32_t* __restrict__ next_queue, int node_cap, int next_cap)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const int si = queue[4 * (size_t)q], sj = queue[4 * (size_t)q + 1], id = queue[4 * (size_t)q + 2];
+    QtNodeDev& nd = nodes[id];
+    bool split = mode == 1;
+    if (mode == 0) {
+        const double rms = sqrt(vals[3 * (size_t)q + 2]);   // NaN for a negative error -> comparison false -> leaf
+        split = rms > tol && e > min_exp;
+    }
+    if (!split) {
+        nd.kind = 1;
+        if (mode == 2) {   // side 1: dummy leaf with rms 1e-4 (encoder.py:150-152)
+            for (int k = 0; k < 6; ++k) nd.rec[k] = 0;
+            nd.vals[0] = 0.0; nd.vals[1] = 0.0; nd.vals[2] = 1e-8;
+        } else {
+            for (int k = 0; k < 6; ++k) nd.rec[k] = rec[6 * (size_t)q + k];
+            for (int k = 0; k < 3; ++k) nd.vals[k] = vals[3 * (size_t)q + k];
+        }
+        return;
+    }
+    const int base = atomicAdd(&counts[0], 4);
+    const int at = atomicAdd(&counts[1 + (e - 1)], 4);
+    if (base + 4 > node_cap || at + 4 > next_cap) { counts[40] = 1; return; }   // cannot happen with the host's bounds; flagged
+    nd.kind = 0;
+    nd.child0 = base;
+    const int ns = 1 << (e - 1);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        QtNodeDev ch;
+        ch.si = si + (c >> 1) * ns; ch.sj = sj + (c & 1) * ns; ch.exp = e - 1; ch.kind = -1; ch.child0 = -1; ch.pad_ = 0;
+        for (int k = 0; k < 6; ++k) ch.rec[k] = 0;
+        ch.vals[0] = ch.vals[1] = ch.vals[2] = 0.0;
+        nodes[base + c] = ch;
+        int32_t* qe = next_queue + 4 * (size_t)(at + c);
+        qe[0] = ch.si; qe[1] = ch.sj; qe[2] = base + c; qe[3] = 0;
+    }
+}
 
 // quadtree/encoder.py:111-125: roots in _partition_image order
-static void qt_roots(std::vector<QtNode>& nodes, std::vector<int>& roots, int si, int sj, int width, int height)
+static void qt_roots(std::vector<QtNodeDev>& nodes, int si, int sj, int width, int height)
 {
     int e = ilog2_floor(std::min(width, height));
     int side = 1 << e;
-    QtNode nd{};
-    nd.si = si; nd.sj = sj; nd.exp = e; nd.kind = -1;
-    roots.push_back((int)nodes.size());
+    QtNodeDev nd{};
+    nd.si = si; nd.sj = sj; nd.exp = e; nd.kind = -1; nd.child0 = -1;
     nodes.push_back(nd);
-    if (side < width) qt_roots(nodes, roots, si, sj + side, width - side, height);
-    if (side < height) qt_roots(nodes, roots, si + side, sj, side, height - side);
+    if (side < width) qt_roots(nodes, si, sj + side, width - side, height);
+    if (side < height) qt_roots(nodes, si + side, sj, side, height - side);
 }
 
 int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_bits, int offset_bits, double max_scale,
@@ -643,135 +738,149 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
     const long long* I1 = h->t_int1.as<long long>();
     const long long* I2 = h->t_int2.as<long long>();
 
-    // ---- domain pools (encoder.py:97-109, 261-283): classify on device, stable bucket on host ----
+    // ---- domain pools (encoder.py:97-109, 261-283), built on the device: [offsets(73) | rows] per pool size ----
     const int npools = std::max(0, max_exp + 1 - (min_needed + 1) + 1);
-    std::vector<std::vector<int32_t>> pool_off(npools), pool_rows(npools);
-    for (int k = 0; k < npools; ++k) {
-        const int side = 1 << (min_needed + 1 + k);
-        const int hs = hstep_in == -1 ? side : hstep_in, vs = vstep_in == -1 ? side : vstep_in;
-        const int nv = H - side >= 0 ? 1 + (H - side) / vs : 0, nh = W - side >= 0 ? 1 + (W - side) / hs : 0;
-        const size_t cnt = (size_t)nv * nh;
-        std::vector<int32_t> cls(cnt * 3);
-        if (cnt) {
-            FIC_TRY(h->t_cls.reserve(cnt * 3 * sizeof(int32_t)));
-            classify_grid_kernel<<<(unsigned)((cnt + 127) / 128), 128, 0, st>>>(I1, I2, W + 1, side, nv, nh, vs, hs, h->t_cls.as<int32_t>());
-            FIC_CHECK_LAUNCH(h, "classify_grid_kernel");
-            FIC_TRY(fic_copy_out(h, cls.data(), h->t_cls.p, cnt * 3 * sizeof(int32_t), false, st));
-            FIC_TRY(fic_sync(h, st));
-        }
-        std::vector<int32_t>& off = pool_off[k];
-        off.assign(73, 0);
-        for (size_t p = 0; p < cnt; ++p) off[cls[3 * p] + 1]++;
-        for (int c = 0; c < 72; ++c)
-            if (off[c + 1] == 0) off[c + 1] = 1;  // placeholder row (0,0,0,0), encoder.py:279-280
-        for (int c = 0; c < 72; ++c) off[c + 1] += off[c];
-        std::vector<int32_t>& rows = pool_rows[k];
-        rows.assign((size_t)off[72] * 4, 0);
-        std::vector<int32_t> cur(off.begin(), off.begin() + 72);
-        for (size_t p = 0; p < cnt; ++p) {
-            int c = cls[3 * p];
-            int32_t* r = rows.data() + 4 * (size_t)cur[c]++;
-            r[0] = (int)(p / nh) * vs; r[1] = (int)(p % nh) * hs; r[2] = cls[3 * p + 1]; r[3] = cls[3 * p + 2];
-        }
-    }
-    // upload pools: [off0(73) rows0 | off1(73) rows1 | ...]
     std::vector<size_t> pool_base(npools);
-    size_t tot = 0;
-    for (int k = 0; k < npools; ++k) { pool_base[k] = tot; tot += 73 + pool_rows[k].size(); tot = (tot + 3) & ~(size_t)3; }
+    size_t tot = 0, max_cnt = 0;
+    struct PoolGeom { int side, hs, vs, nv, nh; size_t cnt; };
+    std::vector<PoolGeom> geom(npools);
+    for (int k = 0; k < npools; ++k) {
+        PoolGeom& g = geom[k];
+        g.side = 1 << (min_needed + 1 + k);
+        g.hs = hstep_in == -1 ? g.side : hstep_in;
+        g.vs = vstep_in == -1 ? g.side : vstep_in;
+        g.nv = H - g.side >= 0 ? 1 + (H - g.side) / g.vs : 0;
+        g.nh = W - g.side >= 0 ? 1 + (W - g.side) / g.hs : 0;
+        g.cnt = (size_t)g.nv * g.nh;
+        FIC_REQUIRE(g.cnt < ((size_t)1 << 30), "fic_qt_encode: %zu domains in one pool", g.cnt);
+        pool_base[k] = tot;
+        tot += 73 + 4 * (g.cnt + 72);          // every class may need its placeholder row
+        tot = (tot + 3) & ~(size_t)3;
+        max_cnt = std::max(max_cnt, g.cnt);
+    }
     FIC_TRY(h->t_lists.reserve((tot + 4) * sizeof(int32_t)));
-    {
-        std::vector<int32_t> flat(tot + 4, 0);
-        for (int k = 0; k < npools; ++k) {
-            std::copy(pool_off[k].begin(), pool_off[k].end(), flat.begin() + pool_base[k]);
-            std::copy(pool_rows[k].begin(), pool_rows[k].end(), flat.begin() + pool_base[k] + 73);
+    if (max_cnt) {
+        const size_t max_blocks = (max_cnt + QP_CHUNK - 1) / QP_CHUNK;
+        FIC_TRY(h->t_cls.reserve(max_cnt * 3 * sizeof(int32_t) + max_blocks * 72 * sizeof(int32_t) + 64));
+    }
+    for (int k = 0; k < npools; ++k) {
+        const PoolGeom& g = geom[k];
+        int32_t* offsets = h->t_lists.as<int32_t>() + pool_base[k];
+        int32_t* rows = offsets + 73;
+        int32_t* cls3 = h->t_cls.as<int32_t>();
+        const int nblocks = (int)((g.cnt + QP_CHUNK - 1) / QP_CHUNK);
+        int32_t* blockhist = cls3 + ((max_cnt * 3 + 3) & ~(size_t)3);
+        if (g.cnt) {
+            classify_grid_kernel<<<(unsigned)((g.cnt + 127) / 128), 128, 0, st>>>(I1, I2, W + 1, g.side, g.nv, g.nh, g.vs, g.hs, cls3);
+            FIC_CHECK_LAUNCH(h, "classify_grid_kernel");
+            qt_pool_count_kernel<<<nblocks, QP_THREADS, 0, st>>>(cls3, (int)g.cnt, blockhist);
+            FIC_CHECK_LAUNCH(h, "qt_pool_count_kernel");
         }
-        FIC_CUDA(cudaMemcpyAsync(h->t_lists.p, flat.data(), flat.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        h->counters[CNT_H2D] += (int64_t)(flat.size() * sizeof(int32_t));
-        FIC_TRY(fic_sync(h, st));
+        qt_pool_scan_kernel<<<1, 96, 0, st>>>(blockhist, nblocks, offsets, rows);
+        FIC_CHECK_LAUNCH(h, "qt_pool_scan_kernel");
+        if (g.cnt) {
+            qt_pool_scatter_kernel<<<nblocks, QP_THREADS, 0, st>>>(cls3, (int)g.cnt, g.nh, g.vs, g.hs, blockhist, offsets, rows);
+            FIC_CHECK_LAUNCH(h, "qt_pool_scatter_kernel");
+        }
     }
 
-    // ---- level-synchronous partition (encoder.py:127-146) ----
-    std::vector<QtNode> nodes;
-    std::vector<int> roots;
-    qt_roots(nodes, roots, 0, 0, W, H);
+    // ---- level-synchronous partition (encoder.py:127-146), decisions on the device ----
+    std::vector<QtNodeDev> nodes;
+    qt_roots(nodes, 0, 0, W, H);
+    const int n_root = (int)nodes.size();
     int top = 0;
-    for (int r : roots) top = std::max(top, nodes[r].exp);
-    std::vector<std::vector<int>> pending(top + 1);
-    for (int r : roots) pending[nodes[r].exp].push_back(r);
-    const int nmodes = onlypos ? 1 : 2;
+    for (const QtNodeDev& r : nodes) top = std::max(top, r.exp);
+    FIC_REQUIRE(top < 32, "fic_qt_encode: image too large");
+    // capacity: a node of exponent e exists at most once per aligned 2^e cell of its root; ragged images add the roots
+    std::vector<size_t> qcap(top + 1), qoff(top + 2, 0);
+    size_t node_cap = n_root;
+    const int low = std::max(0, std::min(min_exp, max_exp));   // splits stop here (forced ones at max_exp, the others at min_exp)
     for (int e = top; e >= 0; --e) {
-        std::vector<int>& cur = pending[e];
-        if (cur.empty()) continue;
-        std::vector<int> to_split;
-        if (e > max_exp) {
-            to_split = cur;
-        } else if (e == 0) {  // side 1: dummy leaf, rms 1e-4 (encoder.py:150-152)
-            for (int id : cur) {
-                QtNode& nd = nodes[id];
-                nd.kind = 1;
-                memset(nd.rec, 0, sizeof(nd.rec));
-                nd.vals[0] = nd.vals[1] = 0.0;
-                nd.vals[2] = 1e-8;
-                // rms 1e-4 > tol could still ask for a split, but exp 0 > min_exp never holds
-            }
-        } else {
-            const int n = (int)cur.size();
+        // roots of a ragged image can have any exponent down to 0; split children exist from `low` upwards
+        qcap[e] = (e >= low ? (size_t)((H >> e) + 1) * ((W >> e) + 1) : 0) + n_root + 4;
+        node_cap += e < top && e >= low ? qcap[e] : 0;
+    }
+    for (int e = 0; e <= top; ++e) qoff[e + 1] = qoff[e] + qcap[e] * 4;
+    FIC_REQUIRE(node_cap < ((size_t)1 << 30), "fic_qt_encode: image too large");
+    FIC_TRY(h->t_work.reserve(qoff[top + 1] * sizeof(int32_t) + 64));
+    FIC_TRY(h->t_nodes.reserve(node_cap * sizeof(QtNodeDev) + 64));
+    FIC_TRY(h->t_count.reserve(64 * sizeof(int)));
+    FIC_TRY(h->pin_a.reserve(256 + 64 * sizeof(int)));
+    int32_t* d_queue = h->t_work.as<int32_t>();
+    QtNodeDev* d_nodes = h->t_nodes.as<QtNodeDev>();
+    int* d_counts = h->t_count.as<int>();
+    int* h_counts = h->pin_a.as<int>() + 64;     // pinned: [0] nodes, [1 + e] queue lengths, [40] overflow flag
+    {
+        // initial state: the roots, each in the queue of its exponent
+        std::vector<int> qn(top + 1, 0);
+        std::vector<std::vector<int32_t>> init(top + 1);
+        for (int r = 0; r < n_root; ++r) {
+            const int e = nodes[r].exp;
+            init[e].insert(init[e].end(), {nodes[r].si, nodes[r].sj, r, 0});
+            qn[e]++;
+        }
+        memset(h_counts, 0, 64 * sizeof(int));
+        h_counts[0] = n_root;
+        for (int e = 0; e <= top; ++e) h_counts[1 + e] = qn[e];
+        FIC_CUDA(cudaMemcpyAsync(d_counts, h_counts, 64 * sizeof(int), cudaMemcpyHostToDevice, st));
+        FIC_CUDA(cudaMemcpyAsync(d_nodes, nodes.data(), (size_t)n_root * sizeof(QtNodeDev), cudaMemcpyHostToDevice, st));
+        for (int e = 0; e <= top; ++e)
+            if (qn[e])
+                FIC_CUDA(cudaMemcpyAsync(d_queue + qoff[e], init[e].data(), init[e].size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        FIC_TRY(fic_sync(h, st));     // the staging vectors go out of scope
+        h->counters[CNT_H2D] += (int64_t)(64 * sizeof(int) + (size_t)n_root * (sizeof(QtNodeDev) + 16));
+    }
+    const int nmodes = onlypos ? 1 : 2;
+    int n_level = h_counts[1 + top];
+    for (int e = top; e >= 0; --e) {
+        if (e < top) n_level = h_counts[1 + e];
+        if (n_level == 0) continue;
+        const int n = n_level;
+        FIC_REQUIRE((size_t)n <= qcap[e], "fic_qt_encode: internal: queue of exponent %d overflows", e);
+        const int32_t* queue = d_queue + qoff[e];
+        int32_t* next_queue = e > 0 ? d_queue + qoff[e - 1] : nullptr;
+        const int next_cap = e > 0 ? (int)qcap[e - 1] : 0;
+        int mode = 0;
+        if (e > max_exp) mode = 1;
+        else if (e == 0) mode = 2;
+        if (mode == 0) {
             const int pk = e - min_needed;
             FIC_REQUIRE(pk >= 0 && pk < npools, "fic_qt_encode: internal: no pool for exponent %d", e);
-            std::vector<int32_t> rng((size_t)n * 2);
-            for (int q = 0; q < n; ++q) { rng[2 * q] = nodes[cur[q]].si; rng[2 * q + 1] = nodes[cur[q]].sj; }
-            FIC_TRY(h->t_work.reserve((size_t)n * 2 * sizeof(int32_t) + 16));
             FIC_TRY(h->t_res.reserve((size_t)n * 6 * sizeof(int32_t) + 16));
             FIC_TRY(h->t_aux.reserve((size_t)n * 3 * sizeof(double) + 16));
-            FIC_CUDA(cudaMemcpyAsync(h->t_work.p, rng.data(), rng.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-            h->counters[CNT_H2D] += (int64_t)(rng.size() * sizeof(int32_t));
             QtPoolDev pool;
             pool.offsets = h->t_lists.as<int32_t>() + pool_base[pk];
             pool.rows = pool.offsets + 73;
-            qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, h->t_work.as<int32_t>(), 1 << e, pool, full, nmodes,
+            qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, 1 << e, pool, full, nmodes,
                                                        max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
                                                        h->t_aux.as<double>());
             FIC_CHECK_LAUNCH(h, "qt_search_kernel");
-            std::vector<int32_t> rec((size_t)n * 6);
-            std::vector<double> vals((size_t)n * 3);
-            FIC_TRY(fic_copy_out(h, rec.data(), h->t_res.p, rec.size() * sizeof(int32_t), false, st));
-            FIC_TRY(fic_copy_out(h, vals.data(), h->t_aux.p, vals.size() * sizeof(double), false, st));
-            FIC_TRY(fic_sync(h, st));  // also keeps `rng` alive until the upload is consumed
-            for (int q = 0; q < n; ++q) {
-                QtNode& nd = nodes[cur[q]];
-                const double rms = sqrt(vals[3 * q + 2]);  // NaN for a negative error -> comparison false -> leaf
-                if (rms > tol && e > min_exp) {
-                    to_split.push_back(cur[q]);
-                } else {
-                    nd.kind = 1;
-                    memcpy(nd.rec, &rec[6 * q], sizeof(nd.rec));
-                    memcpy(nd.vals, &vals[3 * q], sizeof(nd.vals));
-                }
-            }
         }
-        for (int id : to_split) {
-            const int ns = 1 << (e - 1);
-            const int si = nodes[id].si, sj = nodes[id].sj;
-            nodes[id].kind = 0;
-            const int ci[4] = {si, si, si + ns, si + ns}, cj[4] = {sj, sj + ns, sj, sj + ns};  // TL,TR,BL,BR
-            for (int c = 0; c < 4; ++c) {
-                QtNode ch{};
-                ch.si = ci[c]; ch.sj = cj[c]; ch.exp = e - 1; ch.kind = -1;
-                nodes[id].child[c] = (int)nodes.size();
-                pending[e - 1].push_back((int)nodes.size());
-                nodes.push_back(ch);
-            }
+        qt_decide_kernel<<<(n + 127) / 128, 128, 0, st>>>(queue, n, e, mode, tol, min_exp, h->t_res.as<int32_t>(), h->t_aux.as<double>(),
+                                                          d_nodes, d_counts, next_queue, (int)node_cap, next_cap);
+        FIC_CHECK_LAUNCH(h, "qt_decide_kernel");
+        if (e > 0) {   // the one number the next launch needs
+            FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+            FIC_TRY(fic_sync(h, st));
+            h->counters[CNT_D2H] += 64 * sizeof(int);
+            FIC_REQUIRE(h_counts[40] == 0, "fic_qt_encode: internal: node table overflow");
         }
     }
-    // ---- preorder emission ----
+    // ---- node table back, preorder emission ----
+    FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    FIC_TRY(fic_sync(h, st));
+    const int n_nodes = h_counts[0];
+    nodes.resize(n_nodes);
+    FIC_TRY(fic_copy_out(h, nodes.data(), d_nodes, (size_t)n_nodes * sizeof(QtNodeDev), false, st));
+    FIC_TRY(fic_sync(h, st));
     int count = 0;
     std::vector<int> stack;
-    for (int r : roots) {
+    for (int r = 0; r < n_root; ++r) {
         stack.push_back(r);
         while (!stack.empty()) {
             int id = stack.back();
             stack.pop_back();
-            const QtNode& nd = nodes[id];
+            const QtNodeDev& nd = nodes[id];
             if (count >= cap) { fic_set_error("fic_qt_encode: node capacity %d too small", cap); return FIC_ECAP; }
             int32_t* o = out_nodes + 8 * (size_t)count;
             double* v = out_vals + 3 * (size_t)count;
@@ -780,21 +889,190 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             for (int k = 0; k < 3; ++k) v[k] = nd.kind == 1 ? nd.vals[k] : 0.0;
             ++count;
             if (nd.kind == 0)
-                for (int c = 3; c >= 0; --c) stack.push_back(nd.child[c]);
+                for (int c = 3; c >= 0; --c) stack.push_back(nd.child0 + c);
         }
     }
-    if (n_roots) *n_roots = (int32_t)roots.size();
+    if (n_roots) *n_roots = (int32_t)n_root;
     return count;
 }
 
-struct HvNode {
-    int i, j, w, h;
-    int kind;  // 0 internal, 1 leaf
-    int vertical, split;
-    int c1, c2;
+// ---- HV partition on the device (hvv2/encoder.py:35-82) -------------------------------------------------------------
+// One level = all rectangles of one tree depth.  The level's rectangles, node ids and flags (bit 0: small enough to be
+// searched, bit 1: large enough to be split) sit in device arrays; after the search and split launches hv_decide_kernel
+// applies `err < threshold` / "cannot be split any further" (encoder.py:36-43), stores leaf records in the node table or
+// appends the two children (child 1 keeps split + 1 columns / rows) to the node table and to the next level's arrays.
+// The host reads back one integer per level -- the size of the next one -- and the node table at the end.
+struct HvNodeDev {
+    int32_t i, j, w, h;
+    int32_t kind;           // -1 pending, 0 internal, 1 leaf
+    int32_t vertical, split, c1;   // children c1, c1 + 1
     int32_t rec[6];
     double vals[3];
 };
+static_assert(sizeof(HvNodeDev) == 80, "HvNodeDev layout");
+
+__host__ __device__ __forceinline__ int hv_flags(int w, int hgt, int min_w, int min_h, int max_w, int max_h)
+{
+    const bool small = w <= min_w && hgt <= min_h;              // must become a leaf (searched whatever the maximum says)
+    const bool fits = w <= max_w && hgt <= max_h;               // searched
+    return (fits || small ? 1 : 0) | (!small ? 2 : 0);
+}
+
+// One warp per rectangle of the level: merges the chunk winners of its search (hv_pick_kernel's rule), finds the split
+// (hv_split_kernel's rule) and decides.  counts: [0] nodes, [1 + parity] size of the next level (the other one is the
+// current level's and is cleared here for the level after next), [3] error flag (1 = a rectangle that must be split cannot
+// be, 2 = capacity), [4 + parity] number of rectangles of the next level that will be searched.
+// Level arrays (level_cap entries each): rects[4], ids, flags, sidx (index into the search results, -1 = not searched),
+// slist (the rectangles to search, compacted).
+__global__ void hv_decide_kernel(const long long* __restrict__ I1, int W1, const int32_t* __restrict__ rects,
+                                 const int32_t* __restrict__ ids, const int32_t* __restrict__ flags,
+                                 const int32_t* __restrict__ sidx, int n,
+                                 const int32_t* __restrict__ prec, const double* __restrict__ pvals,
+                                 const unsigned long long* __restrict__ pseq, int S, double thr, int min_w, int min_h, int max_w,
+                                 int max_h, HvNodeDev* __restrict__ nodes, int* __restrict__ counts, int parity,
+                                 int32_t* __restrict__ next_rects, int32_t* __restrict__ next_ids, int32_t* __restrict__ next_flags,
+                                 int32_t* __restrict__ next_sidx, int32_t* __restrict__ next_slist, int node_cap, int level_cap)
+{
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // nobody reads or writes these during this launch
+        counts[1 + (parity ^ 1)] = 0;
+        counts[4 + (parity ^ 1)] = 0;
+    }
+    if (q >= n) return;
+    const int id = ids[q], f = flags[q];
+    const int ri = rects[4 * (size_t)q], rj = rects[4 * (size_t)q + 1], w = rects[4 * (size_t)q + 2], hgt = rects[4 * (size_t)q + 3];
+    HvNodeDev& nd = nodes[id];
+    if (f & 1) {
+        // first strict minimum in scan order over the S chunk winners
+        const size_t k0 = (size_t)sidx[q] * S;
+        int bs = lane < S ? lane : 0;
+        double bR = pvals[3 * (k0 + bs) + 2];
+        unsigned long long bq = pseq[k0 + bs];
+        for (int c = lane + 32; c < S; c += 32) {
+            const double R = pvals[3 * (k0 + c) + 2];
+            const unsigned long long sq = pseq[k0 + c];
+            if (fic_better(R, sq, bR, bq)) { bR = R; bq = sq; bs = c; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double oR = __shfl_xor_sync(0xffffffffu, bR, off);
+            const unsigned long long oq = __shfl_xor_sync(0xffffffffu, bq, off);
+            const int os = __shfl_xor_sync(0xffffffffu, bs, off);
+            if (fic_better(oR, oq, bR, bq) || (oq == bq && os < bs)) { bR = oR; bq = oq; bs = os; }
+        }
+        bs = __shfl_sync(0xffffffffu, bs, 0);
+        const size_t src = k0 + bs;
+        const double err = pvals[3 * src + 2];
+        if (!(f & 2) || err < thr) {   // hvv2/encoder.py:38,42: raw MSE against the threshold
+            if (lane == 0) {
+                nd.kind = 1;
+                for (int k = 0; k < 6; ++k) nd.rec[k] = prec[6 * src + k];
+                for (int k = 0; k < 3; ++k) nd.vals[k] = pvals[3 * src + k];
+            }
+            return;
+        }
+    }
+    // biased-difference split (hvv2/encoder.py:45-63, 77-82)
+    bool have[2];
+    int best_k[2];
+    double best_v[2];
+    for (int axis = 0; axis < 2; ++axis) {
+        have[axis] = axis == 0 ? w > min_w : hgt > min_h;
+        const int L = axis == 0 ? w : hgt;
+        double bv = -__longlong_as_double(0x7ff0000000000000ll);
+        int bk = 0x7fffffff;
+        if (have[axis]) {
+            for (int t = lane; t < L - 1; t += 32) {
+                long long s0, s1;
+                if (axis == 0) {  // column sums (np.sum(axis=0))
+                    s0 = box(I1, W1, ri, rj + t, ri + hgt, rj + t + 1);
+                    s1 = box(I1, W1, ri, rj + t + 1, ri + hgt, rj + t + 2);
+                } else {
+                    s0 = box(I1, W1, ri + t, rj, ri + t + 1, rj + w);
+                    s1 = box(I1, W1, ri + t + 1, rj, ri + t + 2, rj + w);
+                }
+                double bt = (double)t, other = DS((double)(L - 1), bt);
+                double bias = DD(bt < other ? bt : other, (double)(L - 1));
+                double v = DM((double)(s0 - s1), bias);
+                if (v > bv || (v == bv && t < bk)) { bv = v; bk = t; }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                double ov = __shfl_xor_sync(0xffffffffu, bv, off);
+                int ok = __shfl_xor_sync(0xffffffffu, bk, off);
+                if (ov > bv || (ov == bv && ok < bk)) { bv = ov; bk = ok; }
+            }
+        }
+        best_k[axis] = have[axis] ? bk : 0;
+        best_v[axis] = have[axis] ? bv : 0.0;
+    }
+    if (lane != 0) return;
+    if (!have[0] && !have[1]) { counts[3] = 1; return; }
+    bool vertical;
+    if (!have[0]) vertical = false;
+    else if (!have[1]) vertical = true;
+    else vertical = fabs(best_v[0]) > fabs(best_v[1]);  // encoder.py:63
+    const int s = vertical ? best_k[0] : best_k[1];
+    const int base = atomicAdd(&counts[0], 2);
+    const int at = atomicAdd(&counts[1 + parity], 2);
+    if (base + 2 > node_cap || at + 2 > level_cap) { counts[3] = 2; return; }
+    nd.kind = 0;
+    nd.vertical = vertical ? 1 : 0;
+    nd.split = s;
+    nd.c1 = base;
+    HvNodeDev a, b;
+    if (vertical) {
+        a.i = ri; a.j = rj; a.w = s + 1; a.h = hgt;
+        b.i = ri; b.j = rj + s + 1; b.w = w - s - 1; b.h = hgt;
+    } else {
+        a.i = ri; a.j = rj; a.w = w; a.h = s + 1;
+        b.i = ri + s + 1; b.j = rj; b.w = w; b.h = hgt - s - 1;
+    }
+    a.kind = b.kind = -1;
+    a.vertical = b.vertical = a.split = b.split = 0;
+    a.c1 = b.c1 = -1;
+    for (int k = 0; k < 6; ++k) a.rec[k] = b.rec[k] = 0;
+    for (int k = 0; k < 3; ++k) a.vals[k] = b.vals[k] = 0.0;
+    nodes[base] = a;
+    nodes[base + 1] = b;
+    const HvNodeDev* ch[2] = {&a, &b};
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        int32_t* r = next_rects + 4 * (size_t)(at + c);
+        r[0] = ch[c]->i; r[1] = ch[c]->j; r[2] = ch[c]->w; r[3] = ch[c]->h;
+        next_ids[at + c] = base + c;
+        const int cf = hv_flags(ch[c]->w, ch[c]->h, min_w, min_h, max_w, max_h);
+        next_flags[at + c] = cf;
+        int k = -1;
+        if (cf & 1) {
+            k = atomicAdd(&counts[4 + parity], 1);
+            next_slist[k] = at + c;
+        }
+        next_sidx[at + c] = k;
+    }
+}
+
+// the search of one level with the chunk winners left in the handle's partial buffers (hv_decide_kernel merges them)
+static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_rects, const int32_t* d_slist,
+                           int count, int max_px, int scale_bits, int offset_bits, double max_scale, int* S_out,
+                           const int32_t** prec_out, const double** pvals_out, const unsigned long long** pseq_out, cudaStream_t st)
+{
+    const float* Dp = h->t_hvpool.as<float>();
+    const int smem_px = max_px <= 10240 ? max_px : 0;
+    int S = (4 * h->num_sms + count - 1) / count;      // aim at >= 4 CTAs per SM
+    if (S > 64) S = 64;
+    if (S < 1) S = 1;
+    const size_t np_ = (size_t)count * S;
+    FIC_TRY(h->t_part.reserve(np_ * (6 * sizeof(int32_t) + 3 * sizeof(double) + sizeof(unsigned long long)) + 64));
+    double* pvals = h->t_part.as<double>();
+    unsigned long long* pseq = reinterpret_cast<unsigned long long*>(pvals + 3 * np_);
+    int32_t* prec = reinterpret_cast<int32_t*>(pseq + np_);
+    hv_search_kernel<<<dim3(count, S), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
+                                                                                 offset_bits, prec, pvals, pseq, smem_px, d_slist);
+    FIC_CHECK_LAUNCH(h, "hv_search_kernel");
+    *S_out = S; *prec_out = prec; *pvals_out = pvals; *pseq_out = pseq;
+    return FIC_OK;
+}
 
 int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h, int min_w, int max_h, int max_w,
                    int scale_bits, int offset_bits, double thr, double max_scale, int32_t* out_nodes, double* out_vals,
@@ -803,103 +1081,87 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
     FIC_TRY(build_integrals(h, d_img, H, W, st));
     FIC_TRY(hv_build_pool(h, d_img, H, W, st));
     const long long* I1 = h->t_int1.as<long long>();
-    std::vector<HvNode> nodes;
-    {
-        HvNode root{};
-        root.i = 0; root.j = 0; root.w = W; root.h = H; root.kind = -1;
-        nodes.push_back(root);
-    }
-    std::vector<int> level{0};
-    while (!level.empty()) {
-        // classify the rectangles of this depth (hvv2/encoder.py:36-43)
-        std::vector<int> search, split;           // node ids
-        std::vector<char> must_leaf;              // parallel to `search`
-        for (int id : level) {
-            const HvNode& nd = nodes[id];
-            if (nd.w <= min_w && nd.h <= min_h) { search.push_back(id); must_leaf.push_back(1); }
-            else if (nd.w <= max_w && nd.h <= max_h) { search.push_back(id); must_leaf.push_back(0); split.push_back(id); }
-            else split.push_back(id);
+    // Capacity: a tree over H*W pixels has at most 2*H*W - 1 nodes and H*W rectangles per depth, far more than real
+    // images produce; start from an estimate and run again with more room if the device reports an overflow.
+    const size_t hard = 2 * (size_t)H * W + 64;
+    size_t node_cap = std::min(hard, std::max((size_t)65536, (size_t)H * W / 4));
+    std::vector<HvNodeDev> nodes;
+    for (;;) {
+        const size_t level_cap = std::min((size_t)H * W + 2, node_cap);
+        FIC_REQUIRE(node_cap < ((size_t)1 << 30), "fic_hv_encode: image too large");
+        FIC_TRY(h->t_nodes.reserve(node_cap * sizeof(HvNodeDev) + 64));
+        FIC_TRY(h->t_work.reserve(2 * level_cap * 8 * sizeof(int32_t) + 64));     // two levels x (rect[4], id, flags, sidx, slist)
+        FIC_TRY(h->t_count.reserve(64 * sizeof(int)));
+        FIC_TRY(h->pin_a.reserve(256 + 64 * sizeof(int)));
+        HvNodeDev* d_nodes = h->t_nodes.as<HvNodeDev>();
+        int* d_counts = h->t_count.as<int>();
+        int* h_counts = h->pin_a.as<int>() + 64;
+        int n_search = 0;
+        int32_t* lvl[2] = {h->t_work.as<int32_t>(), h->t_work.as<int32_t>() + level_cap * 8};
+        {
+            HvNodeDev root{};
+            root.i = 0; root.j = 0; root.w = W; root.h = H; root.kind = -1; root.c1 = -1;
+            const int f = hv_flags(W, H, min_w, min_h, max_w, max_h);
+            int32_t first[8] = {0, 0, W, H, 0, f, (f & 1) ? 0 : -1, 0};
+            memset(h_counts, 0, 8 * sizeof(int));
+            h_counts[0] = 1;
+            FIC_CUDA(cudaMemcpyAsync(d_counts, h_counts, 8 * sizeof(int), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(d_nodes, &root, sizeof(root), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0], first, 4 * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 4, first + 4, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 5, first + 5, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 6, first + 6, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 7, first + 7, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_TRY(fic_sync(h, st));
+            n_search = (f & 1) ? 1 : 0;
         }
-        const int ns = (int)search.size(), np = (int)split.size();
-        std::vector<int32_t> rects((size_t)(ns + np) * 4);
-        for (int q = 0; q < ns; ++q) { const HvNode& nd = nodes[search[q]]; int32_t* r = &rects[4 * (size_t)q]; r[0] = nd.i; r[1] = nd.j; r[2] = nd.w; r[3] = nd.h; }
-        for (int q = 0; q < np; ++q) { const HvNode& nd = nodes[split[q]]; int32_t* r = &rects[4 * (size_t)(ns + q)]; r[0] = nd.i; r[1] = nd.j; r[2] = nd.w; r[3] = nd.h; }
-        FIC_TRY(h->t_work.reserve(rects.size() * sizeof(int32_t) + 16));
-        FIC_TRY(h->t_res.reserve((size_t)(ns * 6 + np * 4) * sizeof(int32_t) + 16));
-        FIC_TRY(h->t_aux.reserve((size_t)(ns * 3 + np * 2) * sizeof(double) + 16));
-        FIC_CUDA(cudaMemcpyAsync(h->t_work.p, rects.data(), rects.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        h->counters[CNT_H2D] += (int64_t)(rects.size() * sizeof(int32_t));
-        int32_t* d_rects = h->t_work.as<int32_t>();
-        int32_t* d_rec = h->t_res.as<int32_t>();
-        int32_t* d_split = d_rec + (size_t)ns * 6;
-        double* d_vals = h->t_aux.as<double>();
-        double* d_splitv = d_vals + (size_t)ns * 3;
-        if (ns) {
-            int max_px = 1;
-            for (int q = 0; q < ns; ++q) { const HvNode& nd = nodes[search[q]]; if (nd.w * nd.h > max_px) max_px = nd.w * nd.h; }
-            FIC_TRY(hv_search_launch(h, d_img, H, W, d_rects, ns, max_px, scale_bits, offset_bits, max_scale, d_rec, d_vals, st));
+        int n = 1, cur = 0, fault = 0, parity = 0;
+        const int max_px = max_w * max_h > 0 ? max_w * max_h : 1;   // searched rectangles are at most max_w x max_h
+        while (n > 0) {
+            const int32_t* rects = lvl[cur];
+            const int32_t* ids = lvl[cur] + level_cap * 4;
+            const int32_t* flags = lvl[cur] + level_cap * 5;
+            const int32_t* sidx = lvl[cur] + level_cap * 6;
+            const int32_t* slist = lvl[cur] + level_cap * 7;
+            int32_t* nrects = lvl[cur ^ 1];
+            int S = 1;
+            const int32_t* prec = nullptr;
+            const double* pvals = nullptr;
+            const unsigned long long* pseq = nullptr;
+            if (n_search)
+                FIC_TRY(hv_search_level(h, d_img, H, W, rects, slist, n_search, max_px, scale_bits, offset_bits, max_scale, &S, &prec,
+                                        &pvals, &pseq, st));
+            hv_decide_kernel<<<(n * 32 + 127) / 128, 128, 0, st>>>(I1, W + 1, rects, ids, flags, sidx, n, prec, pvals, pseq, S, thr,
+                                                                   min_w, min_h, max_w, max_h, d_nodes, d_counts, parity, nrects,
+                                                                   nrects + level_cap * 4, nrects + level_cap * 5,
+                                                                   nrects + level_cap * 6, nrects + level_cap * 7, (int)node_cap,
+                                                                   (int)level_cap);
+            FIC_CHECK_LAUNCH(h, "hv_decide_kernel");
+            // the two numbers the host needs: the size of the next level and how many of its rectangles are searched
+            FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+            FIC_TRY(fic_sync(h, st));
+            h->counters[CNT_D2H] += 8 * sizeof(int);
+            fault = h_counts[3];
+            if (fault) break;
+            n = h_counts[1 + parity];
+            n_search = h_counts[4 + parity];
+            parity ^= 1;
+            cur ^= 1;
         }
-        if (np) {
-            hv_split_kernel<<<(np * 32 + 127) / 128, 128, 0, st>>>(I1, W + 1, d_rects + (size_t)ns * 4, np, min_w, min_h, d_split, d_splitv);
-            FIC_CHECK_LAUNCH(h, "hv_split_kernel");
-        }
-        std::vector<int32_t> rec((size_t)ns * 6 + (size_t)np * 4);
-        std::vector<double> vals((size_t)ns * 3 + (size_t)np * 2);
-        FIC_TRY(fic_copy_out(h, rec.data(), d_rec, rec.size() * sizeof(int32_t), false, st));
-        FIC_TRY(fic_copy_out(h, vals.data(), d_vals, vals.size() * sizeof(double), false, st));
+        if (fault == 2 && node_cap < hard) { node_cap = std::min(hard, node_cap * 4); continue; }
+        FIC_REQUIRE(fault == 0, fault == 1 ? "fic_hv_encode: internal: a rectangle that must be split cannot be"
+                                           : "fic_hv_encode: internal: node table overflow");
+        nodes.resize(h_counts[0]);
+        FIC_TRY(fic_copy_out(h, nodes.data(), d_nodes, nodes.size() * sizeof(HvNodeDev), false, st));
         FIC_TRY(fic_sync(h, st));
-        std::vector<char> is_leaf(nodes.size(), 0);
-        for (int q = 0; q < ns; ++q) {
-            HvNode& nd = nodes[search[q]];
-            const double err = vals[3 * (size_t)q + 2];
-            if (must_leaf[q] || err < thr) {  // hvv2/encoder.py:38,42: raw MSE against the threshold
-                nd.kind = 1;
-                memcpy(nd.rec, &rec[6 * (size_t)q], sizeof(nd.rec));
-                memcpy(nd.vals, &vals[3 * (size_t)q], sizeof(nd.vals));
-                is_leaf[search[q]] = 1;
-            }
-        }
-        std::vector<int> next;
-        for (int q = 0; q < np; ++q) {
-            const int id = split[q];
-            if (is_leaf[id]) continue;
-            const int32_t* sp = &rec[(size_t)ns * 6 + 4 * (size_t)q];
-            const double* sv = &vals[(size_t)ns * 3 + 2 * (size_t)q];
-            const bool have_v = sp[0] != 0, have_h = sp[2] != 0;
-            FIC_REQUIRE(have_v || have_h, "fic_hv_encode: internal: rectangle %dx%d cannot be split", nodes[id].w, nodes[id].h);
-            bool vertical;
-            if (!have_v) vertical = false;
-            else if (!have_h) vertical = true;
-            else vertical = fabs(sv[0]) > fabs(sv[1]);  // encoder.py:63
-            const int s = vertical ? sp[1] : sp[3];
-            HvNode a{}, b{};
-            const HvNode nd = nodes[id];
-            if (vertical) {
-                a.i = nd.i; a.j = nd.j; a.w = s + 1; a.h = nd.h;
-                b.i = nd.i; b.j = nd.j + s + 1; b.w = nd.w - s - 1; b.h = nd.h;
-            } else {
-                a.i = nd.i; a.j = nd.j; a.w = nd.w; a.h = s + 1;
-                b.i = nd.i + s + 1; b.j = nd.j; b.w = nd.w; b.h = nd.h - s - 1;
-            }
-            a.kind = b.kind = -1;
-            nodes[id].kind = 0;
-            nodes[id].vertical = vertical ? 1 : 0;
-            nodes[id].split = s;
-            nodes[id].c1 = (int)nodes.size();
-            nodes.push_back(a);
-            nodes[id].c2 = (int)nodes.size();
-            nodes.push_back(b);
-            next.push_back(nodes[id].c1);
-            next.push_back(nodes[id].c2);
-        }
-        level.swap(next);
+        break;
     }
     int count = 0;
     std::vector<int> stack{0};
     while (!stack.empty()) {
         int id = stack.back();
         stack.pop_back();
-        const HvNode& nd = nodes[id];
+        const HvNodeDev& nd = nodes[id];
         if (count >= cap) { fic_set_error("fic_hv_encode: node capacity %d too small", cap); return FIC_ECAP; }
         int32_t* o = out_nodes + 8 * (size_t)count;
         double* v = out_vals + 3 * (size_t)count;
@@ -911,7 +1173,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             for (int k = 0; k < 3; ++k) v[k] = nd.vals[k];
         } else {
             o[0] = 0; o[1] = nd.vertical; o[2] = nd.split;
-            stack.push_back(nd.c2);
+            stack.push_back(nd.c1 + 1);
             stack.push_back(nd.c1);
         }
         ++count;
