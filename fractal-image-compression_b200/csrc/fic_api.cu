@@ -129,6 +129,7 @@ int fic_destroy(fic_handle* h)
     h->pin_b.release();
     h->pin_out.release();
     h->pin_stage.release();
+    h->pin_tree.release();
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
     cudaEventDestroy(h->tail);
     cudaStreamDestroy(h->own_stream);

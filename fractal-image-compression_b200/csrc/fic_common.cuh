@@ -111,7 +111,7 @@ struct fic_handle {
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     // generic staging
     DevBuf d_img, d_out_a, d_out_b, d_out_c, d_in_a, d_in_b;
-    PinnedBuf pin_a, pin_b, pin_out, pin_stage;
+    PinnedBuf pin_a, pin_b, pin_out, pin_stage, pin_tree;
     // Device -> host results are staged in pinned memory (a copy into pageable memory is a blocking, driver-staged transfer)
     // and handed to the caller's buffers at the next fic_sync() of the stream.
     struct PendingOut { void* dst; size_t at, bytes; };

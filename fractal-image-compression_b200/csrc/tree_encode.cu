@@ -705,6 +705,48 @@ __global__ void qt_decide_kernel(const int32_t* __restrict__ queue /*[n][4]*/, i
     }
 }
 
+// Sizes above max_range_side are split without a search (encoder.py:131-133), so the tree down to that size is known
+// in advance: one launch builds it for every root.  A root of exponent E with D = E - max_exp forced levels owns
+// (4^(D+1) - 4) / 3 descendants, numbered level by level behind `sub_base`: node m of level d (its path in base 4, first
+// split in the top digit) sits at sub_base + (4^d - 4)/3 + m and its children at level d + 1, 4m .. 4m + 3 (TL, TR, BL, BR).
+// The nodes of the last level go to the queue of exponent max_exp at q_base + m.
+struct QtForcedRoot { int32_t node, si, sj, exp, depth, sub_base, q_base, first_thread; };
+
+__global__ void qt_forced_kernel(const QtForcedRoot* __restrict__ roots, int n_roots, int total_threads, QtNodeDev* __restrict__ nodes,
+                                 int32_t* __restrict__ queue)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total_threads) return;
+    int r = 0;
+    while (r + 1 < n_roots && roots[r + 1].first_thread <= t) ++r;     // a handful of roots
+    const QtForcedRoot R = roots[r];
+    int local = t - R.first_thread;     // index among the root's descendants, level order
+    int d = 1, level_start = 0, level_size = 4;
+    while (local >= level_start + level_size) { level_start += level_size; level_size *= 4; ++d; }
+    const int m = local - level_start;
+    int si = R.si, sj = R.sj;
+    for (int k = d - 1; k >= 0; --k) {          // digits of m, first split first
+        const int c = (m >> (2 * k)) & 3;
+        const int half = 1 << (R.exp - (d - k));
+        si += (c >> 1) * half;
+        sj += (c & 1) * half;
+    }
+    QtNodeDev nd;
+    nd.si = si; nd.sj = sj; nd.exp = R.exp - d; nd.pad_ = 0;
+    for (int k = 0; k < 6; ++k) nd.rec[k] = 0;
+    nd.vals[0] = nd.vals[1] = nd.vals[2] = 0.0;
+    if (d < R.depth) {
+        nd.kind = 0;
+        nd.child0 = R.sub_base + level_start + level_size + 4 * m;
+    } else {
+        nd.kind = -1;
+        nd.child0 = -1;
+        int32_t* qe = queue + 4 * (size_t)(R.q_base + m);
+        qe[0] = si; qe[1] = sj; qe[2] = R.sub_base + local; qe[3] = 0;
+    }
+    nodes[R.sub_base + local] = nd;
+}
+
 // quadtree/encoder.py:111-125: roots in _partition_image order
 static void qt_roots(std::vector<QtNodeDev>& nodes, int si, int sj, int width, int height)
 {
@@ -810,32 +852,78 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
     QtNodeDev* d_nodes = h->t_nodes.as<QtNodeDev>();
     int* d_counts = h->t_count.as<int>();
     int* h_counts = h->pin_a.as<int>() + 64;     // pinned: [0] nodes, [1 + e] queue lengths, [40] overflow flag
+    // ---- initial state: the roots; the levels above max_range_side, which split without a search, in one launch ----
+    int start_exp = top;      // first exponent whose queue needs the level loop
     {
-        // initial state: the roots, each in the queue of its exponent
+        std::vector<QtForcedRoot> forced;
         std::vector<int> qn(top + 1, 0);
         std::vector<std::vector<int32_t>> init(top + 1);
+        int n_nodes0 = n_root, threads = 0;
+        const int stop = std::max(max_exp, 0);
         for (int r = 0; r < n_root; ++r) {
             const int e = nodes[r].exp;
-            init[e].insert(init[e].end(), {nodes[r].si, nodes[r].sj, r, 0});
-            qn[e]++;
+            if (e > stop) {
+                const int D = e - stop;
+                FIC_REQUIRE(D < 15, "fic_qt_encode: image too large");
+                const int desc = (int)((((long long)1 << (2 * (D + 1))) - 4) / 3);
+                QtForcedRoot fr{r, nodes[r].si, nodes[r].sj, e, D, n_nodes0, qn[stop], threads};
+                forced.push_back(fr);
+                nodes[r].kind = 0;
+                nodes[r].child0 = n_nodes0;
+                n_nodes0 += desc;
+                threads += desc;
+                qn[stop] += 1 << (2 * D);
+            } else {
+                init[e].insert(init[e].end(), {nodes[r].si, nodes[r].sj, r, 0});
+            }
         }
-        memset(h_counts, 0, 64 * sizeof(int));
-        h_counts[0] = n_root;
-        for (int e = 0; e <= top; ++e) h_counts[1 + e] = qn[e];
-        FIC_CUDA(cudaMemcpyAsync(d_counts, h_counts, 64 * sizeof(int), cudaMemcpyHostToDevice, st));
-        FIC_CUDA(cudaMemcpyAsync(d_nodes, nodes.data(), (size_t)n_root * sizeof(QtNodeDev), cudaMemcpyHostToDevice, st));
+        FIC_REQUIRE((size_t)n_nodes0 <= node_cap, "fic_qt_encode: internal: node table too small for the forced levels");
+        // roots that start at or below max_exp sit behind the forced entries of their queue
+        std::vector<int> q_first(top + 1, 0);
+        for (int e = 0; e <= top; ++e) { q_first[e] = qn[e]; qn[e] += (int)init[e].size() / 4; }
+        // one pinned staging block: counts | roots | forced descriptors | queue entries
+        size_t bytes = 64 * sizeof(int) + (size_t)n_root * sizeof(QtNodeDev) + forced.size() * sizeof(QtForcedRoot);
+        for (int e = 0; e <= top; ++e) bytes += init[e].size() * sizeof(int32_t);
+        // (the block belongs to the tree encoders alone and every call of theirs ends with a host wait, so it is free here)
+        FIC_TRY(h->pin_tree.reserve(bytes + 256));
+        FIC_TRY(h->t_aux.reserve(forced.size() * sizeof(QtForcedRoot) + 64));
+        char* stage = h->pin_tree.as<char>();
+        int* c0 = reinterpret_cast<int*>(stage);
+        memset(c0, 0, 64 * sizeof(int));
+        c0[0] = n_nodes0;
+        for (int e = 0; e <= top; ++e) c0[1 + e] = qn[e];
+        memcpy(h_counts, c0, 64 * sizeof(int));
+        size_t at = 64 * sizeof(int);
+        FIC_CUDA(cudaMemcpyAsync(d_counts, c0, 64 * sizeof(int), cudaMemcpyHostToDevice, st));
+        memcpy(stage + at, nodes.data(), (size_t)n_root * sizeof(QtNodeDev));
+        FIC_CUDA(cudaMemcpyAsync(d_nodes, stage + at, (size_t)n_root * sizeof(QtNodeDev), cudaMemcpyHostToDevice, st));
+        at += (size_t)n_root * sizeof(QtNodeDev);
+        if (!forced.empty()) {
+            memcpy(stage + at, forced.data(), forced.size() * sizeof(QtForcedRoot));
+            FIC_CUDA(cudaMemcpyAsync(h->t_aux.p, stage + at, forced.size() * sizeof(QtForcedRoot), cudaMemcpyHostToDevice, st));
+            at += forced.size() * sizeof(QtForcedRoot);
+        }
         for (int e = 0; e <= top; ++e)
-            if (qn[e])
-                FIC_CUDA(cudaMemcpyAsync(d_queue + qoff[e], init[e].data(), init[e].size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        FIC_TRY(fic_sync(h, st));     // the staging vectors go out of scope
-        h->counters[CNT_H2D] += (int64_t)(64 * sizeof(int) + (size_t)n_root * (sizeof(QtNodeDev) + 16));
+            if (!init[e].empty()) {
+                memcpy(stage + at, init[e].data(), init[e].size() * sizeof(int32_t));
+                FIC_CUDA(cudaMemcpyAsync(d_queue + qoff[e] + 4 * (size_t)q_first[e], stage + at, init[e].size() * sizeof(int32_t),
+                                         cudaMemcpyHostToDevice, st));
+                at += init[e].size() * sizeof(int32_t);
+            }
+        h->counters[CNT_H2D] += (int64_t)at;
+        if (threads) {
+            FIC_REQUIRE((size_t)qn[stop] <= qcap[stop], "fic_qt_encode: internal: queue of exponent %d overflows", stop);
+            qt_forced_kernel<<<(threads + 127) / 128, 128, 0, st>>>(h->t_aux.as<QtForcedRoot>(), (int)forced.size(), threads, d_nodes,
+                                                                    d_queue + qoff[stop]);
+            FIC_CHECK_LAUNCH(h, "qt_forced_kernel");
+            start_exp = stop;
+        }
     }
     const int nmodes = onlypos ? 1 : 2;
-    int n_level = h_counts[1 + top];
-    for (int e = top; e >= 0; --e) {
-        if (e < top) n_level = h_counts[1 + e];
-        if (n_level == 0) continue;
-        const int n = n_level;
+    bool counts_fresh = true;      // h_counts mirrors the device counters
+    for (int e = start_exp; e >= 0; --e) {
+        const int n = h_counts[1 + e];
+        if (n == 0) continue;
         FIC_REQUIRE((size_t)n <= qcap[e], "fic_qt_encode: internal: queue of exponent %d overflows", e);
         const int32_t* queue = d_queue + qoff[e];
         int32_t* next_queue = e > 0 ? d_queue + qoff[e - 1] : nullptr;
@@ -847,28 +935,34 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             const int pk = e - min_needed;
             FIC_REQUIRE(pk >= 0 && pk < npools, "fic_qt_encode: internal: no pool for exponent %d", e);
             FIC_TRY(h->t_res.reserve((size_t)n * 6 * sizeof(int32_t) + 16));
-            FIC_TRY(h->t_aux.reserve((size_t)n * 3 * sizeof(double) + 16));
+            FIC_TRY(h->t_part.reserve((size_t)n * 3 * sizeof(double) + 16));
             QtPoolDev pool;
             pool.offsets = h->t_lists.as<int32_t>() + pool_base[pk];
             pool.rows = pool.offsets + 73;
             qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, 1 << e, pool, full, nmodes,
                                                        max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
-                                                       h->t_aux.as<double>());
+                                                       h->t_part.as<double>());
             FIC_CHECK_LAUNCH(h, "qt_search_kernel");
         }
-        qt_decide_kernel<<<(n + 127) / 128, 128, 0, st>>>(queue, n, e, mode, tol, min_exp, h->t_res.as<int32_t>(), h->t_aux.as<double>(),
+        qt_decide_kernel<<<(n + 127) / 128, 128, 0, st>>>(queue, n, e, mode, tol, min_exp, h->t_res.as<int32_t>(), h->t_part.as<double>(),
                                                           d_nodes, d_counts, next_queue, (int)node_cap, next_cap);
         FIC_CHECK_LAUNCH(h, "qt_decide_kernel");
-        if (e > 0) {   // the one number the next launch needs
+        // Can this level have split anything?  Only then does the host need the new queue length (and node count).
+        const bool may_split = mode == 1 || (mode == 0 && e > min_exp);
+        counts_fresh = !may_split;
+        if (may_split && e > 0) {
             FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
             FIC_TRY(fic_sync(h, st));
             h->counters[CNT_D2H] += 64 * sizeof(int);
             FIC_REQUIRE(h_counts[40] == 0, "fic_qt_encode: internal: node table overflow");
+            counts_fresh = true;
         }
     }
     // ---- node table back, preorder emission ----
-    FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    FIC_TRY(fic_sync(h, st));
+    if (!counts_fresh) {
+        FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 64 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        FIC_TRY(fic_sync(h, st));
+    }
     const int n_nodes = h_counts[0];
     nodes.resize(n_nodes);
     FIC_TRY(fic_copy_out(h, nodes.data(), d_nodes, (size_t)n_nodes * sizeof(QtNodeDev), false, st));
