@@ -13,6 +13,32 @@ from quadtree.common import QuadtreeImage, forest_to_leaves
 AUTO = -1
 
 
+def leaf_visiting_order(leaves: np.ndarray, width: int, height: int) -> np.ndarray:
+    """Indices of `leaves` (rows of `forest_to_leaves`) in the order quadtree/decoder.py visits them: the roots in
+    `_de_partition` order (:63-76), every root breadth first with the children queued TL, TR, BL, BR (:78-116) -- inside
+    a root that is by depth, then by the Morton code of the leaf's corner (row bit above column bit)."""
+    from quadtree.common import iter_root_squares
+    L = np.asarray(leaves)
+    row, col, size = L[:, 0].astype(np.int64), L[:, 1].astype(np.int64), L[:, 2].astype(np.int64)
+    key = np.zeros(len(L), np.int64)
+
+    def spread(v):
+        v = v & 0xffff
+        v = (v | (v << 8)) & 0x00ff00ff
+        v = (v | (v << 4)) & 0x0f0f0f0f
+        v = (v | (v << 2)) & 0x33333333
+        v = (v | (v << 1)) & 0x55555555
+        return v
+
+    for r, (ri, rj, e) in enumerate(iter_root_squares(width, height)):
+        side = 1 << e
+        m = (row >= ri) & (row < ri + side) & (col >= rj) & (col < rj + side)
+        depth = e - np.log2(size[m]).astype(np.int64)
+        morton = (spread(row[m] - ri) << 1) | spread(col[m] - rj)
+        key[m] = (np.int64(r) << 40) | (depth << 34) | morton
+    return np.argsort(key, kind="stable")
+
+
 class QuadtreeDecoder:
     def __init__(self, iterations: int = AUTO, stop_on_relative_error: float = 5e-3, min_iterations=2,
                  max_iterations=10, log_stop=False,
@@ -35,9 +61,7 @@ class QuadtreeDecoder:
 
     def decode(self, quadtree_img: QuadtreeImage, postprocessor=None) -> np.ndarray:
         if self.on_domain_decoded is not None:
-            raise NotImplementedError(
-                "on_domain_decoded observes the image after every single leaf (decoder.py:108-110); the GPU decoder "
-                "updates all leaves of a sweep at once")
+            return self._decode_leaf_by_leaf(quadtree_img, postprocessor)
         info = quadtree_img.info
         leaves, so = forest_to_leaves(quadtree_img, self.use_quantized_values)
         # decoder.py:58-61: a post-processor sees the float image, the clip comes after it.  The stock deblocking
@@ -54,6 +78,37 @@ class QuadtreeDecoder:
             out = np.asarray(postprocessor.postprocess(out, quadtree_img)).clip(0., 255.).astype(np.uint8)
         self.img = out
         return out
+
+    def _decode_leaf_by_leaf(self, quadtree_img: QuadtreeImage, postprocessor=None) -> np.ndarray:
+        """`on_domain_decoded(next_img, counter)` after every single leaf (decoder.py:108-110).  The sweeps are Jacobi
+        sweeps -- a leaf reads the previous sweep's image only -- so the image the reference shows its callback after
+        leaf k of sweep s is sweep s for the leaves visited so far and sweep s - 1 everywhere else.  The GPU decodes
+        whole sweeps; this slow path replays them block by block on the host in the reference's visiting order (roots
+        in `_de_partition` order, breadth first inside a root).  Before the first sweep the reference's `next_img` is
+        uninitialised memory (`np.empty_like`); here it is zeros."""
+        info = quadtree_img.info
+        H, W = info.img_height, info.img_width
+        leaves, so = forest_to_leaves(quadtree_img, self.use_quantized_values)
+        # how many sweeps the decode runs (the AUTO rule needs the decode itself to say)
+        _, done = fic_b200.tree_decode(fic_b200.TREE_QUADTREE, leaves, so, H, W, self.iterations,
+                                       self.stop_on_relative_error, self.min_iterations, self.max_iterations)
+        self.iterations_run = done
+        order = leaf_visiting_order(leaves, W, H)
+        self.next_img = np.zeros((H, W), np.float64)
+        for sweep in range(1, done + 1):
+            cur, _ = fic_b200.tree_decode(fic_b200.TREE_QUADTREE, leaves, so, H, W, sweep, out_f64=True)
+            for k in order:
+                i, j, size = int(leaves[k, 0]), int(leaves[k, 1]), int(leaves[k, 2])
+                self.next_img[i:i + size, j:j + size] = cur[i:i + size, j:j + size]
+                self.decoded_counter += 1
+                self.on_domain_decoded(self.next_img, self.decoded_counter)
+        out = self.next_img.copy()
+        if self.log_stop and self.iterations == AUTO and done < self.max_iterations:
+            print(f'Auto decoding stopped after {done - 1} iterations')
+        if postprocessor is not None:
+            out = np.asarray(postprocessor.postprocess(out, quadtree_img))
+        self.img = out.clip(0., 255.).astype(np.uint8)
+        return self.img
 
     def decode_planes_device(self, quadtree_imgs, out_tensors, postprocessor=None) -> None:
         """Decode several images into uint8 device tensors (torch, one per image) without a host round trip of the

@@ -37,9 +37,12 @@ class QuadtreeEncoder:
         self.error_tolerance = error_tolerance
         self.domain_hstep = domain_hstep
         self.domain_vstep = domain_vstep
-        # filled by encode(), kept for parity with the reference's attributes
+        # filled by encode(), kept for parity with the reference's attributes (encoder.py:65-75)
         self.max_square_exponent = None
+        self.min_needed_range_exponent = None
         self.last_stream = None
+        self._domain_lists = None
+        self._pool_source = None      # what `domain_lists` is built from when somebody asks for it
 
     def encode(self, img: np.ndarray) -> QuadtreeImage:
         return self._encode(img, 0, img.shape)
@@ -48,9 +51,37 @@ class QuadtreeEncoder:
         """`encode` of a uint8 [height, width] plane that already lives in device memory (the colour wrapper's planes)."""
         return self._encode(None, img_ptr, (height, width))
 
+    @property
+    def domain_lists(self):
+        """The reference's attribute of the same name (encoder.py:71-75, 261-283): per domain size -- exponents
+        `min_needed_range_exponent + 1 .. max_range_exponent + 1` -- the 3 x 24 class lists of `(start_i, start_j, rotation,
+        orientation)` rows, `[(0, 0, 0, 0)]` for an empty class.  The search itself uses the pools the library builds in
+        device memory; this view is made on first access from the same classification (`fic_qt_classify`)."""
+        if self._domain_lists is None and self._pool_source is not None:
+            img = self._pool_source
+            lists = []
+            for e in range(self.min_needed_range_exponent + 1, self.max_range_exponent + 2):
+                side = 2 ** e
+                hstep = side if self.domain_hstep == SAME_AS_SIDE else self.domain_hstep
+                vstep = side if self.domain_vstep == SAME_AS_SIDE else self.domain_vstep
+                nv, nh = 1 + (img.shape[0] - side) // vstep, 1 + (img.shape[1] - side) // hstep
+                ii, jj = np.meshgrid(np.arange(max(nv, 0)) * vstep, np.arange(max(nh, 0)) * hstep, indexing="ij")
+                blocks = np.stack([ii.ravel(), jj.ravel(), np.full(ii.size, side), np.zeros(ii.size, np.int64)], 1)
+                cls = fic_b200.qt_classify(img, blocks.astype(np.int32)) if len(blocks) else np.zeros((0, 4), np.int32)
+                per_class = [[[] for _ in range(NUM_VARIANCE_CLASSES)] for _ in range(NUM_MEAN_CLASSES)]
+                for (i, j, _, _), (mc, vc, rot, orient) in zip(blocks.tolist(), cls.tolist()):
+                    per_class[mc][vc].append((i, j, rot, orient))
+                lists.append([[np.array(c if c else [(0, 0, 0, 0)], np.int32) for c in row] for row in per_class])
+            self._domain_lists = lists
+        return self._domain_lists
+
     def _encode(self, img, img_ptr: int, shape) -> QuadtreeImage:
         height, width = shape
         self.max_square_exponent = min(int(np.log2(height)), int(np.log2(width)))
+        self.min_needed_range_exponent = min(self.min_range_exponent,
+                                             max(int(np.log2(_smallest_range_size(width, height))), 1))
+        self._domain_lists = None
+        self._pool_source = None if img is None else np.ascontiguousarray(img)
         nodes, vals, n_roots = fic_b200.qt_encode(
             img, self.scale_bits, self.offset_bits, self.max_scale, self.full_class_search, self.only_positive_scale,
             2 ** self.min_range_exponent, 2 ** self.max_range_exponent, self.error_tolerance, self.domain_hstep,
@@ -58,6 +89,22 @@ class QuadtreeEncoder:
         self.last_stream = (nodes, vals, n_roots)
         info = EncodingInfo(self.scale_bits, self.offset_bits, self.max_scale, width, height)
         return QuadtreeImage(info, stream=(nodes, vals, n_roots))   # node objects are built on first access
+
+
+def _smallest_range_size(width: int, height: int) -> int:
+    """encoder.py:81-95: the smallest square the ragged partition of a width x height image contains."""
+    if width == 0:
+        return height
+    if height == 0:
+        return width
+    if width == 1 or height == 1:
+        return 1
+    max_square = 2 ** int(min(np.log2(width), np.log2(height)))
+    if max_square == width and max_square == height:
+        return max_square
+    fits_on_x, fits_on_y = width // max_square, height // max_square
+    return min(_smallest_range_size(fits_on_x * max_square, height - fits_on_y * max_square),
+               _smallest_range_size(width - fits_on_x * max_square, height))
 
 
 def _classify(img: np.ndarray, start_i: int, start_j: int, side: int) -> tuple[int, int, int, int]:

@@ -230,3 +230,100 @@ def test_hv_decoder_follows_either_numpy_promotion_rule(fic, orc, golden):
         assert np.array_equal(dec.decode(hv), want)
     auto = HVDecoder()          # default: the installed NumPy's rule
     assert auto.numpy1_promotion == ((np.zeros(1, np.float32) * np.float64(1.0)).dtype == np.float32)
+
+
+def _reference_style_decode_with_callback(leaves_in_order, so_in_order, H, W, sweeps):
+    """quadtree/decoder.py:34-116 restated with NumPy for a handful of leaves: Jacobi sweeps, `.T` then `rot90`, the
+    int-truncating pool of utils.average_subsample, one snapshot of `next_img` after every leaf (zeros where the
+    reference's `np.empty_like` buffer holds whatever memory it was given)."""
+    img = np.zeros((H, W), np.float64)
+    nxt = np.zeros((H, W), np.float64)
+    shots = []
+    for _ in range(sweeps):
+        for (ri, rj, size, _, di, dj, orient, rot), (scale, offset) in zip(leaves_in_order.tolist(), so_in_order.tolist()):
+            dom = np.copy(img[di:di + 2 * size, dj:dj + 2 * size])
+            if orient == 1:
+                dom = dom.T
+            dom = np.rot90(dom, rot)
+            d = dom.reshape(-1).reshape((-1, dom.shape[1] * 2)).astype(np.int32)
+            x = d[:, :dom.shape[1]] + d[:, dom.shape[1]:]
+            x = x[:, ::2] + x[:, 1::2]
+            nxt[ri:ri + size, rj:rj + size] = x / 4 * scale + offset
+            shots.append(nxt.copy())
+        img[:] = nxt
+    return shots
+
+
+@pytest.mark.parametrize("shape", [(32, 32), (40, 52)])
+def test_quadtree_decoder_leaf_by_leaf_callback(fic, orc, shape):
+    """`on_domain_decoded` (decoder.py:16,27,108-110): the callback sees `next_img` after every single leaf, in the
+    reference's visiting order; checked against a NumPy restatement of the reference's loop, ragged image included."""
+    from quadtree.common import forest_to_leaves
+    from quadtree.decoder import QuadtreeDecoder, leaf_visiting_order
+    from quadtree.encoder import QuadtreeEncoder
+    H, W = shape
+    img = synthetic_image(33, H, W)
+    q = QuadtreeEncoder(7, 5, 1.0, False, False, 4, 8, 2.0).encode(img)
+    leaves, so = forest_to_leaves(q, True)
+    order = leaf_visiting_order(leaves, W, H)
+    nodes, _, n_roots = q.flat_stream()
+    want_rects, _ = orc.qt_visit_order(nodes, n_roots, H, W)
+    assert np.array_equal(leaves[order][:, :3], want_rects)          # same visiting order as the oracle's walk
+    got = []
+    dec = QuadtreeDecoder(iterations=3, on_domain_decoded=lambda im, k: got.append((k, im.copy())))
+    out = dec.decode(q)
+    want = _reference_style_decode_with_callback(leaves[order], so[order], H, W, 3)
+    assert [k for k, _ in got] == list(range(1, 3 * len(leaves) + 1))
+    for (_, a), b in zip(got, want):
+        assert np.array_equal(a, b)
+    assert np.array_equal(out, QuadtreeDecoder(iterations=3).decode(q))
+
+
+def test_auto_stop_follows_the_oracle_across_the_threshold(fic, orc):
+    """The AUTO rule stops when ||next - img||_F / ||next||_F < stop_on_relative_error (decoder.py:45-50).  The device uses
+    a two-stage deterministic float64 reduction where the reference calls np.linalg.norm: thresholds a hair either side
+    of every ratio the decode actually produces must give the same number of sweeps as the oracle."""
+    from quadtree.common import forest_to_leaves
+    from quadtree.encoder import QuadtreeEncoder
+    img = synthetic_image(44, 96, 80)
+    q = QuadtreeEncoder(7, 5, 1.0, False, False, 4, 8, 2.0).encode(img)
+    leaves, so = forest_to_leaves(q, True)
+    H, W = img.shape
+    states = [np.zeros((H, W))] + [fic.tree_decode(fic.TREE_QUADTREE, leaves, so, H, W, k, out_f64=True)[0] for k in range(1, 11)]
+    ratios = [np.linalg.norm(states[k] - states[k - 1]) / np.linalg.norm(states[k]) for k in range(3, 11)]
+    thresholds = [5e-3]
+    for r in ratios:
+        thresholds += [r * (1 - 1e-6), r * (1 + 1e-6), r * (1 - 1e-10), r * (1 + 1e-10)]
+    seen = set()
+    for thr in thresholds:
+        got, n_got = fic.tree_decode(fic.TREE_QUADTREE, leaves, so, H, W, fic.ITER_AUTO, stop_on_relative_error=thr)
+        ref, n_ref = orc.tree_decode(0, leaves, so, H, W, iterations=-1, stop_rel_err=thr)
+        assert n_got == n_ref, (thr, n_got, n_ref)
+        assert np.array_equal(got, ref)
+        seen.add(n_got)
+    assert len(seen) >= 3          # the thresholds really straddle several stopping points
+
+
+def test_quadtree_encoder_keeps_the_reference_attributes(fic, orc):
+    """`min_needed_range_exponent` and `domain_lists` (encoder.py:65-75, 261-283) on a ragged image."""
+    from quadtree.encoder import QuadtreeEncoder
+    img = synthetic_image(7, 44, 36)
+    enc = QuadtreeEncoder(7, 5, 1.0, False, False, 4, 8, 2.0)
+    enc.encode(img)
+    assert enc.max_square_exponent == 5 and enc.min_needed_range_exponent == 2
+    lists = enc.domain_lists
+    assert len(lists) == enc.max_range_exponent - enc.min_needed_range_exponent + 1
+    for k, pool in enumerate(lists):
+        side = 2 ** (enc.min_needed_range_exponent + 1 + k)
+        assert len(pool) == 3 and all(len(row) == 24 for row in pool)
+        total = 0
+        for mc in range(3):
+            for vc in range(24):
+                rows = pool[mc][vc]
+                if len(rows) == 1 and rows[0].tolist() == [0, 0, 0, 0]:
+                    continue        # placeholder (or the genuine first domain, classified below)
+                for (i, j, rot, orient) in rows.tolist():
+                    assert tuple(orc.qt_classify(img, i, j, side)) == (mc, vc, rot, orient)
+                total += len(rows)
+        assert total in (len(range(0, 44 - side + 1, side)) * len(range(0, 36 - side + 1, side)),
+                         len(range(0, 44 - side + 1, side)) * len(range(0, 36 - side + 1, side)) - 1)
