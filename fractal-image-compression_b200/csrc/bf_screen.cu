@@ -389,10 +389,16 @@ __device__ __forceinline__ void screen_pair(const uint32_t (&va)[32], const uint
 // ---- the screen ---------------------------------------------------------------------------------------------
 // MODE 0 = production; MODE 1 = probe (dump raw accumulators of group 0); MODE 2 / 3 = timing experiments selected by
 // FIC_SCREEN_DEBUG (2: TMEM loads but no screening, 3: no epilogue work at all) -- their results are wrong on purpose.
-template <int MODE>
+// KT = K of the contraction = pixels per block: 64 (8x8 blocks: 128-byte operand rows, SWIZZLE_128B, four MMAs per tile) or
+// 16 (4x4 blocks of the quadtree's smallest ranges: 32-byte rows, SWIZZLE_32B, one MMA per tile).  The shared-memory layout
+// is the K = 64 one in both cases.
+template <int MODE, int KT = KMAIN>
 __global__ void __launch_bounds__(SCREEN_THREADS, 1)
 bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, ScreenParams p)
 {
+    static_assert(KT == 64 || KT == 16, "operand rows of 128 or 32 bytes");
+    constexpr uint32_t A_BYTES = BM * KT * 2, B_BYTES = BN * KT * 2;
+    constexpr uint32_t DESC_SBO = KT == 64 ? 1024 : 256, DESC_LAYOUT = KT == 64 ? 2 : 6;   // 8-row group pitch, swizzle mode
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B tiles want 1024-byte alignment
@@ -436,7 +442,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         while (span.next(grp, j0, j1)) {
             mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
             if (issuer) {
-                mbar_expect_tx(b_full, B_MAIN_BYTES);
+                mbar_expect_tx(b_full, B_BYTES);
                 tma_load_2d(base + OFF_B_MAIN, &mapB, b_full, 0, grp * BN);
             }
             bph ^= 1;
@@ -447,7 +453,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             for (int j = j0; j < j1; ++j) {
                 mbar_wait(empty_bar(s), ph ^ 1, p.err_flag, 2);
                 if (issuer) {
-                    mbar_expect_tx(full_bar(s), A_MAIN_BYTES);
+                    mbar_expect_tx(full_bar(s), A_BYTES);
                     tma_load_2d(base + OFF_A_MAIN + s * A_MAIN_BYTES, &mapA, full_bar(s), 0, t_cur * BM);
                 }
                 __syncwarp();
@@ -465,8 +471,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         // before every instruction), one elected lane issues, and the descriptors are advanced by additions.
         int s = 0, as = 0;
         uint32_t ph = 0, aph = 0, bph = 0;
-        const uint64_t bdesc = make_desc(base + OFF_B_MAIN, 1024, 2);
-        const uint64_t adesc0 = make_desc(base + OFF_A_MAIN, 1024, 2);
+        const uint64_t bdesc = make_desc(base + OFF_B_MAIN, DESC_SBO, DESC_LAYOUT);
+        const uint64_t adesc0 = make_desc(base + OFF_A_MAIN, DESC_SBO, DESC_LAYOUT);
         const bool issuer = elect_one();
         Span span(p, n_groups);
         int grp, j0, j1;
@@ -481,7 +487,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 tcgen05_fence_after();
                 if (issuer) {
 #pragma unroll
-                    for (int k = 0; k < KMAIN / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
+                    for (int k = 0; k < KT / 16; ++k)  // +32 bytes per K=16 step inside the 128-byte swizzle atom
                         umma_f16(d_tmem, adesc + 2 * k, bdesc + 2 * k, IDESC, k > 0);
                     tcgen05_commit(empty_bar(s));   // frees the A stage once the MMAs above have completed
                     tcgen05_commit(tfull_bar(as));  // accumulator ready for the epilogue
@@ -1156,6 +1162,330 @@ int make_map(CUtensorMap* m, void* base, uint64_t rows, uint32_t cols, uint32_t 
 
 inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+
+// =================================================================================================================
+// Quadtree: the dense-pool, all-classes search on the same screen (quadtree/encoder.py:148-193, 285-384 with
+// domain_hstep = domain_vstep = 1 and full_class_search).  Every range of a level is matched against every domain
+// position, which is the brute-force contraction with two differences:
+//   * one isometry per (range, domain) pair and scale sign, derived from the two classifications -- the GEMM still
+//     forms all eight, the epilogue's per-isometry masks tell the rescoring kernel which ones passed, and only the
+//     pair's own isometry is scored;
+//   * the score is the QUANTISED one (fic_q_score), the winner the first minimum in the reference's scan order
+//     (scale sign, class, position).  Its lower bound has the brute-force form with n pixels per block:
+//         n E >= A_r - n u^2 / den_n ,   den_n = n sum(D4^2) - (sum D4)^2 ,
+//     so thresholds, rounds and survivor lists are shared.  For 8x8 blocks the float32 sequential sum of d^2 is the
+//     one inexact input (as in the brute-force encoder); its effect is at most kappa s^2 with |s| <= max_scale <= 1,
+//     covered by the constant guard of the ill-conditioned class for every candidate.  For 4x4 blocks every sum is
+//     exact in float32 and no guard is needed.
+// Ranges the screen cannot decide (constant blocks, bound not below the variance, list overflow) are flagged and
+// searched by qt_search_kernel.
+struct QtcState {
+    double E, s, o, TA0;
+    unsigned long long key;       // (mode * 72 + class) << 32 | position: the reference's scan order
+    int32_t rec[6];               // di, dj, orient, rot, qs, qo of the running winner
+    int32_t flags;                // 1 = handed to the exact search
+    int32_t si, sj;
+    int32_t rot[2], orient[2];    // the range's classification for positive / negative scales
+    float rs, sqr;
+};
+
+template <int S>
+__global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
+                                 float2* __restrict__ hk, uint32_t* __restrict__ sd4, int seed_S, int seed_gx, int n_seed,
+                                 int n_seed_pad, __half* __restrict__ seedA, float2* __restrict__ seedhk)
+{
+    constexpr int N = S * S;
+    const int PW = W - 2 * S + 1, PH = H - 2 * S + 1, BW = W - 1;
+    const int NP = PW * PH;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n_seed_pad - n_seed) {      // padding rows of the seed pool: zero operand, threshold never met
+        uint4* za = reinterpret_cast<uint4*>(seedA + (size_t)(n_seed + p) * N);
+#pragma unroll
+        for (int q = 0; q < N / 8; ++q) za[q] = make_uint4(0u, 0u, 0u, 0u);
+        seedhk[n_seed + p] = make_float2(__int_as_float(0x7f800000), 0.f);
+    }
+    if (p >= NP) return;
+    const int di = p / PW, dj = p - di * PW;
+    int v[N];
+    int s = 0;
+    long long s2 = 0;
+#pragma unroll
+    for (int a = 0; a < S; ++a)
+#pragma unroll
+        for (int b = 0; b < S; ++b) {
+            const int x = P[(size_t)(di + 2 * a) * BW + dj + 2 * b];
+            v[a * S + b] = x;
+            s += x;
+            s2 += x * x;
+        }
+    const int m = (s + N / 2) / N;      // round(SD4 / n); eps = s - n m in [-n/2, n/2)
+    const int seed_k = (di % seed_S == 0 && dj % seed_S == 0) ? (di / seed_S) * seed_gx + dj / seed_S : -1;
+    uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)p * N);
+#pragma unroll
+    for (int q = 0; q < N / 8; ++q) {
+        __half2 h0 = __halves2half2(__int2half_rn(v[8 * q + 0] - m), __int2half_rn(v[8 * q + 1] - m));
+        __half2 h1 = __halves2half2(__int2half_rn(v[8 * q + 2] - m), __int2half_rn(v[8 * q + 3] - m));
+        __half2 h2 = __halves2half2(__int2half_rn(v[8 * q + 4] - m), __int2half_rn(v[8 * q + 5] - m));
+        __half2 h3 = __halves2half2(__int2half_rn(v[8 * q + 6] - m), __int2half_rn(v[8 * q + 7] - m));
+        uint4 o;
+        o.x = *reinterpret_cast<uint32_t*>(&h0);
+        o.y = *reinterpret_cast<uint32_t*>(&h1);
+        o.z = *reinterpret_cast<uint32_t*>(&h2);
+        o.w = *reinterpret_cast<uint32_t*>(&h3);
+        dst[q] = o;
+        if (seed_k >= 0) reinterpret_cast<uint4*>(seedA + (size_t)seed_k * N)[q] = o;
+    }
+    const long long den = (long long)N * s2 - (long long)s * s;   // den_n >= 0, exact
+    float hc = __int_as_float(0x7f800000), kc = 0.f;
+    if (den > 0) {
+        hc = (float)(1.0 / sqrt((double)N / (double)den)) * (1.0f - 1.0f / 1048576.0f);   // 1/h_c, rounded down a little
+        if (N == 64) hc = -hc;        // every 8x8 candidate takes the guarded threshold (tau_B)
+        kc = (float)((double)den * (64.0 / (double)N));   // the seed ranking computes 64 m^2 / kc = n u^2 / den_n
+    }
+    hk[p] = make_float2(hc, kc);
+    if (seed_k >= 0) seedhk[seed_k] = make_float2(hc, kc);
+    sd4[p] = (uint32_t)s;
+}
+
+// one warp per slot: range sums, state, thresholds, the range operand (eight isometric copies, centred)
+template <int S>
+__global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const int32_t* __restrict__ queue /*[n][4]*/,
+                                 const int32_t* __restrict__ rcls /*[n][2][3] = class, rot, orient per scale sign*/, int n_ranges,
+                                 QtcState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
+                                 unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
+                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact)
+{
+    constexpr int N = S * S;
+    const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (slot >= tau_pad) return;
+    if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
+    if (lane == 0) {
+        tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+        seed_best[slot] = 0ull;
+    }
+    if (slot >= n_ranges) {   // padding columns of the last group: zero operand
+        for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
+        return;
+    }
+    const int si = queue[4 * (size_t)slot], sj = queue[4 * (size_t)slot + 1];
+    int px[2] = {0, 0};
+    unsigned sm = 0, q32 = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        const int k = lane + 32 * half;
+        if (k < N) {
+            px[half] = img[(size_t)(si + k / S) * W + sj + k % S];
+            sm += px[half];
+            q32 += px[half] * px[half];
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        sm += __shfl_xor_sync(0xffffffffu, sm, off);
+        q32 += __shfl_xor_sync(0xffffffffu, q32, off);
+    }
+    const int m = ((int)sm + N / 2) / N;
+#pragma unroll
+    for (int t = 0; t < 8; ++t)
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int k = lane + 32 * half;
+            if (k < N) {   // range pixel (i, j) meets the pooled sample (a, b) = iso_t(i, j) (fic_iso_qt_enc)
+                int a, b;
+                fic_iso_qt_enc(t >> 2, t & 3, S, k / S, k % S, a, b);
+                rngB[((size_t)slot * 8 + t) * N + a * S + b] = __int2half_rn(px[half] - m);
+            }
+        }
+    if (lane == 0) {
+        const long long sl = sm, ql = q32;
+        const long long An = (long long)N * ql - sl * sl;            // n A_r, exact
+        QtcState st;
+        st.E = __longlong_as_double(0x7ff0000000000000ll); st.s = 0.0; st.o = 0.0;
+        st.TA0 = (double)An / (double)N - (double)N * 1e-9 * (double)ql;
+        st.key = ~0ull;
+        for (int k = 0; k < 6; ++k) st.rec[k] = 0;
+        st.flags = An == 0 ? 1 : 0;      // constant block: every candidate ties, the scan order decides -> exact search
+        st.si = si; st.sj = sj;
+        for (int md = 0; md < 2; ++md) { st.rot[md] = rcls[6 * (size_t)slot + 3 * md + 1]; st.orient[md] = rcls[6 * (size_t)slot + 3 * md + 2]; }
+        st.rs = (float)sl; st.sqr = (float)ql;     // exact: <= 64 * 255^2 < 2^24
+        state[slot] = st;
+        cnt[slot] = 0;
+        need_exact[slot] = st.flags;
+    }
+}
+
+#define QTC_WARPS 32
+#ifndef QTC_MIN_EXPLAINED
+#define QTC_MIN_EXPLAINED 0.2
+#endif
+template <int S>
+__global__ void __launch_bounds__(QTC_WARPS * 32, 1)
+qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
+                    const int32_t* __restrict__ dcls /*[NP][3] = class, rot, orient*/, int H, int W, QtcState* __restrict__ state,
+                    int* __restrict__ ctrl, uint32_t* __restrict__ cnt, uint32_t* list, uint32_t cap, float2* __restrict__ tau,
+                    int emit, int nmodes, double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ out_rec,
+                    double* __restrict__ out_vals, int32_t* __restrict__ need_exact,
+                    const unsigned long long* __restrict__ seed_best, int seed_S, int seed_gx)
+{
+    constexpr int N = S * S;
+    __shared__ float rv[QTC_WARPS][N];            // the range blocks as floats
+    __shared__ float s_rs[QTC_WARPS], s_sqr[QTC_WARPS];
+    __shared__ int s_rot[QTC_WARPS][2], s_orient[QTC_WARPS][2];
+    __shared__ unsigned long long s_key[QTC_WARPS], s_prev[QTC_WARPS], s_tie[QTC_WARPS];
+    __shared__ double s_E[QTC_WARPS], s_s[QTC_WARPS], s_o[QTC_WARPS];
+    __shared__ int s_rec[QTC_WARPS][6];
+    __shared__ uint32_t s_n[QTC_WARPS + 1];
+    __shared__ int s_live[QTC_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+    const int slot = blockIdx.x * QTC_WARPS + warp;
+    const int n_elig = ctrl[0];
+    const int PW = W - 2 * S + 1;
+    // ---- phase A: warp w prepares range w of the CTA ----
+    if (lane == 0) { s_n[warp] = 0; s_live[warp] = 0; }
+    if (slot < n_elig) {
+        const QtcState st = state[slot];
+        uint32_t n;
+        if (seed_best) {   // seed round: position 0 and the eight isometries of the best-ranked lattice node
+            const unsigned long long key = seed_best[slot];
+            n = key != 0ull ? 16u : 8u;
+            if (lane < n) {
+                uint32_t pos = 0u;
+                if (lane >= 8) {
+                    const uint32_t k = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+                    pos = (k / (uint32_t)seed_gx) * (uint32_t)seed_S * (uint32_t)PW + (k % (uint32_t)seed_gx) * (uint32_t)seed_S;
+                }
+                list[(size_t)slot * cap + lane] = pos * 8u + (uint32_t)(lane & 7);
+            }
+        } else {
+            n = cnt[slot];
+        }
+        if (st.flags & 1) {
+            // already handed to the exact search
+        } else if (n > cap) {
+            if (lane == 0) {
+                state[slot].flags = 1;
+                need_exact[slot] = 1;
+                cnt[slot] = 0;
+                tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
+            }
+        } else {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int k = lane + 32 * half;
+                if (k < N) rv[warp][k] = (float)img[(size_t)(st.si + k / S) * W + st.sj + k % S];
+            }
+            if (lane == 0) {
+                s_rs[warp] = st.rs; s_sqr[warp] = st.sqr;
+                for (int md = 0; md < 2; ++md) { s_rot[warp][md] = st.rot[md]; s_orient[warp][md] = st.orient[md]; }
+                s_n[warp] = n; s_live[warp] = 1;
+                s_E[warp] = st.E; s_s[warp] = st.s; s_o[warp] = st.o; s_tie[warp] = st.key;
+                for (int k = 0; k < 6; ++k) s_rec[warp][k] = st.rec[k];
+                s_key[warp] = s_prev[warp] = rescore_key(st.E);
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t acc = 0;
+        for (int r = 0; r < QTC_WARPS; ++r) { const uint32_t n = s_n[r]; s_n[r] = acc; acc += n; }
+        s_n[QTC_WARPS] = acc;
+    }
+    __syncthreads();
+    // ---- phase B: the CTA's lists laid end to end, one entry per thread and pass ----
+    const uint32_t total = s_n[QTC_WARPS];
+    for (uint32_t base = 0; base < total; base += QTC_WARPS * 32) {
+        const uint32_t e = base + tid;
+        int r = -1;
+        double bE = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
+        unsigned long long btie = ~0ull, key = ~0ull;
+        int brec[6] = {0, 0, 0, 0, 0, 0};
+        if (e < total) {
+            r = 0;
+#pragma unroll
+            for (int step = QTC_WARPS / 2; step > 0; step >>= 1)
+                if (e >= s_n[r + step]) r += step;
+            const int rslot = blockIdx.x * QTC_WARPS + r;
+            const uint32_t ent = list[(size_t)rslot * cap + (e - s_n[r])];
+            const int t = ent & 7, p = ent >> 3;
+            const int dclass = dcls[3 * (size_t)p], drot = dcls[3 * (size_t)p + 1], dorient = dcls[3 * (size_t)p + 2];
+            const int di = p / PW, dj = p - di * PW;
+            for (int md = 0; md < nmodes; ++md) {
+                const int rrot = s_rot[r][md], rorient = s_orient[r][md];
+                int d_rot, d_orient;
+                if (dorient == rorient) { d_rot = (drot - rrot) & 3; d_orient = 0; }
+                else { d_rot = (drot - rrot + 2) & 3; d_orient = 1; }
+                if (d_orient * 4 + d_rot != t) continue;      // this pair's isometry is another column (its own entry, if it passed)
+                // the three float32 sums in the reference's order: row-major over the range block (encoder.py:302-322)
+                const float mc = (float)((sd4[p] + (uint32_t)(N / 2)) / (uint32_t)N);
+                const __half* row = poolA + (size_t)p * N;
+                float ds = 0.f, sds = 0.f, ab = 0.f;
+#pragma unroll 4
+                for (int k = 0; k < N; ++k) {
+                    int a, b;
+                    fic_iso_qt_enc(d_orient, d_rot, S, k / S, k % S, a, b);
+                    const float d = __fmul_rn(__half2float(row[a * S + b]) + mc, 0.25f);
+                    ds = __fadd_rn(ds, d);
+                    sds = __fadd_rn(sds, __fmul_rn(d, d));
+                    ab = __fadd_rn(ab, __fmul_rn(d, rv[r][k]));
+                }
+                const QScore sc = fic_q_score(N, s_rs[r], s_sqr[r], ds, sds, ab, max_scale, scale_bits, offset_bits);
+                const unsigned long long tie = ((unsigned long long)(md * 72 + dclass) << 32) | (unsigned)p;
+                if (fic_better(sc.R, tie, bE, btie)) {
+                    bE = sc.R; btie = tie; bs = sc.s; bo = sc.o;
+                    brec[0] = di; brec[1] = dj; brec[2] = d_orient; brec[3] = d_rot; brec[4] = sc.qs; brec[5] = sc.qo;
+                }
+            }
+            if (btie != ~0ull) {
+                key = rescore_key(bE);
+                atomicMin(&s_key[r], key);
+            }
+        }
+        __syncthreads();
+        if (tid < QTC_WARPS && s_key[tid] != s_prev[tid]) { s_prev[tid] = s_key[tid]; s_tie[tid] = ~0ull; }   // a better score: forget the old tie key
+        __syncthreads();
+        const bool contender = r >= 0 && btie != ~0ull && key == s_key[r];
+        if (contender) atomicMin(&s_tie[r], btie);
+        __syncthreads();
+        if (contender && s_tie[r] == btie) {
+            s_E[r] = bE; s_s[r] = bs; s_o[r] = bo;
+            for (int k = 0; k < 6; ++k) s_rec[r][k] = brec[k];
+        }
+        __syncthreads();
+    }
+    // ---- commit: the range's winner so far, next thresholds or the final record ----
+    if (lane == 0 && s_live[warp]) {
+        const float never = __int_as_float(0x7f800000);
+        QtcState& st = state[slot];
+        cnt[slot] = 0;
+        if (s_tie[warp] == ~0ull) {      // nothing finite at all
+            st.flags = 1;
+            need_exact[slot] = 1;
+            tau[slot] = make_float2(never, never);
+        } else {
+            st.E = s_E[warp]; st.s = s_s[warp]; st.o = s_o[warp]; st.key = s_tie[warp];
+            for (int k = 0; k < 6; ++k) st.rec[k] = s_rec[warp][k];
+            if (emit) {
+                for (int k = 0; k < 6; ++k) out_rec[6 * (size_t)slot + k] = st.rec[k];
+                out_vals[3 * (size_t)slot] = st.s; out_vals[3 * (size_t)slot + 1] = st.o; out_vals[3 * (size_t)slot + 2] = st.E;
+            } else {
+                const double TA = st.TA0 - (double)N * st.E, TB = TA - (double)N * GUARD_ILL;
+                float2 t = make_float2(never, never);
+                // A bound that leaves most of the block's variance unexplained passes most candidates (with 5 contrast bits the
+                // quantised score of the best candidate sits well above its least-squares optimum): such ranges would only
+                // overflow their lists, so they go to the exact search at once.
+                if (st.E == st.E && st.E < 1e300 && TA > 1e-3 && (N == 16 || TB > 0.0) && TA >= QTC_MIN_EXPLAINED * st.TA0) {
+                    t.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);
+                    t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
+                } else {
+                    st.flags = 1;
+                    need_exact[slot] = 1;
+                }
+                tau[slot] = t;
+            }
+        }
+    }
+}
+
 }  // namespace
 
 bool bf_screen_applicable(int H, int W)
@@ -1392,4 +1722,140 @@ int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mod
                       double* d_so, double* d_R, unsigned flags, cudaStream_t st)
 {
     return bf_screen_run(h, d_img, H, W, mode, range_begin, n_ranges, d_idx, d_so, d_R, flags, nullptr, st);
+}
+
+// ---- host driver of the quadtree search on the screen -----------------------------------------------------------------
+// One level of the quadtree partition: the n ranges of side 2^e in d_queue ([n][4] = si, sj, node, -) against all
+// (H - 2^(e+1) + 1) x (W - 2^(e+1) + 1) domain positions.  d_rcls [n][2][3] = (class, rotation, orientation) of every range for
+// positive / negative scales, d_dcls [NP][3] the same for every domain position (row-major grid).  Writes rec [n][6] / vals
+// [n][3] for the ranges it decides and need_exact[n] = 1 for the others.  e = 3 (8x8 ranges, K = 64) or e = 2 (4x4, K = 16).
+template <int S>
+static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_queue, int n_ranges,
+                             const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits,
+                             int offset_bits, int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st)
+{
+    constexpr int N = S * S;
+    const int PW = W - 2 * S + 1, PH = H - 2 * S + 1;
+    const int NP = PW * PH;
+    const int n_tiles = cdiv(NP, BM);
+    const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
+    const int tau_pad = n_cols_pad / 8;
+    const uint16_t* P = h->bf_boxsum.as<uint16_t>();
+    uint32_t cap = 8192;
+    while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
+    FIC_TRY(h->bf_pool.reserve((size_t)n_tiles * BM * N * 2 + 256));
+    FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
+    FIC_TRY(h->bf_stats.reserve((size_t)NP * sizeof(uint32_t) + 256));
+    FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * N * 2 + 256));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * sizeof(QtcState) + 512));
+    FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
+    FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
+    if (!h->bf_ctrl.p) {
+        FIC_TRY(h->bf_ctrl.reserve(256));
+        FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
+    }
+    int seed_S, seed_gx, n_seed, n_seed_pad;
+    {
+        double want = (double)NP / 50.0;
+        if (want < 256.0) want = 256.0;
+        if (want > 8192.0) want = 8192.0;
+        seed_S = (int)floor(sqrt((double)NP / want) + 0.5);
+        if (seed_S < 1) seed_S = 1;
+        seed_gx = cdiv(PW, seed_S);
+        n_seed = seed_gx * cdiv(PH, seed_S);
+        n_seed_pad = cdiv(n_seed, BM) * BM;
+    }
+    const size_t off_seedhk = ((size_t)tau_pad * 8 + 255) & ~(size_t)255;
+    const size_t off_seedA = (off_seedhk + (size_t)n_seed_pad * 8 + 255) & ~(size_t)255;
+    FIC_TRY(h->bf_best.reserve(off_seedA + (size_t)n_seed_pad * N * 2 + 256));
+    __half* poolA = h->bf_pool.as<__half>();
+    float2* hk = h->bf_cand.as<float2>();
+    uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    __half* rngB = h->bf_A.as<__half>();
+    QtcState* state = h->bf_thr.as<QtcState>();
+    float2* tau = reinterpret_cast<float2*>(state + n_ranges);
+    uint32_t* cnt = h->bf_surv.as<uint32_t>();
+    uint32_t* list = h->bf_list.as<uint32_t>();
+    int* ctrl = h->bf_ctrl.as<int>();
+    unsigned char* seed_raw = h->bf_best.as<unsigned char>();
+    unsigned long long* seed_best = reinterpret_cast<unsigned long long*>(seed_raw);
+    float2* seedhk = reinterpret_cast<float2*>(seed_raw + off_seedhk);
+    __half* seedA = reinterpret_cast<__half*>(seed_raw + off_seedA);
+
+    qt_tcpool_kernel<S><<<cdiv(std::max(NP, n_seed_pad), 128), 128, 0, st>>>(P, H, W, poolA, hk, sd4, seed_S, seed_gx, n_seed, n_seed_pad, seedA, seedhk);
+    FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
+    qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad, rngB, d_need_exact);
+    FIC_CHECK_LAUNCH(h, "qt_tcinit_kernel");
+
+    const CUtensorMapSwizzle sw = N == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
+    CUtensorMap mapA, mapB, mapS;
+    FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, N, BM, sw));
+    FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, N, BN, sw));
+    FIC_TRY(make_map(&mapS, seedA, (uint64_t)n_seed_pad, N, BM, sw));
+    if (!h->qt_screen_attr_ready) {
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        h->qt_screen_attr_ready = true;
+    }
+    ScreenParams sp;
+    sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
+    sp.dump = nullptr; sp.seed_best = nullptr; sp.err_flag = ctrl + 2; sp.debug_mode = 0;
+    {
+        ScreenParams ss = sp;
+        ss.hk = seedhk; ss.NP = n_seed; ss.n_tiles = n_seed_pad / BM; ss.m_cur = 1; ss.r_prev = 0;
+        ss.n_round_tiles = ss.n_tiles; ss.window_tiles = ss.n_tiles; ss.seed_best = seed_best;
+        bf_screen_kernel<5, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapB, ss);
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree seed)");
+        qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 0, nmodes,
+                                                                                    max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, seed_best, seed_S, seed_gx);
+        FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel(seed)");
+    }
+    std::vector<int> strides;
+    if (n_tiles < 64) {
+        strides.push_back(1);
+    } else {
+        const double f_prev = (double)n_seed / (double)NP;
+        const int growth = 16;
+        int m = 1;
+        while (1.0 / m > (double)growth * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
+        for (;;) {
+            strides.push_back(m);
+            if (m == 1) break;
+            m = m / growth > 1 ? m / growth : 1;
+        }
+    }
+    sp.window_tiles = (64 << 20) / (BM * N * 2);
+    for (size_t r = 0; r < strides.size(); ++r) {
+        sp.m_cur = strides[r];
+        sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
+        sp.n_round_tiles = cdiv(n_tiles, strides[r]) - (r == 0 ? 0 : cdiv(n_tiles, strides[r - 1]));
+        bf_screen_kernel<0, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree)");
+        const int emit = r + 1 == strides.size();
+        qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, emit, nmodes,
+                                                                                    max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, nullptr, 0, 0);
+        FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel");
+    }
+    return FIC_OK;
+}
+
+bool qt_tc_applicable(int H, int W, int e, double max_scale)
+{
+    if (e != 2 && e != 3) return false;
+    const int S = 1 << e;
+    if (H < 2 * S || W < 2 * S || !(max_scale > 0.0 && max_scale <= 1.0)) return false;
+    return (long long)(H - 2 * S + 1) * (W - 2 * S + 1) >= 2048;      // below that the fixed costs of the pipeline dominate
+}
+
+int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const int32_t* d_queue, int n_ranges,
+                 const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits, int offset_bits,
+                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st)
+{
+    if (e == 3)
+        return qt_tc_search_impl<8>(h, d_img, H, W, d_queue, n_ranges, d_rcls, d_dcls, nmodes, max_scale, scale_bits, offset_bits, d_rec,
+                                    d_vals, d_need_exact, st);
+    return qt_tc_search_impl<4>(h, d_img, H, W, d_queue, n_ranges, d_rcls, d_dcls, nmodes, max_scale, scale_bits, offset_bits, d_rec,
+                                d_vals, d_need_exact, st);
 }

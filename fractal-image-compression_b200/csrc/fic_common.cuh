@@ -128,13 +128,14 @@ struct fic_handle {
     // brute force
     DevBuf bf_boxsum, bf_stats, bf_partial, bf_ranges;
     DevBuf bf_pool, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list, bf_done;
+    bool qt_screen_attr_ready = false;
     bool screen_attr_ready = false;  // the screen / rescoring kernels have their dynamic shared memory limit raised on this device
     bool bf_totals_live = false;     // bf_ctrl holds device-side counter totals that fic_get_counters has to fetch
     // decoders
     DevBuf dec_img, dec_next, dec_map, dec_sched, dec_red, dec_keys, dec_roots;
     bool dec_shadow_ready = false;   // bf_decode_kernel<true> has its dynamic shared memory limit raised on this device
     // quadtree / hv
-    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part, t_nodes, t_count;
+    DevBuf t_int1, t_int2, t_cls, t_lists, t_work, t_res, t_aux, t_hvpool, t_part, t_nodes, t_count, t_rcls, t_need;
 };
 
 static inline cudaStream_t fic_stream(fic_handle* h, void* s) { return s ? (cudaStream_t)s : h->own_stream; }

@@ -342,8 +342,11 @@ qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
                  const long long* __restrict__ I2,
                  const int32_t* __restrict__ ranges /*[n][4] = si,sj,node,-*/, int side, QtPoolDev pool, int full, int nmodes,
                  double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ rec /*[n][6]*/,
-                 double* __restrict__ vals /*[n][3]*/)
+                 double* __restrict__ vals /*[n][3]*/,
+                 const int32_t* __restrict__ need /* optional: only ranges with need[k] != 0 are searched (the others were decided by
+                                                     the tensor-core screen, qt_tc_search) */)
 {
+    if (need && !need[blockIdx.x]) return;
     __shared__ float s_rs, s_sqr;
     __shared__ int seg_begin[2 * 72 + 1];  // prefix of candidate counts over (mode, class) segments
     __shared__ int seg_list[2 * 72];       // class index of the segment
@@ -647,6 +650,27 @@ static int qt_smallest_range(int width, int height)
     return std::min(min_bottom, min_right);
 }
 
+// classification of the queued ranges for positive and negative scales: out[k][mode] = {class, rotation, orientation}
+__global__ void qt_range_class_kernel(const long long* __restrict__ I1, const long long* __restrict__ I2, int W1,
+                                      const int32_t* __restrict__ queue, int n, int side, int32_t* __restrict__ out)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= 2 * n) return;
+    const int q = k >> 1, mode = k & 1;
+    int mc, vc, rot, orient;
+    classify_block(I1, I2, W1, queue[4 * (size_t)q], queue[4 * (size_t)q + 1], side, mode, mc, vc, rot, orient);
+    out[3 * (size_t)k] = mc * 24 + vc;
+    out[3 * (size_t)k + 1] = rot;
+    out[3 * (size_t)k + 2] = orient;
+}
+
+// bf_screen.cu / bf_exact.cu: the dense all-classes search on the tensor-core screen
+bool qt_tc_applicable(int H, int W, int e, double max_scale);
+int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const int32_t* d_queue, int n_ranges,
+                 const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits, int offset_bits,
+                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st);
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
+
 // ---- quadtree partition on the device (quadtree/encoder.py:127-146) ----------------------------------------------
 // Node table and one work queue per size exponent live in device memory.  A level = all pending ranges of one size:
 // one search launch, then qt_decide_kernel applies `rms > tolerance and exponent > min_exponent` (encoder.py:134),
@@ -783,8 +807,8 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
     // ---- domain pools (encoder.py:97-109, 261-283), built on the device: [offsets(73) | rows] per pool size ----
     const int npools = std::max(0, max_exp + 1 - (min_needed + 1) + 1);
     std::vector<size_t> pool_base(npools);
-    size_t tot = 0, max_cnt = 0;
-    struct PoolGeom { int side, hs, vs, nv, nh; size_t cnt; };
+    size_t tot = 0, max_cnt = 0, cls_tot = 0;
+    struct PoolGeom { int side, hs, vs, nv, nh; size_t cnt, cls_off; };
     std::vector<PoolGeom> geom(npools);
     for (int k = 0; k < npools; ++k) {
         PoolGeom& g = geom[k];
@@ -799,19 +823,21 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
         tot += 73 + 4 * (g.cnt + 72);          // every class may need its placeholder row
         tot = (tot + 3) & ~(size_t)3;
         max_cnt = std::max(max_cnt, g.cnt);
+        g.cls_off = cls_tot;                   // the classification of every pool is kept (the tensor-core search reads it)
+        cls_tot += (g.cnt * 3 + 3) & ~(size_t)3;
     }
     FIC_TRY(h->t_lists.reserve((tot + 4) * sizeof(int32_t)));
     if (max_cnt) {
         const size_t max_blocks = (max_cnt + QP_CHUNK - 1) / QP_CHUNK;
-        FIC_TRY(h->t_cls.reserve(max_cnt * 3 * sizeof(int32_t) + max_blocks * 72 * sizeof(int32_t) + 64));
+        FIC_TRY(h->t_cls.reserve(cls_tot * sizeof(int32_t) + max_blocks * 72 * sizeof(int32_t) + 64));
     }
     for (int k = 0; k < npools; ++k) {
         const PoolGeom& g = geom[k];
         int32_t* offsets = h->t_lists.as<int32_t>() + pool_base[k];
         int32_t* rows = offsets + 73;
-        int32_t* cls3 = h->t_cls.as<int32_t>();
+        int32_t* cls3 = h->t_cls.as<int32_t>() + g.cls_off;
         const int nblocks = (int)((g.cnt + QP_CHUNK - 1) / QP_CHUNK);
-        int32_t* blockhist = cls3 + ((max_cnt * 3 + 3) & ~(size_t)3);
+        int32_t* blockhist = h->t_cls.as<int32_t>() + cls_tot;
         if (g.cnt) {
             classify_grid_kernel<<<(unsigned)((g.cnt + 127) / 128), 128, 0, st>>>(I1, I2, W + 1, g.side, g.nv, g.nh, g.vs, g.hs, cls3);
             FIC_CHECK_LAUNCH(h, "classify_grid_kernel");
@@ -920,6 +946,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
         }
     }
     const int nmodes = onlypos ? 1 : 2;
+    bool boxsum_ready = false;     // 2x2 cell sums of the image, made once if a level goes through the tensor-core search
     bool counts_fresh = true;      // h_counts mirrors the device counters
     for (int e = start_exp; e >= 0; --e) {
         const int n = h_counts[1 + e];
@@ -939,9 +966,36 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             QtPoolDev pool;
             pool.offsets = h->t_lists.as<int32_t>() + pool_base[pk];
             pool.rows = pool.offsets + 73;
+            // Dense pools searched over all classes are the brute-force contraction: tensor-core screen first, the CUDA-core
+            // search only for the ranges it leaves undecided.
+            const int32_t* need = nullptr;
+            if (full && geom[pk].hs == 1 && geom[pk].vs == 1 && n >= 32 && qt_tc_applicable(H, W, e, max_scale)) {
+                if (!boxsum_ready) {
+                    FIC_TRY(bf_prepare8(h, d_img, H, W, false, st));
+                    boxsum_ready = true;
+                }
+                FIC_TRY(h->t_rcls.reserve((size_t)n * 6 * sizeof(int32_t) + 64));
+                FIC_TRY(h->t_need.reserve((size_t)n * sizeof(int32_t) + 64));
+                qt_range_class_kernel<<<(2 * n + 127) / 128, 128, 0, st>>>(I1, I2, W + 1, queue, n, 1 << e, h->t_rcls.as<int32_t>());
+                FIC_CHECK_LAUNCH(h, "qt_range_class_kernel");
+                FIC_TRY(qt_tc_search(h, d_img, H, W, e, queue, n, h->t_rcls.as<int32_t>(), h->t_cls.as<int32_t>() + geom[pk].cls_off, nmodes,
+                                     max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(), h->t_part.as<double>(),
+                                     h->t_need.as<int32_t>(), st));
+                need = h->t_need.as<int32_t>();
+#ifdef FIC_TUNING
+                {
+                    std::vector<int32_t> hn(n);
+                    cudaStreamSynchronize(st);
+                    cudaMemcpy(hn.data(), need, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost);
+                    long long f = 0;
+                    for (int v : hn) f += v != 0;
+                    fprintf(stderr, "quadtree level e=%d: %d ranges, %lld left to the exact search\n", e, n, f);
+                }
+#endif
+            }
             qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, 1 << e, pool, full, nmodes,
                                                        max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
-                                                       h->t_part.as<double>());
+                                                       h->t_part.as<double>(), need);
             FIC_CHECK_LAUNCH(h, "qt_search_kernel");
         }
         qt_decide_kernel<<<(n + 127) / 128, 128, 0, st>>>(queue, n, e, mode, tol, min_exp, h->t_res.as<int32_t>(), h->t_part.as<double>(),

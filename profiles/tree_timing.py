@@ -29,6 +29,7 @@ out = {
     "hv_512_ms": med(lambda: fic_b200.hv_encode(img, 4, 4, 16, 16, 5, 7, 25.0, handle=h), 5),
     "qt_512_ms": med(lambda: fic_b200.qt_encode(img, 7, 5, 1.0, False, False, 4, 8, 2.0, handle=h)),
     "qt_512_full_ms": med(lambda: fic_b200.qt_encode(img, 7, 5, 1.0, True, False, 4, 8, 2.0, handle=h)),
+    "qt_512_dense_full_ms": med(lambda: fic_b200.qt_encode(img, 7, 5, 1.0, True, False, 4, 8, 2.0, 1, 1, handle=h), 3),
     "qt_512_dense_ms": med(lambda: fic_b200.qt_encode(img, 7, 5, 1.0, False, False, 4, 8, 2.0, 1, 1, handle=h)),
 }
 print(json.dumps(out))

@@ -327,3 +327,21 @@ def test_quadtree_encoder_keeps_the_reference_attributes(fic, orc):
                 total += len(rows)
         assert total in (len(range(0, 44 - side + 1, side)) * len(range(0, 36 - side + 1, side)),
                          len(range(0, 44 - side + 1, side)) * len(range(0, 36 - side + 1, side)) - 1)
+
+
+@pytest.mark.parametrize("params,shape,seed", [
+    ((7, 5, 1.0, True, False, 4, 8, 2.0, 1, 1), (128, 128), 51),       # the stress row of DESIGN section 6, small
+    ((6, 6, 1.0, True, True, 2, 16, 1.0, 1, 1), (96, 144), 52),        # positive scales only; sizes 2 and 16 stay on CUDA cores
+    ((7, 5, 0.75, True, False, 4, 8, 0.5, 1, 1), (104, 88), 53),       # ragged image, smaller max_scale, low tolerance
+], ids=["default_bits", "positive_only_2_to_16", "ragged_low_tolerance"])
+def test_quadtree_dense_full_class_search_on_the_tensor_cores(fic, orc, params, shape, seed):
+    """Dense pools (domain steps 1) searched over all classes go through the tcgen05 screen for 8x8 and 4x4 ranges
+    (bf_screen.cu: qt_tc_search); node for node against the oracle, flat and saturated regions included."""
+    img = synthetic_image(seed, *shape)
+    img[:24, :40] = 255                 # constant blocks: every candidate ties, the scan order decides
+    img[40:56, 8:24] = (np.indices((16, 16)).sum(0) % 2 * 255).astype(np.uint8)
+    want = orc.qt_encode(img, *params)
+    got = fic.qt_encode(img, *params)
+    assert got[2] == want[2]
+    assert np.array_equal(got[0], want[0])
+    assert np.array_equal(got[1], want[1])
