@@ -19,6 +19,13 @@
 #include "scorer.cuh"
 
 #define TE_THREADS 128
+#define HV_MINB 4        // resident CTAs per SM the HV search is compiled for (128 registers; 5 spills and loses, 3 gains nothing)
+// A rectangle's candidate list is cut into S chunks, one CTA each.  The work of a chunk varies with the rectangle (small
+// rectangles have many positions) and a level's CTAs run in several waves, so fine chunks balance far better than "a few
+// CTAs per SM": same box, lena 512x512, S aimed at 4 / 8 / 16 / 32 / 64 / 128 CTAs per SM: 70.9 / 62.8 / 54.6 / 44.7 / 42.1 /
+// 44.3 ms per encode.
+#define HV_SMULT 64
+#define HV_SCAP 256
 
 // ---- integral images ----------------------------------------------------------------------------
 // rows: one warp per image row, 32 pixels per step, warp inclusive scan plus a running carry (coalesced reads and writes)
@@ -464,7 +471,7 @@ __global__ void hv_pool_kernel(const uint8_t* __restrict__ img, int H, int W, fl
 // gridDim.y contiguous chunks so that the deep, narrow levels of the tree (a handful of rectangles) still fill the
 // GPU.  Each CTA writes the first minimum of its chunk; hv_pick_kernel merges the chunks with the same rule.
 // The three sums run in the reference's order (row-major over the oriented block, float32, no FMA).
-__global__ void __launch_bounds__(TE_THREADS, 4)
+__global__ void __launch_bounds__(TE_THREADS, HV_MINB)
 hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
                  const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
                  int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs, int smem_px,
@@ -588,8 +595,8 @@ static int hv_search_launch(fic_handle* h, const uint8_t* d_img, int H, int W, c
     if (count == 0) return FIC_OK;
     const float* Dp = h->t_hvpool.as<float>();
     int smem_px = max_px <= 10240 ? max_px : 0;      // range pixels in shared memory when they fit (40 KB)
-    int S = (4 * h->num_sms + count - 1) / count;      // aim at >= 4 CTAs per SM
-    if (S > 64) S = 64;
+    int S = (HV_SMULT * h->num_sms + count - 1) / count;      // see HV_SMULT
+    if (S > HV_SCAP) S = HV_SCAP;
     if (S < 1) S = 1;
     if (S == 1) {
         hv_search_kernel<<<dim3(count, 1), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
@@ -1207,8 +1214,8 @@ static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, co
 {
     const float* Dp = h->t_hvpool.as<float>();
     const int smem_px = max_px <= 10240 ? max_px : 0;
-    int S = (4 * h->num_sms + count - 1) / count;      // aim at >= 4 CTAs per SM
-    if (S > 64) S = 64;
+    int S = (HV_SMULT * h->num_sms + count - 1) / count;      // see HV_SMULT
+    if (S > HV_SCAP) S = HV_SCAP;
     if (S < 1) S = 1;
     const size_t np_ = (size_t)count * S;
     FIC_TRY(h->t_part.reserve(np_ * (6 * sizeof(int32_t) + 3 * sizeof(double) + sizeof(unsigned long long)) + 64));
