@@ -898,7 +898,8 @@ __global__ void bf_init_kernel(const uint8_t* __restrict__ img, int W, int mode,
 // an exact integer sum in fp32, the score is the float64 restatement of jit_bfencoder.py:64-95 (scorer.cuh).
 // Ranges with a short list (the common case) are handled by their own warp; the few with a long list are then
 // worked through by the whole CTA one after the other, so a single crowded range cannot become a 256-iteration tail.
-#define RESCORE_WARPS 32
+#define RESCORE_WARPS 16    // ranges per CTA (512 threads, two CTAs per SM): same-box A/B against 32 / 1 and 8 / 4: -0.5 % / +0.4 % of the step
+#define RESCORE_MINB 2
 #define RESCORE_SMEM (RESCORE_WARPS * 8 * 65 * 4)   // dynamic: the oriented range copies
 
 struct RescoreBest {
@@ -1002,7 +1003,7 @@ __device__ void rescore_commit(int slot, int ridx, const RescoreBest& b, RangeSt
     tau[slot] = t;
 }
 
-__global__ void __launch_bounds__(RESCORE_WARPS * 32, 1)   // 1024 threads x 64 registers: a long list is walked 1024 entries at a time
+__global__ void __launch_bounds__(RESCORE_WARPS * 32, RESCORE_MINB)   // 512 threads x 64 registers: a long list is walked 512 entries at a time
 bf_rescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
                   const float* __restrict__ sdd, int H, int W, int range_begin, RangeState* __restrict__ state,
                   int* __restrict__ ctrl, uint32_t* __restrict__ cnt, uint32_t* list /* written in the seed round */, uint32_t cap,
