@@ -230,6 +230,11 @@ struct ScreenParams {
     int* err_flag;
     int debug_mode;          // 0 = normal; 1/2/3 = timing experiments (FIC_SCREEN_DEBUG), results invalid
     unsigned long long* seed_best;   // seed mode: [slots] max of (gain bits << 32 | ~local candidate)
+    // MODE 6 (quadtree exact pass): the accumulator of every (candidate, range, scale sign) pair's own isometry goes to
+    // dump[((grp - grp_begin) * 64 + range_in_group * 2 + sign) * np_pad + candidate]
+    const uint8_t* dtyp;     // [NP] domain type = rotation | orientation << 2
+    const uint8_t* rtyp;     // [slots] range type = rot(+) | orient(+) << 2 | rot(-) << 3 | orient(-) << 5
+    int grp_begin, grp_count, np_pad;
 };
 
 // j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
@@ -414,7 +419,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
-    const int n_groups = (n_elig + 31) / 32;
+    const int grp_off = MODE == 6 ? p.grp_begin : 0;            // MODE 6 works on a batch of column groups
+    const int n_groups = MODE == 6 ? p.grp_count : (n_elig + 31) / 32;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -440,6 +446,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         Span span(p, n_groups);
         int grp, j0, j1;
         while (span.next(grp, j0, j1)) {
+            grp += grp_off;
             mbar_wait(b_empty, bph ^ 1, p.err_flag, 1);  // previous unit's MMAs have finished reading B
             if (issuer) {
                 mbar_expect_tx(b_full, B_BYTES);
@@ -521,6 +528,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         Span span(p, n_groups);
         int grp, j0, j1;
         while (span.next(grp, j0, j1)) {
+            grp += grp_off;
             if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
             // this warp's (tau_A, tau_B) pairs live in a private slice of shared memory; broadcast reads, no bank conflicts
             __syncwarp();
@@ -604,6 +612,52 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     if (lane0) mbar_arrive(my_tempty);
                     rank4(va, 2);
                     rank4(vb, 3);
+                    aph ^= 1;
+                    continue;
+                }
+                if (MODE == 6) {
+                    // exact pass of the quadtree search: no thresholds.  Every (candidate, range, scale sign) pair has ONE
+                    // isometry, derived from the two classifications (quadtree/encoder.py:168-176); its accumulator -- the exact
+                    // integer sum r'.D4' -- is picked out of the range's eight columns and stored for the scoring kernel.
+                    const unsigned dty = my_cand < p.NP ? p.dtyp[my_cand] : 0u;
+                    const int drot = dty & 3, dori = (dty >> 2) & 1;
+                    const uint4 rt4 = *reinterpret_cast<const uint4*>(p.rtyp + (size_t)(grp * 32 + part * 16));
+                    const uint32_t rtw[4] = {rt4.x, rt4.y, rt4.z, rt4.w};
+                    float* out = p.dump + ((size_t)(grp - grp_off) * 64 + (size_t)part * 32) * p.np_pad + my_cand;
+                    uint32_t va[32], vb[32];
+                    auto pick4 = [&](const uint32_t (&v)[32], int c4) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const unsigned rb = (rtw[c4] >> (8 * g)) & 0xffu;
+#pragma unroll
+                            for (int md = 0; md < 2; ++md) {
+                                const int rrot = (rb >> (3 * md)) & 3, rori = (rb >> (3 * md + 2)) & 1;
+                                const bool same = dori == rori;
+                                const int t = ((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4);
+                                const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
+                                const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
+                                const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
+                                out[(size_t)((c4 * 4 + g) * 2 + md) * p.np_pad] = __uint_as_float((t & 4) ? y1 : y0);
+                            }
+                        }
+                    };
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    tmem_ld32(taddr0, va);
+                    tmem_ld32(taddr0 + 32, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    pick4(va, 0);
+                    tmem_ld32(taddr0 + 64, va);
+                    pick4(vb, 1);
+                    tmem_ld32(taddr0 + 96, vb);
+                    tmem_ld_wait(va);
+                    tmem_ld_wait(vb);
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                    pick4(va, 2);
+                    pick4(vb, 3);
                     aph ^= 1;
                     continue;
                 }
@@ -1191,20 +1245,14 @@ struct QtcState {
 };
 
 template <int S>
-__global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, __half* __restrict__ poolA,
-                                 float2* __restrict__ hk, uint32_t* __restrict__ sd4, int seed_S, int seed_gx, int n_seed,
-                                 int n_seed_pad, __half* __restrict__ seedA, float2* __restrict__ seedhk)
+__global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, const int32_t* __restrict__ dcls,
+                                 __half* __restrict__ poolA, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
+                                 uint32_t* __restrict__ sq4, float* __restrict__ sds8, uint8_t* __restrict__ dtyp)
 {
     constexpr int N = S * S;
     const int PW = W - 2 * S + 1, PH = H - 2 * S + 1, BW = W - 1;
     const int NP = PW * PH;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p < n_seed_pad - n_seed) {      // padding rows of the seed pool: zero operand, threshold never met
-        uint4* za = reinterpret_cast<uint4*>(seedA + (size_t)(n_seed + p) * N);
-#pragma unroll
-        for (int q = 0; q < N / 8; ++q) za[q] = make_uint4(0u, 0u, 0u, 0u);
-        seedhk[n_seed + p] = make_float2(__int_as_float(0x7f800000), 0.f);
-    }
     if (p >= NP) return;
     const int di = p / PW, dj = p - di * PW;
     int v[N];
@@ -1220,7 +1268,6 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, _
             s2 += x * x;
         }
     const int m = (s + N / 2) / N;      // round(SD4 / n); eps = s - n m in [-n/2, n/2)
-    const int seed_k = (di % seed_S == 0 && dj % seed_S == 0) ? (di / seed_S) * seed_gx + dj / seed_S : -1;
     uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)p * N);
 #pragma unroll
     for (int q = 0; q < N / 8; ++q) {
@@ -1234,18 +1281,34 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, _
         o.z = *reinterpret_cast<uint32_t*>(&h2);
         o.w = *reinterpret_cast<uint32_t*>(&h3);
         dst[q] = o;
-        if (seed_k >= 0) reinterpret_cast<uint4*>(seedA + (size_t)seed_k * N)[q] = o;
     }
-    const long long den = (long long)N * s2 - (long long)s * s;   // den_n >= 0, exact
-    float hc = __int_as_float(0x7f800000), kc = 0.f;
-    if (den > 0) {
-        hc = (float)(1.0 / sqrt((double)N / (double)den)) * (1.0f - 1.0f / 1048576.0f);   // 1/h_c, rounded down a little
-        if (N == 64) hc = -hc;        // every 8x8 candidate takes the guarded threshold (tau_B)
-        kc = (float)((double)den * (64.0 / (double)N));   // the seed ranking computes 64 m^2 / kc = n u^2 / den_n
-    }
-    hk[p] = make_float2(hc, kc);
-    if (seed_k >= 0) seedhk[seed_k] = make_float2(hc, kc);
+    hk[p] = make_float2(__int_as_float(0x7f800000), 0.f);   // (the exact pass has no thresholds; the kernel still prefetches this)
     sd4[p] = (uint32_t)s;
+    sq4[p] = (uint32_t)s2;
+    dtyp[p] = (uint8_t)((dcls[3 * (size_t)p + 1] & 3) | ((dcls[3 * (size_t)p + 2] & 1) << 2));
+    if (N == 64) {
+        // the one order-dependent input of the scorer for 8x8 blocks: the float32 sequential sum of d^2 in the order the
+        // reference walks the oriented block (row-major over the range pixels, quadtree/encoder.py:302-322), per isometry
+        float sq[N];
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+            const float d = __fmul_rn((float)v[k], 0.25f);
+            sq[k] = __fmul_rn(d, d);
+        }
+        float acc[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc[t] = 0.f;
+#pragma unroll
+        for (int k = 0; k < N; ++k)
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                int a, b;
+                fic_iso_qt_enc(t >> 2, t & 3, S, k / S, k % S, a, b);
+                acc[t] = __fadd_rn(acc[t], sq[a * S + b]);
+            }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) sds8[(size_t)t * NP + p] = acc[t];
+    }
 }
 
 // one warp per slot: range sums, state, thresholds, the range operand (eight isometric copies, centred)
@@ -1254,7 +1317,7 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
                                  const int32_t* __restrict__ rcls /*[n][2][3] = class, rot, orient per scale sign*/, int n_ranges,
                                  QtcState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
                                  unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
-                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact)
+                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact, uint8_t* __restrict__ rtyp)
 {
     constexpr int N = S * S;
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1262,7 +1325,8 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
     if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
     if (lane == 0) {
         tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-        seed_best[slot] = 0ull;
+        seed_best[slot] = 0x7ff0000000000000ull;      // the exact pass keeps the best score found so far here (+inf)
+        rtyp[slot] = 0;
     }
     if (slot >= n_ranges) {   // padding columns of the last group: zero operand
         for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
@@ -1312,6 +1376,87 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
         state[slot] = st;
         cnt[slot] = 0;
         need_exact[slot] = st.flags;
+        rtyp[slot] = (uint8_t)((st.rot[0] & 3) | ((st.orient[0] & 1) << 2) | ((st.rot[1] & 3) << 3) | ((st.orient[1] & 1) << 5));
+    }
+}
+
+// ---- exact pass: every (range, position, scale sign) scored from the GEMM's exact dot product ---------------------------
+// One CTA per (chunk of 256 positions, column group of the batch); a thread owns a position and walks the group's 32 ranges.
+// ab comes from the stored accumulator (r'.D4' un-centred: integers, exact), ds and -- for 4x4 blocks -- sds from the
+// position's integer sums, sds of an 8x8 block from the table of sequential float32 sums: the five inputs of the scorer are
+// bit for bit what the pixel loop of qt_search_kernel produces.  A candidate whose lower bound or score is above the best
+// score found so far for its range (kept in global memory, shared by all CTAs) is dropped; everything else goes to the
+// range's list and the rescoring kernel picks the first minimum in scan order among them.
+template <int S>
+__global__ void __launch_bounds__(256)
+qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_begin, int n_ranges,
+                  const QtcState* __restrict__ state, const uint8_t* __restrict__ rtyp, const uint8_t* __restrict__ dtyp,
+                  const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4, const float* __restrict__ sds8,
+                  unsigned long long* __restrict__ bound, uint32_t* __restrict__ cnt, uint32_t* __restrict__ list, uint32_t cap,
+                  int nmodes, double max_scale, int scale_bits, int offset_bits, int p_stride, int seed_pass)
+{
+    constexpr int N = S * S;
+    __shared__ float s_rs[32], s_sqr[32];
+    __shared__ int s_mr[32], s_rho[32], s_ok[32];
+    __shared__ double s_slack[32];
+    __shared__ unsigned s_rt[32];
+    const int unit = blockIdx.y, grp = grp_begin + unit;
+    if (threadIdx.x < 32) {
+        const int slot = grp * 32 + threadIdx.x;
+        int ok = 0;
+        if (slot < n_ranges) {
+            const QtcState st = state[slot];
+            const int sum = (int)st.rs;
+            const int mr = (sum + N / 2) / N;
+            s_rs[threadIdx.x] = st.rs; s_sqr[threadIdx.x] = st.sqr;
+            s_mr[threadIdx.x] = mr; s_rho[threadIdx.x] = sum - N * mr;
+            s_slack[threadIdx.x] = DS((double)st.sqr, DD(DM((double)st.rs, (double)st.rs), (double)N));
+            s_rt[threadIdx.x] = rtyp[slot];
+            ok = !(st.flags & 1);
+        }
+        s_ok[threadIdx.x] = ok;
+    }
+    __syncthreads();
+    // seed pass: every p_stride-th position first, so that the bounds mean something before all positions are looked at
+    int p = blockIdx.x * 256 + threadIdx.x;
+    if (seed_pass) p *= p_stride;
+    else if (p_stride > 1 && p % p_stride == 0) return;
+    if (p >= NP) return;
+    const unsigned sd = sd4[p], sq = sq4[p];
+    const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
+    const unsigned dty = dtyp[p];
+    const int drot = dty & 3, dori = (dty >> 2) & 1;
+    const float ds = __fmul_rn((float)sd, 0.25f);
+    const double dn = (double)N, dsd = (double)ds;
+    for (int g = 0; g < 32; ++g) {
+        if (!s_ok[g]) continue;
+        const int slot = grp * 32 + g;
+        const float rs = s_rs[g], sqr = s_sqr[g];
+        for (int md = 0; md < nmodes; ++md) {
+            const unsigned rb = s_rt[g];
+            const int rrot = (rb >> (3 * md)) & 3, rori = (rb >> (3 * md + 2)) & 1;
+            const bool same = dori == rori;
+            const int t = ((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4);
+            const float X = dump[((size_t)unit * 64 + (size_t)(g * 2 + md)) * np_pad + p];
+            const int dot = (int)X + s_mr[g] * eps + mc * s_rho[g] + N * s_mr[g] * mc;     // sum r D4, exact
+            const float ab = __fmul_rn((float)dot, 0.25f);
+            const float sds = N == 64 ? sds8[(size_t)t * NP + p] : __fmul_rn((float)sq, 0.0625f);
+            const double B = __longlong_as_double((long long)__ldcg(&bound[slot]));
+            {
+                const double room = DS(s_slack[g], DM(dn, B));
+                if (room > 0.0) {
+                    const double den = DS(DM(dn, (double)sds), DM(dsd, dsd));
+                    const double num = DS(DM(dn, (double)ab), DM((double)rs, dsd));
+                    if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
+                }
+            }
+            const QScore sc = fic_q_score(N, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
+            if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
+                if (sc.R < B) atomicMin(&bound[slot], (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
+                const uint32_t at = atomicAdd(&cnt[slot], 1u);
+                if (at < cap) list[(size_t)slot * cap + at] = (uint32_t)p * 8u + (uint32_t)t;
+            }
+        }
     }
 }
 
@@ -1739,106 +1884,87 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     const int PW = W - 2 * S + 1, PH = H - 2 * S + 1;
     const int NP = PW * PH;
     const int n_tiles = cdiv(NP, BM);
+    const int np_pad = n_tiles * BM;
     const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
     const int tau_pad = n_cols_pad / 8;
+    const int n_groups = tau_pad / 32;
     const uint16_t* P = h->bf_boxsum.as<uint16_t>();
     uint32_t cap = 8192;
     while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
-    FIC_TRY(h->bf_pool.reserve((size_t)n_tiles * BM * N * 2 + 256));
+    // batch of column groups whose selected accumulators are held at once: 64 floats per position and group, at most 1 GiB
+    int batch = (int)(((size_t)1 << 30) / ((size_t)np_pad * 64 * sizeof(float)));
+    if (batch < 1) batch = 1;
+    if (batch > n_groups) batch = n_groups;
+    FIC_TRY(h->bf_pool.reserve((size_t)np_pad * N * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
-    FIC_TRY(h->bf_stats.reserve((size_t)NP * sizeof(uint32_t) + 256));
+    FIC_TRY(h->bf_stats.reserve((size_t)NP * (2 * sizeof(uint32_t) + 8 * sizeof(float) + 1) + 1024));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * N * 2 + 256));
-    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * sizeof(float2) + (size_t)n_ranges * sizeof(QtcState) + 512));
+    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * (sizeof(float2) + 1) + (size_t)n_ranges * sizeof(QtcState) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
+    FIC_TRY(h->bf_best.reserve((size_t)tau_pad * 8 + 256));
+    FIC_TRY(h->bf_dump.reserve((size_t)batch * 64 * np_pad * sizeof(float) + 256));
     if (!h->bf_ctrl.p) {
         FIC_TRY(h->bf_ctrl.reserve(256));
         FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
     }
-    int seed_S, seed_gx, n_seed, n_seed_pad;
-    {
-        double want = (double)NP / 50.0;
-        if (want < 256.0) want = 256.0;
-        if (want > 8192.0) want = 8192.0;
-        seed_S = (int)floor(sqrt((double)NP / want) + 0.5);
-        if (seed_S < 1) seed_S = 1;
-        seed_gx = cdiv(PW, seed_S);
-        n_seed = seed_gx * cdiv(PH, seed_S);
-        n_seed_pad = cdiv(n_seed, BM) * BM;
-    }
-    const size_t off_seedhk = ((size_t)tau_pad * 8 + 255) & ~(size_t)255;
-    const size_t off_seedA = (off_seedhk + (size_t)n_seed_pad * 8 + 255) & ~(size_t)255;
-    FIC_TRY(h->bf_best.reserve(off_seedA + (size_t)n_seed_pad * N * 2 + 256));
     __half* poolA = h->bf_pool.as<__half>();
     float2* hk = h->bf_cand.as<float2>();
     uint32_t* sd4 = h->bf_stats.as<uint32_t>();
+    uint32_t* sq4 = sd4 + NP;
+    float* sds8 = reinterpret_cast<float*>(sq4 + NP);
+    uint8_t* dtyp = reinterpret_cast<uint8_t*>(sds8 + (size_t)8 * NP);
     __half* rngB = h->bf_A.as<__half>();
     QtcState* state = h->bf_thr.as<QtcState>();
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
+    uint8_t* rtyp = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tau + tau_pad) + 15) & ~(uintptr_t)15);   // read 16 bytes at a time
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
-    unsigned char* seed_raw = h->bf_best.as<unsigned char>();
-    unsigned long long* seed_best = reinterpret_cast<unsigned long long*>(seed_raw);
-    float2* seedhk = reinterpret_cast<float2*>(seed_raw + off_seedhk);
-    __half* seedA = reinterpret_cast<__half*>(seed_raw + off_seedA);
+    unsigned long long* bound = h->bf_best.as<unsigned long long>();
+    float* dump = h->bf_dump.as<float>();
 
-    qt_tcpool_kernel<S><<<cdiv(std::max(NP, n_seed_pad), 128), 128, 0, st>>>(P, H, W, poolA, hk, sd4, seed_S, seed_gx, n_seed, n_seed_pad, seedA, seedhk);
+    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, hk, sd4, sq4, sds8, dtyp);
     FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
-    qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, seed_best, ctrl, tau_pad, rngB, d_need_exact);
+    qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, bound, ctrl, tau_pad, rngB,
+                                                                            d_need_exact, rtyp);
     FIC_CHECK_LAUNCH(h, "qt_tcinit_kernel");
 
     const CUtensorMapSwizzle sw = N == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
-    CUtensorMap mapA, mapB, mapS;
+    CUtensorMap mapA, mapB;
     FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, N, BM, sw));
     FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, N, BN, sw));
-    FIC_TRY(make_map(&mapS, seedA, (uint64_t)n_seed_pad, N, BM, sw));
     if (!h->qt_screen_attr_ready) {
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<0, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<5, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         h->qt_screen_attr_ready = true;
     }
     ScreenParams sp;
     sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
-    sp.dump = nullptr; sp.seed_best = nullptr; sp.err_flag = ctrl + 2; sp.debug_mode = 0;
-    {
-        ScreenParams ss = sp;
-        ss.hk = seedhk; ss.NP = n_seed; ss.n_tiles = n_seed_pad / BM; ss.m_cur = 1; ss.r_prev = 0;
-        ss.n_round_tiles = ss.n_tiles; ss.window_tiles = ss.n_tiles; ss.seed_best = seed_best;
-        bf_screen_kernel<5, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapS, mapB, ss);
-        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree seed)");
-        qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 0, nmodes,
-                                                                                    max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, seed_best, seed_S, seed_gx);
-        FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel(seed)");
-    }
-    std::vector<int> strides;
-    if (n_tiles < 64) {
-        strides.push_back(1);
-    } else {
-        const double f_prev = (double)n_seed / (double)NP;
-        const int growth = 16;
-        int m = 1;
-        while (1.0 / m > (double)growth * f_prev && 2 * m * 8 <= n_tiles) m *= 2;
-        for (;;) {
-            strides.push_back(m);
-            if (m == 1) break;
-            m = m / growth > 1 ? m / growth : 1;
-        }
-    }
+    sp.seed_best = nullptr; sp.err_flag = ctrl + 2; sp.debug_mode = 0;
+    sp.m_cur = 1; sp.r_prev = 0; sp.n_round_tiles = n_tiles;
     sp.window_tiles = (64 << 20) / (BM * N * 2);
-    for (size_t r = 0; r < strides.size(); ++r) {
-        sp.m_cur = strides[r];
-        sp.r_prev = r == 0 ? 0 : strides[r - 1] / strides[r];
-        sp.n_round_tiles = cdiv(n_tiles, strides[r]) - (r == 0 ? 0 : cdiv(n_tiles, strides[r - 1]));
-        bf_screen_kernel<0, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
-        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree)");
-        const int emit = r + 1 == strides.size();
-        qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, emit, nmodes,
-                                                                                    max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, nullptr, 0, 0);
-        FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel");
+    sp.dump = dump; sp.dtyp = dtyp; sp.rtyp = rtyp; sp.np_pad = np_pad;
+    // every QTC_SEED_STRIDE-th position is scored first: with the bounds still at +inf every candidate would enter the lists
+    const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 1);
+    for (int g0 = 0; g0 < n_groups; g0 += batch) {
+        const int gc = std::min(batch, n_groups - g0);
+        sp.grp_begin = g0; sp.grp_count = gc;
+        bf_screen_kernel<6, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass)");
+        if (stride > 1) {
+            qt_tcscore_kernel<S><<<dim3(cdiv(cdiv(NP, stride), 256), gc), 256, 0, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt,
+                                                                                       list, cap, nmodes, max_scale, scale_bits, offset_bits, stride, 1);
+            FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel(seed)");
+        }
+        qt_tcscore_kernel<S><<<dim3(cdiv(NP, 256), gc), 256, 0, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt, list, cap,
+                                                                     nmodes, max_scale, scale_bits, offset_bits, stride, 0);
+        FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel");
     }
+    // the lists hold every candidate that was at or below its range's best score when it was looked at: first minimum in scan order
+    qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 1, nmodes,
+                                                                                max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, nullptr, 0, 0);
+    FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel");
     return FIC_OK;
 }
 
