@@ -1,4 +1,8 @@
 #!/bin/bash
-cp fractal-image-compression_b200/fic_b200/libfic_b200.so ab/.shipped.so
-for v in S13 HP4 HP6 HP8 S13; do cp ab/lib$v.so fractal-image-compression_b200/fic_b200/libfic_b200.so; echo "$v $(python profiles/tree_timing.py 2>&1 | tail -1 | cut -c1-45)"; done
-cp ab/.shipped.so fractal-image-compression_b200/fic_b200/libfic_b200.so
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:qt_tcscore_kernel --launch-skip 20 --launch-count 1 -f -o gpurun_out/r2_qtscore python -c "
+import sys,os,numpy as np,time
+sys.path.insert(0,'fractal-image-compression_b200')
+import fic_b200
+img=np.load('tests/golden/images.npz')['lena512']
+fic_b200.qt_encode(img,7,5,1.0,True,False,4,8,2.0,1,1)
+" > gpurun_out/ncu_qtscore.log 2>&1; tail -2 gpurun_out/ncu_qtscore.log
