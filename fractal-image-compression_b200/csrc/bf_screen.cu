@@ -1387,6 +1387,15 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
 // bit for bit what the pixel loop of qt_search_kernel produces.  A candidate whose lower bound or score is above the best
 // score found so far for its range (kept in global memory, shared by all CTAs) is dropped; everything else goes to the
 // range's list and the rescoring kernel picks the first minimum in scan order among them.
+// Out of line on purpose: inlined, the compiler hoists the scorer's divisions that depend only on (range, position) in
+// front of the bound test, and 52 % of the kernel's instructions were spent there for the 5 % of warps that score (ncu).
+template <int N>
+__device__ __noinline__ QScore qt_score_outlined(float rs, float sqr, float ds, float sds, float ab, double max_scale, int scale_bits,
+                                                 int offset_bits)
+{
+    return fic_q_score(N, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
+}
+
 template <int S>
 __global__ void __launch_bounds__(256)
 qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_begin, int n_ranges,
@@ -1421,19 +1430,23 @@ qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_be
     }
     // The loop below would otherwise make one dependent trip to DRAM per candidate (ncu: 17 % of the issue slots used, two
     // thirds of all stall samples on these loads): the 64 x 256 accumulators of the CTA are fetched in one go instead.
-    if (!seed_pass) {
-        const int p0 = blockIdx.x * 256;
-        const float* src = dump + (size_t)unit * 64 * np_pad + p0;      // rows of np_pad floats, np_pad and p0 multiples of 128
+    // Seed pass: every p_stride-th run of 32 positions (one 128-byte line per stored row) is scored first, so that the bounds
+    // mean something before all positions are looked at; the full pass leaves those runs out.
+    const int run_stride = seed_pass ? p_stride : 1;
+    {
+        const float* src = dump + (size_t)unit * 64 * np_pad;      // rows of np_pad floats, np_pad a multiple of 128
         for (int e = threadIdx.x; e < 64 * 64; e += 256) {
             const int row = e >> 6, c4 = e & 63;
-            reinterpret_cast<float4*>(s_x)[row * 64 + c4] = __ldcs(reinterpret_cast<const float4*>(src + (size_t)row * np_pad) + c4);
+            const long long at = ((long long)(blockIdx.x * 8 + (c4 >> 3)) * run_stride) * 32 + (c4 & 7) * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (at < np_pad) v = __ldcs(reinterpret_cast<const float4*>(src + (size_t)row * np_pad + at));
+            reinterpret_cast<float4*>(s_x)[row * 64 + c4] = v;
         }
     }
     __syncthreads();
-    // seed pass: every p_stride-th position first, so that the bounds mean something before all positions are looked at
-    int p = blockIdx.x * 256 + threadIdx.x;
-    if (seed_pass) p *= p_stride;
-    else if (p_stride > 1 && p % p_stride == 0) return;
+    const int q = blockIdx.x * 256 + threadIdx.x;
+    const int p = (q >> 5) * run_stride * 32 + (q & 31);
+    if (!seed_pass && p_stride > 1 && (p >> 5) % p_stride == 0) return;
     if (p >= NP) return;
     const unsigned sd = sd4[p], sq = sq4[p];
     const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
@@ -1450,7 +1463,7 @@ qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_be
             const int rrot = (rb >> (3 * md)) & 3, rori = (rb >> (3 * md + 2)) & 1;
             const bool same = dori == rori;
             const int t = ((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4);
-            const float X = seed_pass ? dump[((size_t)unit * 64 + (size_t)(g * 2 + md)) * np_pad + p] : s_x[(g * 2 + md) * 256 + threadIdx.x];
+            const float X = s_x[(g * 2 + md) * 256 + threadIdx.x];
             const int dot = (int)X + s_mr[g] * eps + mc * s_rho[g] + N * s_mr[g] * mc;     // sum r D4, exact
             const float ab = __fmul_rn((float)dot, 0.25f);
             const float sds = N == 64 ? sds8[(size_t)t * NP + p] : __fmul_rn((float)sq, 0.0625f);
@@ -1463,7 +1476,7 @@ qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_be
                     if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
                 }
             }
-            const QScore sc = fic_q_score(N, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
+            const QScore sc = qt_score_outlined<N>(rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
             if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
                 if (sc.R < B) {
                     const unsigned long long bits = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
@@ -1921,7 +1934,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_best.reserve((size_t)tau_pad * 8 + 256));
-    FIC_TRY(h->bf_dump.reserve((size_t)batch * 64 * np_pad * sizeof(float) + 256 + 1024));
+    FIC_TRY(h->bf_dump.reserve((size_t)batch * 64 * np_pad * sizeof(float) + 256));
     if (!h->bf_ctrl.p) {
         FIC_TRY(h->bf_ctrl.reserve(256));
         FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
@@ -1965,7 +1978,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     sp.m_cur = 1; sp.r_prev = 0; sp.n_round_tiles = n_tiles;
     sp.window_tiles = (64 << 20) / (BM * N * 2);
     sp.dump = dump; sp.dtyp = dtyp; sp.rtyp = rtyp; sp.np_pad = np_pad;
-    // every QTC_SEED_STRIDE-th position is scored first: with the bounds still at +inf every candidate would enter the lists
+    // every stride-th run of 32 positions is scored first: with the bounds still at +inf every candidate would enter the lists
     const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 1);
     for (int g0 = 0; g0 < n_groups; g0 += batch) {
         const int gc = std::min(batch, n_groups - g0);
@@ -1973,7 +1986,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
         bf_screen_kernel<6, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass)");
         if (stride > 1) {
-            qt_tcscore_kernel<S><<<dim3(cdiv(cdiv(NP, stride), 256), gc), 256, QTC_SCORE_SMEM, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt,
+            qt_tcscore_kernel<S><<<dim3(cdiv(cdiv(cdiv(NP, 32), stride) * 32, 256), gc), 256, QTC_SCORE_SMEM, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt,
                                                                                        list, cap, nmodes, max_scale, scale_bits, offset_bits, stride, 1);
             FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel(seed)");
         }

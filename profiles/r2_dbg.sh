@@ -1,5 +1,5 @@
 #!/bin/bash
-timeout 600 ncu --set full --import-source on --clock-control none -k regex:qt_tcscore_kernel --launch-skip 20 --launch-count 1 -f -o gpurun_out/r2_qtscore python -c "
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:qt_tcscore_kernel --launch-skip 21 --launch-count 1 -f -o gpurun_out/r2_qtscore python -c "
 import sys,os,numpy as np,time
 sys.path.insert(0,'fractal-image-compression_b200')
 import fic_b200
