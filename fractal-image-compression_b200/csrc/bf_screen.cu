@@ -1311,13 +1311,23 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
     }
 }
 
+// Per-range constants of the scoring loop, one 32-byte record (written by qt_tcinit_kernel).
+struct __align__(16) QtcRange {
+    int rho;                  // sum r - N * round(sum r / N): the centring remainder of the range
+    int ok;                   // 0: not searched here (past the end, or handed to the exact search)
+    uint32_t tw0, tw1;        // isometry by domain type, eight 4-bit entries, for positive / negative scales
+    double slack;             // sum r^2 - (sum r)^2 / N
+    float rs, sqr;
+};
+
 // one warp per slot: range sums, state, thresholds, the range operand (eight isometric copies, centred)
 template <int S>
 __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const int32_t* __restrict__ queue /*[n][4]*/,
                                  const int32_t* __restrict__ rcls /*[n][2][3] = class, rot, orient per scale sign*/, int n_ranges,
                                  QtcState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
                                  unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
-                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact, uint8_t* __restrict__ rtyp)
+                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact, uint8_t* __restrict__ rtyp,
+                                 QtcRange* __restrict__ rngc)
 {
     constexpr int N = S * S;
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -1327,6 +1337,11 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
         tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
         seed_best[slot] = 0x7ff0000000000000ull;      // the exact pass keeps the best score found so far here (+inf)
         rtyp[slot] = 0;
+        if (slot >= n_ranges) {
+            QtcRange rc;
+            rc.rho = 0; rc.ok = 0; rc.tw0 = rc.tw1 = 0u; rc.slack = 0.0; rc.rs = rc.sqr = 0.f;
+            rngc[slot] = rc;
+        }
     }
     if (slot >= n_ranges) {   // padding columns of the last group: zero operand
         for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
@@ -1377,6 +1392,22 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
         cnt[slot] = 0;
         need_exact[slot] = st.flags;
         rtyp[slot] = (uint8_t)((st.rot[0] & 3) | ((st.orient[0] & 1) << 2) | ((st.rot[1] & 3) << 3) | ((st.orient[1] & 1) << 5));
+        QtcRange rc;
+        rc.rho = (int)sm - N * m;
+        rc.ok = !st.flags;
+        rc.rs = st.rs; rc.sqr = st.sqr;
+        rc.slack = DS((double)st.sqr, DD(DM((double)st.rs, (double)st.rs), (double)N));
+        for (int md = 0; md < 2; ++md) {
+            const int rrot = st.rot[md] & 3, rori = st.orient[md] & 1;
+            uint32_t w = 0;
+            for (int dty = 0; dty < 8; ++dty) {   // the pair's isometry (quadtree/encoder.py:168-176) for each of the eight domain types
+                const int drot = dty & 3, dori = dty >> 2;
+                const bool same = dori == rori;
+                w |= (uint32_t)(((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4)) << (4 * dty);
+            }
+            if (md) rc.tw1 = w; else rc.tw0 = w;
+        }
+        rngc[slot] = rc;
     }
 }
 
@@ -1387,111 +1418,146 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
 // bit for bit what the pixel loop of qt_search_kernel produces.  A candidate whose lower bound or score is above the best
 // score found so far for its range (kept in global memory, shared by all CTAs) is dropped; everything else goes to the
 // range's list and the rescoring kernel picks the first minimum in scan order among them.
-// Out of line on purpose: inlined, the compiler hoists the scorer's divisions that depend only on (range, position) in
-// front of the bound test, and 52 % of the kernel's instructions were spent there for the 5 % of warps that score (ncu).
+#define QTC_POS 128           /* positions per CTA of qt_tcscore_kernel; its 256 threads split a group's 32 ranges in two */
+struct QtcScoreParams {
+    const float* dump; const QtcRange* rngc; const uint8_t* dtyp; const uint32_t* sd4; const uint32_t* sq4; const float* sds8;
+    unsigned long long* bound; uint32_t* cnt; uint32_t* list;
+    double max_scale;
+    uint32_t cap;
+    int np_pad, NP, grp_begin, grp_count, scale_bits, offset_bits, p_stride, seed_pass;
+};
+
+// A candidate the bound test did not drop: exact score, bound update, entry in the range's list.  Out of line on purpose --
+// inlined, the compiler moves whatever here depends only on (range, position) in front of the test (the scorer's divisions,
+// the list addresses), and most of the kernel's instructions were spent on the few per cent of candidates that get here (ncu).
 template <int N>
-__device__ __noinline__ QScore qt_score_outlined(float rs, float sqr, float ds, float sds, float ab, double max_scale, int scale_bits,
-                                                 int offset_bits)
+__device__ __noinline__ void qt_score_survivor(const QtcScoreParams& prm, const QtcRange* rcp, unsigned long long* s_bound_g, int slot, int p,
+                                               int t, int Xi, unsigned sd, unsigned sq)
 {
-    return fic_q_score(N, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
+    const QtcRange rc = *rcp;
+    const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
+    const int mr = ((int)rc.rs - rc.rho) / N;
+    const int dot = Xi + mr * eps + mc * rc.rho + N * mr * mc;     // sum r D4, exact
+    const float ab = __fmul_rn((float)dot, 0.25f);
+    const float ds = __fmul_rn((float)sd, 0.25f);
+    const float sds = N == 64 ? prm.sds8[(size_t)t * prm.NP + p] : __fmul_rn((float)sq, 0.0625f);
+    const QScore sc = fic_q_score(N, rc.rs, rc.sqr, ds, sds, ab, prm.max_scale, prm.scale_bits, prm.offset_bits);
+    const double B = __longlong_as_double((long long)*(volatile unsigned long long*)s_bound_g);
+    if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
+        if (sc.R < B) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
+            atomicMin(s_bound_g, bits);
+            atomicMin(&prm.bound[slot], bits);
+        }
+        if (!prm.seed_pass) {
+            const uint32_t at = atomicAdd(&prm.cnt[slot], 1u);
+            if (at < prm.cap) prm.list[(size_t)slot * prm.cap + at] = (uint32_t)p * 8u + (uint32_t)t;
+        }
+    }
 }
 
-template <int S>
-__global__ void __launch_bounds__(256)
-qt_tcscore_kernel(const float* __restrict__ dump, int np_pad, int NP, int grp_begin, int n_ranges,
-                  const QtcState* __restrict__ state, const uint8_t* __restrict__ rtyp, const uint8_t* __restrict__ dtyp,
-                  const uint32_t* __restrict__ sd4, const uint32_t* __restrict__ sq4, const float* __restrict__ sds8,
-                  unsigned long long* __restrict__ bound, uint32_t* __restrict__ cnt, uint32_t* __restrict__ list, uint32_t cap,
-                  int nmodes, double max_scale, int scale_bits, int offset_bits, int p_stride, int seed_pass)
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+// A CTA owns QTC_POS positions and walks the column groups blockIdx.y, blockIdx.y + gridDim.y, ... of the batch: the slice of
+// stored accumulators (64 x QTC_POS floats) and the 32 range records of the NEXT group are on their way (cp.async) while the
+// current group is scored, and what depends on the position alone is computed once per CTA.
+template <int S, int NM>
+__global__ void __launch_bounds__(256, 3)
+qt_tcscore_kernel(const __grid_constant__ QtcScoreParams prm)
 {
     constexpr int N = S * S;
-    extern __shared__ float s_x[];            // [64][256]: the CTA's slice of the stored accumulators
-    __shared__ float s_rs[32], s_sqr[32];
-    __shared__ int s_mr[32], s_rho[32], s_ok[32];
-    __shared__ double s_slack[32];
-    __shared__ unsigned long long s_bound[32];   // best score per range as this CTA knows it (global value at start + own finds)
-    __shared__ unsigned s_rt[32];
-    const int unit = blockIdx.y, grp = grp_begin + unit;
-    if (threadIdx.x < 32) {
-        const int slot = grp * 32 + threadIdx.x;
-        int ok = 0;
-        if (slot < n_ranges) {
-            const QtcState st = state[slot];
-            const int sum = (int)st.rs;
-            const int mr = (sum + N / 2) / N;
-            s_rs[threadIdx.x] = st.rs; s_sqr[threadIdx.x] = st.sqr;
-            s_mr[threadIdx.x] = mr; s_rho[threadIdx.x] = sum - N * mr;
-            s_slack[threadIdx.x] = DS((double)st.sqr, DD(DM((double)st.rs, (double)st.rs), (double)N));
-            s_rt[threadIdx.x] = rtyp[slot];
-            s_bound[threadIdx.x] = __ldcg(&bound[slot]);
-            ok = !(st.flags & 1);
+    constexpr int Q4 = QTC_POS / 4;               // float4 per row of a slice
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    float* s_x = reinterpret_cast<float*>(s_raw);                                // [2][64][QTC_POS]
+    double* s_den = reinterpret_cast<double*>(s_raw + 2 * 64 * QTC_POS * 4);      // [8][QTC_POS], 8x8 blocks only: N * sds - ds^2 by isometry
+    __shared__ QtcRange s_rng[2][32];
+    __shared__ unsigned long long s_bound[32];   // best score per range as this CTA knows it (global value when the group is begun + own finds)
+    const int pl = threadIdx.x & (QTC_POS - 1), half = threadIdx.x / QTC_POS;
+    // Seed pass: every p_stride-th run of 32 positions (one 128-byte line per stored row) is scored first and only lowers the
+    // bounds -- with the bounds at +inf and a hundred thousand threads on the same ranges at once, nearly all of its
+    // candidates would be listed (measured: 88 %).  The full pass then lists from all positions against bounds that mean something.
+    const int run_stride = prm.seed_pass ? prm.p_stride : 1;
+    auto stage = [&](int unit, int buf) {
+        const float* src = prm.dump + (size_t)unit * 64 * prm.np_pad;      // rows of np_pad floats, np_pad a multiple of 128
+        float* dst = s_x + buf * 64 * QTC_POS;
+        for (int e = threadIdx.x; e < 64 * Q4; e += 256) {
+            const int row = e / Q4, c4 = e % Q4;
+            const long long at = ((long long)(blockIdx.x * (QTC_POS / 32) + (c4 >> 3)) * run_stride) * 32 + (c4 & 7) * 4;
+            if (at < prm.np_pad) cp_async16(dst + row * QTC_POS + c4 * 4, src + (size_t)row * prm.np_pad + at);
         }
-        s_ok[threadIdx.x] = ok;
-    }
-    // The loop below would otherwise make one dependent trip to DRAM per candidate (ncu: 17 % of the issue slots used, two
-    // thirds of all stall samples on these loads): the 64 x 256 accumulators of the CTA are fetched in one go instead.
-    // Seed pass: every p_stride-th run of 32 positions (one 128-byte line per stored row) is scored first, so that the bounds
-    // mean something before all positions are looked at; the full pass leaves those runs out.
-    const int run_stride = seed_pass ? p_stride : 1;
-    {
-        const float* src = dump + (size_t)unit * 64 * np_pad;      // rows of np_pad floats, np_pad a multiple of 128
-        for (int e = threadIdx.x; e < 64 * 64; e += 256) {
-            const int row = e >> 6, c4 = e & 63;
-            const long long at = ((long long)(blockIdx.x * 8 + (c4 >> 3)) * run_stride) * 32 + (c4 & 7) * 4;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (at < np_pad) v = __ldcs(reinterpret_cast<const float4*>(src + (size_t)row * np_pad + at));
-            reinterpret_cast<float4*>(s_x)[row * 64 + c4] = v;
-        }
-    }
-    __syncthreads();
-    const int q = blockIdx.x * 256 + threadIdx.x;
+        if (threadIdx.x < 64)
+            cp_async16(reinterpret_cast<unsigned char*>(&s_rng[buf][0]) + threadIdx.x * 16,
+                       reinterpret_cast<const unsigned char*>(prm.rngc + (size_t)(prm.grp_begin + unit) * 32) + threadIdx.x * 16);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int unit = blockIdx.y;
+    if (unit < prm.grp_count) stage(unit, 0);
+
+    const int q = blockIdx.x * QTC_POS + pl;
     const int p = (q >> 5) * run_stride * 32 + (q & 31);
-    if (!seed_pass && p_stride > 1 && (p >> 5) % p_stride == 0) return;
-    if (p >= NP) return;
-    const unsigned sd = sd4[p], sq = sq4[p];
-    const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
-    const unsigned dty = dtyp[p];
-    const int drot = dty & 3, dori = (dty >> 2) & 1;
-    const float ds = __fmul_rn((float)sd, 0.25f);
-    const double dn = (double)N, dsd = (double)ds;
-    for (int g = 0; g < 32; ++g) {
-        if (!s_ok[g]) continue;
-        const int slot = grp * 32 + g;
-        const float rs = s_rs[g], sqr = s_sqr[g];
-        for (int md = 0; md < nmodes; ++md) {
-            const unsigned rb = s_rt[g];
-            const int rrot = (rb >> (3 * md)) & 3, rori = (rb >> (3 * md + 2)) & 1;
-            const bool same = dori == rori;
-            const int t = ((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4);
-            const float X = s_x[(g * 2 + md) * 256 + threadIdx.x];
-            const int dot = (int)X + s_mr[g] * eps + mc * s_rho[g] + N * s_mr[g] * mc;     // sum r D4, exact
-            const float ab = __fmul_rn((float)dot, 0.25f);
-            const float sds = N == 64 ? sds8[(size_t)t * NP + p] : __fmul_rn((float)sq, 0.0625f);
-            const double B = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound[g]);
-            {
-                const double room = DS(s_slack[g], DM(dn, B));
-                if (room > 0.0) {
-                    const double den = DS(DM(dn, (double)sds), DM(dsd, dsd));
-                    const double num = DS(DM(dn, (double)ab), DM((double)rs, dsd));
-                    if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
+    const bool live = p < prm.NP;
+    unsigned sd = 0, sq = 0, dty = 0;
+    if (live) { sd = prm.sd4[p]; sq = prm.sq4[p]; dty = prm.dtyp[p]; }
+    const int eps = (int)sd - N * (int)((sd + (unsigned)(N / 2)) / (unsigned)N);
+    const double dn = (double)N;
+    double den16 = 0.0;
+    {
+        const double dsd = (double)__fmul_rn((float)sd, 0.25f);
+        if (N == 64) {
+            if (live && half == 0)
+                for (int t = 0; t < 8; ++t) s_den[t * QTC_POS + pl] = DS(DM(dn, (double)prm.sds8[(size_t)t * prm.NP + p]), DM(dsd, dsd));
+        } else {
+            den16 = DS(DM(dn, (double)__fmul_rn((float)sq, 0.0625f)), DM(dsd, dsd));
+        }
+    }
+    const int dsh = 4 * (int)(dty & 7);
+
+    for (int it = 0; unit < prm.grp_count; unit += gridDim.y, ++it) {
+        const int buf = it & 1, grp = prm.grp_begin + unit;
+        if (unit + (int)gridDim.y < prm.grp_count) {
+            stage(unit + gridDim.y, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        if (threadIdx.x < 32) s_bound[threadIdx.x] = __ldcg(&prm.bound[grp * 32 + threadIdx.x]);
+        __syncthreads();
+        // The test per candidate, in the units of the integer numerator 4 * (N * ab - rs * ds) = N * X - rho * eps (X the
+        // stored accumulator of the centred block and range): dropped when its square is below 16 * N * den * (slack - N * B),
+        // the scorer's lower bound with both sides multiplied out; everything not dropped is scored exactly.
+        if (live) {
+            const float* xs = s_x + buf * 64 * QTC_POS + pl;
+            const QtcRange* rcs = &s_rng[buf][half * 16];
+#pragma unroll 1
+            for (int gi = 0; gi < 16; ++gi) {
+                const int g = half * 16 + gi;
+                const int4 ri = *reinterpret_cast<const int4*>(rcs + gi);          // rho, ok, tw0, tw1
+                if (!ri.y) continue;
+                const double slack = rcs[gi].slack;
+                const double B = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound[g]);
+                const double room = DS(slack, DM(dn, B));
+                const double rhs_g = DM(DM(DM(room, dn), 16.0), 0.999999999);
+                const int nre = -ri.x * eps;
+                const bool cullable = room > 0.0;
+#pragma unroll
+                for (int md = 0; md < NM; ++md) {
+                    const int Xi = (int)xs[(g * 2 + md) * QTC_POS];
+                    const int t = (int)(((uint32_t)(md ? ri.w : ri.z) >> dsh) & 7u);
+                    const double den = N == 64 ? s_den[t * QTC_POS + pl] : den16;
+                    const double nd = (double)(N * Xi + nre);
+                    if (cullable && den > 0.0 && DM(nd, nd) < DM(rhs_g, den)) continue;
+                    qt_score_survivor<N>(prm, rcs + gi, &s_bound[g], grp * 32 + g, p, t, Xi, sd, sq);
                 }
-            }
-            const QScore sc = qt_score_outlined<N>(rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
-            if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
-                if (sc.R < B) {
-                    const unsigned long long bits = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
-                    atomicMin(&s_bound[g], bits);
-                    atomicMin(&bound[slot], bits);
-                }
-                const uint32_t at = atomicAdd(&cnt[slot], 1u);
-                if (at < cap) list[(size_t)slot * cap + at] = (uint32_t)p * 8u + (uint32_t)t;
             }
         }
+        __syncthreads();
     }
 }
 
 #define QTC_WARPS 32
-#define QTC_SCORE_SMEM (64 * 256 * 4)    /* dynamic shared memory of qt_tcscore_kernel: its slice of the accumulators */
+#define QTC_SCORE_SMEM(S) (2 * 64 * QTC_POS * 4 + ((S) == 8 ? 8 * QTC_POS * 8 : 0))   /* dynamic shared memory of qt_tcscore_kernel */
 #ifndef QTC_MIN_EXPLAINED
 #define QTC_MIN_EXPLAINED 0.2
 #endif
@@ -1933,7 +1999,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * (sizeof(float2) + 1) + (size_t)n_ranges * sizeof(QtcState) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
-    FIC_TRY(h->bf_best.reserve((size_t)tau_pad * 8 + 256));
+    FIC_TRY(h->bf_best.reserve((size_t)tau_pad * (8 + sizeof(QtcRange)) + 512));
     FIC_TRY(h->bf_dump.reserve((size_t)batch * 64 * np_pad * sizeof(float) + 256));
     if (!h->bf_ctrl.p) {
         FIC_TRY(h->bf_ctrl.reserve(256));
@@ -1953,12 +2019,13 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
     unsigned long long* bound = h->bf_best.as<unsigned long long>();
+    QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + tau_pad) + 15) & ~(uintptr_t)15);
     float* dump = h->bf_dump.as<float>();
 
     qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, hk, sd4, sq4, sds8, dtyp);
     FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
     qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, bound, ctrl, tau_pad, rngB,
-                                                                            d_need_exact, rtyp);
+                                                                            d_need_exact, rtyp, rngc);
     FIC_CHECK_LAUNCH(h, "qt_tcinit_kernel");
 
     const CUtensorMapSwizzle sw = N == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
@@ -1968,8 +2035,10 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     if (!h->qt_screen_attr_ready) {
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(8)));
+        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(8)));
+        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(4)));
+        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(4)));
         h->qt_screen_attr_ready = true;
     }
     ScreenParams sp;
@@ -1985,14 +2054,38 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
         sp.grp_begin = g0; sp.grp_count = gc;
         bf_screen_kernel<6, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
         FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass)");
+        // enough CTAs for eight waves of three per SM; each walks the groups blockIdx.y, blockIdx.y + gridDim.y, ...
+        auto score = [&](int n_pos, int seed) {
+            const int nx = cdiv(n_pos, QTC_POS);
+            const int ny = std::max(1, std::min(gc, cdiv(h->num_sms * 3 * 8, nx)));
+            QtcScoreParams q;
+            q.dump = dump; q.rngc = rngc; q.dtyp = dtyp; q.sd4 = sd4; q.sq4 = sq4; q.sds8 = sds8; q.bound = bound; q.cnt = cnt; q.list = list;
+            q.max_scale = max_scale; q.cap = cap; q.np_pad = np_pad; q.NP = NP; q.grp_begin = g0; q.grp_count = gc;
+            q.scale_bits = scale_bits; q.offset_bits = offset_bits; q.p_stride = stride; q.seed_pass = seed;
+            if (nmodes == 2) qt_tcscore_kernel<S, 2><<<dim3(nx, ny), 256, QTC_SCORE_SMEM(S), st>>>(q);
+            else qt_tcscore_kernel<S, 1><<<dim3(nx, ny), 256, QTC_SCORE_SMEM(S), st>>>(q);
+        };
+#ifdef FIC_QTC_DEBUG
+        auto dbg = [&](const char* what) {
+            const int n = std::min(n_ranges - g0 * 32, gc * 32);
+            std::vector<uint32_t> c(n);
+            cudaStreamSynchronize(st);
+            cudaMemcpy(c.data(), cnt + (size_t)g0 * 32, (size_t)n * 4, cudaMemcpyDeviceToHost);
+            unsigned long long sum = 0; uint32_t mx = 0;
+            for (uint32_t v : c) { sum += v; mx = std::max(mx, v); }
+            fprintf(stderr, "[qtc S=%d g0=%d] %s: ranges %d, listed %llu, longest %u (cap %u)\n", S, g0, what, n, sum, mx, cap);
+        };
+#else
+        auto dbg = [&](const char*) {};
+#endif
         if (stride > 1) {
-            qt_tcscore_kernel<S><<<dim3(cdiv(cdiv(cdiv(NP, 32), stride) * 32, 256), gc), 256, QTC_SCORE_SMEM, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt,
-                                                                                       list, cap, nmodes, max_scale, scale_bits, offset_bits, stride, 1);
+            score(cdiv(cdiv(NP, 32), stride) * 32, 1);
             FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel(seed)");
+            dbg("after the seed pass");
         }
-        qt_tcscore_kernel<S><<<dim3(cdiv(NP, 256), gc), 256, QTC_SCORE_SMEM, st>>>(dump, np_pad, NP, g0, n_ranges, state, rtyp, dtyp, sd4, sq4, sds8, bound, cnt, list, cap,
-                                                                     nmodes, max_scale, scale_bits, offset_bits, stride, 0);
+        score(NP, 0);
         FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel");
+        dbg("after the full pass");
     }
     // the lists hold every candidate that was at or below its range's best score when it was looked at: first minimum in scan order
     qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 1, nmodes,
