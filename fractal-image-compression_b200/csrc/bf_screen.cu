@@ -213,6 +213,15 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32])
                  : "memory");
 }
 
+// Per-range constants of the scoring loop, one 32-byte record (written by qt_tcinit_kernel).
+struct __align__(16) QtcRange {
+    int rho;                  // sum r - N * round(sum r / N): the centring remainder of the range
+    int ok;                   // 0: not searched here (past the end, or handed to the exact search)
+    uint32_t tw0, tw1;        // isometry by domain type, eight 4-bit entries, for positive / negative scales
+    double slack;             // sum r^2 - (sum r)^2 / N
+    float rs, sqr;
+};
+
 struct ScreenParams {
     const float2* hk;        // [NP]
     const float2* tau;       // [slots padded to 32] = (tau_A, tau_B)
@@ -235,6 +244,15 @@ struct ScreenParams {
     const uint8_t* dtyp;     // [NP] domain type = rotation | orientation << 2
     const uint8_t* rtyp;     // [slots] range type = rot(+) | orient(+) << 2 | rot(-) << 3 | orient(-) << 5
     int grp_begin, grp_count, np_pad;
+    // MODE 7 (quadtree exact pass, fused): the bound test runs in the epilogue, survivors are scored from the warp's queue
+    const QtcRange* rngc;    // [slots]
+    unsigned long long* bound;       // [slots] best score found so far (bits of a non-negative double)
+    const uint32_t* sd4;     // [NP] sum D4
+    const uint32_t* sq4;     // [NP] sum D4^2
+    const float* sds8;       // [8][NP], 8x8 blocks: float32 sequential sum of d^2 per isometry
+    const double* den;       // [NP] N * sds - ds^2 (8x8 blocks: the smallest of the eight)
+    double max_scale;
+    int scale_bits, offset_bits, nmodes, seed_pass;
 };
 
 // j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
@@ -314,6 +332,49 @@ __device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, in
     for (uint32_t k = lane; k < n; k += 32) {
         const uint2 ent = q->e[k];
         append_hits(p.cnt, p.list, p.cap, (int)(ent.x >> 8), ent.y, ent.x & 0xffu);
+    }
+    __syncwarp();
+}
+
+// Quadtree exact pass: queue of the candidates the bound test did not drop, one per (position, range, scale sign), scored
+// 32 at a time -- one entry per lane, so the scorer never runs in a divergent warp.  Exact score from the exact dot product
+// (ab), the position's integer sums (ds, and sds of a 4x4 block) and the table of sequential float32 sums (sds of an 8x8
+// block): bit for bit the inputs qt_search_kernel's pixel loop produces.  A candidate at or below the best score of its
+// range lowers the bound and -- outside the seed pass -- enters the range's list; the rescoring kernel picks the first
+// minimum in scan order among the listed.
+constexpr int QT_QCAP = (QUEUE_BYTES - RANGES_PER_WARP * 32) / 16;
+constexpr int QT_QROOM = 4 * 2 * 32;          // a 32-column chunk adds at most 4 ranges x 2 scale signs x 32 lanes
+static_assert(QT_QCAP >= QT_QROOM + 32, "queue of the quadtree pass too small");
+struct QtQueue {
+    QtcRange rng[RANGES_PER_WARP];   // the records of the warp's sixteen ranges, refreshed per column group
+    uint4 e[QT_QCAP];        // x = slot, y = position, z = stored accumulator (int), w = isometry
+};
+static_assert(sizeof(QtcRange) == 32 && sizeof(QtQueue) <= QUEUE_BYTES, "QtQueue must fit a warp's queue slice");
+
+template <int N>
+__device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams& p, int lane, uint32_t n)
+{
+    __syncwarp();
+    for (uint32_t k = lane; k < n; k += 32) {
+        const uint4 en = q->e[k];
+        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)en.z, t = (int)en.w;
+        const QtcRange rc = p.rngc[slot];
+        const unsigned sd = p.sd4[cand], sq = p.sq4[cand];
+        const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
+        const int mr = ((int)rc.rs - rc.rho) / N;
+        const int dot = Xi + mr * eps + mc * rc.rho + N * mr * mc;     // sum r D4, exact
+        const float ab = __fmul_rn((float)dot, 0.25f);
+        const float ds = __fmul_rn((float)sd, 0.25f);
+        const float sds = N == 64 ? p.sds8[(size_t)t * p.NP + cand] : __fmul_rn((float)sq, 0.0625f);
+        const QScore sc = fic_q_score(N, rc.rs, rc.sqr, ds, sds, ab, p.max_scale, p.scale_bits, p.offset_bits);
+        const double B = __longlong_as_double((long long)__ldcg(&p.bound[slot]));
+        if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
+            if (sc.R < B) atomicMin(&p.bound[slot], (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
+            if (!p.seed_pass) {
+                const uint32_t at = atomicAdd(&p.cnt[slot], 1u);
+                if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)cand * 8u + (uint32_t)t;
+            }
+        }
     }
     __syncwarp();
 }
@@ -399,7 +460,7 @@ __device__ __forceinline__ void screen_pair(const uint32_t (&va)[32], const uint
 // is the K = 64 one in both cases.
 template <int MODE, int KT = KMAIN>
 __global__ void __launch_bounds__(SCREEN_THREADS, 1)
-bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, ScreenParams p)
+bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const __grid_constant__ ScreenParams p)
 {
     static_assert(KT == 64 || KT == 16, "operand rows of 128 or 32 bytes");
     constexpr uint32_t A_BYTES = BM * KT * 2, B_BYTES = BN * KT * 2;
@@ -419,8 +480,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
-    const int grp_off = MODE == 6 ? p.grp_begin : 0;            // MODE 6 works on a batch of column groups
-    const int n_groups = MODE == 6 ? p.grp_count : (n_elig + 31) / 32;
+    const int grp_off = MODE == 6 || MODE == 7 ? p.grp_begin : 0;            // the quadtree modes name their column groups
+    const int n_groups = MODE == 6 || MODE == 7 ? p.grp_count : (n_elig + 31) / 32;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -539,6 +600,11 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
             __syncwarp();
             const int slot0 = grp * 32 + part * 16;
+            if (MODE == 7) {   // the sixteen range records of this warp: 512 bytes, one uint4 per lane
+                QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
+                reinterpret_cast<uint4*>(qq->rng)[lane] = __ldg(reinterpret_cast<const uint4*>(p.rngc + slot0) + lane);
+                __syncwarp();
+            }
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
             // tile index of j without a division per tile: t = (j + j / (r_prev - 1) + 1) * m_cur, advanced by 2
@@ -613,6 +679,79 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     rank4(va, 2);
                     rank4(vb, 3);
                     aph ^= 1;
+                    continue;
+                }
+                if (MODE == 7) {
+                    // Exact pass of the quadtree search.  Every (candidate, range, scale sign) pair has ONE isometry, fixed by
+                    // the two classifications (quadtree/encoder.py:168-176); its accumulator X -- the exact integer sum of the
+                    // centred range times the centred block -- is picked out of the range's eight columns and tested here:
+                    // 4 * (N * ab - rs * ds) = N * X - rho * eps is an integer, and the pair is dropped when its square is
+                    // below 16 * N * den * (slack - N * B), the scorer's lower bound against the best score B of the range
+                    // with both sides multiplied out (relative margin 1e-6 on the right).  Everything else is queued.
+                    const bool have = my_cand < p.NP;
+                    unsigned dty = 0, sdc = 0;
+                    double den = 0.0;
+                    if (have) { dty = p.dtyp[my_cand]; sdc = p.sd4[my_cand]; den = p.den[my_cand]; }
+                    const int eps = (int)sdc - KT * (int)((sdc + (unsigned)(KT / 2)) / (unsigned)KT);
+                    const int dsh = 4 * (int)(dty & 7u);
+                    const bool den_ok = have && den > 0.0;
+                    const unsigned long long Bl = __ldcg(&p.bound[slot0 + (lane & 15)]);
+                    QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
+                    const unsigned lt = (1u << lane) - 1u;
+                    uint32_t va[32];
+                    auto test4 = [&](const uint32_t (&v)[32], int c4) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const int r = c4 * 4 + g;
+                            const QtcRange* rp = qq->rng + r;
+                            const int4 ri = *reinterpret_cast<const int4*>(rp);      // rho, ok, tw0, tw1
+                            const double slack = rp->slack;
+                            const double B = __longlong_as_double((long long)__shfl_sync(0xffffffffu, Bl, r));
+                            if (!ri.y) continue;
+                            const double rhs_g = DM(DS(slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
+                            const bool cull_ok = den_ok && rhs_g > 0.0;
+                            const double rhs = DM(rhs_g, den);
+                            const int nre = -ri.x * eps;
+#pragma unroll
+                            for (int md = 0; md < 2; ++md) {
+                                if (md < p.nmodes) {
+                                    const int t = (int)(((uint32_t)(md ? ri.w : ri.z) >> dsh) & 7u);
+                                    const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
+                                    const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
+                                    const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
+                                    const int Xi = (int)__uint_as_float((t & 4) ? y1 : y0);
+                                    const double nd = (double)(KT * Xi + nre);
+                                    const bool surv = have && !(cull_ok && DM(nd, nd) < rhs);
+                                    const unsigned m = __ballot_sync(0xffffffffu, surv);
+                                    if (m) {
+                                        if (surv) qq->e[qn + __popc(m & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, (uint32_t)Xi, (uint32_t)t);
+                                        qn += __popc(m);
+                                    }
+                                }
+                            }
+                        }
+                        if (qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
+                    };
+                    // one 32-column chunk in registers at a time: with two, the per-range constants of the test spill
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    tmem_ld32(taddr0, va);
+                    tmem_ld_wait(va);
+                    test4(va, 0);
+                    tmem_ld32(taddr0 + 32, va);
+                    tmem_ld_wait(va);
+                    test4(va, 1);
+                    tmem_ld32(taddr0 + 64, va);
+                    tmem_ld_wait(va);
+                    test4(va, 2);
+                    tmem_ld32(taddr0 + 96, va);
+                    tmem_ld_wait(va);
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane0) mbar_arrive(my_tempty);
+                    test4(va, 3);
+                    aph ^= 1;
+                    if (qn >= 32u) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                     continue;
                 }
                 if (MODE == 6) {
@@ -731,6 +870,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
         }
         if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
+        if (MODE == 7 && qn) qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, lane, qn);
         }
     tcgen05_fence_before();
     __syncthreads();
@@ -1247,7 +1387,8 @@ struct QtcState {
 template <int S>
 __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, const int32_t* __restrict__ dcls,
                                  __half* __restrict__ poolA, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
-                                 uint32_t* __restrict__ sq4, float* __restrict__ sds8, uint8_t* __restrict__ dtyp)
+                                 uint32_t* __restrict__ sq4, float* __restrict__ sds8, uint8_t* __restrict__ dtyp,
+                                 double* __restrict__ den)
 {
     constexpr int N = S * S;
     const int PW = W - 2 * S + 1, PH = H - 2 * S + 1, BW = W - 1;
@@ -1308,17 +1449,17 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
             }
 #pragma unroll
         for (int t = 0; t < 8; ++t) sds8[(size_t)t * NP + p] = acc[t];
+        // the eight sums differ by rounding only; the bound test of the fused pass uses the smallest denominator (drops less)
+        float lo = acc[0];
+#pragma unroll
+        for (int t = 1; t < 8; ++t) lo = fminf(lo, acc[t]);
+        const double dsd = (double)__fmul_rn((float)s, 0.25f);
+        den[p] = DS(DM((double)N, (double)lo), DM(dsd, dsd));
+    } else {
+        const double dsd = (double)__fmul_rn((float)s, 0.25f);
+        den[p] = DS(DM((double)N, (double)__fmul_rn((float)(uint32_t)s2, 0.0625f)), DM(dsd, dsd));
     }
 }
-
-// Per-range constants of the scoring loop, one 32-byte record (written by qt_tcinit_kernel).
-struct __align__(16) QtcRange {
-    int rho;                  // sum r - N * round(sum r / N): the centring remainder of the range
-    int ok;                   // 0: not searched here (past the end, or handed to the exact search)
-    uint32_t tw0, tw1;        // isometry by domain type, eight 4-bit entries, for positive / negative scales
-    double slack;             // sum r^2 - (sum r)^2 / N
-    float rs, sqr;
-};
 
 // one warp per slot: range sums, state, thresholds, the range operand (eight isometric copies, centred)
 template <int S>
@@ -1988,19 +2129,14 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     const uint16_t* P = h->bf_boxsum.as<uint16_t>();
     uint32_t cap = 8192;
     while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
-    // batch of column groups whose selected accumulators are held at once: 64 floats per position and group, at most 1 GiB
-    int batch = (int)(((size_t)1 << 30) / ((size_t)np_pad * 64 * sizeof(float)));
-    if (batch < 1) batch = 1;
-    if (batch > n_groups) batch = n_groups;
     FIC_TRY(h->bf_pool.reserve((size_t)np_pad * N * 2 + 256));
     FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
-    FIC_TRY(h->bf_stats.reserve((size_t)NP * (2 * sizeof(uint32_t) + 8 * sizeof(float) + 1) + 1024));
+    FIC_TRY(h->bf_stats.reserve((size_t)NP * (2 * sizeof(uint32_t) + 8 * sizeof(float) + 1 + sizeof(double)) + 1024));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * N * 2 + 256));
     FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * (sizeof(float2) + 1) + (size_t)n_ranges * sizeof(QtcState) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
     FIC_TRY(h->bf_best.reserve((size_t)tau_pad * (8 + sizeof(QtcRange)) + 512));
-    FIC_TRY(h->bf_dump.reserve((size_t)batch * 64 * np_pad * sizeof(float) + 256));
     if (!h->bf_ctrl.p) {
         FIC_TRY(h->bf_ctrl.reserve(256));
         FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
@@ -2010,7 +2146,8 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     uint32_t* sd4 = h->bf_stats.as<uint32_t>();
     uint32_t* sq4 = sd4 + NP;
     float* sds8 = reinterpret_cast<float*>(sq4 + NP);
-    uint8_t* dtyp = reinterpret_cast<uint8_t*>(sds8 + (size_t)8 * NP);
+    double* den = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(sds8 + (size_t)8 * NP) + 15) & ~(uintptr_t)15);
+    uint8_t* dtyp = reinterpret_cast<uint8_t*>(den + NP);
     __half* rngB = h->bf_A.as<__half>();
     QtcState* state = h->bf_thr.as<QtcState>();
     float2* tau = reinterpret_cast<float2*>(state + n_ranges);
@@ -2020,9 +2157,8 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     int* ctrl = h->bf_ctrl.as<int>();
     unsigned long long* bound = h->bf_best.as<unsigned long long>();
     QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + tau_pad) + 15) & ~(uintptr_t)15);
-    float* dump = h->bf_dump.as<float>();
 
-    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, hk, sd4, sq4, sds8, dtyp);
+    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, hk, sd4, sq4, sds8, dtyp, den);
     FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
     qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, bound, ctrl, tau_pad, rngB,
                                                                             d_need_exact, rtyp, rngc);
@@ -2033,60 +2169,41 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, N, BM, sw));
     FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, N, BN, sw));
     if (!h->qt_screen_attr_ready) {
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<6, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(8)));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(8)));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(4)));
-        FIC_CUDA(cudaFuncSetAttribute(qt_tcscore_kernel<4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, QTC_SCORE_SMEM(4)));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<7, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<7, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
         h->qt_screen_attr_ready = true;
     }
     ScreenParams sp;
     sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
     sp.seed_best = nullptr; sp.err_flag = ctrl + 2; sp.debug_mode = 0;
-    sp.m_cur = 1; sp.r_prev = 0; sp.n_round_tiles = n_tiles;
+    sp.r_prev = 0;
     sp.window_tiles = (64 << 20) / (BM * N * 2);
-    sp.dump = dump; sp.dtyp = dtyp; sp.rtyp = rtyp; sp.np_pad = np_pad;
-    // every stride-th run of 32 positions is scored first: with the bounds still at +inf every candidate would enter the lists
+    sp.dump = nullptr; sp.dtyp = dtyp; sp.rtyp = rtyp; sp.np_pad = np_pad;
+    sp.grp_begin = 0; sp.grp_count = n_groups;
+    sp.rngc = rngc; sp.bound = bound; sp.sd4 = sd4; sp.sq4 = sq4; sp.sds8 = sds8; sp.den = den;
+    sp.max_scale = max_scale; sp.scale_bits = scale_bits; sp.offset_bits = offset_bits; sp.nmodes = nmodes;
+    // Seed pass: every stride-th tile of 128 positions is looked at first and only lowers the bounds -- with the bounds at
+    // +inf, and every CTA on a different range, nearly all of its candidates would be listed.  The full pass then lists
+    // from all positions against bounds that mean something.
     const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 1);
-    for (int g0 = 0; g0 < n_groups; g0 += batch) {
-        const int gc = std::min(batch, n_groups - g0);
-        sp.grp_begin = g0; sp.grp_count = gc;
-        bf_screen_kernel<6, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
-        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass)");
-        // enough CTAs for eight waves of three per SM; each walks the groups blockIdx.y, blockIdx.y + gridDim.y, ...
-        auto score = [&](int n_pos, int seed) {
-            const int nx = cdiv(n_pos, QTC_POS);
-            const int ny = std::max(1, std::min(gc, cdiv(h->num_sms * 3 * 8, nx)));
-            QtcScoreParams q;
-            q.dump = dump; q.rngc = rngc; q.dtyp = dtyp; q.sd4 = sd4; q.sq4 = sq4; q.sds8 = sds8; q.bound = bound; q.cnt = cnt; q.list = list;
-            q.max_scale = max_scale; q.cap = cap; q.np_pad = np_pad; q.NP = NP; q.grp_begin = g0; q.grp_count = gc;
-            q.scale_bits = scale_bits; q.offset_bits = offset_bits; q.p_stride = stride; q.seed_pass = seed;
-            if (nmodes == 2) qt_tcscore_kernel<S, 2><<<dim3(nx, ny), 256, QTC_SCORE_SMEM(S), st>>>(q);
-            else qt_tcscore_kernel<S, 1><<<dim3(nx, ny), 256, QTC_SCORE_SMEM(S), st>>>(q);
-        };
-#ifdef FIC_QTC_DEBUG
-        auto dbg = [&](const char* what) {
-            const int n = std::min(n_ranges - g0 * 32, gc * 32);
-            std::vector<uint32_t> c(n);
-            cudaStreamSynchronize(st);
-            cudaMemcpy(c.data(), cnt + (size_t)g0 * 32, (size_t)n * 4, cudaMemcpyDeviceToHost);
-            unsigned long long sum = 0; uint32_t mx = 0;
-            for (uint32_t v : c) { sum += v; mx = std::max(mx, v); }
-            fprintf(stderr, "[qtc S=%d g0=%d] %s: ranges %d, listed %llu, longest %u (cap %u)\n", S, g0, what, n, sum, mx, cap);
-        };
-#else
-        auto dbg = [&](const char*) {};
-#endif
-        if (stride > 1) {
-            score(cdiv(cdiv(NP, 32), stride) * 32, 1);
-            FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel(seed)");
-            dbg("after the seed pass");
-        }
-        score(NP, 0);
-        FIC_CHECK_LAUNCH(h, "qt_tcscore_kernel");
-        dbg("after the full pass");
+    if (stride > 1) {
+        sp.m_cur = stride; sp.n_round_tiles = cdiv(n_tiles, stride); sp.seed_pass = 1;
+        bf_screen_kernel<7, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+        FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass, seed)");
     }
+    sp.m_cur = 1; sp.n_round_tiles = n_tiles; sp.seed_pass = 0;
+    bf_screen_kernel<7, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+    FIC_CHECK_LAUNCH(h, "bf_screen_kernel(quadtree exact pass)");
+#ifdef FIC_QTC_DEBUG
+    {
+        std::vector<uint32_t> c(n_ranges);
+        cudaStreamSynchronize(st);
+        cudaMemcpy(c.data(), cnt, (size_t)n_ranges * 4, cudaMemcpyDeviceToHost);
+        unsigned long long sum = 0; uint32_t mx = 0;
+        for (uint32_t v : c) { sum += v; mx = std::max(mx, v); }
+        fprintf(stderr, "[qtc S=%d] ranges %d, listed %llu, longest %u (cap %u)\n", S, n_ranges, sum, mx, cap);
+    }
+#endif
     // the lists hold every candidate that was at or below its range's best score when it was looked at: first minimum in scan order
     qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 1, nmodes,
                                                                                 max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, nullptr, 0, 0);
