@@ -239,12 +239,9 @@ struct ScreenParams {
     int* err_flag;
     int debug_mode;          // 0 = normal; 1/2/3 = timing experiments (FIC_SCREEN_DEBUG), results invalid
     unsigned long long* seed_best;   // seed mode: [slots] max of (gain bits << 32 | ~local candidate)
-    // MODE 6 (quadtree exact pass): the accumulator of every (candidate, range, scale sign) pair's own isometry goes to
-    // dump[((grp - grp_begin) * 64 + range_in_group * 2 + sign) * np_pad + candidate]
+    // MODE 7 (quadtree exact pass): the bound test runs in the epilogue, survivors are scored from the warp's queue
     const uint8_t* dtyp;     // [NP] domain type = rotation | orientation << 2
-    const uint8_t* rtyp;     // [slots] range type = rot(+) | orient(+) << 2 | rot(-) << 3 | orient(-) << 5
-    int grp_begin, grp_count, np_pad;
-    // MODE 7 (quadtree exact pass, fused): the bound test runs in the epilogue, survivors are scored from the warp's queue
+    int grp_begin, grp_count;        // column groups of this launch
     const QtcRange* rngc;    // [slots]
     unsigned long long* bound;       // [slots] best score found so far (bits of a non-negative double)
     const uint32_t* sd4;     // [NP] sum D4
@@ -347,7 +344,7 @@ constexpr int QT_QROOM = 4 * 2 * 32;          // a 32-column chunk adds at most 
 static_assert(QT_QCAP >= QT_QROOM + 32, "queue of the quadtree pass too small");
 struct QtQueue {
     QtcRange rng[RANGES_PER_WARP];   // the records of the warp's sixteen ranges, refreshed per column group
-    uint4 e[QT_QCAP];        // x = slot, y = position, z = stored accumulator (int), w = isometry
+    uint4 e[QT_QCAP];        // x = slot, y = position, z = the accumulator (float bits, an integer), w = isometry
 };
 static_assert(sizeof(QtcRange) == 32 && sizeof(QtQueue) <= QUEUE_BYTES, "QtQueue must fit a warp's queue slice");
 
@@ -357,7 +354,7 @@ __device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams
     __syncwarp();
     for (uint32_t k = lane; k < n; k += 32) {
         const uint4 en = q->e[k];
-        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)en.z, t = (int)en.w;
+        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)__uint_as_float(en.z), t = (int)en.w;
         const QtcRange rc = p.rngc[slot];
         const unsigned sd = p.sd4[cand], sq = p.sq4[cand];
         const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
@@ -480,8 +477,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
-    const int grp_off = MODE == 6 || MODE == 7 ? p.grp_begin : 0;            // the quadtree modes name their column groups
-    const int n_groups = MODE == 6 || MODE == 7 ? p.grp_count : (n_elig + 31) / 32;
+    const int grp_off = MODE == 7 ? p.grp_begin : 0;            // the quadtree modes name their column groups
+    const int n_groups = MODE == 7 ? p.grp_count : (n_elig + 31) / 32;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -593,7 +590,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
             // this warp's (tau_A, tau_B) pairs live in a private slice of shared memory; broadcast reads, no bank conflicts
             __syncwarp();
-            if (lane < 16) {
+            if (MODE != 7 && lane < 16) {
                 const float2 tt = p.tau[grp * 32 + part * 16 + lane];
                 my_tau[lane] = tt.x;
                 my_tau[16 + lane] = tt.y;
@@ -617,7 +614,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             // +-1/h_c of this lane's candidate, fetched one tile ahead; sign = conditioning class; +inf (threshold never
             // met) for the padding rows of the last tile
             const float hk_pad = __int_as_float(0x7f800000);
-            float hq_next = (j < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+            float hq_next = (MODE != 7 && j < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
             // the sixteen tau of the next tile (class picked by the sign of its hq) are fetched at the END of the current
             // tile, when both chunk buffers are dead, so the shared-memory latency is paid under the index arithmetic
             float4 tq0, tq1, tq2, tq3;
@@ -640,7 +637,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     cand += (2 + wraps) * p.m_cur * BM;
                 }
                 const float hq = hq_next;
-                hq_next = (j + 2 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+                hq_next = (MODE != 7 && j + 2 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
                 const int lane = my_cand & 31;            // shadows the outer lane on purpose
                 const uint32_t lane0 = lane == 0;
                 if (MODE == 5) {
@@ -695,10 +692,15 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     const int eps = (int)sdc - KT * (int)((sdc + (unsigned)(KT / 2)) / (unsigned)KT);
                     const int dsh = 4 * (int)(dty & 7u);
                     const bool den_ok = have && den > 0.0;
+                    const float feps = (float)eps;
+                    const bool two = p.nmodes == 2;
                     const unsigned long long Bl = __ldcg(&p.bound[slot0 + (lane & 15)]);
                     QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
                     const unsigned lt = (1u << lane) - 1u;
                     uint32_t va[32];
+                    // The comparison itself runs in float32: X is an integer below 2^24 and N a power of two, so
+                    // fmaf(N, X, -rho * eps) is the numerator rounded once, its square and the converted right-hand side add
+                    // two more roundings -- 2.5e-7 relative in all, inside the 1e-6 the right-hand side was shrunk by.
                     auto test4 = [&](const uint32_t (&v)[32], int c4) {
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
@@ -709,25 +711,26 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                             const double B = __longlong_as_double((long long)__shfl_sync(0xffffffffu, Bl, r));
                             if (!ri.y) continue;
                             const double rhs_g = DM(DS(slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
-                            const bool cull_ok = den_ok && rhs_g > 0.0;
-                            const double rhs = DM(rhs_g, den);
-                            const int nre = -ri.x * eps;
-#pragma unroll
-                            for (int md = 0; md < 2; ++md) {
-                                if (md < p.nmodes) {
-                                    const int t = (int)(((uint32_t)(md ? ri.w : ri.z) >> dsh) & 7u);
-                                    const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
-                                    const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
-                                    const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
-                                    const int Xi = (int)__uint_as_float((t & 4) ? y1 : y0);
-                                    const double nd = (double)(KT * Xi + nre);
-                                    const bool surv = have && !(cull_ok && DM(nd, nd) < rhs);
-                                    const unsigned m = __ballot_sync(0xffffffffu, surv);
-                                    if (m) {
-                                        if (surv) qq->e[qn + __popc(m & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, (uint32_t)Xi, (uint32_t)t);
-                                        qn += __popc(m);
-                                    }
-                                }
+                            // not droppable (bound still too high, degenerate block, padding row): right-hand side below any square
+                            const float rhs = den_ok && rhs_g > 0.0 ? (float)DM(rhs_g, den) : -1.0f;
+                            const float nre = -(float)ri.x * feps;
+                            auto pick = [&](uint32_t tw) {
+                                const int t = (int)((tw >> dsh) & 7u);
+                                const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
+                                const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
+                                const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
+                                return (t & 4) ? y1 : y0;
+                            };
+                            const uint32_t xa = pick((uint32_t)ri.z), xb = two ? pick((uint32_t)ri.w) : 0u;
+                            const float na = fmaf((float)KT, __uint_as_float(xa), nre), nb = fmaf((float)KT, __uint_as_float(xb), nre);
+                            const bool sa = have && !(__fmul_rn(na, na) < rhs), sb = two && have && !(__fmul_rn(nb, nb) < rhs);
+                            if (__any_sync(0xffffffffu, sa || sb)) {
+                                const unsigned ma = __ballot_sync(0xffffffffu, sa);
+                                if (sa) qq->e[qn + __popc(ma & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xa, (uint32_t)ri.z >> dsh & 7u);
+                                qn += __popc(ma);
+                                const unsigned mb = __ballot_sync(0xffffffffu, sb);
+                                if (sb) qq->e[qn + __popc(mb & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xb, (uint32_t)ri.w >> dsh & 7u);
+                                qn += __popc(mb);
                             }
                         }
                         if (qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
@@ -752,52 +755,6 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     test4(va, 3);
                     aph ^= 1;
                     if (qn >= 32u) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
-                    continue;
-                }
-                if (MODE == 6) {
-                    // exact pass of the quadtree search: no thresholds.  Every (candidate, range, scale sign) pair has ONE
-                    // isometry, derived from the two classifications (quadtree/encoder.py:168-176); its accumulator -- the exact
-                    // integer sum r'.D4' -- is picked out of the range's eight columns and stored for the scoring kernel.
-                    const unsigned dty = my_cand < p.NP ? p.dtyp[my_cand] : 0u;
-                    const int drot = dty & 3, dori = (dty >> 2) & 1;
-                    const uint4 rt4 = *reinterpret_cast<const uint4*>(p.rtyp + (size_t)(grp * 32 + part * 16));
-                    const uint32_t rtw[4] = {rt4.x, rt4.y, rt4.z, rt4.w};
-                    float* out = p.dump + ((size_t)(grp - grp_off) * 64 + (size_t)part * 32) * p.np_pad + my_cand;
-                    uint32_t va[32], vb[32];
-                    auto pick4 = [&](const uint32_t (&v)[32], int c4) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            const unsigned rb = (rtw[c4] >> (8 * g)) & 0xffu;
-#pragma unroll
-                            for (int md = 0; md < 2; ++md) {
-                                const int rrot = (rb >> (3 * md)) & 3, rori = (rb >> (3 * md + 2)) & 1;
-                                const bool same = dori == rori;
-                                const int t = ((drot - rrot + (same ? 0 : 2)) & 3) | (same ? 0 : 4);
-                                const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
-                                const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
-                                const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
-                                out[(size_t)((c4 * 4 + g) * 2 + md) * p.np_pad] = __uint_as_float((t & 4) ? y1 : y0);
-                            }
-                        }
-                    };
-                    mbar_wait(my_tfull, aph, p.err_flag, 6);
-                    tcgen05_fence_after();
-                    tmem_ld32(taddr0, va);
-                    tmem_ld32(taddr0 + 32, vb);
-                    tmem_ld_wait(va);
-                    tmem_ld_wait(vb);
-                    pick4(va, 0);
-                    tmem_ld32(taddr0 + 64, va);
-                    pick4(vb, 1);
-                    tmem_ld32(taddr0 + 96, vb);
-                    tmem_ld_wait(va);
-                    tmem_ld_wait(vb);
-                    tcgen05_fence_before();
-                    __syncwarp();
-                    if (lane0) mbar_arrive(my_tempty);
-                    pick4(va, 2);
-                    pick4(vb, 3);
-                    aph ^= 1;
                     continue;
                 }
                 const float qx = fabsf(hq);
@@ -1359,36 +1316,32 @@ inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 
 // =================================================================================================================
-// Quadtree: the dense-pool, all-classes search on the same screen (quadtree/encoder.py:148-193, 285-384 with
+// Quadtree: the dense-pool, all-classes search on the tensor cores (quadtree/encoder.py:148-193, 285-384 with
 // domain_hstep = domain_vstep = 1 and full_class_search).  Every range of a level is matched against every domain
 // position, which is the brute-force contraction with two differences:
 //   * one isometry per (range, domain) pair and scale sign, derived from the two classifications -- the GEMM still
-//     forms all eight, the epilogue's per-isometry masks tell the rescoring kernel which ones passed, and only the
-//     pair's own isometry is scored;
+//     forms all eight and the epilogue picks the pair's own column;
 //   * the score is the QUANTISED one (fic_q_score), the winner the first minimum in the reference's scan order
-//     (scale sign, class, position).  Its lower bound has the brute-force form with n pixels per block:
-//         n E >= A_r - n u^2 / den_n ,   den_n = n sum(D4^2) - (sum D4)^2 ,
-//     so thresholds, rounds and survivor lists are shared.  For 8x8 blocks the float32 sequential sum of d^2 is the
-//     one inexact input (as in the brute-force encoder); its effect is at most kappa s^2 with |s| <= max_scale <= 1,
-//     covered by the constant guard of the ill-conditioned class for every candidate.  For 4x4 blocks every sum is
-//     exact in float32 and no guard is needed.
-// Ranges the screen cannot decide (constant blocks, bound not below the variance, list overflow) are flagged and
-// searched by qt_search_kernel.
+//     (scale sign, class, position).
+// The GEMM's accumulators are exact integers (centred pixel sums in fp16, fp32 accumulation well below 2^24), so the
+// picked column gives the pair's exact dot product and with it all five inputs of the scorer bit for bit -- nothing here
+// is a screen that could be wrong.  What the epilogue tests is the scorer's own lower bound
+//     n E >= A_r - num^2 / (n den) ,   num = n sum(r d) - sum r sum d ,   den = n sum(d^2) - (sum d)^2 ,
+// against the best score found so far for the range: a pair whose bound is above it cannot win and is dropped, everything
+// else is scored exactly and, when at or below the best score at that moment, listed.  qt_tcpick_kernel then takes the
+// first minimum in scan order among the listed.  Constant ranges (every candidate ties, the scan order alone decides) and
+// ranges whose list overflowed are flagged and searched by qt_search_kernel.
 struct QtcState {
-    double E, s, o, TA0;
-    unsigned long long key;       // (mode * 72 + class) << 32 | position: the reference's scan order
-    int32_t rec[6];               // di, dj, orient, rot, qs, qo of the running winner
     int32_t flags;                // 1 = handed to the exact search
     int32_t si, sj;
     int32_t rot[2], orient[2];    // the range's classification for positive / negative scales
-    float rs, sqr;
+    float rs, sqr;                // sum r, sum r^2 (integers below 2^24)
 };
 
 template <int S>
 __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, const int32_t* __restrict__ dcls,
-                                 __half* __restrict__ poolA, float2* __restrict__ hk, uint32_t* __restrict__ sd4,
-                                 uint32_t* __restrict__ sq4, float* __restrict__ sds8, uint8_t* __restrict__ dtyp,
-                                 double* __restrict__ den)
+                                 __half* __restrict__ poolA, uint32_t* __restrict__ sd4, uint32_t* __restrict__ sq4,
+                                 float* __restrict__ sds8, uint8_t* __restrict__ dtyp, double* __restrict__ den)
 {
     constexpr int N = S * S;
     const int PW = W - 2 * S + 1, PH = H - 2 * S + 1, BW = W - 1;
@@ -1423,7 +1376,6 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
         o.w = *reinterpret_cast<uint32_t*>(&h3);
         dst[q] = o;
     }
-    hk[p] = make_float2(__int_as_float(0x7f800000), 0.f);   // (the exact pass has no thresholds; the kernel still prefetches this)
     sd4[p] = (uint32_t)s;
     sq4[p] = (uint32_t)s2;
     dtyp[p] = (uint8_t)((dcls[3 * (size_t)p + 1] & 3) | ((dcls[3 * (size_t)p + 2] & 1) << 2));
@@ -1461,31 +1413,26 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
     }
 }
 
-// one warp per slot: range sums, state, thresholds, the range operand (eight isometric copies, centred)
+// one warp per slot: range sums, state, the record of the bound test, the range operand (eight isometric copies, centred)
 template <int S>
 __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const int32_t* __restrict__ queue /*[n][4]*/,
                                  const int32_t* __restrict__ rcls /*[n][2][3] = class, rot, orient per scale sign*/, int n_ranges,
-                                 QtcState* __restrict__ state, float2* __restrict__ tau, uint32_t* __restrict__ cnt,
-                                 unsigned long long* __restrict__ seed_best, int* __restrict__ ctrl, int tau_pad,
-                                 __half* __restrict__ rngB, int32_t* __restrict__ need_exact, uint8_t* __restrict__ rtyp,
+                                 QtcState* __restrict__ state, uint32_t* __restrict__ cnt, unsigned long long* __restrict__ bound,
+                                 int* __restrict__ ctrl, int slots_pad, __half* __restrict__ rngB, int32_t* __restrict__ need_exact,
                                  QtcRange* __restrict__ rngc)
 {
     constexpr int N = S * S;
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (slot >= tau_pad) return;
+    if (slot >= slots_pad) return;
     if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
-    if (lane == 0) {
-        tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
-        seed_best[slot] = 0x7ff0000000000000ull;      // the exact pass keeps the best score found so far here (+inf)
-        rtyp[slot] = 0;
-        if (slot >= n_ranges) {
+    if (lane == 0) bound[slot] = 0x7ff0000000000000ull;      // best score found so far: +inf
+    if (slot >= n_ranges) {   // padding columns of the last group: zero operand, record that says "skip"
+        for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
+        if (lane == 0) {
             QtcRange rc;
             rc.rho = 0; rc.ok = 0; rc.tw0 = rc.tw1 = 0u; rc.slack = 0.0; rc.rs = rc.sqr = 0.f;
             rngc[slot] = rc;
         }
-    }
-    if (slot >= n_ranges) {   // padding columns of the last group: zero operand
-        for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
         return;
     }
     const int si = queue[4 * (size_t)slot], sj = queue[4 * (size_t)slot + 1];
@@ -1519,20 +1466,14 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
         }
     if (lane == 0) {
         const long long sl = sm, ql = q32;
-        const long long An = (long long)N * ql - sl * sl;            // n A_r, exact
         QtcState st;
-        st.E = __longlong_as_double(0x7ff0000000000000ll); st.s = 0.0; st.o = 0.0;
-        st.TA0 = (double)An / (double)N - (double)N * 1e-9 * (double)ql;
-        st.key = ~0ull;
-        for (int k = 0; k < 6; ++k) st.rec[k] = 0;
-        st.flags = An == 0 ? 1 : 0;      // constant block: every candidate ties, the scan order decides -> exact search
+        st.flags = (long long)N * ql - sl * sl == 0 ? 1 : 0;      // constant block: every candidate ties, the scan order decides -> exact search
         st.si = si; st.sj = sj;
         for (int md = 0; md < 2; ++md) { st.rot[md] = rcls[6 * (size_t)slot + 3 * md + 1]; st.orient[md] = rcls[6 * (size_t)slot + 3 * md + 2]; }
         st.rs = (float)sl; st.sqr = (float)ql;     // exact: <= 64 * 255^2 < 2^24
         state[slot] = st;
         cnt[slot] = 0;
         need_exact[slot] = st.flags;
-        rtyp[slot] = (uint8_t)((st.rot[0] & 3) | ((st.orient[0] & 1) << 2) | ((st.rot[1] & 3) << 3) | ((st.orient[1] & 1) << 5));
         QtcRange rc;
         rc.rho = (int)sm - N * m;
         rc.ok = !st.flags;
@@ -1552,164 +1493,17 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
     }
 }
 
-// ---- exact pass: every (range, position, scale sign) scored from the GEMM's exact dot product ---------------------------
-// One CTA per (chunk of 256 positions, column group of the batch); a thread owns a position and walks the group's 32 ranges.
-// ab comes from the stored accumulator (r'.D4' un-centred: integers, exact), ds and -- for 4x4 blocks -- sds from the
-// position's integer sums, sds of an 8x8 block from the table of sequential float32 sums: the five inputs of the scorer are
-// bit for bit what the pixel loop of qt_search_kernel produces.  A candidate whose lower bound or score is above the best
-// score found so far for its range (kept in global memory, shared by all CTAs) is dropped; everything else goes to the
-// range's list and the rescoring kernel picks the first minimum in scan order among them.
-#define QTC_POS 128           /* positions per CTA of qt_tcscore_kernel; its 256 threads split a group's 32 ranges in two */
-struct QtcScoreParams {
-    const float* dump; const QtcRange* rngc; const uint8_t* dtyp; const uint32_t* sd4; const uint32_t* sq4; const float* sds8;
-    unsigned long long* bound; uint32_t* cnt; uint32_t* list;
-    double max_scale;
-    uint32_t cap;
-    int np_pad, NP, grp_begin, grp_count, scale_bits, offset_bits, p_stride, seed_pass;
-};
-
-// A candidate the bound test did not drop: exact score, bound update, entry in the range's list.  Out of line on purpose --
-// inlined, the compiler moves whatever here depends only on (range, position) in front of the test (the scorer's divisions,
-// the list addresses), and most of the kernel's instructions were spent on the few per cent of candidates that get here (ncu).
-template <int N>
-__device__ __noinline__ void qt_score_survivor(const QtcScoreParams& prm, const QtcRange* rcp, unsigned long long* s_bound_g, int slot, int p,
-                                               int t, int Xi, unsigned sd, unsigned sq)
-{
-    const QtcRange rc = *rcp;
-    const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
-    const int mr = ((int)rc.rs - rc.rho) / N;
-    const int dot = Xi + mr * eps + mc * rc.rho + N * mr * mc;     // sum r D4, exact
-    const float ab = __fmul_rn((float)dot, 0.25f);
-    const float ds = __fmul_rn((float)sd, 0.25f);
-    const float sds = N == 64 ? prm.sds8[(size_t)t * prm.NP + p] : __fmul_rn((float)sq, 0.0625f);
-    const QScore sc = fic_q_score(N, rc.rs, rc.sqr, ds, sds, ab, prm.max_scale, prm.scale_bits, prm.offset_bits);
-    const double B = __longlong_as_double((long long)*(volatile unsigned long long*)s_bound_g);
-    if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
-        if (sc.R < B) {
-            const unsigned long long bits = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
-            atomicMin(s_bound_g, bits);
-            atomicMin(&prm.bound[slot], bits);
-        }
-        if (!prm.seed_pass) {
-            const uint32_t at = atomicAdd(&prm.cnt[slot], 1u);
-            if (at < prm.cap) prm.list[(size_t)slot * prm.cap + at] = (uint32_t)p * 8u + (uint32_t)t;
-        }
-    }
-}
-
-__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
-// A CTA owns QTC_POS positions and walks the column groups blockIdx.y, blockIdx.y + gridDim.y, ... of the batch: the slice of
-// stored accumulators (64 x QTC_POS floats) and the 32 range records of the NEXT group are on their way (cp.async) while the
-// current group is scored, and what depends on the position alone is computed once per CTA.
-template <int S, int NM>
-__global__ void __launch_bounds__(256, 3)
-qt_tcscore_kernel(const __grid_constant__ QtcScoreParams prm)
-{
-    constexpr int N = S * S;
-    constexpr int Q4 = QTC_POS / 4;               // float4 per row of a slice
-    extern __shared__ __align__(16) unsigned char s_raw[];
-    float* s_x = reinterpret_cast<float*>(s_raw);                                // [2][64][QTC_POS]
-    double* s_den = reinterpret_cast<double*>(s_raw + 2 * 64 * QTC_POS * 4);      // [8][QTC_POS], 8x8 blocks only: N * sds - ds^2 by isometry
-    __shared__ QtcRange s_rng[2][32];
-    __shared__ unsigned long long s_bound[32];   // best score per range as this CTA knows it (global value when the group is begun + own finds)
-    const int pl = threadIdx.x & (QTC_POS - 1), half = threadIdx.x / QTC_POS;
-    // Seed pass: every p_stride-th run of 32 positions (one 128-byte line per stored row) is scored first and only lowers the
-    // bounds -- with the bounds at +inf and a hundred thousand threads on the same ranges at once, nearly all of its
-    // candidates would be listed (measured: 88 %).  The full pass then lists from all positions against bounds that mean something.
-    const int run_stride = prm.seed_pass ? prm.p_stride : 1;
-    auto stage = [&](int unit, int buf) {
-        const float* src = prm.dump + (size_t)unit * 64 * prm.np_pad;      // rows of np_pad floats, np_pad a multiple of 128
-        float* dst = s_x + buf * 64 * QTC_POS;
-        for (int e = threadIdx.x; e < 64 * Q4; e += 256) {
-            const int row = e / Q4, c4 = e % Q4;
-            const long long at = ((long long)(blockIdx.x * (QTC_POS / 32) + (c4 >> 3)) * run_stride) * 32 + (c4 & 7) * 4;
-            if (at < prm.np_pad) cp_async16(dst + row * QTC_POS + c4 * 4, src + (size_t)row * prm.np_pad + at);
-        }
-        if (threadIdx.x < 64)
-            cp_async16(reinterpret_cast<unsigned char*>(&s_rng[buf][0]) + threadIdx.x * 16,
-                       reinterpret_cast<const unsigned char*>(prm.rngc + (size_t)(prm.grp_begin + unit) * 32) + threadIdx.x * 16);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    int unit = blockIdx.y;
-    if (unit < prm.grp_count) stage(unit, 0);
-
-    const int q = blockIdx.x * QTC_POS + pl;
-    const int p = (q >> 5) * run_stride * 32 + (q & 31);
-    const bool live = p < prm.NP;
-    unsigned sd = 0, sq = 0, dty = 0;
-    if (live) { sd = prm.sd4[p]; sq = prm.sq4[p]; dty = prm.dtyp[p]; }
-    const int eps = (int)sd - N * (int)((sd + (unsigned)(N / 2)) / (unsigned)N);
-    const double dn = (double)N;
-    double den16 = 0.0;
-    {
-        const double dsd = (double)__fmul_rn((float)sd, 0.25f);
-        if (N == 64) {
-            if (live && half == 0)
-                for (int t = 0; t < 8; ++t) s_den[t * QTC_POS + pl] = DS(DM(dn, (double)prm.sds8[(size_t)t * prm.NP + p]), DM(dsd, dsd));
-        } else {
-            den16 = DS(DM(dn, (double)__fmul_rn((float)sq, 0.0625f)), DM(dsd, dsd));
-        }
-    }
-    const int dsh = 4 * (int)(dty & 7);
-
-    for (int it = 0; unit < prm.grp_count; unit += gridDim.y, ++it) {
-        const int buf = it & 1, grp = prm.grp_begin + unit;
-        if (unit + (int)gridDim.y < prm.grp_count) {
-            stage(unit + gridDim.y, buf ^ 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
-        if (threadIdx.x < 32) s_bound[threadIdx.x] = __ldcg(&prm.bound[grp * 32 + threadIdx.x]);
-        __syncthreads();
-        // The test per candidate, in the units of the integer numerator 4 * (N * ab - rs * ds) = N * X - rho * eps (X the
-        // stored accumulator of the centred block and range): dropped when its square is below 16 * N * den * (slack - N * B),
-        // the scorer's lower bound with both sides multiplied out; everything not dropped is scored exactly.
-        if (live) {
-            const float* xs = s_x + buf * 64 * QTC_POS + pl;
-            const QtcRange* rcs = &s_rng[buf][half * 16];
-#pragma unroll 1
-            for (int gi = 0; gi < 16; ++gi) {
-                const int g = half * 16 + gi;
-                const int4 ri = *reinterpret_cast<const int4*>(rcs + gi);          // rho, ok, tw0, tw1
-                if (!ri.y) continue;
-                const double slack = rcs[gi].slack;
-                const double B = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound[g]);
-                const double room = DS(slack, DM(dn, B));
-                const double rhs_g = DM(DM(DM(room, dn), 16.0), 0.999999999);
-                const int nre = -ri.x * eps;
-                const bool cullable = room > 0.0;
-#pragma unroll
-                for (int md = 0; md < NM; ++md) {
-                    const int Xi = (int)xs[(g * 2 + md) * QTC_POS];
-                    const int t = (int)(((uint32_t)(md ? ri.w : ri.z) >> dsh) & 7u);
-                    const double den = N == 64 ? s_den[t * QTC_POS + pl] : den16;
-                    const double nd = (double)(N * Xi + nre);
-                    if (cullable && den > 0.0 && DM(nd, nd) < DM(rhs_g, den)) continue;
-                    qt_score_survivor<N>(prm, rcs + gi, &s_bound[g], grp * 32 + g, p, t, Xi, sd, sq);
-                }
-            }
-        }
-        __syncthreads();
-    }
-}
-
+// ---- the winner of every range: first minimum in scan order among the listed candidates -------------------------------
+// QTC_WARPS ranges per CTA; their lists are laid end to end and every thread rescores one entry per pass from the pixels
+// (the reference's own float32 sums, row-major over the range block), so a long list is shared by the whole CTA.
 #define QTC_WARPS 32
-#define QTC_SCORE_SMEM(S) (2 * 64 * QTC_POS * 4 + ((S) == 8 ? 8 * QTC_POS * 8 : 0))   /* dynamic shared memory of qt_tcscore_kernel */
-#ifndef QTC_MIN_EXPLAINED
-#define QTC_MIN_EXPLAINED 0.2
-#endif
 template <int S>
 __global__ void __launch_bounds__(QTC_WARPS * 32, 1)
-qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
-                    const int32_t* __restrict__ dcls /*[NP][3] = class, rot, orient*/, int H, int W, QtcState* __restrict__ state,
-                    int* __restrict__ ctrl, uint32_t* __restrict__ cnt, uint32_t* list, uint32_t cap, float2* __restrict__ tau,
-                    int emit, int nmodes, double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ out_rec,
-                    double* __restrict__ out_vals, int32_t* __restrict__ need_exact,
-                    const unsigned long long* __restrict__ seed_best, int seed_S, int seed_gx)
+qt_tcpick_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
+                 const int32_t* __restrict__ dcls /*[NP][3] = class, rot, orient*/, int H, int W, QtcState* __restrict__ state,
+                 const int* __restrict__ ctrl, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
+                 int nmodes, double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ out_rec,
+                 double* __restrict__ out_vals, int32_t* __restrict__ need_exact)
 {
     constexpr int N = S * S;
     __shared__ float rv[QTC_WARPS][N];            // the range blocks as floats
@@ -1728,29 +1522,13 @@ qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ 
     if (lane == 0) { s_n[warp] = 0; s_live[warp] = 0; }
     if (slot < n_elig) {
         const QtcState st = state[slot];
-        uint32_t n;
-        if (seed_best) {   // seed round: position 0 and the eight isometries of the best-ranked lattice node
-            const unsigned long long key = seed_best[slot];
-            n = key != 0ull ? 16u : 8u;
-            if (lane < n) {
-                uint32_t pos = 0u;
-                if (lane >= 8) {
-                    const uint32_t k = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
-                    pos = (k / (uint32_t)seed_gx) * (uint32_t)seed_S * (uint32_t)PW + (k % (uint32_t)seed_gx) * (uint32_t)seed_S;
-                }
-                list[(size_t)slot * cap + lane] = pos * 8u + (uint32_t)(lane & 7);
-            }
-        } else {
-            n = cnt[slot];
-        }
+        const uint32_t n = cnt[slot];
         if (st.flags & 1) {
             // already handed to the exact search
         } else if (n > cap) {
             if (lane == 0) {
                 state[slot].flags = 1;
                 need_exact[slot] = 1;
-                cnt[slot] = 0;
-                tau[slot] = make_float2(__int_as_float(0x7f800000), __int_as_float(0x7f800000));
             }
         } else {
 #pragma unroll
@@ -1762,9 +1540,9 @@ qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ 
                 s_rs[warp] = st.rs; s_sqr[warp] = st.sqr;
                 for (int md = 0; md < 2; ++md) { s_rot[warp][md] = st.rot[md]; s_orient[warp][md] = st.orient[md]; }
                 s_n[warp] = n; s_live[warp] = 1;
-                s_E[warp] = st.E; s_s[warp] = st.s; s_o[warp] = st.o; s_tie[warp] = st.key;
-                for (int k = 0; k < 6; ++k) s_rec[warp][k] = st.rec[k];
-                s_key[warp] = s_prev[warp] = rescore_key(st.E);
+                s_E[warp] = __longlong_as_double(0x7ff0000000000000ll); s_s[warp] = 0.0; s_o[warp] = 0.0; s_tie[warp] = ~0ull;
+                for (int k = 0; k < 6; ++k) s_rec[warp][k] = 0;
+                s_key[warp] = s_prev[warp] = rescore_key(s_E[warp]);
             }
         }
     }
@@ -1798,7 +1576,7 @@ qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ 
                 int d_rot, d_orient;
                 if (dorient == rorient) { d_rot = (drot - rrot) & 3; d_orient = 0; }
                 else { d_rot = (drot - rrot + 2) & 3; d_orient = 1; }
-                if (d_orient * 4 + d_rot != t) continue;      // this pair's isometry is another column (its own entry, if it passed)
+                if (d_orient * 4 + d_rot != t) continue;      // the entry belongs to the other scale sign
                 // the three float32 sums in the reference's order: row-major over the range block (encoder.py:302-322)
                 const float mc = (float)((sd4[p] + (uint32_t)(N / 2)) / (uint32_t)N);
                 const __half* row = poolA + (size_t)p * N;
@@ -1836,36 +1614,14 @@ qt_tcrescore_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ 
         }
         __syncthreads();
     }
-    // ---- commit: the range's winner so far, next thresholds or the final record ----
+    // ---- commit ----
     if (lane == 0 && s_live[warp]) {
-        const float never = __int_as_float(0x7f800000);
-        QtcState& st = state[slot];
-        cnt[slot] = 0;
         if (s_tie[warp] == ~0ull) {      // nothing finite at all
-            st.flags = 1;
+            state[slot].flags = 1;
             need_exact[slot] = 1;
-            tau[slot] = make_float2(never, never);
         } else {
-            st.E = s_E[warp]; st.s = s_s[warp]; st.o = s_o[warp]; st.key = s_tie[warp];
-            for (int k = 0; k < 6; ++k) st.rec[k] = s_rec[warp][k];
-            if (emit) {
-                for (int k = 0; k < 6; ++k) out_rec[6 * (size_t)slot + k] = st.rec[k];
-                out_vals[3 * (size_t)slot] = st.s; out_vals[3 * (size_t)slot + 1] = st.o; out_vals[3 * (size_t)slot + 2] = st.E;
-            } else {
-                const double TA = st.TA0 - (double)N * st.E, TB = TA - (double)N * GUARD_ILL;
-                float2 t = make_float2(never, never);
-                // A bound that leaves most of the block's variance unexplained passes most candidates (with 5 contrast bits the
-                // quantised score of the best candidate sits well above its least-squares optimum): such ranges would only
-                // overflow their lists, so they go to the exact search at once.
-                if (st.E == st.E && st.E < 1e300 && TA > 1e-3 && (N == 16 || TB > 0.0) && TA >= QTC_MIN_EXPLAINED * st.TA0) {
-                    t.x = (float)sqrt(TA) * (1.0f - 1.0f / 1048576.0f);
-                    t.y = TB > 0.0 ? (float)sqrt(TB) * (1.0f - 1.0f / 1048576.0f) : 0.f;
-                } else {
-                    st.flags = 1;
-                    need_exact[slot] = 1;
-                }
-                tau[slot] = t;
-            }
+            for (int k = 0; k < 6; ++k) out_rec[6 * (size_t)slot + k] = s_rec[warp][k];
+            out_vals[3 * (size_t)slot] = s_s[warp]; out_vals[3 * (size_t)slot + 1] = s_o[warp]; out_vals[3 * (size_t)slot + 2] = s_E[warp];
         }
     }
 }
@@ -2108,7 +1864,7 @@ int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mod
     return bf_screen_run(h, d_img, H, W, mode, range_begin, n_ranges, d_idx, d_so, d_R, flags, nullptr, st);
 }
 
-// ---- host driver of the quadtree search on the screen -----------------------------------------------------------------
+// ---- host driver of the quadtree search on the tensor cores -----------------------------------------------------------------
 // One level of the quadtree partition: the n ranges of side 2^e in d_queue ([n][4] = si, sj, node, -) against all
 // (H - 2^(e+1) + 1) x (W - 2^(e+1) + 1) domain positions.  d_rcls [n][2][3] = (class, rotation, orientation) of every range for
 // positive / negative scales, d_dcls [NP][3] the same for every domain position (row-major grid).  Writes rec [n][6] / vals
@@ -2124,25 +1880,24 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     const int n_tiles = cdiv(NP, BM);
     const int np_pad = n_tiles * BM;
     const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
-    const int tau_pad = n_cols_pad / 8;
-    const int n_groups = tau_pad / 32;
+    const int slots_pad = n_cols_pad / 8;
+    const int n_groups = slots_pad / 32;
     const uint16_t* P = h->bf_boxsum.as<uint16_t>();
-    uint32_t cap = 8192;
+    // list entries per range: with the bounds seeded, the longest lists measured are around a hundred entries
+    uint32_t cap = 2048;
     while (cap > 256 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
     FIC_TRY(h->bf_pool.reserve((size_t)np_pad * N * 2 + 256));
-    FIC_TRY(h->bf_cand.reserve((size_t)NP * sizeof(float2) + 256));
     FIC_TRY(h->bf_stats.reserve((size_t)NP * (2 * sizeof(uint32_t) + 8 * sizeof(float) + 1 + sizeof(double)) + 1024));
     FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * N * 2 + 256));
-    FIC_TRY(h->bf_thr.reserve((size_t)tau_pad * (sizeof(float2) + 1) + (size_t)n_ranges * sizeof(QtcState) + 512));
+    FIC_TRY(h->bf_thr.reserve((size_t)n_ranges * sizeof(QtcState) + 512));
     FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
     FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
-    FIC_TRY(h->bf_best.reserve((size_t)tau_pad * (8 + sizeof(QtcRange)) + 512));
+    FIC_TRY(h->bf_best.reserve((size_t)slots_pad * (8 + sizeof(QtcRange)) + 512));
     if (!h->bf_ctrl.p) {
         FIC_TRY(h->bf_ctrl.reserve(256));
         FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
     }
     __half* poolA = h->bf_pool.as<__half>();
-    float2* hk = h->bf_cand.as<float2>();
     uint32_t* sd4 = h->bf_stats.as<uint32_t>();
     uint32_t* sq4 = sd4 + NP;
     float* sds8 = reinterpret_cast<float*>(sq4 + NP);
@@ -2150,18 +1905,16 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     uint8_t* dtyp = reinterpret_cast<uint8_t*>(den + NP);
     __half* rngB = h->bf_A.as<__half>();
     QtcState* state = h->bf_thr.as<QtcState>();
-    float2* tau = reinterpret_cast<float2*>(state + n_ranges);
-    uint8_t* rtyp = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tau + tau_pad) + 15) & ~(uintptr_t)15);   // read 16 bytes at a time
     uint32_t* cnt = h->bf_surv.as<uint32_t>();
     uint32_t* list = h->bf_list.as<uint32_t>();
     int* ctrl = h->bf_ctrl.as<int>();
     unsigned long long* bound = h->bf_best.as<unsigned long long>();
-    QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + tau_pad) + 15) & ~(uintptr_t)15);
+    QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + slots_pad) + 15) & ~(uintptr_t)15);
 
-    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, hk, sd4, sq4, sds8, dtyp, den);
+    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, sd4, sq4, sds8, dtyp, den);
     FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
-    qt_tcinit_kernel<S><<<cdiv((long long)tau_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, tau, cnt, bound, ctrl, tau_pad, rngB,
-                                                                            d_need_exact, rtyp, rngc);
+    qt_tcinit_kernel<S><<<cdiv((long long)slots_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, cnt, bound, ctrl, slots_pad, rngB,
+                                                                              d_need_exact, rngc);
     FIC_CHECK_LAUNCH(h, "qt_tcinit_kernel");
 
     const CUtensorMapSwizzle sw = N == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
@@ -2174,11 +1927,11 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
         h->qt_screen_attr_ready = true;
     }
     ScreenParams sp;
-    sp.hk = hk; sp.tau = tau; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
+    sp.hk = nullptr; sp.tau = nullptr; sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
     sp.seed_best = nullptr; sp.err_flag = ctrl + 2; sp.debug_mode = 0;
     sp.r_prev = 0;
     sp.window_tiles = (64 << 20) / (BM * N * 2);
-    sp.dump = nullptr; sp.dtyp = dtyp; sp.rtyp = rtyp; sp.np_pad = np_pad;
+    sp.dump = nullptr; sp.dtyp = dtyp;
     sp.grp_begin = 0; sp.grp_count = n_groups;
     sp.rngc = rngc; sp.bound = bound; sp.sd4 = sd4; sp.sq4 = sq4; sp.sds8 = sds8; sp.den = den;
     sp.max_scale = max_scale; sp.scale_bits = scale_bits; sp.offset_bits = offset_bits; sp.nmodes = nmodes;
@@ -2204,10 +1957,10 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
         fprintf(stderr, "[qtc S=%d] ranges %d, listed %llu, longest %u (cap %u)\n", S, n_ranges, sum, mx, cap);
     }
 #endif
-    // the lists hold every candidate that was at or below its range's best score when it was looked at: first minimum in scan order
-    qt_tcrescore_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, tau, 1, nmodes,
-                                                                                max_scale, scale_bits, offset_bits, d_rec, d_vals, d_need_exact, nullptr, 0, 0);
-    FIC_CHECK_LAUNCH(h, "qt_tcrescore_kernel");
+    // the lists hold every candidate that was at or below its range's best score when it was looked at
+    qt_tcpick_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, nmodes, max_scale,
+                                                                             scale_bits, offset_bits, d_rec, d_vals, d_need_exact);
+    FIC_CHECK_LAUNCH(h, "qt_tcpick_kernel");
     return FIC_OK;
 }
 

@@ -123,7 +123,7 @@ int fic_destroy(fic_handle* h)
                       &h->bf_partial, &h->bf_ranges, &h->bf_pool, &h->bf_cand, &h->bf_A, &h->bf_thr,
                       &h->bf_surv, &h->bf_ctrl, &h->bf_best, &h->bf_list, &h->dec_img, &h->dec_next, &h->dec_map,
                       &h->dec_sched, &h->dec_red, &h->t_int1, &h->t_int2, &h->t_cls, &h->t_lists, &h->t_work, &h->t_res,
-                      &h->t_aux, &h->t_hvpool, &h->t_part, &h->dec_keys, &h->dec_roots, &h->bf_done, &h->t_nodes, &h->t_count, &h->t_rcls, &h->t_need, &h->bf_dump};
+                      &h->t_aux, &h->t_hvpool, &h->t_part, &h->dec_keys, &h->dec_roots, &h->bf_done, &h->t_nodes, &h->t_count, &h->t_rcls, &h->t_need};
     for (DevBuf* b : bufs) b->release();
     h->pin_a.release();
     h->pin_b.release();
