@@ -339,14 +339,26 @@ __device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, in
 // block): bit for bit the inputs qt_search_kernel's pixel loop produces.  A candidate at or below the best score of its
 // range lowers the bound and -- outside the seed pass -- enters the range's list; the rescoring kernel picks the first
 // minimum in scan order among the listed.
-constexpr int QT_QCAP = (QUEUE_BYTES - RANGES_PER_WARP * 32) / 16;
-constexpr int QT_QROOM = 4 * 2 * 32;          // a 32-column chunk adds at most 4 ranges x 2 scale signs x 32 lanes
+constexpr int QT_COLS = 4;                    // columns per range: (scale sign) x (orientation of the domain's class)
+constexpr int QT_RPW = 128 / QT_COLS;         // ranges one epilogue warp looks at per tile (its 128 columns)
+constexpr int QT_RPG = BN / QT_COLS;          // ranges per column group
+constexpr int QT_QCAP = QUEUE_BYTES / 16;
+constexpr int QT_QROOM = 4 * 2 * 32;          // four ranges add at most 4 x 2 scale signs x 32 lanes entries
 static_assert(QT_QCAP >= QT_QROOM + 32, "queue of the quadtree pass too small");
 struct QtQueue {
-    QtcRange rng[RANGES_PER_WARP];   // the records of the warp's sixteen ranges, refreshed per column group
-    uint4 e[QT_QCAP];        // x = slot, y = position, z = the accumulator (float bits, an integer), w = isometry
+    uint4 e[QT_QCAP];        // x = slot, y = position, z = the accumulator (float bits, an integer), w = scale sign
 };
-static_assert(sizeof(QtcRange) == 32 && sizeof(QtQueue) <= QUEUE_BYTES, "QtQueue must fit a warp's queue slice");
+static_assert(sizeof(QtQueue) <= QUEUE_BYTES, "QtQueue must fit a warp's queue slice");
+
+// The isometry that pairs a domain type with a range type (quadtree/encoder.py:168-176) factors, for each orientation of
+// the domain's class, into a permutation of the domain block that depends on the domain type alone and one of the range
+// block that depends on the range type alone:   sum_k r[k] d[iso_t(k)] = sum_k r[beta(k)] d[alpha(k)] .
+// So the pool holds every block already permuted by its own alpha, the range operand holds two permuted copies per scale
+// sign (one per domain orientation), and the pair's exact dot product is ONE accumulator, picked by the domain's orientation
+// bit -- not one of eight picked by the full isometry.  The tables give alpha / beta as isometry numbers
+// (orientation * 4 + rotation, fic_iso_qt_enc); indices: domain type = rotation | orientation << 2, same for ranges.
+__device__ __constant__ unsigned char QT_ALPHA[8] = {0, 1, 2, 3, 6, 7, 4, 5};
+__device__ __constant__ unsigned char QT_BETA[2][8] = {{0, 1, 2, 3, 6, 5, 4, 7}, {0, 3, 2, 1, 6, 7, 4, 5}};
 
 template <int N>
 __device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams& p, int lane, uint32_t n)
@@ -354,8 +366,10 @@ __device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams
     __syncwarp();
     for (uint32_t k = lane; k < n; k += 32) {
         const uint4 en = q->e[k];
-        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)__uint_as_float(en.z), t = (int)en.w;
+        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)__uint_as_float(en.z);
         const QtcRange rc = p.rngc[slot];
+        if (!rc.ok) continue;     // (a range that is not searched here can still meet a candidate that is never dropped)
+        const int t = (int)(((en.w ? rc.tw1 : rc.tw0) >> (4u * (p.dtyp[cand] & 7u))) & 7u);   // the pair's isometry
         const unsigned sd = p.sd4[cand], sq = p.sq4[cand];
         const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
         const int mr = ((int)rc.rs - rc.rho) / N;
@@ -596,11 +610,13 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 my_tau[16 + lane] = tt.y;
             }
             __syncwarp();
-            const int slot0 = grp * 32 + part * 16;
-            if (MODE == 7) {   // the sixteen range records of this warp: 512 bytes, one uint4 per lane
-                QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
-                reinterpret_cast<uint4*>(qq->rng)[lane] = __ldg(reinterpret_cast<const uint4*>(p.rngc + slot0) + lane);
-                __syncwarp();
+            const int slot0 = MODE == 7 ? grp * QT_RPG + part * QT_RPW : grp * 32 + part * 16;
+            float my_rho = 0.f;
+            double my_slack = -1.0;
+            if (MODE == 7) {   // lane r keeps what the test needs of the r-th range of this warp's 128 columns
+                const QtcRange rc = p.rngc[grp * QT_RPG + part * QT_RPW + lane];
+                my_rho = (float)rc.rho;
+                my_slack = rc.ok ? rc.slack : -1.0;
             }
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
@@ -679,80 +695,75 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     continue;
                 }
                 if (MODE == 7) {
-                    // Exact pass of the quadtree search.  Every (candidate, range, scale sign) pair has ONE isometry, fixed by
-                    // the two classifications (quadtree/encoder.py:168-176); its accumulator X -- the exact integer sum of the
-                    // centred range times the centred block -- is picked out of the range's eight columns and tested here:
+                    // Exact pass of the quadtree search.  The accumulator of a (candidate, range, scale sign) pair -- the exact
+                    // integer sum X of the centred range times the centred block under the pair's isometry -- sits in the
+                    // column its scale sign and the orientation bit of the candidate's class select (see QT_ALPHA).  With it
                     // 4 * (N * ab - rs * ds) = N * X - rho * eps is an integer, and the pair is dropped when its square is
                     // below 16 * N * den * (slack - N * B), the scorer's lower bound against the best score B of the range
-                    // with both sides multiplied out (relative margin 1e-6 on the right).  Everything else is queued.
+                    // with both sides multiplied out and the right one shrunk by 1e-6.  The comparison runs in float32: X is
+                    // an integer below 2^24 and N a power of two, so fmaf(N, X, -rho * eps) is the numerator rounded once;
+                    // its square, the two converted factors of the right-hand side and their product add five more
+                    // roundings, 4e-7 relative in all.  Everything not dropped is queued and scored exactly.
                     const bool have = my_cand < p.NP;
                     unsigned dty = 0, sdc = 0;
-                    double den = 0.0;
-                    if (have) { dty = p.dtyp[my_cand]; sdc = p.sd4[my_cand]; den = p.den[my_cand]; }
-                    const int eps = (int)sdc - KT * (int)((sdc + (unsigned)(KT / 2)) / (unsigned)KT);
-                    const int dsh = 4 * (int)(dty & 7u);
-                    const bool den_ok = have && den > 0.0;
-                    const float feps = (float)eps;
+                    float denf = 0.f;            // 0: this candidate is never dropped (degenerate block)
+                    if (have) {
+                        dty = p.dtyp[my_cand]; sdc = p.sd4[my_cand];
+                        const double den = p.den[my_cand];
+                        denf = den > 0.0 ? (float)den : 0.f;
+                    }
+                    const float neps = -(float)((int)sdc - KT * (int)((sdc + (unsigned)(KT / 2)) / (unsigned)KT));
+                    const bool dori = (dty & 4u) != 0u;
                     const bool two = p.nmodes == 2;
-                    const unsigned long long Bl = __ldcg(&p.bound[slot0 + (lane & 15)]);
+                    // lane r: the right-hand side of range r without the candidate's factor; +inf = drop everything (range not
+                    // searched here), -1 = drop nothing (bound not yet below the range's variance)
+                    float my_rhs;
+                    {
+                        const double B = __longlong_as_double((long long)__ldcg(&p.bound[slot0 + lane]));
+                        const double rhs_g = DM(DS(my_slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
+                        my_rhs = my_slack < 0.0 ? __int_as_float(0x7f800000) : (rhs_g > 0.0 ? (float)rhs_g : -1.0f);
+                    }
                     QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
                     const unsigned lt = (1u << lane) - 1u;
                     uint32_t va[32];
-                    // The comparison itself runs in float32: X is an integer below 2^24 and N a power of two, so
-                    // fmaf(N, X, -rho * eps) is the numerator rounded once, its square and the converted right-hand side add
-                    // two more roundings -- 2.5e-7 relative in all, inside the 1e-6 the right-hand side was shrunk by.
-                    auto test4 = [&](const uint32_t (&v)[32], int c4) {
+                    auto test8 = [&](const uint32_t (&v)[32], int c8) {
 #pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            const int r = c4 * 4 + g;
-                            const QtcRange* rp = qq->rng + r;
-                            const int4 ri = *reinterpret_cast<const int4*>(rp);      // rho, ok, tw0, tw1
-                            const double slack = rp->slack;
-                            const double B = __longlong_as_double((long long)__shfl_sync(0xffffffffu, Bl, r));
-                            if (!ri.y) continue;
-                            const double rhs_g = DM(DS(slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
-                            // not droppable (bound still too high, degenerate block, padding row): right-hand side below any square
-                            const float rhs = den_ok && rhs_g > 0.0 ? (float)DM(rhs_g, den) : -1.0f;
-                            const float nre = -(float)ri.x * feps;
-                            auto pick = [&](uint32_t tw) {
-                                const int t = (int)((tw >> dsh) & 7u);
-                                const uint32_t x0 = (t & 1) ? v[g * 8 + 1] : v[g * 8 + 0], x1 = (t & 1) ? v[g * 8 + 3] : v[g * 8 + 2];
-                                const uint32_t x2 = (t & 1) ? v[g * 8 + 5] : v[g * 8 + 4], x3 = (t & 1) ? v[g * 8 + 7] : v[g * 8 + 6];
-                                const uint32_t y0 = (t & 2) ? x1 : x0, y1 = (t & 2) ? x3 : x2;
-                                return (t & 4) ? y1 : y0;
-                            };
-                            const uint32_t xa = pick((uint32_t)ri.z), xb = two ? pick((uint32_t)ri.w) : 0u;
+                        for (int g = 0; g < 8; ++g) {
+                            const int r = c8 * 8 + g;
+                            const float rhs = __fmul_rn(__shfl_sync(0xffffffffu, my_rhs, r), denf);
+                            const float nre = __fmul_rn(__shfl_sync(0xffffffffu, my_rho, r), neps);
+                            const uint32_t xa = dori ? v[g * 4 + 1] : v[g * 4 + 0], xb = dori ? v[g * 4 + 3] : v[g * 4 + 2];
                             const float na = fmaf((float)KT, __uint_as_float(xa), nre), nb = fmaf((float)KT, __uint_as_float(xb), nre);
                             const bool sa = have && !(__fmul_rn(na, na) < rhs), sb = two && have && !(__fmul_rn(nb, nb) < rhs);
                             if (__any_sync(0xffffffffu, sa || sb)) {
                                 const unsigned ma = __ballot_sync(0xffffffffu, sa);
-                                if (sa) qq->e[qn + __popc(ma & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xa, (uint32_t)ri.z >> dsh & 7u);
+                                if (sa) qq->e[qn + __popc(ma & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xa, 0u);
                                 qn += __popc(ma);
                                 const unsigned mb = __ballot_sync(0xffffffffu, sb);
-                                if (sb) qq->e[qn + __popc(mb & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xb, (uint32_t)ri.w >> dsh & 7u);
+                                if (sb) qq->e[qn + __popc(mb & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xb, 1u);
                                 qn += __popc(mb);
                             }
+                            if ((g & 3) == 3 && qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                         }
-                        if (qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                     };
-                    // one 32-column chunk in registers at a time: with two, the per-range constants of the test spill
+                    // one 32-column chunk in registers at a time keeps the epilogue free of spills
                     mbar_wait(my_tfull, aph, p.err_flag, 6);
                     tcgen05_fence_after();
                     tmem_ld32(taddr0, va);
                     tmem_ld_wait(va);
-                    test4(va, 0);
+                    test8(va, 0);
                     tmem_ld32(taddr0 + 32, va);
                     tmem_ld_wait(va);
-                    test4(va, 1);
+                    test8(va, 1);
                     tmem_ld32(taddr0 + 64, va);
                     tmem_ld_wait(va);
-                    test4(va, 2);
+                    test8(va, 2);
                     tmem_ld32(taddr0 + 96, va);
                     tmem_ld_wait(va);
                     tcgen05_fence_before();
                     __syncwarp();
                     if (lane0) mbar_arrive(my_tempty);
-                    test4(va, 3);
+                    test8(va, 3);
                     aph ^= 1;
                     if (qn >= 32u) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                     continue;
@@ -1362,13 +1373,24 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
             s2 += x * x;
         }
     const int m = (s + N / 2) / N;      // round(SD4 / n); eps = s - n m in [-n/2, n/2)
+    const unsigned dty = (unsigned)((dcls[3 * (size_t)p + 1] & 3) | ((dcls[3 * (size_t)p + 2] & 1) << 2));
+    // the pool row is the block permuted by the alpha of its own type (QT_ALPHA): element k = block[alpha(k)], read again
+    // from the box sums (L1) rather than through a runtime index into v[]
+    const int al = QT_ALPHA[dty];
     uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)p * N);
 #pragma unroll
     for (int q = 0; q < N / 8; ++q) {
-        __half2 h0 = __halves2half2(__int2half_rn(v[8 * q + 0] - m), __int2half_rn(v[8 * q + 1] - m));
-        __half2 h1 = __halves2half2(__int2half_rn(v[8 * q + 2] - m), __int2half_rn(v[8 * q + 3] - m));
-        __half2 h2 = __halves2half2(__int2half_rn(v[8 * q + 4] - m), __int2half_rn(v[8 * q + 5] - m));
-        __half2 h3 = __halves2half2(__int2half_rn(v[8 * q + 6] - m), __int2half_rn(v[8 * q + 7] - m));
+        int w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            int a, b;
+            fic_iso_qt_enc(al >> 2, al & 3, S, (8 * q + i) / S, (8 * q + i) % S, a, b);
+            w[i] = (int)P[(size_t)(di + 2 * a) * BW + dj + 2 * b] - m;
+        }
+        __half2 h0 = __halves2half2(__int2half_rn(w[0]), __int2half_rn(w[1]));
+        __half2 h1 = __halves2half2(__int2half_rn(w[2]), __int2half_rn(w[3]));
+        __half2 h2 = __halves2half2(__int2half_rn(w[4]), __int2half_rn(w[5]));
+        __half2 h3 = __halves2half2(__int2half_rn(w[6]), __int2half_rn(w[7]));
         uint4 o;
         o.x = *reinterpret_cast<uint32_t*>(&h0);
         o.y = *reinterpret_cast<uint32_t*>(&h1);
@@ -1378,7 +1400,7 @@ __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, c
     }
     sd4[p] = (uint32_t)s;
     sq4[p] = (uint32_t)s2;
-    dtyp[p] = (uint8_t)((dcls[3 * (size_t)p + 1] & 3) | ((dcls[3 * (size_t)p + 2] & 1) << 2));
+    dtyp[p] = (uint8_t)dty;
     if (N == 64) {
         // the one order-dependent input of the scorer for 8x8 blocks: the float32 sequential sum of d^2 in the order the
         // reference walks the oriented block (row-major over the range pixels, quadtree/encoder.py:302-322), per isometry
@@ -1427,7 +1449,7 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
     if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
     if (lane == 0) bound[slot] = 0x7ff0000000000000ull;      // best score found so far: +inf
     if (slot >= n_ranges) {   // padding columns of the last group: zero operand, record that says "skip"
-        for (int e = lane; e < 8 * N; e += 32) rngB[(size_t)slot * 8 * N + e] = __float2half_rn(0.f);
+        for (int e = lane; e < QT_COLS * N; e += 32) rngB[(size_t)slot * QT_COLS * N + e] = __float2half_rn(0.f);
         if (lane == 0) {
             QtcRange rc;
             rc.rho = 0; rc.ok = 0; rc.tw0 = rc.tw1 = 0u; rc.slack = 0.0; rc.rs = rc.sqr = 0.f;
@@ -1453,17 +1475,22 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
         q32 += __shfl_xor_sync(0xffffffffu, q32, off);
     }
     const int m = ((int)sm + N / 2) / N;
+    // column c = scale sign * 2 + orientation of the domain's class: element k = range[beta(k)] (QT_BETA), centred
 #pragma unroll
-    for (int t = 0; t < 8; ++t)
+    for (int c = 0; c < QT_COLS; ++c) {
+        const int md = c >> 1;
+        const int rty = (rcls[6 * (size_t)slot + 3 * md + 1] & 3) | ((rcls[6 * (size_t)slot + 3 * md + 2] & 1) << 2);
+        const int be = QT_BETA[c & 1][rty];
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             const int k = lane + 32 * half;
-            if (k < N) {   // range pixel (i, j) meets the pooled sample (a, b) = iso_t(i, j) (fic_iso_qt_enc)
+            if (k < N) {
                 int a, b;
-                fic_iso_qt_enc(t >> 2, t & 3, S, k / S, k % S, a, b);
-                rngB[((size_t)slot * 8 + t) * N + a * S + b] = __int2half_rn(px[half] - m);
+                fic_iso_qt_enc(be >> 2, be & 3, S, k / S, k % S, a, b);
+                rngB[((size_t)slot * QT_COLS + c) * N + k] = __int2half_rn((int)img[(size_t)(si + a) * W + sj + b] - m);
             }
         }
+    }
     if (lane == 0) {
         const long long sl = sm, ql = q32;
         QtcState st;
@@ -1499,7 +1526,7 @@ __global__ void qt_tcinit_kernel(const uint8_t* __restrict__ img, int W, const i
 #define QTC_WARPS 32
 template <int S>
 __global__ void __launch_bounds__(QTC_WARPS * 32, 1)
-qt_tcpick_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poolA, const uint32_t* __restrict__ sd4,
+qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P /*2x2 box sums, (H-1) x (W-1)*/,
                  const int32_t* __restrict__ dcls /*[NP][3] = class, rot, orient*/, int H, int W, QtcState* __restrict__ state,
                  const int* __restrict__ ctrl, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
                  int nmodes, double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ out_rec,
@@ -1578,14 +1605,13 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const __half* __restrict__ poo
                 else { d_rot = (drot - rrot + 2) & 3; d_orient = 1; }
                 if (d_orient * 4 + d_rot != t) continue;      // the entry belongs to the other scale sign
                 // the three float32 sums in the reference's order: row-major over the range block (encoder.py:302-322)
-                const float mc = (float)((sd4[p] + (uint32_t)(N / 2)) / (uint32_t)N);
-                const __half* row = poolA + (size_t)p * N;
+                const uint16_t* blk = P + (size_t)di * (W - 1) + dj;
                 float ds = 0.f, sds = 0.f, ab = 0.f;
 #pragma unroll 4
                 for (int k = 0; k < N; ++k) {
                     int a, b;
                     fic_iso_qt_enc(d_orient, d_rot, S, k / S, k % S, a, b);
-                    const float d = __fmul_rn(__half2float(row[a * S + b]) + mc, 0.25f);
+                    const float d = __fmul_rn((float)blk[(size_t)(2 * a) * (W - 1) + 2 * b], 0.25f);
                     ds = __fadd_rn(ds, d);
                     sds = __fadd_rn(sds, __fmul_rn(d, d));
                     ab = __fadd_rn(ab, __fmul_rn(d, rv[r][k]));
@@ -1879,9 +1905,9 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     const int NP = PW * PH;
     const int n_tiles = cdiv(NP, BM);
     const int np_pad = n_tiles * BM;
-    const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
-    const int slots_pad = n_cols_pad / 8;
-    const int n_groups = slots_pad / 32;
+    const int n_cols_pad = cdiv((long long)n_ranges * QT_COLS, BN) * BN;
+    const int slots_pad = n_cols_pad / QT_COLS;
+    const int n_groups = slots_pad / QT_RPG;
     const uint16_t* P = h->bf_boxsum.as<uint16_t>();
     // list entries per range: with the bounds seeded, the longest lists measured are around a hundred entries
     uint32_t cap = 2048;
@@ -1958,7 +1984,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     }
 #endif
     // the lists hold every candidate that was at or below its range's best score when it was looked at
-    qt_tcpick_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, poolA, sd4, d_dcls, H, W, state, ctrl, cnt, list, cap, nmodes, max_scale,
+    qt_tcpick_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, P, d_dcls, H, W, state, ctrl, cnt, list, cap, nmodes, max_scale,
                                                                              scale_bits, offset_bits, d_rec, d_vals, d_need_exact);
     FIC_CHECK_LAUNCH(h, "qt_tcpick_kernel");
     return FIC_OK;
