@@ -342,11 +342,11 @@ __device__ __noinline__ void queue_flush(WarpQueue* q, const ScreenParams& p, in
 constexpr int QT_COLS = 4;                    // columns per range: (scale sign) x (orientation of the domain's class)
 constexpr int QT_RPW = 128 / QT_COLS;         // ranges one epilogue warp looks at per tile (its 128 columns)
 constexpr int QT_RPG = BN / QT_COLS;          // ranges per column group
-constexpr int QT_QCAP = QUEUE_BYTES / 16;
-constexpr int QT_QROOM = 4 * 2 * 32;          // four ranges add at most 4 x 2 scale signs x 32 lanes entries
+constexpr int QT_QCAP = QUEUE_BYTES / 8;
+constexpr int QT_QROOM = 8 * 2 * 32;          // a 32-column chunk adds at most 8 ranges x 2 scale signs x 32 lanes entries
 static_assert(QT_QCAP >= QT_QROOM + 32, "queue of the quadtree pass too small");
 struct QtQueue {
-    uint4 e[QT_QCAP];        // x = slot, y = position, z = the accumulator (float bits, an integer), w = scale sign
+    uint2 e[QT_QCAP];        // x = the accumulator (float bits, an integer), y = position << 6 | range of the warp's 32 << 1 | scale sign
 };
 static_assert(sizeof(QtQueue) <= QUEUE_BYTES, "QtQueue must fit a warp's queue slice");
 
@@ -361,15 +361,15 @@ __device__ __constant__ unsigned char QT_ALPHA[8] = {0, 1, 2, 3, 6, 7, 4, 5};
 __device__ __constant__ unsigned char QT_BETA[2][8] = {{0, 1, 2, 3, 6, 5, 4, 7}, {0, 3, 2, 1, 6, 7, 4, 5}};
 
 template <int N>
-__device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams& p, int lane, uint32_t n)
+__device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams& p, int slot0, int lane, uint32_t n)
 {
     __syncwarp();
     for (uint32_t k = lane; k < n; k += 32) {
-        const uint4 en = q->e[k];
-        const int slot = (int)en.x, cand = (int)en.y, Xi = (int)__uint_as_float(en.z);
+        const uint2 en = q->e[k];
+        const int slot = slot0 + (int)((en.y >> 1) & 31u), cand = (int)(en.y >> 6), Xi = (int)__uint_as_float(en.x);
         const QtcRange rc = p.rngc[slot];
         if (!rc.ok) continue;     // (a range that is not searched here can still meet a candidate that is never dropped)
-        const int t = (int)(((en.w ? rc.tw1 : rc.tw0) >> (4u * (p.dtyp[cand] & 7u))) & 7u);   // the pair's isometry
+        const int t = (int)((((en.y & 1u) ? rc.tw1 : rc.tw0) >> (4u * (p.dtyp[cand] & 7u))) & 7u);   // the pair's isometry
         const unsigned sd = p.sd4[cand], sq = p.sq4[cand];
         const int mc = (int)((sd + (unsigned)(N / 2)) / (unsigned)N), eps = (int)sd - N * mc;
         const int mr = ((int)rc.rs - rc.rho) / N;
@@ -597,11 +597,13 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         float* my_tau = reinterpret_cast<float*>(gbase + OFF_TAU) + ew * 32;   // [0,16) = tau_A, [16,32) = tau_B
         WarpQueue* queue = reinterpret_cast<WarpQueue*>(gbase + OFF_QUEUE) + ew;
         uint32_t qn = 0;   // queue fill, warp-uniform
+        int qt_slot0 = 0;  // MODE 7: first range of the unit the queued entries belong to
         Span span(p, n_groups);
         int grp, j0, j1;
         while (span.next(grp, j0, j1)) {
             grp += grp_off;
             if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
+            if (MODE == 7 && qn) { qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, qt_slot0, lane, qn); qn = 0; }   // (entries name ranges relative to their unit)
             // this warp's (tau_A, tau_B) pairs live in a private slice of shared memory; broadcast reads, no bank conflicts
             __syncwarp();
             if (MODE != 7 && lane < 16) {
@@ -611,6 +613,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
             __syncwarp();
             const int slot0 = MODE == 7 ? grp * QT_RPG + part * QT_RPW : grp * 32 + part * 16;
+            qt_slot0 = slot0;
             float my_rho = 0.f;
             double my_slack = -1.0;
             if (MODE == 7) {   // lane r keeps what the test needs of the r-th range of this warp's 128 columns
@@ -725,8 +728,21 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     }
                     QtQueue* qq = reinterpret_cast<QtQueue*>(queue);
                     const unsigned lt = (1u << lane) - 1u;
-                    uint32_t va[32];
-                    auto test8 = [&](const uint32_t (&v)[32], int c8) {
+                    const uint32_t ent_cand = (uint32_t)my_cand << 6;
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+                    // One 32-column chunk (eight ranges) in registers at a time, in a rolled loop: the queue is emptied
+                    // between chunks, where no accumulator is live across the call, and from one call site.
+#pragma unroll 1
+                    for (int c8 = 0; c8 < 4; ++c8) {
+                        uint32_t v[32];
+                        tmem_ld32(taddr0 + 32 * c8, v);
+                        tmem_ld_wait(v);
+                        if (c8 == 3) {     // the whole slice has been read: hand the accumulator back
+                            tcgen05_fence_before();
+                            __syncwarp();
+                            if (lane0) mbar_arrive(my_tempty);
+                        }
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
                             const int r = c8 * 8 + g;
@@ -737,35 +753,16 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                             const bool sa = have && !(__fmul_rn(na, na) < rhs), sb = two && have && !(__fmul_rn(nb, nb) < rhs);
                             if (__any_sync(0xffffffffu, sa || sb)) {
                                 const unsigned ma = __ballot_sync(0xffffffffu, sa);
-                                if (sa) qq->e[qn + __popc(ma & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xa, 0u);
+                                if (sa) qq->e[qn + __popc(ma & lt)] = make_uint2(xa, ent_cand | (uint32_t)(r << 1));
                                 qn += __popc(ma);
                                 const unsigned mb = __ballot_sync(0xffffffffu, sb);
-                                if (sb) qq->e[qn + __popc(mb & lt)] = make_uint4((uint32_t)(slot0 + r), (uint32_t)my_cand, xb, 1u);
+                                if (sb) qq->e[qn + __popc(mb & lt)] = make_uint2(xb, ent_cand | (uint32_t)(r << 1) | 1u);
                                 qn += __popc(mb);
                             }
-                            if ((g & 3) == 3 && qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                         }
-                    };
-                    // one 32-column chunk in registers at a time keeps the epilogue free of spills
-                    mbar_wait(my_tfull, aph, p.err_flag, 6);
-                    tcgen05_fence_after();
-                    tmem_ld32(taddr0, va);
-                    tmem_ld_wait(va);
-                    test8(va, 0);
-                    tmem_ld32(taddr0 + 32, va);
-                    tmem_ld_wait(va);
-                    test8(va, 1);
-                    tmem_ld32(taddr0 + 64, va);
-                    tmem_ld_wait(va);
-                    test8(va, 2);
-                    tmem_ld32(taddr0 + 96, va);
-                    tmem_ld_wait(va);
-                    tcgen05_fence_before();
-                    __syncwarp();
-                    if (lane0) mbar_arrive(my_tempty);
-                    test8(va, 3);
+                        if (qn > (uint32_t)(QT_QCAP - QT_QROOM)) { qt_queue_flush<KT>(qq, p, slot0, lane, qn); qn = 0; }
+                    }
                     aph ^= 1;
-                    if (qn >= 32u) { qt_queue_flush<KT>(qq, p, lane, qn); qn = 0; }
                     continue;
                 }
                 const float qx = fabsf(hq);
@@ -838,7 +835,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
         }
         if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
-        if (MODE == 7 && qn) qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, lane, qn);
+        if (MODE == 7 && qn) qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, qt_slot0, lane, qn);
         }
     tcgen05_fence_before();
     __syncthreads();
@@ -1995,7 +1992,8 @@ bool qt_tc_applicable(int H, int W, int e, double max_scale)
     if (e != 2 && e != 3) return false;
     const int S = 1 << e;
     if (H < 2 * S || W < 2 * S || !(max_scale > 0.0 && max_scale <= 1.0)) return false;
-    return (long long)(H - 2 * S + 1) * (W - 2 * S + 1) >= 2048;      // below that the fixed costs of the pipeline dominate
+    const long long np = (long long)(H - 2 * S + 1) * (W - 2 * S + 1);
+    return np >= 2048 && np < (1ll << 26);      // below that the fixed costs of the pipeline dominate; queue entries hold 26 bits of position
 }
 
 int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const int32_t* d_queue, int n_ranges,
