@@ -345,3 +345,28 @@ def test_quadtree_dense_full_class_search_on_the_tensor_cores(fic, orc, params, 
     assert got[2] == want[2]
     assert np.array_equal(got[0], want[0])
     assert np.array_equal(got[1], want[1])
+
+
+@pytest.mark.parametrize("case", ["synthetic272_seed61_positive", "lena512_stress_row"])
+def test_quadtree_dense_full_class_golden(fic, case):
+    """The stress row at sizes where the seed pass of the tensor-core search (every 61st tile) is active: SHA-256 of the
+    node table, values and root count against the oracle's, computed once on the CPU (tests/golden/make_golden_qt_dense.py)."""
+    import hashlib
+    import json
+    import os
+    golden = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "qt_dense_full_golden.json")))
+    if case not in golden:
+        pytest.skip("no golden for this case (the oracle needs tens of minutes for it)")
+    g = golden[case]
+    if case.startswith("lena512"):
+        img = np.load(os.path.join(os.path.dirname(__file__), "golden", "images.npz"))["lena512"]
+    else:
+        img = synthetic_image(61, 272, 272)
+    assert list(img.shape) == g["shape"]
+    nodes, vals, n_roots = fic.qt_encode(img, *g["params"])
+    h = hashlib.sha256()
+    h.update(np.ascontiguousarray(nodes, dtype=np.int32).tobytes())
+    h.update(np.ascontiguousarray(vals, dtype=np.float64).tobytes())
+    h.update(int(n_roots).to_bytes(4, "little"))
+    assert len(nodes) == g["nodes"]
+    assert h.hexdigest() == g["sha256"]
