@@ -568,6 +568,244 @@ hv_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
     te_block_reduce(best, rec + 6 * slot, vals + 3 * slot, seqs ? seqs + slot : nullptr);
 }
 
+// ---- HV search, rectangles of equal shape together --------------------------------------------------------------------
+// The search of a rectangle costs 4 * positions * pixels ~ 4 * H * W multiply-adds whatever its shape, and the rectangles
+// of a level that share a shape (lena 512x512: 78 % of them sit in groups of eight or more, profiles/hv_shape_stats.py)
+// walk the SAME candidate blocks.  A CTA takes four consecutive entries of the level's search list, which
+// hv_group_kernel has sorted by shape, and searches each run of equal shape in one sweep: a thread loads the four pooled
+// samples of a pixel once, keeps sum(d) and sum(d^2) once per isometry, and one sum(d*r) chain per rectangle and isometry
+// (the reference's order and rounding: row-major, float32, multiply then add).  Per multiply-add of sum(d*r) that is 2.75
+// arithmetic instructions and 0.3 loads instead of 5 and 1.  The per-thread winners live in shared memory (they change
+// rarely); everything after the sums is hv_search_kernel's.
+#define HV_GROUP 4
+#define HV_GROUP_MAX_PX 1024                 /* range pixels of the four rectangles in shared memory: 16 KB */
+struct HvGroupBest {                         // per thread and rectangle of the group, structure of arrays in shared memory
+    double R[HV_GROUP][TE_THREADS], s[HV_GROUP][TE_THREADS], o[HV_GROUP][TE_THREADS];
+    unsigned long long seq[HV_GROUP][TE_THREADS];
+    int qs[HV_GROUP][TE_THREADS], qo[HV_GROUP][TE_THREADS];
+};
+
+template <int G>
+__device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
+                                              const int32_t* __restrict__ rects, const int* rq, int x0, double max_scale,
+                                              int scale_bits, int offset_bits, int32_t* __restrict__ rec, double* __restrict__ vals,
+                                              unsigned long long* __restrict__ seqs, unsigned long long* __restrict__ gbound,
+                                              float* s_range, HvGroupBest* sb)
+{
+    __shared__ float s_rs[HV_GROUP], s_sqr[HV_GROUP];
+    __shared__ double s_slack[HV_GROUP];
+    __shared__ unsigned long long s_bound[HV_GROUP];
+    const int tid = threadIdx.x;
+    const int w = rects[4 * (size_t)rq[0] + 2], hgt = rects[4 * (size_t)rq[0] + 3];
+    const int nn = w * hgt;
+    for (int t = tid; t < nn; t += TE_THREADS) {
+        const int i = t / w, j = t - i * w;
+#pragma unroll
+        for (int k = 0; k < G; ++k)
+            s_range[t * G + k] = (float)img[(size_t)(rects[4 * (size_t)rq[k]] + i) * W + rects[4 * (size_t)rq[k] + 1] + j];
+    }
+    // The best score any CTA has found so far for the rectangle (all-ones = none yet: a NaN, which drops nothing).  The
+    // chunks of a rectangle are blockIdx.y, the slow grid dimension, so all but the first few start with a bound that
+    // means something instead of scoring every candidate until they have found one of their own.
+    if (tid < HV_GROUP) s_bound[tid] = tid < G ? __ldcg(&gbound[x0 + tid]) : ~0ull;
+#pragma unroll
+    for (int k = 0; k < G; ++k) { sb->R[k][tid] = __longlong_as_double(0x7ff0000000000000ll); sb->seq[k][tid] = ~0ull; }
+    __syncthreads();
+    if (tid < G) {
+        float rs = 0.f, sq = 0.f;
+        for (int t = 0; t < nn; ++t) {
+            const float v = s_range[t * G + tid];
+            rs = __fadd_rn(rs, v);
+            sq = __fadd_rn(sq, __fmul_rn(v, v));
+        }
+        s_rs[tid] = rs;
+        s_sqr[tid] = sq;
+        s_slack[tid] = DS((double)sq, DD(DM((double)rs, (double)rs), (double)nn));   // sqr - rs^2 / n
+    }
+    __syncthreads();
+    const double dn = (double)nn;
+    const int ndi = H - 2 * hgt > 0 ? (H - 2 * hgt + hgt - 1) / hgt : 0;  // range(0, H-2h, h): exclusive
+    const int ndj = W - 2 * w > 0 ? (W - 2 * w + w - 1) / w : 0;
+    const long long npos = (long long)ndi * ndj;
+    const long long per = (npos + gridDim.y - 1) / gridDim.y;
+    const long long p0 = per * blockIdx.y, p1 = p0 + per < npos ? p0 + per : npos;
+    const int PW = W - 1;
+    for (long long pos = p0 + tid; pos < p1; pos += TE_THREADS) {
+        const int di = (int)(pos / ndj) * hgt, dj = (int)(pos % ndj) * w;
+        const float* top = Dp + (size_t)di * PW + dj;                       // row 0 of the pooled block
+        const float* bot = top + (size_t)(2 * (hgt - 1)) * PW;              // its last row
+        const int last = 2 * (w - 1);
+        float ds[4] = {0.f, 0.f, 0.f, 0.f}, sq[4] = {0.f, 0.f, 0.f, 0.f};    // per isometry (see hv_search_kernel)
+        float ab[G][4];
+#pragma unroll
+        for (int k = 0; k < G; ++k)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) ab[k][e] = 0.f;
+        const float* rp = s_range;
+        for (int i = 0; i < hgt; ++i) {
+            const float* rd = top + (size_t)(2 * i) * PW;
+            const float* ru = bot - (size_t)(2 * i) * PW;
+            for (int j = 0; j < w; ++j, rp += G) {
+                const float d[4] = {rd[2 * j], ru[last - 2 * j], ru[2 * j], rd[last - 2 * j]};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    ds[e] = __fadd_rn(ds[e], d[e]);
+                    sq[e] = __fadd_rn(sq[e], __fmul_rn(d[e], d[e]));
+                }
+#pragma unroll
+                for (int k = 0; k < G; ++k) {
+                    const float r = rp[k];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) ab[k][e] = __fadd_rn(ab[k][e], __fmul_rn(d[e], r));
+                }
+            }
+        }
+        // Lower bound of the score first (see hv_search_kernel), for all G x 4 candidates of this position; the few that pass
+        // go through ONE copy of the quantising scorer (sixteen inlined copies would not fit the instruction cache).
+        double nden[4], dsd[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            dsd[e] = (double)ds[e];
+            const double den = DS(DM(dn, (double)sq[e]), DM(dsd[e], dsd[e]));
+            nden[e] = den > 0.0 ? DM(DM(dn, den), 0.999999999) : -1.0;     // -1: never dropped
+        }
+        unsigned pass = 0u;
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+            const double rsd = (double)s_rs[k];
+            const double bound = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound[k]);
+            const double room = DS(s_slack[k], DM(dn, bound));   // sqr - rs^2/n - n B
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const double num = DS(DM(dn, (double)ab[k][e]), DM(rsd, dsd[e]));
+                const bool drop = room > 0.0 && nden[e] > 0.0 && DM(num, num) < DM(room, nden[e]);
+                if (!drop) pass |= 1u << (k * 4 + e);
+            }
+        }
+        while (pass) {
+            const int idx = __ffs((int)pass) - 1;
+            pass &= pass - 1u;
+            const int k = idx >> 2, iso = idx & 3;
+            const float dsv = iso == 0 ? ds[0] : iso == 1 ? ds[1] : iso == 2 ? ds[2] : ds[3];
+            const float sqv = iso == 0 ? sq[0] : iso == 1 ? sq[1] : iso == 2 ? sq[2] : sq[3];
+            float abv = ab[0][0];
+#pragma unroll
+            for (int kk = 0; kk < G; ++kk)
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (idx == kk * 4 + e) abv = ab[kk][e];
+            const unsigned long long c = (unsigned long long)pos * 4ull + (unsigned)iso;
+            const QScore sc = fic_q_score(nn, s_rs[k], s_sqr[k], dsv, sqv, abv, max_scale, scale_bits, offset_bits);
+            if (fic_better(sc.R, c, sb->R[k][tid], sb->seq[k][tid])) {
+                sb->R[k][tid] = sc.R; sb->seq[k][tid] = c; sb->s[k][tid] = sc.s; sb->o[k][tid] = sc.o;
+                sb->qs[k][tid] = sc.qs; sb->qo[k][tid] = sc.qo;
+                const unsigned long long bits = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
+                if (bits < atomicMin(&s_bound[k], bits)) atomicMin(&gbound[x0 + k], bits);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+        TeBest b;
+        b.R = sb->R[k][tid]; b.seq = sb->seq[k][tid];
+        b.s = b.o = 0.0; b.di = b.dj = b.orient = b.rot = b.qs = b.qo = 0;
+        if (b.seq != ~0ull) {
+            b.s = sb->s[k][tid]; b.o = sb->o[k][tid]; b.qs = sb->qs[k][tid]; b.qo = sb->qo[k][tid];
+            const long long pos = (long long)(b.seq >> 2);
+            const int iso = (int)(b.seq & 3ull);
+            b.di = (int)(pos / ndj) * hgt; b.dj = (int)(pos % ndj) * w; b.orient = iso >> 1; b.rot = (iso & 1) * 2;
+        }
+        const size_t slot = (size_t)(x0 + k) * gridDim.y + blockIdx.y;
+        __syncthreads();      // (te_block_reduce's shared scratch is reused from call to call)
+        te_block_reduce(b, rec + 6 * slot, vals + 3 * slot, seqs + slot);
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(TE_THREADS, HV_MINB)
+hv_search_grouped_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
+                         const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
+                         int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs,
+                         const int32_t* __restrict__ slist /*sorted by shape*/, int count, unsigned long long* __restrict__ gbound)
+{
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    float* s_range = reinterpret_cast<float*>(s_dyn);
+    HvGroupBest* sb = reinterpret_cast<HvGroupBest*>(s_dyn + HV_GROUP * HV_GROUP_MAX_PX * sizeof(float));
+    const int x0 = blockIdx.x * HV_GROUP;
+    const int m = count - x0 < HV_GROUP ? count - x0 : HV_GROUP;
+    int rq[HV_GROUP];
+#pragma unroll
+    for (int k = 0; k < HV_GROUP; ++k) rq[k] = slist[x0 + (k < m ? k : 0)];
+    int a = 0;
+    while (a < m) {
+        int b = a + 1;
+        while (b < m && rects[4 * (size_t)rq[b] + 2] == rects[4 * (size_t)rq[a] + 2] && rects[4 * (size_t)rq[b] + 3] == rects[4 * (size_t)rq[a] + 3]) ++b;
+        int run[HV_GROUP];
+#pragma unroll
+        for (int k = 0; k < HV_GROUP; ++k) run[k] = rq[a + k < m ? a + k : a];
+        switch (b - a) {
+        case 1: hv_group_body<1>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
+        case 2: hv_group_body<2>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
+        case 3: hv_group_body<3>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
+        default: hv_group_body<4>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
+        }
+        a = b;
+    }
+}
+
+// Sorts the search list of a level by shape (counting sort, one CTA): slist_sorted[k] = k-th rectangle, sidx[rect] = k.
+// The order inside a shape is not specified (atomic counters); every rectangle's result is independent of it.
+#define HV_SORT_BINS 4096
+__global__ void __launch_bounds__(1024)
+hv_group_kernel(const int32_t* __restrict__ rects, const int32_t* __restrict__ slist, const int* __restrict__ count_ptr,
+                int32_t* __restrict__ slist_sorted, int32_t* __restrict__ sidx, unsigned long long* __restrict__ gbound)
+{
+    __shared__ int hist[HV_SORT_BINS];
+    __shared__ int warp_sum[32];
+    const int tid = threadIdx.x, n = *count_ptr;
+    for (int b = tid; b < HV_SORT_BINS; b += 1024) hist[b] = 0;
+    __syncthreads();
+    auto key = [&](int r) {
+        const int w = rects[4 * (size_t)r + 2], hgt = rects[4 * (size_t)r + 3];
+        return (w < 63 ? w : 63) * 64 + (hgt < 63 ? hgt : 63);
+    };
+    for (int e = tid; e < n; e += 1024) atomicAdd(&hist[key(slist[e])], 1);
+    __syncthreads();
+    // exclusive scan of the 4096 counters: four per thread, warp scan, scan of the warp totals
+    int v[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[k] = hist[tid * 4 + k]; sum += v[k]; }
+    int incl = sum;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, off);
+        if ((tid & 31) >= off) incl += o;
+    }
+    if ((tid & 31) == 31) warp_sum[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        int ws = warp_sum[tid], wi = ws;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, wi, off);
+            if (tid >= off) wi += o;
+        }
+        warp_sum[tid] = wi - ws;
+    }
+    __syncthreads();
+    int base = warp_sum[tid >> 5] + incl - sum;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { hist[tid * 4 + k] = base; base += v[k]; }
+    __syncthreads();
+    for (int e = tid; e < n; e += 1024) {
+        const int r = slist[e];
+        const int at = atomicAdd(&hist[key(r)], 1);
+        slist_sorted[at] = r;
+        sidx[r] = at;
+        gbound[e] = ~0ull;     // no score yet for the e-th rectangle of the search list
+    }
+}
+
 // merge the chunk winners of every rectangle: first strict minimum in scan order
 __global__ void hv_pick_kernel(const int32_t* __restrict__ prec, const double* __restrict__ pvals,
                                const unsigned long long* __restrict__ pseq, int count, int S, int32_t* __restrict__ rec,
@@ -1209,12 +1447,15 @@ __global__ void hv_decide_kernel(const long long* __restrict__ I1, int W1, const
 
 // the search of one level with the chunk winners left in the handle's partial buffers (hv_decide_kernel merges them)
 static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_rects, const int32_t* d_slist,
-                           int count, int max_px, int scale_bits, int offset_bits, double max_scale, int* S_out,
+                           const int32_t* d_slist_sorted /* list sorted by shape (hv_group_kernel) or nullptr */,
+                           unsigned long long* d_gbound /* with the sorted list: one bound per entry, all-ones */, int count, int max_px, int scale_bits, int offset_bits, double max_scale, int* S_out,
                            const int32_t** prec_out, const double** pvals_out, const unsigned long long** pseq_out, cudaStream_t st)
 {
     const float* Dp = h->t_hvpool.as<float>();
     const int smem_px = max_px <= 10240 ? max_px : 0;
-    int S = (HV_SMULT * h->num_sms + count - 1) / count;      // see HV_SMULT
+    const bool grouped = d_slist_sorted != nullptr;
+    const int n_cta = grouped ? (count + HV_GROUP - 1) / HV_GROUP : count;
+    int S = (HV_SMULT * h->num_sms + n_cta - 1) / n_cta;      // see HV_SMULT
     if (S > HV_SCAP) S = HV_SCAP;
     if (S < 1) S = 1;
     const size_t np_ = (size_t)count * S;
@@ -1222,6 +1463,18 @@ static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, co
     double* pvals = h->t_part.as<double>();
     unsigned long long* pseq = reinterpret_cast<unsigned long long*>(pvals + 3 * np_);
     int32_t* prec = reinterpret_cast<int32_t*>(pseq + np_);
+    if (grouped) {
+        const size_t smem = HV_GROUP * HV_GROUP_MAX_PX * sizeof(float) + sizeof(HvGroupBest);
+        if (!h->hv_group_attr_ready) {
+            FIC_CUDA(cudaFuncSetAttribute(hv_search_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            h->hv_group_attr_ready = true;
+        }
+        hv_search_grouped_kernel<<<dim3(n_cta, S), TE_THREADS, smem, st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits, offset_bits,
+                                                                          prec, pvals, pseq, d_slist_sorted, count, d_gbound);
+        FIC_CHECK_LAUNCH(h, "hv_search_grouped_kernel");
+        *S_out = S; *prec_out = prec; *pvals_out = pvals; *pseq_out = pseq;
+        return FIC_OK;
+    }
     hv_search_kernel<<<dim3(count, S), TE_THREADS, smem_px * sizeof(float), st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits,
                                                                                  offset_bits, prec, pvals, pseq, smem_px, d_slist);
     FIC_CHECK_LAUNCH(h, "hv_search_kernel");
@@ -1245,14 +1498,15 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
         const size_t level_cap = std::min((size_t)H * W + 2, node_cap);
         FIC_REQUIRE(node_cap < ((size_t)1 << 30), "fic_hv_encode: image too large");
         FIC_TRY(h->t_nodes.reserve(node_cap * sizeof(HvNodeDev) + 64));
-        FIC_TRY(h->t_work.reserve(2 * level_cap * 8 * sizeof(int32_t) + 64));     // two levels x (rect[4], id, flags, sidx, slist)
+        FIC_TRY(h->t_work.reserve(2 * level_cap * 9 * sizeof(int32_t) + level_cap * sizeof(unsigned long long) + 128));     // two levels x (rect[4], id, flags, sidx, slist, slist sorted by shape) + bounds
         FIC_TRY(h->t_count.reserve(64 * sizeof(int)));
         FIC_TRY(h->pin_a.reserve(256 + 64 * sizeof(int)));
         HvNodeDev* d_nodes = h->t_nodes.as<HvNodeDev>();
         int* d_counts = h->t_count.as<int>();
         int* h_counts = h->pin_a.as<int>() + 64;
         int n_search = 0;
-        int32_t* lvl[2] = {h->t_work.as<int32_t>(), h->t_work.as<int32_t>() + level_cap * 8};
+        int32_t* lvl[2] = {h->t_work.as<int32_t>(), h->t_work.as<int32_t>() + level_cap * 9};
+        unsigned long long* d_gbound = reinterpret_cast<unsigned long long*>((reinterpret_cast<uintptr_t>(lvl[1] + level_cap * 9) + 15) & ~(uintptr_t)15);
         {
             HvNodeDev root{};
             root.i = 0; root.j = 0; root.w = W; root.h = H; root.kind = -1; root.c1 = -1;
@@ -1267,11 +1521,15 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 5, first + 5, sizeof(int32_t), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 6, first + 6, sizeof(int32_t), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 7, first + 7, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 8, first + 7, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            FIC_CUDA(cudaMemsetAsync(d_gbound, 0xff, sizeof(unsigned long long), st));
             FIC_TRY(fic_sync(h, st));
             n_search = (f & 1) ? 1 : 0;
         }
         int n = 1, cur = 0, fault = 0, parity = 0;
         const int max_px = max_w * max_h > 0 ? max_w * max_h : 1;   // searched rectangles are at most max_w x max_h
+        const int small_px = min_w * min_h > 0 ? min_w * min_h : 1;  // ... or at most min_w x min_h (hv_flags)
+        const bool grouped = std::max(max_px, small_px) <= HV_GROUP_MAX_PX;   // rectangles of equal shape searched together
         while (n > 0) {
             const int32_t* rects = lvl[cur];
             const int32_t* ids = lvl[cur] + level_cap * 4;
@@ -1284,14 +1542,19 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             const double* pvals = nullptr;
             const unsigned long long* pseq = nullptr;
             if (n_search)
-                FIC_TRY(hv_search_level(h, d_img, H, W, rects, slist, n_search, max_px, scale_bits, offset_bits, max_scale, &S, &prec,
-                                        &pvals, &pseq, st));
+                FIC_TRY(hv_search_level(h, d_img, H, W, rects, slist, grouped ? lvl[cur] + level_cap * 8 : nullptr, d_gbound, n_search, max_px,
+                                        scale_bits, offset_bits, max_scale, &S, &prec, &pvals, &pseq, st));
             hv_decide_kernel<<<(n * 32 + 127) / 128, 128, 0, st>>>(I1, W + 1, rects, ids, flags, sidx, n, prec, pvals, pseq, S, thr,
                                                                    min_w, min_h, max_w, max_h, d_nodes, d_counts, parity, nrects,
                                                                    nrects + level_cap * 4, nrects + level_cap * 5,
                                                                    nrects + level_cap * 6, nrects + level_cap * 7, (int)node_cap,
                                                                    (int)level_cap);
             FIC_CHECK_LAUNCH(h, "hv_decide_kernel");
+            if (grouped) {   // the next level's search list sorted by shape; its length stays on the device
+                hv_group_kernel<<<1, 1024, 0, st>>>(nrects, nrects + level_cap * 7, d_counts + 4 + parity, nrects + level_cap * 8,
+                                                    nrects + level_cap * 6, d_gbound);
+                FIC_CHECK_LAUNCH(h, "hv_group_kernel");
+            }
             // the two numbers the host needs: the size of the next level and how many of its rectangles are searched
             FIC_CUDA(cudaMemcpyAsync(h_counts, d_counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
             FIC_TRY(fic_sync(h, st));
