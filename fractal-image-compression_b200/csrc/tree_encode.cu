@@ -590,7 +590,7 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
                                               const int32_t* __restrict__ rects, const int* rq, int x0, double max_scale,
                                               int scale_bits, int offset_bits, int32_t* __restrict__ rec, double* __restrict__ vals,
                                               unsigned long long* __restrict__ seqs, unsigned long long* __restrict__ gbound,
-                                              float* s_range, HvGroupBest* sb)
+                                              float* s_range, HvGroupBest* sb, int g_real /* rq[g_real..G) repeat rq[0] and are ignored */)
 {
     __shared__ float s_rs[HV_GROUP], s_sqr[HV_GROUP];
     __shared__ double s_slack[HV_GROUP];
@@ -607,7 +607,7 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
     // The best score any CTA has found so far for the rectangle (all-ones = none yet: a NaN, which drops nothing).  The
     // chunks of a rectangle are blockIdx.y, the slow grid dimension, so all but the first few start with a bound that
     // means something instead of scoring every candidate until they have found one of their own.
-    if (tid < HV_GROUP) s_bound[tid] = tid < G ? __ldcg(&gbound[x0 + tid]) : ~0ull;
+    if (tid < HV_GROUP) s_bound[tid] = tid < g_real ? __ldcg(&gbound[x0 + tid]) : ~0ull;
 #pragma unroll
     for (int k = 0; k < G; ++k) { sb->R[k][tid] = __longlong_as_double(0x7ff0000000000000ll); sb->seq[k][tid] = ~0ull; }
     __syncthreads();
@@ -679,7 +679,7 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
             for (int e = 0; e < 4; ++e) {
                 const double num = DS(DM(dn, (double)ab[k][e]), DM(rsd, dsd[e]));
                 const bool drop = room > 0.0 && nden[e] > 0.0 && DM(num, num) < DM(room, nden[e]);
-                if (!drop) pass |= 1u << (k * 4 + e);
+                if (!drop && k < g_real) pass |= 1u << (k * 4 + e);
             }
         }
         while (pass) {
@@ -706,6 +706,7 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
     }
 #pragma unroll
     for (int k = 0; k < G; ++k) {
+        if (k >= g_real) break;
         TeBest b;
         b.R = sb->R[k][tid]; b.seq = sb->seq[k][tid];
         b.s = b.o = 0.0; b.di = b.dj = b.orient = b.rot = b.qs = b.qo = 0;
@@ -742,13 +743,12 @@ hv_search_grouped_kernel(const uint8_t* __restrict__ img, const float* __restric
         while (b < m && rects[4 * (size_t)rq[b] + 2] == rects[4 * (size_t)rq[a] + 2] && rects[4 * (size_t)rq[b] + 3] == rects[4 * (size_t)rq[a] + 3]) ++b;
         int run[HV_GROUP];
 #pragma unroll
-        for (int k = 0; k < HV_GROUP; ++k) run[k] = rq[a + k < m ? a + k : a];
-        switch (b - a) {
-        case 1: hv_group_body<1>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
-        case 2: hv_group_body<2>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
-        case 3: hv_group_body<3>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
-        default: hv_group_body<4>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb); break;
-        }
+        for (int k = 0; k < HV_GROUP; ++k) run[k] = rq[k < b - a ? a + k : a];
+        // Two bodies only -- a single rectangle, or up to four with the unused slots repeating the first: different CTAs of an
+        // SM run different bodies at the same time and the kernel's code has to stay in the instruction cache (with four
+        // bodies a third of the stall samples were waits for instructions).
+        if (b - a == 1) hv_group_body<1>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb, 1);
+        else hv_group_body<HV_GROUP>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb, b - a);
         a = b;
     }
 }
