@@ -590,7 +590,8 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
                                               const int32_t* __restrict__ rects, const int* rq, int x0, double max_scale,
                                               int scale_bits, int offset_bits, int32_t* __restrict__ rec, double* __restrict__ vals,
                                               unsigned long long* __restrict__ seqs, unsigned long long* __restrict__ gbound,
-                                              float* s_range, HvGroupBest* sb, int g_real /* rq[g_real..G) repeat rq[0] and are ignored */)
+                                              const float2* __restrict__ rsums, float* s_range, HvGroupBest* sb,
+                                              int g_real /* rq[g_real..G) repeat rq[0] and are ignored */)
 {
     __shared__ float s_rs[HV_GROUP], s_sqr[HV_GROUP];
     __shared__ double s_slack[HV_GROUP];
@@ -611,27 +612,23 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
 #pragma unroll
     for (int k = 0; k < G; ++k) { sb->R[k][tid] = __longlong_as_double(0x7ff0000000000000ll); sb->seq[k][tid] = ~0ull; }
     __syncthreads();
-    if (tid < G) {
-        float rs = 0.f, sq = 0.f;
-        for (int t = 0; t < nn; ++t) {
-            const float v = s_range[t * G + tid];
-            rs = __fadd_rn(rs, v);
-            sq = __fadd_rn(sq, __fmul_rn(v, v));
-        }
-        s_rs[tid] = rs;
-        s_sqr[tid] = sq;
-        s_slack[tid] = DS((double)sq, DD(DM((double)rs, (double)rs), (double)nn));   // sqr - rs^2 / n
+    if (tid < G) {   // the rectangle's two sums: sequential float32 chains, computed once per level by hv_group_kernel
+        const float2 rr = rsums[x0 + (tid < g_real ? tid : 0)];
+        s_rs[tid] = rr.x;
+        s_sqr[tid] = rr.y;
+        s_slack[tid] = DS((double)rr.y, DD(DM((double)rr.x, (double)rr.x), (double)nn));   // sqr - rs^2 / n
     }
     __syncthreads();
     const double dn = (double)nn;
     const int ndi = H - 2 * hgt > 0 ? (H - 2 * hgt + hgt - 1) / hgt : 0;  // range(0, H-2h, h): exclusive
     const int ndj = W - 2 * w > 0 ? (W - 2 * w + w - 1) / w : 0;
-    const long long npos = (long long)ndi * ndj;
-    const long long per = (npos + gridDim.y - 1) / gridDim.y;
-    const long long p0 = per * blockIdx.y, p1 = p0 + per < npos ? p0 + per : npos;
+    const int npos = ndi * ndj;                                           // (at most H * W / 4 < 2^31, hv_encode_impl)
+    const int per = (npos + (int)gridDim.y - 1) / (int)gridDim.y;
+    const int p0 = per * (int)blockIdx.y, p1 = p0 + per < npos ? p0 + per : npos;
     const int PW = W - 1;
-    for (long long pos = p0 + tid; pos < p1; pos += TE_THREADS) {
-        const int di = (int)(pos / ndj) * hgt, dj = (int)(pos % ndj) * w;
+    for (int pos = p0 + tid; pos < p1; pos += TE_THREADS) {
+        const int pi = pos / ndj;
+        const int di = pi * hgt, dj = (pos - pi * ndj) * w;
         const float* top = Dp + (size_t)di * PW + dj;                       // row 0 of the pooled block
         const float* bot = top + (size_t)(2 * (hgt - 1)) * PW;              // its last row
         const int last = 2 * (w - 1);
@@ -712,9 +709,9 @@ __device__ __forceinline__ void hv_group_body(const uint8_t* __restrict__ img, c
         b.s = b.o = 0.0; b.di = b.dj = b.orient = b.rot = b.qs = b.qo = 0;
         if (b.seq != ~0ull) {
             b.s = sb->s[k][tid]; b.o = sb->o[k][tid]; b.qs = sb->qs[k][tid]; b.qo = sb->qo[k][tid];
-            const long long pos = (long long)(b.seq >> 2);
+            const int pos = (int)(b.seq >> 2);
             const int iso = (int)(b.seq & 3ull);
-            b.di = (int)(pos / ndj) * hgt; b.dj = (int)(pos % ndj) * w; b.orient = iso >> 1; b.rot = (iso & 1) * 2;
+            b.di = (pos / ndj) * hgt; b.dj = (pos % ndj) * w; b.orient = iso >> 1; b.rot = (iso & 1) * 2;
         }
         const size_t slot = (size_t)(x0 + k) * gridDim.y + blockIdx.y;
         __syncthreads();      // (te_block_reduce's shared scratch is reused from call to call)
@@ -727,7 +724,8 @@ __global__ void __launch_bounds__(TE_THREADS, HV_MINB)
 hv_search_grouped_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int H, int W,
                          const int32_t* __restrict__ rects /*[n][4] = i,j,w,h*/, double max_scale, int scale_bits, int offset_bits,
                          int32_t* __restrict__ rec, double* __restrict__ vals, unsigned long long* __restrict__ seqs,
-                         const int32_t* __restrict__ slist /*sorted by shape*/, int count, unsigned long long* __restrict__ gbound)
+                         const int32_t* __restrict__ slist /*sorted by shape*/, int count, unsigned long long* __restrict__ gbound,
+                         const float2* __restrict__ rsums /*[count] = (sum r, sum r^2) of the entries of slist*/)
 {
     extern __shared__ __align__(16) unsigned char s_dyn[];
     float* s_range = reinterpret_cast<float*>(s_dyn);
@@ -747,8 +745,8 @@ hv_search_grouped_kernel(const uint8_t* __restrict__ img, const float* __restric
         // Two bodies only -- a single rectangle, or up to four with the unused slots repeating the first: different CTAs of an
         // SM run different bodies at the same time and the kernel's code has to stay in the instruction cache (with four
         // bodies a third of the stall samples were waits for instructions).
-        if (b - a == 1) hv_group_body<1>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb, 1);
-        else hv_group_body<HV_GROUP>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, s_range, sb, b - a);
+        if (b - a == 1) hv_group_body<1>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, rsums, s_range, sb, 1);
+        else hv_group_body<HV_GROUP>(img, Dp, H, W, rects, run, x0 + a, max_scale, scale_bits, offset_bits, rec, vals, seqs, gbound, rsums, s_range, sb, b - a);
         a = b;
     }
 }
@@ -758,7 +756,8 @@ hv_search_grouped_kernel(const uint8_t* __restrict__ img, const float* __restric
 #define HV_SORT_BINS 4096
 __global__ void __launch_bounds__(1024)
 hv_group_kernel(const int32_t* __restrict__ rects, const int32_t* __restrict__ slist, const int* __restrict__ count_ptr,
-                int32_t* __restrict__ slist_sorted, int32_t* __restrict__ sidx, unsigned long long* __restrict__ gbound)
+                int32_t* __restrict__ slist_sorted, int32_t* __restrict__ sidx, unsigned long long* __restrict__ gbound,
+                const uint8_t* __restrict__ img, int W, float2* __restrict__ rsums)
 {
     __shared__ int hist[HV_SORT_BINS];
     __shared__ int warp_sum[32];
@@ -803,6 +802,21 @@ hv_group_kernel(const int32_t* __restrict__ rects, const int32_t* __restrict__ s
         slist_sorted[at] = r;
         sidx[r] = at;
         gbound[e] = ~0ull;     // no score yet for the e-th rectangle of the search list
+    }
+    __syncthreads();
+    // sum r and sum r^2 of every rectangle, in the reference's order (row-major, float32): two serial chains per rectangle,
+    // done here once instead of by one thread of every chunk CTA with the other 127 waiting at the barrier
+    for (int e = tid; e < n; e += 1024) {
+        const int r = slist_sorted[e];
+        const int ri = rects[4 * (size_t)r], rj = rects[4 * (size_t)r + 1], w = rects[4 * (size_t)r + 2], hgt = rects[4 * (size_t)r + 3];
+        float rs = 0.f, sq = 0.f;
+        for (int i = 0; i < hgt; ++i)
+            for (int j = 0; j < w; ++j) {
+                const float v = (float)img[(size_t)(ri + i) * W + rj + j];
+                rs = __fadd_rn(rs, v);
+                sq = __fadd_rn(sq, __fmul_rn(v, v));
+            }
+        rsums[e] = make_float2(rs, sq);
     }
 }
 
@@ -1448,7 +1462,8 @@ __global__ void hv_decide_kernel(const long long* __restrict__ I1, int W1, const
 // the search of one level with the chunk winners left in the handle's partial buffers (hv_decide_kernel merges them)
 static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_rects, const int32_t* d_slist,
                            const int32_t* d_slist_sorted /* list sorted by shape (hv_group_kernel) or nullptr */,
-                           unsigned long long* d_gbound /* with the sorted list: one bound per entry, all-ones */, int count, int max_px, int scale_bits, int offset_bits, double max_scale, int* S_out,
+                           unsigned long long* d_gbound /* with the sorted list: one bound per entry, all-ones */,
+                           const float2* d_rsums /* ... and (sum r, sum r^2) per entry */, int count, int max_px, int scale_bits, int offset_bits, double max_scale, int* S_out,
                            const int32_t** prec_out, const double** pvals_out, const unsigned long long** pseq_out, cudaStream_t st)
 {
     const float* Dp = h->t_hvpool.as<float>();
@@ -1470,7 +1485,7 @@ static int hv_search_level(fic_handle* h, const uint8_t* d_img, int H, int W, co
             h->hv_group_attr_ready = true;
         }
         hv_search_grouped_kernel<<<dim3(n_cta, S), TE_THREADS, smem, st>>>(d_img, Dp, H, W, d_rects, max_scale, scale_bits, offset_bits,
-                                                                          prec, pvals, pseq, d_slist_sorted, count, d_gbound);
+                                                                          prec, pvals, pseq, d_slist_sorted, count, d_gbound, d_rsums);
         FIC_CHECK_LAUNCH(h, "hv_search_grouped_kernel");
         *S_out = S; *prec_out = prec; *pvals_out = pvals; *pseq_out = pseq;
         return FIC_OK;
@@ -1498,7 +1513,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
         const size_t level_cap = std::min((size_t)H * W + 2, node_cap);
         FIC_REQUIRE(node_cap < ((size_t)1 << 30), "fic_hv_encode: image too large");
         FIC_TRY(h->t_nodes.reserve(node_cap * sizeof(HvNodeDev) + 64));
-        FIC_TRY(h->t_work.reserve(2 * level_cap * 9 * sizeof(int32_t) + level_cap * sizeof(unsigned long long) + 128));     // two levels x (rect[4], id, flags, sidx, slist, slist sorted by shape) + bounds
+        FIC_TRY(h->t_work.reserve(2 * level_cap * 9 * sizeof(int32_t) + level_cap * (sizeof(unsigned long long) + sizeof(float2)) + 128));     // two levels x (rect[4], id, flags, sidx, slist, slist sorted by shape) + bounds + range sums
         FIC_TRY(h->t_count.reserve(64 * sizeof(int)));
         FIC_TRY(h->pin_a.reserve(256 + 64 * sizeof(int)));
         HvNodeDev* d_nodes = h->t_nodes.as<HvNodeDev>();
@@ -1507,6 +1522,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
         int n_search = 0;
         int32_t* lvl[2] = {h->t_work.as<int32_t>(), h->t_work.as<int32_t>() + level_cap * 9};
         unsigned long long* d_gbound = reinterpret_cast<unsigned long long*>((reinterpret_cast<uintptr_t>(lvl[1] + level_cap * 9) + 15) & ~(uintptr_t)15);
+        float2* d_rsums = reinterpret_cast<float2*>(d_gbound + level_cap);
         {
             HvNodeDev root{};
             root.i = 0; root.j = 0; root.w = W; root.h = H; root.kind = -1; root.c1 = -1;
@@ -1514,6 +1530,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             int32_t first[8] = {0, 0, W, H, 0, f, (f & 1) ? 0 : -1, 0};
             memset(h_counts, 0, 8 * sizeof(int));
             h_counts[0] = 1;
+            h_counts[6] = (f & 1) ? 1 : 0;      // length of the root level's search list (read by hv_group_kernel below)
             FIC_CUDA(cudaMemcpyAsync(d_counts, h_counts, 8 * sizeof(int), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(d_nodes, &root, sizeof(root), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(lvl[0], first, 4 * sizeof(int32_t), cudaMemcpyHostToDevice, st));
@@ -1522,7 +1539,11 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 6, first + 6, sizeof(int32_t), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 7, first + 7, sizeof(int32_t), cudaMemcpyHostToDevice, st));
             FIC_CUDA(cudaMemcpyAsync(lvl[0] + level_cap * 8, first + 7, sizeof(int32_t), cudaMemcpyHostToDevice, st));
-            FIC_CUDA(cudaMemsetAsync(d_gbound, 0xff, sizeof(unsigned long long), st));
+            if (std::max(max_w * max_h, min_w * min_h) <= HV_GROUP_MAX_PX) {
+                hv_group_kernel<<<1, 1024, 0, st>>>(lvl[0], lvl[0] + level_cap * 7, d_counts + 6, lvl[0] + level_cap * 8, lvl[0] + level_cap * 6,
+                                                    d_gbound, d_img, W, d_rsums);
+                FIC_CHECK_LAUNCH(h, "hv_group_kernel");
+            }
             FIC_TRY(fic_sync(h, st));
             n_search = (f & 1) ? 1 : 0;
         }
@@ -1542,7 +1563,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             const double* pvals = nullptr;
             const unsigned long long* pseq = nullptr;
             if (n_search)
-                FIC_TRY(hv_search_level(h, d_img, H, W, rects, slist, grouped ? lvl[cur] + level_cap * 8 : nullptr, d_gbound, n_search, max_px,
+                FIC_TRY(hv_search_level(h, d_img, H, W, rects, slist, grouped ? lvl[cur] + level_cap * 8 : nullptr, d_gbound, d_rsums, n_search, max_px,
                                         scale_bits, offset_bits, max_scale, &S, &prec, &pvals, &pseq, st));
             hv_decide_kernel<<<(n * 32 + 127) / 128, 128, 0, st>>>(I1, W + 1, rects, ids, flags, sidx, n, prec, pvals, pseq, S, thr,
                                                                    min_w, min_h, max_w, max_h, d_nodes, d_counts, parity, nrects,
@@ -1552,7 +1573,7 @@ int hv_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int min_h,
             FIC_CHECK_LAUNCH(h, "hv_decide_kernel");
             if (grouped) {   // the next level's search list sorted by shape; its length stays on the device
                 hv_group_kernel<<<1, 1024, 0, st>>>(nrects, nrects + level_cap * 7, d_counts + 4 + parity, nrects + level_cap * 8,
-                                                    nrects + level_cap * 6, d_gbound);
+                                                    nrects + level_cap * 6, d_gbound, d_img, W, d_rsums);
                 FIC_CHECK_LAUNCH(h, "hv_group_kernel");
             }
             // the two numbers the host needs: the size of the next level and how many of its rectangles are searched
