@@ -1349,14 +1349,14 @@ struct QtcState {
 template <int S>
 __global__ void qt_tcpool_kernel(const uint16_t* __restrict__ P, int H, int W, const int32_t* __restrict__ dcls,
                                  __half* __restrict__ poolA, uint32_t* __restrict__ sd4, uint32_t* __restrict__ sq4,
-                                 float* __restrict__ sds8, uint8_t* __restrict__ dtyp, double* __restrict__ den)
+                                 float* __restrict__ sds8, uint8_t* __restrict__ dtyp, double* __restrict__ den, int hs, int vs)
 {
     constexpr int N = S * S;
-    const int PW = W - 2 * S + 1, PH = H - 2 * S + 1, BW = W - 1;
+    const int PW = (W - 2 * S) / hs + 1, PH = (H - 2 * S) / vs + 1, BW = W - 1;   // the pool's lattice (quadtree/encoder.py:262-283)
     const int NP = PW * PH;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= NP) return;
-    const int di = p / PW, dj = p - di * PW;
+    const int di = (p / PW) * vs, dj = (p % PW) * hs;
     int v[N];
     int s = 0;
     long long s2 = 0;
@@ -1527,7 +1527,8 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P
                  const int32_t* __restrict__ dcls /*[NP][3] = class, rot, orient*/, int H, int W, QtcState* __restrict__ state,
                  const int* __restrict__ ctrl, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ list, uint32_t cap,
                  int nmodes, double max_scale, int scale_bits, int offset_bits, int32_t* __restrict__ out_rec,
-                 double* __restrict__ out_vals, int32_t* __restrict__ need_exact)
+                 double* __restrict__ out_vals, int32_t* __restrict__ need_exact, int hs, int vs,
+                 const int32_t* __restrict__ pool_offsets /*[73]*/, const int32_t* __restrict__ pool_rows /*[..][4]*/)
 {
     constexpr int N = S * S;
     __shared__ float rv[QTC_WARPS][N];            // the range blocks as floats
@@ -1541,7 +1542,7 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
     const int slot = blockIdx.x * QTC_WARPS + warp;
     const int n_elig = ctrl[0];
-    const int PW = W - 2 * S + 1;
+    const int PW = (W - 2 * S) / hs + 1;
     // ---- phase A: warp w prepares range w of the CTA ----
     if (lane == 0) { s_n[warp] = 0; s_live[warp] = 0; }
     if (slot < n_elig) {
@@ -1594,7 +1595,7 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P
             const uint32_t ent = list[(size_t)rslot * cap + (e - s_n[r])];
             const int t = ent & 7, p = ent >> 3;
             const int dclass = dcls[3 * (size_t)p], drot = dcls[3 * (size_t)p + 1], dorient = dcls[3 * (size_t)p + 2];
-            const int di = p / PW, dj = p - di * PW;
+            const int di = (p / PW) * vs, dj = (p % PW) * hs;
             for (int md = 0; md < nmodes; ++md) {
                 const int rrot = s_rot[r][md], rorient = s_orient[r][md];
                 int d_rot, d_orient;
@@ -1636,6 +1637,54 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P
             for (int k = 0; k < 6; ++k) s_rec[r][k] = brec[k];
         }
         __syncthreads();
+    }
+    // ---- the placeholder rows: a class without a domain is represented by the row (0, 0, rotation 0, orientation 0)
+    // (quadtree/encoder.py:279-280), which the reference's loop over all classes scores like any other domain -- the block at
+    // the origin, with this class's place in the scan order.  (A class whose only domain IS that row gives the same candidate.)
+    if (s_live[warp]) {
+        double bE = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
+        unsigned long long btie = ~0ull;
+        int brec[6] = {0, 0, 0, 0, 0, 0};
+        for (int c = lane; c < 72; c += 32) {
+            const int b0 = pool_offsets[c];
+            if (pool_offsets[c + 1] - b0 != 1) continue;
+            const int32_t* row = pool_rows + 4 * (size_t)b0;
+            if (row[0] | row[1] | row[2] | row[3]) continue;
+            for (int md = 0; md < nmodes; ++md) {
+                const int rrot = s_rot[warp][md], rorient = s_orient[warp][md];
+                const int d_orient = rorient == 0 ? 0 : 1;
+                const int d_rot = rorient == 0 ? ((0 - rrot) & 3) : ((0 - rrot + 2) & 3);
+                float ds = 0.f, sds = 0.f, ab = 0.f;
+                for (int k = 0; k < N; ++k) {
+                    int a, b;
+                    fic_iso_qt_enc(d_orient, d_rot, S, k / S, k % S, a, b);
+                    const float d = __fmul_rn((float)P[(size_t)(2 * a) * (W - 1) + 2 * b], 0.25f);
+                    ds = __fadd_rn(ds, d);
+                    sds = __fadd_rn(sds, __fmul_rn(d, d));
+                    ab = __fadd_rn(ab, __fmul_rn(d, rv[warp][k]));
+                }
+                const QScore sc = fic_q_score(N, s_rs[warp], s_sqr[warp], ds, sds, ab, max_scale, scale_bits, offset_bits);
+                const unsigned long long tie = (unsigned long long)(md * 72 + c) << 32;
+                if (fic_better(sc.R, tie, bE, btie)) {
+                    bE = sc.R; btie = tie; bs = sc.s; bo = sc.o;
+                    brec[0] = 0; brec[1] = 0; brec[2] = d_orient; brec[3] = d_rot; brec[4] = sc.qs; brec[5] = sc.qo;
+                }
+            }
+        }
+        // the warp's best placeholder candidate against the winner among the listed
+        double wE = bE;
+        unsigned long long wt = btie;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double oE = __shfl_xor_sync(0xffffffffu, wE, off);
+            const unsigned long long ot = __shfl_xor_sync(0xffffffffu, wt, off);
+            if (fic_better(oE, ot, wE, wt)) { wE = oE; wt = ot; }
+        }
+        if (wt != ~0ull && btie == wt && fic_better(wE, wt, s_E[warp], s_tie[warp])) {   // tie keys are unique: one lane
+            s_E[warp] = bE; s_s[warp] = bs; s_o[warp] = bo; s_tie[warp] = btie;
+            for (int k = 0; k < 6; ++k) s_rec[warp][k] = brec[k];
+        }
+        __syncwarp();
     }
     // ---- commit ----
     if (lane == 0 && s_live[warp]) {
@@ -1895,10 +1944,11 @@ int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mod
 template <int S>
 static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_queue, int n_ranges,
                              const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits,
-                             int offset_bits, int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st)
+                             int offset_bits, int32_t* d_rec, double* d_vals, int32_t* d_need_exact, int hs, int vs,
+                             const int32_t* d_pool_offsets, const int32_t* d_pool_rows, cudaStream_t st)
 {
     constexpr int N = S * S;
-    const int PW = W - 2 * S + 1, PH = H - 2 * S + 1;
+    const int PW = (W - 2 * S) / hs + 1, PH = (H - 2 * S) / vs + 1;
     const int NP = PW * PH;
     const int n_tiles = cdiv(NP, BM);
     const int np_pad = n_tiles * BM;
@@ -1934,7 +1984,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     unsigned long long* bound = h->bf_best.as<unsigned long long>();
     QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + slots_pad) + 15) & ~(uintptr_t)15);
 
-    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, sd4, sq4, sds8, dtyp, den);
+    qt_tcpool_kernel<S><<<cdiv(NP, 128), 128, 0, st>>>(P, H, W, d_dcls, poolA, sd4, sq4, sds8, dtyp, den, hs, vs);
     FIC_CHECK_LAUNCH(h, "qt_tcpool_kernel");
     qt_tcinit_kernel<S><<<cdiv((long long)slots_pad * 32, 256), 256, 0, st>>>(d_img, W, d_queue, d_rcls, n_ranges, state, cnt, bound, ctrl, slots_pad, rngB,
                                                                               d_need_exact, rngc);
@@ -1961,7 +2011,7 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
     // Seed pass: every stride-th tile of 128 positions is looked at first and only lowers the bounds -- with the bounds at
     // +inf, and every CTA on a different range, nearly all of its candidates would be listed.  The full pass then lists
     // from all positions against bounds that mean something.
-    const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 1);
+    const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : (NP >= 1024 ? 5 : 1));
     if (stride > 1) {
         sp.m_cur = stride; sp.n_round_tiles = cdiv(n_tiles, stride); sp.seed_pass = 1;
         bf_screen_kernel<7, N><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
@@ -1982,27 +2032,29 @@ static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, 
 #endif
     // the lists hold every candidate that was at or below its range's best score when it was looked at
     qt_tcpick_kernel<S><<<cdiv(n_ranges, QTC_WARPS), QTC_WARPS * 32, 0, st>>>(d_img, P, d_dcls, H, W, state, ctrl, cnt, list, cap, nmodes, max_scale,
-                                                                             scale_bits, offset_bits, d_rec, d_vals, d_need_exact);
+                                                                             scale_bits, offset_bits, d_rec, d_vals, d_need_exact, hs, vs,
+                                                                             d_pool_offsets, d_pool_rows);
     FIC_CHECK_LAUNCH(h, "qt_tcpick_kernel");
     return FIC_OK;
 }
 
-bool qt_tc_applicable(int H, int W, int e, double max_scale)
+bool qt_tc_applicable(int H, int W, int e, double max_scale, int hs, int vs)
 {
     if (e != 2 && e != 3) return false;
     const int S = 1 << e;
-    if (H < 2 * S || W < 2 * S || !(max_scale > 0.0 && max_scale <= 1.0)) return false;
-    const long long np = (long long)(H - 2 * S + 1) * (W - 2 * S + 1);
-    return np >= 2048 && np < (1ll << 26);      // below that the fixed costs of the pipeline dominate; queue entries hold 26 bits of position
+    if (H < 2 * S || W < 2 * S || hs < 1 || vs < 1 || !(max_scale > 0.0 && max_scale <= 1.0)) return false;
+    const long long np = (long long)((H - 2 * S) / vs + 1) * ((W - 2 * S) / hs + 1);
+    return np >= 512 && np < (1ll << 26);      // below that the fixed costs of the pipeline dominate; queue entries hold 26 bits of position
 }
 
 int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const int32_t* d_queue, int n_ranges,
                  const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits, int offset_bits,
-                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st)
+                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, int hs, int vs, const int32_t* d_pool_offsets,
+                 const int32_t* d_pool_rows, cudaStream_t st)
 {
     if (e == 3)
         return qt_tc_search_impl<8>(h, d_img, H, W, d_queue, n_ranges, d_rcls, d_dcls, nmodes, max_scale, scale_bits, offset_bits, d_rec,
-                                    d_vals, d_need_exact, st);
+                                    d_vals, d_need_exact, hs, vs, d_pool_offsets, d_pool_rows, st);
     return qt_tc_search_impl<4>(h, d_img, H, W, d_queue, n_ranges, d_rcls, d_dcls, nmodes, max_scale, scale_bits, offset_bits, d_rec,
-                                d_vals, d_need_exact, st);
+                                d_vals, d_need_exact, hs, vs, d_pool_offsets, d_pool_rows, st);
 }

@@ -924,10 +924,11 @@ __global__ void qt_range_class_kernel(const long long* __restrict__ I1, const lo
 }
 
 // bf_screen.cu / bf_exact.cu: the dense all-classes search on the tensor-core screen
-bool qt_tc_applicable(int H, int W, int e, double max_scale);
+bool qt_tc_applicable(int H, int W, int e, double max_scale, int hs, int vs);
 int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const int32_t* d_queue, int n_ranges,
                  const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits, int offset_bits,
-                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, cudaStream_t st);
+                 int32_t* d_rec, double* d_vals, int32_t* d_need_exact, int hs, int vs, const int32_t* d_pool_offsets,
+                 const int32_t* d_pool_rows, cudaStream_t st);
 int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
 
 // ---- quadtree partition on the device (quadtree/encoder.py:127-146) ----------------------------------------------
@@ -1225,10 +1226,10 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
             QtPoolDev pool;
             pool.offsets = h->t_lists.as<int32_t>() + pool_base[pk];
             pool.rows = pool.offsets + 73;
-            // Dense pools searched over all classes are the brute-force contraction: tensor-core screen first, the CUDA-core
-            // search only for the ranges it leaves undecided.
+            // A pool searched over all classes is the brute-force contraction: on the tensor cores (qt_tc_search), the CUDA-core
+            // search only for the ranges it hands back.
             const int32_t* need = nullptr;
-            if (full && geom[pk].hs == 1 && geom[pk].vs == 1 && n >= 32 && qt_tc_applicable(H, W, e, max_scale)) {
+            if (full && n >= 32 && qt_tc_applicable(H, W, e, max_scale, geom[pk].hs, geom[pk].vs)) {
                 if (!boxsum_ready) {
                     FIC_TRY(bf_prepare8(h, d_img, H, W, false, st));
                     boxsum_ready = true;
@@ -1239,7 +1240,7 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
                 FIC_CHECK_LAUNCH(h, "qt_range_class_kernel");
                 FIC_TRY(qt_tc_search(h, d_img, H, W, e, queue, n, h->t_rcls.as<int32_t>(), h->t_cls.as<int32_t>() + geom[pk].cls_off, nmodes,
                                      max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(), h->t_part.as<double>(),
-                                     h->t_need.as<int32_t>(), st));
+                                     h->t_need.as<int32_t>(), geom[pk].hs, geom[pk].vs, pool.offsets, pool.rows, st));
                 need = h->t_need.as<int32_t>();
 #ifdef FIC_TUNING
                 {

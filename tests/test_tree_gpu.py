@@ -370,3 +370,21 @@ def test_quadtree_dense_full_class_golden(fic, case):
     h.update(int(n_roots).to_bytes(4, "little"))
     assert len(nodes) == g["nodes"]
     assert h.hexdigest() == g["sha256"]
+
+
+@pytest.mark.parametrize("params,shape,seed", [
+    ((7, 5, 1.0, True, False, 4, 8, 2.0), (256, 256), 71),             # default steps (= domain side): 32 x 32 domains for the 4x4 ranges
+    ((7, 5, 1.0, True, False, 4, 8, 1.0, 3, 5), (200, 232), 72),       # odd steps, ragged image
+    ((6, 6, 0.5, True, True, 4, 16, 3.0, 2, 2), (160, 192), 73),       # positive scales only, smaller max_scale
+], ids=["default_steps", "steps_3_5", "steps_2_2_positive"])
+def test_quadtree_full_class_search_sparse_pools_on_the_tensor_cores(fic, orc, params, shape, seed):
+    """full_class_search with pools that are not dense: the same tensor-core pass over the pool's lattice (qt_tc_search),
+    including the placeholder rows of classes that have no domain (quadtree/encoder.py:279-280) -- a flat corner makes
+    sure some classes are empty and that constant ranges go to the exact search."""
+    img = synthetic_image(seed, *shape)
+    img[-40:, -56:] = 17
+    want = orc.qt_encode(img, *params)
+    got = fic.qt_encode(img, *params)
+    assert got[2] == want[2]
+    assert np.array_equal(got[0], want[0])
+    assert np.array_equal(got[1], want[1])
