@@ -456,6 +456,116 @@ qt_search_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, 
     te_block_reduce(best, rec + 6 * (size_t)blockIdx.x, vals + 3 * (size_t)blockIdx.x);
 }
 
+// The same search with a WARP per range, for the class-restricted case (full_class_search off) and blocks of at most 64
+// pixels: a range then meets the one or two class lists of its own classification -- a hundred candidates or so in a default
+// pool -- and a CTA per range spends its time in the serial prologue of one thread and in block barriers (ncu launch list of
+// the default 512x512 encode: 278 us for 15 916 CTAs, 10 us per CTA).  Here the lanes load the block, two lanes classify the
+// two scale signs at the same time, the candidates are strided over the lanes and the winner is found by shuffles: no
+// block barrier at all, four ranges per CTA.  Scoring, order and tie-break are qt_search_kernel's.
+#define QT_WARP_RANGES 4
+__global__ void __launch_bounds__(QT_WARP_RANGES * 32)
+qt_search_warp_kernel(const uint8_t* __restrict__ img, const float* __restrict__ Dp, int W, const long long* __restrict__ I1,
+                      const long long* __restrict__ I2, const int32_t* __restrict__ ranges /*[n][4] = si,sj,node,-*/, int n, int side,
+                      QtPoolDev pool, int nmodes, double max_scale, int scale_bits, int offset_bits,
+                      int32_t* __restrict__ rec /*[n][6]*/, double* __restrict__ vals /*[n][3]*/)
+{
+    __shared__ float s_range[QT_WARP_RANGES][64];
+    __shared__ unsigned long long s_bound[QT_WARP_RANGES];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * QT_WARP_RANGES + warp;
+    if (q >= n) return;
+    const int si = ranges[4 * (size_t)q], sj = ranges[4 * (size_t)q + 1];
+    const int nn = side * side;
+    for (int t = lane; t < nn; t += 32) s_range[warp][t] = (float)img[(size_t)(si + t / side) * W + sj + t % side];
+    if (lane == 0) s_bound[warp] = 0x7ff0000000000000ull;
+    int mc = 0, vc = 0, rot = 0, orient = 0;
+    if (lane < nmodes) classify_block(I1, I2, W + 1, si, sj, side, lane, mc, vc, rot, orient);
+    __syncwarp();
+    float rs = 0.f, sqr = 0.f;
+    if (lane == 0) {   // the reference's sequential float32 sums
+        for (int t = 0; t < nn; ++t) rs = __fadd_rn(rs, s_range[warp][t]);
+        for (int t = 0; t < nn; ++t) sqr = __fadd_rn(sqr, __fmul_rn(s_range[warp][t], s_range[warp][t]));
+    }
+    rs = __shfl_sync(0xffffffffu, rs, 0);
+    sqr = __shfl_sync(0xffffffffu, sqr, 0);
+    const int cls = mc * 24 + vc;
+    const int cls0 = __shfl_sync(0xffffffffu, cls, 0), cls1 = __shfl_sync(0xffffffffu, cls, 1);
+    const int rot0 = __shfl_sync(0xffffffffu, rot, 0), rot1 = __shfl_sync(0xffffffffu, rot, 1);
+    const int ori0 = __shfl_sync(0xffffffffu, orient, 0), ori1 = __shfl_sync(0xffffffffu, orient, 1);
+    const int b0 = pool.offsets[cls0], n0 = pool.offsets[cls0 + 1] - b0;
+    const int b1 = nmodes > 1 ? pool.offsets[cls1] : 0, n1 = nmodes > 1 ? pool.offsets[cls1 + 1] - b1 : 0;
+    const int total = n0 + n1;
+    const double dn = (double)nn;
+    const double slack_a = DS((double)sqr, DD(DM((double)rs, (double)rs), dn));   // sqr - rs^2 / n
+    const int PW = W - 1;
+    TeBest best;
+    te_init(best);
+    for (int c = lane; c < total; c += 32) {
+        const bool second = c >= n0;
+        const int32_t* row = pool.rows + 4 * (size_t)(second ? b1 + (c - n0) : b0 + c);
+        const int di = row[0], dj = row[1], drot = row[2], dorient = row[3];
+        const int rrot = second ? rot1 : rot0, rorient = second ? ori1 : ori0;
+        int d_rot, d_orient;
+        if (dorient == rorient) { d_rot = (drot - rrot) & 3; d_orient = 0; }
+        else { d_rot = (drot - rrot + 2) & 3; d_orient = 1; }
+        int a00, b00, a10, b10, a01, b01;      // the isometry is affine in (i, j): three corners instead of every pixel
+        fic_iso_qt_enc(d_orient, d_rot, side, 0, 0, a00, b00);
+        fic_iso_qt_enc(d_orient, d_rot, side, 1, 0, a10, b10);
+        fic_iso_qt_enc(d_orient, d_rot, side, 0, 1, a01, b01);
+        const int step_i = 2 * ((a10 - a00) * PW + (b10 - b00)), step_j = 2 * ((a01 - a00) * PW + (b01 - b00));
+        const float* drow = Dp + (size_t)(di + 2 * a00) * PW + dj + 2 * b00;
+        float ds = 0.f, sds = 0.f, ab = 0.f;
+        int t = 0;
+        for (int i = 0; i < side; ++i, drow += step_i) {
+            const float* qd = drow;
+            for (int j = 0; j < side; ++j, qd += step_j, ++t) {
+                const float d = *qd;
+                ds = __fadd_rn(ds, d);
+                sds = __fadd_rn(sds, __fmul_rn(d, d));
+                ab = __fadd_rn(ab, __fmul_rn(d, s_range[warp][t]));
+            }
+        }
+        {   // exact lower bound of the score (see hv_search_kernel) against the warp's best
+            const double bound = __longlong_as_double((long long)*(volatile unsigned long long*)&s_bound[warp]);
+            const double room = DS(slack_a, DM(dn, bound));
+            if (room > 0.0) {
+                const double dsd = (double)ds;
+                const double den = DS(DM(dn, (double)sds), DM(dsd, dsd));
+                const double num = DS(DM(dn, (double)ab), DM((double)rs, dsd));
+                if (den > 0.0 && DM(num, num) < DM(DM(DM(room, dn), den), 0.999999999)) continue;
+            }
+        }
+        const QScore sc = fic_q_score(nn, rs, sqr, ds, sds, ab, max_scale, scale_bits, offset_bits);
+        if (fic_better(sc.R, (unsigned long long)c, best.R, best.seq)) {
+            best.R = sc.R; best.seq = c; best.s = sc.s; best.o = sc.o; best.qs = sc.qs; best.qo = sc.qo;
+            best.di = di; best.dj = dj; best.orient = d_orient; best.rot = d_rot;
+            atomicMin(&s_bound[warp], (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
+        }
+    }
+    __syncwarp();
+    // first strict minimum in scan order over the lanes (te_block_reduce's rule)
+    double R = best.R;
+    unsigned long long seq = best.seq;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const double oR = __shfl_xor_sync(0xffffffffu, R, off);
+        const unsigned long long oS = __shfl_xor_sync(0xffffffffu, seq, off);
+        if (fic_better(oR, oS, R, seq)) { R = oR; seq = oS; }
+    }
+    int32_t* rec6 = rec + 6 * (size_t)q;
+    double* vals3 = vals + 3 * (size_t)q;
+    if (seq == ~0ull) {
+        if (lane == 0) {
+            for (int k = 0; k < 6; ++k) rec6[k] = 0;
+            vals3[0] = 0.0; vals3[1] = 0.0;
+            vals3[2] = __longlong_as_double(0x7ff0000000000000ll);
+        }
+    } else if (best.seq == seq) {   // seq values are unique per range
+        rec6[0] = best.di; rec6[1] = best.dj; rec6[2] = best.orient; rec6[3] = best.rot; rec6[4] = best.qs; rec6[5] = best.qo;
+        vals3[0] = best.s; vals3[1] = best.o; vals3[2] = best.R;
+    }
+}
+
 // ---- HV domain search (hvv2/encoder.py:97-126) -----------------------------------------------------
 // 2x2-pooled image at every pixel offset: Dp[y][x] = (img[y][x] + img[y][x+1] + img[y+1][x] + img[y+1][x+1]) * 0.25,
 // exact in float32 (the reference's average_subsample of a domain block reads every second entry of it).
@@ -1253,10 +1363,18 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
                 }
 #endif
             }
-            qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, 1 << e, pool, full, nmodes,
-                                                       max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
-                                                       h->t_part.as<double>(), need);
-            FIC_CHECK_LAUNCH(h, "qt_search_kernel");
+            // (a warp per range while the class lists are short -- 256 domains per class on average; beyond that a CTA per range)
+            if (!full && !need && (1 << e) * (1 << e) <= 64 && geom[pk].cnt <= (size_t)72 * 256) {
+                qt_search_warp_kernel<<<(n + QT_WARP_RANGES - 1) / QT_WARP_RANGES, QT_WARP_RANGES * 32, 0, st>>>(
+                    d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, n, 1 << e, pool, nmodes, max_scale, scale_bits, offset_bits,
+                    h->t_res.as<int32_t>(), h->t_part.as<double>());
+                FIC_CHECK_LAUNCH(h, "qt_search_warp_kernel");
+            } else {
+                qt_search_kernel<<<n, TE_THREADS, 0, st>>>(d_img, h->t_hvpool.as<float>(), W, I1, I2, queue, 1 << e, pool, full, nmodes,
+                                                           max_scale, scale_bits, offset_bits, h->t_res.as<int32_t>(),
+                                                           h->t_part.as<double>(), need);
+                FIC_CHECK_LAUNCH(h, "qt_search_kernel");
+            }
         }
         qt_decide_kernel<<<(n + 127) / 128, 128, 0, st>>>(queue, n, e, mode, tol, min_exp, h->t_res.as<int32_t>(), h->t_part.as<double>(),
                                                           d_nodes, d_counts, next_queue, (int)node_cap, next_cap);
