@@ -58,30 +58,48 @@ __global__ void integral_rows_kernel(const uint8_t* __restrict__ img, int H, int
         cq += __shfl_sync(0xffffffffu, q, 31);
     }
 }
-// columns: one thread per column (coalesced across the warp), sixteen rows loaded before any is stored so that the
-// loads are not serialised behind the in-place stores
-__global__ void integral_cols_kernel(int H, int W, long long* __restrict__ I1, long long* __restrict__ I2)
+// columns: a CTA takes 32 columns, its sixteen warps sixteen bands of rows: every thread sums its band of its column,
+// the band totals are scanned in shared memory, then the band is walked again (L1/L2) with the running sum and stored.
+// (One thread per column over all rows was 56 us at 512x512 -- 513 threads on the whole GPU.)
+#define INTEGRAL_BANDS 16
+__global__ void __launch_bounds__(32 * INTEGRAL_BANDS)
+integral_cols_kernel(int H, int W, long long* __restrict__ I1, long long* __restrict__ I2)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    if (x > W) return;
+    __shared__ long long tot1[INTEGRAL_BANDS][32], tot2[INTEGRAL_BANDS][32];
+    const int lane = threadIdx.x & 31, band = threadIdx.x >> 5;
+    const int x = blockIdx.x * 32 + lane;
     const int W1 = W + 1;
-    constexpr int U = 16;
+    const int per = (H + INTEGRAL_BANDS - 1) / INTEGRAL_BANDS;
+    const int y0 = 1 + band * per, y1 = y0 + per <= H + 1 ? y0 + per : H + 1;    // rows [y0, y1)
+    const bool live = x <= W;
     long long s = 0, q = 0;
-    for (int y0 = 1; y0 <= H; y0 += U) {
-        long long a[U], b[U];
+    if (live)
+        for (int y = y0; y < y1; ++y) {
+            s += I1[(size_t)y * W1 + x];
+            q += I2[(size_t)y * W1 + x];
+        }
+    tot1[band][lane] = s;
+    tot2[band][lane] = q;
+    __syncthreads();
+    s = 0; q = 0;
+    for (int b = 0; b < band; ++b) { s += tot1[b][lane]; q += tot2[b][lane]; }
+    if (!live) return;
+    constexpr int U = 8;     // rows loaded before any is stored, so that the loads are not serialised behind the in-place stores
+    for (int yb = y0; yb < y1; yb += U) {
+        long long a[U], c[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const bool in = y0 + u <= H;
-            a[u] = in ? I1[(size_t)(y0 + u) * W1 + x] : 0;
-            b[u] = in ? I2[(size_t)(y0 + u) * W1 + x] : 0;
+            const bool in = yb + u < y1;
+            a[u] = in ? I1[(size_t)(yb + u) * W1 + x] : 0;
+            c[u] = in ? I2[(size_t)(yb + u) * W1 + x] : 0;
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (y0 + u <= H) {
+            if (yb + u < y1) {
                 s += a[u];
-                q += b[u];
-                I1[(size_t)(y0 + u) * W1 + x] = s;
-                I2[(size_t)(y0 + u) * W1 + x] = q;
+                q += c[u];
+                I1[(size_t)(yb + u) * W1 + x] = s;
+                I2[(size_t)(yb + u) * W1 + x] = q;
             }
         }
     }
@@ -98,7 +116,7 @@ static int build_integrals(fic_handle* h, const uint8_t* d_img, int H, int W, cu
     FIC_TRY(h->t_int2.reserve(n * sizeof(long long)));
     integral_rows_kernel<<<((H + 1) * 32 + 127) / 128, 128, 0, st>>>(d_img, H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
     FIC_CHECK_LAUNCH(h, "integral_rows_kernel");
-    integral_cols_kernel<<<(W + 1 + 31) / 32, 32, 0, st>>>(H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
+    integral_cols_kernel<<<(W + 1 + 31) / 32, 32 * INTEGRAL_BANDS, 0, st>>>(H, W, h->t_int1.as<long long>(), h->t_int2.as<long long>());
     FIC_CHECK_LAUNCH(h, "integral_cols_kernel");
     return FIC_OK;
 }
@@ -1153,6 +1171,104 @@ static void qt_roots(std::vector<QtNodeDev>& nodes, int si, int sj, int width, i
     if (side < height) qt_roots(nodes, si + side, sj, side, height - side);
 }
 
+// The preorder stream of include/fic.h from the node table, on the device (one CTA; the host used to walk the table with a
+// stack, a fifth of a default 512x512 encode).  A node's children are four consecutive nodes one size exponent below it, so
+// the nodes are first bucketed by exponent (counting sort), subtree sizes are added up from the smallest exponent to the
+// largest, preorder positions handed down from the largest to the smallest -- roots one after the other, a child behind
+// its parent and its elder siblings' subtrees -- and every node writes its record at its position.
+#define QT_EMIT_EXPS 32
+#define QT_EMIT_ILP 4          /* nodes a thread works on at once: the kernel is one CTA and nothing but dependent loads */
+__global__ void __launch_bounds__(1024)
+qt_emit_kernel(const QtNodeDev* __restrict__ nodes, int n_nodes, int n_root, int32_t* __restrict__ order /*[n]*/,
+               int32_t* __restrict__ sz /*[n]*/, int32_t* __restrict__ pre /*[n]*/, int32_t* __restrict__ out_nodes /*[n][8]*/,
+               double* __restrict__ out_vals /*[n][3]*/)
+{
+    __shared__ int cnt[QT_EMIT_EXPS], first[QT_EMIT_EXPS + 1], fill[QT_EMIT_EXPS];
+    constexpr int U = QT_EMIT_ILP, STEP = 1024 * QT_EMIT_ILP;
+    const int tid = threadIdx.x;
+    if (tid < QT_EMIT_EXPS) cnt[tid] = 0;
+    __syncthreads();
+    for (int base = tid; base < n_nodes; base += STEP) {
+        int e[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) e[u] = base + u * 1024 < n_nodes ? nodes[base + u * 1024].exp & (QT_EMIT_EXPS - 1) : -1;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (e[u] >= 0) atomicAdd(&cnt[e[u]], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0;
+        for (int e = 0; e < QT_EMIT_EXPS; ++e) { first[e] = acc; fill[e] = acc; acc += cnt[e]; }
+        first[QT_EMIT_EXPS] = acc;
+    }
+    __syncthreads();
+    for (int base = tid; base < n_nodes; base += STEP) {
+        int e[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) e[u] = base + u * 1024 < n_nodes ? nodes[base + u * 1024].exp & (QT_EMIT_EXPS - 1) : -1;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (e[u] >= 0) order[atomicAdd(&fill[e[u]], 1)] = base + u * 1024;
+    }
+    __syncthreads();
+    for (int e = 0; e < QT_EMIT_EXPS; ++e) {          // subtree sizes, small blocks first
+        const int k1 = first[e + 1];
+        if (first[e] == k1) continue;                  // (uniform: no barrier needed for an empty exponent)
+        for (int base = first[e] + tid; base < k1; base += STEP) {
+            int id[U], kind[U], c0[U], s[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) id[u] = base + u * 1024 < k1 ? order[base + u * 1024] : -1;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                kind[u] = id[u] >= 0 ? nodes[id[u]].kind : 1;
+                c0[u] = id[u] >= 0 ? nodes[id[u]].child0 : 0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) s[u] = kind[u] == 0 ? 1 + sz[c0[u]] + sz[c0[u] + 1] + sz[c0[u] + 2] + sz[c0[u] + 3] : 1;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (id[u] >= 0) sz[id[u]] = s[u];
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        int acc = 0;
+        for (int r = 0; r < n_root; ++r) { pre[r] = acc; acc += sz[r]; }
+    }
+    __syncthreads();
+    for (int e = QT_EMIT_EXPS - 1; e >= 0; --e) {     // positions, large blocks first
+        const int k1 = first[e + 1];
+        if (first[e] == k1) continue;
+        for (int base = first[e] + tid; base < k1; base += STEP) {
+            int id[U], at[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) id[u] = base + u * 1024 < k1 ? order[base + u * 1024] : -1;
+#pragma unroll
+            for (int u = 0; u < U; ++u) at[u] = id[u] >= 0 ? pre[id[u]] : 0;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (id[u] < 0) continue;
+                const QtNodeDev nd = nodes[id[u]];
+                int32_t* o = out_nodes + 8 * (size_t)at[u];
+                double* v = out_vals + 3 * (size_t)at[u];
+                const bool leaf = nd.kind == 1;
+                reinterpret_cast<int4*>(o)[0] = make_int4(nd.kind, leaf ? nd.rec[0] : 0, leaf ? nd.rec[1] : 0, leaf ? nd.rec[2] : 0);
+                reinterpret_cast<int4*>(o)[1] = make_int4(leaf ? nd.rec[3] : 0, leaf ? nd.rec[4] : 0, leaf ? nd.rec[5] : 0, nd.exp);
+                v[0] = leaf ? nd.vals[0] : 0.0; v[1] = leaf ? nd.vals[1] : 0.0; v[2] = leaf ? nd.vals[2] : 0.0;
+                if (nd.kind == 0) {
+                    const int s0 = sz[nd.child0], s1 = sz[nd.child0 + 1], s2 = sz[nd.child0 + 2];
+                    pre[nd.child0] = at[u] + 1;
+                    pre[nd.child0 + 1] = at[u] + 1 + s0;
+                    pre[nd.child0 + 2] = at[u] + 1 + s0 + s1;
+                    pre[nd.child0 + 3] = at[u] + 1 + s0 + s1 + s2;
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_bits, int offset_bits, double max_scale,
                    int full, int onlypos, int min_side, int max_side, double tol, int hstep_in, int vstep_in,
                    int32_t* out_nodes, double* out_vals, int cap, int32_t* n_roots, cudaStream_t st)
@@ -1396,28 +1512,19 @@ int qt_encode_impl(fic_handle* h, const uint8_t* d_img, int H, int W, int scale_
         FIC_TRY(fic_sync(h, st));
     }
     const int n_nodes = h_counts[0];
-    nodes.resize(n_nodes);
-    FIC_TRY(fic_copy_out(h, nodes.data(), d_nodes, (size_t)n_nodes * sizeof(QtNodeDev), false, st));
+    if (n_nodes > cap) { fic_set_error("fic_qt_encode: node capacity %d too small", cap); return FIC_ECAP; }
+    FIC_REQUIRE(top < QT_EMIT_EXPS, "fic_qt_encode: image too large");
+    FIC_TRY(h->d_in_a.reserve((size_t)n_nodes * 3 * sizeof(int32_t) + 64));
+    FIC_TRY(h->d_out_a.reserve((size_t)n_nodes * 8 * sizeof(int32_t) + 64));
+    FIC_TRY(h->d_out_b.reserve((size_t)n_nodes * 3 * sizeof(double) + 64));
+    int32_t* d_order = h->d_in_a.as<int32_t>();
+    qt_emit_kernel<<<1, 1024, 0, st>>>(d_nodes, n_nodes, n_root, d_order, d_order + n_nodes, d_order + 2 * (size_t)n_nodes,
+                                       h->d_out_a.as<int32_t>(), h->d_out_b.as<double>());
+    FIC_CHECK_LAUNCH(h, "qt_emit_kernel");
+    FIC_TRY(fic_copy_out(h, out_nodes, h->d_out_a.p, (size_t)n_nodes * 8 * sizeof(int32_t), false, st));
+    FIC_TRY(fic_copy_out(h, out_vals, h->d_out_b.p, (size_t)n_nodes * 3 * sizeof(double), false, st));
     FIC_TRY(fic_sync(h, st));
-    int count = 0;
-    std::vector<int> stack;
-    for (int r = 0; r < n_root; ++r) {
-        stack.push_back(r);
-        while (!stack.empty()) {
-            int id = stack.back();
-            stack.pop_back();
-            const QtNodeDev& nd = nodes[id];
-            if (count >= cap) { fic_set_error("fic_qt_encode: node capacity %d too small", cap); return FIC_ECAP; }
-            int32_t* o = out_nodes + 8 * (size_t)count;
-            double* v = out_vals + 3 * (size_t)count;
-            o[0] = nd.kind; o[7] = nd.exp;
-            for (int k = 0; k < 6; ++k) o[1 + k] = nd.kind == 1 ? nd.rec[k] : 0;
-            for (int k = 0; k < 3; ++k) v[k] = nd.kind == 1 ? nd.vals[k] : 0.0;
-            ++count;
-            if (nd.kind == 0)
-                for (int c = 3; c >= 0; --c) stack.push_back(nd.child0 + c);
-        }
-    }
+    const int count = n_nodes;
     if (n_roots) *n_roots = (int32_t)n_root;
     return count;
 }
