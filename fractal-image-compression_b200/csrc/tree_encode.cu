@@ -1552,7 +1552,7 @@ __host__ __device__ __forceinline__ int hv_flags(int w, int hgt, int min_w, int 
 }
 
 // One warp per rectangle of the level: merges the chunk winners of its search (hv_pick_kernel's rule), finds the split
-// (hv_split_kernel's rule) and decides.  counts: [0] nodes, [1 + parity] size of the next level (the other one is the
+// (the biased-difference rule, hvv2/encoder.py:45-63) and decides.  counts: [0] nodes, [1 + parity] size of the next level (the other one is the
 // current level's and is cleared here for the level after next), [3] error flag (1 = a rectangle that must be split cannot
 // be, 2 = capacity), [4 + parity] number of rectangles of the next level that will be searched.
 // Level arrays (level_cap entries each): rects[4], ids, flags, sidx (index into the search results, -1 = not searched),
