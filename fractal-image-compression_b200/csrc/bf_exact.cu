@@ -392,8 +392,9 @@ template <int MODE>
 __global__ void __launch_bounds__(BF_THREADS)
 bf_scan_generic_kernel(const uint8_t* __restrict__ img, int H, int W, int R, int si, int sj, int npi, int npj,
                        int range_begin, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
-                       double* __restrict__ out_R)
+                       double* __restrict__ out_R, const int32_t* __restrict__ need = nullptr /* optional: only slots with need[slot] != 0 */)
 {
+    if (need && !need[blockIdx.x]) return;
     __shared__ BestRec red[BF_THREADS / 32];
     __shared__ double red_s[BF_THREADS / 32], red_o[BF_THREADS / 32];
     const int tid = threadIdx.x;
@@ -609,6 +610,24 @@ int bf_exact_generic(fic_handle* h, const uint8_t* d_img, int H, int W, int rang
     else
         bf_scan_generic_kernel<FIC_BF_MODE_NUMPY><<<n_ranges, BF_THREADS, 0, st>>>(d_img, H, W, range, si, sj, npi, npj,
                                                                                    range_begin, d_idx, d_so, d_R);
+    FIC_CHECK_LAUNCH(h, "bf_scan_generic_kernel");
+    return FIC_OK;
+}
+
+// the same scan for the ranges flagged in d_need only (the 4x4 tensor-core path hands back what it cannot decide)
+int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
+                            int range_begin, int n_ranges, const int32_t* d_need, int32_t* d_idx, double* d_so, double* d_R,
+                            cudaStream_t st)
+{
+    if (n_ranges <= 0) return FIC_OK;
+    const int D = 2 * range;
+    int npi = H - D > 0 ? ceil_div(H - D, si) : 0, npj = W - D > 0 ? ceil_div(W - D, sj) : 0;
+    if (mode == FIC_BF_MODE_JIT)
+        bf_scan_generic_kernel<FIC_BF_MODE_JIT><<<n_ranges, BF_THREADS, 0, st>>>(d_img, H, W, range, si, sj, npi, npj, range_begin, d_idx,
+                                                                                 d_so, d_R, d_need);
+    else
+        bf_scan_generic_kernel<FIC_BF_MODE_NUMPY><<<n_ranges, BF_THREADS, 0, st>>>(d_img, H, W, range, si, sj, npi, npj, range_begin,
+                                                                                   d_idx, d_so, d_R, d_need);
     FIC_CHECK_LAUNCH(h, "bf_scan_generic_kernel");
     return FIC_OK;
 }

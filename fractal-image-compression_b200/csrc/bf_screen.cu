@@ -250,6 +250,10 @@ struct ScreenParams {
     const double* den;       // [NP] N * sds - ds^2 (8x8 blocks: the smallest of the eight)
     double max_scale;
     int scale_bits, offset_bits, nmodes, seed_pass;
+    // MODE 8 (brute force, 4x4 ranges): survivors are rescored from the pixels
+    const uint8_t* img;      // the image, row pitch img_W
+    const uint16_t* boxsum;  // 2x2 cell sums at every pixel offset, (H-1) x (W-1)
+    int img_W, lat_si, lat_sj, lat_npj;      // lattice of domain positions: (q / lat_npj * lat_si, q % lat_npj * lat_sj)
 };
 
 // j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
@@ -390,6 +394,63 @@ __device__ __noinline__ void qt_queue_flush(const QtQueue* q, const ScreenParams
     __syncwarp();
 }
 
+// ---- brute force with 4x4 ranges (MODE 8) -----------------------------------------------------------------------------
+// Sixteen pixels per block: every float32 sum of the reference (jit_bfencoder.py:40-62) is exact -- sum d^2 needs 24 bits,
+// sum d r 22 -- so the integer sums ARE the reference's sums and, as in the quadtree pass, the GEMM's accumulator gives the
+// exact dot product.  All eight isometries of a (range, domain) pair are candidates (eight columns per range, one
+// accumulator each); the epilogue tests the scorer's lower bound against the best score of the range and queues what it
+// cannot drop as (position, range, isometry) -- four bytes; the survivor's sums are rebuilt from the pixels when it is scored.
+constexpr int BF4_QCAP = QUEUE_BYTES / 4;
+static_assert(BF4_QCAP >= 4 * 8 * 32 + 32, "queue of the 4x4 brute-force pass too small");   // a 32-column chunk adds at most 1024 entries
+struct Bf4Queue {
+    uint32_t e[BF4_QCAP];     // position << 7 | range of the warp's 16 << 3 | isometry
+};
+
+// score of range `rc` (origin in tw0 / tw1) against the domain at lattice position q under isometry t, the reference's way
+__device__ __forceinline__ BfScore bf4_score_pair(const ScreenParams& p, const QtcRange& rc, int q, int t)
+{
+    const int di = (q / p.lat_npj) * p.lat_si, dj = (q % p.lat_npj) * p.lat_sj;
+    const int BW = p.img_W - 1;
+    const uint8_t* rp = p.img + (size_t)rc.tw0 * p.img_W + rc.tw1;
+    const uint16_t* dp = p.boxsum + (size_t)di * BW + dj;
+    int sd = 0, sq = 0, ab = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int a, b;
+            fic_iso_bf(t >> 2, t & 3, 4, i, j, a, b);
+            const int d4 = dp[(size_t)(2 * a) * BW + 2 * b];
+            sd += d4;
+            sq += d4 * d4;
+            ab += d4 * (int)rp[(size_t)i * p.img_W + j];
+        }
+    const float ds = __fmul_rn((float)sd, 0.25f);
+    return fic_bfjit_score(16.0, 0.0625, (double)rc.rs, (double)rc.sqr, (double)ds, (double)__fmul_rn((float)sq, 0.0625f),
+                           (double)__fmul_rn(ds, ds), (double)__fmul_rn((float)ab, 0.25f));
+}
+
+__device__ __noinline__ void bf4_queue_flush(const Bf4Queue* q, const ScreenParams& p, int slot0, int lane, uint32_t n)
+{
+    __syncwarp();
+    for (uint32_t k = lane; k < n; k += 32) {
+        const uint32_t en = q->e[k];
+        const int slot = slot0 + (int)((en >> 3) & 15u), cand = (int)(en >> 7), t = (int)(en & 7u);
+        const QtcRange rc = p.rngc[slot];
+        if (!(rc.ok & 1)) continue;
+        const BfScore sc = bf4_score_pair(p, rc, cand, t);
+        const double B = __longlong_as_double((long long)__ldcg(&p.bound[slot]));
+        if (sc.R <= B && sc.R < __longlong_as_double(0x7ff0000000000000ll)) {
+            if (sc.R < B) atomicMin(&p.bound[slot], (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0));
+            if (!p.seed_pass) {
+                const uint32_t at = atomicAdd(&p.cnt[slot], 1u);
+                if (at < p.cap) p.list[(size_t)slot * p.cap + at] = (uint32_t)cand * 8u + (uint32_t)t;
+            }
+        }
+    }
+    __syncwarp();
+}
+
 template <bool APPEND>
 __device__ __forceinline__ void screen_chunk(const uint32_t (&v)[32], const float* theta, const ScreenParams& p, int slot0,
                                              int my_cand, WarpQueue* q, uint32_t& qn, int lane)
@@ -491,8 +552,8 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_elig = *p.n_elig;
-    const int grp_off = MODE == 7 ? p.grp_begin : 0;            // the quadtree modes name their column groups
-    const int n_groups = MODE == 7 ? p.grp_count : (n_elig + 31) / 32;
+    const int grp_off = MODE == 7 || MODE == 8 ? p.grp_begin : 0;            // the quadtree modes name their column groups
+    const int n_groups = MODE == 7 || MODE == 8 ? p.grp_count : (n_elig + 31) / 32;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -604,9 +665,10 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             grp += grp_off;
             if (MODE == 0 && qn) { queue_flush(queue, p, lane, qn); qn = 0; }
             if (MODE == 7 && qn) { qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, qt_slot0, lane, qn); qn = 0; }   // (entries name ranges relative to their unit)
+            if (MODE == 8 && qn) { bf4_queue_flush(reinterpret_cast<Bf4Queue*>(queue), p, qt_slot0, lane, qn); qn = 0; }
             // this warp's (tau_A, tau_B) pairs live in a private slice of shared memory; broadcast reads, no bank conflicts
             __syncwarp();
-            if (MODE != 7 && lane < 16) {
+            if (MODE != 7 && MODE != 8 && lane < 16) {
                 const float2 tt = p.tau[grp * 32 + part * 16 + lane];
                 my_tau[lane] = tt.x;
                 my_tau[16 + lane] = tt.y;
@@ -621,6 +683,11 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 my_rho = (float)rc.rho;
                 my_slack = rc.ok ? rc.slack : -1.0;
             }
+            if (MODE == 8) {   // sixteen ranges of eight columns: lanes r and r + 16 keep range r
+                const QtcRange rc = p.rngc[slot0 + (lane & 15)];
+                my_rho = (float)rc.rho;
+                my_slack = (rc.ok & 1) ? rc.slack : -1.0;
+            }
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
             // tile index of j without a division per tile: t = (j + j / (r_prev - 1) + 1) * m_cur, advanced by 2
@@ -633,7 +700,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             // +-1/h_c of this lane's candidate, fetched one tile ahead; sign = conditioning class; +inf (threshold never
             // met) for the padding rows of the last tile
             const float hk_pad = __int_as_float(0x7f800000);
-            float hq_next = (MODE != 7 && j < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+            float hq_next = (MODE != 7 && MODE != 8 && j < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
             // the sixteen tau of the next tile (class picked by the sign of its hq) are fetched at the END of the current
             // tile, when both chunk buffers are dead, so the shared-memory latency is paid under the index arithmetic
             float4 tq0, tq1, tq2, tq3;
@@ -656,7 +723,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     cand += (2 + wraps) * p.m_cur * BM;
                 }
                 const float hq = hq_next;
-                hq_next = (MODE != 7 && j + 2 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
+                hq_next = (MODE != 7 && MODE != 8 && j + 2 < j1 && cand < p.NP) ? p.hk[cand].x : hk_pad;
                 const int lane = my_cand & 31;            // shadows the outer lane on purpose
                 const uint32_t lane0 = lane == 0;
                 if (MODE == 5) {
@@ -694,6 +761,75 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     if (lane0) mbar_arrive(my_tempty);
                     rank4(va, 2);
                     rank4(vb, 3);
+                    aph ^= 1;
+                    continue;
+                }
+                if (MODE == 8) {
+                    // Brute force, 4x4 ranges: the eight accumulators of a (candidate, range) pair are the exact dot products
+                    // of the eight isometries.  Same test as the quadtree pass (integer numerator N * X - rho * eps, float32
+                    // comparison inside the 1e-6 the right-hand side is shrunk by), here for every column.  Masks first, for the
+                    // four ranges of a 32-column chunk; the queue is filled from the masks afterwards, so that no accumulator
+                    // is live across the (out of line) flush.
+                    const bool have = my_cand < p.NP;
+                    unsigned sdc = 0;
+                    float denf = 0.f;            // 0: this candidate is never dropped (degenerate block)
+                    if (have) {
+                        sdc = p.sd4[my_cand];
+                        const double den = p.den[my_cand];
+                        denf = den > 0.0 ? (float)den : 0.f;
+                    }
+                    const float neps = -(float)((int)sdc - KT * (int)((sdc + (unsigned)(KT / 2)) / (unsigned)KT));
+                    float my_rhs;
+                    {
+                        const double B = __longlong_as_double((long long)__ldcg(&p.bound[slot0 + (lane & 15)]));
+                        const double rhs_g = DM(DS(my_slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
+                        my_rhs = my_slack < 0.0 ? __int_as_float(0x7f800000) : (rhs_g > 0.0 ? (float)rhs_g : -1.0f);
+                    }
+                    Bf4Queue* qq = reinterpret_cast<Bf4Queue*>(queue);
+                    const unsigned lt = (1u << lane) - 1u;
+                    const uint32_t ent_cand = (uint32_t)my_cand << 7;
+                    mbar_wait(my_tfull, aph, p.err_flag, 6);
+                    tcgen05_fence_after();
+#pragma unroll 1
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        unsigned m8[4];
+                        {
+                            uint32_t v[32];
+                            tmem_ld32(taddr0 + 32 * c4, v);
+                            tmem_ld_wait(v);
+                            if (c4 == 3) {     // the whole slice has been read: hand the accumulator back
+                                tcgen05_fence_before();
+                                __syncwarp();
+                                if (lane0) mbar_arrive(my_tempty);
+                            }
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                const int r = c4 * 4 + g;
+                                const float rhs = __fmul_rn(__shfl_sync(0xffffffffu, my_rhs, r), denf);
+                                const float nre = __fmul_rn(__shfl_sync(0xffffffffu, my_rho, r), neps);
+                                unsigned m = 0u;
+#pragma unroll
+                                for (int t = 0; t < 8; ++t) {
+                                    const float na = fmaf((float)KT, __uint_as_float(v[g * 8 + t]), nre);
+                                    m |= (__fmul_rn(na, na) < rhs ? 0u : 1u) << t;
+                                }
+                                m8[g] = have ? m : 0u;
+                            }
+                        }
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            if (!__any_sync(0xffffffffu, m8[g] != 0u)) continue;
+                            const uint32_t ent = ent_cand | (uint32_t)((c4 * 4 + g) << 3);
+#pragma unroll
+                            for (int t = 0; t < 8; ++t) {
+                                const bool s1 = (m8[g] >> t) & 1u;
+                                const unsigned mb = __ballot_sync(0xffffffffu, s1);
+                                if (s1) qq->e[qn + __popc(mb & lt)] = ent | (uint32_t)t;
+                                qn += __popc(mb);
+                            }
+                        }
+                        if (qn > (uint32_t)(BF4_QCAP - 4 * 8 * 32)) { bf4_queue_flush(qq, p, slot0, lane, qn); qn = 0; }
+                    }
                     aph ^= 1;
                     continue;
                 }
@@ -836,6 +972,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
         if (MODE == 0 && qn) queue_flush(queue, p, lane, qn);
         if (MODE == 7 && qn) qt_queue_flush<KT>(reinterpret_cast<QtQueue*>(queue), p, qt_slot0, lane, qn);
+        if (MODE == 8 && qn) bf4_queue_flush(reinterpret_cast<Bf4Queue*>(queue), p, qt_slot0, lane, qn);
         }
     tcgen05_fence_before();
     __syncthreads();
@@ -1698,6 +1835,140 @@ qt_tcpick_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P
     }
 }
 
+// ---- brute force, 4x4 ranges: pool, range operand, winners ------------------------------------------------------------
+// pool row = the pooled 4x4 block (cell sums, centred by their rounded mean) in plain row-major order; the isometries sit on
+// the range side.  Lattice position q = (q / npj * si, q % npj * sj), jit_bfencoder.py:27-30.
+__global__ void bf4_pool_kernel(const uint16_t* __restrict__ P, int W, int si, int sj, int npj, int NP, __half* __restrict__ poolA,
+                                uint32_t* __restrict__ sd4, uint32_t* __restrict__ sq4, double* __restrict__ den)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= NP) return;
+    const int BW = W - 1;
+    const uint16_t* dp = P + (size_t)(q / npj) * si * BW + (q % npj) * sj;
+    int v[16], s = 0, s2 = 0;
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int x = dp[(size_t)(2 * a) * BW + 2 * b];
+            v[a * 4 + b] = x;
+            s += x;
+            s2 += x * x;
+        }
+    const int m = (s + 8) / 16;
+    uint4* dst = reinterpret_cast<uint4*>(poolA + (size_t)q * 16);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        __half2 h0 = __halves2half2(__int2half_rn(v[8 * h + 0] - m), __int2half_rn(v[8 * h + 1] - m));
+        __half2 h1 = __halves2half2(__int2half_rn(v[8 * h + 2] - m), __int2half_rn(v[8 * h + 3] - m));
+        __half2 h2 = __halves2half2(__int2half_rn(v[8 * h + 4] - m), __int2half_rn(v[8 * h + 5] - m));
+        __half2 h3 = __halves2half2(__int2half_rn(v[8 * h + 6] - m), __int2half_rn(v[8 * h + 7] - m));
+        uint4 o;
+        o.x = *reinterpret_cast<uint32_t*>(&h0);
+        o.y = *reinterpret_cast<uint32_t*>(&h1);
+        o.z = *reinterpret_cast<uint32_t*>(&h2);
+        o.w = *reinterpret_cast<uint32_t*>(&h3);
+        dst[h] = o;
+    }
+    sd4[q] = (uint32_t)s;
+    sq4[q] = (uint32_t)s2;
+    // n sum(d^2) - (sum d)^2 with d = cell / 4: exact in float64
+    den[q] = DS((double)s2, DM(DM((double)s, (double)s), 0.0625));
+}
+
+// one warp per range slot: sums, the record of the bound test (range origin in tw0 / tw1), eight isometric copies of the
+// centred block as operand columns -- column t holds range pixel k at the place isometry t reads for it (fic_iso_bf)
+__global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, int slots_pad,
+                                __half* __restrict__ rngB, QtcRange* __restrict__ rngc, unsigned long long* __restrict__ bound,
+                                uint32_t* __restrict__ cnt, int* __restrict__ ctrl, int32_t* __restrict__ need_exact)
+{
+    const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (slot >= slots_pad) return;
+    if (slot == 0 && lane < 16) ctrl[lane] = lane == 0 ? n_ranges : 0;
+    if (lane == 0) bound[slot] = 0x7ff0000000000000ull;
+    if (slot >= n_ranges) {
+        for (int e = lane; e < 8 * 16; e += 32) rngB[(size_t)slot * 128 + e] = __float2half_rn(0.f);
+        if (lane == 0) {
+            QtcRange rc;
+            rc.rho = 0; rc.ok = 0; rc.tw0 = rc.tw1 = 0u; rc.slack = 0.0; rc.rs = rc.sqr = 0.f;
+            rngc[slot] = rc;
+        }
+        return;
+    }
+    const int ridx = range_begin + slot, rw = W / 4;
+    const int si = (ridx / rw) * 4, sj = (ridx % rw) * 4;
+    const int k = lane & 15;
+    const int px = img[(size_t)(si + k / 4) * W + sj + k % 4];
+    int sm = lane < 16 ? px : 0, q2 = lane < 16 ? px * px : 0;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        sm += __shfl_xor_sync(0xffffffffu, sm, off);
+        q2 += __shfl_xor_sync(0xffffffffu, q2, off);
+    }
+    const int m = (sm + 8) / 16;
+#pragma unroll
+    for (int tt = 0; tt < 4; ++tt) {        // lanes 0-15 write isometries 0..3, lanes 16-31 isometries 4..7
+        const int t = tt + (lane >> 4) * 4;
+        int a, b;
+        fic_iso_bf(t >> 2, t & 3, 4, k / 4, k % 4, a, b);
+        rngB[((size_t)slot * 8 + t) * 16 + a * 4 + b] = __int2half_rn(px - m);
+    }
+    if (lane == 0) {
+        QtcRange rc;
+        const bool flat = 16 * q2 - sm * sm == 0;       // constant block: every candidate scores alike up to rounding -> exact scan
+        rc.rho = sm - 16 * m;
+        rc.ok = flat ? 0 : 1;
+        rc.tw0 = (uint32_t)si; rc.tw1 = (uint32_t)sj;
+        rc.rs = (float)sm; rc.sqr = (float)q2;
+        rc.slack = DS((double)q2, DM(DM((double)sm, (double)sm), 0.0625));
+        rngc[slot] = rc;
+        cnt[slot] = 0;
+        need_exact[slot] = flat ? 1 : 0;
+    }
+}
+
+// one warp per range: the first minimum in scan order (position * 8 + isometry) among the listed candidates
+__global__ void bf4_pick_kernel(const ScreenParams p, int n_ranges, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                                double* __restrict__ out_R, int32_t* __restrict__ need_exact)
+{
+    const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (slot >= n_ranges) return;
+    const QtcRange rc = p.rngc[slot];
+    if (!(rc.ok & 1)) return;
+    const uint32_t n = p.cnt[slot];
+    if (n > p.cap || n == 0) {
+        if (lane == 0) need_exact[slot] = 1;
+        return;
+    }
+    double bR = __longlong_as_double(0x7ff0000000000000ll), bs = 0.0, bo = 0.0;
+    unsigned long long bseq = ~0ull;
+    for (uint32_t e = lane; e < n; e += 32) {
+        const uint32_t ent = p.list[(size_t)slot * p.cap + e];
+        const BfScore sc = bf4_score_pair(p, rc, (int)(ent >> 3), (int)(ent & 7u));
+        if (fic_better(sc.R, (unsigned long long)ent, bR, bseq)) { bR = sc.R; bseq = ent; bs = sc.s; bo = sc.o; }
+    }
+    double wR = bR;
+    unsigned long long ws = bseq;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const double oR = __shfl_xor_sync(0xffffffffu, wR, off);
+        const unsigned long long oS = __shfl_xor_sync(0xffffffffu, ws, off);
+        if (fic_better(oR, oS, wR, ws)) { wR = oR; ws = oS; }
+    }
+    if (ws == ~0ull) {
+        if (lane == 0) need_exact[slot] = 1;
+    } else if (bseq == ws) {      // entries are unique: one lane
+        const int q = (int)(ws >> 3), t = (int)(ws & 7ull);
+        out_idx[4 * (size_t)slot + 0] = (q / p.lat_npj) * p.lat_si;
+        out_idx[4 * (size_t)slot + 1] = (q % p.lat_npj) * p.lat_sj;
+        out_idx[4 * (size_t)slot + 2] = t >> 2;
+        out_idx[4 * (size_t)slot + 3] = t & 3;
+        out_so[2 * (size_t)slot] = bs;
+        out_so[2 * (size_t)slot + 1] = bo;
+        if (out_R) out_R[slot] = bR;
+    }
+}
+
 }  // namespace
 
 bool bf_screen_applicable(int H, int W)
@@ -2057,4 +2328,95 @@ int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const
                                     d_vals, d_need_exact, hs, vs, d_pool_offsets, d_pool_rows, st);
     return qt_tc_search_impl<4>(h, d_img, H, W, d_queue, n_ranges, d_rcls, d_dcls, nmodes, max_scale, scale_bits, offset_bits, d_rec,
                                 d_vals, d_need_exact, hs, vs, d_pool_offsets, d_pool_rows, st);
+}
+
+// ---- brute force with 4x4 ranges on the tensor cores (JitedBruteForceEncoder semantics) --------------------------------
+int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
+                            int range_begin, int n_ranges, const int32_t* d_need, int32_t* d_idx, double* d_so, double* d_R,
+                            cudaStream_t st);
+int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_stats, cudaStream_t st);
+
+bool bf4_tc_applicable(int H, int W, int si, int sj, int mode)
+{
+    if (mode != FIC_BF_MODE_JIT || H < 16 || W < 16 || H % 4 || W % 4 || si < 1 || sj < 1) return false;
+    const long long np = (long long)((H - 8 + si - 1) / si) * ((W - 8 + sj - 1) / sj);
+    return np >= 4096 && np < (1ll << 25);      // (queue entries hold 25 bits of position)
+}
+
+int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int range_begin, int n_ranges, int32_t* d_idx,
+                  double* d_so, double* d_R, cudaStream_t st)
+{
+    if (n_ranges <= 0) return FIC_OK;
+    constexpr int N = 16;
+    const int npi = (H - 8 + si - 1) / si, npj = (W - 8 + sj - 1) / sj;
+    const int NP = npi * npj;
+    const int n_tiles = cdiv(NP, BM);
+    const int n_cols_pad = cdiv((long long)n_ranges * 8, BN) * BN;
+    const int slots_pad = n_cols_pad / 8;
+    const int n_groups = slots_pad / 32;
+    uint32_t cap = 1024;
+    while (cap > 128 && (size_t)n_ranges * cap * 4 > ((size_t)1 << 30)) cap >>= 1;
+    FIC_TRY(h->bf_boxsum.reserve((size_t)(H - 1) * (W - 1) * sizeof(uint16_t)));
+    FIC_TRY(h->bf_pool.reserve((size_t)n_tiles * BM * N * 2 + 256));
+    FIC_TRY(h->bf_stats.reserve((size_t)NP * (2 * sizeof(uint32_t) + sizeof(double)) + 1024));
+    FIC_TRY(h->bf_A.reserve((size_t)n_cols_pad * N * 2 + 256));
+    FIC_TRY(h->bf_surv.reserve((size_t)n_ranges * 4 + 64));
+    FIC_TRY(h->bf_list.reserve((size_t)n_ranges * cap * 4 + 256));
+    FIC_TRY(h->bf_best.reserve((size_t)slots_pad * (8 + sizeof(QtcRange)) + 512));
+    FIC_TRY(h->t_need.reserve((size_t)n_ranges * sizeof(int32_t) + 64));
+    if (!h->bf_ctrl.p) {
+        FIC_TRY(h->bf_ctrl.reserve(256));
+        FIC_CUDA(cudaMemsetAsync(h->bf_ctrl.p, 0, 256, st));
+    }
+    uint16_t* P = h->bf_boxsum.as<uint16_t>();
+    __half* poolA = h->bf_pool.as<__half>();
+    double* den = h->bf_stats.as<double>();
+    uint32_t* sd4 = reinterpret_cast<uint32_t*>(den + NP);
+    uint32_t* sq4 = sd4 + NP;
+    __half* rngB = h->bf_A.as<__half>();
+    uint32_t* cnt = h->bf_surv.as<uint32_t>();
+    uint32_t* list = h->bf_list.as<uint32_t>();
+    int* ctrl = h->bf_ctrl.as<int>();
+    unsigned long long* bound = h->bf_best.as<unsigned long long>();
+    QtcRange* rngc = reinterpret_cast<QtcRange*>((reinterpret_cast<uintptr_t>(bound + slots_pad) + 15) & ~(uintptr_t)15);
+    int32_t* need = h->t_need.as<int32_t>();
+
+    FIC_TRY(bf_prepare8(h, d_img, H, W, false, st));      // (the 2x2 cell sums; its statistics buffers are not used here)
+    P = h->bf_boxsum.as<uint16_t>();
+    den = h->bf_stats.as<double>();
+    sd4 = reinterpret_cast<uint32_t*>(den + NP);
+    sq4 = sd4 + NP;
+    bf4_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, W, si, sj, npj, NP, poolA, sd4, sq4, den);
+    FIC_CHECK_LAUNCH(h, "bf4_pool_kernel");
+    bf4_init_kernel<<<cdiv((long long)slots_pad * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, slots_pad, rngB, rngc, bound, cnt,
+                                                                        ctrl, need);
+    FIC_CHECK_LAUNCH(h, "bf4_init_kernel");
+    CUtensorMap mapA, mapB;
+    FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, N, BM, CU_TENSOR_MAP_SWIZZLE_32B));
+    FIC_TRY(make_map(&mapB, rngB, (uint64_t)n_cols_pad, N, BN, CU_TENSOR_MAP_SWIZZLE_32B));
+    if (!h->bf4_attr_ready) {
+        FIC_CUDA(cudaFuncSetAttribute(bf_screen_kernel<8, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCREEN_SMEM));
+        h->bf4_attr_ready = true;
+    }
+    ScreenParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.n_elig = ctrl; sp.cnt = cnt; sp.list = list; sp.cap = cap; sp.NP = NP; sp.n_tiles = n_tiles;
+    sp.err_flag = ctrl + 2;
+    sp.r_prev = 0;
+    sp.window_tiles = (64 << 20) / (BM * N * 2);
+    sp.grp_begin = 0; sp.grp_count = n_groups;
+    sp.rngc = rngc; sp.bound = bound; sp.sd4 = sd4; sp.sq4 = sq4; sp.den = den;
+    sp.img = d_img; sp.boxsum = P; sp.img_W = W; sp.lat_si = si; sp.lat_sj = sj; sp.lat_npj = npj;
+    // seed pass over every stride-th tile (only lowers the bounds), then the full pass (see qt_tc_search_impl)
+    const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 5);
+    sp.m_cur = stride; sp.n_round_tiles = cdiv(n_tiles, stride); sp.seed_pass = 1;
+    bf_screen_kernel<8, 16><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+    FIC_CHECK_LAUNCH(h, "bf_screen_kernel(4x4 ranges, seed)");
+    sp.m_cur = 1; sp.n_round_tiles = n_tiles; sp.seed_pass = 0;
+    bf_screen_kernel<8, 16><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
+    FIC_CHECK_LAUNCH(h, "bf_screen_kernel(4x4 ranges)");
+    bf4_pick_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(sp, n_ranges, d_idx, d_so, d_R, need);
+    FIC_CHECK_LAUNCH(h, "bf4_pick_kernel");
+    // constant ranges, empty or overflowed lists: the exact scan, for those ranges only
+    return bf_exact_generic_listed(h, d_img, H, W, 4, si, sj, FIC_BF_MODE_JIT, range_begin, n_ranges, need, d_idx, d_so, d_R, st);
 }

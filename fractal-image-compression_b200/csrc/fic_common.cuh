@@ -129,6 +129,7 @@ struct fic_handle {
     DevBuf bf_boxsum, bf_stats, bf_partial, bf_ranges;
     DevBuf bf_pool, bf_cand, bf_A, bf_thr, bf_surv, bf_ctrl, bf_best, bf_list, bf_done;
     bool qt_screen_attr_ready = false;
+    bool bf4_attr_ready = false;        // bf_screen_kernel<8, 16> (4x4 brute force) has its dynamic shared memory limit raised
     bool hv_group_attr_ready = false;   // hv_search_grouped_kernel has its dynamic shared memory limit raised on this device
     bool screen_attr_ready = false;  // the screen / rescoring kernels have their dynamic shared memory limit raised on this device
     bool bf_totals_live = false;     // bf_ctrl holds device-side counter totals that fic_get_counters has to fetch
