@@ -1915,7 +1915,7 @@ __global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int rang
     }
     if (lane == 0) {
         QtcRange rc;
-        const bool flat = 16 * q2 - sm * sm == 0;       // constant block: every candidate scores alike up to rounding -> exact scan
+        const bool flat = 16 * q2 - sm * sm == 0;       // constant block: every candidate scores exactly 0 (bf4_pick_kernel)
         rc.rho = sm - 16 * m;
         rc.ok = flat ? 0 : 1;
         rc.tw0 = (uint32_t)si; rc.tw1 = (uint32_t)sj;
@@ -1923,7 +1923,7 @@ __global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int rang
         rc.slack = DS((double)q2, DM(DM((double)sm, (double)sm), 0.0625));
         rngc[slot] = rc;
         cnt[slot] = 0;
-        need_exact[slot] = flat ? 1 : 0;
+        need_exact[slot] = 0;
     }
 }
 
@@ -1934,7 +1934,19 @@ __global__ void bf4_pick_kernel(const ScreenParams p, int n_ranges, int32_t* __r
     const int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (slot >= n_ranges) return;
     const QtcRange rc = p.rngc[slot];
-    if (!(rc.ok & 1)) return;
+    if (!(rc.ok & 1)) {
+        // A constant range: num = n * ab - rs * ds is exactly zero for every candidate (ab = c * ds without rounding), so the
+        // contrast is zero, the offset the gray level and the score exactly +0 whatever the domain -- the first candidate
+        // of the scan wins (jit_bfencoder.py keeps the first strict minimum), and its record is the scorer's.
+        if (lane == 0) {
+            const BfScore sc = bf4_score_pair(p, rc, 0, 0);
+            for (int k = 0; k < 4; ++k) out_idx[4 * (size_t)slot + k] = 0;
+            out_so[2 * (size_t)slot] = sc.s;
+            out_so[2 * (size_t)slot + 1] = sc.o;
+            if (out_R) out_R[slot] = sc.R;
+        }
+        return;
+    }
     const uint32_t n = p.cnt[slot];
     if (n > p.cap || n == 0) {
         if (lane == 0) need_exact[slot] = 1;
@@ -2417,6 +2429,6 @@ int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int
     FIC_CHECK_LAUNCH(h, "bf_screen_kernel(4x4 ranges)");
     bf4_pick_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(sp, n_ranges, d_idx, d_so, d_R, need);
     FIC_CHECK_LAUNCH(h, "bf4_pick_kernel");
-    // constant ranges, empty or overflowed lists: the exact scan, for those ranges only
+    // empty or overflowed lists (neither seen so far): the exact scan, for those ranges only
     return bf_exact_generic_listed(h, d_img, H, W, 4, si, sj, FIC_BF_MODE_JIT, range_begin, n_ranges, need, d_idx, d_so, d_R, st);
 }
