@@ -807,13 +807,18 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                                 const int r = c4 * 4 + g;
                                 const float rhs = __fmul_rn(__shfl_sync(0xffffffffu, my_rhs, r), denf);
                                 const float nre = __fmul_rn(__shfl_sync(0xffffffffu, my_rho, r), neps);
-                                unsigned m = 0u;
+                                // the eight numerators; the largest magnitude decides for all of them in the common case
+                                float na[8];
 #pragma unroll
-                                for (int t = 0; t < 8; ++t) {
-                                    const float na = fmaf((float)KT, __uint_as_float(v[g * 8 + t]), nre);
-                                    m |= (__fmul_rn(na, na) < rhs ? 0u : 1u) << t;
+                                for (int t = 0; t < 8; ++t) na[t] = fmaf((float)KT, __uint_as_float(v[g * 8 + t]), nre);
+                                const float mx = fmaxf(fmaxf(fmaxf(fabsf(na[0]), fabsf(na[1])), fmaxf(fabsf(na[2]), fabsf(na[3]))),
+                                                       fmaxf(fmaxf(fabsf(na[4]), fabsf(na[5])), fmaxf(fabsf(na[6]), fabsf(na[7]))));
+                                unsigned m = 0u;
+                                if (have && !(__fmul_rn(mx, mx) < rhs)) {
+#pragma unroll
+                                    for (int t = 0; t < 8; ++t) m |= (__fmul_rn(na[t], na[t]) < rhs ? 0u : 1u) << t;
                                 }
-                                m8[g] = have ? m : 0u;
+                                m8[g] = m;
                             }
                         }
 #pragma unroll
