@@ -254,6 +254,7 @@ struct ScreenParams {
     const uint8_t* img;      // the image, row pitch img_W
     const uint16_t* boxsum;  // 2x2 cell sums at every pixel offset, (H-1) x (W-1)
     int img_W, lat_si, lat_sj, lat_npj;      // lattice of domain positions: (q / lat_npj * lat_si, q % lat_npj * lat_sj)
+    int bf_mode;             // FIC_BF_MODE_JIT or FIC_BF_MODE_NUMPY: which scorer the survivors get
 };
 
 // j-th tile of the round, in increasing order.  Rounds use nested strides m_1 > m_2 > ... > m_last = 1 (each divides
@@ -425,6 +426,8 @@ __device__ __forceinline__ BfScore bf4_score_pair(const ScreenParams& p, const Q
             sq += d4 * d4;
             ab += d4 * (int)rp[(size_t)i * p.img_W + j];
         }
+    if (p.bf_mode == FIC_BF_MODE_NUMPY)      // bf_encoder.py:56-71: float64 sums (exact), no clamp; rc.sqr is the uint8-wrapped sum
+        return fic_bfnp_score(16.0, 0.0625, (double)rc.rs, (double)rc.sqr, DM((double)sd, 0.25), DM((double)sq, 0.0625), DM((double)ab, 0.25));
     const float ds = __fmul_rn((float)sd, 0.25f);
     return fic_bfjit_score(16.0, 0.0625, (double)rc.rs, (double)rc.sqr, (double)ds, (double)__fmul_rn((float)sq, 0.0625f),
                            (double)__fmul_rn(ds, ds), (double)__fmul_rn((float)ab, 0.25f));
@@ -683,10 +686,12 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 my_rho = (float)rc.rho;
                 my_slack = rc.ok ? rc.slack : -1.0;
             }
+            bool my_ok = false;
             if (MODE == 8) {   // sixteen ranges of eight columns: lanes r and r + 16 keep range r
                 const QtcRange rc = p.rngc[slot0 + (lane & 15)];
                 my_rho = (float)rc.rho;
-                my_slack = (rc.ok & 1) ? rc.slack : -1.0;
+                my_slack = rc.slack;       // (may be negative: the NumPy encoder's sum of squares wraps at 256)
+                my_ok = (rc.ok & 1) != 0;
             }
             int j = j0 + ((n ^ stage) & 1);   // first tile of this unit that is mine
             n += j1 - j0;
@@ -783,7 +788,7 @@ bf_screen_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     {
                         const double B = __longlong_as_double((long long)__ldcg(&p.bound[slot0 + (lane & 15)]));
                         const double rhs_g = DM(DS(my_slack, DM((double)KT, B)), 16.0 * KT * 0.999999);
-                        my_rhs = my_slack < 0.0 ? __int_as_float(0x7f800000) : (rhs_g > 0.0 ? (float)rhs_g : -1.0f);
+                        my_rhs = !my_ok ? __int_as_float(0x7f800000) : (rhs_g > 0.0 ? (float)rhs_g : -1.0f);
                     }
                     Bf4Queue* qq = reinterpret_cast<Bf4Queue*>(queue);
                     const unsigned lt = (1u << lane) - 1u;
@@ -1883,7 +1888,7 @@ __global__ void bf4_pool_kernel(const uint16_t* __restrict__ P, int W, int si, i
 
 // one warp per range slot: sums, the record of the bound test (range origin in tw0 / tw1), eight isometric copies of the
 // centred block as operand columns -- column t holds range pixel k at the place isometry t reads for it (fic_iso_bf)
-__global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int range_begin, int n_ranges, int slots_pad,
+__global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int mode, int range_begin, int n_ranges, int slots_pad,
                                 __half* __restrict__ rngB, QtcRange* __restrict__ rngc, unsigned long long* __restrict__ bound,
                                 uint32_t* __restrict__ cnt, int* __restrict__ ctrl, int32_t* __restrict__ need_exact)
 {
@@ -1904,11 +1909,12 @@ __global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int rang
     const int si = (ridx / rw) * 4, sj = (ridx % rw) * 4;
     const int k = lane & 15;
     const int px = img[(size_t)(si + k / 4) * W + sj + k % 4];
-    int sm = lane < 16 ? px : 0, q2 = lane < 16 ? px * px : 0;
+    int sm = lane < 16 ? px : 0, q2 = lane < 16 ? px * px : 0, qw = lane < 16 ? (px * px) & 255 : 0;
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
         sm += __shfl_xor_sync(0xffffffffu, sm, off);
         q2 += __shfl_xor_sync(0xffffffffu, q2, off);
+        qw += __shfl_xor_sync(0xffffffffu, qw, off);
     }
     const int m = (sm + 8) / 16;
 #pragma unroll
@@ -1924,8 +1930,9 @@ __global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int rang
         rc.rho = sm - 16 * m;
         rc.ok = flat ? 0 : 1;
         rc.tw0 = (uint32_t)si; rc.tw1 = (uint32_t)sj;
-        rc.rs = (float)sm; rc.sqr = (float)q2;
-        rc.slack = DS((double)q2, DM(DM((double)sm, (double)sm), 0.0625));
+        const int sqr = mode == FIC_BF_MODE_NUMPY ? qw : q2;      // bf_encoder.py:33 squares the uint8 pixels in uint8
+        rc.rs = (float)sm; rc.sqr = (float)sqr;
+        rc.slack = DS((double)sqr, DM(DM((double)sm, (double)sm), 0.0625));
         rngc[slot] = rc;
         cnt[slot] = 0;
         need_exact[slot] = 0;
@@ -2347,7 +2354,7 @@ int qt_tc_search(fic_handle* h, const uint8_t* d_img, int H, int W, int e, const
                                 d_vals, d_need_exact, hs, vs, d_pool_offsets, d_pool_rows, st);
 }
 
-// ---- brute force with 4x4 ranges on the tensor cores (JitedBruteForceEncoder semantics) --------------------------------
+// ---- brute force with 4x4 ranges on the tensor cores (both encoders' arithmetic) --------------------------------
 int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, int range, int si, int sj, int mode,
                             int range_begin, int n_ranges, const int32_t* d_need, int32_t* d_idx, double* d_so, double* d_R,
                             cudaStream_t st);
@@ -2355,13 +2362,13 @@ int bf_prepare8(fic_handle* h, const uint8_t* d_img, int H, int W, bool with_sta
 
 bool bf4_tc_applicable(int H, int W, int si, int sj, int mode)
 {
-    if (mode != FIC_BF_MODE_JIT || H < 16 || W < 16 || H % 4 || W % 4 || si < 1 || sj < 1) return false;
+    if ((mode != FIC_BF_MODE_JIT && mode != FIC_BF_MODE_NUMPY) || H < 16 || W < 16 || H % 4 || W % 4 || si < 1 || sj < 1) return false;
     const long long np = (long long)((H - 8 + si - 1) / si) * ((W - 8 + sj - 1) / sj);
     return np >= 4096 && np < (1ll << 25);      // (queue entries hold 25 bits of position)
 }
 
-int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int range_begin, int n_ranges, int32_t* d_idx,
-                  double* d_so, double* d_R, cudaStream_t st)
+int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int sj, int mode, int range_begin, int n_ranges,
+                  int32_t* d_idx, double* d_so, double* d_R, cudaStream_t st)
 {
     if (n_ranges <= 0) return FIC_OK;
     constexpr int N = 16;
@@ -2405,8 +2412,8 @@ int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int
     sq4 = sd4 + NP;
     bf4_pool_kernel<<<cdiv(NP, 128), 128, 0, st>>>(P, W, si, sj, npj, NP, poolA, sd4, sq4, den);
     FIC_CHECK_LAUNCH(h, "bf4_pool_kernel");
-    bf4_init_kernel<<<cdiv((long long)slots_pad * 32, 256), 256, 0, st>>>(d_img, W, range_begin, n_ranges, slots_pad, rngB, rngc, bound, cnt,
-                                                                        ctrl, need);
+    bf4_init_kernel<<<cdiv((long long)slots_pad * 32, 256), 256, 0, st>>>(d_img, W, mode, range_begin, n_ranges, slots_pad, rngB, rngc, bound,
+                                                                        cnt, ctrl, need);
     FIC_CHECK_LAUNCH(h, "bf4_init_kernel");
     CUtensorMap mapA, mapB;
     FIC_TRY(make_map(&mapA, poolA, (uint64_t)NP, N, BM, CU_TENSOR_MAP_SWIZZLE_32B));
@@ -2423,7 +2430,7 @@ int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int
     sp.window_tiles = (64 << 20) / (BM * N * 2);
     sp.grp_begin = 0; sp.grp_count = n_groups;
     sp.rngc = rngc; sp.bound = bound; sp.sd4 = sd4; sp.sq4 = sq4; sp.den = den;
-    sp.img = d_img; sp.boxsum = P; sp.img_W = W; sp.lat_si = si; sp.lat_sj = sj; sp.lat_npj = npj;
+    sp.img = d_img; sp.boxsum = P; sp.img_W = W; sp.lat_si = si; sp.lat_sj = sj; sp.lat_npj = npj; sp.bf_mode = mode;
     // seed pass over every stride-th tile (only lowers the bounds), then the full pass (see qt_tc_search_impl)
     const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 5);
     sp.m_cur = stride; sp.n_round_tiles = cdiv(n_tiles, stride); sp.seed_pass = 1;
@@ -2435,5 +2442,5 @@ int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int
     bf4_pick_kernel<<<cdiv((long long)n_ranges * 32, 256), 256, 0, st>>>(sp, n_ranges, d_idx, d_so, d_R, need);
     FIC_CHECK_LAUNCH(h, "bf4_pick_kernel");
     // empty or overflowed lists (neither seen so far): the exact scan, for those ranges only
-    return bf_exact_generic_listed(h, d_img, H, W, 4, si, sj, FIC_BF_MODE_JIT, range_begin, n_ranges, need, d_idx, d_so, d_R, st);
+    return bf_exact_generic_listed(h, d_img, H, W, 4, si, sj, mode, range_begin, n_ranges, need, d_idx, d_so, d_R, st);
 }

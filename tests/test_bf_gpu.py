@@ -92,17 +92,18 @@ def test_other_range_sizes_against_oracle(fic, orc, rs, mode):
 
 @pytest.mark.parametrize("shape,strides,seed", [((96, 96), (1, 1), 21), ((128, 100), (2, 1), 22), ((104, 120), (1, 3), 23)],
                          ids=["96x96", "128x100_strides_2_1", "104x120_strides_1_3"])
-def test_range_size_4_on_the_tensor_cores(fic, orc, shape, strides, seed):
-    """4x4 ranges with the jit encoder's arithmetic go through the K = 16 tensor-core pass (bf_screen.cu: bf4_tc_encode) once
+@pytest.mark.parametrize("mode", [1, 0], ids=["jit", "numpy"])
+def test_range_size_4_on_the_tensor_cores(fic, orc, shape, strides, seed, mode):
+    """4x4 ranges (both encoders' arithmetic: every sum is exact with sixteen pixels) go through the K = 16 tensor-core pass (bf_screen.cu: bf4_tc_encode) once
     the lattice has 4096 positions; a flat patch (constant ranges: handed to the exact scan), a saturated one and a
     checkerboard are in the image.  All records against the oracle, and against the library's own exact scan."""
     img = synthetic_image(seed, *shape)
     img[:12, :20] = 200
     img[40:52, 60:72] = 255
     img[60:68, 8:16] = (np.indices((8, 8)).sum(0) % 2 * 255).astype(np.uint8)
-    want = orc.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=1)
-    got = fic.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=1)
-    exact = fic.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=1, flags=fic.BF_EXACT_ONLY)
+    want = orc.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=mode)
+    got = fic.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=mode)
+    exact = fic.bf_encode(img, range_size=4, domain_size=8, strides=strides, mode=mode, flags=fic.BF_EXACT_ONLY)
     for x, y, z in zip(got, want, exact):
         assert np.array_equal(x, y)
         assert np.array_equal(z, y)
