@@ -513,6 +513,233 @@ bf_scan_generic_kernel(const uint8_t* __restrict__ img, const uint16_t* __restri
     }
 }
 
+// ---- generic range size, jit arithmetic, four ranges per CTA ----------------------------------------------------------
+// Two of the three sums of a candidate -- sum d and sum d^2 in the order of its isometry -- do not depend on the range:
+// bf_gen_stats_kernel computes them once per (position, isometry).  The scan then gives a CTA four consecutive ranges: a
+// thread walks the pooled block of its position once per isometry for all four (one load and one conversion per sample
+// instead of four, one float4 of range pixels from shared memory), keeping 32 sum(d r) chains, each in the reference's
+// order and rounding.  Winners are kept as (score, scan index) per thread in shared memory and the winning candidate of
+// a range is scored once more at the end for (s, o).  Per (range, isometry, pixel): 2.8 instructions instead of 9.
+#define BF_GEN_G 4
+__global__ void bf_gen_stats_kernel(const uint16_t* __restrict__ P, int W, int R, int si, int sj, int npj, int NP,
+                                    float* __restrict__ ds_tab /*[8][NP]*/, float* __restrict__ sds_tab /*[8][NP]*/)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= NP) return;
+    const int BW = W - 1;
+    const int di = (q / npj) * si, dj = (q % npj) * sj;
+    int step_i[8], step_j[8];
+    const uint16_t* drow[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        int a00, b00, a10, b10, a01, b01;
+        fic_iso_bf(t >> 2, t & 3, R, 0, 0, a00, b00);
+        fic_iso_bf(t >> 2, t & 3, R, 1, 0, a10, b10);
+        fic_iso_bf(t >> 2, t & 3, R, 0, 1, a01, b01);
+        step_i[t] = 2 * ((a10 - a00) * BW + (b10 - b00));
+        step_j[t] = 2 * ((a01 - a00) * BW + (b01 - b00));
+        drow[t] = P + (size_t)(di + 2 * a00) * BW + dj + 2 * b00;
+    }
+    float dsf[8], sdsf[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) dsf[t] = sdsf[t] = 0.f;
+    for (int i = 0; i < R; ++i) {
+        for (int j = 0; j < R; ++j) {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                const float d = __fmul_rn((float)drow[t][j * step_j[t]], 0.25f);
+                dsf[t] = __fadd_rn(dsf[t], d);
+                sdsf[t] = __fadd_rn(sdsf[t], __fmul_rn(d, d));
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) drow[t] += step_i[t];
+    }
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        ds_tab[(size_t)t * NP + q] = dsf[t];
+        sds_tab[(size_t)t * NP + q] = sdsf[t];
+    }
+}
+
+__global__ void __launch_bounds__(BF_THREADS)
+bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, int H, int W, int R, int si, int sj,
+                        int npi, int npj, int range_begin, int n_ranges, const float* __restrict__ ds_tab,
+                        const float* __restrict__ sds_tab, BestRec* __restrict__ partial /*[n_ranges][gridDim.y]*/)
+{
+    extern __shared__ __align__(16) unsigned char s_dyn4[];
+    const int nn = R * R;
+    float4* s_rng = reinterpret_cast<float4*>(s_dyn4);                                   // [nn]: pixel k of the four ranges
+    double* s_bR = reinterpret_cast<double*>(s_dyn4 + (size_t)nn * sizeof(float4));       // [BF_GEN_G][BF_THREADS]
+    unsigned long long* s_bseq = reinterpret_cast<unsigned long long*>(s_bR + BF_GEN_G * BF_THREADS);
+    __shared__ BestRec red[BF_GEN_G][BF_THREADS / 32];
+    __shared__ double s_rs[BF_GEN_G], s_sq[BF_GEN_G];
+    const int tid = threadIdx.x;
+    const int slot0 = blockIdx.x * BF_GEN_G;
+    const int g_real = n_ranges - slot0 < BF_GEN_G ? n_ranges - slot0 : BF_GEN_G;
+    const int rw = W / R;
+    int ri[BF_GEN_G], rj[BF_GEN_G];
+#pragma unroll
+    for (int g = 0; g < BF_GEN_G; ++g) {
+        const int ridx = range_begin + slot0 + (g < g_real ? g : 0);
+        ri[g] = (ridx / rw) * R; rj[g] = (ridx % rw) * R;
+    }
+    for (int k = tid; k < nn; k += BF_THREADS) {
+        const int i = k / R, j = k % R;
+        s_rng[k] = make_float4((float)img[(size_t)(ri[0] + i) * W + rj[0] + j], (float)img[(size_t)(ri[1] + i) * W + rj[1] + j],
+                               (float)img[(size_t)(ri[2] + i) * W + rj[2] + j], (float)img[(size_t)(ri[3] + i) * W + rj[3] + j]);
+    }
+#pragma unroll
+    for (int g = 0; g < BF_GEN_G; ++g) { s_bR[g * BF_THREADS + tid] = __longlong_as_double(0x7ff0000000000000ll); s_bseq[g * BF_THREADS + tid] = ~0ull; }
+    __syncthreads();
+    if (tid < BF_GEN_G) {
+        unsigned long long rs = 0, sq = 0;
+        for (int k = 0; k < nn; ++k) {
+            const float4 v4 = s_rng[k];
+            const unsigned v = (unsigned)(tid == 0 ? v4.x : tid == 1 ? v4.y : tid == 2 ? v4.z : v4.w);
+            rs += v;
+            sq += v * v;
+        }
+        s_rs[tid] = (double)rs;
+        s_sq[tid] = (double)sq;
+    }
+    __syncthreads();
+    const double n = (double)nn, inv_n = DD(1.0, n);
+    const int NP = npi * npj;
+    const int BW = W - 1;
+    // the positions are cut into gridDim.y contiguous chunks, one CTA each: few ranges still fill the GPU
+    const int per = (NP + (int)gridDim.y - 1) / (int)gridDim.y;
+    const int q0 = per * (int)blockIdx.y, q1 = q0 + per < NP ? q0 + per : NP;
+    for (int q = q0 + tid; q < q1; q += BF_THREADS) {
+        const int di = (q / npj) * si, dj = (q % npj) * sj;
+        int step_i[8], step_j[8];
+        const uint16_t* drow[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            int a00, b00, a10, b10, a01, b01;
+            fic_iso_bf(t >> 2, t & 3, R, 0, 0, a00, b00);
+            fic_iso_bf(t >> 2, t & 3, R, 1, 0, a10, b10);
+            fic_iso_bf(t >> 2, t & 3, R, 0, 1, a01, b01);
+            step_i[t] = 2 * ((a10 - a00) * BW + (b10 - b00));
+            step_j[t] = 2 * ((a01 - a00) * BW + (b01 - b00));
+            drow[t] = P + (size_t)(di + 2 * a00) * BW + dj + 2 * b00;
+        }
+        float ab[BF_GEN_G][8];
+#pragma unroll
+        for (int g = 0; g < BF_GEN_G; ++g)
+#pragma unroll
+            for (int t = 0; t < 8; ++t) ab[g][t] = 0.f;
+        int k = 0;
+        for (int i = 0; i < R; ++i) {
+            for (int j = 0; j < R; ++j, ++k) {
+                const float4 r4 = s_rng[k];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const float d = __fmul_rn((float)drow[t][j * step_j[t]], 0.25f);
+                    ab[0][t] = __fadd_rn(ab[0][t], __fmul_rn(d, r4.x));
+                    ab[1][t] = __fadd_rn(ab[1][t], __fmul_rn(d, r4.y));
+                    ab[2][t] = __fadd_rn(ab[2][t], __fmul_rn(d, r4.z));
+                    ab[3][t] = __fadd_rn(ab[3][t], __fmul_rn(d, r4.w));
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) drow[t] += step_i[t];
+        }
+        // one copy of the scorer: the 32 candidates of this position in turn (scan order inside a range: isometry)
+#pragma unroll 1
+        for (int idx = 0; idx < BF_GEN_G * 8; ++idx) {
+            const int g = idx >> 3, t = idx & 7;
+            if (g >= g_real) break;
+            float abv = 0.f;
+#pragma unroll
+            for (int gg = 0; gg < BF_GEN_G; ++gg)
+#pragma unroll
+                for (int tt = 0; tt < 8; ++tt)
+                    if (idx == gg * 8 + tt) abv = ab[gg][tt];
+            const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
+            const BfScore sc = fic_bfjit_score(n, inv_n, s_rs[g], s_sq[g], (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abv);
+            const unsigned long long seq = (unsigned long long)q * 8ull + (unsigned)t;
+            if (fic_better(sc.R, seq, s_bR[g * BF_THREADS + tid], s_bseq[g * BF_THREADS + tid])) {
+                s_bR[g * BF_THREADS + tid] = sc.R;
+                s_bseq[g * BF_THREADS + tid] = seq;
+            }
+        }
+    }
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int g = 0; g < BF_GEN_G; ++g) {
+        double bR = s_bR[g * BF_THREADS + tid];
+        unsigned long long bseq = s_bseq[g * BF_THREADS + tid];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double oR = __shfl_xor_sync(0xffffffffu, bR, off);
+            const unsigned long long oS = __shfl_xor_sync(0xffffffffu, bseq, off);
+            if (fic_better(oR, oS, bR, bseq)) { bR = oR; bseq = oS; }
+        }
+        if (lane == 0) { red[g][warp].R = bR; red[g][warp].seq = bseq; }
+    }
+    __syncthreads();
+    if (tid < g_real) {
+        const int g = tid;
+        BestRec b = red[g][0];
+        for (int w = 1; w < BF_THREADS / 32; ++w)
+            if (fic_better(red[g][w].R, red[g][w].seq, b.R, b.seq)) b = red[g][w];
+        partial[(size_t)(slot0 + g) * gridDim.y + blockIdx.y] = b;
+    }
+}
+
+// merges the chunk winners of a range (first strict minimum in scan order) and scores the winner once more for its (s, o):
+// the same sums in the same order
+__global__ void bf_gen_finalize_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, int W, int R, int si, int sj,
+                                       int npj, int NP, int range_begin, int n_ranges, int n_chunks,
+                                       const BestRec* __restrict__ partial, const float* __restrict__ ds_tab,
+                                       const float* __restrict__ sds_tab, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
+                                       double* __restrict__ out_R)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_ranges) return;
+    BestRec b = partial[(size_t)slot * n_chunks];
+    for (int c = 1; c < n_chunks; ++c) {
+        const BestRec o = partial[(size_t)slot * n_chunks + c];
+        if (fic_better(o.R, o.seq, b.R, b.seq)) b = o;
+    }
+    if (b.seq == ~0ull) {
+        for (int k = 0; k < 4; ++k) out_idx[4 * (size_t)slot + k] = 0;
+        out_so[2 * (size_t)slot] = 0.0; out_so[2 * (size_t)slot + 1] = 0.0;
+        if (out_R) out_R[slot] = 0.0;
+        return;
+    }
+    const int nn = R * R, BW = W - 1, rw = W / R;
+    const int ridx = range_begin + slot;
+    const int ri = (ridx / rw) * R, rj = (ridx % rw) * R;
+    unsigned long long rs = 0, sq = 0;
+    for (int k = 0; k < nn; ++k) {
+        const unsigned v = img[(size_t)(ri + k / R) * W + rj + k % R];
+        rs += v;
+        sq += v * v;
+    }
+    const int t = (int)(b.seq & 7ull), q = (int)(b.seq >> 3);
+    const int di = (q / npj) * si, dj = (q % npj) * sj;
+    float abf = 0.f;
+    for (int i = 0; i < R; ++i)
+        for (int j = 0; j < R; ++j) {
+            int sa, sb;
+            fic_iso_bf(t >> 2, t & 3, R, i, j, sa, sb);
+            const float d = __fmul_rn((float)P[(size_t)(di + 2 * sa) * BW + dj + 2 * sb], 0.25f);
+            abf = __fadd_rn(abf, __fmul_rn(d, (float)img[(size_t)(ri + i) * W + rj + j]));
+        }
+    const double n = (double)nn, inv_n = DD(1.0, n);
+    const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
+    const BfScore sc = fic_bfjit_score(n, inv_n, (double)rs, (double)sq, (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abf);
+    out_idx[4 * (size_t)slot + 0] = di;
+    out_idx[4 * (size_t)slot + 1] = dj;
+    out_idx[4 * (size_t)slot + 2] = t >> 2;
+    out_idx[4 * (size_t)slot + 3] = t & 3;
+    out_so[2 * (size_t)slot] = sc.s;
+    out_so[2 * (size_t)slot + 1] = sc.o;
+    if (out_R) out_R[slot] = sc.R;
+}
+
 // ---- host side -------------------------------------------------------------------------------
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
@@ -645,6 +872,31 @@ int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, i
         FIC_CHECK_LAUNCH(h, "bf_boxsum_kernel");
     }
     const int nn = range * range;
+    const long long NPq = (long long)npi * npj;
+    if (mode == FIC_BF_MODE_JIT && !d_need && NPq > 0 && NPq < (1ll << 28) && nn <= 1024 && H > 1 && W > 1) {
+        // four ranges per CTA over per-position tables of sum d / sum d^2 (see bf_scan_generic4_kernel)
+        FIC_TRY(h->bf_stats.reserve((size_t)NPq * 16 * sizeof(float) + 256));
+        float* ds_tab = h->bf_stats.as<float>();
+        float* sds_tab = ds_tab + (size_t)8 * NPq;
+        bf_gen_stats_kernel<<<ceil_div(NPq, 128), 128, 0, st>>>(h->bf_boxsum.as<uint16_t>(), W, range, si, sj, npj, (int)NPq, ds_tab, sds_tab);
+        FIC_CHECK_LAUNCH(h, "bf_gen_stats_kernel");
+        const size_t smem = (size_t)nn * sizeof(float4) + BF_GEN_G * BF_THREADS * (sizeof(double) + sizeof(unsigned long long));
+        const int n_cta = ceil_div(n_ranges, BF_GEN_G);
+        int n_chunks = (8 * h->num_sms + n_cta - 1) / n_cta;       // about eight CTAs per SM in all
+        const int max_chunks = (int)std::max<long long>(1, NPq / BF_THREADS);
+        if (n_chunks > max_chunks) n_chunks = max_chunks;
+        if (n_chunks < 1) n_chunks = 1;
+        FIC_TRY(h->bf_partial.reserve((size_t)n_ranges * n_chunks * sizeof(BestRec) + 64));
+        BestRec* partial = h->bf_partial.as<BestRec>();
+        bf_scan_generic4_kernel<<<dim3(n_cta, n_chunks), BF_THREADS, smem, st>>>(d_img, h->bf_boxsum.as<uint16_t>(), H, W, range, si, sj, npi,
+                                                                                  npj, range_begin, n_ranges, ds_tab, sds_tab, partial);
+        FIC_CHECK_LAUNCH(h, "bf_scan_generic4_kernel");
+        bf_gen_finalize_kernel<<<ceil_div(n_ranges, 128), 128, 0, st>>>(d_img, h->bf_boxsum.as<uint16_t>(), W, range, si, sj, npj, (int)NPq,
+                                                                         range_begin, n_ranges, n_chunks, partial, ds_tab, sds_tab, d_idx,
+                                                                         d_so, d_R);
+        FIC_CHECK_LAUNCH(h, "bf_gen_finalize_kernel");
+        return FIC_OK;
+    }
     const int smem_px = nn <= 10240 ? nn : 0;      // range block in shared memory when it fits 40 KB
     if (mode == FIC_BF_MODE_JIT)
         bf_scan_generic_kernel<FIC_BF_MODE_JIT><<<n_ranges, BF_THREADS, smem_px * sizeof(float), st>>>(
