@@ -1939,6 +1939,20 @@ __global__ void bf4_init_kernel(const uint8_t* __restrict__ img, int W, int mode
     }
 }
 
+// A first bound for every range before any tile is looked at: the score of one candidate (a position in the middle of the
+// lattice, identity).  With the bounds at +inf the first tile of the seed pass would queue -- and score -- all of its 1024
+// candidates per range.
+__global__ void bf4_first_bound_kernel(const ScreenParams p, int n_ranges)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_ranges) return;
+    const QtcRange rc = p.rngc[slot];
+    if (!(rc.ok & 1)) return;
+    const BfScore sc = bf4_score_pair(p, rc, p.NP / 2, 0);
+    if (sc.R < __longlong_as_double(0x7ff0000000000000ll))
+        p.bound[slot] = (unsigned long long)__double_as_longlong(sc.R > 0.0 ? sc.R : 0.0);
+}
+
 // one warp per range: the first minimum in scan order (position * 8 + isometry) among the listed candidates
 __global__ void bf4_pick_kernel(const ScreenParams p, int n_ranges, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
                                 double* __restrict__ out_R, int32_t* __restrict__ need_exact)
@@ -2433,6 +2447,8 @@ int bf4_tc_encode(fic_handle* h, const uint8_t* d_img, int H, int W, int si, int
     sp.img = d_img; sp.boxsum = P; sp.img_W = W; sp.lat_si = si; sp.lat_sj = sj; sp.lat_npj = npj; sp.bf_mode = mode;
     // seed pass over every stride-th tile (only lowers the bounds), then the full pass (see qt_tc_search_impl)
     const int stride = NP >= 64 * 1024 ? 61 : (NP >= 8192 ? 13 : 5);
+    bf4_first_bound_kernel<<<cdiv(n_ranges, 128), 128, 0, st>>>(sp, n_ranges);
+    FIC_CHECK_LAUNCH(h, "bf4_first_bound_kernel");
     sp.m_cur = stride; sp.n_round_tiles = cdiv(n_tiles, stride); sp.seed_pass = 1;
     bf_screen_kernel<8, 16><<<h->num_sms, SCREEN_THREADS, SCREEN_SMEM, st>>>(mapA, mapB, sp);
     FIC_CHECK_LAUNCH(h, "bf_screen_kernel(4x4 ranges, seed)");
