@@ -1471,11 +1471,12 @@ inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 
 // =================================================================================================================
-// Quadtree: the dense-pool, all-classes search on the tensor cores (quadtree/encoder.py:148-193, 285-384 with
-// domain_hstep = domain_vstep = 1 and full_class_search).  Every range of a level is matched against every domain
-// position, which is the brute-force contraction with two differences:
-//   * one isometry per (range, domain) pair and scale sign, derived from the two classifications -- the GEMM still
-//     forms all eight and the epilogue picks the pair's own column;
+// Quadtree: the all-classes search on the tensor cores (quadtree/encoder.py:148-193, 285-384 with full_class_search; any
+// pool lattice, dense or not).  Every range of a level is matched against every domain of the pool, which is the
+// brute-force contraction with two differences:
+//   * one isometry per (range, domain) pair and scale sign, derived from the two classifications -- it factors into a
+//     permutation of the domain block and one of the range block (QT_ALPHA / QT_BETA), so the range operand has four
+//     columns (scale sign x orientation of the domain's class) and the epilogue picks the pair's own with one select;
 //   * the score is the QUANTISED one (fic_q_score), the winner the first minimum in the reference's scan order
 //     (scale sign, class, position).
 // The GEMM's accumulators are exact integers (centred pixel sums in fp16, fp32 accumulation well below 2^24), so the
