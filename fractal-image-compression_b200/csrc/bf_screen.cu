@@ -2247,10 +2247,12 @@ int bf_screen_encode8(fic_handle* h, const uint8_t* d_img, int H, int W, int mod
 }
 
 // ---- host driver of the quadtree search on the tensor cores -----------------------------------------------------------------
-// One level of the quadtree partition: the n ranges of side 2^e in d_queue ([n][4] = si, sj, node, -) against all
-// (H - 2^(e+1) + 1) x (W - 2^(e+1) + 1) domain positions.  d_rcls [n][2][3] = (class, rotation, orientation) of every range for
-// positive / negative scales, d_dcls [NP][3] the same for every domain position (row-major grid).  Writes rec [n][6] / vals
-// [n][3] for the ranges it decides and need_exact[n] = 1 for the others.  e = 3 (8x8 ranges, K = 64) or e = 2 (4x4, K = 16).
+// One level of the quadtree partition: the n ranges of side 2^e in d_queue ([n][4] = si, sj, node, -) against the
+// ((H - 2^(e+1)) / vs + 1) x ((W - 2^(e+1)) / hs + 1) domains of the pool's lattice (steps vs, hs).  d_rcls [n][2][3] = (class,
+// rotation, orientation) of every range for positive / negative scales, d_dcls [NP][3] the same for every domain (row-major
+// lattice), d_pool_offsets / d_pool_rows the pool's class lists (for the placeholder rows of empty classes).  Writes rec
+// [n][6] / vals [n][3] for the ranges it decides and need_exact[n] = 1 for the others.  e = 3 (8x8 ranges, K = 64) or e = 2
+// (4x4, K = 16).
 template <int S>
 static int qt_tc_search_impl(fic_handle* h, const uint8_t* d_img, int H, int W, const int32_t* d_queue, int n_ranges,
                              const int32_t* d_rcls, const int32_t* d_dcls, int nmodes, double max_scale, int scale_bits,
