@@ -521,13 +521,28 @@ bf_scan_generic_kernel(const uint8_t* __restrict__ img, const uint16_t* __restri
 // order and rounding.  Winners are kept as (score, scan index) per thread in shared memory and the winning candidate of
 // a range is scored once more at the end for (s, o).  Per (range, isometry, pixel): 2.8 instructions instead of 9.
 #define BF_GEN_G 4
+// (NumPy semantics: the sums are integers and do not depend on the isometry -- isd_tab / isq_tab [NP] instead)
+template <int MODE>
 __global__ void bf_gen_stats_kernel(const uint16_t* __restrict__ P, int W, int R, int si, int sj, int npj, int NP,
-                                    float* __restrict__ ds_tab /*[8][NP]*/, float* __restrict__ sds_tab /*[8][NP]*/)
+                                    float* __restrict__ ds_tab /*[8][NP]*/, float* __restrict__ sds_tab /*[8][NP]*/,
+                                    long long* __restrict__ isd_tab /*[NP]*/, long long* __restrict__ isq_tab /*[NP]*/)
 {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= NP) return;
     const int BW = W - 1;
     const int di = (q / npj) * si, dj = (q % npj) * sj;
+    if (MODE == FIC_BF_MODE_NUMPY) {
+        long long sd = 0, sq = 0;
+        for (int i = 0; i < R; ++i)
+            for (int j = 0; j < R; ++j) {
+                const long long d4 = P[(size_t)(di + 2 * i) * BW + dj + 2 * j];
+                sd += d4;
+                sq += d4 * d4;
+            }
+        isd_tab[q] = sd;
+        isq_tab[q] = sq;
+        return;
+    }
     int step_i[8], step_j[8];
     const uint16_t* drow[8];
 #pragma unroll
@@ -562,10 +577,12 @@ __global__ void bf_gen_stats_kernel(const uint16_t* __restrict__ P, int W, int R
     }
 }
 
+template <int MODE>
 __global__ void __launch_bounds__(BF_THREADS)
 bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, int H, int W, int R, int si, int sj,
                         int npi, int npj, int range_begin, int n_ranges, const float* __restrict__ ds_tab,
-                        const float* __restrict__ sds_tab, BestRec* __restrict__ partial /*[n_ranges][gridDim.y]*/)
+                        const float* __restrict__ sds_tab, const long long* __restrict__ isd_tab,
+                        const long long* __restrict__ isq_tab, BestRec* __restrict__ partial /*[n_ranges][gridDim.y]*/)
 {
     extern __shared__ __align__(16) unsigned char s_dyn4[];
     const int nn = R * R;
@@ -598,7 +615,7 @@ bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restr
             const float4 v4 = s_rng[k];
             const unsigned v = (unsigned)(tid == 0 ? v4.x : tid == 1 ? v4.y : tid == 2 ? v4.z : v4.w);
             rs += v;
-            sq += v * v;
+            sq += MODE == FIC_BF_MODE_JIT ? v * v : ((v * v) & 255u);      // bf_encoder.py:33 squares in uint8
         }
         s_rs[tid] = (double)rs;
         s_sq[tid] = (double)sq;
@@ -625,21 +642,30 @@ bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restr
             drow[t] = P + (size_t)(di + 2 * a00) * BW + dj + 2 * b00;
         }
         float ab[BF_GEN_G][8];
+        int iab[BF_GEN_G][8];        // NumPy semantics: integer sums (nn <= 1024: below 2^31)
 #pragma unroll
         for (int g = 0; g < BF_GEN_G; ++g)
 #pragma unroll
-            for (int t = 0; t < 8; ++t) ab[g][t] = 0.f;
+            for (int t = 0; t < 8; ++t) { ab[g][t] = 0.f; iab[g][t] = 0; }
         int k = 0;
         for (int i = 0; i < R; ++i) {
             for (int j = 0; j < R; ++j, ++k) {
                 const float4 r4 = s_rng[k];
 #pragma unroll
                 for (int t = 0; t < 8; ++t) {
-                    const float d = __fmul_rn((float)drow[t][j * step_j[t]], 0.25f);
-                    ab[0][t] = __fadd_rn(ab[0][t], __fmul_rn(d, r4.x));
-                    ab[1][t] = __fadd_rn(ab[1][t], __fmul_rn(d, r4.y));
-                    ab[2][t] = __fadd_rn(ab[2][t], __fmul_rn(d, r4.z));
-                    ab[3][t] = __fadd_rn(ab[3][t], __fmul_rn(d, r4.w));
+                    if (MODE == FIC_BF_MODE_JIT) {
+                        const float d = __fmul_rn((float)drow[t][j * step_j[t]], 0.25f);
+                        ab[0][t] = __fadd_rn(ab[0][t], __fmul_rn(d, r4.x));
+                        ab[1][t] = __fadd_rn(ab[1][t], __fmul_rn(d, r4.y));
+                        ab[2][t] = __fadd_rn(ab[2][t], __fmul_rn(d, r4.z));
+                        ab[3][t] = __fadd_rn(ab[3][t], __fmul_rn(d, r4.w));
+                    } else {
+                        const int d4 = drow[t][j * step_j[t]];
+                        iab[0][t] += d4 * (int)r4.x;
+                        iab[1][t] += d4 * (int)r4.y;
+                        iab[2][t] += d4 * (int)r4.z;
+                        iab[3][t] += d4 * (int)r4.w;
+                    }
                 }
             }
 #pragma unroll
@@ -651,13 +677,20 @@ bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restr
             const int g = idx >> 3, t = idx & 7;
             if (g >= g_real) break;
             float abv = 0.f;
+            int iabv = 0;
 #pragma unroll
             for (int gg = 0; gg < BF_GEN_G; ++gg)
 #pragma unroll
                 for (int tt = 0; tt < 8; ++tt)
-                    if (idx == gg * 8 + tt) abv = ab[gg][tt];
-            const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
-            const BfScore sc = fic_bfjit_score(n, inv_n, s_rs[g], s_sq[g], (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abv);
+                    if (idx == gg * 8 + tt) { abv = ab[gg][tt]; iabv = iab[gg][tt]; }
+            BfScore sc;
+            if (MODE == FIC_BF_MODE_JIT) {
+                const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
+                sc = fic_bfjit_score(n, inv_n, s_rs[g], s_sq[g], (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abv);
+            } else {
+                sc = fic_bfnp_score(n, inv_n, s_rs[g], s_sq[g], DM((double)isd_tab[q], 0.25), DM((double)isq_tab[q], 0.0625),
+                                    DM((double)iabv, 0.25));
+            }
             const unsigned long long seq = (unsigned long long)q * 8ull + (unsigned)t;
             if (fic_better(sc.R, seq, s_bR[g * BF_THREADS + tid], s_bseq[g * BF_THREADS + tid])) {
                 s_bR[g * BF_THREADS + tid] = sc.R;
@@ -690,11 +723,13 @@ bf_scan_generic4_kernel(const uint8_t* __restrict__ img, const uint16_t* __restr
 
 // merges the chunk winners of a range (first strict minimum in scan order) and scores the winner once more for its (s, o):
 // the same sums in the same order
+template <int MODE>
 __global__ void bf_gen_finalize_kernel(const uint8_t* __restrict__ img, const uint16_t* __restrict__ P, int W, int R, int si, int sj,
                                        int npj, int NP, int range_begin, int n_ranges, int n_chunks,
                                        const BestRec* __restrict__ partial, const float* __restrict__ ds_tab,
-                                       const float* __restrict__ sds_tab, int32_t* __restrict__ out_idx, double* __restrict__ out_so,
-                                       double* __restrict__ out_R)
+                                       const float* __restrict__ sds_tab, const long long* __restrict__ isd_tab,
+                                       const long long* __restrict__ isq_tab, int32_t* __restrict__ out_idx,
+                                       double* __restrict__ out_so, double* __restrict__ out_R)
 {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n_ranges) return;
@@ -716,21 +751,29 @@ __global__ void bf_gen_finalize_kernel(const uint8_t* __restrict__ img, const ui
     for (int k = 0; k < nn; ++k) {
         const unsigned v = img[(size_t)(ri + k / R) * W + rj + k % R];
         rs += v;
-        sq += v * v;
+        sq += MODE == FIC_BF_MODE_JIT ? v * v : ((v * v) & 255u);
     }
     const int t = (int)(b.seq & 7ull), q = (int)(b.seq >> 3);
     const int di = (q / npj) * si, dj = (q % npj) * sj;
     float abf = 0.f;
+    long long iab = 0;
     for (int i = 0; i < R; ++i)
         for (int j = 0; j < R; ++j) {
             int sa, sb;
             fic_iso_bf(t >> 2, t & 3, R, i, j, sa, sb);
-            const float d = __fmul_rn((float)P[(size_t)(di + 2 * sa) * BW + dj + 2 * sb], 0.25f);
-            abf = __fadd_rn(abf, __fmul_rn(d, (float)img[(size_t)(ri + i) * W + rj + j]));
+            const int d4 = P[(size_t)(di + 2 * sa) * BW + dj + 2 * sb];
+            const int rv = img[(size_t)(ri + i) * W + rj + j];
+            abf = __fadd_rn(abf, __fmul_rn(__fmul_rn((float)d4, 0.25f), (float)rv));
+            iab += (long long)d4 * rv;
         }
     const double n = (double)nn, inv_n = DD(1.0, n);
-    const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
-    const BfScore sc = fic_bfjit_score(n, inv_n, (double)rs, (double)sq, (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abf);
+    BfScore sc;
+    if (MODE == FIC_BF_MODE_JIT) {
+        const float dsf = ds_tab[(size_t)t * NP + q], sdsf = sds_tab[(size_t)t * NP + q];
+        sc = fic_bfjit_score(n, inv_n, (double)rs, (double)sq, (double)dsf, (double)sdsf, (double)__fmul_rn(dsf, dsf), (double)abf);
+    } else {
+        sc = fic_bfnp_score(n, inv_n, (double)rs, (double)sq, DM((double)isd_tab[q], 0.25), DM((double)isq_tab[q], 0.0625), DM((double)iab, 0.25));
+    }
     out_idx[4 * (size_t)slot + 0] = di;
     out_idx[4 * (size_t)slot + 1] = dj;
     out_idx[4 * (size_t)slot + 2] = t >> 2;
@@ -873,13 +916,14 @@ int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, i
     }
     const int nn = range * range;
     const long long NPq = (long long)npi * npj;
-    if (mode == FIC_BF_MODE_JIT && !d_need && NPq > 0 && NPq < (1ll << 28) && nn <= 1024 && H > 1 && W > 1) {
+    if (!d_need && NPq > 0 && NPq < (1ll << 28) && nn <= 1024 && H > 1 && W > 1) {
         // four ranges per CTA over per-position tables of sum d / sum d^2 (see bf_scan_generic4_kernel)
         FIC_TRY(h->bf_stats.reserve((size_t)NPq * 16 * sizeof(float) + 256));
         float* ds_tab = h->bf_stats.as<float>();
         float* sds_tab = ds_tab + (size_t)8 * NPq;
-        bf_gen_stats_kernel<<<ceil_div(NPq, 128), 128, 0, st>>>(h->bf_boxsum.as<uint16_t>(), W, range, si, sj, npj, (int)NPq, ds_tab, sds_tab);
-        FIC_CHECK_LAUNCH(h, "bf_gen_stats_kernel");
+        long long* isd_tab = h->bf_stats.as<long long>();      // (NumPy semantics: two integer tables in the same buffer)
+        long long* isq_tab = isd_tab + NPq;
+        const uint16_t* P = h->bf_boxsum.as<uint16_t>();
         const size_t smem = (size_t)nn * sizeof(float4) + BF_GEN_G * BF_THREADS * (sizeof(double) + sizeof(unsigned long long));
         const int n_cta = ceil_div(n_ranges, BF_GEN_G);
         int n_chunks = (8 * h->num_sms + n_cta - 1) / n_cta;       // about eight CTAs per SM in all
@@ -888,12 +932,23 @@ int bf_exact_generic_listed(fic_handle* h, const uint8_t* d_img, int H, int W, i
         if (n_chunks < 1) n_chunks = 1;
         FIC_TRY(h->bf_partial.reserve((size_t)n_ranges * n_chunks * sizeof(BestRec) + 64));
         BestRec* partial = h->bf_partial.as<BestRec>();
-        bf_scan_generic4_kernel<<<dim3(n_cta, n_chunks), BF_THREADS, smem, st>>>(d_img, h->bf_boxsum.as<uint16_t>(), H, W, range, si, sj, npi,
-                                                                                  npj, range_begin, n_ranges, ds_tab, sds_tab, partial);
-        FIC_CHECK_LAUNCH(h, "bf_scan_generic4_kernel");
-        bf_gen_finalize_kernel<<<ceil_div(n_ranges, 128), 128, 0, st>>>(d_img, h->bf_boxsum.as<uint16_t>(), W, range, si, sj, npj, (int)NPq,
-                                                                         range_begin, n_ranges, n_chunks, partial, ds_tab, sds_tab, d_idx,
-                                                                         d_so, d_R);
+        if (mode == FIC_BF_MODE_JIT) {
+            bf_gen_stats_kernel<FIC_BF_MODE_JIT><<<ceil_div(NPq, 128), 128, 0, st>>>(P, W, range, si, sj, npj, (int)NPq, ds_tab, sds_tab, isd_tab, isq_tab);
+            FIC_CHECK_LAUNCH(h, "bf_gen_stats_kernel");
+            bf_scan_generic4_kernel<FIC_BF_MODE_JIT><<<dim3(n_cta, n_chunks), BF_THREADS, smem, st>>>(
+                d_img, P, H, W, range, si, sj, npi, npj, range_begin, n_ranges, ds_tab, sds_tab, isd_tab, isq_tab, partial);
+            FIC_CHECK_LAUNCH(h, "bf_scan_generic4_kernel");
+            bf_gen_finalize_kernel<FIC_BF_MODE_JIT><<<ceil_div(n_ranges, 128), 128, 0, st>>>(
+                d_img, P, W, range, si, sj, npj, (int)NPq, range_begin, n_ranges, n_chunks, partial, ds_tab, sds_tab, isd_tab, isq_tab, d_idx, d_so, d_R);
+        } else {
+            bf_gen_stats_kernel<FIC_BF_MODE_NUMPY><<<ceil_div(NPq, 128), 128, 0, st>>>(P, W, range, si, sj, npj, (int)NPq, ds_tab, sds_tab, isd_tab, isq_tab);
+            FIC_CHECK_LAUNCH(h, "bf_gen_stats_kernel");
+            bf_scan_generic4_kernel<FIC_BF_MODE_NUMPY><<<dim3(n_cta, n_chunks), BF_THREADS, smem, st>>>(
+                d_img, P, H, W, range, si, sj, npi, npj, range_begin, n_ranges, ds_tab, sds_tab, isd_tab, isq_tab, partial);
+            FIC_CHECK_LAUNCH(h, "bf_scan_generic4_kernel");
+            bf_gen_finalize_kernel<FIC_BF_MODE_NUMPY><<<ceil_div(n_ranges, 128), 128, 0, st>>>(
+                d_img, P, W, range, si, sj, npj, (int)NPq, range_begin, n_ranges, n_chunks, partial, ds_tab, sds_tab, isd_tab, isq_tab, d_idx, d_so, d_R);
+        }
         FIC_CHECK_LAUNCH(h, "bf_gen_finalize_kernel");
         return FIC_OK;
     }

@@ -112,13 +112,14 @@ def test_range_size_4_on_the_tensor_cores(fic, orc, shape, strides, seed, mode):
 @pytest.mark.parametrize("rs,shape,strides,seed", [(16, (80, 112), (1, 1), 31), (16, (96, 96), (3, 2), 32), (32, (128, 160), (1, 1), 33),
                                                    (2, (40, 36), (1, 1), 34)],
                          ids=["r16_35_ranges", "r16_strides_3_2", "r32", "r2"])
-def test_generic_range_sizes_four_ranges_per_cta(fic, orc, rs, shape, strides, seed):
-    """Range sizes other than 4 and 8 with the jit encoder's arithmetic: four ranges per CTA over per-position tables of
+@pytest.mark.parametrize("mode", [1, 0], ids=["jit", "numpy"])
+def test_generic_range_sizes_four_ranges_per_cta(fic, orc, rs, shape, strides, seed, mode):
+    """Range sizes other than 4 and 8 (both encoders' arithmetic): four ranges per CTA over per-position tables of
     sum d and sum d^2 (bf_exact.cu: bf_scan_generic4_kernel), range counts that are not a multiple of four included."""
     img = synthetic_image(seed, *shape)
     img[:rs, :rs] = 128
-    want = orc.bf_encode(img, range_size=rs, domain_size=2 * rs, strides=strides, mode=1)
-    got = fic.bf_encode(img, range_size=rs, domain_size=2 * rs, strides=strides, mode=1)
+    want = orc.bf_encode(img, range_size=rs, domain_size=2 * rs, strides=strides, mode=mode)
+    got = fic.bf_encode(img, range_size=rs, domain_size=2 * rs, strides=strides, mode=mode)
     for x, y in zip(got, want):
         assert np.array_equal(x, y)
 
